@@ -1,0 +1,128 @@
+"""Oracle (CPU restatement) against the golden vectors frozen from the reference's own JIT functions."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import gogoro_oracle as go
+from oracle import humanoid_oracle as ho
+from oracle import isaac_helpers as ih
+
+# The golden vectors were produced by the same torch CPU operators the oracle uses, so on the
+# machine that made them the match is bit-exact.  Another host CPU may pick a different SIMD
+# path for atan2/sin/cos: allow 4 ulp-ish slack there, integers stay exact.
+RTOL, ATOL = 2e-6, 2e-6
+
+
+def _load(golden_dir, name):
+    z = np.load(os.path.join(golden_dir, name))
+    return {k: torch.from_numpy(z[k]) for k in z.files}
+
+
+def _wrap_close(a, b, atol):
+    d = torch.remainder(a - b + np.pi, 2 * np.pi) - np.pi
+    return bool((d.abs() <= atol).all())
+
+
+def test_humanoid_observations_golden(golden_dir):
+    g = _load(golden_dir, "humanoid_jit.npz")
+    n, d = g["root_states"].shape[0], 21
+    dof_pos = g["dof_state"].view(n, d, 2)[..., 0]
+    dof_vel = g["dof_state"].view(n, d, 2)[..., 1]
+    targets = torch.tensor([1000.0, 0.0, 0.0]).repeat(n, 1)
+    b0 = torch.tensor([1.0, 0.0, 0.0]).repeat(n, 1)
+    b1 = torch.tensor([0.0, 0.0, 1.0]).repeat(n, 1)
+    for inv, key, upk, hk in ((torch.tensor([0.0, 0.0, 0.0, 1.0]).repeat(n, 1), "obs", "up_vec", "heading_vec"),
+                              (g["inv_start_rot2"], "obs2", "up_vec2", "heading_vec2")):
+        obs, pot, prev, up, head = ho.humanoid_observations(
+            g["root_states"], targets, g["potentials"], inv, dof_pos, dof_vel, g["dof_force"],
+            g["dof_limits_lower"], g["dof_limits_upper"], 0.1, g["sensors"], g["actions"], 0.0166, 0.01, 0.25, b0, b1)
+        ang = [7, 8, 9]
+        rest = [c for c in range(110) if c not in ang]
+        torch.testing.assert_close(obs[:, rest], g[key][:, rest], rtol=RTOL, atol=ATOL)
+        assert _wrap_close(obs[:, ang], g[key][:, ang], 4e-6)
+        torch.testing.assert_close(up, g[upk], rtol=RTOL, atol=ATOL)
+        torch.testing.assert_close(head, g[hk], rtol=RTOL, atol=ATOL)
+    torch.testing.assert_close(pot, g["potentials_out"], rtol=RTOL, atol=0)
+    assert torch.equal(prev, g["prev_potentials_out"])
+
+
+def test_humanoid_reward_golden(golden_dir):
+    g = _load(golden_dir, "humanoid_jit.npz")
+    eff = g["motor_efforts"]
+    rew, reset = ho.humanoid_reward(g["obs"], g["reset_buf"], g["progress_buf"], g["actions"], 0.1, 0.5,
+                                    g["potentials_out"], g["prev_potentials_out"], 0.01, 0.05, 0.25,
+                                    float(eff.max()), eff, 0.8, -1.0, 1000.0)
+    assert torch.equal(reset, g["reset_out"]) and reset.dtype == torch.int64
+    assert torch.equal(rew, g["rew"])
+    assert set(rew.tolist()) <= {-1.0, 2.0, float(np.float32(2.0) + np.float32(0.1))}
+    n = g["obs"].shape[0]
+    wm = ho.humanoid_wm_reward(g["obs"].view(2, n // 2, 110), g["actions"].view(2, n // 2, 21), 0.1, 0.5, 0.01, 0.05,
+                               0.25, float(eff.max()), eff, 0.8, -1.0)
+    torch.testing.assert_close(wm, g["wm_reward"], rtol=0, atol=0)
+
+
+def test_humanoid_scripted_matches_eager(golden_dir):
+    g = _load(golden_dir, "humanoid_jit.npz")
+    eff = g["motor_efforts"]
+    args = (g["obs"], g["reset_buf"], g["progress_buf"], g["actions"], 0.1, 0.5, g["potentials_out"],
+            g["prev_potentials_out"], 0.01, 0.05, 0.25, float(eff.max()), eff, 0.8, -1.0, 1000.0)
+    r0, s0 = ho.humanoid_reward(*args)
+    r1, s1 = ho.scripted("humanoid_reward")(*args)
+    assert torch.equal(r0, r1) and torch.equal(s0, s1)
+
+
+def test_gogoro_golden(golden_dir):
+    g = _load(golden_dir, "gogoro_jit.npz")
+    n = g["root_tensor"].shape[0]
+    obs = go.gogoro_observations(g["root_tensor"].clone(), g["desired_yaw"].clone(), g["last_command"].clone())
+    lin = [1, 2, 3, 5]
+    torch.testing.assert_close(obs[:, lin], g["obs"][:, lin], rtol=RTOL, atol=ATOL)
+    assert _wrap_close(obs[:, [0, 4]], g["obs"][:, [0, 4]], 4e-6)
+    rew, reset = go.gogoro_reward(g["obs"].view(n, 1, 6), g["progress_buf"], g["action_history"], 1000)
+    assert torch.equal(reset, g["reset"]) and reset.dtype == torch.int64
+    torch.testing.assert_close(rew, g["rew"], rtol=RTOL, atol=ATOL)
+    sad = go.shortest_angle_distance(g["sad_y1"], g["sad_y2"])
+    torch.testing.assert_close(sad, g["sad"], rtol=RTOL, atol=ATOL)
+    assert float(sad.min()) >= -np.pi - 1e-6 and float(sad.max()) <= np.pi + 1e-6
+
+
+def test_helpers_against_poselib(golden_dir):
+    """isaac_helpers (restated, unpinned upstream) vs the reference's in-tree rotation3d.py, fp64."""
+    g = _load(golden_dir, "poselib_quat.npz")
+    a, b, v = g["a"], g["b"], g["v"]
+    torch.testing.assert_close(ih.quat_mul(a, b), g["quat_mul"], rtol=0, atol=1e-14)
+    torch.testing.assert_close(ih.quat_conjugate(a), g["quat_conjugate"], rtol=0, atol=0)
+    torch.testing.assert_close(ih.quat_rotate(a, v), g["quat_rotate"], rtol=0, atol=1e-13)
+    torch.testing.assert_close(ih.quat_apply(a, v), g["quat_rotate"], rtol=0, atol=1e-13)
+    torch.testing.assert_close(ih.quat_rotate_inverse(a, v), g["quat_rotate_conj"], rtol=0, atol=1e-13)
+
+
+def test_helper_properties():
+    g = torch.Generator().manual_seed(3)
+    q = torch.randn((512, 4), generator=g); q = q / q.norm(dim=-1, keepdim=True)
+    v = torch.randn((512, 3), generator=g)
+    back = ih.quat_rotate_inverse(q, ih.quat_rotate(q, v))
+    torch.testing.assert_close(back, v, rtol=1e-5, atol=1e-5)
+    roll, pitch, yaw = ih.get_euler_xyz(q)
+    for ang in (roll, pitch, yaw):
+        assert float(ang.min()) >= 0.0 and float(ang.max()) <= float(np.float32(2 * np.pi))
+    # Euler -> quat (reference's in-file euler_to_quaternion, gogoro_new.py:496-502) -> Euler round trip
+    r = (torch.rand(512, generator=g) * 2 - 1) * 3.0
+    p = (torch.rand(512, generator=g) * 2 - 1) * 1.4
+    y = (torch.rand(512, generator=g) * 2 - 1) * 3.0
+    r2, p2, y2 = ih.get_euler_xyz(go.euler_to_quaternion(r, p, y))
+    for x, x2 in ((r, r2), (p, p2), (y, y2)):
+        dd = torch.remainder(x2 - x + np.pi, 2 * np.pi) - np.pi
+        assert float(dd.abs().max()) < 5e-5
+    lo = -torch.rand(21, generator=g) - 0.5
+    hi = torch.rand(21, generator=g) + 0.5
+    # (2*lo - hi) - lo rounds twice: end point -1 holds to 1 ulp, +1 holds exactly
+    torch.testing.assert_close(ih.unscale(lo, lo, hi), -torch.ones(21), rtol=0, atol=2.4e-7)
+    assert torch.equal(ih.unscale(hi, lo, hi), torch.ones(21))
+    x = torch.linspace(-10, 10, 1001)
+    na = ih.normalize_angle(x)
+    assert float(na.min()) >= -np.pi - 1e-6 and float(na.max()) <= np.pi + 1e-6
+    assert ih.get_axis_params(1., 2) == [0.0, 0.0, 1.0]
+    assert ih.get_axis_params(1.34, 2) == [0.0, 0.0, 1.34]

@@ -1,0 +1,58 @@
+"""Oracle vs the reference's own TorchScript functions, lifted live from /root/reference.
+
+Runs only where the reference tree exists (the build container); on the GPU box the
+same check is carried by the golden fixtures (test_oracle_golden.py).  Same torch
+operators on the same CPU => bit-exact equality is required.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import gogoro_oracle as go
+from oracle import humanoid_oracle as ho
+from oracle import lift_reference as L
+from thormang_isaacgym_b200 import synthetic as syn
+
+pytestmark = pytest.mark.skipif(not L.reference_available(), reason="/root/reference not present")
+
+
+@pytest.mark.parametrize("n", [1, 31, 32, 33, 4096])
+def test_humanoid_bit_exact(n):
+    ref = L.humanoid()
+    asset = syn.humanoid_asset()
+    st = syn.humanoid_state(n, seed=1234 + n, asset=asset)
+    d = 21
+    dof_pos = st["dof_state"].view(n, d, 2)[..., 0]
+    dof_vel = st["dof_state"].view(n, d, 2)[..., 1]
+    targets = torch.tensor([1000.0, 0.0, 0.0]).repeat(n, 1)
+    inv = torch.tensor([0.0, 0.0, 0.0, 1.0]).repeat(n, 1)
+    b0 = torch.tensor([1.0, 0.0, 0.0]).repeat(n, 1)
+    b1 = torch.tensor([0.0, 0.0, 1.0]).repeat(n, 1)
+    lo, hi, eff = asset["dof_limits_lower"], asset["dof_limits_upper"], asset["motor_efforts"]
+    want = ref.compute_humanoid_observations(torch.zeros(n, 110), st["root_states"], targets, st["potentials"], inv,
+                                             dof_pos, dof_vel, st["dof_force"], lo, hi, 0.1, st["sensors"],
+                                             st["actions"], 0.0166, 0.01, 0.25, b0, b1)
+    got = ho.humanoid_observations(st["root_states"], targets, st["potentials"], inv, dof_pos, dof_vel,
+                                   st["dof_force"], lo, hi, 0.1, st["sensors"], st["actions"], 0.0166, 0.01, 0.25,
+                                   b0, b1)
+    for w, g_ in zip(want, got):
+        assert torch.equal(w, g_)
+    rw = ref.compute_humanoid_reward(want[0], st["reset_buf"], st["progress_buf"], st["actions"], 0.1, 0.5, want[1],
+                                     want[2], 0.01, 0.05, 0.25, float(eff.max()), eff, 0.8, -1.0, 1000.0)
+    rg = ho.humanoid_reward(got[0], st["reset_buf"], st["progress_buf"], st["actions"], 0.1, 0.5, got[1], got[2],
+                            0.01, 0.05, 0.25, float(eff.max()), eff, 0.8, -1.0, 1000.0)
+    assert torch.equal(rw[0], rg[0]) and torch.equal(rw[1], rg[1])
+
+
+@pytest.mark.parametrize("n", [1, 33, 4096])
+def test_gogoro_bit_exact(n):
+    ref = L.gogoro()
+    st = syn.gogoro_state(n, seed=77 + n)
+    want = ref.compute_gogoro_observations(st["root_tensor"].clone(), st["yaw_command"].clone(),
+                                           st["curent_command"].clone())
+    got = go.gogoro_observations(st["root_tensor"].clone(), st["yaw_command"].clone(), st["curent_command"].clone())
+    assert torch.equal(want, got)
+    rw = ref.compute_gogoro_reward(curent_obs=want.view(n, 1, 6), progress_buf=st["progress_buf"],
+                                   action_history=st["action_history"], max_episode_length=torch.tensor(1000))
+    rg = go.gogoro_reward(got.view(n, 1, 6), st["progress_buf"], st["action_history"], 1000)
+    assert torch.equal(rw[0], rg[0]) and torch.equal(rw[1], rg[1])

@@ -1,0 +1,140 @@
+"""Seeded synthetic env states for tests and benchmarks.
+
+There is no PhysX here, so "state after a physics step" is drawn from the
+distributions listed in SURVEY.md 8(d): they put about a third of the humanoids
+below the termination height, ~1 % of the envs into reset, a few joints beyond
+98 % of their range, ~5 % of the scooters past the tilt limit, and force the
+progress counters onto the episode-end / command-resample boundaries.
+
+Everything is generated on the CPU with an explicit ``torch.Generator`` so that
+rank r of a sharded run (seed 1234 + r) and the CPU oracle see the same numbers,
+then moved to ``device``.
+"""
+import math
+from typing import Dict
+
+import torch
+
+HUMANOID_DOF = 21
+HUMANOID_SENSOR = 12
+GOGORO_DOF = 39
+GOGORO_HISTORY = 5
+
+
+def _gen(seed: int) -> torch.Generator:
+    g = torch.Generator(device="cpu")
+    g.manual_seed(seed)
+    return g
+
+
+def _u(g, shape, lo, hi):
+    return lo + (hi - lo) * torch.rand(shape, generator=g, dtype=torch.float32)
+
+
+def _n(g, shape, std=1.0):
+    return std * torch.randn(shape, generator=g, dtype=torch.float32)
+
+
+def humanoid_asset(seed: int = 7, num_dof: int = HUMANOID_DOF) -> Dict[str, torch.Tensor]:
+    """Per-task constants the reference reads from the MJCF asset (humanoid.py:160-171,205-215)."""
+    g = _gen(seed)
+    lower = -_u(g, (num_dof,), 0.5, 1.5)
+    upper = _u(g, (num_dof,), 0.5, 1.5)
+    efforts = _u(g, (num_dof,), 22.5, 135.0)
+    return {"dof_limits_lower": lower, "dof_limits_upper": upper, "motor_efforts": efforts}
+
+
+def humanoid_state(n: int, seed: int = 1234, asset: Dict[str, torch.Tensor] = None, dt: float = 0.0166,
+                   device="cpu", reset_frac: float = 0.01) -> Dict[str, torch.Tensor]:
+    """One post-physics snapshot for ``n`` humanoids (config 1/2/4 of BASELINE.json)."""
+    asset = asset if asset is not None else humanoid_asset()
+    lo, hi = asset["dof_limits_lower"], asset["dof_limits_upper"]
+    d = lo.shape[0]
+    g = _gen(seed)
+    root = torch.empty((n, 13), dtype=torch.float32)
+    root[:, 0:2] = _u(g, (n, 2), -5.0, 5.0)
+    root[:, 2] = _u(g, (n,), 0.3, 1.8)
+    q = _n(g, (n, 4))
+    root[:, 3:7] = q / q.norm(dim=-1, keepdim=True).clamp(min=1e-6)
+    root[:, 7:10] = _n(g, (n, 3), 1.0)
+    root[:, 10:13] = _n(g, (n, 3), 2.0)
+    span = hi - lo
+    dof_pos = (lo - 0.05 * span) + torch.rand((n, d), generator=g) * (1.1 * span)
+    dof_vel = _n(g, (n, d), 5.0)
+    dof_state = torch.stack((dof_pos, dof_vel), dim=-1).reshape(n * d, 2).contiguous()
+    dof_force = _n(g, (n, d), 50.0)
+    sensors = _n(g, (n, HUMANOID_SENSOR), 100.0)
+    actions = _u(g, (n, d), -1.0, 1.0)
+    progress = torch.randint(0, 1000, (n,), generator=g, dtype=torch.int64)
+    forced = torch.rand((n,), generator=g) < 0.01
+    progress = torch.where(forced, 998 + (torch.arange(n) % 2), progress)
+    reset = (torch.rand((n,), generator=g) < reset_frac).to(torch.int64)
+    potentials = -_u(g, (n,), 900.0, 1100.0) / dt
+    out = dict(root_states=root, dof_state=dof_state, dof_force=dof_force, sensors=sensors, actions=actions,
+               progress_buf=progress, reset_buf=reset, potentials=potentials)
+    return {k: v.to(device) for k, v in out.items()}
+
+
+def humanoid_reset_noise(n: int, seed: int, num_dof: int = HUMANOID_DOF, device="cpu"):
+    """U(0,1) draws for up to ``n`` resets: the [K, D] x 2 that humanoid.py:258-259 consume."""
+    g = _gen(seed + 77)
+    return (torch.rand((n, num_dof), generator=g).to(device), torch.rand((n, num_dof), generator=g).to(device))
+
+
+def _euler_to_quat(roll, pitch, yaw):
+    sr, cr = torch.sin(roll / 2), torch.cos(roll / 2)
+    sp, cp = torch.sin(pitch / 2), torch.cos(pitch / 2)
+    sy, cy = torch.sin(yaw / 2), torch.cos(yaw / 2)
+    return torch.stack((sr * cp * cy - cr * sp * sy, cr * sp * cy + sr * cp * sy,
+                        cr * cp * sy - sr * sp * cy, cr * cp * cy + sr * sp * sy), dim=-1)
+
+
+def gogoro_state(n: int, seed: int = 1234, device="cpu", num_dof: int = GOGORO_DOF) -> Dict[str, torch.Tensor]:
+    """One post-physics snapshot for ``n`` scooters (config 3 of BASELINE.json)."""
+    g = _gen(seed)
+    roll = _n(g, (n,), 0.15)
+    pitch = _n(g, (n,), 0.05)
+    yaw = _u(g, (n,), -math.pi, math.pi)
+    root = torch.empty((n, 13), dtype=torch.float32)
+    root[:, 0:2] = _u(g, (n, 2), -50.0, 50.0)
+    root[:, 2] = _u(g, (n,), 0.0, 0.1)
+    root[:, 3:7] = _euler_to_quat(roll, pitch, yaw)
+    speed = _u(g, (n,), 4.0, 13.0)
+    root[:, 7] = torch.cos(yaw) * speed
+    root[:, 8] = torch.sin(yaw) * speed
+    root[:, 9] = 0.0
+    root[:, 7:10] += _n(g, (n, 3), 0.2)
+    root[:, 10:13] = _n(g, (n, 3), 0.5)
+    dof_state = _n(g, (n * num_dof, 2), 0.3)
+    progress = torch.randint(0, 1000, (n,), generator=g, dtype=torch.int64)
+    forced = torch.rand((n,), generator=g) < 0.02
+    ladder = torch.tensor([298, 299, 300, 997, 998, 999], dtype=torch.int64)
+    progress = torch.where(forced, ladder[torch.arange(n) % 6], progress)
+    out = dict(
+        root_tensor=root, state_dof=dof_state, progress_buf=progress,
+        reset_buf=(torch.rand((n,), generator=g) < 0.01).to(torch.int64),
+        yaw_command=_u(g, (n,), -math.pi, math.pi),
+        curent_command=_u(g, (n,), -0.5, 0.5),
+        curent_speed=_u(g, (n,), 4.0, 13.0),
+        steer_offsets=_n(g, (n,), 0.01),
+        imu_offsets=_n(g, (n,), 0.05),
+        curent_speed_offset=_u(g, (n,), -0.5, 0.5),
+        action_history=_u(g, (n, GOGORO_HISTORY), -1.0, 1.0),
+        actions=_u(g, (n, 1), -1.5, 1.5),
+        thormang_pose=_u(g, (1, num_dof), -1.5, 1.5).repeat(n, 1),
+    )
+    return {k: v.to(device) for k, v in out.items()}
+
+
+def gogoro_noise(n: int, seed: int, device="cpu") -> Dict[str, torch.Tensor]:
+    """Unit draws for one Gogoro step: N(0,1) steer [N], N(0,1) sensors [N,5], reset draws [N,10]
+    (cols 0,2,3,4 uniform, others normal), U(0,1) speed [N] and yaw [N]."""
+    g = _gen(seed + 991)
+    reset_unit = torch.randn((n, 10), generator=g)
+    uni = torch.rand((n, 10), generator=g)
+    for col in (0, 2, 3, 4):
+        reset_unit[:, col] = uni[:, col]
+    out = dict(steer_unit=torch.randn((n,), generator=g), sensor_unit=torch.randn((n, 5), generator=g),
+               reset_unit=reset_unit, speed_unit=torch.rand((n,), generator=g),
+               yaw_unit=torch.rand((n,), generator=g))
+    return {k: v.to(device) for k, v in out.items()}
