@@ -1,0 +1,288 @@
+/*
+ * thormang_b200.h -- C ABI of the B200-native env-step hot path.
+ *
+ * The reference (Yougo-robotics/thormang_isaacgym) has NO FFI/plugin layer: the
+ * boundary it offers is the Python VecTask subclass contract
+ * (isaacgymenvs/tasks/base/vec_task.py:254-277,313-406).  This header is the
+ * C-ABI a maintainer binds underneath that contract (ctypes stub shown in
+ * INTEGRATION.md); every entry point cites the reference method it replaces.
+ *
+ * Conventions
+ *  - plain C, no torch / CUDA types in signatures; `stream` is a cudaStream_t
+ *    passed as void* (NULL = legacy default stream).
+ *  - every pointer in the *Buffers structs is a DEVICE pointer borrowed from the
+ *    caller (torch owns the memory); the library never frees them and only
+ *    dereferences them inside a call that was given them or after tk_*_bind.
+ *  - all entry points are asynchronous on `stream`, never synchronise the host,
+ *    never allocate after tk_*_create, never throw, never exit.
+ *  - return value: 0 = ok, < 0 = TkStatus error; tk_last_error() has the text.
+ *  - quaternions are xyzw; reset_buf / progress_buf are int64 like
+ *    vec_task.py:269-276; timeout_buf is 1 byte per env (torch.bool), the dtype
+ *    vec_task.py:345 rebinds it to.
+ *  - state tensors keep Isaac Gym's AoS layout: root_states [N,13] fp32,
+ *    dof_state [N*D,2] fp32 (pos,vel interleaved), dof_force [N,D],
+ *    force sensors [N,12]; rows contiguous.
+ *  - a handle is bound to one device and is not thread-safe.
+ */
+#ifndef THORMANG_B200_H
+#define THORMANG_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TK_ABI_VERSION 1
+#define TK_MAX_DOF 64
+#define TK_STATS 8
+
+typedef enum TkStatus {
+    TK_OK = 0,
+    TK_ERR_INVALID = -1,   /* bad argument / params */
+    TK_ERR_CUDA = -2,      /* a CUDA runtime call failed */
+    TK_ERR_UNBOUND = -3,   /* a required buffer was not bound */
+    TK_ERR_ALIGN = -4      /* a pointer is not 4-byte (fp32) / 8-byte (int64) aligned */
+} TkStatus;
+
+/* How the random draws of reset_idx reach the kernel (humanoid.py:258-259,
+ * gogoro_new.py:474-492,554-559 call torch.rand/randn on the spot). */
+typedef enum TkNoiseMode {
+    TK_NOISE_NONE = 0,     /* no reset can happen (pointers ignored; a set reset bit resets with u = 0.5) */
+    TK_NOISE_COMPACT = 1,  /* row k belongs to the k-th env (ascending id) being reset: the reference's order */
+    TK_NOISE_DENSE = 2,    /* row n belongs to env n */
+    TK_NOISE_PHILOX = 3    /* drawn in-kernel: Philox4x32-10 keyed by (seed, step, global env id) */
+} TkNoiseMode;
+
+const char* tk_last_error(void);
+int tk_abi_version(void);
+/* sm count / compute capability of `device` (for grid sizing reports) */
+int tk_device_info(int device, int* sm_count, int* cc_major, int* cc_minor);
+
+/* ------------------------------------------------------------------------------------------
+ * Humanoid  (isaacgymenvs/tasks/humanoid.py, cfg/task/Humanoid.yaml)
+ * ------------------------------------------------------------------------------------------ */
+
+typedef struct TkHumanoidParams {
+    int32_t device;
+    int32_t num_envs;
+    int32_t num_dof;                 /* 21 (humanoid.py:68) */
+    int32_t reserved0;
+    float dt;                        /* cfg["sim"]["dt"], humanoid.py:115 */
+    float dof_vel_scale;             /* humanoid.py:48 */
+    float angular_velocity_scale;    /* humanoid.py:49 */
+    float contact_force_scale;       /* humanoid.py:50 */
+    float power_scale;               /* humanoid.py:51 */
+    float heading_weight;            /* humanoid.py:52 */
+    float up_weight;                 /* humanoid.py:53 */
+    float actions_cost_scale;        /* humanoid.py:54 */
+    float energy_cost_scale;         /* humanoid.py:55 */
+    float joints_at_limit_cost_scale;/* humanoid.py:56 */
+    float death_cost;                /* humanoid.py:57 */
+    float termination_height;        /* humanoid.py:58 */
+    float max_episode_length;        /* humanoid.py:65 (passed to the JIT fn as float) */
+    float clip_actions;              /* vec_task.py:108 */
+    float max_motor_effort;          /* humanoid.py:170 */
+    float reserved1;
+    /* rows of the replicated [N,*] tensors of humanoid.py:106-113 (identical for every env) */
+    float targets[3];
+    float inv_start_rot[4];
+    float basis_vec0[3];
+    float basis_vec1[3];
+    float reserved2[3];
+    float dof_limits_lower[TK_MAX_DOF];  /* humanoid.py:205-215 */
+    float dof_limits_upper[TK_MAX_DOF];
+    float motor_efforts[TK_MAX_DOF];     /* humanoid.py:160-171 */
+} TkHumanoidParams;
+
+typedef struct TkHumanoidBuffers {
+    /* simulator-owned, aliased (humanoid.py:78-98) */
+    float* root_states;              /* [N,13] */
+    float* dof_state;                /* [N*D,2] */
+    const float* dof_force;          /* [N,D] */
+    const float* sensors;            /* [N,12] */
+    /* task-owned (humanoid.py:92-117, vec_task.py:263-277) */
+    float* actions;                  /* [N,D]  self.actions */
+    float* obs_buf;                  /* [N,110] */
+    float* rew_buf;                  /* [N] */
+    int64_t* reset_buf;              /* [N] */
+    int64_t* progress_buf;           /* [N] */
+    uint8_t* timeout_buf;            /* [N] bool, may be NULL */
+    int64_t* randomize_buf;          /* [N], may be NULL (only domain randomisation reads it) */
+    float* potentials;               /* [N] */
+    float* prev_potentials;          /* [N] */
+    float* up_vec;                   /* [N,3], may be NULL (debug viz only, humanoid.py:298-316) */
+    float* heading_vec;              /* [N,3], may be NULL */
+    const float* initial_root_states;/* [N,13] */
+    const float* initial_dof_pos;    /* [N,D] */
+    float* episode_return;           /* [N], may be NULL: running return for the episode statistics */
+} TkHumanoidBuffers;
+
+typedef struct TkResetNoise {
+    int32_t mode;                    /* TkNoiseMode */
+    int32_t reserved;
+    const float* unit_a;             /* Humanoid: U(0,1) [rows,D] for positions (humanoid.py:258)   | Gogoro: [rows,10] see below */
+    const float* unit_b;             /* Humanoid: U(0,1) [rows,D] for velocities (humanoid.py:259)  | Gogoro: unused */
+    int64_t rows;                    /* rows available in unit_a / unit_b */
+    uint64_t seed;                   /* PHILOX */
+    uint64_t step;                   /* PHILOX: step counter */
+    int64_t env_id_offset;           /* PHILOX: global id of local env 0 (range-sharded multi-GPU runs) */
+} TkResetNoise;
+
+typedef struct TkHumanoid TkHumanoid;
+
+int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out);
+int tk_humanoid_destroy(TkHumanoid* h);
+int tk_humanoid_bind(TkHumanoid* h, const TkHumanoidBuffers* buffers);
+
+/* Humanoid.pre_physics_step (humanoid.py:281-285) fused with the action clamp of VecTask.step
+ * (vec_task.py:327, applied when clip != 0): bound actions[N,D] = clamp(actions_in);
+ * forces_out[N,D] = actions * motor_efforts * power_scale (the tensor handed to set_dof_actuation_force_tensor). */
+int tk_humanoid_pre_physics(TkHumanoid* h, const float* actions_in, float* forces_out, int32_t clip, void* stream);
+
+/* Humanoid.compute_observations (humanoid.py:239-251) = compute_humanoid_observations (humanoid.py:379-417):
+ * writes obs_buf, potentials, prev_potentials, up_vec, heading_vec. */
+int tk_humanoid_compute_observations(TkHumanoid* h, void* stream);
+
+/* Humanoid.compute_reward (humanoid.py:219-237) = compute_humanoid_reward (humanoid.py:323-376):
+ * reads obs_buf, reset_buf, progress_buf; writes rew_buf, reset_buf. */
+int tk_humanoid_compute_reward(TkHumanoid* h, void* stream);
+
+/* Humanoid.reset_idx (humanoid.py:253-279): env_ids[k] int64 device pointer, unit_pos/unit_vel U(0,1) [k,D]. */
+int tk_humanoid_reset_idx(TkHumanoid* h, const int64_t* env_ids, int32_t k, const float* unit_pos,
+                          const float* unit_vel, void* stream);
+
+/* Humanoid.post_physics_step (humanoid.py:287-296) + the timeout line of VecTask.step (vec_task.py:345),
+ * ONE fused kernel: progress++/randomize++, reset of the envs whose reset_buf != 0 (no host sync, no nonzero()),
+ * observations, reward, reset mask, timeout mask, per-CTA episode-statistics partials. */
+int tk_humanoid_post_physics(TkHumanoid* h, const TkResetNoise* noise, void* stream);
+
+/* All reward terms of humanoid.py:344-363 incl. the ones the fork leaves out of the total:
+ * terms[N,7] = heading_reward, up_reward, actions_cost, dof_at_limit_cost, electricity_cost, alive, progress. */
+int tk_humanoid_reward_terms(TkHumanoid* h, float* terms, void* stream);
+
+/* World-model style reward, second compute_reward of humanoid.py:425-472 over obs[M,110] (M = B*T). */
+int tk_humanoid_wm_reward(TkHumanoid* h, const float* obs, int64_t m, float* reward_out, void* stream);
+
+/* Materialise the U(0,1) draws TK_NOISE_PHILOX uses for (seed, step): unit_pos/unit_vel [N,D] (parity checks). */
+int tk_humanoid_philox_noise(TkHumanoid* h, uint64_t seed, uint64_t step, int64_t env_id_offset,
+                             float* unit_pos, float* unit_vel, void* stream);
+
+/* Episode statistics.  Every tk_humanoid_post_physics adds its per-CTA partial sums into a handle-owned
+ * [grid, TK_STATS] fp64 array (each CTA owns its row: no atomics, deterministic).  This call sums the rows in a
+ * fixed order into stats_out[TK_STATS] (device, fp64) -- sum reward, #reset, #timeout, sum episode_return of reset
+ * envs, sum episode length of reset envs, sum up_proj, sum heading_proj, env-steps -- and zeroes the partials, so the
+ * result covers the steps since the previous call.  accumulate != 0 adds to stats_out instead of overwriting.
+ * This vector is the payload of the NCCL all-reduce in multi-GPU runs. */
+int tk_humanoid_stats(TkHumanoid* h, double* stats_out, int32_t accumulate, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Gogoro scooter, registered variant  (isaacgymenvs/tasks/gogoro_new.py, cfg/task/Gogoro.yaml)
+ * ------------------------------------------------------------------------------------------ */
+
+typedef struct TkGogoroParams {
+    int32_t device;
+    int32_t num_envs;
+    int32_t num_dof;                 /* 39 for scooter_V13.urdf */
+    int32_t steering_joint;          /* dof_name_to_id['steering_joint'], gogoro_new.py:363 */
+    int32_t rear_wheel_joint;        /* dof_name_to_id['rear_wheel_joint'], gogoro_new.py:367 */
+    int32_t max_episode_length;      /* cfg["env"]["max_steps"], gogoro_new.py:39 */
+    int32_t speed_freq_update;       /* gogoro_new.py:56 */
+    int32_t yaw_freq_update;         /* gogoro_new.py:57 */
+    float max_steering;              /* gogoro_new.py:86 */
+    float max_steering_change;       /* gogoro_new.py:87 */
+    /* [mean,std] or [lo,hi] pairs of cfg["noises"], gogoro_new.py:46-68.  Kept in double: the reference forms
+     * hi - lo in Python doubles before torch rounds the scalar to fp32 (get_randoms, gogoro_new.py:466-467). */
+    double imu_filter_noise[2];
+    double imu_noise[2];
+    double speed_sensor_noise[2];
+    double steering_action_noise[2];
+    double speed_range[2];
+    double seat_offset_x_range[2];
+    double seat_offset_y_range[2];
+    double seat_offset_z_range[2];
+    double seat_offset_xr_range[2];
+    double steering_offset[2];
+    double speed_sensor_offset[2];
+} TkGogoroParams;
+
+typedef struct TkGogoroBuffers {
+    /* simulator-owned, aliased (gogoro_new.py:125-138) */
+    float* root_tensor;              /* [N,13] */
+    float* state_dof;                /* [N*D,2] */
+    /* task-owned */
+    float* obs_buf;                  /* [N,6]  (noisy observations, gogoro_new.py:462) */
+    float* buffer_obs;               /* [N,1,6] (clean observations, gogoro_new.py:105,436-437) */
+    float* rew_buf;                  /* [N] */
+    int64_t* reset_buf;              /* [N] */
+    int64_t* progress_buf;           /* [N] */
+    uint8_t* timeout_buf;            /* [N] bool, may be NULL */
+    float* yaw_command;              /* [N] gogoro_new.py:81 */
+    float* curent_command;           /* [N] gogoro_new.py:91 */
+    float* curent_speed;             /* [N] gogoro_new.py:90 */
+    float* steer_offsets;            /* [N] gogoro_new.py:71 */
+    float* imu_offsets;              /* [N] gogoro_new.py:70 */
+    float* curent_speed_offset;      /* [N] gogoro_new.py:72 */
+    float* action_history;           /* [N,5] gogoro_new.py:92 */
+    float* config_vector;            /* [N,5] gogoro_new.py:78 */
+    const float* thormang_pose;      /* [N,D] gogoro_new.py:234,262 */
+    const float* root_reset_tensor;  /* [N,13] gogoro_new.py:144-145 */
+    float* dof_pos_command;          /* [N,D] persistent position-target tensor (gogoro_new.py:360-364) */
+    float* dof_speed_command;        /* [N,D] persistent velocity-target tensor (gogoro_new.py:366-369) */
+    float* episode_return;           /* [N], may be NULL */
+} TkGogoroBuffers;
+
+/* Unit draws of one Gogoro post_physics_step.  sensor_unit N(0,1) [N,5] in the order the reference draws them
+ * (gogoro_new.py:451-460).  reset rows [rows,10] in TkResetNoise.unit_a, columns in draw order: 0 U speed (:479),
+ * 1 N steer offset (:481, dead), 2 U speed-sensor offset (:482), 3 U initial_target (:486), 4 U initial_rot (:487),
+ * 5..9 N config_vector[0..4] (:554-559).  speed_unit U(0,1): COMPACT = k-th env whose progress hits
+ * speed_freq_update (:384-386), DENSE = by env id; yaw_unit U(0,1) [N] by env id (:387 draws n_envs values). */
+typedef struct TkGogoroNoise {
+    TkResetNoise reset;
+    const float* sensor_unit;        /* [N,5]; NULL with PHILOX */
+    const float* speed_unit;         /* NULL with PHILOX */
+    const float* yaw_unit;           /* [N]; NULL with PHILOX */
+} TkGogoroNoise;
+
+typedef struct TkGogoro TkGogoro;
+
+int tk_gogoro_create(const TkGogoroParams* params, TkGogoro** out);
+int tk_gogoro_destroy(TkGogoro* h);
+int tk_gogoro_bind(TkGogoro* h, const TkGogoroBuffers* buffers);
+
+/* Gogoro.pre_physics_step (gogoro_new.py:347-369): history shift, incremental steer, clamps, the two live
+ * columns of the position / velocity target tensors.  steer_unit N(0,1) [N] (NULL = Philox with seed/step).
+ * zero_fill != 0 also rewrites the 2 x [N,D] targets with zeros first, like the fresh torch.zeros of :360,366. */
+int tk_gogoro_pre_physics(TkGogoro* h, const float* actions, const float* steer_unit, uint64_t seed, uint64_t step,
+                          int64_t env_id_offset, int32_t zero_fill, void* stream);
+
+/* compute_gogoro_observations (gogoro_new.py:692-723) into obs_out[N,6] (clean). */
+int tk_gogoro_compute_observations(TkGogoro* h, float* obs_out, void* stream);
+
+/* compute_gogoro_reward (gogoro_new.py:645-684) on cur_obs[N,6]: writes rew_buf, reset_buf. */
+int tk_gogoro_compute_reward(TkGogoro* h, const float* cur_obs, void* stream);
+
+/* Gogoro.compute_obs_rwd (gogoro_new.py:424-462): observations, history (B = 1), reward, reset, sensor-noise model. */
+int tk_gogoro_compute_obs_rwd(TkGogoro* h, const float* sensor_unit, uint64_t seed, uint64_t step,
+                              int64_t env_id_offset, void* stream);
+
+/* Gogoro.reset_idx (gogoro_new.py:505-590 with randomize :474-482 and generate_spawn_r :485-492), PhysX property
+ * calls left out.  env_ids[k] int64, unit [k,10]. */
+int tk_gogoro_reset_idx(TkGogoro* h, const int64_t* env_ids, int32_t k, const float* unit, void* stream);
+
+/* Gogoro.post_physics_step (gogoro_new.py:373-389) + vec_task.py:345, ONE fused kernel. */
+int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream);
+
+/* stats: sum reward, #reset, #timeout, sum episode_return of reset envs, sum episode length of reset envs,
+ * sum |tilt|, sum |yaw error|, N */
+int tk_gogoro_stats(TkGogoro* h, double* stats_out, int32_t accumulate, void* stream);
+
+/* Materialise the PHILOX draws of one step for parity checks: steer_unit [N], sensor_unit [N,5], reset_unit [N,10],
+ * speed_unit [N], yaw_unit [N] (any pointer may be NULL). */
+int tk_gogoro_philox_noise(TkGogoro* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* steer_unit,
+                           float* sensor_unit, float* reset_unit, float* speed_unit, float* yaw_unit, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* THORMANG_B200_H */

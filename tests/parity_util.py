@@ -1,0 +1,116 @@
+"""Shared helpers of the parity tests: build the CUDA task and the CPU oracle from one synthetic state."""
+import math
+
+import numpy as np
+import torch
+
+from oracle import gogoro_oracle as go
+from oracle import humanoid_oracle as ho
+from thormang_isaacgym_b200 import config as tcfg
+from thormang_isaacgym_b200 import synthetic as syn
+
+# Parity tolerances (north_star: fp32 observations and rewards within 1e-5 relative).
+# rtol = 1e-5 everywhere.  atol covers values near zero, where "relative" has no meaning:
+#   * 2e-6 on ordinary columns (about 16 ulp at magnitude 1: sums with cancellation such as R^-1 v);
+#   * angle columns are compared modulo 2*pi with atol 5e-6: the reference itself quantises angles to
+#     ulp(2*pi) = 4.8e-7 through `% (2*pi)` (get_euler_xyz), and a 1-ulp libm difference in atan2 next to the
+#     cut flips the representative by 2*pi (SURVEY.md section 7 "fp32 transcendental parity").
+RTOL = 1e-5
+ATOL = 2e-6
+ANGLE_ATOL = 5e-6
+
+
+def close(got, want, rtol=RTOL, atol=ATOL, what=""):
+    got, want = got.detach().cpu().float(), want.detach().cpu().float()
+    assert got.shape == want.shape, f"{what}: shape {tuple(got.shape)} vs {tuple(want.shape)}"
+    err = (got - want).abs()
+    tol = atol + rtol * want.abs()
+    bad = err > tol
+    if bool(bad.any()):
+        idx = torch.nonzero(bad)[0].tolist()
+        raise AssertionError(f"{what}: {int(bad.sum())} / {bad.numel()} outside tolerance; first at {idx}: "
+                             f"got {got[tuple(idx)].item():.9g} want {want[tuple(idx)].item():.9g}; max err {err.max().item():.3g}")
+
+
+def angle_close(got, want, atol=ANGLE_ATOL, what=""):
+    got, want = got.detach().cpu().double(), want.detach().cpu().double()
+    d = torch.remainder(got - want + math.pi, 2 * math.pi) - math.pi
+    assert float(d.abs().max()) <= atol, f"{what}: max angular error {float(d.abs().max()):.3g}"
+
+
+def exact(got, want, what=""):
+    got, want = got.detach().cpu(), want.detach().cpu()
+    assert got.shape == want.shape and got.dtype == want.dtype, f"{what}: {got.dtype}{tuple(got.shape)} vs {want.dtype}{tuple(want.shape)}"
+    if not torch.equal(got, want):
+        bad = torch.nonzero(got != want)
+        raise AssertionError(f"{what}: {bad.shape[0]} mismatches, first at {bad[0].tolist()}: "
+                             f"{got[tuple(bad[0].tolist())].item()} vs {want[tuple(bad[0].tolist())].item()}")
+
+
+HUMANOID_ANGLE_COLS = [7, 8, 9]
+
+
+def humanoid_obs_close(got, want, what="obs"):
+    rest = [c for c in range(got.shape[1]) if c not in HUMANOID_ANGLE_COLS]
+    close(got[:, rest], want[:, rest], what=what)
+    angle_close(got[:, HUMANOID_ANGLE_COLS], want[:, HUMANOID_ANGLE_COLS], what=what + "[angles]")
+
+
+def gogoro_obs_close(got, want, what="obs", noisy=False):
+    lin = [1, 2, 5] if noisy else [1, 2, 3, 5]
+    close(got[:, lin], want[:, lin], what=what)
+    angle_close(got[:, [0, 4]], want[:, [0, 4]], what=what + "[angles]")
+    if noisy:   # channel 3 = round(delta_yaw): exact unless delta_yaw sits within the angle tolerance of k + 0.5
+        g, w = got[:, 3].cpu(), want[:, 3].cpu()
+        assert float((g - w).abs().max()) <= 1.0 and float((g != w).float().mean()) < 1e-3, what + "[round]"
+
+
+# ------------------------------------------------------------------------------------------------
+def make_humanoid_pair(n, seed=1234, device="cuda:0", state=None, asset=None, start_rotation=None, **env_over):
+    """(cuda task, cpu oracle, state) initialised from the same synthetic snapshot."""
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.humanoid import Humanoid
+    asset = asset or syn.humanoid_asset()
+    state = state or syn.humanoid_state(n, seed=seed, asset=asset)
+    cfg = tcfg.humanoid_cfg(n, seed=seed)
+    cfg["env"].update(env_over)
+    sim = FakeSim(n, 21, device, num_sensor_floats=12, asset=asset)
+    sim.load_state(state)
+    cfg["sim_backend"] = sim
+    env = Humanoid(cfg, device, device, -1, True)
+    env.actions.copy_(state["actions"].to(device))
+    env.progress_buf.copy_(state["progress_buf"].to(device))
+    env.reset_buf.copy_(state["reset_buf"].to(device))
+    env.potentials.copy_(state["potentials"].to(device))
+    consts = ho.HumanoidConsts.from_cfg(cfg)
+    orc = ho.HumanoidOracle(consts, state["root_states"].clone(), state["dof_state"].clone(), state["dof_force"].clone(),
+                            state["sensors"].clone(), asset["dof_limits_lower"], asset["dof_limits_upper"],
+                            asset["motor_efforts"])
+    orc.actions = state["actions"].clone()
+    orc.progress_buf = state["progress_buf"].clone()
+    orc.reset_buf = state["reset_buf"].clone()
+    orc.potentials = state["potentials"].clone()
+    return env, orc, state
+
+
+def make_gogoro_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.gogoro_new import Gogoro
+    state = state or syn.gogoro_state(n, seed=seed)
+    cfg = tcfg.gogoro_cfg(n, seed=seed)
+    cfg["env"].update(env_over)
+    cfg["env"]["resetOnInit"] = False
+    names = ["steering_joint", "rear_wheel_joint"] + [f"j{i}" for i in range(37)]
+    sim = FakeSim(n, 39, device, num_sensor_floats=0, dof_names=names)
+    sim.load_state(state)
+    cfg["sim_backend"] = sim
+    env = Gogoro(cfg, device, device, -1, True)
+    consts = go.GogoroConsts.from_cfg(cfg, steering_joint=0, rear_wheel_joint=1)
+    orc = go.GogoroOracle(consts, state["root_tensor"].clone(), state["state_dof"].clone(), state["thormang_pose"].clone())
+    for name in ("yaw_command", "curent_command", "curent_speed", "steer_offsets", "imu_offsets",
+                 "curent_speed_offset", "action_history", "progress_buf", "reset_buf", "thormang_pose"):
+        getattr(env, name).copy_(state[name].to(device))
+        setattr(orc, name, state[name].clone())
+    # the oracle's views must alias its own dof tensor after the attribute swaps above
+    orc.thormang_pose = state["thormang_pose"].clone()
+    return env, orc, state

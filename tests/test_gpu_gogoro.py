@@ -1,0 +1,177 @@
+"""GPU parity: Gogoro scooter CUDA path (through the C ABI) vs the CPU oracle on identical synthetic state."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import parity_util as U
+from thormang_isaacgym_b200 import synthetic as syn
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.mark.parametrize("n", [1, 31, 33, 255, 256, 257, 4096, 65536])
+def test_observations_and_reward(n):
+    from oracle import gogoro_oracle as go
+    env, orc, st = U.make_gogoro_pair(n, seed=300 + n)
+    got = env.compute_observations()
+    want = go.gogoro_observations(orc.root_tensor.clone(), orc.yaw_command.clone(), orc.curent_command.clone())
+    U.gogoro_obs_close(got, want)
+    # reward on identical observations: masks exact, reward within tolerance
+    env.compute_reward(want.to(DEV))
+    rew, reset = go.gogoro_reward(want.view(n, 1, 6), orc.progress_buf, orc.action_history, 1000)
+    U.exact(env.reset_buf, reset, "reset_buf")
+    U.close(env.rew_buf, rew, what="rew_buf")
+
+
+def test_golden_vectors(golden_dir):
+    z = np.load(os.path.join(golden_dir, "gogoro_jit.npz"))
+    g = {k: torch.from_numpy(z[k]) for k in z.files}
+    n = g["root_tensor"].shape[0]
+    st = syn.gogoro_state(n, seed=1)
+    st.update(root_tensor=g["root_tensor"], yaw_command=g["desired_yaw"], curent_command=g["last_command"],
+              action_history=g["action_history"], progress_buf=g["progress_buf"])
+    env, _, _ = U.make_gogoro_pair(n, state=st)
+    U.gogoro_obs_close(env.compute_observations(), g["obs"], "obs vs golden")
+    env.compute_reward(g["obs"].to(DEV))
+    U.exact(env.reset_buf, g["reset"], "reset vs golden")
+    U.close(env.rew_buf, g["rew"], what="rew vs golden")
+
+
+def _compare_state(env, orc, quat_atol=2e-6):
+    for name in ("curent_speed", "curent_speed_offset", "steer_offsets", "imu_offsets", "config_vector",
+                 "curent_command", "action_history", "progress_buf", "reset_buf"):
+        U.exact(getattr(env, name), getattr(orc, name), name)
+    U.exact(env.state_dof, orc.state_dof, "state_dof")
+    # the spawn quaternion goes through sin/cos (euler_to_quaternion): few-ulp libm difference, everything else exact
+    cols = [0, 1, 2, 7, 8, 9, 10, 11, 12]
+    U.exact(env.root_tensor[:, cols], orc.root_tensor[:, cols], "root_tensor (non-quaternion columns)")
+    U.close(env.root_tensor[:, 3:7], orc.root_tensor[:, 3:7], atol=quat_atol, what="root quaternion")
+    U.close(env.yaw_command, orc.yaw_command, atol=1e-6, what="yaw_command")
+
+
+def test_pre_physics():
+    n = 3000
+    env, orc, st = U.make_gogoro_pair(n, seed=12)
+    nz = syn.gogoro_noise(n, seed=5)
+    env.pre_physics_step(st["actions"].to(DEV), nz["steer_unit"].to(DEV))
+    orc.pre_physics_step(st["actions"], nz["steer_unit"])
+    U.exact(env.action_history, orc.action_history, "action_history")
+    U.exact(env.curent_command, orc.curent_command, "curent_command")
+    U.exact(env.dof_pos_command, orc.dof_pos_command, "dof_pos_command")
+    U.exact(env.dof_speed_command, orc.dof_speed_command, "dof_speed_command")
+    assert env.sim.dof_position_target is env.dof_pos_command
+    # full-rewrite mode (fresh zeros like gogoro_new.py:360,366)
+    env.dof_pos_command.fill_(7.0); env.dof_speed_command.fill_(7.0)
+    env.zero_fill_targets = True
+    env.pre_physics_step(st["actions"].to(DEV), nz["steer_unit"].to(DEV))
+    orc.pre_physics_step(st["actions"], nz["steer_unit"])
+    U.exact(env.dof_pos_command, orc.dof_pos_command, "dof_pos_command (zero fill)")
+    U.exact(env.dof_speed_command, orc.dof_speed_command, "dof_speed_command (zero fill)")
+
+
+def test_reset_idx():
+    n = 700
+    env, orc, st = U.make_gogoro_pair(n, seed=13)
+    ids = torch.tensor([0, 1, 31, 32, 255, 256, 699])
+    nz = syn.gogoro_noise(n, seed=6)
+    unit = nz["reset_unit"][:len(ids)]
+    env.reset_idx(ids.to(DEV), unit.to(DEV))
+    orc.reset_idx(ids, unit)
+    _compare_state(env, orc)
+    U.exact(env.buffer_obs, orc.buffer_obs, "buffer_obs")
+    U.exact(env.obs_buf, orc.obs_buf, "obs_buf")
+
+
+@pytest.mark.parametrize("n", [1, 257, 4096, 65536])
+@pytest.mark.parametrize("mode", ["compact", "philox"])
+def test_fused_post_physics(n, mode):
+    env, orc, st = U.make_gogoro_pair(n, seed=40 + n)
+    if n > 300:
+        for i in (0, 31, 32, 255, 256, n - 1):
+            st["reset_buf"][i] = 1
+        st["progress_buf"][5] = 299; st["reset_buf"][5] = 0
+        st["progress_buf"][256] = 299; st["reset_buf"][256] = 1   # would hit 300 but is reset first
+        env.reset_buf.copy_(st["reset_buf"].to(DEV)); orc.reset_buf = st["reset_buf"].clone()
+        env.progress_buf.copy_(st["progress_buf"].to(DEV)); orc.progress_buf = st["progress_buf"].clone()
+    nz = syn.gogoro_noise(n, seed=8)
+    ids = orc.reset_buf.nonzero().flatten()
+    speed_ids = ((orc.reset_buf == 0) & (orc.progress_buf + 1 == 300)).nonzero().flatten()
+    if mode == "compact":
+        sensor, reset_unit, speed_unit, yaw_unit = nz["sensor_unit"], nz["reset_unit"][:max(len(ids), 1)], nz["speed_unit"][:max(len(speed_ids), 1)], nz["yaw_unit"]
+        env.post_physics_step(sensor.to(DEV), reset_unit.to(DEV), speed_unit.to(DEV), yaw_unit.to(DEV))
+    else:
+        pn = {k: v.cpu() for k, v in env.philox_noise().items()}
+        assert abs(float(pn["sensor_unit"].mean())) < 0.1 and abs(float(pn["sensor_unit"].std()) - 1.0) < 0.1 or n < 1000
+        sensor, reset_unit, speed_unit, yaw_unit = pn["sensor_unit"], pn["reset_unit"][ids], pn["speed_unit"][speed_ids], pn["yaw_unit"]
+        env.post_physics_step()
+    orc.post_physics_step(sensor, reset_unit, speed_unit, yaw_unit)
+    orc.timeout_buf = (orc.progress_buf >= 999) & (orc.reset_buf != 0)
+    # reset rows start from a sin/cos-built quaternion: compare those obs with a looser angle tolerance
+    U.gogoro_obs_close(env.buffer_obs[:, 0], orc.buffer_obs[:, 0], "buffer_obs")
+    U.gogoro_obs_close(env.obs_buf, orc.obs_buf, "obs_buf (noisy)", noisy=True)
+    U.close(env.rew_buf, orc.rew_buf, rtol=2e-5, atol=2e-5, what="rew_buf")
+    U.exact(env.timeout_buf, orc.timeout_buf, "timeout_buf")
+    _compare_state(env, orc)
+    stats = env.episode_statistics().cpu()
+    want = torch.tensor([orc.rew_buf.double().sum(), (orc.reset_buf != 0).sum(), orc.timeout_buf.sum(), 0.0,
+                         orc.progress_buf[orc.reset_buf != 0].sum(), orc.buffer_obs[:, 0, 0].abs().double().sum(),
+                         orc.buffer_obs[:, 0, 4].abs().double().sum(), n], dtype=torch.float64)
+    keep = [0, 1, 2, 4, 5, 6, 7]
+    U.close(stats[keep], want[keep], rtol=1e-5, atol=1e-2, what="episode statistics")
+
+
+def test_compute_obs_rwd_method():
+    n = 1025
+    env, orc, st = U.make_gogoro_pair(n, seed=17)
+    nz = syn.gogoro_noise(n, seed=9)
+    env.compute_obs_rwd(nz["sensor_unit"].to(DEV))
+    orc.compute_obs_rwd(nz["sensor_unit"])
+    U.gogoro_obs_close(env.buffer_obs[:, 0], orc.buffer_obs[:, 0], "buffer_obs")
+    U.gogoro_obs_close(env.obs_buf, orc.obs_buf, "obs_buf", noisy=True)
+    U.exact(env.reset_buf, orc.reset_buf, "reset_buf")
+    U.exact(env.progress_buf, orc.progress_buf, "progress_buf (untouched)")
+    U.close(env.rew_buf, orc.rew_buf, rtol=2e-5, atol=2e-5, what="rew_buf")
+
+
+def test_rollout():
+    n, horizon = 1024, 10
+    env, orc, st = U.make_gogoro_pair(n, seed=23)
+    g = torch.Generator().manual_seed(3)
+
+    def physics_t(root, dt):
+        root[:, 0:3] += dt * root[:, 7:10]
+        root[:, 10:13] *= 0.99
+
+    for t in range(horizon):
+        a = torch.rand(n, 1, generator=g) * 3 - 1.5
+        nz = syn.gogoro_noise(n, seed=100 + t)
+        ids = orc.reset_buf.nonzero().flatten()
+        env.pre_physics_step(a.to(DEV), nz["steer_unit"].to(DEV))
+        physics_t(env.root_tensor, 0.03)
+        env.post_physics_step(nz["sensor_unit"].to(DEV), nz["reset_unit"].to(DEV), nz["speed_unit"].to(DEV), nz["yaw_unit"].to(DEV))
+        orc.step(a, nz["steer_unit"], nz["sensor_unit"], nz["reset_unit"], nz["speed_unit"], nz["yaw_unit"],
+                 physics=lambda o: physics_t(o.root_tensor, 0.03))
+        U.exact(env.reset_buf, orc.reset_buf, f"reset t={t}")
+        U.exact(env.progress_buf, orc.progress_buf, f"progress t={t}")
+        U.gogoro_obs_close(env.obs_buf, orc.obs_buf, f"obs t={t}", noisy=True)
+        U.close(env.rew_buf, orc.rew_buf, rtol=2e-5, atol=2e-5, what=f"rew t={t}")
+        orc.root_tensor.copy_(env.root_tensor.cpu()); orc.yaw_command.copy_(env.yaw_command.cpu())
+
+
+def test_sharded_equals_unsharded():
+    n = 65536
+    st = syn.gogoro_state(n, seed=1234)
+    env, _, _ = U.make_gogoro_pair(n, state={k: v.clone() for k, v in st.items()})
+    env.post_physics_step()
+    half = n // 2
+    for r in range(2):
+        sl = slice(r * half, (r + 1) * half)
+        sub = {k: (v[sl.start * 39:sl.stop * 39].clone() if k == "state_dof" else v[sl].clone()) for k, v in st.items()}
+        e2, _, _ = U.make_gogoro_pair(half, state=sub, envIdOffset=r * half)
+        e2.noise_seed = env.noise_seed
+        e2.post_physics_step()
+        for k in ("obs_buf", "buffer_obs", "rew_buf", "reset_buf", "progress_buf", "yaw_command", "curent_speed", "root_tensor"):
+            U.exact(getattr(e2, k), getattr(env, k)[sl], f"shard {r} {k}")

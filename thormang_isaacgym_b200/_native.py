@@ -1,0 +1,135 @@
+"""ctypes binding of ``libthormang_b200.so`` (C ABI: include/thormang_b200.h).
+
+There is NO fallback: if the shared library is missing or a call fails, this module
+raises.  Nothing here computes anything; it only marshals raw device pointers.
+"""
+import ctypes as C
+import os
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libthormang_b200.so")
+
+TK_MAX_DOF = 64
+TK_STATS = 8
+NOISE_NONE, NOISE_COMPACT, NOISE_DENSE, NOISE_PHILOX = 0, 1, 2, 3
+
+_f, _d, _i32, _i64, _u64, _p = C.c_float, C.c_double, C.c_int32, C.c_int64, C.c_uint64, C.c_void_p
+
+
+class HumanoidParams(C.Structure):
+    _fields_ = [
+        ("device", _i32), ("num_envs", _i32), ("num_dof", _i32), ("reserved0", _i32),
+        ("dt", _f), ("dof_vel_scale", _f), ("angular_velocity_scale", _f), ("contact_force_scale", _f),
+        ("power_scale", _f), ("heading_weight", _f), ("up_weight", _f), ("actions_cost_scale", _f),
+        ("energy_cost_scale", _f), ("joints_at_limit_cost_scale", _f), ("death_cost", _f),
+        ("termination_height", _f), ("max_episode_length", _f), ("clip_actions", _f), ("max_motor_effort", _f),
+        ("reserved1", _f),
+        ("targets", _f * 3), ("inv_start_rot", _f * 4), ("basis_vec0", _f * 3), ("basis_vec1", _f * 3),
+        ("reserved2", _f * 3),
+        ("dof_limits_lower", _f * TK_MAX_DOF), ("dof_limits_upper", _f * TK_MAX_DOF),
+        ("motor_efforts", _f * TK_MAX_DOF),
+    ]
+
+
+class HumanoidBuffers(C.Structure):
+    _fields_ = [(name, _p) for name in (
+        "root_states", "dof_state", "dof_force", "sensors", "actions", "obs_buf", "rew_buf", "reset_buf",
+        "progress_buf", "timeout_buf", "randomize_buf", "potentials", "prev_potentials", "up_vec", "heading_vec",
+        "initial_root_states", "initial_dof_pos", "episode_return")]
+
+
+class ResetNoise(C.Structure):
+    _fields_ = [("mode", _i32), ("reserved", _i32), ("unit_a", _p), ("unit_b", _p), ("rows", _i64),
+                ("seed", _u64), ("step", _u64), ("env_id_offset", _i64)]
+
+
+class GogoroParams(C.Structure):
+    _fields_ = [
+        ("device", _i32), ("num_envs", _i32), ("num_dof", _i32), ("steering_joint", _i32),
+        ("rear_wheel_joint", _i32), ("max_episode_length", _i32), ("speed_freq_update", _i32),
+        ("yaw_freq_update", _i32), ("max_steering", _f), ("max_steering_change", _f),
+        ("imu_filter_noise", _d * 2), ("imu_noise", _d * 2), ("speed_sensor_noise", _d * 2),
+        ("steering_action_noise", _d * 2), ("speed_range", _d * 2), ("seat_offset_x_range", _d * 2),
+        ("seat_offset_y_range", _d * 2), ("seat_offset_z_range", _d * 2), ("seat_offset_xr_range", _d * 2),
+        ("steering_offset", _d * 2), ("speed_sensor_offset", _d * 2),
+    ]
+
+
+class GogoroBuffers(C.Structure):
+    _fields_ = [(name, _p) for name in (
+        "root_tensor", "state_dof", "obs_buf", "buffer_obs", "rew_buf", "reset_buf", "progress_buf", "timeout_buf",
+        "yaw_command", "curent_command", "curent_speed", "steer_offsets", "imu_offsets", "curent_speed_offset",
+        "action_history", "config_vector", "thormang_pose", "root_reset_tensor", "dof_pos_command",
+        "dof_speed_command", "episode_return")]
+
+
+class GogoroNoise(C.Structure):
+    _fields_ = [("reset", ResetNoise), ("sensor_unit", _p), ("speed_unit", _p), ("yaw_unit", _p)]
+
+
+# every symbol include/thormang_b200.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "tk_last_error": (C.c_char_p, []),
+    "tk_abi_version": (C.c_int, []),
+    "tk_device_info": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "tk_humanoid_create": (C.c_int, [C.POINTER(HumanoidParams), C.POINTER(_p)]),
+    "tk_humanoid_destroy": (C.c_int, [_p]),
+    "tk_humanoid_bind": (C.c_int, [_p, C.POINTER(HumanoidBuffers)]),
+    "tk_humanoid_pre_physics": (C.c_int, [_p, _p, _p, _i32, _p]),
+    "tk_humanoid_compute_observations": (C.c_int, [_p, _p]),
+    "tk_humanoid_compute_reward": (C.c_int, [_p, _p]),
+    "tk_humanoid_reset_idx": (C.c_int, [_p, _p, _i32, _p, _p, _p]),
+    "tk_humanoid_post_physics": (C.c_int, [_p, C.POINTER(ResetNoise), _p]),
+    "tk_humanoid_reward_terms": (C.c_int, [_p, _p, _p]),
+    "tk_humanoid_wm_reward": (C.c_int, [_p, _p, _i64, _p, _p]),
+    "tk_humanoid_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p, _p]),
+    "tk_humanoid_stats": (C.c_int, [_p, _p, _i32, _p]),
+    "tk_gogoro_create": (C.c_int, [C.POINTER(GogoroParams), C.POINTER(_p)]),
+    "tk_gogoro_destroy": (C.c_int, [_p]),
+    "tk_gogoro_bind": (C.c_int, [_p, C.POINTER(GogoroBuffers)]),
+    "tk_gogoro_pre_physics": (C.c_int, [_p, _p, _p, _u64, _u64, _i64, _i32, _p]),
+    "tk_gogoro_compute_observations": (C.c_int, [_p, _p, _p]),
+    "tk_gogoro_compute_reward": (C.c_int, [_p, _p, _p]),
+    "tk_gogoro_compute_obs_rwd": (C.c_int, [_p, _p, _u64, _u64, _i64, _p]),
+    "tk_gogoro_reset_idx": (C.c_int, [_p, _p, _i32, _p, _p]),
+    "tk_gogoro_post_physics": (C.c_int, [_p, C.POINTER(GogoroNoise), _p]),
+    "tk_gogoro_stats": (C.c_int, [_p, _p, _i32, _p]),
+    "tk_gogoro_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p, _p, _p, _p, _p]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load the extension (once).  Raises ImportError if it was not built: there is no CPU path."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} not found: build it with `python -m thormang_isaacgym_b200.build` "
+                "(thormang_isaacgym_b200 has no CPU fallback)")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(handle, name)   # AttributeError if the .so does not export a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        if handle.tk_abi_version() != 1:
+            raise ImportError("libthormang_b200.so ABI version mismatch")
+        _lib = handle
+    return _lib
+
+
+def check(rc: int, what: str = ""):
+    if rc != 0:
+        msg = lib().tk_last_error()
+        raise RuntimeError(f"{what or 'thormang_b200'} failed (code {rc}): {msg.decode() if msg else '?'}")
+
+
+def ptr(t) -> int:
+    """Raw device pointer of a torch tensor (None -> NULL)."""
+    return 0 if t is None else t.data_ptr()
+
+
+def current_stream_ptr(device) -> int:
+    import torch
+    return torch.cuda.current_stream(device).cuda_stream

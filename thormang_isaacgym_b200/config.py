@@ -1,0 +1,55 @@
+"""Plain-dict task configs (hydra / omegaconf are not installed here and are outside the hot path).
+
+Values restate ``/root/reference/isaacgymenvs/cfg/task/Humanoid.yaml:7-29,42-47`` and
+``cfg/task/Gogoro.yaml:5-93`` -- the constants the env-step path consumes.  The dicts have the
+shape ``isaacgymenvs.make`` hands to the task constructors after ``omegaconf_to_dict``
+(isaacgymenvs/__init__.py:37-41).
+"""
+import copy
+
+
+def humanoid_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
+    return copy.deepcopy({
+        "name": "Humanoid",
+        "physics_engine": "physx",
+        "seed": seed,
+        "env": {
+            "numEnvs": num_envs, "envSpacing": 5, "episodeLength": 1000, "enableDebugVis": False,
+            "clipActions": 1.0, "powerScale": 1.0,
+            "headingWeight": 0.5, "upWeight": 0.1,
+            "actionsCost": 0.01, "energyCost": 0.05, "dofVelocityScale": 0.1, "angularVelocityScale": 0.25,
+            "contactForceScale": 0.01, "jointsAtLimitCost": 0.25, "deathCost": -1.0, "terminationHeight": 0.8,
+            "plane": {"staticFriction": 1.0, "dynamicFriction": 1.0, "restitution": 0.0},
+        },
+        "sim": {"dt": 0.0166, "substeps": 2, "up_axis": "z", "use_gpu_pipeline": True, "gravity": [0.0, 0.0, -9.81]},
+        "task": {"randomize": False, "randomization_params": {}},
+    })
+
+
+GOGORO_JOINTS_POS = {
+    "l_arm_el_y": 0.0, "l_arm_wr_r": 0.0, "head_y": 0.0, "r_arm_grip": 0.0, "l_arm_wr_p": 0.0, "torso_y": 0.0,
+    "r_arm_sh_r": -1.57, "l_arm_sh_p1": 0.0, "l_arm_sh_r": 1.57, "l_leg_an_r": 0.0, "l_leg_an_p": 0.0,
+    "r_leg_hip_p": 1.4, "r_leg_an_p": 0.0, "l_arm_wr_y": 0.0, "l_leg_hip_p": -1.4, "r_leg_hip_y": 0.0,
+    "l_leg_hip_r": 0.0, "l_leg_kn_p": 1.4, "r_arm_sh_p2": 0.0, "r_arm_sh_p1": 0.0, "l_leg_hip_y": 0.0,
+    "r_leg_hip_r": 0.0, "l_arm_sh_p2": 0.0, "r_arm_wr_y": 0.0, "head_p": 0.0, "r_arm_wr_p": 0.0, "r_arm_wr_r": 0.0,
+    "r_arm_el_y": 0.0, "l_arm_grip": 0.0, "r_leg_an_r": 0.0, "r_leg_kn_p": -1.4,
+}
+
+
+def gogoro_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
+    return copy.deepcopy({
+        "name": "Gogoro",
+        "physics_engine": "physx",
+        "seed": seed,
+        "env": {"numEnvs": num_envs, "max_steps": 1000},
+        "sim": {"dt": 0.03, "up_axis": "z", "use_gpu_pipeline": True, "gravity": [0.0, 0.0, -9.81], "substeps": 3},
+        "noises": {
+            "seat_offset_x_range": [0, 0.02], "seat_offset_y_range": [0, 0.02], "seat_offset_z_range": [0, 0.02],
+            "steering_offset": [0, 0.01], "imu_filter_noise": [0, 0.001], "imu_noise": [0, 0.001],
+            "seat_offset_xr_range": [0, 0.05], "speed_sensor_offset": [-0.5, 0.5], "speed_sensor_noise": [0, 0.3],
+            "steering_action_noise": [0, 0.03], "spawn_x_angle": [0, 0.05], "steering_damping_range": [100, 1000],
+            "IK_noise_amplitude": [0, 3], "speed_range": [4.0, 13.0], "speed_freq_update": 300, "yaw_freq_update": 300,
+        },
+        "joints_pos": dict(GOGORO_JOINTS_POS),
+        "task": {"randomize": False, "randomization_params": {}},
+    })

@@ -1,0 +1,246 @@
+// Shared device/host helpers for the env-step kernels (sm_100a only).
+//
+// Floating-point policy: the translation units are compiled with -fmad=false, so `a*b+c`
+// is two IEEE operations exactly like the separate torch CPU kernels of the reference.
+// Where the reference's CPU kernels DO fuse (torch.cross, torch.norm -- measured, see
+// DESIGN.md "Numerics") the fused form is written explicitly with fmaf().
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+#include "../../include/thormang_b200.h"
+
+namespace tk {
+
+// ---------------------------------------------------------------------------------------------
+// host-side error plumbing
+// ---------------------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+const char* last_error();
+
+#define TK_CUDA(call)                                                   \
+    do {                                                                \
+        cudaError_t _e = (call);                                        \
+        if (_e != cudaSuccess) return tk::cuda_fail(_e, #call);         \
+    } while (0)
+
+#define TK_REQUIRE(cond, code, ...)                                     \
+    do {                                                                \
+        if (!(cond)) {                                                  \
+            tk::set_error(__VA_ARGS__);                                 \
+            return (code);                                              \
+        }                                                               \
+    } while (0)
+
+static inline bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
+
+// ---------------------------------------------------------------------------------------------
+// constants (fp32 values of the python doubles the reference passes to torch)
+// ---------------------------------------------------------------------------------------------
+__device__ __host__ constexpr float kPi = 3.14159265358979323846f;        // (float)np.pi
+__device__ __host__ constexpr float kTwoPi = 6.28318530717958647692f;     // (float)(2*np.pi)
+
+// ---------------------------------------------------------------------------------------------
+// PTX wrappers: cache-hinted vector access, bulk (TMA) copies, mbarrier
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 ldg_stream4(const float* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+// same, but through the coherent path: for arrays this kernel may also write (root_states, dof_state)
+__device__ __forceinline__ float4 ld_stream4(const float* p) {
+    float4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ float2 ldg_stream2(const float* p) {
+    float2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0,%1}, [%2];" : "=f"(r.x), "=f"(r.y) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ float ldg_stream1(const float* p) {
+    float r;
+    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void stg_stream4(float* p, float4 v) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+// generic-proxy writes to shared memory -> visible to the async (TMA) proxy
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// shared -> global bulk copy (UBLKCP); dst/src 16-byte aligned, bytes % 16 == 0
+__device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
+
+// global -> shared bulk copy completing on an mbarrier
+__device__ __forceinline__ void bulk_load(void* sdst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(sdst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {}
+}
+
+// ---------------------------------------------------------------------------------------------
+// quaternion / angle arithmetic, operation order = oracle/isaac_helpers.py (restated
+// isaacgym.torch_utils) evaluated by torch's CPU kernels
+// ---------------------------------------------------------------------------------------------
+struct V3 { float x, y, z; };
+struct Q4 { float x, y, z, w; };
+
+// torch.cross CPU kernel: a1*b2 - a2*b1 compiles to fma(a1, b2, -(a2*b1))
+__device__ __forceinline__ V3 cross_ref(V3 a, V3 b) {
+    V3 r;
+    r.x = fmaf(a.y, b.z, -(a.z * b.y));
+    r.y = fmaf(a.z, b.x, -(a.x * b.z));
+    r.z = fmaf(a.x, b.y, -(a.y * b.x));
+    return r;
+}
+// torch.bmm [N,1,3]x[N,3,1]: (a0*b0 + a1*b1) + a2*b2, unfused
+__device__ __forceinline__ float dot_ref(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+// torch.norm(p=2, dim=-1) on 3 elements: sqrt(fma(z,z,fma(y,y,x*x)))
+__device__ __forceinline__ float norm3_ref(V3 a) { return sqrtf(fmaf(a.z, a.z, fmaf(a.y, a.y, a.x * a.x))); }
+
+// quat_mul, 9-multiply factorisation
+__device__ __forceinline__ Q4 quat_mul_ref(Q4 a, Q4 b) {
+    float ww = (a.z + a.x) * (b.x + b.y);
+    float yy = (a.w - a.y) * (b.w + b.z);
+    float zz = (a.w + a.y) * (b.w - b.z);
+    float xx = ww + yy + zz;
+    float qq = 0.5f * (xx + (a.z - a.x) * (b.x - b.y));
+    Q4 r;
+    r.w = qq - ww + (a.z - a.y) * (b.y - b.z);
+    r.x = qq - xx + (a.x + a.w) * (b.x + b.w);
+    r.y = qq - yy + (a.w - a.x) * (b.y + b.z);
+    r.z = qq - zz + (a.z + a.y) * (b.w - b.x);
+    return r;
+}
+
+// quat_rotate (sign = +1) / quat_rotate_inverse (sign = -1): a +- b + c
+template <int SIGN>
+__device__ __forceinline__ V3 quat_rotate_ref(Q4 q, V3 v) {
+    V3 qv{q.x, q.y, q.z};
+    float s = 2.0f * (q.w * q.w) - 1.0f;
+    V3 cr = cross_ref(qv, v);
+    float d = dot_ref(qv, v);
+    V3 r;
+    float ax = v.x * s, ay = v.y * s, az = v.z * s;
+    float bx = cr.x * q.w * 2.0f, by = cr.y * q.w * 2.0f, bz = cr.z * q.w * 2.0f;
+    float cx = qv.x * d * 2.0f, cy = qv.y * d * 2.0f, cz = qv.z * d * 2.0f;
+    if (SIGN > 0) {
+        r.x = ax + bx + cx; r.y = ay + by + cy; r.z = az + bz + cz;
+    } else {
+        r.x = ax - bx + cx; r.y = ay - by + cy; r.z = az - bz + cz;
+    }
+    return r;
+}
+
+// torch `x % (2*pi)` for x = atan2(..) in [-pi, pi]: fmod is the identity there, the floor-mod
+// fix-up adds the divisor to negative non-zero values (result can round to exactly 2*pi)
+__device__ __forceinline__ float mod_two_pi_of_atan2(float x) { return (x != 0.0f && x < 0.0f) ? x + kTwoPi : x; }
+// general torch floor-mod by 2*pi
+__device__ __forceinline__ float floor_mod_two_pi(float a) {
+    float m = fmodf(a, kTwoPi);
+    if (m != 0.0f && m < 0.0f) m += kTwoPi;
+    return m;
+}
+__device__ __forceinline__ float normalize_angle_ref(float x) {
+    float s, c;
+    sincosf(x, &s, &c);
+    return atan2f(s, c);
+}
+// roll and yaw of get_euler_xyz (pitch is never consumed on the hot path)
+__device__ __forceinline__ void euler_roll_yaw_ref(Q4 q, float* roll, float* yaw) {
+    float sinr_cosp = 2.0f * (q.w * q.x + q.y * q.z);
+    float cosr_cosp = q.w * q.w - q.x * q.x - q.y * q.y + q.z * q.z;
+    float siny_cosp = 2.0f * (q.w * q.z + q.x * q.y);
+    float cosy_cosp = q.w * q.w + q.x * q.x - q.y * q.y - q.z * q.z;
+    *roll = mod_two_pi_of_atan2(atan2f(sinr_cosp, cosr_cosp));
+    *yaw = mod_two_pi_of_atan2(atan2f(siny_cosp, cosy_cosp));
+}
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10 counter RNG (in-kernel reset / sensor noise); u in [0,1)
+// ---------------------------------------------------------------------------------------------
+struct Philox4 { uint32_t x, y, z, w; };
+__device__ __host__ __forceinline__ uint32_t mulhi32(uint32_t a, uint32_t b) {
+    return static_cast<uint32_t>((static_cast<uint64_t>(a) * b) >> 32);
+}
+__device__ __host__ inline Philox4 philox4x32_10(uint64_t seed, uint64_t ctr_lo, uint64_t ctr_hi) {
+    uint32_t k0 = static_cast<uint32_t>(seed), k1 = static_cast<uint32_t>(seed >> 32);
+    Philox4 c{static_cast<uint32_t>(ctr_lo), static_cast<uint32_t>(ctr_lo >> 32), static_cast<uint32_t>(ctr_hi),
+              static_cast<uint32_t>(ctr_hi >> 32)};
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = mulhi32(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        uint32_t hi1 = mulhi32(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        Philox4 n{hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0};
+        c = n;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return c;
+}
+__device__ __host__ __forceinline__ float u01(uint32_t bits) { return static_cast<float>(bits >> 8) * (1.0f / 16777216.0f); }
+// standard normal pair by Box-Muller from two 32-bit words
+__device__ __forceinline__ float2 normal_pair(uint32_t a, uint32_t b) {
+    float u1 = (static_cast<float>(a >> 8) + 1.0f) * (1.0f / 16777216.0f);   // (0,1]
+    float u2 = u01(b);
+    float r = sqrtf(-2.0f * logf(u1));
+    float s, c;
+    sincosf(kTwoPi * u2, &s, &c);
+    return make_float2(r * c, r * s);
+}
+// counter layout: ctr_lo = global env id, ctr_hi = (step << 8) | stream-id
+__device__ __host__ __forceinline__ Philox4 philox_env(uint64_t seed, uint64_t step, int64_t env, uint32_t stream_id) {
+    return philox4x32_10(seed, static_cast<uint64_t>(env), (step << 8) | stream_id);
+}
+
+// ---------------------------------------------------------------------------------------------
+// warp helpers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+}  // namespace tk

@@ -1,0 +1,751 @@
+// Gogoro scooter (registered variant) env-step hot path for B200 (sm_100a).
+//
+// Replaces, behind the C ABI of include/thormang_b200.h, the TorchScript functions and method
+// bodies of /root/reference/isaacgymenvs/tasks/gogoro_new.py:
+//   pre_physics_step :347-369, post_physics_step :373-389, compute_obs_rwd :424-462,
+//   reset_idx :505-590 (+ randomize :474-482, generate_spawn_r :485-492, euler_to_quaternion :496-502),
+//   compute_gogoro_observations :692-723, shortest_angle_distance :687-689, compute_gogoro_reward :645-684.
+//
+// 192 B / env-step of algorithmic traffic, one env per thread.  The AoS rows that are not a
+// multiple of 16 bytes (root 52 B, action history 20 B, sensor noise 20 B, the two 24 B obs rows)
+// are moved as flat, coalesced 128-bit tile copies through shared memory (row strides 13 / 5 / 6
+// words: odd or conflict-light), everything else is a coalesced 4/8-byte access per thread.
+#include "tk_common.cuh"
+
+#include <new>
+
+namespace tk {
+namespace gogoro {
+
+constexpr int kRoot = 13;
+constexpr int kObs = 6;
+constexpr int kHist = 5;
+constexpr int kSensorNoise = 5;
+constexpr int kResetNoise = 10;
+constexpr int kTile = 256;     // envs per CTA == threads per CTA
+constexpr int kWarps = kTile / 32;
+
+struct KParams {
+    float* root;
+    float* state_dof;
+    float* obs_buf;
+    float* buffer_obs;
+    float* rew;
+    long long* reset;
+    long long* progress;
+    uint8_t* timeout;
+    float* yaw_command;
+    float* curent_command;
+    float* curent_speed;
+    float* steer_offsets;
+    float* imu_offsets;
+    float* curent_speed_offset;
+    float* action_history;
+    float* config_vector;
+    const float* thormang_pose;
+    const float* root_reset;
+    float* pos_cmd;
+    float* vel_cmd;
+    float* ep_return;
+    double* partials;
+    const int* tile_base_reset;   // COMPACT: resets before this tile
+    const int* tile_base_speed;   // COMPACT: speed resamples before this tile
+    const float* reset_unit;
+    const float* sensor_unit;
+    const float* speed_unit;
+    const float* yaw_unit;
+    long long reset_rows;
+    unsigned long long seed, step;
+    long long env_off;
+    int noise_mode;
+    int n, num_dof, steering_joint, rear_wheel_joint, max_episode_length, speed_freq, yaw_freq;
+    int vec_ok;
+    float max_steering, max_steering_change;
+    // (float)lo / (float)mean, (float)(hi - lo) / (float)std with the span formed in double (get_randoms :466-467)
+    float imu_filter[2], imu[2], speed_sensor[2], steer_action[2], speed[2], seat_x[2], seat_y[2], seat_z[2], seat_xr[2],
+        steer_off[2], speed_off[2];
+};
+
+// philox stream ids per (env, step); see tk_gogoro_philox_noise for the materialised layout
+enum { kStreamSensor = 0, kStreamMisc = 1, kStreamResetU = 2, kStreamResetN0 = 3, kStreamResetN1 = 4 };
+
+struct StepNoise {
+    float sensor[kSensorNoise];
+    float steer, speed_u, yaw_u;
+};
+__device__ __forceinline__ StepNoise philox_step_noise(unsigned long long seed, unsigned long long step, long long env) {
+    StepNoise s;
+    Philox4 a = philox_env(seed, step, env, kStreamSensor);
+    Philox4 b = philox_env(seed, step, env, kStreamMisc);
+    float2 n01 = normal_pair(a.x, a.y), n23 = normal_pair(a.z, a.w), n4s = normal_pair(b.x, b.y);
+    s.sensor[0] = n01.x; s.sensor[1] = n01.y; s.sensor[2] = n23.x; s.sensor[3] = n23.y; s.sensor[4] = n4s.x;
+    s.steer = n4s.y;
+    s.speed_u = u01(b.z);
+    s.yaw_u = u01(b.w);
+    return s;
+}
+__device__ __forceinline__ void philox_reset_noise(unsigned long long seed, unsigned long long step, long long env, float* u) {
+    Philox4 a = philox_env(seed, step, env, kStreamResetU);
+    Philox4 b = philox_env(seed, step, env, kStreamResetN0);
+    Philox4 c = philox_env(seed, step, env, kStreamResetN1);
+    float2 p0 = normal_pair(b.x, b.y), p1 = normal_pair(b.z, b.w), p2 = normal_pair(c.x, c.y);
+    u[0] = u01(a.x); u[2] = u01(a.y); u[3] = u01(a.z); u[4] = u01(a.w);
+    u[1] = p0.x; u[5] = p0.y; u[6] = p1.x; u[7] = p1.y; u[8] = p2.x; u[9] = p2.y;
+}
+
+// compute_gogoro_observations :692-723
+__device__ __forceinline__ void observe(const float* r, float desired_yaw, float last_command, float* o) {
+    Q4 q{r[3], r[4], r[5], r[6]};
+    float roll, yaw;
+    euler_roll_yaw_ref(q, &roll, &yaw);                                             // :696
+    V3 lin = quat_rotate_ref<-1>(q, V3{r[7], r[8], r[9]});                          // :698
+    V3 ang = quat_rotate_ref<-1>(q, V3{r[10], r[11], r[12]});                       // :699
+    roll = (roll > kPi) ? roll - kTwoPi : roll;                                     // :704
+    roll = (roll < -kPi) ? roll + kTwoPi : roll;                                    // :705
+    yaw = (yaw > kPi) ? yaw - kTwoPi : yaw;                                         // :707
+    yaw = (yaw < -kPi) ? yaw + kTwoPi : yaw;                                        // :708
+    float delta = floor_mod_two_pi(desired_yaw - yaw + kPi) - kPi;                  // :710, :689
+    o[0] = roll; o[1] = ang.x; o[2] = ang.z; o[3] = lin.x; o[4] = delta; o[5] = last_command;
+}
+
+// compute_gogoro_reward :645-684; hist = 5 action-history values
+__device__ __forceinline__ float reward_of(const float* o, const float* hist, bool* felt_out) {
+    const float tilt = o[0], dtilt = o[1], yaw_e = o[4];
+    float tilt_err = fminf(fmaxf(tilt / 0.30f, -1.0f), 1.0f);                       // :655-656
+    float yaw_err = fminf(fmaxf(yaw_e / kPi, -1.0f), 1.0f);                         // :658-659
+    float dtilt_err = fminf(fmaxf(dtilt / 0.3f, -1.0f), 1.0f);                      // :661-662
+    float t30 = yaw_err * 30.0f;
+    float reward1 = 1.0f / (1.0f + t30 * t30);                                      // :667
+    float reward2 = 1.0f - tilt_err * tilt_err;                                     // :670
+    float reward4 = 1.0f - dtilt_err * dtilt_err;                                   // :671
+    float ce = 0.0f;
+#pragma unroll
+    for (int i = 0; i < kHist; ++i) ce += 1.0f - hist[i] * hist[i];                 // :673
+    float reward = reward1 * 5.0f + reward2 * 0.2f + reward4 * 0.3f + ce * 0.5f;    // :675
+    const bool felt = fabsf(tilt) >= 0.30f;                                         // :677
+    *felt_out = felt;
+    return felt ? -100.0f : reward;                                                 // :682
+}
+
+__device__ __forceinline__ float uniform_of(const float* pair, float u) { return pair[0] + u * pair[1]; }   // get_randoms
+__device__ __forceinline__ float normal_of(const float* pair, float z) { return pair[0] + z * pair[1]; }    // get_randoms_norm
+
+// reset_idx :505-590 for env `ne`, executed by ONE thread (rare, divergent).  u = the 10 unit draws.
+// Writes global state; returns the new root row in r[13] and zeroed history / command in the caller's registers.
+__device__ __forceinline__ void reset_env(const KParams& p, long long ne, const float* u, float* r, float* yaw_cmd) {
+    p.curent_speed[ne] = uniform_of(p.speed, u[0]);                                 // :479
+    // :481 steer_offsets <- N(steering_offset) is overwritten at :575, dead
+    p.curent_speed_offset[ne] = uniform_of(p.speed_off, u[2]);                      // :482
+    const float initial_target = (u[3] * 2.0f - 1.0f) * kPi;                        // :486
+    const float initial_rot = initial_target + (-1.57f + u[4] * static_cast<float>(1.57 - (-1.57)));   // :487
+    const float half = initial_rot / 2.0f;
+    float sy, cy;
+    sincosf(half, &sy, &cy);
+    const float sr = 0.0f, cr = 1.0f, sp = 0.0f, cp = 1.0f;                         // sin/cos of roll/2 = pitch/2 = 0
+    const float qx = sr * cp * cy - cr * sp * sy;                                   // :497-500
+    const float qy = cr * sp * cy + sr * cp * sy;
+    const float qz = cr * cp * sy - sr * sp * cy;
+    const float qw = cr * cp * cy + sr * sp * sy;
+#pragma unroll
+    for (int c = 0; c < kRoot; ++c) r[c] = p.root_reset[ne * kRoot + c];            // :518
+    r[3] = qx; r[4] = qy; r[5] = qz; r[6] = qw;                                     // :519
+#pragma unroll
+    for (int c = 7; c < kRoot; ++c) r[c] = 0.0f;                                    // :520
+    r[2] = 0.03f;                                                                   // :537
+#pragma unroll
+    for (int c = 0; c < kRoot; ++c) p.root[ne * kRoot + c] = r[c];                  // :547
+    float2* ds = reinterpret_cast<float2*>(p.state_dof) + ne * p.num_dof;
+    for (int j = 0; j < p.num_dof; ++j) ds[j] = make_float2(p.thormang_pose[ne * p.num_dof + j], 0.0f);   // :549-550
+    float cfgv[5];
+    cfgv[0] = normal_of(p.seat_x, u[5]);                                            // :554
+    cfgv[1] = normal_of(p.seat_y, u[6]);                                            // :555
+    cfgv[2] = normal_of(p.seat_z, u[7]);                                            // :556
+    cfgv[3] = normal_of(p.seat_xr, u[8]);                                           // :557
+    cfgv[4] = normal_of(p.steer_off, u[9]);                                         // :559
+#pragma unroll
+    for (int c = 0; c < 5; ++c) p.config_vector[ne * 5 + c] = cfgv[c];
+    p.imu_offsets[ne] = cfgv[3];                                                    // :574
+    p.steer_offsets[ne] = cfgv[4];                                                  // :575
+    *yaw_cmd = initial_target;                                                      // :589
+}
+
+struct Smem {
+    alignas(16) float root[kTile * kRoot];
+    alignas(16) float hist[kTile * kHist];
+    alignas(16) float noise[kTile * kSensorNoise];
+    alignas(16) float clean[kTile * kObs];
+    alignas(16) float noisy[kTile * kObs];
+    unsigned ballots[2][kWarps];
+    float wsum[kWarps][TK_STATS];
+};
+
+__device__ __forceinline__ void tile_load(float* dst, const float* src, int cnt, bool vec, int tid) {
+    if (vec) {
+        const int c4 = cnt >> 2;
+        for (int i = tid; i < c4; i += kTile) reinterpret_cast<float4*>(dst)[i] = ld_stream4(src + 4 * i);
+        for (int i = (c4 << 2) + tid; i < cnt; i += kTile) dst[i] = src[i];
+    } else {
+        for (int i = tid; i < cnt; i += kTile) dst[i] = src[i];
+    }
+}
+__device__ __forceinline__ void tile_store(float* dst, const float* src, int cnt, bool vec, int tid) {
+    if (vec) {
+        const int c4 = cnt >> 2;
+        for (int i = tid; i < c4; i += kTile) stg_stream4(dst + 4 * i, reinterpret_cast<const float4*>(src)[i]);
+        for (int i = (c4 << 2) + tid; i < cnt; i += kTile) dst[i] = src[i];
+    } else {
+        for (int i = tid; i < cnt; i += kTile) dst[i] = src[i];
+    }
+}
+
+// MODE 0: fused post_physics_step; 1: compute_obs_rwd only; 2: observations only (obs_out = clean [N,6])
+template <int MODE>
+__global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constant__ KParams p, float* __restrict__ obs_out) {
+    __shared__ Smem s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int env0 = blockIdx.x * kTile;
+    const int nt = min(kTile, p.n - env0);
+    const long long n = env0 + tid;
+    const bool valid = tid < nt;
+    const bool vec = p.vec_ok != 0;
+    const bool philox = p.noise_mode == TK_NOISE_PHILOX;
+
+    tile_load(s.root, p.root + static_cast<size_t>(env0) * kRoot, nt * kRoot, vec, tid);
+    if (MODE != 2) {
+        tile_load(s.hist, p.action_history + static_cast<size_t>(env0) * kHist, nt * kHist, vec, tid);
+        if (!philox && p.sensor_unit)
+            tile_load(s.noise, p.sensor_unit + static_cast<size_t>(env0) * kSensorNoise, nt * kSensorNoise, vec, tid);
+    }
+
+    long long prog = 0;
+    bool do_reset = false, do_speed = false;
+    float yaw_cmd = 0.f, cur_cmd = 0.f;
+    if (valid) {
+        yaw_cmd = p.yaw_command[n];
+        cur_cmd = p.curent_command[n];
+        if (MODE != 2) prog = p.progress[n];
+        if (MODE == 0) {
+            prog += 1;                                                              // :375
+            do_reset = p.reset[n] != 0;                                             // :377
+            if (do_reset) prog = 0;                                                 // :583
+            do_speed = prog == p.speed_freq;                                        // :384 (after the reset)
+        }
+    }
+    if (MODE == 0) {
+        unsigned b0 = __ballot_sync(0xffffffffu, do_reset), b1 = __ballot_sync(0xffffffffu, do_speed);
+        if (lane == 0) { s.ballots[0][warp] = b0; s.ballots[1][warp] = b1; }
+    }
+    __syncthreads();
+
+    float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_tilt = 0.f, st_yaw = 0.f;
+    bool out_reset = false, out_timeout = false;
+    if (valid) {
+        float r[kRoot], hist[kHist];
+#pragma unroll
+        for (int c = 0; c < kRoot; ++c) r[c] = s.root[tid * kRoot + c];
+        StepNoise sn;
+        if (MODE != 2) {
+#pragma unroll
+            for (int c = 0; c < kHist; ++c) hist[c] = s.hist[tid * kHist + c];
+            if (philox) {
+                sn = philox_step_noise(p.seed, p.step, p.env_off + n);
+            } else {
+#pragma unroll
+                for (int c = 0; c < kSensorNoise; ++c) sn.sensor[c] = p.sensor_unit ? s.noise[tid * kSensorNoise + c] : 0.0f;
+                sn.yaw_u = p.yaw_unit ? p.yaw_unit[n] : 0.5f;
+                sn.speed_u = 0.5f;
+            }
+        }
+        if (MODE == 0 && do_reset) {
+            float u[kResetNoise];
+            if (philox) {
+                philox_reset_noise(p.seed, p.step, p.env_off + n, u);
+            } else {
+                long long row = n;
+                if (p.noise_mode == TK_NOISE_COMPACT) {
+                    int rank = p.tile_base_reset[blockIdx.x];
+                    for (int w = 0; w < warp; ++w) rank += __popc(s.ballots[0][w]);
+                    rank += __popc(s.ballots[0][warp] & ((1u << lane) - 1u));
+                    row = rank;
+                }
+#pragma unroll
+                for (int c = 0; c < kResetNoise; ++c)
+                    u[c] = (p.noise_mode != TK_NOISE_NONE && row < p.reset_rows) ? p.reset_unit[row * kResetNoise + c]
+                                                                                 : ((c == 0 || (c >= 2 && c <= 4)) ? 0.5f : 0.0f);
+            }
+            reset_env(p, n, u, r, &yaw_cmd);
+            cur_cmd = 0.0f;                                                         // :587
+            p.curent_command[n] = 0.0f;
+#pragma unroll
+            for (int c = 0; c < kHist; ++c) { hist[c] = 0.0f; p.action_history[n * kHist + c] = 0.0f; }   // :590
+        }
+
+        float o[kObs];
+        observe(r, yaw_cmd, cur_cmd, o);                                            // :430-434
+        if (MODE == 2) {
+#pragma unroll
+            for (int c = 0; c < kObs; ++c) s.clean[tid * kObs + c] = o[c];
+        } else {
+#pragma unroll
+            for (int c = 0; c < kObs; ++c) s.clean[tid * kObs + c] = o[c];          // :436-437 (buff_size 1: plain overwrite)
+            bool felt;
+            float reward = reward_of(o, hist, &felt);                               // :439-444
+            const bool finished = prog >= p.max_episode_length - 1;                 // :678
+            out_reset = felt || finished;                                           // :679-680
+            p.rew[n] = reward;
+            p.reset[n] = out_reset ? 1 : 0;
+            // sensor-noise model on a copy :449-460
+            float z[kObs];
+            z[0] = o[0] + (normal_of(p.imu_filter, sn.sensor[0]) + p.imu_offsets[n]);   // :451
+            z[1] = o[1] + normal_of(p.imu, sn.sensor[1]);                           // :452
+            z[2] = o[2] + normal_of(p.imu, sn.sensor[2]);                           // :453
+            z[3] = rintf(o[4]);                                                     // :455-458: channel 3 <- round(channel 4), sic
+            z[4] = o[4] + normal_of(p.imu_filter, sn.sensor[4]);                    // :460
+            z[5] = o[5];
+#pragma unroll
+            for (int c = 0; c < kObs; ++c) s.noisy[tid * kObs + c] = z[c];          // :462
+            st_rew = reward; st_tilt = fabsf(o[0]); st_yaw = fabsf(o[4]);
+        }
+        if (MODE == 0) {
+            p.progress[n] = prog;
+            // command resampling :384-389
+            if (do_speed) {
+                float su = sn.speed_u;
+                if (!philox && p.speed_unit) {
+                    long long row = n;
+                    if (p.noise_mode == TK_NOISE_COMPACT) {
+                        int rank = p.tile_base_speed[blockIdx.x];
+                        for (int w = 0; w < warp; ++w) rank += __popc(s.ballots[1][w]);
+                        rank += __popc(s.ballots[1][warp] & ((1u << lane) - 1u));
+                        row = rank;
+                    }
+                    su = p.speed_unit[row];
+                }
+                p.curent_speed[n] = uniform_of(p.speed, su);                        // :386
+            }
+            if (prog == p.yaw_freq) yaw_cmd = -kPi + sn.yaw_u * kTwoPi;             // :387
+            yaw_cmd = (yaw_cmd > kPi) ? yaw_cmd - kTwoPi : yaw_cmd;                 // :388
+            yaw_cmd = (yaw_cmd < -kPi) ? yaw_cmd + kTwoPi : yaw_cmd;                // :389
+            p.yaw_command[n] = yaw_cmd;
+            out_timeout = (prog >= p.max_episode_length - 1) && out_reset;          // vec_task.py:345
+            if (p.timeout) p.timeout[n] = out_timeout ? 1 : 0;
+            if (p.ep_return) {
+                float ret = (do_reset ? 0.0f : p.ep_return[n]) + st_rew;
+                if (out_reset) st_ret = ret;
+                p.ep_return[n] = ret;
+            }
+            if (out_reset) st_len = static_cast<float>(prog);
+        }
+    }
+
+    if (MODE == 0) {
+        const unsigned m_reset = __ballot_sync(0xffffffffu, out_reset);
+        const unsigned m_to = __ballot_sync(0xffffffffu, out_timeout);
+        const unsigned m_valid = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            st_rew += __shfl_xor_sync(0xffffffffu, st_rew, o);
+            st_ret += __shfl_xor_sync(0xffffffffu, st_ret, o);
+            st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
+            st_tilt += __shfl_xor_sync(0xffffffffu, st_tilt, o);
+            st_yaw += __shfl_xor_sync(0xffffffffu, st_yaw, o);
+        }
+        if (lane == 0) {
+            float* w = s.wsum[warp];
+            w[0] = st_rew; w[1] = static_cast<float>(__popc(m_reset)); w[2] = static_cast<float>(__popc(m_to));
+            w[3] = st_ret; w[4] = st_len; w[5] = st_tilt; w[6] = st_yaw; w[7] = static_cast<float>(__popc(m_valid));
+        }
+    }
+    __syncthreads();
+    if (MODE == 0 && tid < TK_STATS) {
+        double acc = 0.0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) acc += static_cast<double>(s.wsum[w][tid]);
+        p.partials[static_cast<size_t>(blockIdx.x) * TK_STATS + tid] += acc;   // running sum since the last tk_*_stats
+    }
+    if (MODE == 2) {
+        tile_store(obs_out + static_cast<size_t>(env0) * kObs, s.clean, nt * kObs,
+                   vec && (reinterpret_cast<uintptr_t>(obs_out) & 15) == 0, tid);
+    } else {
+        tile_store(p.buffer_obs + static_cast<size_t>(env0) * kObs, s.clean, nt * kObs, vec, tid);
+        tile_store(p.obs_buf + static_cast<size_t>(env0) * kObs, s.noisy, nt * kObs, vec, tid);
+    }
+}
+
+// per-tile counts of the two COMPACT predicates: reset != 0 ; reset == 0 && progress + 1 == speed_freq
+__global__ void tile_count_kernel(const long long* __restrict__ reset, const long long* __restrict__ progress, int n, int tiles,
+                                  int speed_freq, int* __restrict__ c_reset, int* __restrict__ c_speed) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= tiles) return;
+    int a = 0, b = 0;
+    for (int i = lane; i < kTile; i += 32) {
+        int e = warp * kTile + i;
+        if (e < n) {
+            const bool rs = reset[e] != 0;
+            a += rs ? 1 : 0;
+            b += (!rs && progress[e] + 1 == speed_freq) ? 1 : 0;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+    if (lane == 0) { c_reset[warp] = a; c_speed[warp] = b; }
+}
+
+__global__ void exclusive_scan_kernel(const int* __restrict__ counts, int tiles, int* __restrict__ base) {
+    // single CTA, sequential over chunks of blockDim.x tiles
+    __shared__ int warp_tot[32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int start = 0; start < tiles; start += blockDim.x) {
+        const int i = start + threadIdx.x;
+        const int v = (i < tiles) ? counts[i] : 0;
+        int x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_tot[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            int t = (lane < (blockDim.x >> 5)) ? warp_tot[lane] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int y = __shfl_up_sync(0xffffffffu, t, o);
+                if (lane >= o) t += y;
+            }
+            warp_tot[lane] = t;
+        }
+        __syncthreads();
+        const int before = carry + (warp > 0 ? warp_tot[warp - 1] : 0) + (x - v);
+        if (i < tiles) base[i] = before;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = before + v;
+        __syncthreads();
+    }
+}
+
+// pre_physics_step :347-369, one env per thread
+__global__ void __launch_bounds__(256) gogoro_pre_kernel(const __grid_constant__ KParams p, const float* __restrict__ actions,
+                                                          const float* __restrict__ steer_unit, int zero_fill) {
+    const long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (zero_fill) {
+        // fresh torch.zeros targets of :360,366 (376 B/env mode): flat coalesced fill by the whole grid
+        const long long total = static_cast<long long>(p.n) * p.num_dof;
+        // (the two live columns are written by a second launch of this kernel with zero_fill = 0)
+        for (long long i = n; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) { p.pos_cmd[i] = 0.0f; p.vel_cmd[i] = 0.0f; }
+        return;
+    }
+    if (n >= p.n) return;
+    const float a = actions[n];                                                     // actions[:,0], num_acts = 1
+    float* h = p.action_history + n * kHist;
+    float h1 = h[1], h2 = h[2], h3 = h[3], h4 = h[4];
+    h[0] = h1; h[1] = h2; h[2] = h3; h[3] = h4; h[4] = a;                           // :349-350
+    float a2 = a * p.max_steering_change;                                           // :353
+    a2 = fminf(fmaxf(a2, -p.max_steering_change), p.max_steering_change);           // :354
+    float cmd = p.curent_command[n] + a2;                                           // :355
+    cmd = fminf(fmaxf(cmd, -p.max_steering), p.max_steering);                       // :359
+    p.curent_command[n] = cmd;
+    float z = steer_unit ? steer_unit[n] : philox_step_noise(p.seed, p.step, p.env_off + n).steer;
+    float noise = normal_of(p.steer_action, z);                                     // :362
+    p.pos_cmd[n * p.num_dof + p.steering_joint] = cmd + p.steer_offsets[n] + noise; // :363
+    p.vel_cmd[n * p.num_dof + p.rear_wheel_joint] = p.curent_speed[n];              // :367
+}
+
+// compute_gogoro_reward on an explicit obs tensor (method-level entry)
+__global__ void gogoro_reward_kernel(const __grid_constant__ KParams p, const float* __restrict__ obs) {
+    const long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (n >= p.n) return;
+    float o[kObs], hist[kHist];
+#pragma unroll
+    for (int c = 0; c < kObs; ++c) o[c] = obs[n * kObs + c];
+#pragma unroll
+    for (int c = 0; c < kHist; ++c) hist[c] = p.action_history[n * kHist + c];
+    bool felt;
+    float reward = reward_of(o, hist, &felt);
+    const bool finished = p.progress[n] >= p.max_episode_length - 1;
+    p.rew[n] = reward;
+    p.reset[n] = (felt || finished) ? 1 : 0;
+}
+
+// reset_idx :505-590 for an explicit id list, one thread per listed env
+__global__ void gogoro_reset_idx_kernel(const __grid_constant__ KParams p, const long long* __restrict__ ids, int k,
+                                        const float* __restrict__ unit) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= k) return;
+    const long long ne = ids[i];
+    if (ne < 0 || ne >= p.n) return;
+    float u[kResetNoise], r[kRoot], yaw_cmd;
+#pragma unroll
+    for (int c = 0; c < kResetNoise; ++c) u[c] = unit[static_cast<size_t>(i) * kResetNoise + c];
+    reset_env(p, ne, u, r, &yaw_cmd);
+    p.progress[ne] = 0;                                                             // :583
+    p.reset[ne] = 0;                                                                // :584
+#pragma unroll
+    for (int c = 0; c < kObs; ++c) { p.obs_buf[ne * kObs + c] = 0.0f; p.buffer_obs[ne * kObs + c] = 0.0f; }   // :585-586
+    p.curent_command[ne] = 0.0f;                                                    // :587
+    p.yaw_command[ne] = yaw_cmd;                                                    // :589
+#pragma unroll
+    for (int c = 0; c < kHist; ++c) p.action_history[ne * kHist + c] = 0.0f;        // :590
+}
+
+__global__ void gogoro_philox_kernel(int n, unsigned long long seed, unsigned long long step, long long env_off,
+                                     float* steer, float* sensor, float* reset_unit, float* speed, float* yaw) {
+    const long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    StepNoise sn = philox_step_noise(seed, step, env_off + e);
+    if (steer) steer[e] = sn.steer;
+    if (sensor) for (int c = 0; c < kSensorNoise; ++c) sensor[e * kSensorNoise + c] = sn.sensor[c];
+    if (speed) speed[e] = sn.speed_u;
+    if (yaw) yaw[e] = sn.yaw_u;
+    if (reset_unit) {
+        float u[kResetNoise];
+        philox_reset_noise(seed, step, env_off + e, u);
+        for (int c = 0; c < kResetNoise; ++c) reset_unit[e * kResetNoise + c] = u[c];
+    }
+}
+
+__global__ void stats_finalize_kernel(double* __restrict__ partials, int rows, double* __restrict__ out, int accumulate) {
+    const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (k >= TK_STATS) return;
+    double acc = 0.0;
+    for (int r = lane; r < rows; r += 32) {
+        acc += partials[static_cast<size_t>(r) * TK_STATS + k];
+        partials[static_cast<size_t>(r) * TK_STATS + k] = 0.0;   // the partials restart from zero
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) out[k] = accumulate ? out[k] + acc : acc;
+}
+
+}  // namespace gogoro
+}  // namespace tk
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+using namespace tk;
+using namespace tk::gogoro;
+
+struct TkGogoro {
+    TkGogoroParams params;
+    TkGogoroBuffers buf;
+    bool bound;
+    int tiles;
+    double* partials;
+    int* counts;   // [2, tiles]
+    int* bases;    // [2, tiles]
+    int last_grid;
+};
+
+static void pair_uniform(const double* in, float* out) { out[0] = static_cast<float>(in[0]); out[1] = static_cast<float>(in[1] - in[0]); }
+static void pair_normal(const double* in, float* out) { out[0] = static_cast<float>(in[0]); out[1] = static_cast<float>(in[1]); }
+
+static void fill_kparams(const TkGogoro* h, KParams& k) {
+    const TkGogoroParams& P = h->params;
+    const TkGogoroBuffers& B = h->buf;
+    k.root = B.root_tensor; k.state_dof = B.state_dof; k.obs_buf = B.obs_buf; k.buffer_obs = B.buffer_obs; k.rew = B.rew_buf;
+    k.reset = reinterpret_cast<long long*>(B.reset_buf); k.progress = reinterpret_cast<long long*>(B.progress_buf);
+    k.timeout = B.timeout_buf; k.yaw_command = B.yaw_command; k.curent_command = B.curent_command;
+    k.curent_speed = B.curent_speed; k.steer_offsets = B.steer_offsets; k.imu_offsets = B.imu_offsets;
+    k.curent_speed_offset = B.curent_speed_offset; k.action_history = B.action_history; k.config_vector = B.config_vector;
+    k.thormang_pose = B.thormang_pose; k.root_reset = B.root_reset_tensor; k.pos_cmd = B.dof_pos_command;
+    k.vel_cmd = B.dof_speed_command; k.ep_return = B.episode_return;
+    k.partials = h->partials; k.tile_base_reset = h->bases; k.tile_base_speed = h->bases + h->tiles;
+    k.reset_unit = nullptr; k.sensor_unit = nullptr; k.speed_unit = nullptr; k.yaw_unit = nullptr; k.reset_rows = 0;
+    k.seed = 0; k.step = 0; k.env_off = 0; k.noise_mode = TK_NOISE_NONE;
+    k.n = P.num_envs; k.num_dof = P.num_dof; k.steering_joint = P.steering_joint; k.rear_wheel_joint = P.rear_wheel_joint;
+    k.max_episode_length = P.max_episode_length; k.speed_freq = P.speed_freq_update; k.yaw_freq = P.yaw_freq_update;
+    k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.action_history, 16) && aligned_to(B.obs_buf, 16) &&
+               aligned_to(B.buffer_obs, 16);
+    k.max_steering = P.max_steering; k.max_steering_change = P.max_steering_change;
+    pair_normal(P.imu_filter_noise, k.imu_filter); pair_normal(P.imu_noise, k.imu); pair_normal(P.speed_sensor_noise, k.speed_sensor);
+    pair_normal(P.steering_action_noise, k.steer_action); pair_uniform(P.speed_range, k.speed);
+    pair_normal(P.seat_offset_x_range, k.seat_x); pair_normal(P.seat_offset_y_range, k.seat_y);
+    pair_normal(P.seat_offset_z_range, k.seat_z); pair_normal(P.seat_offset_xr_range, k.seat_xr);
+    pair_normal(P.steering_offset, k.steer_off); pair_uniform(P.speed_sensor_offset, k.speed_off);
+}
+
+static int check_bound(const TkGogoro* h) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_REQUIRE(h->bound, TK_ERR_UNBOUND, "tk_gogoro_bind was not called");
+    return TK_OK;
+}
+
+extern "C" {
+
+int tk_gogoro_create(const TkGogoroParams* params, TkGogoro** out) {
+    TK_REQUIRE(params && out, TK_ERR_INVALID, "null argument");
+    TK_REQUIRE(params->num_envs > 0, TK_ERR_INVALID, "num_envs must be positive (got %d)", params->num_envs);
+    TK_REQUIRE(params->num_dof > 0 && params->num_dof <= 4096, TK_ERR_INVALID, "bad num_dof %d", params->num_dof);
+    TK_REQUIRE(params->steering_joint >= 0 && params->steering_joint < params->num_dof && params->rear_wheel_joint >= 0 &&
+                   params->rear_wheel_joint < params->num_dof,
+               TK_ERR_INVALID, "joint index out of range");
+    TK_CUDA(cudaSetDevice(params->device));
+    TkGogoro* h = new (std::nothrow) TkGogoro();
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "out of host memory");
+    h->params = *params;
+    h->bound = false;
+    h->tiles = (params->num_envs + kTile - 1) / kTile;
+    h->last_grid = 0;
+    h->partials = nullptr; h->counts = nullptr; h->bases = nullptr;
+    cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * h->tiles);
+    if (e == cudaSuccess) e = cudaMalloc(&h->counts, sizeof(int) * 2 * h->tiles);
+    if (e == cudaSuccess) e = cudaMalloc(&h->bases, sizeof(int) * 2 * h->tiles);
+    if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * h->tiles);
+    if (e == cudaSuccess) e = cudaMemset(h->bases, 0, sizeof(int) * 2 * h->tiles);
+    if (e != cudaSuccess) {
+        cudaFree(h->partials); cudaFree(h->counts); cudaFree(h->bases);
+        delete h;
+        return cuda_fail(e, "tk_gogoro_create");
+    }
+    *out = h;
+    return TK_OK;
+}
+
+int tk_gogoro_destroy(TkGogoro* h) {
+    if (!h) return TK_OK;
+    cudaSetDevice(h->params.device);
+    cudaFree(h->partials); cudaFree(h->counts); cudaFree(h->bases);
+    delete h;
+    return TK_OK;
+}
+
+int tk_gogoro_bind(TkGogoro* h, const TkGogoroBuffers* b) {
+    TK_REQUIRE(h && b, TK_ERR_INVALID, "null argument");
+    const void* req[] = {b->root_tensor, b->state_dof, b->obs_buf, b->buffer_obs, b->rew_buf, b->reset_buf, b->progress_buf,
+                         b->yaw_command, b->curent_command, b->curent_speed, b->steer_offsets, b->imu_offsets,
+                         b->curent_speed_offset, b->action_history, b->config_vector, b->thormang_pose, b->root_reset_tensor,
+                         b->dof_pos_command, b->dof_speed_command};
+    const char* names[] = {"root_tensor", "state_dof", "obs_buf", "buffer_obs", "rew_buf", "reset_buf", "progress_buf",
+                           "yaw_command", "curent_command", "curent_speed", "steer_offsets", "imu_offsets",
+                           "curent_speed_offset", "action_history", "config_vector", "thormang_pose", "root_reset_tensor",
+                           "dof_pos_command", "dof_speed_command"};
+    for (unsigned i = 0; i < sizeof(req) / sizeof(req[0]); ++i) {
+        TK_REQUIRE(req[i] != nullptr, TK_ERR_UNBOUND, "buffer %s is NULL", names[i]);
+        TK_REQUIRE(aligned_to(req[i], 4), TK_ERR_ALIGN, "buffer %s is not 4-byte aligned", names[i]);
+    }
+    TK_REQUIRE(aligned_to(b->reset_buf, 8) && aligned_to(b->progress_buf, 8), TK_ERR_ALIGN, "int64 buffers must be 8-byte aligned");
+    TK_REQUIRE(aligned_to(b->state_dof, 8), TK_ERR_ALIGN, "state_dof must be 8-byte aligned ((pos,vel) pairs)");
+    h->buf = *b;
+    h->bound = true;
+    return TK_OK;
+}
+
+int tk_gogoro_pre_physics(TkGogoro* h, const float* actions, const float* steer_unit, uint64_t seed, uint64_t step,
+                          int64_t env_id_offset, int32_t zero_fill, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(actions != nullptr, TK_ERR_INVALID, "null actions");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    KParams k; fill_kparams(h, k);
+    k.seed = seed; k.step = step; k.env_off = env_id_offset;
+    const int blocks = (k.n + 255) / 256;
+    if (zero_fill) {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->params.device);
+        const long long want = (static_cast<long long>(k.n) * k.num_dof + 255) / 256;
+        const int zb = static_cast<int>(want < static_cast<long long>(sms) * 8 ? (want < 1 ? 1 : want) : static_cast<long long>(sms) * 8);
+        gogoro_pre_kernel<<<zb, 256, 0, st>>>(k, actions, steer_unit, 1);
+    }
+    gogoro_pre_kernel<<<blocks, 256, 0, st>>>(k, actions, steer_unit, 0);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_compute_observations(TkGogoro* h, float* obs_out, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(obs_out != nullptr, TK_ERR_INVALID, "null obs_out");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    gogoro_tile_kernel<2><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, obs_out);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_compute_reward(TkGogoro* h, const float* cur_obs, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(cur_obs != nullptr, TK_ERR_INVALID, "null cur_obs");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    gogoro_reward_kernel<<<(k.n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(k, cur_obs);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_compute_obs_rwd(TkGogoro* h, const float* sensor_unit, uint64_t seed, uint64_t step, int64_t env_id_offset,
+                              void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    k.sensor_unit = sensor_unit;
+    k.noise_mode = sensor_unit ? TK_NOISE_DENSE : TK_NOISE_PHILOX;
+    k.seed = seed; k.step = step; k.env_off = env_id_offset;
+    k.vec_ok = k.vec_ok && (!sensor_unit || aligned_to(sensor_unit, 16));
+    gogoro_tile_kernel<1><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, nullptr);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_reset_idx(TkGogoro* h, const int64_t* env_ids, int32_t kcount, const float* unit, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    if (kcount == 0) return TK_OK;
+    TK_REQUIRE(kcount > 0 && env_ids && unit, TK_ERR_INVALID, "bad reset_idx arguments");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    gogoro_reset_idx_kernel<<<(kcount + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        k, reinterpret_cast<const long long*>(env_ids), kcount, unit);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(noise != nullptr, TK_ERR_INVALID, "null noise descriptor");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    KParams k; fill_kparams(h, k);
+    const int mode = noise->reset.mode;
+    TK_REQUIRE(mode >= TK_NOISE_NONE && mode <= TK_NOISE_PHILOX, TK_ERR_INVALID, "bad noise mode %d", mode);
+    k.noise_mode = mode;
+    k.reset_unit = noise->reset.unit_a; k.reset_rows = noise->reset.rows;
+    k.seed = noise->reset.seed; k.step = noise->reset.step; k.env_off = noise->reset.env_id_offset;
+    k.sensor_unit = noise->sensor_unit; k.speed_unit = noise->speed_unit; k.yaw_unit = noise->yaw_unit;
+    if (mode == TK_NOISE_COMPACT || mode == TK_NOISE_DENSE)
+        TK_REQUIRE(noise->reset.unit_a != nullptr, TK_ERR_INVALID, "reset noise rows missing");
+    k.vec_ok = k.vec_ok && (!k.sensor_unit || aligned_to(k.sensor_unit, 16));
+    if (mode == TK_NOISE_COMPACT) {
+        const int wpb = 8;
+        tile_count_kernel<<<(h->tiles + wpb - 1) / wpb, wpb * 32, 0, st>>>(k.reset, k.progress, k.n, h->tiles, k.speed_freq,
+                                                                          h->counts, h->counts + h->tiles);
+        exclusive_scan_kernel<<<1, 1024, 0, st>>>(h->counts, h->tiles, h->bases);
+        exclusive_scan_kernel<<<1, 1024, 0, st>>>(h->counts + h->tiles, h->tiles, h->bases + h->tiles);
+    }
+    gogoro_tile_kernel<0><<<h->tiles, kTile, 0, st>>>(k, nullptr);
+    TK_CUDA(cudaGetLastError());
+    h->last_grid = h->tiles;
+    return TK_OK;
+}
+
+int tk_gogoro_stats(TkGogoro* h, double* stats_out, int32_t accumulate, void* stream) {
+    TK_REQUIRE(h && stats_out, TK_ERR_INVALID, "null argument");
+    TK_REQUIRE(h->last_grid > 0, TK_ERR_INVALID, "tk_gogoro_post_physics has not run yet");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    tk::gogoro::stats_finalize_kernel<<<1, TK_STATS * 32, 0, static_cast<cudaStream_t>(stream)>>>(h->partials, h->last_grid,
+                                                                                                  stats_out, accumulate);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_philox_noise(TkGogoro* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* steer_unit,
+                           float* sensor_unit, float* reset_unit, float* speed_unit, float* yaw_unit, void* stream) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    gogoro_philox_kernel<<<(h->params.num_envs + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        h->params.num_envs, seed, step, env_id_offset, steer_unit, sensor_unit, reset_unit, speed_unit, yaw_unit);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,857 @@
+// Humanoid env-step hot path for B200 (sm_100a).
+//
+// Replaces, behind the C ABI of include/thormang_b200.h, the TorchScript functions and method
+// bodies of /root/reference/isaacgymenvs/tasks/humanoid.py:
+//   pre_physics_step :281-285, post_physics_step :287-296, reset_idx :253-279,
+//   compute_humanoid_observations :379-417, compute_humanoid_reward :323-376, compute_reward :425-472.
+//
+// Data layout in HBM is Isaac Gym's (AoS): root_states [N,13], dof_state [N*D,2], dof_force [N,D],
+// sensors [N,12], actions [N,D], obs_buf [N,110].  The fused post-physics kernel is a pure
+// streaming kernel (924 B / env-step, ~0.3 flop/B): one CTA owns a tile of kTile consecutive
+// envs, whose slice of EVERY array is one contiguous, 16-byte aligned byte range.
+//   * inputs are read with coalesced 128-bit streaming loads and scattered into the
+//     shared-memory image of the tile's obs rows (scaled copies = 96 of the 110 columns);
+//   * the 14 columns that need the torso math are computed one env per thread from a
+//     shared-memory copy of the root rows (stride 13 words: bank-conflict free);
+//   * the finished [kTile,110] tile leaves as ONE cp.async.bulk (TMA) shared->global store;
+//   * per-task constants (limits, 1/range, efforts) are staged once in shared memory;
+//   * per-env flags/potentials/reward are coalesced 4/8-byte accesses, one env per thread.
+// No tensor cores: nothing on this path is a contraction.
+#include "tk_common.cuh"
+
+#include <new>
+
+namespace tk {
+namespace humanoid {
+
+constexpr int kRoot = 13;
+constexpr int kSensor = 12;
+constexpr int kTile = 128;      // envs per CTA
+constexpr int kThreads = 128;   // one env per thread in the torso-math phase
+constexpr int kWarps = kThreads / 32;
+
+template <int D>
+struct Layout {
+    static constexpr int kPos = 12;
+    static constexpr int kVel = kPos + D;
+    static constexpr int kForce = kVel + D;
+    static constexpr int kSens = kForce + D;
+    static constexpr int kAct = kSens + kSensor;
+    static constexpr int kPot = kAct + D;
+    static constexpr int kObs = kPot + 2;   // 110 for D = 21 (humanoid.py:67)
+};
+
+struct KParams {
+    float* root;
+    float* dof_state;
+    const float* dof_force;
+    const float* sensors;
+    float* actions;
+    float* obs;
+    float* rew;
+    long long* reset;
+    long long* progress;
+    uint8_t* timeout;
+    long long* randomize;
+    float* pot;
+    float* prev_pot;
+    float* up_vec;
+    float* heading_vec;
+    const float* init_root;
+    const float* init_dof_pos;
+    float* ep_return;
+    double* partials;           // [grid, TK_STATS]
+    const int* tile_rank_base;  // COMPACT noise: resets in envs before this tile
+    const float* unit_a;
+    const float* unit_b;
+    long long noise_rows;
+    unsigned long long seed;
+    unsigned long long step;
+    long long env_off;
+    int noise_mode;
+    int n;
+    int vec_ok;                 // all tile bases 16-byte aligned -> vector loads + bulk store
+    float dt, dof_vel_scale, ang_vel_scale, contact_scale, power_scale;
+    float heading_weight, up_weight, actions_cost_scale, energy_cost_scale, joints_cost_scale;
+    float death_cost, termination_height, max_episode_length, clip_actions, max_motor_effort;
+    float tgt[3], isr[4], b0[3], b1[3];
+    float lo[TK_MAX_DOF], hi[TK_MAX_DOF], effort[TK_MAX_DOF];
+};
+
+// ---------------------------------------------------------------------------------------------
+// torso math of one env: compute_humanoid_observations :386-405 (+ compute_heading_and_up, compute_rot)
+// ---------------------------------------------------------------------------------------------
+struct Head {
+    float c[12];      // obs columns 0..11
+    float pot;        // potentials'
+    V3 up, heading;   // up_vec, heading_vec
+};
+
+__device__ __forceinline__ Head torso_math(const float* r, const KParams& p) {
+    Head h;
+    V3 pos{r[0], r[1], r[2]};
+    Q4 q{r[3], r[4], r[5], r[6]};
+    V3 lin{r[7], r[8], r[9]};
+    V3 ang{r[10], r[11], r[12]};
+
+    V3 tt{p.tgt[0] - pos.x, p.tgt[1] - pos.y, 0.0f};              // :391-392
+    float nrm = norm3_ref(tt);
+    h.pot = (-nrm) / p.dt;                                        // :395
+
+    float nclamp = fmaxf(nrm, 1e-9f);                             // normalize(): x / clamp(norm, min=eps)
+    V3 td{tt.x / nclamp, tt.y / nclamp, tt.z / nclamp};
+    Q4 tq = quat_mul_ref(q, Q4{p.isr[0], p.isr[1], p.isr[2], p.isr[3]});
+    h.up = quat_rotate_ref<1>(tq, V3{p.b1[0], p.b1[1], p.b1[2]});
+    h.heading = quat_rotate_ref<1>(tq, V3{p.b0[0], p.b0[1], p.b0[2]});
+    float up_proj = h.up.z;
+    float heading_proj = dot_ref(h.heading, td);
+
+    V3 vel_loc = quat_rotate_ref<-1>(tq, lin);
+    V3 angvel_loc = quat_rotate_ref<-1>(tq, ang);
+    float roll, yaw;
+    euler_roll_yaw_ref(tq, &roll, &yaw);
+    float walk = atan2f(p.tgt[2] - pos.z, p.tgt[0] - pos.x);      // z and x, sic (compute_rot)
+    float att = walk - yaw;
+
+    h.c[0] = pos.z;
+    h.c[1] = vel_loc.x; h.c[2] = vel_loc.y; h.c[3] = vel_loc.z;
+    h.c[4] = angvel_loc.x * p.ang_vel_scale; h.c[5] = angvel_loc.y * p.ang_vel_scale; h.c[6] = angvel_loc.z * p.ang_vel_scale;
+    h.c[7] = normalize_angle_ref(yaw);
+    h.c[8] = normalize_angle_ref(roll);
+    h.c[9] = normalize_angle_ref(att);
+    h.c[10] = up_proj;
+    h.c[11] = heading_proj;
+    return h;
+}
+
+__device__ __forceinline__ float unscale_ref(float x, float lo, float hi) { return (2.0f * x - hi - lo) / (hi - lo); }
+
+// ---------------------------------------------------------------------------------------------
+// fused kernel.  FUSED = post_physics_step (progress++, reset prologue, obs, reward, masks, stats);
+//               !FUSED = compute_observations only.
+// ---------------------------------------------------------------------------------------------
+template <int D>
+struct Smem {
+    static constexpr int kObs = Layout<D>::kObs;
+    alignas(128) float obs[kTile * kObs];
+    alignas(16) float root[kTile * kRoot];
+    float lo[D], hi[D];
+    unsigned ballots[kWarps];
+    float wsum[kWarps][TK_STATS];
+};
+
+template <int D, bool FUSED>
+__global__ void __launch_bounds__(kThreads) humanoid_tile_kernel(const __grid_constant__ KParams p) {
+    using L = Layout<D>;
+    constexpr int OBS = L::kObs;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem<D>& s = *reinterpret_cast<Smem<D>*>(smem_raw);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int env0 = blockIdx.x * kTile;
+    const int nt = min(kTile, p.n - env0);
+    const int n = env0 + tid;
+    const bool valid = tid < nt;
+    const bool vec = p.vec_ok != 0;
+
+    if (tid < D) { s.lo[tid] = p.lo[tid]; s.hi[tid] = p.hi[tid]; }
+
+    // ---- per-env flags (coalesced 8-byte accesses)
+    long long prog = 0;
+    bool do_reset = false;
+    if (FUSED) {
+        if (valid) {
+            prog = p.progress[n] + 1;                              // :288
+            do_reset = p.reset[n] != 0;                            // :291
+            if (p.randomize) p.randomize[n] += 1;                  // :289
+        }
+        unsigned b = __ballot_sync(0xffffffffu, do_reset);
+        if (lane == 0) s.ballots[warp] = b;
+    }
+    float pot_old = 0.0f;
+    if (valid) pot_old = p.pot[n];
+
+    // ---- root rows -> shared (flat copy)
+    {
+        const float* src = p.root + static_cast<size_t>(env0) * kRoot;
+        const int cnt = nt * kRoot;
+        if (vec) {
+            const int c4 = cnt >> 2;
+            for (int i = tid; i < c4; i += kThreads) reinterpret_cast<float4*>(s.root)[i] = ld_stream4(src + 4 * i);
+            for (int i = (c4 << 2) + tid; i < cnt; i += kThreads) s.root[i] = src[i];
+        } else {
+            for (int i = tid; i < cnt; i += kThreads) s.root[i] = src[i];
+        }
+    }
+    __syncthreads();   // s.lo/s.hi, ballots visible
+
+    // ---- dof_state (pos,vel interleaved) -> obs columns kPos.., kVel..
+    {
+        const float* src = p.dof_state + static_cast<size_t>(env0) * D * 2;
+        const int cnt = nt * D;   // (pos,vel) pairs
+        const float dvs = p.dof_vel_scale;
+        if (vec) {
+            const int c2 = cnt >> 1;
+#pragma unroll 4
+            for (int i = tid; i < c2; i += kThreads) {
+                float4 v = ld_stream4(src + 4 * i);
+                int e0 = 2 * i, n0 = e0 / D, j0 = e0 - n0 * D;
+                int e1 = e0 + 1, n1 = e1 / D, j1 = e1 - n1 * D;
+                s.obs[n0 * OBS + L::kPos + j0] = unscale_ref(v.x, s.lo[j0], s.hi[j0]);
+                s.obs[n0 * OBS + L::kVel + j0] = v.y * dvs;
+                s.obs[n1 * OBS + L::kPos + j1] = unscale_ref(v.z, s.lo[j1], s.hi[j1]);
+                s.obs[n1 * OBS + L::kVel + j1] = v.w * dvs;
+            }
+            if ((cnt & 1) && tid == 0) {
+                int e0 = cnt - 1, n0 = e0 / D, j0 = e0 - n0 * D;
+                s.obs[n0 * OBS + L::kPos + j0] = unscale_ref(src[2 * e0], s.lo[j0], s.hi[j0]);
+                s.obs[n0 * OBS + L::kVel + j0] = src[2 * e0 + 1] * dvs;
+            }
+        } else {
+            for (int e0 = tid; e0 < cnt; e0 += kThreads) {
+                int n0 = e0 / D, j0 = e0 - n0 * D;
+                s.obs[n0 * OBS + L::kPos + j0] = unscale_ref(src[2 * e0], s.lo[j0], s.hi[j0]);
+                s.obs[n0 * OBS + L::kVel + j0] = src[2 * e0 + 1] * dvs;
+            }
+        }
+    }
+    // ---- dof_force * contact_force_scale -> kForce.. ; actions -> kAct..
+    {
+        const float* srcf = p.dof_force + static_cast<size_t>(env0) * D;
+        const float* srca = p.actions + static_cast<size_t>(env0) * D;
+        const int cnt = nt * D;
+        const float cfs = p.contact_scale;
+        if (vec) {
+            const int c4 = cnt >> 2;
+#pragma unroll 2
+            for (int i = tid; i < c4; i += kThreads) {
+                float4 f = ldg_stream4(srcf + 4 * i);
+                float4 a = ldg_stream4(srca + 4 * i);
+                const float fv[4] = {f.x, f.y, f.z, f.w};
+                const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    int e = 4 * i + k, nn = e / D, j = e - nn * D;
+                    s.obs[nn * OBS + L::kForce + j] = fv[k] * cfs;
+                    s.obs[nn * OBS + L::kAct + j] = av[k];
+                }
+            }
+            for (int e = (c4 << 2) + tid; e < cnt; e += kThreads) {
+                int nn = e / D, j = e - nn * D;
+                s.obs[nn * OBS + L::kForce + j] = srcf[e] * cfs;
+                s.obs[nn * OBS + L::kAct + j] = srca[e];
+            }
+        } else {
+            for (int e = tid; e < cnt; e += kThreads) {
+                int nn = e / D, j = e - nn * D;
+                s.obs[nn * OBS + L::kForce + j] = srcf[e] * cfs;
+                s.obs[nn * OBS + L::kAct + j] = srca[e];
+            }
+        }
+    }
+    // ---- force sensors * contact_force_scale -> kSens..
+    {
+        const float* src = p.sensors + static_cast<size_t>(env0) * kSensor;
+        const int cnt = nt * kSensor;   // always a multiple of 4
+        const float cfs = p.contact_scale;
+        if (vec) {
+            for (int i = tid; i < (cnt >> 2); i += kThreads) {
+                float4 v = ldg_stream4(src + 4 * i);
+                int e = 4 * i, nn = e / kSensor, k = e - nn * kSensor;
+                float* dst = &s.obs[nn * OBS + L::kSens + k];
+                dst[0] = v.x * cfs; dst[1] = v.y * cfs; dst[2] = v.z * cfs; dst[3] = v.w * cfs;
+            }
+        } else {
+            for (int e = tid; e < cnt; e += kThreads) {
+                int nn = e / kSensor, k = e - nn * kSensor;
+                s.obs[nn * OBS + L::kSens + k] = src[e] * cfs;
+            }
+        }
+    }
+
+    // ---- reset prologue (rare): reset_idx :253-279 for the tile's flagged envs, one warp per env
+    if (FUSED) {
+        __syncthreads();   // staged tile complete before it is patched
+        const unsigned mine = s.ballots[warp];
+        if (mine) {
+            int rank = (p.noise_mode == TK_NOISE_COMPACT) ? p.tile_rank_base[blockIdx.x] : 0;
+            for (int w = 0; w < warp; ++w) rank += __popc(s.ballots[w]);
+            unsigned bits = mine;
+            while (bits) {
+                const int le = __ffs(bits) - 1;
+                bits &= bits - 1;
+                const int e = warp * 32 + le;
+                const int ne = env0 + e;
+                const long long row = (p.noise_mode == TK_NOISE_COMPACT) ? rank : ne;
+                ++rank;
+                for (int j = lane; j < D; j += 32) {
+                    float ua = 0.5f, ub = 0.5f;
+                    if (p.noise_mode == TK_NOISE_PHILOX) {
+                        Philox4 r = philox_env(p.seed, p.step, p.env_off + ne, static_cast<uint32_t>(j >> 1));
+                        ua = u01((j & 1) ? r.z : r.x);
+                        ub = u01((j & 1) ? r.w : r.y);
+                    } else if (p.noise_mode != TK_NOISE_NONE && row < p.noise_rows) {
+                        ua = p.unit_a[row * D + j];
+                        ub = p.unit_b[row * D + j];
+                    }
+                    float positions = 0.4f * ua + (-0.2f);                         // :258 torch_rand_float(-0.2, 0.2)
+                    float velocities = 0.2f * ub + (-0.1f);                        // :259 torch_rand_float(-0.1, 0.1)
+                    float np_ = p.init_dof_pos[static_cast<size_t>(ne) * D + j] + positions;
+                    np_ = fmaxf(fminf(np_, s.hi[j]), s.lo[j]);                     // :261 tensor_clamp
+                    float2* ds = reinterpret_cast<float2*>(p.dof_state) + (static_cast<size_t>(ne) * D + j);
+                    *ds = make_float2(np_, velocities);                            // :261-262 (through the strided views)
+                    s.obs[e * OBS + L::kPos + j] = unscale_ref(np_, s.lo[j], s.hi[j]);
+                    s.obs[e * OBS + L::kVel + j] = velocities * p.dof_vel_scale;
+                }
+                if (lane < kRoot) {                                                // :265-267 root row <- initial_root_states
+                    float v = p.init_root[static_cast<size_t>(ne) * kRoot + lane];
+                    p.root[static_cast<size_t>(ne) * kRoot + lane] = v;
+                    s.root[e * kRoot + lane] = v;
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- torso math, one env per thread
+    float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_up = 0.f, st_head = 0.f;
+    bool out_reset = false, out_timeout = false;
+    if (valid) {
+        float r[kRoot];
+#pragma unroll
+        for (int c = 0; c < kRoot; ++c) r[c] = s.root[tid * kRoot + c];
+        Head h = torso_math(r, p);
+        // after a reset potentials = prev_potentials = -|targets - initial_pos| / dt (:273-276): the root row now IS
+        // the initial row, so that value equals the freshly computed potential
+        const float prev_new = (FUSED && do_reset) ? h.pot : pot_old;              // :394
+        float* o = &s.obs[tid * OBS];
+#pragma unroll
+        for (int c = 0; c < 12; ++c) o[c] = h.c[c];
+        o[L::kPot] = h.pot / 60000.0f;                                             // :414
+        o[L::kPot + 1] = prev_new / 60000.0f;
+        p.pot[n] = h.pot;
+        p.prev_pot[n] = prev_new;
+        if (p.up_vec) { p.up_vec[n * 3 + 0] = h.up.x; p.up_vec[n * 3 + 1] = h.up.y; p.up_vec[n * 3 + 2] = h.up.z; }
+        if (p.heading_vec) {
+            p.heading_vec[n * 3 + 0] = h.heading.x; p.heading_vec[n * 3 + 1] = h.heading.y; p.heading_vec[n * 3 + 2] = h.heading.z;
+        }
+        if (FUSED) {
+            if (do_reset) prog = 0;                                                // :278 (reset_buf -> 0, :279)
+            // compute_humanoid_reward :349-350, :362-374 (live formula: alive + up)
+            float up_reward = (h.c[10] > 0.93f) ? (0.0f + p.up_weight) : 0.0f;
+            float total = 2.0f + up_reward;
+            const bool fallen = h.c[0] < p.termination_height;
+            if (fallen) total = 1.0f * p.death_cost;
+            const bool finished = static_cast<float>(prog) >= p.max_episode_length - 1.0f;
+            out_reset = fallen || finished;
+            out_timeout = finished && out_reset;                                    // vec_task.py:345
+            p.rew[n] = total;
+            p.reset[n] = out_reset ? 1 : 0;
+            p.progress[n] = prog;
+            if (p.timeout) p.timeout[n] = out_timeout ? 1 : 0;
+            st_rew = total; st_up = h.c[10]; st_head = h.c[11];
+            if (p.ep_return) {
+                float ret = (do_reset ? 0.0f : p.ep_return[n]) + total;
+                if (out_reset) st_ret = ret;
+                p.ep_return[n] = ret;
+            }
+            if (out_reset) st_len = static_cast<float>(prog);
+        }
+    }
+
+    // ---- statistics partials (fixed reduction order -> deterministic)
+    if (FUSED) {
+        const unsigned m_reset = __ballot_sync(0xffffffffu, out_reset);
+        const unsigned m_to = __ballot_sync(0xffffffffu, out_timeout);
+        const unsigned m_valid = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            st_rew += __shfl_xor_sync(0xffffffffu, st_rew, o);
+            st_ret += __shfl_xor_sync(0xffffffffu, st_ret, o);
+            st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
+            st_up += __shfl_xor_sync(0xffffffffu, st_up, o);
+            st_head += __shfl_xor_sync(0xffffffffu, st_head, o);
+        }
+        if (lane == 0) {
+            float* w = s.wsum[warp];
+            w[0] = st_rew; w[1] = static_cast<float>(__popc(m_reset)); w[2] = static_cast<float>(__popc(m_to));
+            w[3] = st_ret; w[4] = st_len; w[5] = st_up; w[6] = st_head; w[7] = static_cast<float>(__popc(m_valid));
+        }
+    }
+    fence_proxy_async_smem();   // obs tile written through the generic proxy, read by the bulk-copy engine
+    __syncthreads();
+
+    if (FUSED && tid < TK_STATS) {
+        double acc = 0.0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) acc += static_cast<double>(s.wsum[w][tid]);
+        p.partials[static_cast<size_t>(blockIdx.x) * TK_STATS + tid] += acc;   // running sum since the last tk_*_stats
+    }
+
+    // ---- obs tile -> global
+    float* dst = p.obs + static_cast<size_t>(env0) * OBS;
+    const int cnt = nt * OBS;
+    if (vec && (cnt & 3) == 0) {
+        if (tid == 0) {
+            bulk_store(dst, s.obs, static_cast<uint32_t>(cnt) * 4u);
+            bulk_commit();
+            bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
+        }
+    } else {
+        for (int i = tid; i < cnt; i += kThreads) dst[i] = s.obs[i];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// COMPACT noise order: exclusive prefix of the per-tile reset counts (two tiny kernels)
+// ---------------------------------------------------------------------------------------------
+__global__ void tile_reset_count_kernel(const long long* __restrict__ reset, int n, int tiles, int* __restrict__ counts) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= tiles) return;
+    int c = 0;
+    for (int i = lane; i < kTile; i += 32) {
+        int e = warp * kTile + i;
+        if (e < n && reset[e] != 0) ++c;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if (lane == 0) counts[warp] = c;
+}
+
+__global__ void tile_exclusive_scan_kernel(const int* __restrict__ counts, int tiles, int* __restrict__ base) {
+    __shared__ int warp_tot[32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int start = 0; start < tiles; start += blockDim.x) {
+        const int i = start + threadIdx.x;
+        const int v = (i < tiles) ? counts[i] : 0;
+        int x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_tot[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            int t = (lane < (blockDim.x >> 5)) ? warp_tot[lane] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int y = __shfl_up_sync(0xffffffffu, t, o);
+                if (lane >= o) t += y;
+            }
+            warp_tot[lane] = t;   // inclusive over warps
+        }
+        __syncthreads();
+        const int before = carry + (warp > 0 ? warp_tot[warp - 1] : 0) + (x - v);
+        if (i < tiles) base[i] = before;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = before + v;
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// pre_physics_step :281-285 (+ clamp vec_task.py:327): flat stream over N*D floats
+// ---------------------------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(256) humanoid_pre_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
+                                                            float* __restrict__ forces, int clip, int vec) {
+    __shared__ float eff[D];
+    if (threadIdx.x < D) eff[threadIdx.x] = p.effort[threadIdx.x];
+    __syncthreads();
+    const long long total = static_cast<long long>(p.n) * D;
+    const float c = p.clip_actions, ps = p.power_scale;
+    const long long gtid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const long long gstride = static_cast<long long>(gridDim.x) * blockDim.x;
+    if (vec) {
+        const long long t4 = total >> 2;
+        for (long long i = gtid; i < t4; i += gstride) {
+            float4 a = ldg_stream4(in + 4 * i);
+            float av[4] = {a.x, a.y, a.z, a.w}, fv[4];
+            const int j0 = static_cast<int>((4 * i) % D);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float x = av[k];
+                if (clip) x = fminf(fmaxf(x, -c), c);
+                int j = j0 + k; if (j >= D) j -= D;
+                av[k] = x;
+                fv[k] = x * eff[j] * ps;                                           // :283
+            }
+            stg_stream4(p.actions + 4 * i, make_float4(av[0], av[1], av[2], av[3]));
+            stg_stream4(forces + 4 * i, make_float4(fv[0], fv[1], fv[2], fv[3]));
+        }
+        for (long long e = (t4 << 2) + gtid; e < total; e += gstride) {
+            float x = in[e];
+            if (clip) x = fminf(fmaxf(x, -c), c);
+            p.actions[e] = x;
+            forces[e] = x * eff[e % D] * ps;
+        }
+    } else {
+        for (long long e = gtid; e < total; e += gstride) {
+            float x = in[e];
+            if (clip) x = fminf(fmaxf(x, -c), c);
+            p.actions[e] = x;
+            forces[e] = x * eff[e % D] * ps;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// split entry points (method-level drop-in; not the hot configuration)
+// ---------------------------------------------------------------------------------------------
+template <int D>
+__global__ void humanoid_reward_kernel(const __grid_constant__ KParams p) {
+    using L = Layout<D>;
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.n) return;
+    const float* o = p.obs + static_cast<size_t>(n) * L::kObs;
+    float up_reward = (o[10] > 0.93f) ? (0.0f + p.up_weight) : 0.0f;               // :349-350
+    float total = 2.0f + up_reward;                                                // :362,365
+    const bool fallen = o[0] < p.termination_height;
+    if (fallen) total = 1.0f * p.death_cost;                                       // :370
+    long long reset = fallen ? 1 : p.reset[n];                                     // :373
+    if (static_cast<float>(p.progress[n]) >= p.max_episode_length - 1.0f) reset = 1;   // :374
+    p.rew[n] = total;
+    p.reset[n] = reset;
+}
+
+// all terms of :344-363, one warp per env (lane = DOF), sequential-order sums via shuffles
+template <int D>
+__global__ void humanoid_terms_kernel(const __grid_constant__ KParams p, float* __restrict__ terms) {
+    using L = Layout<D>;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= p.n) return;
+    const float* o = p.obs + static_cast<size_t>(warp) * L::kObs;
+    float a2 = 0.f, lim = 0.f, el = 0.f;
+    if (lane < D) {
+        float a = p.actions[static_cast<size_t>(warp) * D + lane];
+        float ratio = p.effort[lane] / p.max_motor_effort;                         // :355
+        float pa = fabsf(o[L::kPos + lane]);
+        float scaled = p.joints_cost_scale * (pa - 0.98f) / 0.02f;                 // :356
+        a2 = a * a;                                                                // :352
+        lim = ((pa > 0.98f) ? 1.0f : 0.0f) * scaled * ratio;                       // :357
+        el = fabsf(a * o[L::kVel + lane]) * ratio;                                 // :359
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        a2 += __shfl_xor_sync(0xffffffffu, a2, off);
+        lim += __shfl_xor_sync(0xffffffffu, lim, off);
+        el += __shfl_xor_sync(0xffffffffu, el, off);
+    }
+    if (lane == 0) {
+        float hp = o[11];
+        float* t = terms + static_cast<size_t>(warp) * 7;
+        t[0] = (hp > 0.8f) ? (1.0f * p.heading_weight) : (p.heading_weight * hp / 0.8f);   // :345-346
+        t[1] = (o[10] > 0.93f) ? (0.0f + p.up_weight) : 0.0f;                       // :349-350
+        t[2] = a2; t[3] = lim; t[4] = el;
+        t[5] = 2.0f;                                                               // :362
+        t[6] = p.pot[warp] - p.prev_pot[warp];                                     // :363
+    }
+}
+
+// compute_reward :425-472 over obs[M,110]
+template <int D>
+__global__ void humanoid_wm_reward_kernel(const __grid_constant__ KParams p, const float* __restrict__ obs, long long m,
+                                          float* __restrict__ out) {
+    using L = Layout<D>;
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const float* o = obs + i * L::kObs;
+    float hp = o[11];
+    float heading_reward = (hp > 0.8f) ? (1.0f * p.heading_weight) : (p.heading_weight * hp / 0.8f);
+    float up_reward = (o[10] > 0.93f) ? (0.0f + p.up_weight) : 0.0f;
+    float progress_reward = o[L::kPot] - o[L::kPot + 1];
+    float total = progress_reward + 2.0f + up_reward + heading_reward;             // :467
+    if (o[0] < p.termination_height) total = 1.0f * p.death_cost;                  // :470
+    out[i] = total;
+}
+
+// reset_idx :253-279 for an explicit id list; one warp per listed env
+template <int D>
+__global__ void humanoid_reset_idx_kernel(const __grid_constant__ KParams p, const long long* __restrict__ ids, int k,
+                                          const float* __restrict__ unit_pos, const float* __restrict__ unit_vel) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= k) return;
+    const long long ne = ids[warp];
+    if (ne < 0 || ne >= p.n) return;
+    for (int j = lane; j < D; j += 32) {
+        float positions = 0.4f * unit_pos[static_cast<size_t>(warp) * D + j] + (-0.2f);
+        float velocities = 0.2f * unit_vel[static_cast<size_t>(warp) * D + j] + (-0.1f);
+        float np_ = p.init_dof_pos[ne * D + j] + positions;
+        np_ = fmaxf(fminf(np_, p.hi[j]), p.lo[j]);
+        reinterpret_cast<float2*>(p.dof_state)[ne * D + j] = make_float2(np_, velocities);
+    }
+    if (lane < kRoot) p.root[ne * kRoot + lane] = p.init_root[ne * kRoot + lane];
+    if (lane == 0) {
+        V3 tt{p.tgt[0] - p.init_root[ne * kRoot + 0], p.tgt[1] - p.init_root[ne * kRoot + 1], 0.0f};   // :273-274
+        float v = (-norm3_ref(tt)) / p.dt;                                          // :275
+        p.prev_pot[ne] = v;
+        p.pot[ne] = v;                                                             // :276
+        p.progress[ne] = 0;                                                        // :278
+        p.reset[ne] = 0;                                                           // :279
+    }
+}
+
+template <int D>
+__global__ void humanoid_philox_kernel(int n, unsigned long long seed, unsigned long long step, long long env_off,
+                                       float* __restrict__ ua, float* __restrict__ ub) {
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= static_cast<long long>(n) * D) return;
+    const long long e = i / D;
+    const int j = static_cast<int>(i - e * D);
+    Philox4 r = philox_env(seed, step, env_off + e, static_cast<uint32_t>(j >> 1));
+    ua[i] = u01((j & 1) ? r.z : r.x);
+    ub[i] = u01((j & 1) ? r.w : r.y);
+}
+
+__global__ void stats_finalize_kernel(double* __restrict__ partials, int rows, double* __restrict__ out, int accumulate) {
+    // one warp per statistic, fixed order
+    const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (k >= TK_STATS) return;
+    double acc = 0.0;
+    for (int r = lane; r < rows; r += 32) {
+        acc += partials[static_cast<size_t>(r) * TK_STATS + k];
+        partials[static_cast<size_t>(r) * TK_STATS + k] = 0.0;   // the partials restart from zero
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) out[k] = accumulate ? out[k] + acc : acc;
+}
+
+}  // namespace humanoid
+}  // namespace tk
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+using namespace tk;
+using namespace tk::humanoid;
+
+struct TkHumanoid {
+    TkHumanoidParams params;
+    TkHumanoidBuffers buf;
+    bool bound;
+    int tiles;
+    double* partials;     // [tiles, TK_STATS]
+    int* tile_counts;     // [tiles]
+    int* tile_base;       // [tiles]
+    int last_grid;
+};
+
+static constexpr int kD = 21;
+
+static void fill_kparams(const TkHumanoid* h, KParams& k) {
+    const TkHumanoidParams& P = h->params;
+    const TkHumanoidBuffers& B = h->buf;
+    k.root = B.root_states; k.dof_state = B.dof_state; k.dof_force = B.dof_force; k.sensors = B.sensors;
+    k.actions = B.actions; k.obs = B.obs_buf; k.rew = B.rew_buf;
+    k.reset = reinterpret_cast<long long*>(B.reset_buf); k.progress = reinterpret_cast<long long*>(B.progress_buf);
+    k.timeout = B.timeout_buf; k.randomize = reinterpret_cast<long long*>(B.randomize_buf);
+    k.pot = B.potentials; k.prev_pot = B.prev_potentials; k.up_vec = B.up_vec; k.heading_vec = B.heading_vec;
+    k.init_root = B.initial_root_states; k.init_dof_pos = B.initial_dof_pos; k.ep_return = B.episode_return;
+    k.partials = h->partials; k.tile_rank_base = h->tile_base;
+    k.unit_a = nullptr; k.unit_b = nullptr; k.noise_rows = 0; k.seed = 0; k.step = 0; k.env_off = 0;
+    k.noise_mode = TK_NOISE_NONE;
+    k.n = P.num_envs;
+    k.vec_ok = aligned_to(B.root_states, 16) && aligned_to(B.dof_state, 16) && aligned_to(B.dof_force, 16) &&
+               aligned_to(B.sensors, 16) && aligned_to(B.actions, 16) && aligned_to(B.obs_buf, 16);
+    k.dt = P.dt; k.dof_vel_scale = P.dof_vel_scale; k.ang_vel_scale = P.angular_velocity_scale;
+    k.contact_scale = P.contact_force_scale; k.power_scale = P.power_scale; k.heading_weight = P.heading_weight;
+    k.up_weight = P.up_weight; k.actions_cost_scale = P.actions_cost_scale; k.energy_cost_scale = P.energy_cost_scale;
+    k.joints_cost_scale = P.joints_at_limit_cost_scale; k.death_cost = P.death_cost;
+    k.termination_height = P.termination_height; k.max_episode_length = P.max_episode_length;
+    k.clip_actions = P.clip_actions; k.max_motor_effort = P.max_motor_effort;
+    for (int i = 0; i < 3; ++i) { k.tgt[i] = P.targets[i]; k.b0[i] = P.basis_vec0[i]; k.b1[i] = P.basis_vec1[i]; }
+    for (int i = 0; i < 4; ++i) k.isr[i] = P.inv_start_rot[i];
+    for (int i = 0; i < TK_MAX_DOF; ++i) { k.lo[i] = P.dof_limits_lower[i]; k.hi[i] = P.dof_limits_upper[i]; k.effort[i] = P.motor_efforts[i]; }
+}
+
+static int check_bound(const TkHumanoid* h) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_REQUIRE(h->bound, TK_ERR_UNBOUND, "tk_humanoid_bind was not called");
+    return TK_OK;
+}
+
+extern "C" {
+
+int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
+    TK_REQUIRE(params && out, TK_ERR_INVALID, "null argument");
+    TK_REQUIRE(params->num_envs > 0, TK_ERR_INVALID, "num_envs must be positive (got %d)", params->num_envs);
+    TK_REQUIRE(params->num_dof == kD, TK_ERR_INVALID, "Humanoid kernels are built for num_dof = %d (got %d)", kD, params->num_dof);
+    TK_REQUIRE(params->dt > 0.f, TK_ERR_INVALID, "dt must be positive");
+    TK_CUDA(cudaSetDevice(params->device));
+    TkHumanoid* h = new (std::nothrow) TkHumanoid();
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "out of host memory");
+    h->params = *params;
+    h->bound = false;
+    h->tiles = (params->num_envs + kTile - 1) / kTile;
+    h->last_grid = 0;
+    h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr;
+    cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * h->tiles);
+    if (e == cudaSuccess) e = cudaMalloc(&h->tile_counts, sizeof(int) * h->tiles);
+    if (e == cudaSuccess) e = cudaMalloc(&h->tile_base, sizeof(int) * h->tiles);
+    if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * h->tiles);
+    if (e == cudaSuccess) e = cudaMemset(h->tile_base, 0, sizeof(int) * h->tiles);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(humanoid_tile_kernel<kD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(sizeof(Smem<kD>)));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(humanoid_tile_kernel<kD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(sizeof(Smem<kD>)));
+    if (e != cudaSuccess) {
+        cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base);
+        delete h;
+        return cuda_fail(e, "tk_humanoid_create");
+    }
+    *out = h;
+    return TK_OK;
+}
+
+int tk_humanoid_destroy(TkHumanoid* h) {
+    if (!h) return TK_OK;
+    cudaSetDevice(h->params.device);
+    cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base);
+    delete h;
+    return TK_OK;
+}
+
+int tk_humanoid_bind(TkHumanoid* h, const TkHumanoidBuffers* b) {
+    TK_REQUIRE(h && b, TK_ERR_INVALID, "null argument");
+    const void* req[] = {b->root_states, b->dof_state, b->dof_force, b->sensors, b->actions, b->obs_buf, b->rew_buf,
+                         b->reset_buf, b->progress_buf, b->potentials, b->prev_potentials, b->initial_root_states,
+                         b->initial_dof_pos};
+    const char* names[] = {"root_states", "dof_state", "dof_force", "sensors", "actions", "obs_buf", "rew_buf",
+                           "reset_buf", "progress_buf", "potentials", "prev_potentials", "initial_root_states",
+                           "initial_dof_pos"};
+    for (unsigned i = 0; i < sizeof(req) / sizeof(req[0]); ++i) {
+        TK_REQUIRE(req[i] != nullptr, TK_ERR_UNBOUND, "buffer %s is NULL", names[i]);
+        TK_REQUIRE(aligned_to(req[i], 4), TK_ERR_ALIGN, "buffer %s is not 4-byte aligned", names[i]);
+    }
+    TK_REQUIRE(aligned_to(b->reset_buf, 8) && aligned_to(b->progress_buf, 8), TK_ERR_ALIGN, "int64 buffers must be 8-byte aligned");
+    TK_REQUIRE(aligned_to(b->dof_state, 8), TK_ERR_ALIGN, "dof_state must be 8-byte aligned ((pos,vel) pairs)");
+    TK_REQUIRE(!b->randomize_buf || aligned_to(b->randomize_buf, 8), TK_ERR_ALIGN, "randomize_buf must be 8-byte aligned");
+    h->buf = *b;
+    h->bound = true;
+    return TK_OK;
+}
+
+int tk_humanoid_pre_physics(TkHumanoid* h, const float* actions_in, float* forces_out, int32_t clip, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(actions_in && forces_out, TK_ERR_INVALID, "null actions_in / forces_out");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    const int vec = aligned_to(actions_in, 16) && aligned_to(forces_out, 16) && aligned_to(h->buf.actions, 16);
+    const long long total4 = (static_cast<long long>(k.n) * kD + 3) / 4;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->params.device);
+    long long blocks = (total4 + 255) / 256;
+    if (blocks > static_cast<long long>(sms) * 8) blocks = static_cast<long long>(sms) * 8;
+    if (blocks < 1) blocks = 1;
+    humanoid_pre_kernel<kD><<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(k, actions_in, forces_out,
+                                                                                                         clip, vec);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_humanoid_compute_observations(TkHumanoid* h, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    humanoid_tile_kernel<kD, false><<<h->tiles, kThreads, sizeof(Smem<kD>), static_cast<cudaStream_t>(stream)>>>(k);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_humanoid_compute_reward(TkHumanoid* h, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    humanoid_reward_kernel<kD><<<(k.n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_humanoid_reset_idx(TkHumanoid* h, const int64_t* env_ids, int32_t kcount, const float* unit_pos, const float* unit_vel,
+                          void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    if (kcount == 0) return TK_OK;
+    TK_REQUIRE(kcount > 0 && env_ids && unit_pos && unit_vel, TK_ERR_INVALID, "bad reset_idx arguments");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    const int wpb = 8;
+    humanoid_reset_idx_kernel<kD><<<(kcount + wpb - 1) / wpb, wpb * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        k, reinterpret_cast<const long long*>(env_ids), kcount, unit_pos, unit_vel);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_humanoid_post_physics(TkHumanoid* h, const TkResetNoise* noise, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_CUDA(cudaSetDevice(h->params.device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    KParams k; fill_kparams(h, k);
+    if (noise) {
+        k.noise_mode = noise->mode;
+        k.unit_a = noise->unit_a; k.unit_b = noise->unit_b; k.noise_rows = noise->rows;
+        k.seed = noise->seed; k.step = noise->step; k.env_off = noise->env_id_offset;
+        if (noise->mode == TK_NOISE_COMPACT || noise->mode == TK_NOISE_DENSE)
+            TK_REQUIRE(noise->unit_a && noise->unit_b && noise->rows >= 0, TK_ERR_INVALID, "noise arrays missing");
+        TK_REQUIRE(noise->mode >= TK_NOISE_NONE && noise->mode <= TK_NOISE_PHILOX, TK_ERR_INVALID, "bad noise mode %d", noise->mode);
+    }
+    if (k.noise_mode == TK_NOISE_COMPACT) {
+        const int wpb = 8;
+        tile_reset_count_kernel<<<(h->tiles + wpb - 1) / wpb, wpb * 32, 0, st>>>(k.reset, k.n, h->tiles, h->tile_counts);
+        tile_exclusive_scan_kernel<<<1, 1024, 0, st>>>(h->tile_counts, h->tiles, h->tile_base);
+    }
+    humanoid_tile_kernel<kD, true><<<h->tiles, kThreads, sizeof(Smem<kD>), st>>>(k);
+    TK_CUDA(cudaGetLastError());
+    h->last_grid = h->tiles;
+    return TK_OK;
+}
+
+int tk_humanoid_reward_terms(TkHumanoid* h, float* terms, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(terms != nullptr, TK_ERR_INVALID, "null terms");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    const int wpb = 8;
+    humanoid_terms_kernel<kD><<<(k.n + wpb - 1) / wpb, wpb * 32, 0, static_cast<cudaStream_t>(stream)>>>(k, terms);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_humanoid_wm_reward(TkHumanoid* h, const float* obs, int64_t m, float* reward_out, void* stream) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_REQUIRE(obs && reward_out && m >= 0, TK_ERR_INVALID, "bad wm_reward arguments");
+    if (m == 0) return TK_OK;
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    humanoid_wm_reward_kernel<kD><<<static_cast<unsigned>((m + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        k, obs, m, reward_out);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_humanoid_philox_noise(TkHumanoid* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* unit_pos,
+                             float* unit_vel, void* stream) {
+    TK_REQUIRE(h && unit_pos && unit_vel, TK_ERR_INVALID, "null argument");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    const long long total = static_cast<long long>(h->params.num_envs) * kD;
+    humanoid_philox_kernel<kD><<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        h->params.num_envs, seed, step, env_id_offset, unit_pos, unit_vel);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_humanoid_stats(TkHumanoid* h, double* stats_out, int32_t accumulate, void* stream) {
+    TK_REQUIRE(h && stats_out, TK_ERR_INVALID, "null argument");
+    TK_REQUIRE(h->last_grid > 0, TK_ERR_INVALID, "tk_humanoid_post_physics has not run yet");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    stats_finalize_kernel<<<1, TK_STATS * 32, 0, static_cast<cudaStream_t>(stream)>>>(h->partials, h->last_grid, stats_out, accumulate);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+}  // extern "C"

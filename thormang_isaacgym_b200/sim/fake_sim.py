@@ -1,0 +1,83 @@
+"""Fake-sim shim: plain torch tensors standing in for the PhysX-owned buffers.
+
+The reference tasks never own their state: ``gymtorch.wrap_tensor`` hands them views of
+simulator memory (isaacgymenvs/tasks/humanoid.py:78-98, gogoro_new.py:125-138) and the
+``gymapi`` calls are device-pointer hand-offs.  PhysX / isaacgym cannot be installed here,
+so this class provides the same tensors in the same layout and the handful of calls the
+hot path makes:
+
+* ``refresh_*``                                 no-op (the tensors are always current);
+* ``set_actor_root_state_tensor_indexed(src, ids)``   row copy ``root[ids] = src[ids]``;
+* ``set_dof_state_tensor_indexed(src, ids)``    row copy unless ``src`` IS the dof-state tensor;
+* ``set_dof_actuation_force_tensor`` / ``set_dof_position_target_tensor`` /
+  ``set_dof_velocity_target_tensor``             keep a reference (``sim.actuation_force`` ...);
+* ``simulate()``                                 calls an optional user ``physics(sim)`` callback
+  (identity by default), i.e. the "fake physics" of BASELINE config 5.
+
+Any object with these attributes can be injected instead (``cfg["sim_backend"]``), e.g. a
+real simulator exposing its device buffers through ``torch.as_tensor``/DLPack.
+"""
+from typing import Callable, Dict, List, Optional
+
+import torch
+
+
+class FakeSim:
+    def __init__(self, num_envs: int, num_dof: int, device, num_sensor_floats: int = 12,
+                 dof_names: Optional[List[str]] = None, asset: Optional[Dict[str, torch.Tensor]] = None,
+                 physics: Optional[Callable[["FakeSim"], None]] = None):
+        self.num_envs, self.num_dof, self.device = num_envs, num_dof, torch.device(device)
+        f = dict(dtype=torch.float32, device=self.device)
+        self.root_states = torch.zeros((num_envs, 13), **f)
+        self.root_states[:, 6] = 1.0                     # identity quaternion (xyzw)
+        self.dof_state = torch.zeros((num_envs * num_dof, 2), **f)
+        self.dof_force = torch.zeros((num_envs, num_dof), **f)
+        self.force_sensor = torch.zeros((num_envs, num_sensor_floats), **f)
+        self.dof_names = dof_names or [f"dof_{i}" for i in range(num_dof)]
+        self.asset = {k: v.to(self.device) for k, v in (asset or {}).items()}
+        self.physics = physics
+        self.actuation_force = None
+        self.dof_position_target = None
+        self.dof_velocity_target = None
+        self.dt = None
+
+    # -- tensor API -------------------------------------------------------------------------
+    def acquire_actor_root_state_tensor(self): return self.root_states
+    def acquire_dof_state_tensor(self): return self.dof_state
+    def acquire_dof_force_tensor(self): return self.dof_force
+    def acquire_force_sensor_tensor(self): return self.force_sensor
+    def refresh_actor_root_state_tensor(self): return True
+    def refresh_dof_state_tensor(self): return True
+    def refresh_dof_force_tensor(self): return True
+    def refresh_force_sensor_tensor(self): return True
+
+    def set_actor_root_state_tensor_indexed(self, src: torch.Tensor, ids: torch.Tensor) -> bool:
+        idx = ids.long()
+        self.root_states[idx] = src[idx]
+        return True
+
+    def set_dof_state_tensor_indexed(self, src: torch.Tensor, ids: torch.Tensor) -> bool:
+        if src.data_ptr() != self.dof_state.data_ptr():
+            idx = ids.long()
+            d = self.num_dof
+            self.dof_state.view(self.num_envs, d, 2)[idx] = src.view(self.num_envs, d, 2)[idx]
+        return True
+
+    def set_dof_actuation_force_tensor(self, t): self.actuation_force = t; return True
+    def set_dof_position_target_tensor(self, t): self.dof_position_target = t; return True
+    def set_dof_velocity_target_tensor(self, t): self.dof_velocity_target = t; return True
+
+    def simulate(self):
+        if self.physics is not None:
+            self.physics(self)
+
+    def fetch_results(self, wait=True): return True
+
+    # -- helpers for tests / benches --------------------------------------------------------
+    def load_state(self, state: Dict[str, torch.Tensor]):
+        """Copy a synthetic snapshot (thormang_isaacgym_b200.synthetic) into the sim buffers."""
+        alias = {"root_states": "root_states", "root_tensor": "root_states", "dof_state": "dof_state",
+                 "state_dof": "dof_state", "dof_force": "dof_force", "sensors": "force_sensor"}
+        for key, attr in alias.items():
+            if key in state:
+                getattr(self, attr).copy_(state[key].to(self.device))

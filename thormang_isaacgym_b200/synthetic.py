@@ -45,8 +45,13 @@ def humanoid_asset(seed: int = 7, num_dof: int = HUMANOID_DOF) -> Dict[str, torc
 
 
 def humanoid_state(n: int, seed: int = 1234, asset: Dict[str, torch.Tensor] = None, dt: float = 0.0166,
-                   device="cpu", reset_frac: float = 0.01) -> Dict[str, torch.Tensor]:
-    """One post-physics snapshot for ``n`` humanoids (config 1/2/4 of BASELINE.json)."""
+                   device="cpu", reset_frac: float = 0.01, fallen_frac: float = None) -> Dict[str, torch.Tensor]:
+    """One post-physics snapshot for ``n`` humanoids (config 1/2/4 of BASELINE.json).
+
+    ``fallen_frac=None`` keeps the SURVEY 8(d) height distribution U(0.3, 1.8) (about a third below the
+    termination height: good for parity coverage).  A number puts that fraction of the torsos below 0.8 and the
+    rest in U(0.85, 1.8): the steady-state reset rate of a training run (0.1-3 % per step), used
+    by the benchmarks."""
     asset = asset if asset is not None else humanoid_asset()
     lo, hi = asset["dof_limits_lower"], asset["dof_limits_upper"]
     d = lo.shape[0]
@@ -54,6 +59,9 @@ def humanoid_state(n: int, seed: int = 1234, asset: Dict[str, torch.Tensor] = No
     root = torch.empty((n, 13), dtype=torch.float32)
     root[:, 0:2] = _u(g, (n, 2), -5.0, 5.0)
     root[:, 2] = _u(g, (n,), 0.3, 1.8)
+    if fallen_frac is not None:
+        low = torch.rand((n,), generator=g) < fallen_frac
+        root[:, 2] = torch.where(low, _u(g, (n,), 0.3, 0.79), _u(g, (n,), 0.85, 1.8))
     q = _n(g, (n, 4))
     root[:, 3:7] = q / q.norm(dim=-1, keepdim=True).clamp(min=1e-6)
     root[:, 7:10] = _n(g, (n, 3), 1.0)
