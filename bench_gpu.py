@@ -1,0 +1,278 @@
+"""GPU arm of bench.py (see bench.py for the contract).  One process per GPU; env ranges sharded per rank."""
+import json
+import math
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import bench as B   # noqa: E402  (constants, ClockSampler, CPU arm)
+
+HORIZON = 32        # PPO horizon_length of cfg/train/HumanoidPPO.yaml:66: statistics are all-reduced once per horizon
+
+
+def _make_humanoid(n, seed, device, env_off=0, stats=True):
+    import torch
+    from thormang_isaacgym_b200 import config as tcfg
+    from thormang_isaacgym_b200 import synthetic as syn
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.humanoid import Humanoid
+    asset = syn.humanoid_asset()
+    st = syn.humanoid_state(n, seed=seed, asset=asset, fallen_frac=0.01)
+    cfg = tcfg.humanoid_cfg(n, seed=1234)
+    cfg["env"]["envIdOffset"] = env_off
+    cfg["env"]["episodeStatistics"] = stats
+    sim = FakeSim(n, 21, device, num_sensor_floats=12, asset=asset)
+    sim.load_state(st)
+    cfg["sim_backend"] = sim
+    dev_index = torch.device(device).index or 0
+    env = Humanoid(cfg, device, f"cuda:{dev_index}", -1, True)
+    env.actions.copy_(st["actions"].to(device))
+    env.progress_buf.copy_(st["progress_buf"].to(device))
+    env.reset_buf.copy_(st["reset_buf"].to(device))
+    env.potentials.copy_(st["potentials"].to(device))
+    return env, st
+
+
+def _make_gogoro(n, seed, device, env_off=0):
+    import torch
+    from thormang_isaacgym_b200 import config as tcfg
+    from thormang_isaacgym_b200 import synthetic as syn
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.gogoro_new import Gogoro
+    st = syn.gogoro_state(n, seed=seed)
+    cfg = tcfg.gogoro_cfg(n, seed=1234)
+    cfg["env"]["envIdOffset"] = env_off
+    cfg["env"]["resetOnInit"] = False
+    names = ["steering_joint", "rear_wheel_joint"] + [f"j{i}" for i in range(37)]
+    sim = FakeSim(n, 39, device, num_sensor_floats=0, dof_names=names)
+    sim.load_state(st)
+    cfg["sim_backend"] = sim
+    dev_index = torch.device(device).index or 0
+    env = Gogoro(cfg, device, f"cuda:{dev_index}", -1, True)
+    for name in ("yaw_command", "curent_command", "curent_speed", "steer_offsets", "imu_offsets",
+                 "curent_speed_offset", "action_history", "progress_buf", "reset_buf", "thormang_pose"):
+        getattr(env, name).copy_(st[name].to(device))
+    return env, st
+
+
+def _rotating_sets(n, bytes_per_env):
+    per_set = n * bytes_per_env
+    return max(3, int(math.ceil(2.2 * B.L2_BYTES / per_set)))
+
+
+def _time_steps(torch, step_fn, steps, warmup, barrier=None):
+    """W untimed steps, then exactly K steps between two events on the launching stream.
+    step_fn(i) returns the number of kernels of ours it launched.  Returns (ms, launches, (t0, t1))."""
+    for i in range(warmup):
+        step_fn(i)
+    torch.cuda.synchronize()
+    if barrier:
+        barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    ev0.record()
+    launches = 0
+    for i in range(steps):
+        launches += step_fn(warmup + i)
+    ev1.record()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    if barrier:
+        barrier()
+    return ev0.elapsed_time(ev1), launches, (t0, t1)
+
+
+def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, barrier=None, horizon_hook=None):
+    """Fused post-physics kernel over rotating state sets.  Returns dict(ms_total, launches, sets, window)."""
+    bpe = B.HUMANOID_BYTES_PER_ENV if task == "humanoid" else B.GOGORO_BYTES_PER_ENV
+    sets = _rotating_sets(n, bpe)
+    make = _make_humanoid if task == "humanoid" else _make_gogoro
+    envs = [make(n, seed + 17 * s, device, env_off)[0] for s in range(sets)]
+
+    def step(i):
+        envs[i % sets].post_physics_step()
+        extra = 0
+        if horizon_hook is not None and (i + 1) % HORIZON == 0:
+            extra = horizon_hook(envs)
+        return 1 + extra
+
+    ms, launches, window = _time_steps(torch, step, steps, warmup, barrier)
+    del envs
+    return {"ms_total": ms, "launches": launches, "sets": sets, "window": window}
+
+
+def _e2e_bench(torch, n, device, steps, chunks, env_off, barrier=None):
+    """Public-API path with HOST buffers: per step H2D(state) -> fused kernel -> D2H(obs, rew, reset), chunk-pipelined."""
+    from thormang_isaacgym_b200 import synthetic as syn
+    from thormang_isaacgym_b200.host_io import ChunkedHostBridge
+    while n % chunks:
+        chunks //= 2
+    chunks = max(1, chunks)
+    bridge = ChunkedHostBridge(lambda m, off: _make_humanoid(m, 4321, device, env_off + off, stats=False)[0], n, chunks)
+    st = syn.humanoid_state(n, seed=4321, asset=syn.humanoid_asset(), fallen_frac=0.01)
+    bridge.fill_host(st)
+    for _ in range(3):
+        bridge.step()
+    bridge.synchronize()
+    torch.cuda.synchronize()
+    if barrier:
+        barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        bridge.step()
+    bridge.synchronize()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    if barrier:
+        barrier()
+    # sanity: what came back is what the kernel wrote
+    b0 = bridge.bridges[0]
+    assert torch.equal(b0.host_out["reset_buf"], b0.env.reset_buf.cpu()), "e2e read-back mismatch"
+    return {"seconds": t1 - t0, "h2d": bridge.h2d_bytes, "d2h": bridge.d2h_bytes, "chunks": chunks,
+            "launches": steps * chunks, "window": (t0, t1)}
+
+
+def _step_loop_bench(torch, n, device, horizon, reps):
+    """BASELINE config 5: pre_physics (clamp + force write) -> fake physics (identity) -> fused post_physics, PPO horizon."""
+    env, st = _make_humanoid(n, 999, device)
+    acts = [torch.rand((n, 21), device=device) * 2.4 - 1.2 for _ in range(4)]
+
+    def one(i):
+        env._clip_in_kernel = True
+        env.pre_physics_step(acts[i % 4])
+        env._clip_in_kernel = False
+        env.sim.simulate()
+        env.post_physics_step()
+        return 2
+    ms, launches, _ = _time_steps(torch, one, horizon * reps, horizon)
+    return {"envs": n, "horizon": horizon, "env_steps_per_s": n * horizon * reps / (ms * 1e-3),
+            "ms_per_step": ms / (horizon * reps), "launches_per_step": 2,
+            "note": "pre (252 B/env) + post (924 B/env) on ONE state set: L2-resident at this size, not an HBM number"}
+
+
+def run_gpu_arm(args, rank, world):
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl=ours) needs a CUDA device: the env-step path has no CPU fallback")
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    device = f"cuda:{local_rank}"
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(device))
+    barrier = (lambda: dist.barrier(device_ids=[local_rank])) if dist else None
+
+    from thormang_isaacgym_b200 import _native
+    _native.lib()   # fail loudly if the extension is missing
+
+    task, n = args.task, args.envs_per_gpu
+    bpe = B.HUMANOID_BYTES_PER_ENV if task == "humanoid" else B.GOGORO_BYTES_PER_ENV
+    sampler = B.ClockSampler(local_rank)
+    sampler.start()
+    windows = []
+
+    # ---- episode statistics: finalize per state set on device, one 8 x fp64 NCCL all-reduce per horizon (side stream)
+    side = torch.cuda.Stream(device=device)
+    reduced = torch.zeros(8, device=device, dtype=torch.float64)
+
+    def horizon_hook(envs):
+        total = None
+        for e in envs:
+            s = e.episode_statistics()
+            total = s.clone() if total is None else total + s
+        if dist:
+            done = torch.cuda.Event()
+            done.record()
+            with torch.cuda.stream(side):
+                side.wait_event(done)
+                reduced.copy_(total)
+                dist.all_reduce(reduced, op=dist.ReduceOp.SUM)
+        else:
+            reduced.copy_(total)
+        return len(envs)
+
+    res = _kernel_bench(torch, task, n, device, args.steps, max(args.warmup, 3), seed=1234 + 1000 * rank, env_off=rank * n,
+                        barrier=barrier, horizon_hook=horizon_hook)
+    windows.append(res["window"])
+    ms_local = res["ms_total"]
+    ms_t = torch.tensor([ms_local], device=device, dtype=torch.float64)
+    if dist:
+        dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
+    ms_total = float(ms_t.item())
+    value = n * world * args.steps / (ms_total * 1e-3)
+    ms_per_step = ms_total / args.steps
+
+    # ---- end-to-end through the public API with host buffers
+    e2e = None
+    if task == "humanoid" and args.e2e_steps > 0:
+        r = _e2e_bench(torch, n, device, args.e2e_steps, args.e2e_chunks, rank * n, barrier)
+        windows.append(r["window"])
+        sec = torch.tensor([r["seconds"]], device=device, dtype=torch.float64)
+        if dist:
+            dist.all_reduce(sec, op=dist.ReduceOp.MAX)
+        e2e = {"value": n * world * args.e2e_steps / float(sec.item()), "unit": "env-steps/s",
+               "h2d_bytes_per_step": r["h2d"] * world, "d2h_bytes_per_step": r["d2h"] * world,
+               "steps": args.e2e_steps, "chunks_per_gpu": r["chunks"],
+               "path": "HostBridge: pinned host state -> H2D -> Humanoid.post_physics_step() -> D2H obs/rew/reset, "
+                       "range-sharded into chunks on separate streams so PCIe copies overlap the kernels"}
+
+    sampler.stop()
+    clocks = sampler.summary(windows)
+    if rank != 0:
+        if dist:
+            dist.barrier(device_ids=[local_rank])
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = B.measured_peak_gbs()
+    achieved = n * bpe / (ms_local / args.steps * 1e-3) / 1e9
+    line = {
+        "metric": B.METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": B.workload_config(args, res["sets"]),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": B.recorded_traffic(task), "peak_source": peak_src,
+                     "kernel": "humanoid_tile_kernel<21,true>" if task == "humanoid" else "gogoro_tile_kernel<0>",
+                     "algorithmic_bytes_per_env_step": bpe,
+                     "how": "algorithmic bytes x envs per launch / (CUDA-event time of the timed region / launches), rank 0"},
+        "e2e": e2e,
+        "gpu_launches": res["launches"],
+        "clocks": clocks,
+        "stats_allreduce": {"per": f"{HORIZON} steps", "payload_bytes": 64, "backend": "nccl" if dist else "none (1 GPU)",
+                            "last": [float(x) for x in reduced.cpu().tolist()]},
+    }
+
+    if world == 1 and not args.no_cpu_baseline:
+        v, ms_cpu, done, threads = B.time_cpu(task, n, 1234, 400, 3, budget_s=args.cpu_seconds)
+        line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": threads, "kind": "port",
+                                "ms_per_step": ms_cpu,
+                                "sample": f"{done} steps x {n} envs of the same post-physics path (reset+obs+reward), "
+                                          "oracle/ torch port TorchScript-compiled like the reference, "
+                                          f"torch.set_num_threads({threads})"}
+    if world == 1 and not args.no_extras:
+        extras = {}
+        try:
+            for label, t, m in (("config2_humanoid_16384", "humanoid", 16384), ("humanoid_65536", "humanoid", 65536),
+                                ("humanoid_262144", "humanoid", 262144),
+                                ("config3_gogoro_65536", "gogoro", 65536), ("gogoro_4194304", "gogoro", 4194304)):
+                k = 300 if m <= 262144 else 60
+                r = _kernel_bench(torch, t, m, device, k, 20, seed=77)
+                b = B.HUMANOID_BYTES_PER_ENV if t == "humanoid" else B.GOGORO_BYTES_PER_ENV
+                gbs = m * b / (r["ms_total"] / k * 1e-3) / 1e9
+                extras[label] = {"env_steps_per_s": m * k / (r["ms_total"] * 1e-3), "us_per_step": 1e3 * r["ms_total"] / k,
+                                 "achieved_GBps": gbs, "frac_of_peak": gbs / peak, "rotating_sets": r["sets"]}
+            extras["config5_step_loop_131072x32"] = _step_loop_bench(torch, 131072, device, 32, 8)
+        except Exception as exc:   # extras must never cost the headline line
+            extras["error"] = repr(exc)
+        line["extras"] = extras
+    print(json.dumps(line), flush=True)
+    if dist:
+        dist.barrier(device_ids=[local_rank])
+        dist.destroy_process_group()

@@ -1,0 +1,76 @@
+"""Host <-> device staging for callers whose simulator state lives in host memory.
+
+The reference's CPU pipeline (``sim_device="cpu"``, vec_task.py:338-339 ``fetch_results``) keeps the
+state tensors on the host.  ``HostBridge`` is the public way to drive the CUDA env-step path from
+such a caller: pinned staging buffers, asynchronous copies on the task's stream, no allocation per
+step.  It is also the path ``bench.py`` times for its end-to-end (``e2e``) number: every step copies
+the step's inputs host->device, runs the fused post-physics kernel and copies the results back.
+
+To overlap the PCIe transfers with the kernel the env range can be split into ``chunks`` range
+shards, each a task object of its own on its own stream (the path has no cross-env dependence, so
+range shards reproduce the unsharded results bit for bit -- tests/test_gpu_humanoid.py).
+"""
+from typing import Dict, List
+
+import torch
+
+HUMANOID_INPUTS = ("root_states", "dof_state", "dof_force", "sensors", "actions")
+HUMANOID_OUTPUTS = ("obs_buf", "rew_buf", "reset_buf")
+
+
+class HostBridge:
+    """Pinned staging + async copies for one Humanoid task object."""
+
+    def __init__(self, env, stream: torch.cuda.Stream = None):
+        self.env = env
+        self.stream = stream or torch.cuda.Stream(device=env.device)
+        self.dev_in: Dict[str, torch.Tensor] = {
+            "root_states": env.root_states, "dof_state": env.dof_state, "dof_force": env.dof_force_tensor,
+            "sensors": env.vec_sensor_tensor, "actions": env.actions}
+        self.dev_out: Dict[str, torch.Tensor] = {k: getattr(env, k) for k in HUMANOID_OUTPUTS}
+        self.host_in = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in self.dev_in.items()}
+        self.host_out = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in self.dev_out.items()}
+        self.h2d_bytes = sum(v.numel() * v.element_size() for v in self.host_in.values())
+        self.d2h_bytes = sum(v.numel() * v.element_size() for v in self.host_out.values())
+
+    def fill_host(self, state: Dict[str, torch.Tensor]):
+        """Copy a host-side snapshot (synthetic.humanoid_state keys) into the pinned input buffers."""
+        for k in HUMANOID_INPUTS:
+            self.host_in[k].copy_(state[k].view(self.host_in[k].shape))
+
+    def step(self):
+        """H2D of the inputs, fused post-physics kernel, D2H of obs / reward / reset -- all async on ``stream``."""
+        with torch.cuda.stream(self.stream):
+            for k, dst in self.dev_in.items():
+                dst.copy_(self.host_in[k], non_blocking=True)
+            self.env.post_physics_step()
+            for k, src in self.dev_out.items():
+                self.host_out[k].copy_(src, non_blocking=True)
+
+    def synchronize(self):
+        self.stream.synchronize()
+
+
+class ChunkedHostBridge:
+    """Range-shard ``n`` envs into ``chunks`` task objects, one stream each, so copies overlap the kernels."""
+
+    def __init__(self, make_env, n: int, chunks: int):
+        assert n % chunks == 0, "env count must divide into the chunks"
+        self.per = n // chunks
+        self.bridges: List[HostBridge] = [HostBridge(make_env(self.per, c * self.per)) for c in range(chunks)]
+        self.h2d_bytes = sum(b.h2d_bytes for b in self.bridges)
+        self.d2h_bytes = sum(b.d2h_bytes for b in self.bridges)
+
+    def fill_host(self, state: Dict[str, torch.Tensor], num_dof: int = 21):
+        for c, b in enumerate(self.bridges):
+            lo, hi = c * self.per, (c + 1) * self.per
+            sub = {k: (state[k][lo * num_dof:hi * num_dof] if k == "dof_state" else state[k][lo:hi]) for k in HUMANOID_INPUTS}
+            b.fill_host(sub)
+
+    def step(self):
+        for b in self.bridges:
+            b.step()
+
+    def synchronize(self):
+        for b in self.bridges:
+            b.synchronize()
