@@ -15,7 +15,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libthormang_b200.so")
 SOURCES = ["tk_common.cu", "tk_humanoid.cu", "tk_gogoro.cu"]
-HEADERS = ["tk_common.cuh", os.path.join("..", "..", "include", "thormang_b200.h")]
+HEADERS = ["tk_common.cuh", "tk_humanoid_tile.cuh", os.path.join("..", "..", "include", "thormang_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

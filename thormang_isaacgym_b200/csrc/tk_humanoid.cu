@@ -7,18 +7,19 @@
 //
 // Data layout in HBM is Isaac Gym's (AoS): root_states [N,13], dof_state [N*D,2], dof_force [N,D],
 // sensors [N,12], actions [N,D], obs_buf [N,110].  The fused post-physics kernel is a pure
-// streaming kernel (924 B / env-step, ~0.3 flop/B): one CTA owns a tile of kTile consecutive
-// envs, whose slice of EVERY array is one contiguous, 16-byte aligned byte range.
-//   * inputs are read with coalesced 128-bit streaming loads and scattered into the
-//     shared-memory image of the tile's obs rows (scaled copies = 96 of the 110 columns);
-//   * the 14 columns that need the torso math are computed one env per thread from a
+// streaming kernel (924 B / env-step, ~0.3 flop/B): one CTA owns a tile of T consecutive
+// envs, whose slice of EVERY array is one contiguous, 16-byte aligned byte range (tk_humanoid_tile.cuh).
+//   * the tile's inputs arrive as five cp.async.bulk (TMA) global->shared copies on one mbarrier;
+//   * scaled copies (96 of the 110 columns) go shared->shared into the image of the tile's obs rows;
+//   * the 14 columns that need the torso math are computed one env per thread from the
 //     shared-memory copy of the root rows (stride 13 words: bank-conflict free);
-//   * the finished [kTile,110] tile leaves as ONE cp.async.bulk (TMA) shared->global store;
+//   * the finished [T,110] tile leaves as ONE cp.async.bulk (TMA) shared->global store;
 //   * per-task constants (limits, 1/range, efforts) are staged once in shared memory;
 //   * per-env flags/potentials/reward are coalesced 4/8-byte accesses, one env per thread.
 // No tensor cores: nothing on this path is a contraction.
 #include "tk_common.cuh"
 
+#include <cstdlib>
 #include <new>
 
 namespace tk {
@@ -26,9 +27,7 @@ namespace humanoid {
 
 constexpr int kRoot = 13;
 constexpr int kSensor = 12;
-constexpr int kTile = 128;      // envs per CTA
-constexpr int kThreads = 128;   // one env per thread in the torso-math phase
-constexpr int kWarps = kThreads / 32;
+constexpr int kDefaultTile = 64;   // envs per CTA == threads per CTA (TK_HUMANOID_TILE = 32 | 64 | 128 overrides)
 
 template <int D>
 struct Layout {
@@ -126,291 +125,23 @@ __device__ __forceinline__ Head torso_math(const float* r, const KParams& p) {
 
 __device__ __forceinline__ float unscale_ref(float x, float lo, float hi) { return (2.0f * x - hi - lo) / (hi - lo); }
 
-// ---------------------------------------------------------------------------------------------
-// fused kernel.  FUSED = post_physics_step (progress++, reset prologue, obs, reward, masks, stats);
-//               !FUSED = compute_observations only.
-// ---------------------------------------------------------------------------------------------
-template <int D>
-struct Smem {
-    static constexpr int kObs = Layout<D>::kObs;
-    alignas(128) float obs[kTile * kObs];
-    alignas(16) float root[kTile * kRoot];
-    float lo[D], hi[D];
-    unsigned ballots[kWarps];
-    float wsum[kWarps][TK_STATS];
-};
+}  // namespace humanoid
+}  // namespace tk
 
-template <int D, bool FUSED>
-__global__ void __launch_bounds__(kThreads) humanoid_tile_kernel(const __grid_constant__ KParams p) {
-    using L = Layout<D>;
-    constexpr int OBS = L::kObs;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    Smem<D>& s = *reinterpret_cast<Smem<D>*>(smem_raw);
+#include "tk_humanoid_tile.cuh"
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int env0 = blockIdx.x * kTile;
-    const int nt = min(kTile, p.n - env0);
-    const int n = env0 + tid;
-    const bool valid = tid < nt;
-    const bool vec = p.vec_ok != 0;
-
-    if (tid < D) { s.lo[tid] = p.lo[tid]; s.hi[tid] = p.hi[tid]; }
-
-    // ---- per-env flags (coalesced 8-byte accesses)
-    long long prog = 0;
-    bool do_reset = false;
-    if (FUSED) {
-        if (valid) {
-            prog = p.progress[n] + 1;                              // :288
-            do_reset = p.reset[n] != 0;                            // :291
-            if (p.randomize) p.randomize[n] += 1;                  // :289
-        }
-        unsigned b = __ballot_sync(0xffffffffu, do_reset);
-        if (lane == 0) s.ballots[warp] = b;
-    }
-    float pot_old = 0.0f;
-    if (valid) pot_old = p.pot[n];
-
-    // ---- root rows -> shared (flat copy)
-    {
-        const float* src = p.root + static_cast<size_t>(env0) * kRoot;
-        const int cnt = nt * kRoot;
-        if (vec) {
-            const int c4 = cnt >> 2;
-            for (int i = tid; i < c4; i += kThreads) reinterpret_cast<float4*>(s.root)[i] = ld_stream4(src + 4 * i);
-            for (int i = (c4 << 2) + tid; i < cnt; i += kThreads) s.root[i] = src[i];
-        } else {
-            for (int i = tid; i < cnt; i += kThreads) s.root[i] = src[i];
-        }
-    }
-    __syncthreads();   // s.lo/s.hi, ballots visible
-
-    // ---- dof_state (pos,vel interleaved) -> obs columns kPos.., kVel..
-    {
-        const float* src = p.dof_state + static_cast<size_t>(env0) * D * 2;
-        const int cnt = nt * D;   // (pos,vel) pairs
-        const float dvs = p.dof_vel_scale;
-        if (vec) {
-            const int c2 = cnt >> 1;
-#pragma unroll 4
-            for (int i = tid; i < c2; i += kThreads) {
-                float4 v = ld_stream4(src + 4 * i);
-                int e0 = 2 * i, n0 = e0 / D, j0 = e0 - n0 * D;
-                int e1 = e0 + 1, n1 = e1 / D, j1 = e1 - n1 * D;
-                s.obs[n0 * OBS + L::kPos + j0] = unscale_ref(v.x, s.lo[j0], s.hi[j0]);
-                s.obs[n0 * OBS + L::kVel + j0] = v.y * dvs;
-                s.obs[n1 * OBS + L::kPos + j1] = unscale_ref(v.z, s.lo[j1], s.hi[j1]);
-                s.obs[n1 * OBS + L::kVel + j1] = v.w * dvs;
-            }
-            if ((cnt & 1) && tid == 0) {
-                int e0 = cnt - 1, n0 = e0 / D, j0 = e0 - n0 * D;
-                s.obs[n0 * OBS + L::kPos + j0] = unscale_ref(src[2 * e0], s.lo[j0], s.hi[j0]);
-                s.obs[n0 * OBS + L::kVel + j0] = src[2 * e0 + 1] * dvs;
-            }
-        } else {
-            for (int e0 = tid; e0 < cnt; e0 += kThreads) {
-                int n0 = e0 / D, j0 = e0 - n0 * D;
-                s.obs[n0 * OBS + L::kPos + j0] = unscale_ref(src[2 * e0], s.lo[j0], s.hi[j0]);
-                s.obs[n0 * OBS + L::kVel + j0] = src[2 * e0 + 1] * dvs;
-            }
-        }
-    }
-    // ---- dof_force * contact_force_scale -> kForce.. ; actions -> kAct..
-    {
-        const float* srcf = p.dof_force + static_cast<size_t>(env0) * D;
-        const float* srca = p.actions + static_cast<size_t>(env0) * D;
-        const int cnt = nt * D;
-        const float cfs = p.contact_scale;
-        if (vec) {
-            const int c4 = cnt >> 2;
-#pragma unroll 2
-            for (int i = tid; i < c4; i += kThreads) {
-                float4 f = ldg_stream4(srcf + 4 * i);
-                float4 a = ldg_stream4(srca + 4 * i);
-                const float fv[4] = {f.x, f.y, f.z, f.w};
-                const float av[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    int e = 4 * i + k, nn = e / D, j = e - nn * D;
-                    s.obs[nn * OBS + L::kForce + j] = fv[k] * cfs;
-                    s.obs[nn * OBS + L::kAct + j] = av[k];
-                }
-            }
-            for (int e = (c4 << 2) + tid; e < cnt; e += kThreads) {
-                int nn = e / D, j = e - nn * D;
-                s.obs[nn * OBS + L::kForce + j] = srcf[e] * cfs;
-                s.obs[nn * OBS + L::kAct + j] = srca[e];
-            }
-        } else {
-            for (int e = tid; e < cnt; e += kThreads) {
-                int nn = e / D, j = e - nn * D;
-                s.obs[nn * OBS + L::kForce + j] = srcf[e] * cfs;
-                s.obs[nn * OBS + L::kAct + j] = srca[e];
-            }
-        }
-    }
-    // ---- force sensors * contact_force_scale -> kSens..
-    {
-        const float* src = p.sensors + static_cast<size_t>(env0) * kSensor;
-        const int cnt = nt * kSensor;   // always a multiple of 4
-        const float cfs = p.contact_scale;
-        if (vec) {
-            for (int i = tid; i < (cnt >> 2); i += kThreads) {
-                float4 v = ldg_stream4(src + 4 * i);
-                int e = 4 * i, nn = e / kSensor, k = e - nn * kSensor;
-                float* dst = &s.obs[nn * OBS + L::kSens + k];
-                dst[0] = v.x * cfs; dst[1] = v.y * cfs; dst[2] = v.z * cfs; dst[3] = v.w * cfs;
-            }
-        } else {
-            for (int e = tid; e < cnt; e += kThreads) {
-                int nn = e / kSensor, k = e - nn * kSensor;
-                s.obs[nn * OBS + L::kSens + k] = src[e] * cfs;
-            }
-        }
-    }
-
-    // ---- reset prologue (rare): reset_idx :253-279 for the tile's flagged envs, one warp per env
-    if (FUSED) {
-        __syncthreads();   // staged tile complete before it is patched
-        const unsigned mine = s.ballots[warp];
-        if (mine) {
-            int rank = (p.noise_mode == TK_NOISE_COMPACT) ? p.tile_rank_base[blockIdx.x] : 0;
-            for (int w = 0; w < warp; ++w) rank += __popc(s.ballots[w]);
-            unsigned bits = mine;
-            while (bits) {
-                const int le = __ffs(bits) - 1;
-                bits &= bits - 1;
-                const int e = warp * 32 + le;
-                const int ne = env0 + e;
-                const long long row = (p.noise_mode == TK_NOISE_COMPACT) ? rank : ne;
-                ++rank;
-                for (int j = lane; j < D; j += 32) {
-                    float ua = 0.5f, ub = 0.5f;
-                    if (p.noise_mode == TK_NOISE_PHILOX) {
-                        Philox4 r = philox_env(p.seed, p.step, p.env_off + ne, static_cast<uint32_t>(j >> 1));
-                        ua = u01((j & 1) ? r.z : r.x);
-                        ub = u01((j & 1) ? r.w : r.y);
-                    } else if (p.noise_mode != TK_NOISE_NONE && row < p.noise_rows) {
-                        ua = p.unit_a[row * D + j];
-                        ub = p.unit_b[row * D + j];
-                    }
-                    float positions = 0.4f * ua + (-0.2f);                         // :258 torch_rand_float(-0.2, 0.2)
-                    float velocities = 0.2f * ub + (-0.1f);                        // :259 torch_rand_float(-0.1, 0.1)
-                    float np_ = p.init_dof_pos[static_cast<size_t>(ne) * D + j] + positions;
-                    np_ = fmaxf(fminf(np_, s.hi[j]), s.lo[j]);                     // :261 tensor_clamp
-                    float2* ds = reinterpret_cast<float2*>(p.dof_state) + (static_cast<size_t>(ne) * D + j);
-                    *ds = make_float2(np_, velocities);                            // :261-262 (through the strided views)
-                    s.obs[e * OBS + L::kPos + j] = unscale_ref(np_, s.lo[j], s.hi[j]);
-                    s.obs[e * OBS + L::kVel + j] = velocities * p.dof_vel_scale;
-                }
-                if (lane < kRoot) {                                                // :265-267 root row <- initial_root_states
-                    float v = p.init_root[static_cast<size_t>(ne) * kRoot + lane];
-                    p.root[static_cast<size_t>(ne) * kRoot + lane] = v;
-                    s.root[e * kRoot + lane] = v;
-                }
-            }
-        }
-    }
-    __syncthreads();
-
-    // ---- torso math, one env per thread
-    float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_up = 0.f, st_head = 0.f;
-    bool out_reset = false, out_timeout = false;
-    if (valid) {
-        float r[kRoot];
-#pragma unroll
-        for (int c = 0; c < kRoot; ++c) r[c] = s.root[tid * kRoot + c];
-        Head h = torso_math(r, p);
-        // after a reset potentials = prev_potentials = -|targets - initial_pos| / dt (:273-276): the root row now IS
-        // the initial row, so that value equals the freshly computed potential
-        const float prev_new = (FUSED && do_reset) ? h.pot : pot_old;              // :394
-        float* o = &s.obs[tid * OBS];
-#pragma unroll
-        for (int c = 0; c < 12; ++c) o[c] = h.c[c];
-        o[L::kPot] = h.pot / 60000.0f;                                             // :414
-        o[L::kPot + 1] = prev_new / 60000.0f;
-        p.pot[n] = h.pot;
-        p.prev_pot[n] = prev_new;
-        if (p.up_vec) { p.up_vec[n * 3 + 0] = h.up.x; p.up_vec[n * 3 + 1] = h.up.y; p.up_vec[n * 3 + 2] = h.up.z; }
-        if (p.heading_vec) {
-            p.heading_vec[n * 3 + 0] = h.heading.x; p.heading_vec[n * 3 + 1] = h.heading.y; p.heading_vec[n * 3 + 2] = h.heading.z;
-        }
-        if (FUSED) {
-            if (do_reset) prog = 0;                                                // :278 (reset_buf -> 0, :279)
-            // compute_humanoid_reward :349-350, :362-374 (live formula: alive + up)
-            float up_reward = (h.c[10] > 0.93f) ? (0.0f + p.up_weight) : 0.0f;
-            float total = 2.0f + up_reward;
-            const bool fallen = h.c[0] < p.termination_height;
-            if (fallen) total = 1.0f * p.death_cost;
-            const bool finished = static_cast<float>(prog) >= p.max_episode_length - 1.0f;
-            out_reset = fallen || finished;
-            out_timeout = finished && out_reset;                                    // vec_task.py:345
-            p.rew[n] = total;
-            p.reset[n] = out_reset ? 1 : 0;
-            p.progress[n] = prog;
-            if (p.timeout) p.timeout[n] = out_timeout ? 1 : 0;
-            st_rew = total; st_up = h.c[10]; st_head = h.c[11];
-            if (p.ep_return) {
-                float ret = (do_reset ? 0.0f : p.ep_return[n]) + total;
-                if (out_reset) st_ret = ret;
-                p.ep_return[n] = ret;
-            }
-            if (out_reset) st_len = static_cast<float>(prog);
-        }
-    }
-
-    // ---- statistics partials (fixed reduction order -> deterministic)
-    if (FUSED) {
-        const unsigned m_reset = __ballot_sync(0xffffffffu, out_reset);
-        const unsigned m_to = __ballot_sync(0xffffffffu, out_timeout);
-        const unsigned m_valid = __ballot_sync(0xffffffffu, valid);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            st_rew += __shfl_xor_sync(0xffffffffu, st_rew, o);
-            st_ret += __shfl_xor_sync(0xffffffffu, st_ret, o);
-            st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
-            st_up += __shfl_xor_sync(0xffffffffu, st_up, o);
-            st_head += __shfl_xor_sync(0xffffffffu, st_head, o);
-        }
-        if (lane == 0) {
-            float* w = s.wsum[warp];
-            w[0] = st_rew; w[1] = static_cast<float>(__popc(m_reset)); w[2] = static_cast<float>(__popc(m_to));
-            w[3] = st_ret; w[4] = st_len; w[5] = st_up; w[6] = st_head; w[7] = static_cast<float>(__popc(m_valid));
-        }
-    }
-    fence_proxy_async_smem();   // obs tile written through the generic proxy, read by the bulk-copy engine
-    __syncthreads();
-
-    if (FUSED && tid < TK_STATS) {
-        double acc = 0.0;
-#pragma unroll
-        for (int w = 0; w < kWarps; ++w) acc += static_cast<double>(s.wsum[w][tid]);
-        p.partials[static_cast<size_t>(blockIdx.x) * TK_STATS + tid] += acc;   // running sum since the last tk_*_stats
-    }
-
-    // ---- obs tile -> global
-    float* dst = p.obs + static_cast<size_t>(env0) * OBS;
-    const int cnt = nt * OBS;
-    if (vec && (cnt & 3) == 0) {
-        if (tid == 0) {
-            bulk_store(dst, s.obs, static_cast<uint32_t>(cnt) * 4u);
-            bulk_commit();
-            bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
-        }
-    } else {
-        for (int i = tid; i < cnt; i += kThreads) dst[i] = s.obs[i];
-    }
-}
+namespace tk {
+namespace humanoid {
 
 // ---------------------------------------------------------------------------------------------
 // COMPACT noise order: exclusive prefix of the per-tile reset counts (two tiny kernels)
 // ---------------------------------------------------------------------------------------------
-__global__ void tile_reset_count_kernel(const long long* __restrict__ reset, int n, int tiles, int* __restrict__ counts) {
+__global__ void tile_reset_count_kernel(const long long* __restrict__ reset, int n, int tiles, int tile, int* __restrict__ counts) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= tiles) return;
     int c = 0;
-    for (int i = lane; i < kTile; i += 32) {
-        int e = warp * kTile + i;
+    for (int i = lane; i < tile; i += 32) {
+        int e = warp * tile + i;
         if (e < n && reset[e] != 0) ++c;
     }
 #pragma unroll
@@ -633,6 +364,7 @@ struct TkHumanoid {
     TkHumanoidParams params;
     TkHumanoidBuffers buf;
     bool bound;
+    int tile;             // envs per CTA (32 | 64 | 128)
     int tiles;
     double* partials;     // [tiles, TK_STATS]
     int* tile_counts;     // [tiles]
@@ -641,6 +373,31 @@ struct TkHumanoid {
 };
 
 static constexpr int kD = 21;
+
+template <int T>
+static cudaError_t set_attr_for() {
+    cudaError_t e = cudaFuncSetAttribute(humanoid_tile_kernel<kD, T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(sizeof(TileSmem<kD, T>)));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(humanoid_tile_kernel<kD, T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(sizeof(TileSmem<kD, T>)));
+    return e;
+}
+static cudaError_t set_tile_attributes() {
+    cudaError_t e = set_attr_for<32>();
+    if (e == cudaSuccess) e = set_attr_for<64>();
+    if (e == cudaSuccess) e = set_attr_for<128>();
+    return e;
+}
+
+template <bool FUSED>
+static void launch_tile(const TkHumanoid* h, const KParams& k, cudaStream_t st) {
+    switch (h->tile) {
+        case 32: humanoid_tile_kernel<kD, 32, FUSED><<<h->tiles, 32, sizeof(TileSmem<kD, 32>), st>>>(k); break;
+        case 128: humanoid_tile_kernel<kD, 128, FUSED><<<h->tiles, 128, sizeof(TileSmem<kD, 128>), st>>>(k); break;
+        default: humanoid_tile_kernel<kD, 64, FUSED><<<h->tiles, 64, sizeof(TileSmem<kD, 64>), st>>>(k); break;
+    }
+}
 
 static void fill_kparams(const TkHumanoid* h, KParams& k) {
     const TkHumanoidParams& P = h->params;
@@ -686,7 +443,12 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "out of host memory");
     h->params = *params;
     h->bound = false;
-    h->tiles = (params->num_envs + kTile - 1) / kTile;
+    h->tile = kDefaultTile;
+    if (const char* env = getenv("TK_HUMANOID_TILE")) {
+        const int t = atoi(env);
+        if (t == 32 || t == 64 || t == 128) h->tile = t;
+    }
+    h->tiles = (params->num_envs + h->tile - 1) / h->tile;
     h->last_grid = 0;
     h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * h->tiles);
@@ -694,12 +456,7 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     if (e == cudaSuccess) e = cudaMalloc(&h->tile_base, sizeof(int) * h->tiles);
     if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * h->tiles);
     if (e == cudaSuccess) e = cudaMemset(h->tile_base, 0, sizeof(int) * h->tiles);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(humanoid_tile_kernel<kD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(sizeof(Smem<kD>)));
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(humanoid_tile_kernel<kD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(sizeof(Smem<kD>)));
+    if (e == cudaSuccess) e = set_tile_attributes();
     if (e != cudaSuccess) {
         cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base);
         delete h;
@@ -759,7 +516,7 @@ int tk_humanoid_compute_observations(TkHumanoid* h, void* stream) {
     if (int rc = check_bound(h)) return rc;
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
-    humanoid_tile_kernel<kD, false><<<h->tiles, kThreads, sizeof(Smem<kD>), static_cast<cudaStream_t>(stream)>>>(k);
+    launch_tile<false>(h, k, static_cast<cudaStream_t>(stream));
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
@@ -802,10 +559,10 @@ int tk_humanoid_post_physics(TkHumanoid* h, const TkResetNoise* noise, void* str
     }
     if (k.noise_mode == TK_NOISE_COMPACT) {
         const int wpb = 8;
-        tile_reset_count_kernel<<<(h->tiles + wpb - 1) / wpb, wpb * 32, 0, st>>>(k.reset, k.n, h->tiles, h->tile_counts);
+        tile_reset_count_kernel<<<(h->tiles + wpb - 1) / wpb, wpb * 32, 0, st>>>(k.reset, k.n, h->tiles, h->tile, h->tile_counts);
         tile_exclusive_scan_kernel<<<1, 1024, 0, st>>>(h->tile_counts, h->tiles, h->tile_base);
     }
-    humanoid_tile_kernel<kD, true><<<h->tiles, kThreads, sizeof(Smem<kD>), st>>>(k);
+    launch_tile<true>(h, k, st);
     TK_CUDA(cudaGetLastError());
     h->last_grid = h->tiles;
     return TK_OK;
