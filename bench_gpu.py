@@ -178,23 +178,15 @@ def run_gpu_arm(args, rank, world):
     windows = []
 
     # ---- episode statistics: finalize per state set on device, one 8 x fp64 NCCL all-reduce per horizon (side stream)
-    side = torch.cuda.Stream(device=device)
-    reduced = torch.zeros(8, device=device, dtype=torch.float64)
+    from thormang_isaacgym_b200.parallel import EpisodeStatsReducer
+    reducer = EpisodeStatsReducer(device)
+    local_total = torch.zeros(8, device=device, dtype=torch.float64)
 
     def horizon_hook(envs):
-        total = None
+        local_total.zero_()
         for e in envs:
-            s = e.episode_statistics()
-            total = s.clone() if total is None else total + s
-        if dist:
-            done = torch.cuda.Event()
-            done.record()
-            with torch.cuda.stream(side):
-                side.wait_event(done)
-                reduced.copy_(total)
-                dist.all_reduce(reduced, op=dist.ReduceOp.SUM)
-        else:
-            reduced.copy_(total)
+            local_total.add_(e.episode_statistics())
+        reducer.launch(local_total)      # side stream; NCCL all-reduce when world > 1
         return len(envs)
 
     res = _kernel_bench(torch, task, n, device, args.steps, max(args.warmup, 3), seed=1234 + 1000 * rank, env_off=rank * n,
@@ -246,7 +238,7 @@ def run_gpu_arm(args, rank, world):
         "gpu_launches": res["launches"],
         "clocks": clocks,
         "stats_allreduce": {"per": f"{HORIZON} steps", "payload_bytes": 64, "backend": "nccl" if dist else "none (1 GPU)",
-                            "last": [float(x) for x in reduced.cpu().tolist()]},
+                            "last": reducer.result()},
     }
 
     if world == 1 and not args.no_cpu_baseline:

@@ -73,6 +73,7 @@ def make_humanoid_pair(n, seed=1234, device="cuda:0", state=None, asset=None, st
     asset = asset or syn.humanoid_asset()
     state = state or syn.humanoid_state(n, seed=seed, asset=asset)
     cfg = tcfg.humanoid_cfg(n, seed=seed)
+    cfg["env"]["trackRandomizeBuf"] = True
     cfg["env"].update(env_over)
     sim = FakeSim(n, 21, device, num_sensor_floats=12, asset=asset)
     sim.load_state(state)

@@ -1,0 +1,104 @@
+"""world_size-2 gloo test (CPU) of the N > 1 host logic: env-range sharding, global-env-id offsets and the
+episode-statistics all-reduce.  The per-rank math is the CPU oracle (this is a test; the product kernels need a GPU):
+sharded outputs concatenated == unsharded outputs bit for bit, reduced statistics == single-process sums."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from thormang_isaacgym_b200 import parallel as par
+
+
+def test_shard_range_partitions_exactly():
+    for total in (1, 7, 4096, 1_000_003):
+        for world in (1, 2, 3, 8):
+            edges = [par.shard_range(total, r, world) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == total
+            assert all(edges[i][1] == edges[i + 1][0] for i in range(world - 1))
+            sizes = [b - a for a, b in edges]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        par.shard_range(10, 2, 2)
+    cfg = {"env": {"numEnvs": 1048576}}
+    par.shard_cfg(cfg, 3, 8)
+    assert cfg["env"] == {"numEnvs": 131072, "envIdOffset": 393216}
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _humanoid_step(state, asset, noise, lo, hi):
+    from oracle import humanoid_oracle as ho
+    from thormang_isaacgym_b200 import config as tcfg
+    n = hi - lo
+    d = 21
+    sub = {k: (v[lo * d:hi * d].clone() if k == "dof_state" else v[lo:hi].clone()) for k, v in state.items()}
+    orc = ho.HumanoidOracle(ho.HumanoidConsts.from_cfg(tcfg.humanoid_cfg(n)), sub["root_states"], sub["dof_state"],
+                            sub["dof_force"], sub["sensors"], asset["dof_limits_lower"], asset["dof_limits_upper"],
+                            asset["motor_efforts"])
+    orc.actions, orc.progress_buf, orc.reset_buf, orc.potentials = (sub["actions"], sub["progress_buf"], sub["reset_buf"],
+                                                                    sub["potentials"])
+    # dense noise rows by GLOBAL env id -> compact rows for this shard (what Philox keyed by global id gives each env)
+    ids = orc.reset_buf.nonzero().flatten()
+    ua, ub = noise[0][lo:hi][ids], noise[1][lo:hi][ids]
+    orc.post_physics_step(ua if len(ids) else noise[0][:1], ub if len(ids) else noise[1][:1])
+    timeout = (orc.progress_buf >= 999) & (orc.reset_buf != 0)
+    stats = torch.tensor([orc.rew_buf.double().sum(), (orc.reset_buf != 0).sum(), timeout.sum(), 0.0,
+                          orc.progress_buf[orc.reset_buf != 0].sum(), orc.obs_buf[:, 10].double().sum(),
+                          orc.obs_buf[:, 11].double().sum(), n], dtype=torch.float64)
+    return orc, stats
+
+
+def _worker(rank, world, port, total, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    from thormang_isaacgym_b200 import synthetic as syn
+    asset = syn.humanoid_asset()
+    state = syn.humanoid_state(total, seed=1234, asset=asset)
+    noise = syn.humanoid_reset_noise(total, seed=5)
+    lo, hi = par.shard_range(total, rank, world)
+    orc, stats = _humanoid_step(state, asset, noise, lo, hi)
+    red = par.EpisodeStatsReducer("cpu")
+    red.launch(stats)
+    res = red.result()
+    torch.save({"obs": orc.obs_buf, "rew": orc.rew_buf, "reset": orc.reset_buf, "dof": orc.dof_state, "stats": res,
+                "range": (lo, hi)}, os.path.join(out_dir, f"rank{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_sharding_and_allreduce(tmp_path):
+    total, world = 1001, 2          # odd total: ragged shards
+    port = _free_port()
+    mp.spawn(_worker, args=(world, port, total, str(tmp_path)), nprocs=world, join=True)
+    from thormang_isaacgym_b200 import synthetic as syn
+    asset = syn.humanoid_asset()
+    state = syn.humanoid_state(total, seed=1234, asset=asset)
+    noise = syn.humanoid_reset_noise(total, seed=5)
+    full, full_stats = _humanoid_step(state, asset, noise, 0, total)
+    parts = [torch.load(os.path.join(str(tmp_path), f"rank{r}.pt"), weights_only=False) for r in range(world)]
+    assert parts[0]["range"] == (0, 501) and parts[1]["range"] == (501, 1001)
+    # torch's CPU kernels take a vector (SLEEF) or a scalar (libm) path depending on where a row falls in the
+    # tensor, so even the reference is only ulp-level shard-invariant on the CPU; the CUDA kernels are exactly
+    # shard-invariant (tests/test_gpu_humanoid.py::test_full_size_properties).
+    import parity_util as U
+    U.humanoid_obs_close(torch.cat([p["obs"] for p in parts]), full.obs_buf, "sharded obs")
+    assert torch.equal(torch.cat([p["rew"] for p in parts]), full.rew_buf)
+    assert torch.equal(torch.cat([p["reset"] for p in parts]), full.reset_buf)
+    assert torch.equal(torch.cat([p["dof"] for p in parts]), full.dof_state)
+    for p in parts:   # every rank holds the same, global, statistics
+        got = torch.tensor([p["stats"][k] for k in par.STAT_NAMES], dtype=torch.float64)
+        torch.testing.assert_close(got, full_stats, rtol=1e-9, atol=1e-4)
+        assert got[1] == full_stats[1] and got[2] == full_stats[2] and got[4] == full_stats[4]
+        assert p["stats"]["env_steps"] == total
+        assert abs(p["stats"]["mean_reward"] - float(full.rew_buf.double().mean())) < 1e-9

@@ -187,6 +187,15 @@ __device__ __forceinline__ float normalize_angle_ref(float x) {
     sincosf(x, &s, &c);
     return atan2f(s, c);
 }
+// normalize_angle (atan2(sin x, cos x)) for |x| < 3*pi without the three transcendentals: wrap by +-2*pi.
+// Differs from the sin/cos/atan2 sequence by the rounding of fl(2*pi) (1.7e-7) plus one ulp -- the same order as
+// the libm-vs-CUDA difference of that sequence itself; at exactly +-pi the representative may differ by 2*pi
+// (parity compares angles modulo 2*pi).
+__device__ __forceinline__ float normalize_angle_fast(float x) {
+    x = (x > kPi) ? x - kTwoPi : x;
+    x = (x < -kPi) ? x + kTwoPi : x;
+    return x;
+}
 // roll and yaw of get_euler_xyz (pitch is never consumed on the hot path)
 __device__ __forceinline__ void euler_roll_yaw_ref(Q4 q, float* roll, float* yaw) {
     float sinr_cosp = 2.0f * (q.w * q.x + q.y * q.z);

@@ -27,7 +27,6 @@ namespace humanoid {
 
 constexpr int kRoot = 13;
 constexpr int kSensor = 12;
-constexpr int kDefaultTile = 64;   // envs per CTA == threads per CTA (TK_HUMANOID_TILE = 32 | 64 | 128 overrides)
 
 template <int D>
 struct Layout {
@@ -75,6 +74,7 @@ struct KParams {
     float death_cost, termination_height, max_episode_length, clip_actions, max_motor_effort;
     float tgt[3], isr[4], b0[3], b1[3];
     float lo[TK_MAX_DOF], hi[TK_MAX_DOF], effort[TK_MAX_DOF];
+    float rinv[TK_MAX_DOF];     // 1 / (hi - lo), rounded to fp32 on the host
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -115,14 +115,18 @@ __device__ __forceinline__ Head torso_math(const float* r, const KParams& p) {
     h.c[0] = pos.z;
     h.c[1] = vel_loc.x; h.c[2] = vel_loc.y; h.c[3] = vel_loc.z;
     h.c[4] = angvel_loc.x * p.ang_vel_scale; h.c[5] = angvel_loc.y * p.ang_vel_scale; h.c[6] = angvel_loc.z * p.ang_vel_scale;
-    h.c[7] = normalize_angle_ref(yaw);
-    h.c[8] = normalize_angle_ref(roll);
-    h.c[9] = normalize_angle_ref(att);
+    h.c[7] = normalize_angle_fast(yaw);
+    h.c[8] = normalize_angle_fast(roll);
+    h.c[9] = normalize_angle_fast(att);
     h.c[10] = up_proj;
     h.c[11] = heading_proj;
     return h;
 }
 
+// unscale (humanoid.py:406): (2x - hi - lo) / (hi - lo).  The numerator is formed exactly as the reference does;
+// the division is a multiplication by the host-rounded reciprocal (<= 1.5 ulp from the IEEE quotient, i.e. 2e-7
+// relative: far inside the 1e-5 parity tolerance, and no threshold of the live reward reads these columns).
+__device__ __forceinline__ float unscale_fast(float x, float lo, float hi, float rinv) { return (2.0f * x - hi - lo) * rinv; }
 __device__ __forceinline__ float unscale_ref(float x, float lo, float hi) { return (2.0f * x - hi - lo) / (hi - lo); }
 
 }  // namespace humanoid
@@ -364,7 +368,6 @@ struct TkHumanoid {
     TkHumanoidParams params;
     TkHumanoidBuffers buf;
     bool bound;
-    int tile;             // envs per CTA (32 | 64 | 128)
     int tiles;
     double* partials;     // [tiles, TK_STATS]
     int* tile_counts;     // [tiles]
@@ -374,29 +377,9 @@ struct TkHumanoid {
 
 static constexpr int kD = 21;
 
-template <int T>
-static cudaError_t set_attr_for() {
-    cudaError_t e = cudaFuncSetAttribute(humanoid_tile_kernel<kD, T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>(sizeof(TileSmem<kD, T>)));
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(humanoid_tile_kernel<kD, T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(sizeof(TileSmem<kD, T>)));
-    return e;
-}
-static cudaError_t set_tile_attributes() {
-    cudaError_t e = set_attr_for<32>();
-    if (e == cudaSuccess) e = set_attr_for<64>();
-    if (e == cudaSuccess) e = set_attr_for<128>();
-    return e;
-}
-
 template <bool FUSED>
 static void launch_tile(const TkHumanoid* h, const KParams& k, cudaStream_t st) {
-    switch (h->tile) {
-        case 32: humanoid_tile_kernel<kD, 32, FUSED><<<h->tiles, 32, sizeof(TileSmem<kD, 32>), st>>>(k); break;
-        case 128: humanoid_tile_kernel<kD, 128, FUSED><<<h->tiles, 128, sizeof(TileSmem<kD, 128>), st>>>(k); break;
-        default: humanoid_tile_kernel<kD, 64, FUSED><<<h->tiles, 64, sizeof(TileSmem<kD, 64>), st>>>(k); break;
-    }
+    humanoid_warp_kernel<kD, FUSED><<<h->tiles, kTile, 0, st>>>(k);
 }
 
 static void fill_kparams(const TkHumanoid* h, KParams& k) {
@@ -422,7 +405,9 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     k.clip_actions = P.clip_actions; k.max_motor_effort = P.max_motor_effort;
     for (int i = 0; i < 3; ++i) { k.tgt[i] = P.targets[i]; k.b0[i] = P.basis_vec0[i]; k.b1[i] = P.basis_vec1[i]; }
     for (int i = 0; i < 4; ++i) k.isr[i] = P.inv_start_rot[i];
-    for (int i = 0; i < TK_MAX_DOF; ++i) { k.lo[i] = P.dof_limits_lower[i]; k.hi[i] = P.dof_limits_upper[i]; k.effort[i] = P.motor_efforts[i]; }
+    for (int i = 0; i < TK_MAX_DOF; ++i) { k.lo[i] = P.dof_limits_lower[i]; k.hi[i] = P.dof_limits_upper[i]; k.effort[i] = P.motor_efforts[i];
+        const float span = P.dof_limits_upper[i] - P.dof_limits_lower[i];
+        k.rinv[i] = (span != 0.0f) ? 1.0f / span : 0.0f; }
 }
 
 static int check_bound(const TkHumanoid* h) {
@@ -443,12 +428,7 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "out of host memory");
     h->params = *params;
     h->bound = false;
-    h->tile = kDefaultTile;
-    if (const char* env = getenv("TK_HUMANOID_TILE")) {
-        const int t = atoi(env);
-        if (t == 32 || t == 64 || t == 128) h->tile = t;
-    }
-    h->tiles = (params->num_envs + h->tile - 1) / h->tile;
+    h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->last_grid = 0;
     h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * h->tiles);
@@ -456,7 +436,6 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     if (e == cudaSuccess) e = cudaMalloc(&h->tile_base, sizeof(int) * h->tiles);
     if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * h->tiles);
     if (e == cudaSuccess) e = cudaMemset(h->tile_base, 0, sizeof(int) * h->tiles);
-    if (e == cudaSuccess) e = set_tile_attributes();
     if (e != cudaSuccess) {
         cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base);
         delete h;
@@ -559,7 +538,7 @@ int tk_humanoid_post_physics(TkHumanoid* h, const TkResetNoise* noise, void* str
     }
     if (k.noise_mode == TK_NOISE_COMPACT) {
         const int wpb = 8;
-        tile_reset_count_kernel<<<(h->tiles + wpb - 1) / wpb, wpb * 32, 0, st>>>(k.reset, k.n, h->tiles, h->tile, h->tile_counts);
+        tile_reset_count_kernel<<<(h->tiles + wpb - 1) / wpb, wpb * 32, 0, st>>>(k.reset, k.n, h->tiles, kTile, h->tile_counts);
         tile_exclusive_scan_kernel<<<1, 1024, 0, st>>>(h->tile_counts, h->tiles, h->tile_base);
     }
     launch_tile<true>(h, k, st);

@@ -1,142 +1,124 @@
-// Fused Humanoid post-physics tile kernel (included by tk_humanoid.cu; needs KParams, Layout, torso_math).
+// Fused Humanoid post-physics kernel: one warp = one CTA = one tile of 32 consecutive envs
+// (included by tk_humanoid.cu; needs KParams, Layout, torso_math, unscale_fast).
 //
-// One CTA of T threads owns T consecutive envs.  Its slice of every AoS array is one contiguous,
-// 16-byte aligned byte range, so the whole tile moves with the bulk-copy (TMA) engine:
+// The slice of every AoS array that belongs to 32 consecutive envs is one contiguous, 16-byte
+// aligned byte range, so the whole tile moves with the bulk-copy (TMA) engine, and the SAME
+// 14 KB of shared memory holds first the staged inputs (32 x 109 floats) and then the image of
+// the 32 obs rows (32 x 110 floats):
 //
-//   thread 0:  mbarrier.expect_tx + 5 x cp.async.bulk global->shared   (root, dof_state, dof_force, actions, sensors)
-//   all:       coalesced per-env scalars (progress, reset, potentials) while the bulk loads fly
-//   all:       wait(mbarrier)  ->  scaled copies shared->shared into the [T,110] obs image (96 of 110 columns)
-//   (rare)     reset prologue patches the staged rows and writes the new state to global memory
-//   all:       torso math, one env per thread (root rows at stride 13 words: bank-conflict free)
-//   thread 0:  fence.proxy.async + ONE cp.async.bulk shared->global for the finished obs tile
+//   lane 0:  mbarrier.expect_tx + 5 x cp.async.bulk global->shared  (dof_state, dof_force, actions, sensors, root)
+//   all:     coalesced per-env scalars (progress, reset, potentials, episode return) while the bulk loads fly
+//   all:     wait(mbarrier); (rare) reset prologue patches the staged rows of flagged envs, lane = DOF
+//   lane e:  reads ITS env's 109 input floats into registers (immediate offsets, LDS.64/.128 where aligned)
+//   __syncwarp  -- every input of the tile is now in registers, the buffer may be overwritten in place
+//   lane e:  scaled copies + torso math in registers, writes ITS obs row with 55 conflict-free STS.64
+//   lane 0:  fence.proxy.async + ONE cp.async.bulk shared->global for the finished [32,110] tile
 //
-// No thread ever issues a global load/store for the 876 B/env of bulk data; registers only hold
-// the env being computed.  Shared memory per env: 436 B staged input + 440 B obs image.
+// No thread issues a global load/store for the 876 B/env of bulk data and there is no index
+// arithmetic per element: every shared-memory access is [lane base + immediate].  14 KB of shared
+// memory and 162 registers per thread => 12 resident single-warp CTAs per SM (register-limited), each
+// at a different point of load / math / store: 168 KB of loads in flight per SM, far more than
+// the ~22 KB Little's law asks for at 6.5 TB/s (the kernel is a pure stream: 924 B/env-step, ~0.3 flop/B).
 #pragma once
 
 namespace tk {
 namespace humanoid {
 
-template <int D, int T>
-struct TileSmem {
-    static constexpr int kObs = Layout<D>::kObs;
-    alignas(128) float obs[T * kObs];
-    alignas(16) float root[T * kRoot];
-    alignas(16) float dof[T * D * 2];
-    alignas(16) float force[T * D];
-    alignas(16) float act[T * D];
-    alignas(16) float sens[T * kSensor];
-    alignas(8) uint64_t bar;
-    float lo[D], hi[D];
-    unsigned ballots[(T + 31) / 32];
-    float wsum[(T + 31) / 32][TK_STATS];
+constexpr int kTile = 32;   // envs per CTA == one warp
+
+template <int D>
+struct WarpTile {
+    static constexpr int T = kTile;
+    static constexpr int OBS = Layout<D>::kObs;
+    // float offsets of the staged inputs inside the tile buffer (each a multiple of 4 floats = 16 bytes)
+    static constexpr int oDof = 0;
+    static constexpr int oForce = oDof + T * 2 * D;
+    static constexpr int oAct = oForce + T * D;
+    static constexpr int oSens = oAct + T * D;
+    static constexpr int oRoot = oSens + T * kSensor;
+    static constexpr int kIn = oRoot + T * kRoot;
+    static constexpr int kBuf = T * OBS;
+    static_assert(kIn <= kBuf, "staged inputs must fit in the obs image");
+    static_assert(oForce % 4 == 0 && oAct % 4 == 0 && oSens % 4 == 0 && oRoot % 4 == 0, "16-byte aligned regions");
 };
 
-template <int T>
-__device__ __forceinline__ void coop_copy(float* dst, const float* src, int cnt, int tid) {
-    for (int i = tid; i < cnt; i += T) dst[i] = src[i];
+__device__ __forceinline__ void warp_copy(float* dst, const float* src, int cnt, int lane) {
+    for (int i = lane; i < cnt; i += 32) dst[i] = src[i];
 }
 
-template <int D, int T, bool FUSED>
-__global__ void __launch_bounds__(T) humanoid_tile_kernel(const __grid_constant__ KParams p) {
+#ifndef TK_HUMANOID_MIN_CTAS
+#define TK_HUMANOID_MIN_CTAS 12
+#endif
+
+template <int D, bool FUSED>
+__global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_kernel(const __grid_constant__ KParams p) {
     using L = Layout<D>;
+    using WT = WarpTile<D>;
     constexpr int OBS = L::kObs;
-    constexpr int W = (T + 31) / 32;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    TileSmem<D, T>& s = *reinterpret_cast<TileSmem<D, T>*>(smem_raw);
+    __shared__ __align__(128) float buf[WT::kBuf];
+    __shared__ __align__(8) uint64_t bar;
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int env0 = blockIdx.x * T;
-    const int nt = min(T, p.n - env0);
-    const int n = env0 + tid;
-    const bool valid = tid < nt;
-    const bool bulk = (p.vec_ok != 0) && (nt == T);   // full, 16-byte aligned tile -> TMA both ways
+    const int lane = threadIdx.x;
+    const int env0 = blockIdx.x * kTile;
+    const int nt = min(kTile, p.n - env0);
+    const int n = env0 + lane;
+    const bool valid = lane < nt;
+    const bool bulk = (p.vec_ok != 0) && (nt == kTile);   // full, 16-byte aligned tile -> TMA both ways
 
-    const float* g_root = p.root + static_cast<size_t>(env0) * kRoot;
     const float* g_dof = p.dof_state + static_cast<size_t>(env0) * D * 2;
     const float* g_force = p.dof_force + static_cast<size_t>(env0) * D;
     const float* g_act = p.actions + static_cast<size_t>(env0) * D;
     const float* g_sens = p.sensors + static_cast<size_t>(env0) * kSensor;
+    const float* g_root = p.root + static_cast<size_t>(env0) * kRoot;
 
     if (bulk) {
-        if (tid == 0) {
-            mbar_init(&s.bar, 1);
+        if (lane == 0) {
+            mbar_init(&bar, 1);
             mbar_fence_init();
-            constexpr uint32_t kBytes = T * (kRoot + 4 * D + kSensor) * 4;
-            mbar_expect_tx(&s.bar, kBytes);
-            bulk_load(s.dof, g_dof, T * D * 2 * 4, &s.bar);
-            bulk_load(s.force, g_force, T * D * 4, &s.bar);
-            bulk_load(s.act, g_act, T * D * 4, &s.bar);
-            bulk_load(s.sens, g_sens, T * kSensor * 4, &s.bar);
-            bulk_load(s.root, g_root, T * kRoot * 4, &s.bar);
+            mbar_expect_tx(&bar, WT::kIn * 4);
+            bulk_load(buf + WT::oDof, g_dof, kTile * D * 2 * 4, &bar);
+            bulk_load(buf + WT::oForce, g_force, kTile * D * 4, &bar);
+            bulk_load(buf + WT::oAct, g_act, kTile * D * 4, &bar);
+            bulk_load(buf + WT::oSens, g_sens, kTile * kSensor * 4, &bar);
+            bulk_load(buf + WT::oRoot, g_root, kTile * kRoot * 4, &bar);
         }
     } else {
-        coop_copy<T>(s.dof, g_dof, nt * D * 2, tid);
-        coop_copy<T>(s.force, g_force, nt * D, tid);
-        coop_copy<T>(s.act, g_act, nt * D, tid);
-        coop_copy<T>(s.sens, g_sens, nt * kSensor, tid);
-        coop_copy<T>(s.root, g_root, nt * kRoot, tid);
+        warp_copy(buf + WT::oDof, g_dof, nt * D * 2, lane);
+        warp_copy(buf + WT::oForce, g_force, nt * D, lane);
+        warp_copy(buf + WT::oAct, g_act, nt * D, lane);
+        warp_copy(buf + WT::oSens, g_sens, nt * kSensor, lane);
+        warp_copy(buf + WT::oRoot, g_root, nt * kRoot, lane);
     }
-    if (tid < D) { s.lo[tid] = p.lo[tid]; s.hi[tid] = p.hi[tid]; }
 
     // ---- per-env scalars (coalesced), overlapped with the bulk loads
     long long prog = 0;
     bool do_reset = false;
-    float pot_old = 0.0f;
+    float pot_old = 0.0f, ret_old = 0.0f;
     if (valid) {
         pot_old = p.pot[n];
         if (FUSED) {
             prog = p.progress[n] + 1;                              // humanoid.py:288
             do_reset = p.reset[n] != 0;                            // :291
+            if (p.ep_return) ret_old = p.ep_return[n];
             if (p.randomize) p.randomize[n] += 1;                  // :289
         }
     }
-    if (FUSED) {
-        unsigned b = __ballot_sync(0xffffffffu, do_reset);
-        if (lane == 0) s.ballots[warp] = b;
-    }
-    __syncthreads();                       // mbarrier init, lo/hi, ballots, cooperative copies visible
-    if (bulk) mbar_wait(&s.bar, 0);        // bulk loads landed
+    __syncwarp();                          // mbarrier init / cooperative copies visible to the warp
+    if (bulk) mbar_wait(&bar, 0);          // bulk loads landed
 
-    // ---- scaled copies shared -> obs image
-    {
-        const int cnt = nt * D;
-        const float dvs = p.dof_vel_scale, cfs = p.contact_scale;
-        const float2* dof2 = reinterpret_cast<const float2*>(s.dof);
-#pragma unroll 4
-        for (int e = tid; e < cnt; e += T) {
-            const int nn = e / D, j = e - nn * D;
-            const float2 pv = dof2[e];
-            float* o = &s.obs[nn * OBS + j];
-            o[L::kPos] = unscale_ref(pv.x, s.lo[j], s.hi[j]);      // :406
-            o[L::kVel] = pv.y * dvs;                               // :413
-            o[L::kForce] = s.force[e] * cfs;
-            o[L::kAct] = s.act[e];
-        }
-        const int cs = nt * kSensor;
-#pragma unroll 2
-        for (int e = tid; e < cs; e += T) {
-            const int nn = e / kSensor, k = e - nn * kSensor;
-            s.obs[nn * OBS + L::kSens + k] = s.sens[e] * cfs;      // :414
-        }
-    }
-
-    // ---- reset prologue (rare): reset_idx :253-279 for this tile's flagged envs, one warp per env
+    // ---- reset prologue (rare): reset_idx :253-279 for this tile's flagged envs, lane = DOF
     if (FUSED) {
-        __syncthreads();
-        const unsigned mine = s.ballots[warp];
-        if (mine) {
+        unsigned bits = __ballot_sync(0xffffffffu, do_reset);
+        if (bits) {
             int rank = (p.noise_mode == TK_NOISE_COMPACT) ? p.tile_rank_base[blockIdx.x] : 0;
-            for (int w = 0; w < warp; ++w) rank += __popc(s.ballots[w]);
-            unsigned bits = mine;
             while (bits) {
-                const int le = __ffs(bits) - 1;
+                const int e = __ffs(bits) - 1;
                 bits &= bits - 1;
-                const int e = warp * 32 + le;
                 const int ne = env0 + e;
                 const long long row = (p.noise_mode == TK_NOISE_COMPACT) ? rank : ne;
                 ++rank;
-                for (int j = lane; j < D; j += 32) {
+                if (lane < D) {
+                    const int j = lane;
                     float ua = 0.5f, ub = 0.5f;
                     if (p.noise_mode == TK_NOISE_PHILOX) {
                         Philox4 r = philox_env(p.seed, p.step, p.env_off + ne, static_cast<uint32_t>(j >> 1));
@@ -149,37 +131,77 @@ __global__ void __launch_bounds__(T) humanoid_tile_kernel(const __grid_constant_
                     const float positions = 0.4f * ua + (-0.2f);                   // :258 torch_rand_float(-0.2, 0.2)
                     const float velocities = 0.2f * ub + (-0.1f);                  // :259 torch_rand_float(-0.1, 0.1)
                     float np_ = p.init_dof_pos[static_cast<size_t>(ne) * D + j] + positions;
-                    np_ = fmaxf(fminf(np_, s.hi[j]), s.lo[j]);                     // :261 tensor_clamp
-                    reinterpret_cast<float2*>(p.dof_state)[static_cast<size_t>(ne) * D + j] = make_float2(np_, velocities);
-                    s.obs[e * OBS + L::kPos + j] = unscale_ref(np_, s.lo[j], s.hi[j]);
-                    s.obs[e * OBS + L::kVel + j] = velocities * p.dof_vel_scale;
+                    np_ = fmaxf(fminf(np_, p.hi[j]), p.lo[j]);                     // :261 tensor_clamp
+                    const float2 pv = make_float2(np_, velocities);
+                    reinterpret_cast<float2*>(p.dof_state)[static_cast<size_t>(ne) * D + j] = pv;   // :261-262
+                    reinterpret_cast<float2*>(buf + WT::oDof)[e * D + j] = pv;
                 }
-                if (lane < kRoot) {                                                // :265-267
+                if (lane < kRoot) {                                                // :265-267 root row <- initial_root_states
                     const float v = p.init_root[static_cast<size_t>(ne) * kRoot + lane];
                     p.root[static_cast<size_t>(ne) * kRoot + lane] = v;
-                    s.root[e * kRoot + lane] = v;
+                    buf[WT::oRoot + e * kRoot + lane] = v;
                 }
             }
+            __syncwarp();
         }
-        __syncthreads();
     }
 
-    // ---- torso math, one env per thread
+    // ---- lane e pulls ITS env's inputs into registers
+    float o[OBS];
+    float r[kRoot];
+    {
+        const float2* dof2 = reinterpret_cast<const float2*>(buf + WT::oDof) + lane * D;
+        const float* fo = buf + WT::oForce + lane * D;
+        const float* ac = buf + WT::oAct + lane * D;
+        const float4* se = reinterpret_cast<const float4*>(buf + WT::oSens) + lane * (kSensor / 4);
+        const float* rr = buf + WT::oRoot + lane * kRoot;
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+            const float2 pv = dof2[j];
+            o[L::kPos + j] = pv.x;
+            o[L::kVel + j] = pv.y;
+            o[L::kForce + j] = fo[j];
+            o[L::kAct + j] = ac[j];
+        }
+#pragma unroll
+        for (int k = 0; k < kSensor / 4; ++k) {
+            const float4 v = se[k];
+            o[L::kSens + 4 * k + 0] = v.x; o[L::kSens + 4 * k + 1] = v.y;
+            o[L::kSens + 4 * k + 2] = v.z; o[L::kSens + 4 * k + 3] = v.w;
+        }
+#pragma unroll
+        for (int c = 0; c < kRoot; ++c) r[c] = rr[c];
+    }
+    __syncwarp();   // the whole tile is in registers: from here on the buffer is the obs image
+
     float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_up = 0.f, st_head = 0.f;
     bool out_reset = false, out_timeout = false;
     if (valid) {
-        float r[kRoot];
+        // ---- scaled copies (humanoid.py:406, 413-414), constants straight from the parameter bank
+        const float dvs = p.dof_vel_scale, cfs = p.contact_scale;
 #pragma unroll
-        for (int c = 0; c < kRoot; ++c) r[c] = s.root[tid * kRoot + c];
+        for (int j = 0; j < D; ++j) {
+            o[L::kPos + j] = unscale_fast(o[L::kPos + j], p.lo[j], p.hi[j], p.rinv[j]);
+            o[L::kVel + j] *= dvs;
+            o[L::kForce + j] *= cfs;
+        }
+#pragma unroll
+        for (int k = 0; k < kSensor; ++k) o[L::kSens + k] *= cfs;
+
+        // ---- torso math
         const Head h = torso_math(r, p);
         // after a reset potentials = prev_potentials = -|targets - initial_pos| / dt (:273-276); the root row now IS the
         // initial row, so that value equals the freshly computed potential
         const float prev_new = (FUSED && do_reset) ? h.pot : pot_old;              // :394
-        float* o = &s.obs[tid * OBS];
 #pragma unroll
         for (int c = 0; c < 12; ++c) o[c] = h.c[c];
         o[L::kPot] = h.pot / 60000.0f;                                             // :414
         o[L::kPot + 1] = prev_new / 60000.0f;
+
+        float2* row = reinterpret_cast<float2*>(buf + lane * OBS);                 // 440-byte rows: 8-byte aligned
+#pragma unroll
+        for (int k = 0; k < OBS / 2; ++k) row[k] = make_float2(o[2 * k], o[2 * k + 1]);
+
         p.pot[n] = h.pot;
         p.prev_pot[n] = prev_new;
         if (p.up_vec) { p.up_vec[n * 3 + 0] = h.up.x; p.up_vec[n * 3 + 1] = h.up.y; p.up_vec[n * 3 + 2] = h.up.z; }
@@ -201,54 +223,55 @@ __global__ void __launch_bounds__(T) humanoid_tile_kernel(const __grid_constant_
             if (p.timeout) p.timeout[n] = out_timeout ? 1 : 0;
             st_rew = total; st_up = h.c[10]; st_head = h.c[11];
             if (p.ep_return) {
-                const float ret = (do_reset ? 0.0f : p.ep_return[n]) + total;
+                const float ret = (do_reset ? 0.0f : ret_old) + total;
                 if (out_reset) st_ret = ret;
                 p.ep_return[n] = ret;
             }
             if (out_reset) st_len = static_cast<float>(prog);
         }
     }
+    fence_proxy_async_smem();   // obs image was written through the generic proxy, the bulk engine reads it
+    __syncwarp();
 
-    // ---- statistics partials (fixed reduction order -> deterministic)
+    // ---- obs tile -> global
+    float* dst = p.obs + static_cast<size_t>(env0) * OBS;
+    if (bulk) {
+        if (lane == 0) {
+            bulk_store(dst, buf, WT::kBuf * 4);
+            bulk_commit();
+        }
+    } else {
+        warp_copy(dst, buf, nt * OBS, lane);
+    }
+
+    // ---- statistics partials: one row per tile, fixed reduction order -> deterministic
     if (FUSED) {
         const unsigned m_reset = __ballot_sync(0xffffffffu, out_reset);
         const unsigned m_to = __ballot_sync(0xffffffffu, out_timeout);
         const unsigned m_valid = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            st_rew += __shfl_xor_sync(0xffffffffu, st_rew, o);
-            st_ret += __shfl_xor_sync(0xffffffffu, st_ret, o);
-            st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
-            st_up += __shfl_xor_sync(0xffffffffu, st_up, o);
-            st_head += __shfl_xor_sync(0xffffffffu, st_head, o);
+        for (int off = 16; off > 0; off >>= 1) {
+            st_rew += __shfl_xor_sync(0xffffffffu, st_rew, off);
+            st_ret += __shfl_xor_sync(0xffffffffu, st_ret, off);
+            st_len += __shfl_xor_sync(0xffffffffu, st_len, off);
+            st_up += __shfl_xor_sync(0xffffffffu, st_up, off);
+            st_head += __shfl_xor_sync(0xffffffffu, st_head, off);
         }
-        if (lane == 0) {
-            float* w = s.wsum[warp];
-            w[0] = st_rew; w[1] = static_cast<float>(__popc(m_reset)); w[2] = static_cast<float>(__popc(m_to));
-            w[3] = st_ret; w[4] = st_len; w[5] = st_up; w[6] = st_head; w[7] = static_cast<float>(__popc(m_valid));
+        if (lane < TK_STATS) {
+            float v = st_rew;
+            v = (lane == 1) ? static_cast<float>(__popc(m_reset)) : v;
+            v = (lane == 2) ? static_cast<float>(__popc(m_to)) : v;
+            v = (lane == 3) ? st_ret : v;
+            v = (lane == 4) ? st_len : v;
+            v = (lane == 5) ? st_up : v;
+            v = (lane == 6) ? st_head : v;
+            v = (lane == 7) ? static_cast<float>(__popc(m_valid)) : v;
+            // running sum since the last tk_humanoid_stats.  The slot belongs to this tile alone, so the sum is
+            // deterministic; a reduction (RED, no return value) keeps the warp from waiting on the read-modify-write.
+            atomicAdd(p.partials + static_cast<size_t>(blockIdx.x) * TK_STATS + lane, static_cast<double>(v));
         }
     }
-    fence_proxy_async_smem();   // obs image was written through the generic proxy, the bulk engine reads it
-    __syncthreads();
-
-    if (FUSED && tid < TK_STATS) {
-        double acc = 0.0;
-#pragma unroll
-        for (int w = 0; w < W; ++w) acc += static_cast<double>(s.wsum[w][tid]);
-        p.partials[static_cast<size_t>(blockIdx.x) * TK_STATS + tid] += acc;   // running sum since the last tk_humanoid_stats
-    }
-
-    // ---- obs tile -> global
-    float* dst = p.obs + static_cast<size_t>(env0) * OBS;
-    if (bulk) {
-        if (tid == 0) {
-            bulk_store(dst, s.obs, T * OBS * 4);
-            bulk_commit();
-            bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
-        }
-    } else {
-        coop_copy<T>(dst, s.obs, nt * OBS, tid);
-    }
+    if (bulk && lane == 0) bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
 }
 
 }  // namespace humanoid

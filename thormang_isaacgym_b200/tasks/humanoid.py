@@ -95,6 +95,9 @@ class Humanoid(VecTask):
         self.actions = torch.zeros((n, d), **f)
         self.forces = torch.zeros((n, d), **f)
         self.episode_return = torch.zeros(n, **f) if env.get("episodeStatistics", True) else None
+        # humanoid.py:289 bumps randomize_buf every step, but only domain randomisation (out of scope, randomize is
+        # False in Humanoid.yaml:64) ever reads it: the kernel skips that 16 B/env read-modify-write unless asked
+        self.track_randomize_buf = bool(env.get("trackRandomizeBuf", False))
         self.episode_stats = torch.zeros(nat.TK_STATS, device=dev, dtype=torch.float64)
         # in-kernel reset noise
         self.noise_seed = int(cfg.get("seed", 0)) & 0xFFFFFFFFFFFFFFFF
@@ -161,7 +164,8 @@ class Humanoid(VecTask):
                 ("root_states", self.root_states), ("dof_state", self.dof_state), ("dof_force", self.dof_force_tensor),
                 ("sensors", self.vec_sensor_tensor), ("actions", self.actions), ("obs_buf", self.obs_buf),
                 ("rew_buf", self.rew_buf), ("reset_buf", self.reset_buf), ("progress_buf", self.progress_buf),
-                ("timeout_buf", self.timeout_buf), ("randomize_buf", self.randomize_buf),
+                ("timeout_buf", self.timeout_buf),
+                ("randomize_buf", self.randomize_buf if self.track_randomize_buf else None),
                 ("potentials", self.potentials), ("prev_potentials", self.prev_potentials), ("up_vec", self.up_vec),
                 ("heading_vec", self.heading_vec), ("initial_root_states", self.initial_root_states),
                 ("initial_dof_pos", self.initial_dof_pos), ("episode_return", self.episode_return)):

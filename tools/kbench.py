@@ -20,7 +20,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--task", default="humanoid")
     ap.add_argument("--envs", default="131072")
-    ap.add_argument("--tiles", default="32,64,128")
+    ap.add_argument("--tiles", default="32")
     ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--warmup", type=int, default=20)
     args = ap.parse_args()
