@@ -214,6 +214,7 @@ def run_gpu_arm(args, rank, world):
                "path": "HostBridge: pinned host state -> H2D -> Humanoid.post_physics_step() -> D2H obs/rew/reset, "
                        "range-sharded into chunks on separate streams so PCIe copies overlap the kernels"}
 
+    stats_last = reducer.result()
     sampler.stop()
     clocks = sampler.summary(windows)
     if rank != 0:
@@ -238,7 +239,7 @@ def run_gpu_arm(args, rank, world):
         "gpu_launches": res["launches"],
         "clocks": clocks,
         "stats_allreduce": {"per": f"{HORIZON} steps", "payload_bytes": 64, "backend": "nccl" if dist else "none (1 GPU)",
-                            "last": reducer.result()},
+                            "last": stats_last},
     }
 
     if world == 1 and not args.no_cpu_baseline:

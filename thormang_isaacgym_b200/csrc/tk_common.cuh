@@ -46,33 +46,15 @@ __device__ __host__ constexpr float kTwoPi = 6.28318530717958647692f;     // (fl
 // ---------------------------------------------------------------------------------------------
 // PTX wrappers: cache-hinted vector access, bulk (TMA) copies, mbarrier
 // ---------------------------------------------------------------------------------------------
+// read-only streaming loads (non-coherent path, no L1 allocation).  Not volatile: the compiler may batch them.
 __device__ __forceinline__ float4 ldg_stream4(const float* p) {
     float4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
     return r;
 }
-// same, but through the coherent path: for arrays this kernel may also write (root_states, dof_state)
-__device__ __forceinline__ float4 ld_stream4(const float* p) {
-    float4 r;
-    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
-    return r;
-}
-__device__ __forceinline__ float2 ldg_stream2(const float* p) {
-    float2 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0,%1}, [%2];" : "=f"(r.x), "=f"(r.y) : "l"(p));
-    return r;
-}
-__device__ __forceinline__ float ldg_stream1(const float* p) {
-    float r;
-    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
-    return r;
-}
-__device__ __forceinline__ void stg_stream4(float* p, float4 v) {
-    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-                 : "memory");
-}
+// same through the coherent path, evict-first: for arrays this kernel may also write (root_states, dof_state)
+__device__ __forceinline__ float4 ld_stream4(const float* p) { return __ldcs(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ void stg_stream4(float* p, float4 v) { __stcs(reinterpret_cast<float4*>(p), v); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 
@@ -182,6 +164,16 @@ __device__ __forceinline__ float floor_mod_two_pi(float a) {
     if (m != 0.0f && m < 0.0f) m += kTwoPi;
     return m;
 }
+// same result, cheap for |a| < 4*pi (all the hot path produces): fmod is the identity below 2*pi and an exact
+// subtraction (Sterbenz) in [2*pi, 4*pi); anything else takes the library fmodf
+__device__ __forceinline__ float floor_mod_two_pi_near(float a) {
+    float m;
+    if (fabsf(a) < kTwoPi) m = a;
+    else if (a >= kTwoPi && a < 2.0f * kTwoPi) m = a - kTwoPi;
+    else m = fmodf(a, kTwoPi);
+    if (m != 0.0f && m < 0.0f) m += kTwoPi;
+    return m;
+}
 __device__ __forceinline__ float normalize_angle_ref(float x) {
     float s, c;
     sincosf(x, &s, &c);
@@ -229,13 +221,14 @@ __device__ __host__ inline Philox4 philox4x32_10(uint64_t seed, uint64_t ctr_lo,
     return c;
 }
 __device__ __host__ __forceinline__ float u01(uint32_t bits) { return static_cast<float>(bits >> 8) * (1.0f / 16777216.0f); }
-// standard normal pair by Box-Muller from two 32-bit words
+// standard normal pair by Box-Muller from two 32-bit words.  Hardware-approximate log / sin / cos: this is noise,
+// and parity checks materialise the very same values through tk_*_philox_noise.
 __device__ __forceinline__ float2 normal_pair(uint32_t a, uint32_t b) {
     float u1 = (static_cast<float>(a >> 8) + 1.0f) * (1.0f / 16777216.0f);   // (0,1]
     float u2 = u01(b);
-    float r = sqrtf(-2.0f * logf(u1));
+    float r = sqrtf(-2.0f * __logf(u1));
     float s, c;
-    sincosf(kTwoPi * u2, &s, &c);
+    __sincosf(kTwoPi * u2, &s, &c);
     return make_float2(r * c, r * s);
 }
 // counter layout: ctr_lo = global env id, ctr_hi = (step << 8) | stream-id

@@ -69,20 +69,24 @@ struct KParams {
 // philox stream ids per (env, step); see tk_gogoro_philox_noise for the materialised layout
 enum { kStreamSensor = 0, kStreamMisc = 1, kStreamResetU = 2, kStreamResetN0 = 3, kStreamResetN1 = 4 };
 
+// Per (env, step): stream kStreamSensor -> the four LIVE sensor normals (gogoro_new.py:451-453,460; the draw of
+// :455 is dead because :457-458 overwrite channel 3), stream kStreamMisc -> steer normal, the dead draw, and the two
+// resample uniforms (needed only on the rare steps where progress hits the update frequency).
 struct StepNoise {
     float sensor[kSensorNoise];
-    float steer, speed_u, yaw_u;
 };
-__device__ __forceinline__ StepNoise philox_step_noise(unsigned long long seed, unsigned long long step, long long env) {
+__device__ __forceinline__ StepNoise philox_sensor_noise(unsigned long long seed, unsigned long long step, long long env) {
     StepNoise s;
     Philox4 a = philox_env(seed, step, env, kStreamSensor);
-    Philox4 b = philox_env(seed, step, env, kStreamMisc);
-    float2 n01 = normal_pair(a.x, a.y), n23 = normal_pair(a.z, a.w), n4s = normal_pair(b.x, b.y);
-    s.sensor[0] = n01.x; s.sensor[1] = n01.y; s.sensor[2] = n23.x; s.sensor[3] = n23.y; s.sensor[4] = n4s.x;
-    s.steer = n4s.y;
-    s.speed_u = u01(b.z);
-    s.yaw_u = u01(b.w);
+    float2 n01 = normal_pair(a.x, a.y), n24 = normal_pair(a.z, a.w);
+    s.sensor[0] = n01.x; s.sensor[1] = n01.y; s.sensor[2] = n24.x; s.sensor[3] = 0.0f; s.sensor[4] = n24.y;
     return s;
+}
+struct MiscNoise { float steer, dead3, speed_u, yaw_u; };
+__device__ __forceinline__ MiscNoise philox_misc_noise(unsigned long long seed, unsigned long long step, long long env) {
+    Philox4 b = philox_env(seed, step, env, kStreamMisc);
+    float2 n = normal_pair(b.x, b.y);
+    return MiscNoise{n.x, n.y, u01(b.z), u01(b.w)};
 }
 __device__ __forceinline__ void philox_reset_noise(unsigned long long seed, unsigned long long step, long long env, float* u) {
     Philox4 a = philox_env(seed, step, env, kStreamResetU);
@@ -104,16 +108,17 @@ __device__ __forceinline__ void observe(const float* r, float desired_yaw, float
     roll = (roll < -kPi) ? roll + kTwoPi : roll;                                    // :705
     yaw = (yaw > kPi) ? yaw - kTwoPi : yaw;                                         // :707
     yaw = (yaw < -kPi) ? yaw + kTwoPi : yaw;                                        // :708
-    float delta = floor_mod_two_pi(desired_yaw - yaw + kPi) - kPi;                  // :710, :689
+    float delta = floor_mod_two_pi_near(desired_yaw - yaw + kPi) - kPi;             // :710, :689
     o[0] = roll; o[1] = ang.x; o[2] = ang.z; o[3] = lin.x; o[4] = delta; o[5] = last_command;
 }
 
 // compute_gogoro_reward :645-684; hist = 5 action-history values
 __device__ __forceinline__ float reward_of(const float* o, const float* hist, bool* felt_out) {
     const float tilt = o[0], dtilt = o[1], yaw_e = o[4];
-    float tilt_err = fminf(fmaxf(tilt / 0.30f, -1.0f), 1.0f);                       // :655-656
-    float yaw_err = fminf(fmaxf(yaw_e / kPi, -1.0f), 1.0f);                         // :658-659
-    float dtilt_err = fminf(fmaxf(dtilt / 0.3f, -1.0f), 1.0f);                      // :661-662
+    // divisions by constants as multiplications by the rounded reciprocal (<= 1.5 ulp; the masks do not use them)
+    float tilt_err = fminf(fmaxf(tilt * (1.0f / 0.30f), -1.0f), 1.0f);              // :655-656
+    float yaw_err = fminf(fmaxf(yaw_e * (1.0f / kPi), -1.0f), 1.0f);                // :658-659
+    float dtilt_err = fminf(fmaxf(dtilt * (1.0f / 0.3f), -1.0f), 1.0f);             // :661-662
     float t30 = yaw_err * 30.0f;
     float reward1 = 1.0f / (1.0f + t30 * t30);                                      // :667
     float reward2 = 1.0f - tilt_err * tilt_err;                                     // :670
@@ -219,10 +224,13 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
 
     long long prog = 0;
     bool do_reset = false, do_speed = false;
-    float yaw_cmd = 0.f, cur_cmd = 0.f;
+    float yaw_cmd = 0.f, cur_cmd = 0.f, imu_off = 0.f, ret_old = 0.f;
     if (valid) {
+        // every per-env scalar is requested up front, together with the tile copies: one memory round trip per tile
         yaw_cmd = p.yaw_command[n];
         cur_cmd = p.curent_command[n];
+        if (MODE != 2) imu_off = p.imu_offsets[n];
+        if (MODE == 0 && p.ep_return) ret_old = p.ep_return[n];
         if (MODE != 2) prog = p.progress[n];
         if (MODE == 0) {
             prog += 1;                                                              // :375
@@ -248,12 +256,10 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
 #pragma unroll
             for (int c = 0; c < kHist; ++c) hist[c] = s.hist[tid * kHist + c];
             if (philox) {
-                sn = philox_step_noise(p.seed, p.step, p.env_off + n);
+                sn = philox_sensor_noise(p.seed, p.step, p.env_off + n);
             } else {
 #pragma unroll
                 for (int c = 0; c < kSensorNoise; ++c) sn.sensor[c] = p.sensor_unit ? s.noise[tid * kSensorNoise + c] : 0.0f;
-                sn.yaw_u = p.yaw_unit ? p.yaw_unit[n] : 0.5f;
-                sn.speed_u = 0.5f;
             }
         }
         if (MODE == 0 && do_reset) {
@@ -274,6 +280,7 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
                                                                                  : ((c == 0 || (c >= 2 && c <= 4)) ? 0.5f : 0.0f);
             }
             reset_env(p, n, u, r, &yaw_cmd);
+            imu_off = normal_of(p.seat_xr, u[8]);                                   // :557,574 (what reset_env just stored)
             cur_cmd = 0.0f;                                                         // :587
             p.curent_command[n] = 0.0f;
 #pragma unroll
@@ -296,7 +303,7 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
             p.reset[n] = out_reset ? 1 : 0;
             // sensor-noise model on a copy :449-460
             float z[kObs];
-            z[0] = o[0] + (normal_of(p.imu_filter, sn.sensor[0]) + p.imu_offsets[n]);   // :451
+            z[0] = o[0] + (normal_of(p.imu_filter, sn.sensor[0]) + imu_off);             // :451
             z[1] = o[1] + normal_of(p.imu, sn.sensor[1]);                           // :452
             z[2] = o[2] + normal_of(p.imu, sn.sensor[2]);                           // :453
             z[3] = rintf(o[4]);                                                     // :455-458: channel 3 <- round(channel 4), sic
@@ -309,8 +316,17 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         if (MODE == 0) {
             p.progress[n] = prog;
             // command resampling :384-389
+            const bool do_yaw = prog == p.yaw_freq;
+            float su = 0.5f, yu = 0.5f;
+            if (do_speed || do_yaw) {                                               // rare: second Philox block
+                if (philox) {
+                    MiscNoise mn = philox_misc_noise(p.seed, p.step, p.env_off + n);
+                    su = mn.speed_u; yu = mn.yaw_u;
+                } else if (p.yaw_unit) {
+                    yu = p.yaw_unit[n];
+                }
+            }
             if (do_speed) {
-                float su = sn.speed_u;
                 if (!philox && p.speed_unit) {
                     long long row = n;
                     if (p.noise_mode == TK_NOISE_COMPACT) {
@@ -323,14 +339,14 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
                 }
                 p.curent_speed[n] = uniform_of(p.speed, su);                        // :386
             }
-            if (prog == p.yaw_freq) yaw_cmd = -kPi + sn.yaw_u * kTwoPi;             // :387
+            if (do_yaw) yaw_cmd = -kPi + yu * kTwoPi;                               // :387
             yaw_cmd = (yaw_cmd > kPi) ? yaw_cmd - kTwoPi : yaw_cmd;                 // :388
             yaw_cmd = (yaw_cmd < -kPi) ? yaw_cmd + kTwoPi : yaw_cmd;                // :389
             p.yaw_command[n] = yaw_cmd;
             out_timeout = (prog >= p.max_episode_length - 1) && out_reset;          // vec_task.py:345
             if (p.timeout) p.timeout[n] = out_timeout ? 1 : 0;
             if (p.ep_return) {
-                float ret = (do_reset ? 0.0f : p.ep_return[n]) + st_rew;
+                float ret = (do_reset ? 0.0f : ret_old) + st_rew;
                 if (out_reset) st_ret = ret;
                 p.ep_return[n] = ret;
             }
@@ -448,7 +464,7 @@ __global__ void __launch_bounds__(256) gogoro_pre_kernel(const __grid_constant__
     float cmd = p.curent_command[n] + a2;                                           // :355
     cmd = fminf(fmaxf(cmd, -p.max_steering), p.max_steering);                       // :359
     p.curent_command[n] = cmd;
-    float z = steer_unit ? steer_unit[n] : philox_step_noise(p.seed, p.step, p.env_off + n).steer;
+    float z = steer_unit ? steer_unit[n] : philox_misc_noise(p.seed, p.step, p.env_off + n).steer;
     float noise = normal_of(p.steer_action, z);                                     // :362
     p.pos_cmd[n * p.num_dof + p.steering_joint] = cmd + p.steer_offsets[n] + noise; // :363
     p.vel_cmd[n * p.num_dof + p.rear_wheel_joint] = p.curent_speed[n];              // :367
@@ -495,11 +511,13 @@ __global__ void gogoro_philox_kernel(int n, unsigned long long seed, unsigned lo
                                      float* steer, float* sensor, float* reset_unit, float* speed, float* yaw) {
     const long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (e >= n) return;
-    StepNoise sn = philox_step_noise(seed, step, env_off + e);
-    if (steer) steer[e] = sn.steer;
+    StepNoise sn = philox_sensor_noise(seed, step, env_off + e);
+    MiscNoise mn = philox_misc_noise(seed, step, env_off + e);
+    sn.sensor[3] = mn.dead3;   // the draw of gogoro_new.py:455 never reaches an output
+    if (steer) steer[e] = mn.steer;
     if (sensor) for (int c = 0; c < kSensorNoise; ++c) sensor[e * kSensorNoise + c] = sn.sensor[c];
-    if (speed) speed[e] = sn.speed_u;
-    if (yaw) yaw[e] = sn.yaw_u;
+    if (speed) speed[e] = mn.speed_u;
+    if (yaw) yaw[e] = mn.yaw_u;
     if (reset_unit) {
         float u[kResetNoise];
         philox_reset_noise(seed, step, env_off + e, u);

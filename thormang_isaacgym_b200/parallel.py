@@ -56,11 +56,13 @@ class EpisodeStatsReducer:
         """Start reducing ``local_stats`` (fp64[8] on ``device``); returns immediately."""
         dist = self._dist()
         if self._stream is not None:
+            snap = local_stats.clone()          # on the caller's stream: the caller may overwrite local_stats at once
             ready = torch.cuda.Event()
             ready.record()
             with torch.cuda.stream(self._stream):
                 self._stream.wait_event(ready)
-                self.buffer.copy_(local_stats)
+                self.buffer.copy_(snap)
+                snap.record_stream(self._stream)
                 if dist is not None:
                     self._work = dist.all_reduce(self.buffer, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         else:
