@@ -75,6 +75,7 @@ struct KParams {
     float tgt[3], isr[4], b0[3], b1[3];
     float lo[TK_MAX_DOF], hi[TK_MAX_DOF], effort[TK_MAX_DOF];
     float rinv[TK_MAX_DOF];     // 1 / (hi - lo), rounded to fp32 on the host
+    long long* dbg_ts;          // developer timeline probe (tools/tile_timeline.py); NULL in normal use
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -373,13 +374,27 @@ struct TkHumanoid {
     int* tile_counts;     // [tiles]
     int* tile_base;       // [tiles]
     int last_grid;
+    int use_pdl;          // programmatic dependent launch (TK_HUMANOID_PDL=0 disables)
+    long long* dbg_ts;
 };
 
 static constexpr int kD = 21;
 
 template <bool FUSED>
 static void launch_tile(const TkHumanoid* h, const KParams& k, cudaStream_t st) {
-    humanoid_warp_kernel<kD, FUSED><<<h->tiles, kTile, 0, st>>>(k);
+    // Programmatic dependent launch: the CTAs of this launch may be scheduled while the previous kernel in the stream
+    // drains; the kernel itself executes griddepcontrol.wait before it touches global memory, so stream order is kept.
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(h->tiles);
+    cfg.blockDim = dim3(kTile);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = h->use_pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, humanoid_warp_kernel<kD, FUSED>, k);
 }
 
 static void fill_kparams(const TkHumanoid* h, KParams& k) {
@@ -391,7 +406,7 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     k.timeout = B.timeout_buf; k.randomize = reinterpret_cast<long long*>(B.randomize_buf);
     k.pot = B.potentials; k.prev_pot = B.prev_potentials; k.up_vec = B.up_vec; k.heading_vec = B.heading_vec;
     k.init_root = B.initial_root_states; k.init_dof_pos = B.initial_dof_pos; k.ep_return = B.episode_return;
-    k.partials = h->partials; k.tile_rank_base = h->tile_base;
+    k.partials = h->partials; k.tile_rank_base = h->tile_base; k.dbg_ts = h->dbg_ts;
     k.unit_a = nullptr; k.unit_b = nullptr; k.noise_rows = 0; k.seed = 0; k.step = 0; k.env_off = 0;
     k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs;
@@ -428,6 +443,9 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "out of host memory");
     h->params = *params;
     h->bound = false;
+    h->dbg_ts = nullptr;
+    h->use_pdl = 1;
+    if (const char* env = getenv("TK_HUMANOID_PDL")) h->use_pdl = atoi(env) != 0;
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->last_grid = 0;
     h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr;
@@ -578,6 +596,13 @@ int tk_humanoid_philox_noise(TkHumanoid* h, uint64_t seed, uint64_t step, int64_
     humanoid_philox_kernel<kD><<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
         h->params.num_envs, seed, step, env_id_offset, unit_pos, unit_vel);
     TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+// developer probe, not part of the public header: per-tile globaltimer stamps [tiles, 8] (tools/tile_timeline.py)
+int tk_debug_humanoid_timeline(TkHumanoid* h, long long* device_buffer) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    h->dbg_ts = device_buffer;
     return TK_OK;
 }
 

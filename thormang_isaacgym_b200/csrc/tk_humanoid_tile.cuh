@@ -46,6 +46,40 @@ __device__ __forceinline__ void warp_copy(float* dst, const float* src, int cnt,
     for (int i = lane; i < cnt; i += 32) dst[i] = src[i];
 }
 
+// reset_idx :253-279 for env `ne` (lane = DOF): draws the noise, writes the new (pos, vel) pairs and the initial root
+// row to GLOBAL memory and returns this lane's values so that the caller can patch its staged copy.
+// `rank` = index of this env among the envs being reset (COMPACT noise rows follow the reference's nonzero() order).
+template <int D>
+__device__ __forceinline__ void reset_env_values(const KParams& p, int ne, int rank, int lane, float2* pv_out, float* root_out) {
+    const long long row = (p.noise_mode == TK_NOISE_COMPACT) ? rank : ne;
+    float2 pv = make_float2(0.0f, 0.0f);
+    float rv = 0.0f;
+    // both global reads are requested before the noise is computed
+    const float idp = (lane < D) ? p.init_dof_pos[static_cast<size_t>(ne) * D + lane] : 0.0f;
+    if (lane < kRoot) rv = p.init_root[static_cast<size_t>(ne) * kRoot + lane];    // :265-267 root row <- initial_root_states
+    if (lane < D) {
+        const int j = lane;
+        float ua = 0.5f, ub = 0.5f;
+        if (p.noise_mode == TK_NOISE_PHILOX) {
+            Philox4 r = philox_env(p.seed, p.step, p.env_off + ne, static_cast<uint32_t>(j >> 1));
+            ua = u01((j & 1) ? r.z : r.x);
+            ub = u01((j & 1) ? r.w : r.y);
+        } else if (p.noise_mode != TK_NOISE_NONE && row < p.noise_rows) {
+            ua = p.unit_a[row * D + j];
+            ub = p.unit_b[row * D + j];
+        }
+        const float positions = 0.4f * ua + (-0.2f);                   // :258 torch_rand_float(-0.2, 0.2)
+        const float velocities = 0.2f * ub + (-0.1f);                  // :259 torch_rand_float(-0.1, 0.1)
+        float np_ = idp + positions;
+        np_ = fmaxf(fminf(np_, p.hi[j]), p.lo[j]);                     // :261 tensor_clamp
+        pv = make_float2(np_, velocities);
+        reinterpret_cast<float2*>(p.dof_state)[static_cast<size_t>(ne) * D + j] = pv;   // :261-262
+    }
+    if (lane < kRoot) p.root[static_cast<size_t>(ne) * kRoot + lane] = rv;
+    *pv_out = pv;
+    *root_out = rv;
+}
+
 #ifndef TK_HUMANOID_MIN_CTAS
 #define TK_HUMANOID_MIN_CTAS 12
 #endif
@@ -64,6 +98,13 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     const int n = env0 + lane;
     const bool valid = lane < nt;
     const bool bulk = (p.vec_ok != 0) && (nt == kTile);   // full, 16-byte aligned tile -> TMA both ways
+    long long* ts = p.dbg_ts ? p.dbg_ts + static_cast<size_t>(blockIdx.x) * 8 : nullptr;
+#define TK_STAMP(i) do { if (ts && lane == 0) { long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ts[i] = g; } } while (0)
+    // programmatic dependent launch: let the next kernel in the stream start scheduling, and do not touch global
+    // memory before the previous kernel has completed and flushed (no-ops when launched without the attribute)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    TK_STAMP(0);
 
     const float* g_dof = p.dof_state + static_cast<size_t>(env0) * D * 2;
     const float* g_force = p.dof_force + static_cast<size_t>(env0) * D;
@@ -74,14 +115,17 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     if (bulk) {
         if (lane == 0) {
             mbar_init(&bar, 1);
-            mbar_fence_init();
+            fence_proxy_async_smem();      // the init (generic proxy) must be visible to the bulk-copy engine (async proxy)
             mbar_expect_tx(&bar, WT::kIn * 4);
-            bulk_load(buf + WT::oDof, g_dof, kTile * D * 2 * 4, &bar);
-            bulk_load(buf + WT::oForce, g_force, kTile * D * 4, &bar);
-            bulk_load(buf + WT::oAct, g_act, kTile * D * 4, &bar);
-            bulk_load(buf + WT::oSens, g_sens, kTile * kSensor * 4, &bar);
-            bulk_load(buf + WT::oRoot, g_root, kTile * kRoot * 4, &bar);
         }
+        __syncwarp();
+        // one bulk load per lane: issuing a cp.async.bulk holds the issuing thread for ~0.25 us (tools/tile_timeline.py),
+        // five lanes pay that once instead of one lane paying it five times
+        if (lane == 0) bulk_load(buf + WT::oDof, g_dof, kTile * D * 2 * 4, &bar);
+        else if (lane == 1) bulk_load(buf + WT::oForce, g_force, kTile * D * 4, &bar);
+        else if (lane == 2) bulk_load(buf + WT::oAct, g_act, kTile * D * 4, &bar);
+        else if (lane == 3) bulk_load(buf + WT::oRoot, g_root, kTile * kRoot * 4, &bar);
+        else if (lane == 4) bulk_load(buf + WT::oSens, g_sens, kTile * kSensor * 4, &bar);
     } else {
         warp_copy(buf + WT::oDof, g_dof, nt * D * 2, lane);
         warp_copy(buf + WT::oForce, g_force, nt * D, lane);
@@ -103,47 +147,57 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
             if (p.randomize) p.randomize[n] += 1;                  // :289
         }
     }
-    __syncwarp();                          // mbarrier init / cooperative copies visible to the warp
-    if (bulk) mbar_wait(&bar, 0);          // bulk loads landed
+    TK_STAMP(1);
 
-    // ---- reset prologue (rare): reset_idx :253-279 for this tile's flagged envs, lane = DOF
+    // ---- reset prologue (rare): reset_idx :253-279 for this tile's flagged envs, lane = DOF.  The new state does not
+    // depend on the staged tile, so for the first kPre flagged envs it is computed and written to global memory WHILE
+    // the bulk loads are still in flight; only the patch of the staged copy waits for them.
+    constexpr int kPre = 2;
+    unsigned reset_bits = 0;
+    int rank0 = 0;
+    float2 pre_pv[kPre];
+    float pre_root[kPre];
     if (FUSED) {
-        unsigned bits = __ballot_sync(0xffffffffu, do_reset);
-        if (bits) {
-            int rank = (p.noise_mode == TK_NOISE_COMPACT) ? p.tile_rank_base[blockIdx.x] : 0;
-            while (bits) {
-                const int e = __ffs(bits) - 1;
-                bits &= bits - 1;
-                const int ne = env0 + e;
-                const long long row = (p.noise_mode == TK_NOISE_COMPACT) ? rank : ne;
-                ++rank;
-                if (lane < D) {
-                    const int j = lane;
-                    float ua = 0.5f, ub = 0.5f;
-                    if (p.noise_mode == TK_NOISE_PHILOX) {
-                        Philox4 r = philox_env(p.seed, p.step, p.env_off + ne, static_cast<uint32_t>(j >> 1));
-                        ua = u01((j & 1) ? r.z : r.x);
-                        ub = u01((j & 1) ? r.w : r.y);
-                    } else if (p.noise_mode != TK_NOISE_NONE && row < p.noise_rows) {
-                        ua = p.unit_a[row * D + j];
-                        ub = p.unit_b[row * D + j];
-                    }
-                    const float positions = 0.4f * ua + (-0.2f);                   // :258 torch_rand_float(-0.2, 0.2)
-                    const float velocities = 0.2f * ub + (-0.1f);                  // :259 torch_rand_float(-0.1, 0.1)
-                    float np_ = p.init_dof_pos[static_cast<size_t>(ne) * D + j] + positions;
-                    np_ = fmaxf(fminf(np_, p.hi[j]), p.lo[j]);                     // :261 tensor_clamp
-                    const float2 pv = make_float2(np_, velocities);
-                    reinterpret_cast<float2*>(p.dof_state)[static_cast<size_t>(ne) * D + j] = pv;   // :261-262
-                    reinterpret_cast<float2*>(buf + WT::oDof)[e * D + j] = pv;
-                }
-                if (lane < kRoot) {                                                // :265-267 root row <- initial_root_states
-                    const float v = p.init_root[static_cast<size_t>(ne) * kRoot + lane];
-                    p.root[static_cast<size_t>(ne) * kRoot + lane] = v;
-                    buf[WT::oRoot + e * kRoot + lane] = v;
+        reset_bits = __ballot_sync(0xffffffffu, do_reset);
+        if (reset_bits) {
+            rank0 = (p.noise_mode == TK_NOISE_COMPACT) ? p.tile_rank_base[blockIdx.x] : 0;
+            unsigned bits = reset_bits;
+#pragma unroll
+            for (int q = 0; q < kPre; ++q) {
+                if (bits) {
+                    const int e = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    reset_env_values<D>(p, env0 + e, rank0 + q, lane, &pre_pv[q], &pre_root[q]);
                 }
             }
-            __syncwarp();
         }
+    }
+    TK_STAMP(2);
+    __syncwarp();                          // mbarrier init / cooperative copies visible to the warp
+    if (bulk) mbar_wait(&bar, 0);          // bulk loads landed
+    TK_STAMP(3);
+
+    if (FUSED && reset_bits) {             // patch the staged rows
+        unsigned bits = reset_bits;
+#pragma unroll
+        for (int q = 0; q < kPre; ++q) {
+            if (bits) {
+                const int e = __ffs(bits) - 1;
+                bits &= bits - 1;
+                if (lane < D) reinterpret_cast<float2*>(buf + WT::oDof)[e * D + lane] = pre_pv[q];
+                if (lane < kRoot) buf[WT::oRoot + e * kRoot + lane] = pre_root[q];
+            }
+        }
+        for (int q = kPre; bits; ++q) {    // more than kPre resets in one tile: the rest after the wait
+            const int e = __ffs(bits) - 1;
+            bits &= bits - 1;
+            float2 pv;
+            float rv;
+            reset_env_values<D>(p, env0 + e, rank0 + q, lane, &pv, &rv);
+            if (lane < D) reinterpret_cast<float2*>(buf + WT::oDof)[e * D + lane] = pv;
+            if (lane < kRoot) buf[WT::oRoot + e * kRoot + lane] = rv;
+        }
+        __syncwarp();
     }
 
     // ---- lane e pulls ITS env's inputs into registers
@@ -173,6 +227,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
         for (int c = 0; c < kRoot; ++c) r[c] = rr[c];
     }
     __syncwarp();   // the whole tile is in registers: from here on the buffer is the obs image
+    TK_STAMP(4);
 
     float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_up = 0.f, st_head = 0.f;
     bool out_reset = false, out_timeout = false;
@@ -230,6 +285,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
             if (out_reset) st_len = static_cast<float>(prog);
         }
     }
+    TK_STAMP(5);
     fence_proxy_async_smem();   // obs image was written through the generic proxy, the bulk engine reads it
     __syncwarp();
 
@@ -272,6 +328,8 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
         }
     }
     if (bulk && lane == 0) bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
+    TK_STAMP(6);
+#undef TK_STAMP
 }
 
 }  // namespace humanoid

@@ -22,18 +22,20 @@ def main():
     ap.add_argument("--envs", default="131072")
     ap.add_argument("--tiles", default="32")
     ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--pdl", default="1")
     ap.add_argument("--warmup", type=int, default=20)
     args = ap.parse_args()
     peak, _ = B.measured_peak_gbs()
     bpe = B.HUMANOID_BYTES_PER_ENV if args.task == "humanoid" else B.GOGORO_BYTES_PER_ENV
     for n in [int(x) for x in args.envs.split(",")]:
-        for tile in [int(x) for x in args.tiles.split(",")]:
+        for tile in [int(x) for x in args.pdl.split(",")]:
+            os.environ["TK_HUMANOID_PDL"] = str(tile)
             os.environ["TK_HUMANOID_TILE"] = str(tile)
             os.environ["TK_GOGORO_TILE"] = str(tile)
             r = G._kernel_bench(torch, args.task, n, "cuda:0", args.steps, args.warmup, seed=5)
             us = 1e3 * r["ms_total"] / args.steps
             gbs = n * bpe / (us * 1e-6) / 1e9
-            print(json.dumps({"task": args.task, "envs": n, "tile": tile, "us_per_step": round(us, 2),
+            print(json.dumps({"task": args.task, "envs": n, "pdl": tile, "us_per_step": round(us, 2),
                               "GBps": round(gbs, 1), "frac": round(gbs / peak, 4), "sets": r["sets"]}), flush=True)
 
 

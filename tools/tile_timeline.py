@@ -1,0 +1,46 @@
+"""Per-tile phase timeline of the Humanoid stream kernel (developer probe; globaltimer stamps in ns).
+
+    python tools/tile_timeline.py --envs 16384
+"""
+import argparse
+import ctypes as C
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+import bench_gpu as G  # noqa: E402
+from thormang_isaacgym_b200 import _native as nat  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--envs", type=int, default=16384)
+a = ap.parse_args()
+n = a.envs
+envs = [G._make_humanoid(n, 10 + s, "cuda:0")[0] for s in range(8)]
+lib = nat.lib()
+lib.tk_debug_humanoid_timeline.argtypes = [C.c_void_p, C.c_void_p]
+tiles = (n + 31) // 32
+for e in envs:
+    e.post_physics_step()
+torch.cuda.synchronize()
+buf = torch.zeros((tiles, 8), dtype=torch.int64, device="cuda:0")
+e = envs[3]
+lib.tk_debug_humanoid_timeline(e._handle, C.c_void_p(buf.data_ptr()))
+# flush L2 with the other sets, then the probed launch
+for o in envs[4:] + envs[:3]:
+    o.post_physics_step()
+torch.cuda.synchronize()
+e.post_physics_step()
+torch.cuda.synchronize()
+t = buf.cpu().double()
+t0 = t[:, 0].min()
+names = ["start", "scalars issued", "scalars landed", "bulk landed", "inputs in regs", "math+STS done", "store read done"]
+print(f"tiles {tiles}; kernel span {(t[:, 6].max() - t0) / 1e3:.2f} us")
+for i, nm in enumerate(names):
+    col = t[:, i] - t0
+    print(f"{nm:18s} min {col.min()/1e3:7.2f}  median {col.median()/1e3:7.2f}  max {col.max()/1e3:7.2f} us")
+d = t[:, 1:7] - t[:, 0:6]
+for i, nm in enumerate(["issue", "scalar wait", "bulk wait", "reset+reg read", "math+STS", "store"]):
+    print(f"  phase {nm:14s} median {d[:, i].median()/1e3:6.2f}  mean {d[:, i].mean()/1e3:6.2f}  p95 {d[:, i].quantile(0.95)/1e3:6.2f} us")
