@@ -63,9 +63,10 @@ def recorded_traffic(task):
     path = os.path.join(ROOT, "profiles", "traffic.json")
     try:
         with open(path) as fh:
-            return json.load(fh).get(task)
+            doc = json.load(fh)
+            return doc.get(task), doc.get(task + "_note")
     except Exception:
-        return None
+        return None, None
 
 
 class ClockSampler:

@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libthormang_b200.so")
+LIB_PATH = os.environ.get("THORMANG_B200_LIB") or os.path.join(_PKG, "libthormang_b200.so")   # env: developer A/B builds
 
 TK_MAX_DOF = 64
 TK_STATS = 8
