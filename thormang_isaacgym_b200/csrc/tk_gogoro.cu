@@ -214,6 +214,9 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
     const bool valid = tid < nt;
     const bool vec = p.vec_ok != 0;
     const bool philox = p.noise_mode == TK_NOISE_PHILOX;
+    // programmatic dependent launch (no-ops without the launch attribute)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 
     tile_load(s.root, p.root + static_cast<size_t>(env0) * kRoot, nt * kRoot, vec, tid);
     if (MODE != 2) {
@@ -740,7 +743,21 @@ int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream
         exclusive_scan_kernel<<<1, 1024, 0, st>>>(h->counts, h->tiles, h->bases);
         exclusive_scan_kernel<<<1, 1024, 0, st>>>(h->counts + h->tiles, h->tiles, h->bases + h->tiles);
     }
-    gogoro_tile_kernel<0><<<h->tiles, kTile, 0, st>>>(k, nullptr);
+    {
+        // programmatic dependent launch: CTAs may be scheduled while the previous kernel in the stream drains; the
+        // kernel executes griddepcontrol.wait before it touches global memory, so stream order is kept
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(h->tiles);
+        cfg.blockDim = dim3(kTile);
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        float* no_out = nullptr;
+        cudaLaunchKernelEx(&cfg, gogoro_tile_kernel<0>, k, no_out);
+    }
     TK_CUDA(cudaGetLastError());
     h->last_grid = h->tiles;
     return TK_OK;

@@ -146,6 +146,11 @@ class Gogoro(VecTask):
         handle = C.c_void_p()
         nat.check(lib.tk_gogoro_create(C.byref(p), C.byref(handle)), "tk_gogoro_create")
         self._handle, self._lib = handle, lib
+        self._post_physics = lib.tk_gogoro_post_physics
+        self._torch_device = torch.device(self.device)
+        self._philox_noise = nat.GogoroNoise()
+        self._philox_noise.reset.mode = nat.NOISE_PHILOX
+        self._philox_noise_ref = C.byref(self._philox_noise)
         self._bind()
 
     def _bind(self):
@@ -238,8 +243,19 @@ class Gogoro(VecTask):
                           speed_unit: Optional[torch.Tensor] = None, yaw_unit: Optional[torch.Tensor] = None,
                           noise_mode: Optional[int] = None):
         """gogoro_new.py:373-389 + vec_task.py:345 as one fused kernel (Philox noise unless the draws are supplied)."""
-        nz = nat.GogoroNoise()
         supplied = sensor_unit is not None or reset_unit is not None
+        if not supplied and noise_mode is None and speed_unit is None and yaw_unit is None:
+            # production path: in-kernel Philox, nothing allocated per step
+            nz = self._philox_noise
+            nz.reset.seed, nz.reset.step, nz.reset.env_id_offset = self.noise_seed, self.step_count, self.env_id_offset
+            rc = self._post_physics(self._handle, self._philox_noise_ref,
+                                    torch.cuda.current_stream(self._torch_device).cuda_stream)
+            if rc:
+                nat.check(rc, "tk_gogoro_post_physics")
+            self.step_count += 1
+            self.curent_step += 1
+            return
+        nz = nat.GogoroNoise()
         if noise_mode is None:
             noise_mode = nat.NOISE_COMPACT if supplied else nat.NOISE_PHILOX
         nz.reset.mode = noise_mode

@@ -156,6 +156,11 @@ class Humanoid(VecTask):
         nat.check(lib.tk_humanoid_create(C.byref(p), C.byref(handle)), "tk_humanoid_create")
         self._handle = handle
         self._lib = lib
+        self._post_physics = lib.tk_humanoid_post_physics
+        self._torch_device = torch.device(self.device)
+        self._noise = nat.ResetNoise()
+        self._noise.seed, self._noise.env_id_offset = self.noise_seed, self.env_id_offset
+        self._noise_ref = C.byref(self._noise)
         self._bind()
 
     def _bind(self):
@@ -232,16 +237,18 @@ class Humanoid(VecTask):
     def post_physics_step(self, unit_pos: Optional[torch.Tensor] = None, unit_vel: Optional[torch.Tensor] = None,
                           noise_mode: Optional[int] = None):
         """humanoid.py:287-296 + vec_task.py:345 as one fused kernel."""
-        noise = nat.ResetNoise()
+        noise = self._noise                     # one struct per task object: nothing is allocated per step
         if unit_pos is not None:
             unit_pos, unit_vel = unit_pos.contiguous(), unit_vel.contiguous()
             noise.mode = nat.NOISE_COMPACT if noise_mode is None else noise_mode
             noise.unit_a, noise.unit_b, noise.rows = nat.ptr(unit_pos), nat.ptr(unit_vel), unit_pos.shape[0]
         else:
             noise.mode = nat.NOISE_PHILOX if noise_mode is None else noise_mode
+            noise.unit_a, noise.unit_b, noise.rows = None, None, 0
         noise.seed, noise.step, noise.env_id_offset = self.noise_seed, self.step_count, self.env_id_offset
-        nat.check(self._lib.tk_humanoid_post_physics(self._handle, C.byref(noise), self._stream()),
-                  "tk_humanoid_post_physics")
+        rc = self._post_physics(self._handle, self._noise_ref, torch.cuda.current_stream(self._torch_device).cuda_stream)
+        if rc:
+            nat.check(rc, "tk_humanoid_post_physics")
         self.step_count += 1
 
     # ------------------------------------------------------------------------------------------
