@@ -125,7 +125,8 @@ typedef struct TkResetNoise {
     const float* unit_b;             /* Humanoid: U(0,1) [rows,D] for velocities (humanoid.py:259)  | Gogoro: unused */
     int64_t rows;                    /* rows available in unit_a / unit_b */
     uint64_t seed;                   /* PHILOX */
-    uint64_t step;                   /* PHILOX: step counter */
+    uint64_t step;                   /* PHILOX: step offset, ADDED to the handle's device-side count of completed fused
+                                      * post-physics launches (a captured CUDA graph draws fresh noise on every replay) */
     int64_t env_id_offset;           /* PHILOX: global id of local env 0 (range-sharded multi-GPU runs) */
 } TkResetNoise;
 

@@ -175,3 +175,27 @@ def test_sharded_equals_unsharded():
         e2.post_physics_step()
         for k in ("obs_buf", "buffer_obs", "rew_buf", "reset_buf", "progress_buf", "yaw_command", "curent_speed", "root_tensor"):
             U.exact(getattr(e2, k), getattr(env, k)[sl], f"shard {r} {k}")
+
+
+def test_cuda_graph_replay_matches_eager():
+    n = 4096
+    env_a, _, st = U.make_gogoro_pair(n, seed=61)
+    env_b, _, _ = U.make_gogoro_pair(n, seed=61, state={k: v.clone() for k, v in st.items()})
+    a = st["actions"].to(DEV)
+
+    def step(env):
+        env.pre_physics_step(a)
+        env.post_physics_step()
+
+    for _ in range(4):
+        step(env_a)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        step(env_b)
+        step(env_b)
+    g.replay(); g.replay()
+    torch.cuda.synchronize()
+    for name in ("obs_buf", "buffer_obs", "rew_buf", "reset_buf", "progress_buf", "root_tensor", "curent_command",
+                 "action_history", "yaw_command", "curent_speed", "dof_pos_command"):
+        U.exact(getattr(env_b, name), getattr(env_a, name), f"graph vs eager: {name}")

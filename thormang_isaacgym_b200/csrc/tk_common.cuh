@@ -237,6 +237,21 @@ __device__ __host__ __forceinline__ Philox4 philox_env(uint64_t seed, uint64_t s
 }
 
 // ---------------------------------------------------------------------------------------------
+// Device-side step counter.  One thread per CTA calls this when the CTA's work is done; the last CTA of the launch
+// bumps the counter that the Philox streams add to their `step`, so a CUDA graph that captured the launch draws
+// fresh noise on every replay.  Nothing of the running launch reads the counter after this point, and the next
+// launch reads it only after griddepcontrol.wait / stream order.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void launch_epilogue(unsigned int* ticket, unsigned long long* step_dev) {
+    __threadfence();
+    const unsigned int t = atomicAdd(ticket, 1u);
+    if (t == gridDim.x - 1) {
+        *step_dev = *step_dev + 1ull;
+        *ticket = 0u;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // warp helpers
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double v) {

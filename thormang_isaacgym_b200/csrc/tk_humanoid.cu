@@ -75,6 +75,8 @@ struct KParams {
     float tgt[3], isr[4], b0[3], b1[3];
     float lo[TK_MAX_DOF], hi[TK_MAX_DOF], effort[TK_MAX_DOF];
     float rinv[TK_MAX_DOF];     // 1 / (hi - lo), rounded to fp32 on the host
+    unsigned long long* step_dev;   // device-side count of completed fused post-physics launches (added to `step`)
+    unsigned int* ticket;           // CTAs of the current launch that have finished
     long long* dbg_ts;          // developer timeline probe (tools/tile_timeline.py); NULL in normal use
 };
 
@@ -333,7 +335,9 @@ __global__ void humanoid_reset_idx_kernel(const __grid_constant__ KParams p, con
 
 template <int D>
 __global__ void humanoid_philox_kernel(int n, unsigned long long seed, unsigned long long step, long long env_off,
-                                       float* __restrict__ ua, float* __restrict__ ub) {
+                                       const unsigned long long* __restrict__ step_dev, float* __restrict__ ua,
+                                       float* __restrict__ ub) {
+    step += *step_dev;   // the draws of the NEXT fused launch
     const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= static_cast<long long>(n) * D) return;
     const long long e = i / D;
@@ -375,6 +379,8 @@ struct TkHumanoid {
     int* tile_base;       // [tiles]
     int last_grid;
     int use_pdl;          // programmatic dependent launch (TK_HUMANOID_PDL=0 disables)
+    unsigned long long* step_dev;
+    unsigned int* ticket;
     long long* dbg_ts;
 };
 
@@ -406,7 +412,7 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     k.timeout = B.timeout_buf; k.randomize = reinterpret_cast<long long*>(B.randomize_buf);
     k.pot = B.potentials; k.prev_pot = B.prev_potentials; k.up_vec = B.up_vec; k.heading_vec = B.heading_vec;
     k.init_root = B.initial_root_states; k.init_dof_pos = B.initial_dof_pos; k.ep_return = B.episode_return;
-    k.partials = h->partials; k.tile_rank_base = h->tile_base; k.dbg_ts = h->dbg_ts;
+    k.partials = h->partials; k.tile_rank_base = h->tile_base; k.dbg_ts = h->dbg_ts; k.step_dev = h->step_dev; k.ticket = h->ticket;
     k.unit_a = nullptr; k.unit_b = nullptr; k.noise_rows = 0; k.seed = 0; k.step = 0; k.env_off = 0;
     k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs;
@@ -448,14 +454,18 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     if (const char* env = getenv("TK_HUMANOID_PDL")) h->use_pdl = atoi(env) != 0;
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->last_grid = 0;
-    h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr;
+    h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr; h->step_dev = nullptr; h->ticket = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->tile_counts, sizeof(int) * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->tile_base, sizeof(int) * h->tiles);
     if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * h->tiles);
     if (e == cudaSuccess) e = cudaMemset(h->tile_base, 0, sizeof(int) * h->tiles);
+    if (e == cudaSuccess) e = cudaMalloc(&h->step_dev, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&h->ticket, sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMemset(h->step_dev, 0, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(h->ticket, 0, sizeof(unsigned int));
     if (e != cudaSuccess) {
-        cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base);
+        cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base); cudaFree(h->step_dev); cudaFree(h->ticket);
         delete h;
         return cuda_fail(e, "tk_humanoid_create");
     }
@@ -466,7 +476,7 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
 int tk_humanoid_destroy(TkHumanoid* h) {
     if (!h) return TK_OK;
     cudaSetDevice(h->params.device);
-    cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base);
+    cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base); cudaFree(h->step_dev); cudaFree(h->ticket);
     delete h;
     return TK_OK;
 }
@@ -594,7 +604,7 @@ int tk_humanoid_philox_noise(TkHumanoid* h, uint64_t seed, uint64_t step, int64_
     TK_CUDA(cudaSetDevice(h->params.device));
     const long long total = static_cast<long long>(h->params.num_envs) * kD;
     humanoid_philox_kernel<kD><<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        h->params.num_envs, seed, step, env_id_offset, unit_pos, unit_vel);
+        h->params.num_envs, seed, step, env_id_offset, h->step_dev, unit_pos, unit_vel);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }

@@ -102,7 +102,8 @@ class Humanoid(VecTask):
         # in-kernel reset noise
         self.noise_seed = int(cfg.get("seed", 0)) & 0xFFFFFFFFFFFFFFFF
         self.env_id_offset = int(env.get("envIdOffset", 0))   # global id of local env 0 (multi-GPU range sharding)
-        self.step_count = 0
+        self.step_count = 0        # launches issued from this object (information only)
+        self.step_offset = 0       # added to the device-side launch counter that keys the in-kernel Philox streams
         self._handle = None
         self._create_native()
 
@@ -245,7 +246,7 @@ class Humanoid(VecTask):
         else:
             noise.mode = nat.NOISE_PHILOX if noise_mode is None else noise_mode
             noise.unit_a, noise.unit_b, noise.rows = None, None, 0
-        noise.seed, noise.step, noise.env_id_offset = self.noise_seed, self.step_count, self.env_id_offset
+        noise.seed, noise.step, noise.env_id_offset = self.noise_seed, self.step_offset, self.env_id_offset
         rc = self._post_physics(self._handle, self._noise_ref, torch.cuda.current_stream(self._torch_device).cuda_stream)
         if rc:
             nat.check(rc, "tk_humanoid_post_physics")
@@ -271,7 +272,7 @@ class Humanoid(VecTask):
         ua = torch.empty((self.num_envs, self.num_dof), device=self.device)
         ub = torch.empty_like(ua)
         nat.check(self._lib.tk_humanoid_philox_noise(self._handle, self.noise_seed,
-                                                     self.step_count if step is None else step, self.env_id_offset,
+                                                     self.step_offset if step is None else step, self.env_id_offset,
                                                      nat.ptr(ua), nat.ptr(ub), self._stream()), "tk_humanoid_philox_noise")
         return ua, ub
 
