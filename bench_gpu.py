@@ -86,12 +86,32 @@ def _time_steps(torch, step_fn, steps, warmup, barrier=None):
     return ev0.elapsed_time(ev1), launches, (t0, t1)
 
 
-def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, barrier=None, horizon_hook=None):
-    """Fused post-physics kernel over rotating state sets.  Returns dict(ms_total, launches, sets, window)."""
+def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, barrier=None, horizon_hook=None,
+                  graph=False):
+    """Fused post-physics kernel over rotating state sets.  Returns dict(ms_total, launches, sets, window).
+    graph=True: one pass over the sets is captured in a CUDA graph and replayed (steps is rounded to whole passes)."""
     bpe = B.HUMANOID_BYTES_PER_ENV if task == "humanoid" else B.GOGORO_BYTES_PER_ENV
     sets = _rotating_sets(n, bpe)
     make = _make_humanoid if task == "humanoid" else _make_gogoro
     envs = [make(n, seed + 17 * s, device, env_off)[0] for s in range(sets)]
+
+    if graph:
+        for e in envs:
+            e.post_physics_step()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for e in envs:
+                e.advance_noise_epoch()
+                e.post_physics_step()
+        passes = max(1, steps // sets)
+
+        def replay(i):
+            g.replay()
+            return sets
+        ms, launches, window = _time_steps(torch, replay, passes, max(1, warmup // sets), barrier)
+        del envs
+        return {"ms_total": ms, "launches": launches, "sets": sets, "window": window, "steps": passes * sets}
 
     def step(i):
         envs[i % sets].post_physics_step()
@@ -102,7 +122,7 @@ def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, b
 
     ms, launches, window = _time_steps(torch, step, steps, warmup, barrier)
     del envs
-    return {"ms_total": ms, "launches": launches, "sets": sets, "window": window}
+    return {"ms_total": ms, "launches": launches, "sets": sets, "window": window, "steps": steps}
 
 
 def _e2e_bench(torch, n, device, steps, chunks, env_off, barrier=None):
@@ -136,8 +156,25 @@ def _e2e_bench(torch, n, device, steps, chunks, env_off, barrier=None):
             "launches": steps * chunks, "window": (t0, t1)}
 
 
-def _step_loop_bench(torch, n, device, horizon, reps):
-    """BASELINE config 5: pre_physics (clamp + force write) -> fake physics (identity) -> fused post_physics, PPO horizon."""
+def _pcie_probe(torch, device, mb=64):
+    """Pinned-memory copy bandwidth of this box, for reading the e2e number (one direction at a time)."""
+    host = torch.empty(mb * 1024 * 1024, dtype=torch.uint8, pin_memory=True)
+    dev = torch.empty_like(host, device=device)
+    out = {}
+    for name, (dst, src) in (("h2d_GBps", (dev, host)), ("d2h_GBps", (host, dev))):
+        dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(5):
+            dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        out[name] = 5 * host.numel() / (time.perf_counter() - t0) / 1e9
+    return out
+
+
+def _step_loop_bench(torch, n, device, horizon, reps, graph=False):
+    """BASELINE config 5: pre_physics (clamp + force write) -> fake physics (identity) -> fused post_physics, PPO horizon.
+    graph=True captures one horizon (2 x horizon kernels) in a CUDA graph and replays it."""
     env, st = _make_humanoid(n, 999, device)
     acts = [torch.rand((n, 21), device=device) * 2.4 - 1.2 for _ in range(4)]
 
@@ -148,9 +185,20 @@ def _step_loop_bench(torch, n, device, horizon, reps):
         env.sim.simulate()
         env.post_physics_step()
         return 2
-    ms, launches, _ = _time_steps(torch, one, horizon * reps, horizon)
+    if graph:
+        for i in range(4):
+            one(i)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            env.advance_noise_epoch()
+            for i in range(horizon):
+                one(i)
+        ms, launches, _ = _time_steps(torch, lambda i: (g.replay(), 2 * horizon)[1], reps, 2)
+    else:
+        ms, launches, _ = _time_steps(torch, one, horizon * reps, horizon)
     return {"envs": n, "horizon": horizon, "env_steps_per_s": n * horizon * reps / (ms * 1e-3),
-            "ms_per_step": ms / (horizon * reps), "launches_per_step": 2,
+            "us_per_step": 1e3 * ms / (horizon * reps), "launches_per_step": 2, "cuda_graph": graph,
             "note": "pre (252 B/env) + post (924 B/env) on ONE state set: L2-resident at this size, not an HBM number"}
 
 
@@ -256,16 +304,26 @@ def run_gpu_arm(args, rank, world):
     if world == 1 and not args.no_extras:
         extras = {}
         try:
-            for label, t, m in (("config2_humanoid_16384", "humanoid", 16384), ("humanoid_65536", "humanoid", 65536),
-                                ("humanoid_262144", "humanoid", 262144),
-                                ("config3_gogoro_65536", "gogoro", 65536), ("gogoro_4194304", "gogoro", 4194304)):
+            for label, t, m, gr in (("config2_humanoid_16384", "humanoid", 16384, False),
+                                    ("config2_humanoid_16384_cuda_graph", "humanoid", 16384, True),
+                                    ("humanoid_65536", "humanoid", 65536, False),
+                                    ("humanoid_65536_cuda_graph", "humanoid", 65536, True),
+                                    ("humanoid_262144", "humanoid", 262144, False),
+                                    ("humanoid_1048576", "humanoid", 1048576, False),
+                                    ("config3_gogoro_65536", "gogoro", 65536, False),
+                                    ("config3_gogoro_65536_cuda_graph", "gogoro", 65536, True),
+                                    ("gogoro_4194304", "gogoro", 4194304, False)):
                 k = 300 if m <= 262144 else 60
-                r = _kernel_bench(torch, t, m, device, k, 20, seed=77)
+                r = _kernel_bench(torch, t, m, device, k, 20, seed=77, graph=gr)
+                k = r["steps"]
                 b = B.HUMANOID_BYTES_PER_ENV if t == "humanoid" else B.GOGORO_BYTES_PER_ENV
                 gbs = m * b / (r["ms_total"] / k * 1e-3) / 1e9
                 extras[label] = {"env_steps_per_s": m * k / (r["ms_total"] * 1e-3), "us_per_step": 1e3 * r["ms_total"] / k,
                                  "achieved_GBps": gbs, "frac_of_peak": gbs / peak, "rotating_sets": r["sets"]}
             extras["config5_step_loop_131072x32"] = _step_loop_bench(torch, 131072, device, 32, 8)
+            extras["config5_step_loop_4096x32_cuda_graph"] = _step_loop_bench(torch, 4096, device, 32, 20, graph=True)
+            extras["config5_step_loop_4096x32"] = _step_loop_bench(torch, 4096, device, 32, 20)
+            extras["pcie"] = _pcie_probe(torch, device)
         except Exception as exc:   # extras must never cost the headline line
             extras["error"] = repr(exc)
         line["extras"] = extras

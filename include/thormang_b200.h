@@ -125,8 +125,8 @@ typedef struct TkResetNoise {
     const float* unit_b;             /* Humanoid: U(0,1) [rows,D] for velocities (humanoid.py:259)  | Gogoro: unused */
     int64_t rows;                    /* rows available in unit_a / unit_b */
     uint64_t seed;                   /* PHILOX */
-    uint64_t step;                   /* PHILOX: step offset, ADDED to the handle's device-side count of completed fused
-                                      * post-physics launches (a captured CUDA graph draws fresh noise on every replay) */
+    uint64_t step;                   /* PHILOX: step counter (< 2^32); the handle's device-side noise epoch is added as
+                                      * the upper 32 bits, see tk_*_advance_epoch */
     int64_t env_id_offset;           /* PHILOX: global id of local env 0 (range-sharded multi-GPU runs) */
 } TkResetNoise;
 
@@ -168,6 +168,10 @@ int tk_humanoid_wm_reward(TkHumanoid* h, const float* obs, int64_t m, float* rew
 /* Materialise the U(0,1) draws TK_NOISE_PHILOX uses for (seed, step): unit_pos/unit_vel [N,D] (parity checks). */
 int tk_humanoid_philox_noise(TkHumanoid* h, uint64_t seed, uint64_t step, int64_t env_id_offset,
                              float* unit_pos, float* unit_vel, void* stream);
+
+/* Bump the device-side noise epoch (one single-thread kernel).  Host-supplied `step` values are frozen inside a captured
+ * CUDA graph; capturing ONE call of this per graph makes every replay draw fresh Philox noise.  Not needed otherwise. */
+int tk_humanoid_advance_epoch(TkHumanoid* h, void* stream);
 
 /* Episode statistics.  Every tk_humanoid_post_physics adds its per-CTA partial sums into a handle-owned
  * [grid, TK_STATS] fp64 array (each CTA owns its row: no atomics, deterministic).  This call sums the rows in a
@@ -273,6 +277,9 @@ int tk_gogoro_reset_idx(TkGogoro* h, const int64_t* env_ids, int32_t k, const fl
 
 /* Gogoro.post_physics_step (gogoro_new.py:373-389) + vec_task.py:345, ONE fused kernel. */
 int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream);
+
+/* same as tk_humanoid_advance_epoch */
+int tk_gogoro_advance_epoch(TkGogoro* h, void* stream);
 
 /* stats: sum reward, #reset, #timeout, sum episode_return of reset envs, sum episode length of reset envs,
  * sum |tilt|, sum |yaw error|, N */

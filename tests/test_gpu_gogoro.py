@@ -183,15 +183,19 @@ def test_cuda_graph_replay_matches_eager():
     env_b, _, _ = U.make_gogoro_pair(n, seed=61, state={k: v.clone() for k, v in st.items()})
     a = st["actions"].to(DEV)
 
-    def step(env):
+    def step(env, key=None):
+        if key is not None:
+            env.step_count = key
         env.pre_physics_step(a)
         env.post_physics_step()
 
-    for _ in range(4):
-        step(env_a)
+    for r in range(2):
+        for i in range(2):
+            step(env_a, key=i + ((r + 1) << 32))    # captured step i of replay r: host step i, device epoch r + 1
     torch.cuda.synchronize()
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g):
+        env_b.advance_noise_epoch()
         step(env_b)
         step(env_b)
     g.replay(); g.replay()

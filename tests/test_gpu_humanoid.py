@@ -277,25 +277,29 @@ def test_error_behaviour():
 
 
 def test_cuda_graph_replay_matches_eager():
-    """The C-ABI calls allocate nothing and never synchronise, so a rollout can be captured in a CUDA graph.  The Philox
-    step lives in a device-side counter: every replay draws fresh reset noise, exactly like the eager run."""
+    """The C-ABI calls allocate nothing and never synchronise, so a rollout can be captured in a CUDA graph.  The host
+    step counter is frozen in the captured launches; the device-side noise epoch (bumped once per replay) supplies the
+    upper 32 bits of the Philox step, so every replay draws fresh reset noise -- reproduced here by an eager run."""
     n = 4096
     env_a, _, st = U.make_humanoid_pair(n, seed=31)
     env_b, _, _ = U.make_humanoid_pair(n, seed=31, state={k: v.clone() for k, v in st.items()})
     acts = [(torch.rand(n, 21, generator=torch.Generator().manual_seed(i)) * 2 - 1).to(DEV) for i in range(2)]
 
-    def two_steps(env):
-        for a in acts:
+    def two_steps(env, epoch=None):
+        for i, a in enumerate(acts):
             env._clip_in_kernel = True
             env.pre_physics_step(a)
             env._clip_in_kernel = False
+            if epoch is not None:
+                env.step_count = i + (epoch << 32)      # what the captured launch + device epoch amount to
             env.post_physics_step()
 
-    for _ in range(3):
-        two_steps(env_a)
+    for r in range(3):
+        two_steps(env_a, epoch=r + 1)
     torch.cuda.synchronize()
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g):
+        env_b.advance_noise_epoch()
         two_steps(env_b)
     for _ in range(3):
         g.replay()

@@ -84,6 +84,8 @@ SYMBOLS = {
     "tk_humanoid_wm_reward": (C.c_int, [_p, _p, _i64, _p, _p]),
     "tk_humanoid_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p, _p]),
     "tk_humanoid_stats": (C.c_int, [_p, _p, _i32, _p]),
+    "tk_humanoid_advance_epoch": (C.c_int, [_p, _p]),
+    "tk_gogoro_advance_epoch": (C.c_int, [_p, _p]),
     "tk_gogoro_create": (C.c_int, [C.POINTER(GogoroParams), C.POINTER(_p)]),
     "tk_gogoro_destroy": (C.c_int, [_p]),
     "tk_gogoro_bind": (C.c_int, [_p, C.POINTER(GogoroBuffers)]),

@@ -22,6 +22,8 @@ int cuda_fail(cudaError_t e, const char* what) {
 
 const char* last_error() { return g_error; }
 
+__global__ void advance_epoch_kernel(unsigned long long* epoch) { *epoch += 1ull; }
+
 }  // namespace tk
 
 extern "C" {

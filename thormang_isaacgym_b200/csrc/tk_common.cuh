@@ -237,19 +237,16 @@ __device__ __host__ __forceinline__ Philox4 philox_env(uint64_t seed, uint64_t s
 }
 
 // ---------------------------------------------------------------------------------------------
-// Device-side step counter.  One thread per CTA calls this when the CTA's work is done; the last CTA of the launch
-// bumps the counter that the Philox streams add to their `step`, so a CUDA graph that captured the launch draws
-// fresh noise on every replay.  Nothing of the running launch reads the counter after this point, and the next
-// launch reads it only after griddepcontrol.wait / stream order.
+// Noise epoch.  The Philox streams are keyed by (seed, step, global env id); `step` comes from the host with every
+// call, so it is frozen inside a captured CUDA graph.  A device-side epoch, bumped by tk_*_advance_epoch (one
+// single-thread kernel, captured once per graph), is folded into the upper 32 bits of the step: every replay of the
+// graph draws fresh noise.  (A per-launch device counter was tried first: one same-address RED per CTA cost 20 % of
+// the kernel time at 32768 CTAs.)
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void launch_epilogue(unsigned int* ticket, unsigned long long* step_dev) {
-    __threadfence();
-    const unsigned int t = atomicAdd(ticket, 1u);
-    if (t == gridDim.x - 1) {
-        *step_dev = *step_dev + 1ull;
-        *ticket = 0u;
-    }
+__device__ __forceinline__ unsigned long long effective_step(unsigned long long step, const unsigned long long* epoch) {
+    return step + (*epoch << 32);
 }
+__global__ void advance_epoch_kernel(unsigned long long* epoch);
 
 // ---------------------------------------------------------------------------------------------
 // warp helpers

@@ -56,8 +56,7 @@ struct KParams {
     const float* yaw_unit;
     long long reset_rows;
     unsigned long long seed, step;
-    unsigned long long* step_dev;   // device-side count of completed fused post-physics launches (added to `step`)
-    unsigned int* ticket;
+    unsigned long long* step_dev;   // device-side noise epoch (upper 32 bits of the Philox step), see tk_common.cuh
     long long env_off;
     int noise_mode;
     int n, num_dof, steering_joint, rear_wheel_joint, max_episode_length, speed_freq, yaw_freq;
@@ -219,7 +218,7 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
     // programmatic dependent launch (no-ops without the launch attribute)
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    const unsigned long long step_now = philox ? p.step + *p.step_dev : 0ull;
+    const unsigned long long step_now = philox ? effective_step(p.step, p.step_dev) : 0ull;
 
     tile_load(s.root, p.root + static_cast<size_t>(env0) * kRoot, nt * kRoot, vec, tid);
     if (MODE != 2) {
@@ -392,7 +391,6 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         tile_store(p.buffer_obs + static_cast<size_t>(env0) * kObs, s.clean, nt * kObs, vec, tid);
         tile_store(p.obs_buf + static_cast<size_t>(env0) * kObs, s.noisy, nt * kObs, vec, tid);
     }
-    if (MODE == 0 && tid == 0) launch_epilogue(p.ticket, p.step_dev);
 }
 
 // per-tile counts of the two COMPACT predicates: reset != 0 ; reset == 0 && progress + 1 == speed_freq
@@ -471,7 +469,7 @@ __global__ void __launch_bounds__(256) gogoro_pre_kernel(const __grid_constant__
     float cmd = p.curent_command[n] + a2;                                           // :355
     cmd = fminf(fmaxf(cmd, -p.max_steering), p.max_steering);                       // :359
     p.curent_command[n] = cmd;
-    float z = steer_unit ? steer_unit[n] : philox_misc_noise(p.seed, p.step + *p.step_dev, p.env_off + n).steer;
+    float z = steer_unit ? steer_unit[n] : philox_misc_noise(p.seed, effective_step(p.step, p.step_dev), p.env_off + n).steer;
     float noise = normal_of(p.steer_action, z);                                     // :362
     p.pos_cmd[n * p.num_dof + p.steering_joint] = cmd + p.steer_offsets[n] + noise; // :363
     p.vel_cmd[n * p.num_dof + p.rear_wheel_joint] = p.curent_speed[n];              // :367
@@ -515,9 +513,9 @@ __global__ void gogoro_reset_idx_kernel(const __grid_constant__ KParams p, const
 }
 
 __global__ void gogoro_philox_kernel(int n, unsigned long long seed, unsigned long long step, long long env_off,
-                                     const unsigned long long* __restrict__ step_dev, float* steer, float* sensor,
-                                     float* reset_unit, float* speed, float* yaw) {
-    step += *step_dev;   // the draws of the NEXT pre/post-physics launches
+                                     const unsigned long long* __restrict__ epoch, float* steer,
+                                     float* sensor, float* reset_unit, float* speed, float* yaw) {
+    step = effective_step(step, epoch);   // the draws of the NEXT pre/post-physics launches
     const long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (e >= n) return;
     StepNoise sn = philox_sensor_noise(seed, step, env_off + e);
@@ -565,7 +563,6 @@ struct TkGogoro {
     int* bases;    // [2, tiles]
     int last_grid;
     unsigned long long* step_dev;
-    unsigned int* ticket;
 };
 
 static void pair_uniform(const double* in, float* out) { out[0] = static_cast<float>(in[0]); out[1] = static_cast<float>(in[1] - in[0]); }
@@ -583,7 +580,7 @@ static void fill_kparams(const TkGogoro* h, KParams& k) {
     k.vel_cmd = B.dof_speed_command; k.ep_return = B.episode_return;
     k.partials = h->partials; k.tile_base_reset = h->bases; k.tile_base_speed = h->bases + h->tiles;
     k.reset_unit = nullptr; k.sensor_unit = nullptr; k.speed_unit = nullptr; k.yaw_unit = nullptr; k.reset_rows = 0;
-    k.seed = 0; k.step = 0; k.env_off = 0; k.noise_mode = TK_NOISE_NONE; k.step_dev = h->step_dev; k.ticket = h->ticket;
+    k.seed = 0; k.step = 0; k.env_off = 0; k.noise_mode = TK_NOISE_NONE; k.step_dev = h->step_dev;
     k.n = P.num_envs; k.num_dof = P.num_dof; k.steering_joint = P.steering_joint; k.rear_wheel_joint = P.rear_wheel_joint;
     k.max_episode_length = P.max_episode_length; k.speed_freq = P.speed_freq_update; k.yaw_freq = P.yaw_freq_update;
     k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.action_history, 16) && aligned_to(B.obs_buf, 16) &&
@@ -618,18 +615,16 @@ int tk_gogoro_create(const TkGogoroParams* params, TkGogoro** out) {
     h->bound = false;
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->last_grid = 0;
-    h->partials = nullptr; h->counts = nullptr; h->bases = nullptr; h->step_dev = nullptr; h->ticket = nullptr;
+    h->partials = nullptr; h->counts = nullptr; h->bases = nullptr; h->step_dev = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->counts, sizeof(int) * 2 * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->bases, sizeof(int) * 2 * h->tiles);
     if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * h->tiles);
     if (e == cudaSuccess) e = cudaMemset(h->bases, 0, sizeof(int) * 2 * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->step_dev, sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMalloc(&h->ticket, sizeof(unsigned int));
     if (e == cudaSuccess) e = cudaMemset(h->step_dev, 0, sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMemset(h->ticket, 0, sizeof(unsigned int));
     if (e != cudaSuccess) {
-        cudaFree(h->partials); cudaFree(h->counts); cudaFree(h->bases); cudaFree(h->step_dev); cudaFree(h->ticket);
+        cudaFree(h->partials); cudaFree(h->counts); cudaFree(h->bases); cudaFree(h->step_dev);
         delete h;
         return cuda_fail(e, "tk_gogoro_create");
     }
@@ -640,7 +635,7 @@ int tk_gogoro_create(const TkGogoroParams* params, TkGogoro** out) {
 int tk_gogoro_destroy(TkGogoro* h) {
     if (!h) return TK_OK;
     cudaSetDevice(h->params.device);
-    cudaFree(h->partials); cudaFree(h->counts); cudaFree(h->bases); cudaFree(h->step_dev); cudaFree(h->ticket);
+    cudaFree(h->partials); cudaFree(h->counts); cudaFree(h->bases); cudaFree(h->step_dev);
     delete h;
     return TK_OK;
 }
@@ -772,6 +767,14 @@ int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream
     }
     TK_CUDA(cudaGetLastError());
     h->last_grid = h->tiles;
+    return TK_OK;
+}
+
+int tk_gogoro_advance_epoch(TkGogoro* h, void* stream) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    advance_epoch_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(h->step_dev);
+    TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
 

@@ -75,8 +75,7 @@ struct KParams {
     float tgt[3], isr[4], b0[3], b1[3];
     float lo[TK_MAX_DOF], hi[TK_MAX_DOF], effort[TK_MAX_DOF];
     float rinv[TK_MAX_DOF];     // 1 / (hi - lo), rounded to fp32 on the host
-    unsigned long long* step_dev;   // device-side count of completed fused post-physics launches (added to `step`)
-    unsigned int* ticket;           // CTAs of the current launch that have finished
+    unsigned long long* step_dev;   // device-side noise epoch (upper 32 bits of the Philox step), see tk_common.cuh
     long long* dbg_ts;          // developer timeline probe (tools/tile_timeline.py); NULL in normal use
 };
 
@@ -335,9 +334,9 @@ __global__ void humanoid_reset_idx_kernel(const __grid_constant__ KParams p, con
 
 template <int D>
 __global__ void humanoid_philox_kernel(int n, unsigned long long seed, unsigned long long step, long long env_off,
-                                       const unsigned long long* __restrict__ step_dev, float* __restrict__ ua,
-                                       float* __restrict__ ub) {
-    step += *step_dev;   // the draws of the NEXT fused launch
+                                       const unsigned long long* __restrict__ epoch,
+                                       float* __restrict__ ua, float* __restrict__ ub) {
+    step = effective_step(step, epoch);
     const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= static_cast<long long>(n) * D) return;
     const long long e = i / D;
@@ -380,7 +379,6 @@ struct TkHumanoid {
     int last_grid;
     int use_pdl;          // programmatic dependent launch (TK_HUMANOID_PDL=0 disables)
     unsigned long long* step_dev;
-    unsigned int* ticket;
     long long* dbg_ts;
 };
 
@@ -412,7 +410,7 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     k.timeout = B.timeout_buf; k.randomize = reinterpret_cast<long long*>(B.randomize_buf);
     k.pot = B.potentials; k.prev_pot = B.prev_potentials; k.up_vec = B.up_vec; k.heading_vec = B.heading_vec;
     k.init_root = B.initial_root_states; k.init_dof_pos = B.initial_dof_pos; k.ep_return = B.episode_return;
-    k.partials = h->partials; k.tile_rank_base = h->tile_base; k.dbg_ts = h->dbg_ts; k.step_dev = h->step_dev; k.ticket = h->ticket;
+    k.partials = h->partials; k.tile_rank_base = h->tile_base; k.dbg_ts = h->dbg_ts; k.step_dev = h->step_dev;
     k.unit_a = nullptr; k.unit_b = nullptr; k.noise_rows = 0; k.seed = 0; k.step = 0; k.env_off = 0;
     k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs;
@@ -454,18 +452,16 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     if (const char* env = getenv("TK_HUMANOID_PDL")) h->use_pdl = atoi(env) != 0;
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->last_grid = 0;
-    h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr; h->step_dev = nullptr; h->ticket = nullptr;
+    h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr; h->step_dev = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->tile_counts, sizeof(int) * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->tile_base, sizeof(int) * h->tiles);
     if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * h->tiles);
     if (e == cudaSuccess) e = cudaMemset(h->tile_base, 0, sizeof(int) * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->step_dev, sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMalloc(&h->ticket, sizeof(unsigned int));
     if (e == cudaSuccess) e = cudaMemset(h->step_dev, 0, sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMemset(h->ticket, 0, sizeof(unsigned int));
     if (e != cudaSuccess) {
-        cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base); cudaFree(h->step_dev); cudaFree(h->ticket);
+        cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base); cudaFree(h->step_dev);
         delete h;
         return cuda_fail(e, "tk_humanoid_create");
     }
@@ -476,7 +472,7 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
 int tk_humanoid_destroy(TkHumanoid* h) {
     if (!h) return TK_OK;
     cudaSetDevice(h->params.device);
-    cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base); cudaFree(h->step_dev); cudaFree(h->ticket);
+    cudaFree(h->partials); cudaFree(h->tile_counts); cudaFree(h->tile_base); cudaFree(h->step_dev);
     delete h;
     return TK_OK;
 }
@@ -613,6 +609,14 @@ int tk_humanoid_philox_noise(TkHumanoid* h, uint64_t seed, uint64_t step, int64_
 int tk_debug_humanoid_timeline(TkHumanoid* h, long long* device_buffer) {
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
     h->dbg_ts = device_buffer;
+    return TK_OK;
+}
+
+int tk_humanoid_advance_epoch(TkHumanoid* h, void* stream) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    advance_epoch_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(h->step_dev);
+    TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
 

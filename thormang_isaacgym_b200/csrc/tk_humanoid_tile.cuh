@@ -61,7 +61,7 @@ __device__ __forceinline__ void reset_env_values(const KParams& p, int ne, int r
         const int j = lane;
         float ua = 0.5f, ub = 0.5f;
         if (p.noise_mode == TK_NOISE_PHILOX) {
-            Philox4 r = philox_env(p.seed, p.step + *p.step_dev, p.env_off + ne, static_cast<uint32_t>(j >> 1));
+            Philox4 r = philox_env(p.seed, effective_step(p.step, p.step_dev), p.env_off + ne, static_cast<uint32_t>(j >> 1));
             ua = u01((j & 1) ? r.z : r.x);
             ub = u01((j & 1) ? r.w : r.y);
         } else if (p.noise_mode != TK_NOISE_NONE && row < p.noise_rows) {
@@ -332,7 +332,6 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
             atomicAdd(p.partials + static_cast<size_t>(blockIdx.x) * TK_STATS + lane, static_cast<double>(v));
         }
     }
-    if (FUSED && lane == 0) launch_epilogue(p.ticket, p.step_dev);
     if (bulk && lane == 0) bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
     TK_STAMP(6);
 #undef TK_STAMP

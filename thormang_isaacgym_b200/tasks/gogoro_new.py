@@ -96,8 +96,7 @@ class Gogoro(VecTask):
         self.episode_stats = torch.zeros(nat.TK_STATS, device=dev, dtype=torch.float64)
         self.noise_seed = int(cfg.get("seed", 0)) & 0xFFFFFFFFFFFFFFFF
         self.env_id_offset = int(cfg["env"].get("envIdOffset", 0))
-        self.step_count = 0        # launches issued from this object (information only)
-        self.step_offset = 0       # added to the device-side launch counter that keys the in-kernel Philox streams
+        self.step_count = 0        # keys the in-kernel Philox streams together with the seed and the global env id
         self._handle = None
         self._create_native()
         if cfg["env"].get("resetOnInit", True):
@@ -198,7 +197,7 @@ class Gogoro(VecTask):
         """gogoro_new.py:347-369.  ``steer_unit``: the N(0,1) draw of :362 (in-kernel Philox when omitted)."""
         a = actions.to(self.device, dtype=torch.float).contiguous()
         nat.check(self._lib.tk_gogoro_pre_physics(self._handle, nat.ptr(a), nat.ptr(steer_unit), self.noise_seed,
-                                                  self.step_offset, self.env_id_offset,
+                                                  self.step_count, self.env_id_offset,
                                                   1 if self.zero_fill_targets else 0, self._stream()),
                   "tk_gogoro_pre_physics")
         self.sim.set_dof_position_target_tensor(self.dof_pos_command)
@@ -221,7 +220,7 @@ class Gogoro(VecTask):
         self.sim.refresh_actor_root_state_tensor()
         self.sim.refresh_dof_state_tensor()
         su = None if sensor_unit is None else sensor_unit.contiguous()
-        nat.check(self._lib.tk_gogoro_compute_obs_rwd(self._handle, nat.ptr(su), self.noise_seed, self.step_offset,
+        nat.check(self._lib.tk_gogoro_compute_obs_rwd(self._handle, nat.ptr(su), self.noise_seed, self.step_count,
                                                       self.env_id_offset, self._stream()), "tk_gogoro_compute_obs_rwd")
         self.curent_step += 1
 
@@ -248,7 +247,7 @@ class Gogoro(VecTask):
         if not supplied and noise_mode is None and speed_unit is None and yaw_unit is None:
             # production path: in-kernel Philox, nothing allocated per step
             nz = self._philox_noise
-            nz.reset.seed, nz.reset.step, nz.reset.env_id_offset = self.noise_seed, self.step_offset, self.env_id_offset
+            nz.reset.seed, nz.reset.step, nz.reset.env_id_offset = self.noise_seed, self.step_count, self.env_id_offset
             rc = self._post_physics(self._handle, self._philox_noise_ref,
                                     torch.cuda.current_stream(self._torch_device).cuda_stream)
             if rc:
@@ -275,7 +274,7 @@ class Gogoro(VecTask):
                 nz.reset.rows = reset_unit.shape[0]
             keep.append(reset_unit)
             nz.reset.unit_a = nat.ptr(reset_unit)
-        nz.reset.seed, nz.reset.step, nz.reset.env_id_offset = self.noise_seed, self.step_offset, self.env_id_offset
+        nz.reset.seed, nz.reset.step, nz.reset.env_id_offset = self.noise_seed, self.step_count, self.env_id_offset
         nat.check(self._lib.tk_gogoro_post_physics(self._handle, C.byref(nz), self._stream()), "tk_gogoro_post_physics")
         self.step_count += 1
         self.curent_step += 1
@@ -287,10 +286,15 @@ class Gogoro(VecTask):
                    reset_unit=torch.empty((n, RESET_NOISE_COLS), device=dev), speed_unit=torch.empty(n, device=dev),
                    yaw_unit=torch.empty(n, device=dev))
         nat.check(self._lib.tk_gogoro_philox_noise(
-            self._handle, self.noise_seed, self.step_offset if step is None else step, self.env_id_offset,
+            self._handle, self.noise_seed, self.step_count if step is None else step, self.env_id_offset,
             nat.ptr(out["steer_unit"]), nat.ptr(out["sensor_unit"]), nat.ptr(out["reset_unit"]),
             nat.ptr(out["speed_unit"]), nat.ptr(out["yaw_unit"]), self._stream()), "tk_gogoro_philox_noise")
         return out
+
+    def advance_noise_epoch(self):
+        """Capture ONE call of this inside a CUDA graph of steps: ``step_count`` is frozen in the captured launches, the
+        device-side epoch bumped here makes every replay draw fresh in-kernel noise."""
+        nat.check(self._lib.tk_gogoro_advance_epoch(self._handle, self._stream()), "tk_gogoro_advance_epoch")
 
     def episode_statistics(self, accumulate: bool = False) -> torch.Tensor:
         """fp64[8]: sum reward, #reset, #timeout, sum return/length of finished episodes, sum |tilt|, sum |yaw err|, N."""

@@ -102,8 +102,7 @@ class Humanoid(VecTask):
         # in-kernel reset noise
         self.noise_seed = int(cfg.get("seed", 0)) & 0xFFFFFFFFFFFFFFFF
         self.env_id_offset = int(env.get("envIdOffset", 0))   # global id of local env 0 (multi-GPU range sharding)
-        self.step_count = 0        # launches issued from this object (information only)
-        self.step_offset = 0       # added to the device-side launch counter that keys the in-kernel Philox streams
+        self.step_count = 0        # keys the in-kernel Philox streams together with the seed and the global env id
         self._handle = None
         self._create_native()
 
@@ -246,7 +245,7 @@ class Humanoid(VecTask):
         else:
             noise.mode = nat.NOISE_PHILOX if noise_mode is None else noise_mode
             noise.unit_a, noise.unit_b, noise.rows = None, None, 0
-        noise.seed, noise.step, noise.env_id_offset = self.noise_seed, self.step_offset, self.env_id_offset
+        noise.seed, noise.step, noise.env_id_offset = self.noise_seed, self.step_count, self.env_id_offset
         rc = self._post_physics(self._handle, self._noise_ref, torch.cuda.current_stream(self._torch_device).cuda_stream)
         if rc:
             nat.check(rc, "tk_humanoid_post_physics")
@@ -272,9 +271,14 @@ class Humanoid(VecTask):
         ua = torch.empty((self.num_envs, self.num_dof), device=self.device)
         ub = torch.empty_like(ua)
         nat.check(self._lib.tk_humanoid_philox_noise(self._handle, self.noise_seed,
-                                                     self.step_offset if step is None else step, self.env_id_offset,
+                                                     self.step_count if step is None else step, self.env_id_offset,
                                                      nat.ptr(ua), nat.ptr(ub), self._stream()), "tk_humanoid_philox_noise")
         return ua, ub
+
+    def advance_noise_epoch(self):
+        """Capture ONE call of this inside a CUDA graph of steps: ``step_count`` is frozen in the captured launches, the
+        device-side epoch bumped here makes every replay draw fresh in-kernel noise."""
+        nat.check(self._lib.tk_humanoid_advance_epoch(self._handle, self._stream()), "tk_humanoid_advance_epoch")
 
     def episode_statistics(self, accumulate: bool = False) -> torch.Tensor:
         """fp64[8] on device: sum reward, #reset, #timeout, sum return/length of finished episodes, sum up_proj,
