@@ -42,7 +42,7 @@ def parse_args():
     ap.add_argument("--task", default="humanoid", choices=["humanoid", "gogoro"])
     ap.add_argument("--envs-per-gpu", type=int, default=131072)
     ap.add_argument("--e2e-steps", type=int, default=20)
-    ap.add_argument("--e2e-chunks", type=int, default=8)
+    ap.add_argument("--e2e-chunks", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the extra (non-headline) configurations")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)

@@ -128,11 +128,11 @@ def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, b
 def _e2e_bench(torch, n, device, steps, chunks, env_off, barrier=None):
     """Public-API path with HOST buffers: per step H2D(state) -> fused kernel -> D2H(obs, rew, reset), chunk-pipelined."""
     from thormang_isaacgym_b200 import synthetic as syn
-    from thormang_isaacgym_b200.host_io import ChunkedHostBridge
+    from thormang_isaacgym_b200.host_io import ChunkedHostBridge, make_humanoid_for_host
     while n % chunks:
         chunks //= 2
     chunks = max(1, chunks)
-    bridge = ChunkedHostBridge(lambda m, off: _make_humanoid(m, 4321, device, env_off + off, stats=False)[0], n, chunks)
+    bridge = ChunkedHostBridge(lambda m, off: make_humanoid_for_host(m, device, env_off + off, seed=1234), n, chunks)
     st = syn.humanoid_state(n, seed=4321, asset=syn.humanoid_asset(), fallen_frac=0.01)
     bridge.fill_host(st)
     for _ in range(3):
@@ -262,8 +262,8 @@ def run_gpu_arm(args, rank, world):
         e2e = {"value": n * world * args.e2e_steps / float(sec.item()), "unit": "env-steps/s",
                "h2d_bytes_per_step": r["h2d"] * world, "d2h_bytes_per_step": r["d2h"] * world,
                "steps": args.e2e_steps, "chunks_per_gpu": r["chunks"],
-               "path": "HostBridge: pinned host state -> H2D -> Humanoid.post_physics_step() -> D2H obs/rew/reset, "
-                       "range-sharded into chunks on separate streams so PCIe copies overlap the kernels"}
+               "path": "HostBridge: pinned host state slab -> one H2D -> Humanoid.post_physics_step() -> one D2H of the "
+                       "obs|rew|reset slab, range-sharded into chunks on separate streams so PCIe copies overlap the kernels"}
 
     stats_last = reducer.result()
     sampler.stop()

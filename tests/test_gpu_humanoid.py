@@ -307,3 +307,33 @@ def test_cuda_graph_replay_matches_eager():
     for name in ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "dof_state", "root_states", "potentials", "forces"):
         U.exact(getattr(env_b, name), getattr(env_a, name), f"graph vs eager: {name}")
     assert int(env_a.progress_buf.max()) >= 5
+
+
+def test_host_bridge_slabs_match_plain_task():
+    """host_io: slab-backed task (one H2D, one D2H per step) == plain task on the same host state."""
+    from thormang_isaacgym_b200 import config as tcfg
+    from thormang_isaacgym_b200.host_io import ChunkedHostBridge, HostBridge, make_humanoid_for_host
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.humanoid import Humanoid
+    n = 2048
+    asset = syn.humanoid_asset()
+    st = syn.humanoid_state(n, seed=5, asset=asset)
+    cfg = tcfg.humanoid_cfg(n, seed=0)
+    cfg["env"]["episodeStatistics"] = False
+    cfg["sim_backend"] = FakeSim(n, 21, DEV, num_sensor_floats=12, asset=asset)
+    plain = Humanoid(cfg, DEV, DEV, -1, True)
+    chunked = ChunkedHostBridge(lambda m, off: make_humanoid_for_host(m, DEV, off, seed=0), n, 4)
+    assert chunked.bridges[0].in_slab is not None and chunked.bridges[0].out_slab is not None
+    whole = HostBridge(plain)
+    for b in (chunked, whole):
+        b.fill_host(st) if isinstance(b, HostBridge) else b.fill_host(st)
+    for _ in range(3):      # step 0 resets every env (reset_buf starts at ones), later steps reset the fallen ones
+        chunked.step(); whole.step()
+    chunked.synchronize(); whole.synchronize()
+    per = n // 4
+    for c, b in enumerate(chunked.bridges):
+        sl = slice(c * per, (c + 1) * per)
+        for k in ("obs_buf", "rew_buf", "reset_buf"):
+            U.exact(b.host_out[k], whole.host_out[k][sl], f"chunk {c} {k}")
+            U.exact(b.host_out[k], getattr(b.env, k).cpu(), f"chunk {c} {k} read-back")
+    assert chunked.h2d_bytes >= 436 * n and chunked.d2h_bytes >= 452 * n

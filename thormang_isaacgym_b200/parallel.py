@@ -46,6 +46,7 @@ class EpisodeStatsReducer:
         self.buffer = torch.zeros(len(STAT_NAMES), dtype=torch.float64, device=self.device)
         self._stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
         self._work = None
+        self._copied = None
 
     @staticmethod
     def _dist():
@@ -56,15 +57,17 @@ class EpisodeStatsReducer:
         """Start reducing ``local_stats`` (fp64[8] on ``device``); returns immediately."""
         dist = self._dist()
         if self._stream is not None:
-            snap = local_stats.clone()          # on the caller's stream: the caller may overwrite local_stats at once
+            # the caller's stream must not overwrite local_stats before the side stream has copied it: the copy of the
+            # PREVIOUS launch is awaited here (one horizon later: never a real wait), this launch's copy is marked below
+            if self._copied is not None:
+                torch.cuda.current_stream(self.device).wait_event(self._copied)
             ready = torch.cuda.Event()
             ready.record()
             with torch.cuda.stream(self._stream):
                 self._stream.wait_event(ready)
-                self.buffer.copy_(snap)
-                snap.record_stream(self._stream)
-                if dist is not None:
-                    self._work = dist.all_reduce(self.buffer, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                self.buffer.copy_(local_stats)
+                self._copied = torch.cuda.Event()
+                self._copied.record()
         else:
             self.buffer.copy_(local_stats)
             if dist is not None:

@@ -25,14 +25,34 @@ import torch
 class FakeSim:
     def __init__(self, num_envs: int, num_dof: int, device, num_sensor_floats: int = 12,
                  dof_names: Optional[List[str]] = None, asset: Optional[Dict[str, torch.Tensor]] = None,
-                 physics: Optional[Callable[["FakeSim"], None]] = None):
+                 physics: Optional[Callable[["FakeSim"], None]] = None, slab: bool = False):
         self.num_envs, self.num_dof, self.device = num_envs, num_dof, torch.device(device)
         f = dict(dtype=torch.float32, device=self.device)
-        self.root_states = torch.zeros((num_envs, 13), **f)
+        self.state_slab = None
+        self.actions_view = None
+        if slab:
+            # one allocation for everything a host-resident simulator uploads per step (host_io.HostBridge):
+            # root | dof_state | dof_force | sensors | actions, each region 256-byte aligned -> a single H2D copy
+            sizes = [num_envs * 13, num_envs * num_dof * 2, num_envs * num_dof, num_envs * num_sensor_floats,
+                     num_envs * num_dof]
+            offs, total = [], 0
+            for sz in sizes:
+                offs.append(total)
+                total += (sz + 63) // 64 * 64
+            self.state_slab = torch.zeros(total, **f)
+            cut = lambda i, shape: self.state_slab[offs[i]:offs[i] + sizes[i]].view(shape)
+            self.root_states = cut(0, (num_envs, 13))
+            self.dof_state = cut(1, (num_envs * num_dof, 2))
+            self.dof_force = cut(2, (num_envs, num_dof))
+            self.force_sensor = cut(3, (num_envs, num_sensor_floats))
+            self.actions_view = cut(4, (num_envs, num_dof))
+            self.slab_layout = dict(zip(("root_states", "dof_state", "dof_force", "sensors", "actions"), zip(offs, sizes)))
+        else:
+            self.root_states = torch.zeros((num_envs, 13), **f)
+            self.dof_state = torch.zeros((num_envs * num_dof, 2), **f)
+            self.dof_force = torch.zeros((num_envs, num_dof), **f)
+            self.force_sensor = torch.zeros((num_envs, num_sensor_floats), **f)
         self.root_states[:, 6] = 1.0                     # identity quaternion (xyzw)
-        self.dof_state = torch.zeros((num_envs * num_dof, 2), **f)
-        self.dof_force = torch.zeros((num_envs, num_dof), **f)
-        self.force_sensor = torch.zeros((num_envs, num_sensor_floats), **f)
         self.dof_names = dof_names or [f"dof_{i}" for i in range(num_dof)]
         self.asset = {k: v.to(self.device) for k, v in (asset or {}).items()}
         self.physics = physics

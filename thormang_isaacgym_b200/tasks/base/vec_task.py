@@ -107,10 +107,24 @@ class VecTask(Env):
     def allocate_buffers(self):
         """vec_task.py:254-277: same names, shapes, dtypes and initial values."""
         dev = self.device
-        self.obs_buf = torch.zeros((self.num_envs, self.num_obs), device=dev, dtype=torch.float)
+        n = self.num_envs
+        self.output_slab = None
+        if self.cfg["env"].get("outputSlab", False):
+            # host-driven pipelines (host_io.HostBridge): obs | rew | reset carved out of ONE allocation so that a step's
+            # results leave the device as a single copy.  Same shapes, dtypes and initial values as below.
+            def up(x): return (x + 255) // 256 * 256
+            o_obs, o_rew = 0, up(n * self.num_obs * 4)
+            o_reset = o_rew + up(n * 4)
+            self.output_slab = torch.zeros(o_reset + n * 8, device=dev, dtype=torch.uint8)
+            self.obs_buf = self.output_slab[o_obs:o_obs + n * self.num_obs * 4].view(torch.float).view(n, self.num_obs)
+            self.rew_buf = self.output_slab[o_rew:o_rew + n * 4].view(torch.float)
+            self.reset_buf = self.output_slab[o_reset:o_reset + n * 8].view(torch.long)
+            self.reset_buf.fill_(1)
+        else:
+            self.obs_buf = torch.zeros((n, self.num_obs), device=dev, dtype=torch.float)
+            self.rew_buf = torch.zeros(n, device=dev, dtype=torch.float)
+            self.reset_buf = torch.ones(n, device=dev, dtype=torch.long)
         self.states_buf = torch.zeros((self.num_envs, self.num_states), device=dev, dtype=torch.float)
-        self.rew_buf = torch.zeros(self.num_envs, device=dev, dtype=torch.float)
-        self.reset_buf = torch.ones(self.num_envs, device=dev, dtype=torch.long)
         # the reference allocates int64 and rebinds to a bool tensor in step() (vec_task.py:345); the kernels
         # write the bool directly
         self.timeout_buf = torch.zeros(self.num_envs, device=dev, dtype=torch.bool)

@@ -92,7 +92,8 @@ class Humanoid(VecTask):
         self.dt = cfg["sim"]["dt"]
         self.potentials = torch.tensor([-1000. / self.dt], **f).repeat(n)
         self.prev_potentials = self.potentials.clone()
-        self.actions = torch.zeros((n, d), **f)
+        # a slab-backed simulator (host-driven pipelines) provides the storage of self.actions next to its state
+        self.actions = sim.actions_view if getattr(sim, "actions_view", None) is not None else torch.zeros((n, d), **f)
         self.forces = torch.zeros((n, d), **f)
         self.episode_return = torch.zeros(n, **f) if env.get("episodeStatistics", True) else None
         # humanoid.py:289 bumps randomize_buf every step, but only domain randomisation (out of scope, randomize is
