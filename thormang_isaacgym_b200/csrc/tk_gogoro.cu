@@ -22,7 +22,7 @@ constexpr int kObs = 6;
 constexpr int kHist = 5;
 constexpr int kSensorNoise = 5;
 constexpr int kResetNoise = 10;
-constexpr int kTile = 256;     // envs per CTA == threads per CTA
+constexpr int kTile = 32;      // envs per CTA == one warp (tile slices of every array are 16-byte aligned bulk-copy operands)
 constexpr int kWarps = kTile / 32;
 
 struct KParams {
@@ -181,6 +181,7 @@ struct Smem {
     alignas(16) float noise[kTile * kSensorNoise];
     alignas(16) float clean[kTile * kObs];
     alignas(16) float noisy[kTile * kObs];
+    alignas(8) uint64_t bar;
     unsigned ballots[2][kWarps];
     float wsum[kWarps][TK_STATS];
 };
@@ -220,11 +221,25 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const unsigned long long step_now = philox ? effective_step(p.step, p.step_dev) : 0ull;
 
-    tile_load(s.root, p.root + static_cast<size_t>(env0) * kRoot, nt * kRoot, vec, tid);
-    if (MODE != 2) {
-        tile_load(s.hist, p.action_history + static_cast<size_t>(env0) * kHist, nt * kHist, vec, tid);
-        if (!philox && p.sensor_unit)
-            tile_load(s.noise, p.sensor_unit + static_cast<size_t>(env0) * kSensorNoise, nt * kSensorNoise, vec, tid);
+    // full, 16-byte aligned tile: the bulk-copy (TMA) engine moves root / history / noise rows in and both obs rows out
+    const bool use_noise = (MODE != 2) && !philox && p.sensor_unit != nullptr;
+    const bool bulk = vec && nt == kTile;
+    if (bulk) {
+        if (tid == 0) {
+            mbar_init(&s.bar, 1);
+            fence_proxy_async_smem();
+            mbar_expect_tx(&s.bar, (kRoot + (MODE != 2 ? kHist : 0) + (use_noise ? kSensorNoise : 0)) * kTile * 4);
+        }
+        __syncwarp();
+        if (tid == 0) bulk_load(s.root, p.root + static_cast<size_t>(env0) * kRoot, kTile * kRoot * 4, &s.bar);
+        else if (tid == 1 && MODE != 2) bulk_load(s.hist, p.action_history + static_cast<size_t>(env0) * kHist, kTile * kHist * 4, &s.bar);
+        else if (tid == 2 && use_noise) bulk_load(s.noise, p.sensor_unit + static_cast<size_t>(env0) * kSensorNoise, kTile * kSensorNoise * 4, &s.bar);
+    } else {
+        tile_load(s.root, p.root + static_cast<size_t>(env0) * kRoot, nt * kRoot, false, tid);
+        if (MODE != 2) {
+            tile_load(s.hist, p.action_history + static_cast<size_t>(env0) * kHist, nt * kHist, false, tid);
+            if (use_noise) tile_load(s.noise, p.sensor_unit + static_cast<size_t>(env0) * kSensorNoise, nt * kSensorNoise, false, tid);
+        }
     }
 
     long long prog = 0;
@@ -249,6 +264,7 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         if (lane == 0) { s.ballots[0][warp] = b0; s.ballots[1][warp] = b1; }
     }
     __syncthreads();
+    if (bulk) mbar_wait(&s.bar, 0);        // bulk loads landed
 
     float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_tilt = 0.f, st_yaw = 0.f;
     bool out_reset = false, out_timeout = false;
@@ -377,19 +393,24 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
             w[3] = st_ret; w[4] = st_len; w[5] = st_tilt; w[6] = st_yaw; w[7] = static_cast<float>(__popc(m_valid));
         }
     }
+    fence_proxy_async_smem();              // obs rows written via the generic proxy, read by the bulk-copy engine
     __syncthreads();
     if (MODE == 0 && tid < TK_STATS) {
         double acc = 0.0;
 #pragma unroll
         for (int w = 0; w < kWarps; ++w) acc += static_cast<double>(s.wsum[w][tid]);
-        p.partials[static_cast<size_t>(blockIdx.x) * TK_STATS + tid] += acc;   // running sum since the last tk_*_stats
+        // running sum since the last tk_*_stats; the slot belongs to this tile alone (deterministic), RED = no stall
+        atomicAdd(p.partials + static_cast<size_t>(blockIdx.x) * TK_STATS + tid, acc);
     }
-    if (MODE == 2) {
-        tile_store(obs_out + static_cast<size_t>(env0) * kObs, s.clean, nt * kObs,
-                   vec && (reinterpret_cast<uintptr_t>(obs_out) & 15) == 0, tid);
+    float* out_clean = (MODE == 2) ? obs_out + static_cast<size_t>(env0) * kObs : p.buffer_obs + static_cast<size_t>(env0) * kObs;
+    const bool bulk_out = bulk && (MODE != 2 || (reinterpret_cast<uintptr_t>(obs_out) & 15) == 0);
+    if (bulk_out) {
+        if (tid == 0) bulk_store(out_clean, s.clean, kTile * kObs * 4);
+        if (tid == 1 && MODE != 2) bulk_store(p.obs_buf + static_cast<size_t>(env0) * kObs, s.noisy, kTile * kObs * 4);
+        if (tid < 2) { bulk_commit(); bulk_wait_read<0>(); }   // shared memory must stay alive until the engine has read it
     } else {
-        tile_store(p.buffer_obs + static_cast<size_t>(env0) * kObs, s.clean, nt * kObs, vec, tid);
-        tile_store(p.obs_buf + static_cast<size_t>(env0) * kObs, s.noisy, nt * kObs, vec, tid);
+        tile_store(out_clean, s.clean, nt * kObs, false, tid);
+        if (MODE != 2) tile_store(p.obs_buf + static_cast<size_t>(env0) * kObs, s.noisy, nt * kObs, false, tid);
     }
 }
 
