@@ -6,10 +6,10 @@
 //   reset_idx :505-590 (+ randomize :474-482, generate_spawn_r :485-492, euler_to_quaternion :496-502),
 //   compute_gogoro_observations :692-723, shortest_angle_distance :687-689, compute_gogoro_reward :645-684.
 //
-// 192 B / env-step of algorithmic traffic, one env per thread.  The AoS rows that are not a
-// multiple of 16 bytes (root 52 B, action history 20 B, sensor noise 20 B, the two 24 B obs rows)
-// are moved as flat, coalesced 128-bit tile copies through shared memory (row strides 13 / 5 / 6
-// words: odd or conflict-light), everything else is a coalesced 4/8-byte access per thread.
+// 192 B / env-step of algorithmic traffic (172 B with in-kernel Philox noise).  One warp = one CTA = 32 consecutive
+// envs, lane e owns env e.  The AoS rows that are not a multiple of 16 bytes (root 52 B, action history 20 B, supplied
+// sensor noise 20 B, the two 24 B obs rows) move as cp.async.bulk (TMA) tile copies through shared memory (row strides
+// 13 / 5 / 6 words: conflict-free or 2-way), everything else is a coalesced 4/8-byte access per lane.
 #include "tk_common.cuh"
 
 #include <new>
