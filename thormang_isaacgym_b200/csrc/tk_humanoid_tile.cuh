@@ -6,9 +6,12 @@
 // 14 KB of shared memory holds first the staged inputs (32 x 109 floats) and then the image of
 // the 32 obs rows (32 x 110 floats):
 //
-//   lane 0:  mbarrier.expect_tx + 5 x cp.async.bulk global->shared  (dof_state, dof_force, actions, sensors, root)
+//   all:     preamble (parameters, addresses, mbarrier.init) may overlap the previous kernel's drain (PDL), then
+//            griddepcontrol.wait -- nothing of global memory is touched before the previous kernel has completed
+//   lanes 0-4: mbarrier.expect_tx + one cp.async.bulk global->shared each (dof_state, dof_force, actions, root, sensors)
 //   all:     coalesced per-env scalars (progress, reset, potentials, episode return) while the bulk loads fly
-//   all:     wait(mbarrier); (rare) reset prologue patches the staged rows of flagged envs, lane = DOF
+//   (rare)   reset_idx for flagged envs, lane = DOF: computed and written to global memory BEFORE the wait
+//   all:     wait(mbarrier); patch the staged rows of the envs that were reset
 //   lane e:  reads ITS env's 109 input floats into registers (immediate offsets, LDS.64/.128 where aligned)
 //   __syncwarp  -- every input of the tile is now in registers, the buffer may be overwritten in place
 //   lane e:  scaled copies + torso math in registers, writes ITS obs row with 55 conflict-free STS.64
@@ -16,9 +19,11 @@
 //
 // No thread issues a global load/store for the 876 B/env of bulk data and there is no index
 // arithmetic per element: every shared-memory access is [lane base + immediate].  14 KB of shared
-// memory and 162 registers per thread => 12 resident single-warp CTAs per SM (register-limited), each
+// memory and 160 registers per thread => 12 resident single-warp CTAs per SM (register-limited), each
 // at a different point of load / math / store: 168 KB of loads in flight per SM, far more than
 // the ~22 KB Little's law asks for at 6.5 TB/s (the kernel is a pure stream: 924 B/env-step, ~0.3 flop/B).
+// Alternatives that were built and measured slower (three warps per tile, persistent CTAs with a
+// double-buffered TMA prefetch) are recorded in DESIGN.md 3.1.
 #pragma once
 
 namespace tk {
