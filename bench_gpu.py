@@ -266,6 +266,9 @@ def run_gpu_arm(args, rank, world):
                        "obs|rew|reset slab, range-sharded into chunks on separate streams so PCIe copies overlap the kernels"}
 
     stats_last = reducer.result()
+    # self-check of the collective: every rank contributes the same number of env-steps per finalize
+    local_steps = float(n * HORIZON)
+    stats_ok = (args.steps < HORIZON) or abs(stats_last["env_steps"] - world * local_steps) < 0.5
     sampler.stop()
     clocks = sampler.summary(windows)
     if rank != 0:
@@ -290,7 +293,7 @@ def run_gpu_arm(args, rank, world):
         "e2e": e2e,
         "gpu_launches": res["launches"],
         "clocks": clocks,
-        "stats_allreduce": {"per": f"{HORIZON} steps", "payload_bytes": 64, "backend": "nccl" if dist else "none (1 GPU)",
+        "stats_allreduce": {"per": f"{HORIZON} steps", "payload_bytes": 64, "backend": "nccl" if dist else "none (1 GPU)", "sum_over_ranks_ok": bool(stats_ok),
                             "last": stats_last},
     }
 

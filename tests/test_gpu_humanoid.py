@@ -337,3 +337,25 @@ def test_host_bridge_slabs_match_plain_task():
             U.exact(b.host_out[k], whole.host_out[k][sl], f"chunk {c} {k}")
             U.exact(b.host_out[k], getattr(b.env, k).cpu(), f"chunk {c} {k} read-back")
     assert chunked.h2d_bytes >= 436 * n and chunked.d2h_bytes >= 452 * n
+
+
+def test_stats_reducer_cuda_path_single_rank_nccl():
+    """EpisodeStatsReducer on the GPU path (side stream + NCCL all-reduce), world_size 1: result == local statistics."""
+    import torch.distributed as dist
+    from thormang_isaacgym_b200.parallel import EpisodeStatsReducer
+    if not dist.is_initialized():
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29533", rank=0, world_size=1,
+                                device_id=torch.device(DEV))
+    try:
+        n = 1024
+        env, orc, _ = U.make_humanoid_pair(n, seed=8)
+        env.post_physics_step()
+        red = EpisodeStatsReducer(DEV)
+        red.launch(env.episode_statistics())
+        assert red._work is not None, "the all-reduce must be issued when a process group exists"
+        out = red.result()
+        assert out["env_steps"] == n
+        assert abs(out["sum_reward"] - float(env.rew_buf.double().sum())) < 1e-3
+        assert out["num_reset"] == int((env.reset_buf != 0).sum())
+    finally:
+        dist.destroy_process_group()

@@ -68,6 +68,8 @@ class EpisodeStatsReducer:
                 self.buffer.copy_(local_stats)
                 self._copied = torch.cuda.Event()
                 self._copied.record()
+                if dist is not None:
+                    self._work = dist.all_reduce(self.buffer, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         else:
             self.buffer.copy_(local_stats)
             if dist is not None:
