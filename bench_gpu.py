@@ -222,7 +222,8 @@ def run_gpu_arm(args, rank, world):
     task, n = args.task, args.envs_per_gpu
     bpe = B.HUMANOID_BYTES_PER_ENV if task == "humanoid" else B.GOGORO_BYTES_PER_ENV
     sampler = B.ClockSampler(local_rank)
-    sampler.start()
+    if not os.environ.get("TK_BENCH_NO_SAMPLER"):
+        sampler.start()
     windows = []
 
     # ---- episode statistics: finalize per state set on device, one 8 x fp64 NCCL all-reduce per horizon (side stream)
@@ -241,7 +242,7 @@ def run_gpu_arm(args, rank, world):
         return 1
 
     res = _kernel_bench(torch, task, n, device, args.steps, max(args.warmup, 3), seed=1234 + 1000 * rank, env_off=rank * n,
-                        barrier=barrier, horizon_hook=horizon_hook)
+                        barrier=barrier, horizon_hook=None if os.environ.get("TK_BENCH_NO_HOOK") else horizon_hook)
     windows.append(res["window"])
     ms_local = res["ms_total"]
     ms_t = torch.tensor([ms_local], device=device, dtype=torch.float64)

@@ -174,7 +174,7 @@ int tk_humanoid_philox_noise(TkHumanoid* h, uint64_t seed, uint64_t step, int64_
 int tk_humanoid_advance_epoch(TkHumanoid* h, void* stream);
 
 /* Episode statistics.  Every tk_humanoid_post_physics adds its per-CTA partial sums into a handle-owned
- * [grid, TK_STATS] fp64 array (each CTA owns its row: no atomics, deterministic).  This call sums the rows in a
+ * small fp64 array (256 rows of TK_STATS accumulators, RED.ADD.F64 per tile).  This call sums the rows in a
  * fixed order into stats_out[TK_STATS] (device, fp64) -- sum reward, #reset, #timeout, sum episode_return of reset
  * envs, sum episode length of reset envs, sum up_proj, sum heading_proj, env-steps -- and zeroes the partials, so the
  * result covers the steps since the previous call.  accumulate != 0 adds to stats_out instead of overwriting.

@@ -249,6 +249,15 @@ __device__ __forceinline__ unsigned long long effective_step(unsigned long long 
 __global__ void advance_epoch_kernel(unsigned long long* epoch);
 
 // ---------------------------------------------------------------------------------------------
+// Episode-statistics partials: kStatSlots rows of TK_STATS fp64 accumulators per handle.  A tile adds its eight warp
+// sums to row (tile & (kStatSlots-1)) with RED.ADD.F64 (no return value); tk_*_stats sums the rows in a fixed order.
+// 256 rows keep same-address contention negligible (one address hit by every CTA cost 20 % at 32768 CTAs) and keep
+// the finalize kernel at ~2 us (a row per tile made it a 40 us single-CTA walk over 4096 rows).  fp64 adds of
+// warp-level fp32 sums: the order of the REDs within a row is not fixed, results agree to ~1e-13 relative.
+// ---------------------------------------------------------------------------------------------
+constexpr int kStatSlots = 256;
+
+// ---------------------------------------------------------------------------------------------
 // warp helpers
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double v) {

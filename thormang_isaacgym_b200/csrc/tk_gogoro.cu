@@ -399,8 +399,8 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         double acc = 0.0;
 #pragma unroll
         for (int w = 0; w < kWarps; ++w) acc += static_cast<double>(s.wsum[w][tid]);
-        // running sum since the last tk_*_stats; the slot belongs to this tile alone (deterministic), RED = no stall
-        atomicAdd(p.partials + static_cast<size_t>(blockIdx.x) * TK_STATS + tid, acc);
+        // running sum since the last tk_*_stats (slot scheme: tk_common.cuh)
+        atomicAdd(p.partials + static_cast<size_t>(blockIdx.x & (kStatSlots - 1)) * TK_STATS + tid, acc);
     }
     float* out_clean = (MODE == 2) ? obs_out + static_cast<size_t>(env0) * kObs : p.buffer_obs + static_cast<size_t>(env0) * kObs;
     const bool bulk_out = bulk && (MODE != 2 || (reinterpret_cast<uintptr_t>(obs_out) & 15) == 0);
@@ -637,10 +637,10 @@ int tk_gogoro_create(const TkGogoroParams* params, TkGogoro** out) {
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->last_grid = 0;
     h->partials = nullptr; h->counts = nullptr; h->bases = nullptr; h->step_dev = nullptr;
-    cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * h->tiles);
+    cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMalloc(&h->counts, sizeof(int) * 2 * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->bases, sizeof(int) * 2 * h->tiles);
-    if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * h->tiles);
+    if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMemset(h->bases, 0, sizeof(int) * 2 * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->step_dev, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemset(h->step_dev, 0, sizeof(unsigned long long));
@@ -787,7 +787,7 @@ int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream
         cudaLaunchKernelEx(&cfg, gogoro_tile_kernel<0>, k, no_out);
     }
     TK_CUDA(cudaGetLastError());
-    h->last_grid = h->tiles;
+    h->last_grid = kStatSlots;
     return TK_OK;
 }
 

@@ -58,7 +58,7 @@ struct KParams {
     const float* init_root;
     const float* init_dof_pos;
     float* ep_return;
-    double* partials;           // [grid, TK_STATS]
+    double* partials;           // [kStatSlots, TK_STATS]
     const int* tile_rank_base;  // COMPACT noise: resets in envs before this tile
     const float* unit_a;
     const float* unit_b;
@@ -373,7 +373,7 @@ struct TkHumanoid {
     TkHumanoidBuffers buf;
     bool bound;
     int tiles;
-    double* partials;     // [tiles, TK_STATS]
+    double* partials;     // [kStatSlots, TK_STATS]
     int* tile_counts;     // [tiles]
     int* tile_base;       // [tiles]
     int last_grid;
@@ -453,10 +453,10 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->last_grid = 0;
     h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr; h->step_dev = nullptr;
-    cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * h->tiles);
+    cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMalloc(&h->tile_counts, sizeof(int) * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->tile_base, sizeof(int) * h->tiles);
-    if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * h->tiles);
+    if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMemset(h->tile_base, 0, sizeof(int) * h->tiles);
     if (e == cudaSuccess) e = cudaMalloc(&h->step_dev, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemset(h->step_dev, 0, sizeof(unsigned long long));
@@ -567,7 +567,7 @@ int tk_humanoid_post_physics(TkHumanoid* h, const TkResetNoise* noise, void* str
     }
     launch_tile<true>(h, k, st);
     TK_CUDA(cudaGetLastError());
-    h->last_grid = h->tiles;
+    h->last_grid = kStatSlots;
     return TK_OK;
 }
 

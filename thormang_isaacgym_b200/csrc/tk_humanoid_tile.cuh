@@ -332,9 +332,8 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
             v = (lane == 5) ? st_up : v;
             v = (lane == 6) ? st_head : v;
             v = (lane == 7) ? static_cast<float>(__popc(m_valid)) : v;
-            // running sum since the last tk_humanoid_stats.  The slot belongs to this tile alone, so the sum is
-            // deterministic; a reduction (RED, no return value) keeps the warp from waiting on the read-modify-write.
-            atomicAdd(p.partials + static_cast<size_t>(blockIdx.x) * TK_STATS + lane, static_cast<double>(v));
+            // running sum since the last tk_humanoid_stats (slot scheme: tk_common.cuh)
+            atomicAdd(p.partials + static_cast<size_t>(blockIdx.x & (kStatSlots - 1)) * TK_STATS + lane, static_cast<double>(v));
         }
     }
     if (bulk && lane == 0) bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
