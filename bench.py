@@ -41,7 +41,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--task", default="humanoid", choices=["humanoid", "gogoro"])
     ap.add_argument("--envs-per-gpu", type=int, default=131072)
-    ap.add_argument("--e2e-steps", type=int, default=20)
+    ap.add_argument("--e2e-steps", type=int, default=40)
     ap.add_argument("--e2e-chunks", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the extra (non-headline) configurations")
@@ -221,7 +221,8 @@ def run_reference_arm(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": args.gpus,
         "steps": done, "warmup": max(1, min(args.warmup, 5)), "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, rotating_sets=1, note="CPU arm: one state set, host memory"),
+        "config": workload_config(args, rotating_sets=max(3, -(-int(2.2 * L2_BYTES) // (n * (HUMANOID_BYTES_PER_ENV if args.task == "humanoid" else GOGORO_BYTES_PER_ENV)))),
+                                  note="same config as the GPU arm; the CPU arm itself steps one state set held in host memory"),
         "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": threads, "kind": "port",
                          "sample": f"{done} steps x {n} envs of the {args.task} post-physics path (reset+obs+reward), "
                                    "oracle/ torch port TorchScript-compiled like the reference, "

@@ -169,6 +169,19 @@ def _pcie_probe(torch, device, mb=64):
             dst.copy_(src, non_blocking=True)
         torch.cuda.synchronize()
         out[name] = 5 * host.numel() / (time.perf_counter() - t0) / 1e9
+    # both directions at once on two streams: what a perfectly overlapped e2e step could reach per direction
+    host2 = torch.empty_like(host).pin_memory()
+    dev2 = torch.empty_like(dev)
+    s1, s2 = torch.cuda.Stream(device=device), torch.cuda.Stream(device=device)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        with torch.cuda.stream(s1):
+            dev.copy_(host, non_blocking=True)
+        with torch.cuda.stream(s2):
+            host2.copy_(dev2, non_blocking=True)
+    torch.cuda.synchronize()
+    out["duplex_GBps_per_direction"] = 5 * host.numel() / (time.perf_counter() - t0) / 1e9
     return out
 
 

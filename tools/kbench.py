@@ -24,9 +24,31 @@ def main():
     ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--pdl", default="1")
     ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--kernel", default="post", choices=["post", "pre"])
     args = ap.parse_args()
     peak, _ = B.measured_peak_gbs()
     bpe = B.HUMANOID_BYTES_PER_ENV if args.task == "humanoid" else B.GOGORO_BYTES_PER_ENV
+    if args.kernel == "pre":
+        pre_bytes = 252 if args.task == "humanoid" else 48
+        for n in [int(x) for x in args.envs.split(",")]:
+            sets = max(3, int(2.2 * B.L2_BYTES / (n * pre_bytes)) + 1)
+            sets = min(sets, 64)
+            make = G._make_humanoid if args.task == "humanoid" else G._make_gogoro
+            envs = [make(n, 5 + s, "cuda:0")[0] for s in range(sets)]
+            width = 21 if args.task == "humanoid" else 1
+            acts = [torch.rand((n, width), device="cuda:0") * 2.4 - 1.2 for _ in range(sets)]
+
+            def step(i):
+                e = envs[i % sets]
+                e._clip_in_kernel = True
+                e.pre_physics_step(acts[i % sets])
+                return 1
+            ms, _, _ = G._time_steps(torch, step, args.steps, args.warmup)
+            us = 1e3 * ms / args.steps
+            gbs = n * pre_bytes / (us * 1e-6) / 1e9
+            print(json.dumps({"task": args.task, "kernel": "pre_physics", "envs": n, "us_per_step": round(us, 2),
+                              "GBps": round(gbs, 1), "frac": round(gbs / peak, 4), "sets": sets}), flush=True)
+        return
     for n in [int(x) for x in args.envs.split(",")]:
         for tile in [int(x) for x in args.pdl.split(",")]:
             os.environ["TK_HUMANOID_PDL"] = str(tile)
