@@ -29,6 +29,10 @@ LIFT_TABLE: Dict[str, Iterable[str]] = {
         "compute_humanoid_observations",  # humanoid.py:379-417
         "compute_reward",                 # humanoid.py:425-472
     ),
+    "isaacgymenvs/tasks/ant.py": (
+        "compute_ant_reward",             # ant.py:318-364
+        "compute_ant_observations",       # ant.py:367-408
+    ),
     "isaacgymenvs/tasks/gogoro_new.py": (
         "compute_gogoro_reward",          # gogoro_new.py:645-684
         "shortest_angle_distance",        # gogoro_new.py:687-689
@@ -101,6 +105,10 @@ def lift(rel_file: str) -> ModuleType:
 
 def humanoid() -> ModuleType:
     return lift("isaacgymenvs/tasks/humanoid.py")
+
+
+def ant() -> ModuleType:
+    return lift("isaacgymenvs/tasks/ant.py")
 
 
 def gogoro() -> ModuleType:

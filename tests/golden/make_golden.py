@@ -140,6 +140,54 @@ def gogoro_golden(n_rand=96):
     print("gogoro_jit.npz", n, "rows; resets", int(reset.sum()))
 
 
+def ant_golden(n_rand=96):
+    ref = L.ant()
+    asset = syn.ant_asset()
+    st = syn.ant_state(n_rand, seed=4244, asset=asset)
+    root = st["root_states"]
+    base = root[0].clone()
+    edge = []
+    for z in (0.31, float(np.nextafter(np.float32(0.31), np.float32(0))), float(np.nextafter(np.float32(0.31), np.float32(1)))):
+        r = base.clone(); r[2] = z; edge.append(r)
+    for pitch in (math.pi / 2, -math.pi / 2):
+        r = base.clone(); r[3:7] = _euler_q(0.3, pitch, -1.0); edge.append(r)
+    r = base.clone(); r[0] = 1000.0; r[1] = 0.0; edge.append(r)
+    r = base.clone(); r[3:7] = torch.tensor([0.0, 0.0, 0.0, 1.0]); edge.append(r)
+    r = base.clone(); r[3:7] = _euler_q(0.0, 0.0, -1e-4); edge.append(r)
+    edge = torch.stack(edge)
+    ne = edge.shape[0]
+    n = n_rand + ne
+    ext = syn.ant_state(ne, seed=98, asset=asset)
+    root = torch.cat([root, edge])
+    dof_state = torch.cat([st["dof_state"], ext["dof_state"]])
+    sensors = torch.cat([st["sensors"], ext["sensors"]])
+    actions = torch.cat([st["actions"], ext["actions"]])
+    potentials = torch.cat([st["potentials"], ext["potentials"]])
+    progress = torch.cat([st["progress_buf"], torch.tensor([996, 997, 998, 999, 1000, 0, 1, 500][:ne])])
+    reset = torch.cat([st["reset_buf"], torch.tensor([0, 1, 0, 1, 0, 1, 0, 0][:ne])])
+    d = 8
+    dof_pos = dof_state.view(n, d, 2)[..., 0]
+    dof_vel = dof_state.view(n, d, 2)[..., 1]
+    lo, hi = asset["dof_limits_lower"], asset["dof_limits_upper"]
+    dof_pos[n_rand + 0] = hi                       # scaled position exactly 1 (> 0.99 branch)
+    dof_pos[n_rand + 1] = 0.5 * (hi + lo) + 0.495 * (hi - lo)
+    targets = torch.tensor([1000.0, 0.0, 0.0]).repeat(n, 1)
+    inv = torch.tensor([0.0, 0.0, 0.0, 1.0]).repeat(n, 1)
+    b0 = torch.tensor([1.0, 0.0, 0.0]).repeat(n, 1)
+    b1 = torch.tensor([0.0, 0.0, 1.0]).repeat(n, 1)
+    obs, pot, prev_pot, up_vec, heading_vec = ref.compute_ant_observations(
+        torch.zeros(n, 60), root, targets, potentials, inv, dof_pos, dof_vel, lo, hi, 0.2, sensors, actions, 0.0166,
+        0.1, b0, b1, 2)
+    rew, reset_out = ref.compute_ant_reward(obs, reset, progress, actions, 0.1, 0.5, pot, prev_pot, 0.005, 0.05, 0.1,
+                                            0.31, -2.0, 1000.0)
+    np.savez_compressed(os.path.join(HERE, "ant_jit.npz"), **_np(dict(
+        root_states=root, dof_state=dof_state, sensors=sensors, actions=actions, potentials=potentials,
+        progress_buf=progress, reset_buf=reset, dof_limits_lower=lo, dof_limits_upper=hi,
+        joint_gears=asset["joint_gears"], obs=obs, potentials_out=pot, prev_potentials_out=prev_pot, up_vec=up_vec,
+        heading_vec=heading_vec, rew=rew, reset_out=reset_out, n_rand=n_rand)))
+    print("ant_jit.npz", n, "rows; resets", int(reset_out.sum()))
+
+
 def poselib_golden(n=256):
     path = os.path.join(L.REFERENCE_ROOT, "isaacgymenvs/tasks/amp/poselib/poselib/core/rotation3d.py")
     spec = importlib.util.spec_from_file_location("_ref_rotation3d", path)
@@ -161,4 +209,5 @@ if __name__ == "__main__":
         sys.exit("reference tree not found: golden vectors can only be regenerated in the build container")
     humanoid_golden()
     gogoro_golden()
+    ant_golden()
     poselib_golden()

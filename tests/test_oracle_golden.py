@@ -126,3 +126,28 @@ def test_helper_properties():
     assert float(na.min()) >= -np.pi - 1e-6 and float(na.max()) <= np.pi + 1e-6
     assert ih.get_axis_params(1., 2) == [0.0, 0.0, 1.0]
     assert ih.get_axis_params(1.34, 2) == [0.0, 0.0, 1.34]
+
+
+def test_ant_golden(golden_dir):
+    from oracle import ant_oracle as ao
+    g = _load(golden_dir, "ant_jit.npz")
+    n, d = g["root_states"].shape[0], 8
+    dof_pos = g["dof_state"].view(n, d, 2)[..., 0]
+    dof_vel = g["dof_state"].view(n, d, 2)[..., 1]
+    targets = torch.tensor([1000.0, 0.0, 0.0]).repeat(n, 1)
+    inv = torch.tensor([0.0, 0.0, 0.0, 1.0]).repeat(n, 1)
+    b0 = torch.tensor([1.0, 0.0, 0.0]).repeat(n, 1)
+    b1 = torch.tensor([0.0, 0.0, 1.0]).repeat(n, 1)
+    obs, pot, prev, up, head = ao.ant_observations(g["root_states"], targets, g["potentials"], inv, dof_pos, dof_vel,
+                                                   g["dof_limits_lower"], g["dof_limits_upper"], 0.2, g["sensors"],
+                                                   g["actions"], 0.0166, 0.1, b0, b1, 2)
+    ang = [7, 8, 9]
+    rest = [c for c in range(60) if c not in ang]
+    torch.testing.assert_close(obs[:, rest], g["obs"][:, rest], rtol=RTOL, atol=ATOL)
+    assert _wrap_close(obs[:, ang], g["obs"][:, ang], 4e-6)
+    torch.testing.assert_close(pot, g["potentials_out"], rtol=RTOL, atol=0)
+    rew, reset = ao.ant_reward(g["obs"], g["reset_buf"], g["progress_buf"], g["actions"], 0.1, 0.5, g["potentials_out"],
+                               g["prev_potentials_out"], 0.005, 0.05, 0.1, 0.31, -2.0, 1000.0)
+    assert torch.equal(reset, g["reset_out"])
+    torch.testing.assert_close(rew, g["rew"], rtol=RTOL, atol=ATOL)
+    assert float((g["obs"][:, 12:20] > 0.99).sum()) > 0, "fixture must exercise the joints-at-limit term"

@@ -56,3 +56,30 @@ def test_gogoro_bit_exact(n):
                                    action_history=st["action_history"], max_episode_length=torch.tensor(1000))
     rg = go.gogoro_reward(got.view(n, 1, 6), st["progress_buf"], st["action_history"], 1000)
     assert torch.equal(rw[0], rg[0]) and torch.equal(rw[1], rg[1])
+
+
+@pytest.mark.parametrize("n", [1, 33, 4096])
+def test_ant_bit_exact(n):
+    from oracle import ant_oracle as ao
+    ref = L.ant()
+    asset = syn.ant_asset()
+    st = syn.ant_state(n, seed=500 + n, asset=asset)
+    d = 8
+    dof_pos = st["dof_state"].view(n, d, 2)[..., 0]
+    dof_vel = st["dof_state"].view(n, d, 2)[..., 1]
+    targets = torch.tensor([1000.0, 0.0, 0.0]).repeat(n, 1)
+    inv = torch.tensor([0.0, 0.0, 0.0, 1.0]).repeat(n, 1)
+    b0 = torch.tensor([1.0, 0.0, 0.0]).repeat(n, 1)
+    b1 = torch.tensor([0.0, 0.0, 1.0]).repeat(n, 1)
+    lo, hi = asset["dof_limits_lower"], asset["dof_limits_upper"]
+    want = ref.compute_ant_observations(torch.zeros(n, 60), st["root_states"], targets, st["potentials"], inv, dof_pos,
+                                        dof_vel, lo, hi, 0.2, st["sensors"], st["actions"], 0.0166, 0.1, b0, b1, 2)
+    got = ao.ant_observations(st["root_states"], targets, st["potentials"], inv, dof_pos, dof_vel, lo, hi, 0.2,
+                              st["sensors"], st["actions"], 0.0166, 0.1, b0, b1, 2)
+    for w, g_ in zip(want, got):
+        assert torch.equal(w, g_)
+    rw = ref.compute_ant_reward(want[0], st["reset_buf"], st["progress_buf"], st["actions"], 0.1, 0.5, want[1], want[2],
+                                0.005, 0.05, 0.1, 0.31, -2.0, 1000.0)
+    rg = ao.ant_reward(got[0], st["reset_buf"], st["progress_buf"], st["actions"], 0.1, 0.5, got[1], got[2], 0.005, 0.05,
+                       0.1, 0.31, -2.0, 1000.0)
+    assert torch.equal(rw[0], rg[0]) and torch.equal(rw[1], rg[1])

@@ -83,6 +83,31 @@ def humanoid_state(n: int, seed: int = 1234, asset: Dict[str, torch.Tensor] = No
     return {k: v.to(device) for k, v in out.items()}
 
 
+def ant_asset(seed: int = 9) -> Dict[str, torch.Tensor]:
+    """Per-task constants of the Ant asset (ant.py:160-162,199-209): 8 DOFs, joint gears as motor efforts."""
+    a = humanoid_asset(seed=seed, num_dof=8)
+    a["joint_gears"] = a.pop("motor_efforts")
+    return a
+
+
+def ant_state(n: int, seed: int = 1234, asset: Dict[str, torch.Tensor] = None, dt: float = 0.0166, device="cpu",
+              fallen_frac: float = None) -> Dict[str, torch.Tensor]:
+    """One post-physics snapshot for ``n`` ants: the Humanoid distributions at D = 8, 24 sensor floats, torso
+    heights around the 0.31 termination height."""
+    asset = asset if asset is not None else ant_asset()
+    h = humanoid_state(n, seed=seed, asset={"dof_limits_lower": asset["dof_limits_lower"],
+                                            "dof_limits_upper": asset["dof_limits_upper"]}, dt=dt)
+    g = _gen(seed + 5)
+    h["root_states"][:, 2] = _u(g, (n,), 0.1, 0.9)
+    if fallen_frac is not None:
+        low = torch.rand((n,), generator=g) < fallen_frac
+        h["root_states"][:, 2] = torch.where(low, _u(g, (n,), 0.1, 0.3), _u(g, (n,), 0.35, 0.9))
+    h["sensors"] = _n(g, (n, 24), 10.0)
+    h["prev_potentials"] = h["potentials"] + _n(g, (n,), 5.0)
+    h.pop("dof_force")
+    return {k: v.to(device) for k, v in h.items()}
+
+
 def humanoid_reset_noise(n: int, seed: int, num_dof: int = HUMANOID_DOF, device="cpu"):
     """U(0,1) draws for up to ``n`` resets: the [K, D] x 2 that humanoid.py:258-259 consume."""
     g = _gen(seed + 77)
