@@ -37,6 +37,13 @@ extern "C" {
 #define TK_MAX_DOF 64
 #define TK_STATS 8
 
+/* The Humanoid entry points also serve Ant (isaacgymenvs/tasks/ant.py), the same path with 8 DOFs, 60 observations
+ * (no dof_force block, 24 sensor floats, raw Euler angles, no potential columns; ant.py:367-408) and every reward term
+ * live (ant.py:318-364).  TkHumanoidParams.variant selects the kernel instantiation; motor_efforts carries joint_gears
+ * (ant.py:273-277), sensors is [N,24], dof_force may be NULL, obs_buf is [N,60]. */
+#define TK_VARIANT_HUMANOID 0
+#define TK_VARIANT_ANT 1
+
 typedef enum TkStatus {
     TK_OK = 0,
     TK_ERR_INVALID = -1,   /* bad argument / params */
@@ -66,8 +73,8 @@ int tk_device_info(int device, int* sm_count, int* cc_major, int* cc_minor);
 typedef struct TkHumanoidParams {
     int32_t device;
     int32_t num_envs;
-    int32_t num_dof;                 /* 21 (humanoid.py:68) */
-    int32_t reserved0;
+    int32_t num_dof;                 /* 21 (humanoid.py:68) | 8 (ant.py:68) */
+    int32_t variant;                 /* TK_VARIANT_HUMANOID (0) | TK_VARIANT_ANT */
     float dt;                        /* cfg["sim"]["dt"], humanoid.py:115 */
     float dof_vel_scale;             /* humanoid.py:48 */
     float angular_velocity_scale;    /* humanoid.py:49 */

@@ -136,6 +136,7 @@ class AntOracle:
         self.reset_buf = torch.ones(n, dtype=torch.long)
         self.progress_buf = torch.zeros(n, dtype=torch.long)
         self.timeout_buf = torch.zeros(n, dtype=torch.long)
+        self.randomize_buf = torch.zeros(n, dtype=torch.long)
         self.actions = torch.zeros((n, d), dtype=torch.float)
         self.forces = torch.zeros((n, d), dtype=torch.float)
 
@@ -176,6 +177,7 @@ class AntOracle:
 
     def post_physics_step(self, unit_pos: Optional[Tensor] = None, unit_vel: Optional[Tensor] = None):   # ant.py:279-287
         self.progress_buf += 1
+        self.randomize_buf += 1                                                # ant.py:281
         env_ids = self.reset_buf.nonzero(as_tuple=False).flatten()
         if len(env_ids) > 0:
             self.reset_idx(env_ids, unit_pos[:len(env_ids)], unit_vel[:len(env_ids)])

@@ -115,3 +115,43 @@ def make_gogoro_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
     # the oracle's views must alias its own dof tensor after the attribute swaps above
     orc.thormang_pose = state["thormang_pose"].clone()
     return env, orc, state
+
+
+ANT_ANGLE_COLS = [7, 8, 9]
+
+
+def ant_obs_close(got, want, what="obs"):
+    rest = [c for c in range(got.shape[1]) if c not in ANT_ANGLE_COLS]
+    close(got[:, rest], want[:, rest], what=what)
+    angle_close(got[:, ANT_ANGLE_COLS], want[:, ANT_ANGLE_COLS], what=what + "[angles]")
+
+
+def make_ant_pair(n, seed=1234, device="cuda:0", state=None, asset=None, **env_over):
+    """(cuda Ant task, cpu AntOracle, state) from one synthetic snapshot."""
+    from oracle import ant_oracle as ao
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.ant import Ant
+    asset = asset or syn.ant_asset()
+    state = state or syn.ant_state(n, seed=seed, asset=asset)
+    cfg = tcfg.ant_cfg(n, seed=seed)
+    cfg["env"]["trackRandomizeBuf"] = True
+    cfg["env"].update(env_over)
+    sim = FakeSim(n, 8, device, num_sensor_floats=24, asset=asset)
+    sim.load_state(state)
+    cfg["sim_backend"] = sim
+    env = Ant(cfg, device, device, -1, True)
+    env.actions.copy_(state["actions"].to(device))
+    env.progress_buf.copy_(state["progress_buf"].to(device))
+    env.reset_buf.copy_(state["reset_buf"].to(device))
+    env.potentials.copy_(state["potentials"].to(device))
+    env.prev_potentials.copy_(state["prev_potentials"].to(device))
+    consts = ao.AntConsts.from_cfg(cfg)
+    orc = ao.AntOracle(consts, state["root_states"].clone(), state["dof_state"].clone(), state["sensors"].clone(),
+                       asset["dof_limits_lower"], asset["dof_limits_upper"], asset["joint_gears"])
+    orc.actions = state["actions"].clone()
+    orc.progress_buf = state["progress_buf"].clone()
+    orc.reset_buf = state["reset_buf"].clone()
+    orc.potentials = state["potentials"].clone()
+    orc.prev_potentials = state["prev_potentials"].clone()
+    orc.randomize_buf = torch.zeros(n, dtype=torch.long)
+    return env, orc, state

@@ -12,13 +12,14 @@ LIB_PATH = os.environ.get("THORMANG_B200_LIB") or os.path.join(_PKG, "libthorman
 TK_MAX_DOF = 64
 TK_STATS = 8
 NOISE_NONE, NOISE_COMPACT, NOISE_DENSE, NOISE_PHILOX = 0, 1, 2, 3
+VARIANT_HUMANOID, VARIANT_ANT = 0, 1
 
 _f, _d, _i32, _i64, _u64, _p = C.c_float, C.c_double, C.c_int32, C.c_int64, C.c_uint64, C.c_void_p
 
 
 class HumanoidParams(C.Structure):
     _fields_ = [
-        ("device", _i32), ("num_envs", _i32), ("num_dof", _i32), ("reserved0", _i32),
+        ("device", _i32), ("num_envs", _i32), ("num_dof", _i32), ("variant", _i32),
         ("dt", _f), ("dof_vel_scale", _f), ("angular_velocity_scale", _f), ("contact_force_scale", _f),
         ("power_scale", _f), ("heading_weight", _f), ("up_weight", _f), ("actions_cost_scale", _f),
         ("energy_cost_scale", _f), ("joints_at_limit_cost_scale", _f), ("death_cost", _f),

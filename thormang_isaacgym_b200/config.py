@@ -26,6 +26,25 @@ def humanoid_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
     })
 
 
+def ant_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
+    """cfg/task/Ant.yaml:7-29,42-47."""
+    return copy.deepcopy({
+        "name": "Ant",
+        "physics_engine": "physx",
+        "seed": seed,
+        "env": {
+            "numEnvs": num_envs, "envSpacing": 5, "episodeLength": 1000, "enableDebugVis": False,
+            "clipActions": 1.0, "powerScale": 1.0, "controlFrequencyInv": 1,
+            "headingWeight": 0.5, "upWeight": 0.1,
+            "actionsCost": 0.005, "energyCost": 0.05, "dofVelocityScale": 0.2, "contactForceScale": 0.1,
+            "jointsAtLimitCost": 0.1, "deathCost": -2.0, "terminationHeight": 0.31,
+            "plane": {"staticFriction": 1.0, "dynamicFriction": 1.0, "restitution": 0.0},
+        },
+        "sim": {"dt": 0.0166, "substeps": 2, "up_axis": "z", "use_gpu_pipeline": True, "gravity": [0.0, 0.0, -9.81]},
+        "task": {"randomize": False, "randomization_params": {}},
+    })
+
+
 GOGORO_JOINTS_POS = {
     "l_arm_el_y": 0.0, "l_arm_wr_r": 0.0, "head_y": 0.0, "r_arm_grip": 0.0, "l_arm_wr_p": 0.0, "torso_y": 0.0,
     "r_arm_sh_r": -1.57, "l_arm_sh_p1": 0.0, "l_arm_sh_r": 1.57, "l_leg_an_r": 0.0, "l_leg_an_p": 0.0,

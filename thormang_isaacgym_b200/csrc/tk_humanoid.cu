@@ -26,18 +26,30 @@ namespace tk {
 namespace humanoid {
 
 constexpr int kRoot = 13;
-constexpr int kSensor = 12;
+constexpr int kVarHumanoid = TK_VARIANT_HUMANOID, kVarAnt = TK_VARIANT_ANT;
 
-template <int D>
-struct Layout {
+// Column layout of one obs row.  Humanoid (humanoid.py:409-414): 12 torso columns, dof_pos_scaled, dof_vel, dof_force,
+// 12 sensor floats, actions, the two potentials = 110.  Ant (ant.py:399-404): no dof_force block, 24 sensor floats, no
+// potential columns = 60.
+template <int D_, int NSENSOR, bool HAS_FORCE, int VARIANT>
+struct Spec {
+    static constexpr int D = D_;
+    static constexpr int kSensor = NSENSOR;
+    static constexpr bool kHasForce = HAS_FORCE;
+    static constexpr int kVariant = VARIANT;
     static constexpr int kPos = 12;
     static constexpr int kVel = kPos + D;
     static constexpr int kForce = kVel + D;
-    static constexpr int kSens = kForce + D;
-    static constexpr int kAct = kSens + kSensor;
+    static constexpr int kSens = kForce + (HAS_FORCE ? D : 0);
+    static constexpr int kAct = kSens + NSENSOR;
     static constexpr int kPot = kAct + D;
-    static constexpr int kObs = kPot + 2;   // 110 for D = 21 (humanoid.py:67)
+    static constexpr int kObs = kPot + (VARIANT == kVarHumanoid ? 2 : 0);
 };
+using HumanoidSpec = Spec<21, 12, true, kVarHumanoid>;   // 110 observations (humanoid.py:67)
+using AntSpec = Spec<8, 24, false, kVarAnt>;             // 60 observations (ant.py:67)
+static_assert(HumanoidSpec::kObs == 110 && AntSpec::kObs == 60, "obs widths of the reference");
+template <int D>
+using Layout = Spec<D, 12, true, kVarHumanoid>;
 
 struct KParams {
     float* root;
@@ -88,6 +100,7 @@ struct Head {
     V3 up, heading;   // up_vec, heading_vec
 };
 
+template <int VARIANT>
 __device__ __forceinline__ Head torso_math(const float* r, const KParams& p) {
     Head h;
     V3 pos{r[0], r[1], r[2]};
@@ -116,10 +129,15 @@ __device__ __forceinline__ Head torso_math(const float* r, const KParams& p) {
 
     h.c[0] = pos.z;
     h.c[1] = vel_loc.x; h.c[2] = vel_loc.y; h.c[3] = vel_loc.z;
-    h.c[4] = angvel_loc.x * p.ang_vel_scale; h.c[5] = angvel_loc.y * p.ang_vel_scale; h.c[6] = angvel_loc.z * p.ang_vel_scale;
-    h.c[7] = normalize_angle_fast(yaw);
-    h.c[8] = normalize_angle_fast(roll);
-    h.c[9] = normalize_angle_fast(att);
+    if (VARIANT == kVarAnt) {   // ant.py:399: raw angular velocity and raw Euler angles in [0, 2*pi]
+        h.c[4] = angvel_loc.x; h.c[5] = angvel_loc.y; h.c[6] = angvel_loc.z;
+        h.c[7] = yaw; h.c[8] = roll; h.c[9] = att;
+    } else {                    // humanoid.py:403-405,410
+        h.c[4] = angvel_loc.x * p.ang_vel_scale; h.c[5] = angvel_loc.y * p.ang_vel_scale; h.c[6] = angvel_loc.z * p.ang_vel_scale;
+        h.c[7] = normalize_angle_fast(yaw);
+        h.c[8] = normalize_angle_fast(roll);
+        h.c[9] = normalize_angle_fast(att);
+    }
     h.c[10] = up_proj;
     h.c[11] = heading_proj;
     return h;
@@ -255,6 +273,35 @@ __global__ void humanoid_reward_kernel(const __grid_constant__ KParams p) {
     p.reset[n] = reset;
 }
 
+// compute_ant_reward (ant.py:318-364) as a method-level entry point: one env per thread, sums in column order
+__global__ void ant_reward_kernel(const __grid_constant__ KParams p) {
+    using L = AntSpec;
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.n) return;
+    const float* o = p.obs + static_cast<size_t>(n) * L::kObs;
+    const float* a = p.actions + static_cast<size_t>(n) * L::D;
+    const float hp = o[11];
+    const float heading_reward = (hp > 0.8f) ? (1.0f * p.heading_weight) : (p.heading_weight * hp / 0.8f);   // :337-338
+    const float up_reward = (o[10] > 0.93f) ? (0.0f + p.up_weight) : 0.0f;                                   // :341-342
+    float actions_cost = 0.0f, electricity_cost = 0.0f;
+    int at_limit = 0;
+#pragma unroll
+    for (int j = 0; j < L::D; ++j) {
+        actions_cost += a[j] * a[j];                                               // :345
+        electricity_cost += fabsf(a[j] * o[L::kVel + j]);                          // :346
+        at_limit += (o[L::kPos + j] > 0.99f) ? 1 : 0;                              // :347
+    }
+    const float progress_reward = p.pot[n] - p.prev_pot[n];                        // :351
+    float total = progress_reward + 0.5f + up_reward + heading_reward - p.actions_cost_scale * actions_cost -
+                  p.energy_cost_scale * electricity_cost - static_cast<float>(at_limit) * p.joints_cost_scale;   // :353-354
+    const bool fallen = o[0] < p.termination_height;
+    if (fallen) total = 1.0f * p.death_cost;                                       // :357
+    long long reset = fallen ? 1 : p.reset[n];                                     // :360
+    if (static_cast<float>(p.progress[n]) >= p.max_episode_length - 1.0f) reset = 1;   // :361
+    p.rew[n] = total;
+    p.reset[n] = reset;
+}
+
 // all terms of :344-363, one warp per env (lane = DOF), sequential-order sums via shuffles
 template <int D>
 __global__ void humanoid_terms_kernel(const __grid_constant__ KParams p, float* __restrict__ terms) {
@@ -371,6 +418,7 @@ using namespace tk::humanoid;
 struct TkHumanoid {
     TkHumanoidParams params;
     TkHumanoidBuffers buf;
+    int variant;          // TK_VARIANT_HUMANOID | TK_VARIANT_ANT: selects the kernel instantiation
     bool bound;
     int tiles;
     double* partials;     // [kStatSlots, TK_STATS]
@@ -382,7 +430,8 @@ struct TkHumanoid {
     long long* dbg_ts;
 };
 
-static constexpr int kD = 21;
+static constexpr int kD = HumanoidSpec::D;
+static constexpr int kDAnt = AntSpec::D;
 
 template <bool FUSED>
 static void launch_tile(const TkHumanoid* h, const KParams& k, cudaStream_t st) {
@@ -398,7 +447,8 @@ static void launch_tile(const TkHumanoid* h, const KParams& k, cudaStream_t st) 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = h->use_pdl ? 1 : 0;
-    cudaLaunchKernelEx(&cfg, humanoid_warp_kernel<kD, FUSED>, k);
+    if (h->variant == kVarAnt) cudaLaunchKernelEx(&cfg, humanoid_warp_kernel<AntSpec, FUSED>, k);
+    else cudaLaunchKernelEx(&cfg, humanoid_warp_kernel<HumanoidSpec, FUSED>, k);
 }
 
 static void fill_kparams(const TkHumanoid* h, KParams& k) {
@@ -415,7 +465,7 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs;
     k.vec_ok = aligned_to(B.root_states, 16) && aligned_to(B.dof_state, 16) && aligned_to(B.dof_force, 16) &&
-               aligned_to(B.sensors, 16) && aligned_to(B.actions, 16) && aligned_to(B.obs_buf, 16);
+               aligned_to(B.sensors, 16) && aligned_to(B.actions, 16) && aligned_to(B.obs_buf, 16);   // NULL dof_force (Ant) passes
     k.dt = P.dt; k.dof_vel_scale = P.dof_vel_scale; k.ang_vel_scale = P.angular_velocity_scale;
     k.contact_scale = P.contact_force_scale; k.power_scale = P.power_scale; k.heading_weight = P.heading_weight;
     k.up_weight = P.up_weight; k.actions_cost_scale = P.actions_cost_scale; k.energy_cost_scale = P.energy_cost_scale;
@@ -440,12 +490,17 @@ extern "C" {
 int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     TK_REQUIRE(params && out, TK_ERR_INVALID, "null argument");
     TK_REQUIRE(params->num_envs > 0, TK_ERR_INVALID, "num_envs must be positive (got %d)", params->num_envs);
-    TK_REQUIRE(params->num_dof == kD, TK_ERR_INVALID, "Humanoid kernels are built for num_dof = %d (got %d)", kD, params->num_dof);
+    TK_REQUIRE(params->variant == kVarHumanoid || params->variant == kVarAnt, TK_ERR_INVALID, "unknown variant %d", params->variant);
+    if (params->variant == kVarAnt)
+        TK_REQUIRE(params->num_dof == kDAnt, TK_ERR_INVALID, "Ant kernels are built for num_dof = %d (got %d)", kDAnt, params->num_dof);
+    else
+        TK_REQUIRE(params->num_dof == kD, TK_ERR_INVALID, "Humanoid kernels are built for num_dof = %d (got %d)", kD, params->num_dof);
     TK_REQUIRE(params->dt > 0.f, TK_ERR_INVALID, "dt must be positive");
     TK_CUDA(cudaSetDevice(params->device));
     TkHumanoid* h = new (std::nothrow) TkHumanoid();
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "out of host memory");
     h->params = *params;
+    h->variant = params->variant;
     h->bound = false;
     h->dbg_ts = nullptr;
     h->use_pdl = 1;
@@ -486,6 +541,7 @@ int tk_humanoid_bind(TkHumanoid* h, const TkHumanoidBuffers* b) {
                            "reset_buf", "progress_buf", "potentials", "prev_potentials", "initial_root_states",
                            "initial_dof_pos"};
     for (unsigned i = 0; i < sizeof(req) / sizeof(req[0]); ++i) {
+        if (i == 2 && h->variant == kVarAnt) continue;   // Ant has no dof_force block (ant.py:399-404)
         TK_REQUIRE(req[i] != nullptr, TK_ERR_UNBOUND, "buffer %s is NULL", names[i]);
         TK_REQUIRE(aligned_to(req[i], 4), TK_ERR_ALIGN, "buffer %s is not 4-byte aligned", names[i]);
     }
@@ -503,14 +559,17 @@ int tk_humanoid_pre_physics(TkHumanoid* h, const float* actions_in, float* force
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
     const int vec = aligned_to(actions_in, 16) && aligned_to(forces_out, 16) && aligned_to(h->buf.actions, 16);
-    const long long total4 = (static_cast<long long>(k.n) * kD + 3) / 4;
+    const int dof = h->params.num_dof;
+    const long long total4 = (static_cast<long long>(k.n) * dof + 3) / 4;
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->params.device);
     long long blocks = (total4 + 255) / 256;
     if (blocks > static_cast<long long>(sms) * 8) blocks = static_cast<long long>(sms) * 8;
     if (blocks < 1) blocks = 1;
-    humanoid_pre_kernel<kD><<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(k, actions_in, forces_out,
-                                                                                                         clip, vec);
+    if (h->variant == kVarAnt)   // ant.py:273-277: forces = actions * joint_gears * power_scale
+        humanoid_pre_kernel<kDAnt><<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(k, actions_in, forces_out, clip, vec);
+    else
+        humanoid_pre_kernel<kD><<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(k, actions_in, forces_out, clip, vec);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
@@ -528,7 +587,8 @@ int tk_humanoid_compute_reward(TkHumanoid* h, void* stream) {
     if (int rc = check_bound(h)) return rc;
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
-    humanoid_reward_kernel<kD><<<(k.n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
+    if (h->variant == kVarAnt) ant_reward_kernel<<<(k.n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
+    else humanoid_reward_kernel<kD><<<(k.n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
@@ -541,8 +601,12 @@ int tk_humanoid_reset_idx(TkHumanoid* h, const int64_t* env_ids, int32_t kcount,
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
     const int wpb = 8;
-    humanoid_reset_idx_kernel<kD><<<(kcount + wpb - 1) / wpb, wpb * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-        k, reinterpret_cast<const long long*>(env_ids), kcount, unit_pos, unit_vel);
+    if (h->variant == kVarAnt)
+        humanoid_reset_idx_kernel<kDAnt><<<(kcount + wpb - 1) / wpb, wpb * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            k, reinterpret_cast<const long long*>(env_ids), kcount, unit_pos, unit_vel);
+    else
+        humanoid_reset_idx_kernel<kD><<<(kcount + wpb - 1) / wpb, wpb * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+            k, reinterpret_cast<const long long*>(env_ids), kcount, unit_pos, unit_vel);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
@@ -574,6 +638,7 @@ int tk_humanoid_post_physics(TkHumanoid* h, const TkResetNoise* noise, void* str
 int tk_humanoid_reward_terms(TkHumanoid* h, float* terms, void* stream) {
     if (int rc = check_bound(h)) return rc;
     TK_REQUIRE(terms != nullptr, TK_ERR_INVALID, "null terms");
+    TK_REQUIRE(h->variant == kVarHumanoid, TK_ERR_INVALID, "reward_terms is a Humanoid entry point (Ant's terms are all live in rew_buf)");
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
     const int wpb = 8;
@@ -585,6 +650,7 @@ int tk_humanoid_reward_terms(TkHumanoid* h, float* terms, void* stream) {
 int tk_humanoid_wm_reward(TkHumanoid* h, const float* obs, int64_t m, float* reward_out, void* stream) {
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
     TK_REQUIRE(obs && reward_out && m >= 0, TK_ERR_INVALID, "bad wm_reward arguments");
+    TK_REQUIRE(h->variant == kVarHumanoid, TK_ERR_INVALID, "wm_reward is a Humanoid entry point (humanoid.py:425-472)");
     if (m == 0) return TK_OK;
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
@@ -598,9 +664,13 @@ int tk_humanoid_philox_noise(TkHumanoid* h, uint64_t seed, uint64_t step, int64_
                              float* unit_vel, void* stream) {
     TK_REQUIRE(h && unit_pos && unit_vel, TK_ERR_INVALID, "null argument");
     TK_CUDA(cudaSetDevice(h->params.device));
-    const long long total = static_cast<long long>(h->params.num_envs) * kD;
-    humanoid_philox_kernel<kD><<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        h->params.num_envs, seed, step, env_id_offset, h->step_dev, unit_pos, unit_vel);
+    const long long total = static_cast<long long>(h->params.num_envs) * h->params.num_dof;
+    if (h->variant == kVarAnt)
+        humanoid_philox_kernel<kDAnt><<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+            h->params.num_envs, seed, step, env_id_offset, h->step_dev, unit_pos, unit_vel);
+    else
+        humanoid_philox_kernel<kD><<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+            h->params.num_envs, seed, step, env_id_offset, h->step_dev, unit_pos, unit_vel);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }

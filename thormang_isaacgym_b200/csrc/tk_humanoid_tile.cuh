@@ -1,5 +1,6 @@
 // Fused Humanoid post-physics kernel: one warp = one CTA = one tile of 32 consecutive envs
-// (included by tk_humanoid.cu; needs KParams, Layout, torso_math, unscale_fast).
+// (included by tk_humanoid.cu; needs KParams, Spec, torso_math, unscale_fast).  The same kernel, instantiated with
+// AntSpec, is the Ant post-physics step (ant.py:279-287 with D = 8, 60 observations, every reward term live).
 //
 // The slice of every AoS array that belongs to 32 consecutive envs is one contiguous, 16-byte
 // aligned byte range, so the whole tile moves with the bulk-copy (TMA) engine, and the SAME
@@ -31,20 +32,22 @@ namespace humanoid {
 
 constexpr int kTile = 32;   // envs per CTA == one warp
 
-template <int D>
+template <class S>
 struct WarpTile {
     static constexpr int T = kTile;
-    static constexpr int OBS = Layout<D>::kObs;
+    static constexpr int D = S::D;
+    static constexpr int OBS = S::kObs;
     // float offsets of the staged inputs inside the tile buffer (each a multiple of 4 floats = 16 bytes)
     static constexpr int oDof = 0;
     static constexpr int oForce = oDof + T * 2 * D;
-    static constexpr int oAct = oForce + T * D;
+    static constexpr int oAct = oForce + (S::kHasForce ? T * D : 0);
     static constexpr int oSens = oAct + T * D;
-    static constexpr int oRoot = oSens + T * kSensor;
+    static constexpr int oRoot = oSens + T * S::kSensor;
     static constexpr int kIn = oRoot + T * kRoot;
-    static constexpr int kBuf = T * OBS;
-    static_assert(kIn <= kBuf, "staged inputs must fit in the obs image");
+    static constexpr int kOut = T * OBS;                       // the obs image of the tile (what the bulk store moves)
+    static constexpr int kBuf = kIn > kOut ? kIn : kOut;       // Humanoid: 109 inputs < 110 outputs; Ant: 61 > 60
     static_assert(oForce % 4 == 0 && oAct % 4 == 0 && oSens % 4 == 0 && oRoot % 4 == 0, "16-byte aligned regions");
+    static_assert((T * OBS) % 4 == 0 && S::kSensor % 4 == 0 && OBS % 2 == 0, "vector accesses");
 };
 
 __device__ __forceinline__ void warp_copy(float* dst, const float* src, int cnt, int lane) {
@@ -54,7 +57,7 @@ __device__ __forceinline__ void warp_copy(float* dst, const float* src, int cnt,
 // reset_idx :253-279 for env `ne` (lane = DOF): draws the noise, writes the new (pos, vel) pairs and the initial root
 // row to GLOBAL memory and returns this lane's values so that the caller can patch its staged copy.
 // `rank` = index of this env among the envs being reset (COMPACT noise rows follow the reference's nonzero() order).
-template <int D>
+template <int D>   // reset_idx of humanoid.py:253-279 and ant.py:247-271 (identical bodies)
 __device__ __forceinline__ void reset_env_values(const KParams& p, int ne, int rank, int lane, float2* pv_out, float* root_out) {
     const long long row = (p.noise_mode == TK_NOISE_COMPACT) ? rank : ne;
     float2 pv = make_float2(0.0f, 0.0f);
@@ -89,10 +92,12 @@ __device__ __forceinline__ void reset_env_values(const KParams& p, int ne, int r
 #define TK_HUMANOID_MIN_CTAS 12
 #endif
 
-template <int D, bool FUSED>
+template <class S, bool FUSED>
 __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_kernel(const __grid_constant__ KParams p) {
-    using L = Layout<D>;
-    using WT = WarpTile<D>;
+    using L = S;
+    using WT = WarpTile<S>;
+    constexpr int D = S::D;
+    constexpr int kSensor = S::kSensor;
     constexpr int OBS = L::kObs;
     __shared__ __align__(128) float buf[WT::kBuf];
     __shared__ __align__(8) uint64_t bar;
@@ -110,7 +115,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     const float* g_dof = p.dof_state + static_cast<size_t>(env0) * D * 2;
-    const float* g_force = p.dof_force + static_cast<size_t>(env0) * D;
+    const float* g_force = S::kHasForce ? p.dof_force + static_cast<size_t>(env0) * D : nullptr;
     const float* g_act = p.actions + static_cast<size_t>(env0) * D;
     const float* g_sens = p.sensors + static_cast<size_t>(env0) * kSensor;
     const float* g_root = p.root + static_cast<size_t>(env0) * kRoot;
@@ -132,13 +137,13 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
         // one bulk load per lane: issuing a cp.async.bulk holds the issuing thread for ~0.25 us (tools/tile_timeline.py),
         // five lanes pay that once instead of one lane paying it five times
         if (lane == 0) bulk_load(buf + WT::oDof, g_dof, kTile * D * 2 * 4, &bar);
-        else if (lane == 1) bulk_load(buf + WT::oForce, g_force, kTile * D * 4, &bar);
+        else if (S::kHasForce && lane == 1) bulk_load(buf + WT::oForce, g_force, kTile * D * 4, &bar);
         else if (lane == 2) bulk_load(buf + WT::oAct, g_act, kTile * D * 4, &bar);
         else if (lane == 3) bulk_load(buf + WT::oRoot, g_root, kTile * kRoot * 4, &bar);
         else if (lane == 4) bulk_load(buf + WT::oSens, g_sens, kTile * kSensor * 4, &bar);
     } else {
         warp_copy(buf + WT::oDof, g_dof, nt * D * 2, lane);
-        warp_copy(buf + WT::oForce, g_force, nt * D, lane);
+        if (S::kHasForce) warp_copy(buf + WT::oForce, g_force, nt * D, lane);
         warp_copy(buf + WT::oAct, g_act, nt * D, lane);
         warp_copy(buf + WT::oSens, g_sens, nt * kSensor, lane);
         warp_copy(buf + WT::oRoot, g_root, nt * kRoot, lane);
@@ -224,7 +229,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
             const float2 pv = dof2[j];
             o[L::kPos + j] = pv.x;
             o[L::kVel + j] = pv.y;
-            o[L::kForce + j] = fo[j];
+            if (S::kHasForce) o[L::kForce + j] = fo[j];
             o[L::kAct + j] = ac[j];
         }
 #pragma unroll
@@ -242,26 +247,31 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_up = 0.f, st_head = 0.f;
     bool out_reset = false, out_timeout = false;
     if (valid) {
-        // ---- scaled copies (humanoid.py:406, 413-414), constants straight from the parameter bank
+        // ---- scaled copies (humanoid.py:406, 413-414 | ant.py:389, 402-404), constants straight from the parameter bank
         const float dvs = p.dof_vel_scale, cfs = p.contact_scale;
 #pragma unroll
         for (int j = 0; j < D; ++j) {
-            o[L::kPos + j] = unscale_fast(o[L::kPos + j], p.lo[j], p.hi[j], p.rinv[j]);
+            // Ant counts `dof_pos_scaled > 0.99` in its reward (ant.py:347): the true IEEE quotient keeps that
+            // threshold bit-exact; Humanoid's live reward never reads these columns -> reciprocal multiply
+            o[L::kPos + j] = (S::kVariant == kVarAnt) ? unscale_ref(o[L::kPos + j], p.lo[j], p.hi[j])
+                                                      : unscale_fast(o[L::kPos + j], p.lo[j], p.hi[j], p.rinv[j]);
             o[L::kVel + j] *= dvs;
-            o[L::kForce + j] *= cfs;
+            if (S::kHasForce) o[L::kForce + j] *= cfs;
         }
 #pragma unroll
         for (int k = 0; k < kSensor; ++k) o[L::kSens + k] *= cfs;
 
         // ---- torso math
-        const Head h = torso_math(r, p);
+        const Head h = torso_math<S::kVariant>(r, p);
         // after a reset potentials = prev_potentials = -|targets - initial_pos| / dt (:273-276); the root row now IS the
         // initial row, so that value equals the freshly computed potential
         const float prev_new = (FUSED && do_reset) ? h.pot : pot_old;              // :394
 #pragma unroll
         for (int c = 0; c < 12; ++c) o[c] = h.c[c];
-        o[L::kPot] = h.pot / 60000.0f;                                             // :414
-        o[L::kPot + 1] = prev_new / 60000.0f;
+        if (S::kVariant == kVarHumanoid) {
+            o[L::kPot] = h.pot / 60000.0f;                                         // :414
+            o[L::kPot + 1] = prev_new / 60000.0f;
+        }
 
         float2* row = reinterpret_cast<float2*>(buf + lane * OBS);                 // 440-byte rows: 8-byte aligned
 #pragma unroll
@@ -275,10 +285,30 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
         }
         if (FUSED) {
             if (do_reset) prog = 0;                                                // :278 (and reset_buf -> 0, :279)
-            const float up_reward = (h.c[10] > 0.93f) ? (0.0f + p.up_weight) : 0.0f;   // :349-350
-            float total = 2.0f + up_reward;                                        // :362,365
+            const float up_reward = (h.c[10] > 0.93f) ? (0.0f + p.up_weight) : 0.0f;   // :349-350 | ant.py:341-342
+            float total;
+            if (S::kVariant == kVarAnt) {
+                // compute_ant_reward, ant.py:337-354: every term live
+                const float hp = h.c[11];
+                const float heading_reward = (hp > 0.8f) ? (1.0f * p.heading_weight) : (p.heading_weight * hp / 0.8f);
+                float actions_cost = 0.0f, electricity_cost = 0.0f;
+                int at_limit = 0;
+#pragma unroll
+                for (int j = 0; j < D; ++j) {
+                    const float a = o[L::kAct + j];
+                    actions_cost += a * a;                                         // :345
+                    electricity_cost += fabsf(a * o[L::kVel + j]);                 // :346 (obs[:, 20:28] = scaled dof_vel)
+                    at_limit += (o[L::kPos + j] > 0.99f) ? 1 : 0;                  // :347
+                }
+                const float progress_reward = h.pot - prev_new;                    // :351
+                total = progress_reward + 0.5f + up_reward + heading_reward - p.actions_cost_scale * actions_cost -
+                        p.energy_cost_scale * electricity_cost -
+                        static_cast<float>(at_limit) * p.joints_cost_scale;        // :353-354
+            } else {
+                total = 2.0f + up_reward;                                          // humanoid.py:362,365
+            }
             const bool fallen = h.c[0] < p.termination_height;
-            if (fallen) total = 1.0f * p.death_cost;                               // :370
+            if (fallen) total = 1.0f * p.death_cost;                               // :370 | ant.py:357
             const bool finished = static_cast<float>(prog) >= p.max_episode_length - 1.0f;   // :374
             out_reset = fallen || finished;                                        // :373-374 (reset_buf is 0 here)
             out_timeout = finished && out_reset;                                   // vec_task.py:345
@@ -303,7 +333,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     float* dst = p.obs + static_cast<size_t>(env0) * OBS;
     if (bulk) {
         if (lane == 0) {
-            bulk_store(dst, buf, WT::kBuf * 4);
+            bulk_store(dst, buf, WT::kOut * 4);
             bulk_commit();
         }
     } else {

@@ -1,8 +1,10 @@
-"""Task registry, same shape as ``isaacgymenvs/tasks/__init__.py:54-78`` for the two hot-path tasks."""
+"""Task registry, same shape as ``isaacgymenvs/tasks/__init__.py:54-78`` for the hot-path tasks."""
+from .ant import Ant
 from .gogoro_new import Gogoro
 from .humanoid import Humanoid
 
 isaacgym_task_map = {
     "Humanoid": Humanoid,
+    "Ant": Ant,
     "Gogoro": Gogoro,
 }

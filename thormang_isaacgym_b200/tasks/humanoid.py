@@ -33,6 +33,12 @@ NUM_DOF = 21
 
 class Humanoid(VecTask):
     fuses_action_clip = True
+    # what the sibling task built from the same kernel template overrides (tasks/ant.py)
+    _NUM_OBS, _NUM_DOF, _NUM_SENSOR = NUM_OBS, NUM_DOF, 12
+    _VARIANT = nat.VARIANT_HUMANOID
+    _HAS_DOF_FORCE = True
+    _EFFORT_KEY = "motor_efforts"                                                 # humanoid.py:160-171
+    _asset = staticmethod(humanoid_asset)
 
     def __init__(self, cfg, rl_device, sim_device, graphics_device_id, headless,
                  virtual_screen_capture=False, force_render=False):
@@ -56,8 +62,8 @@ class Humanoid(VecTask):
         self.termination_height = env["terminationHeight"]
         self.debug_viz = False
         self.max_episode_length = env["episodeLength"]
-        env["numObservations"] = NUM_OBS                                          # humanoid.py:67
-        env["numActions"] = NUM_DOF                                               # humanoid.py:68
+        env["numObservations"] = self._NUM_OBS                                    # humanoid.py:67
+        env["numActions"] = self._NUM_DOF                                         # humanoid.py:68
 
         super().__init__(config=cfg, rl_device=rl_device, sim_device=sim_device,
                          graphics_device_id=graphics_device_id, headless=headless,
@@ -65,8 +71,8 @@ class Humanoid(VecTask):
 
         sim, dev, n, d = self.sim, self.device, self.num_envs, self.num_dof
         # humanoid.py:78-98: aliases of simulator memory
-        self.vec_sensor_tensor = sim.acquire_force_sensor_tensor().view(n, 12)
-        self.dof_force_tensor = sim.acquire_dof_force_tensor().view(n, d)
+        self.vec_sensor_tensor = sim.acquire_force_sensor_tensor().view(n, self._NUM_SENSOR)
+        self.dof_force_tensor = sim.acquire_dof_force_tensor().view(n, d) if self._HAS_DOF_FORCE else None
         self.root_states = sim.acquire_actor_root_state_tensor()
         self.initial_root_states = self.root_states.clone()
         self.initial_root_states[:, 7:13] = 0
@@ -114,17 +120,17 @@ class Humanoid(VecTask):
         n = self.cfg["env"]["numEnvs"]
         sim = self.cfg.get("sim_backend")
         if sim is None:
-            sim = FakeSim(n, NUM_DOF, self.device, num_sensor_floats=12, asset=humanoid_asset())
+            sim = FakeSim(n, self._NUM_DOF, self.device, num_sensor_floats=self._NUM_SENSOR, asset=self._asset())
         self.sim = sim
         self.num_dof = sim.num_dof
-        if self.num_dof != NUM_DOF:
-            raise ValueError(f"Humanoid kernels are built for {NUM_DOF} DOFs, simulator has {self.num_dof}")
+        if self.num_dof != self._NUM_DOF:
+            raise ValueError(f"{type(self).__name__} kernels are built for {self._NUM_DOF} DOFs, simulator has {self.num_dof}")
         dev = self.device
         lo = sim.asset["dof_limits_lower"].to(dev).float()
         hi = sim.asset["dof_limits_upper"].to(dev).float()
         self.dof_limits_lower = torch.minimum(lo, hi)                             # humanoid.py:205-215 (swap if lower > upper)
         self.dof_limits_upper = torch.maximum(lo, hi)
-        self.motor_efforts = sim.asset["motor_efforts"].to(dev).float()           # humanoid.py:160-171
+        self.motor_efforts = sim.asset[self._EFFORT_KEY].to(dev).float()          # humanoid.py:160-171 | ant.py:160-162
         self.max_motor_effort = float(self.motor_efforts.max())
         self.start_rotation = torch.tensor([0.0, 0.0, 0.0, 1.0], device=dev)      # humanoid.py:180-182
 
@@ -132,7 +138,7 @@ class Humanoid(VecTask):
         lib = nat.lib()
         p = nat.HumanoidParams()
         p.device = self.device_id
-        p.num_envs, p.num_dof = self.num_envs, self.num_dof
+        p.num_envs, p.num_dof, p.variant = self.num_envs, self.num_dof, self._VARIANT
         p.dt = self.dt
         p.dof_vel_scale, p.angular_velocity_scale = self.dof_vel_scale, self.angular_velocity_scale
         p.contact_force_scale, p.power_scale = self.contact_force_scale, self.power_scale
@@ -212,7 +218,8 @@ class Humanoid(VecTask):
         self.sim.refresh_dof_state_tensor()
         self.sim.refresh_actor_root_state_tensor()
         self.sim.refresh_force_sensor_tensor()
-        self.sim.refresh_dof_force_tensor()
+        if self._HAS_DOF_FORCE:
+            self.sim.refresh_dof_force_tensor()
         nat.check(self._lib.tk_humanoid_compute_observations(self._handle, self._stream()),
                   "tk_humanoid_compute_observations")
 
