@@ -76,7 +76,7 @@ def test_gogoro_step_api():
 def test_factory_and_registry():
     import thormang_isaacgym_b200 as pkg
     from thormang_isaacgym_b200.tasks import isaacgym_task_map
-    assert set(isaacgym_task_map) == {"Humanoid", "Gogoro"}
+    assert {"Humanoid", "Gogoro"} <= set(isaacgym_task_map)
     env = pkg.make(seed=3, task="Humanoid", num_envs=64, sim_device=DEV, rl_device=DEV)
     obs_d, rew, reset, extras = env.step(env.zero_actions())
     assert obs_d["obs"].shape == (64, 110) and rew.shape == (64,) and reset.dtype == torch.int64

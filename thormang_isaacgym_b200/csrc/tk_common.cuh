@@ -78,6 +78,13 @@ __device__ __forceinline__ void bulk_load(void* sdst, const void* gsrc, uint32_t
                  "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// L2 prefetch of a contiguous global range through the bulk-copy engine (no destination, no completion to wait for);
+// src 16-byte aligned, bytes % 16 == 0.  A hint only: L2 is the point of coherence, later writes by other kernels
+// update the resident lines.
+__device__ __forceinline__ void bulk_prefetch_l2(const void* gsrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void prefetch_l2(const void* gsrc) { asm volatile("prefetch.global.L2 [%0];" ::"l"(gsrc)); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }

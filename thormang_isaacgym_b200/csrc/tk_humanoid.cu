@@ -89,6 +89,10 @@ struct KParams {
     float rinv[TK_MAX_DOF];     // 1 / (hi - lo), rounded to fp32 on the host
     unsigned long long* step_dev;   // device-side noise epoch (upper 32 bits of the Philox step), see tk_common.cuh
     long long* dbg_ts;          // developer timeline probe (tools/tile_timeline.py); NULL in normal use
+    int stagger_cycles;         // first-wave stagger: resident slot s of an SM delays its bulk loads by s * cycles (0 = off)
+    int stagger_ctas;           // CTAs of the first wave (resident CTAs per SM x SMs)
+    int sm_count;
+    int prefetch;               // L2 prefetch of the tile inputs ahead of griddepcontrol.wait
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -426,6 +430,11 @@ struct TkHumanoid {
     int* tile_base;       // [tiles]
     int last_grid;
     int use_pdl;          // programmatic dependent launch (TK_HUMANOID_PDL=0 disables)
+    int stagger_cycles;   // TK_HUMANOID_STAGGER (SM cycles per resident slot), see the kernel
+    int stagger_slots;    // TK_HUMANOID_STAGGER_SLOTS
+    int smem_pad;         // TK_HUMANOID_SMEM_PAD: extra dynamic shared memory per CTA (caps the resident CTAs per SM)
+    int prefetch;         // TK_HUMANOID_PREFETCH: L2 prefetch ahead of griddepcontrol.wait (default: small grids only)
+    int sm_count;
     unsigned long long* step_dev;
     long long* dbg_ts;
 };
@@ -440,7 +449,7 @@ static void launch_tile(const TkHumanoid* h, const KParams& k, cudaStream_t st) 
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(h->tiles);
     cfg.blockDim = dim3(kTile);
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = h->smem_pad;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -461,6 +470,8 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     k.pot = B.potentials; k.prev_pot = B.prev_potentials; k.up_vec = B.up_vec; k.heading_vec = B.heading_vec;
     k.init_root = B.initial_root_states; k.init_dof_pos = B.initial_dof_pos; k.ep_return = B.episode_return;
     k.partials = h->partials; k.tile_rank_base = h->tile_base; k.dbg_ts = h->dbg_ts; k.step_dev = h->step_dev;
+    k.prefetch = h->prefetch;
+    k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count;
     k.unit_a = nullptr; k.unit_b = nullptr; k.noise_rows = 0; k.seed = 0; k.step = 0; k.env_off = 0;
     k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs;
@@ -505,7 +516,31 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     h->dbg_ts = nullptr;
     h->use_pdl = 1;
     if (const char* env = getenv("TK_HUMANOID_PDL")) h->use_pdl = atoi(env) != 0;
+    // First-wave stagger (see the kernel): 500 SM cycles per resident slot; anything in 400..700 measured the same
+    // (B200: 16.5 -> 14.0 us at 65536 envs, 25.4 -> 23.0 us at 131072).  The slot count is the kernel's real occupancy.
+    h->stagger_cycles = 500; h->stagger_slots = 12; h->smem_pad = 0; h->sm_count = 148;
+    cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, params->device);
+    {
+        int occ = 0;
+        cudaError_t oe = (params->variant == kVarAnt)
+            ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, humanoid_warp_kernel<AntSpec, true>, kTile, 0)
+            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, humanoid_warp_kernel<HumanoidSpec, true>, kTile, 0);
+        if (oe == cudaSuccess && occ > 0) h->stagger_slots = occ;
+        else cudaGetLastError();
+    }
+    h->prefetch = -1;   // auto, resolved below
+    if (const char* env = getenv("TK_HUMANOID_PREFETCH")) h->prefetch = atoi(env);
+    if (const char* env = getenv("TK_HUMANOID_STAGGER")) h->stagger_cycles = atoi(env);
+    if (const char* env = getenv("TK_HUMANOID_STAGGER_SLOTS")) h->stagger_slots = atoi(env);
+    if (const char* env = getenv("TK_HUMANOID_SMEM_PAD")) {
+        h->smem_pad = atoi(env);
+        cudaFuncSetAttribute(humanoid_warp_kernel<HumanoidSpec, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_pad);
+        cudaFuncSetAttribute(humanoid_warp_kernel<AntSpec, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_pad);
+    }
     h->tiles = (params->num_envs + kTile - 1) / kTile;
+    // L2 prefetch ahead of griddepcontrol.wait pays only while the whole grid is resident at once and thin (measured:
+    // 10.1 -> 8.3 us at 16384 envs, but +1.8 us at 65536 where it re-synchronises the staggered first wave)
+    if (h->prefetch < 0) h->prefetch = (h->tiles <= 4 * h->sm_count) ? 2 : 0;
     h->last_grid = 0;
     h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr; h->step_dev = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);

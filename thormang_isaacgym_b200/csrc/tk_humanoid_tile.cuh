@@ -121,6 +121,37 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     const float* g_root = p.root + static_cast<size_t>(env0) * kRoot;
 
     if (bulk && lane == 0) mbar_init(&bar, 1);
+    // L2 prefetch of this tile's inputs, issued BEFORE griddepcontrol.wait: under programmatic dependent launch this
+    // CTA becomes resident while the previous kernel in the stream is still draining, and the HBM reads of its 14 KB
+    // overlap that drain instead of starting after it.  A prefetch consumes nothing, so stream order is intact: L2 is
+    // the point of coherence and any later write of the previous kernel lands in the resident line; the real loads
+    // below still come after the wait.
+    if (bulk && p.prefetch == 1) {          // through the bulk-copy engine
+        if (lane == 0) bulk_prefetch_l2(g_dof, kTile * D * 2 * 4);
+        else if (S::kHasForce && lane == 1) bulk_prefetch_l2(g_force, kTile * D * 4);
+        else if (lane == 2) bulk_prefetch_l2(g_act, kTile * D * 4);
+        else if (lane == 3) bulk_prefetch_l2(g_root, kTile * kRoot * 4);
+        else if (lane == 4) bulk_prefetch_l2(g_sens, kTile * kSensor * 4);
+    } else if (bulk && p.prefetch == 2 && blockIdx.x < static_cast<unsigned>(p.stagger_ctas)) {
+        // through the load/store unit, one 128-byte line per instruction, first-wave CTAs only (later CTAs start
+        // after the dependency has resolved: a prefetch would only add requests)
+        auto pf = [&](const float* base, int bytes) {
+            for (int o = lane * 128; o < bytes; o += 32 * 128) prefetch_l2(reinterpret_cast<const char*>(base) + o);
+        };
+        pf(g_dof, kTile * D * 2 * 4);
+        if (S::kHasForce) pf(g_force, kTile * D * 4);
+        pf(g_act, kTile * D * 4);
+        pf(g_root, kTile * kRoot * 4);
+        pf(g_sens, kTile * kSensor * 4);
+    }
+    if (bulk && p.prefetch) {
+        if (lane == 5) prefetch_l2(p.pot + env0);
+        else if (FUSED && lane == 6) prefetch_l2(p.progress + env0);
+        else if (FUSED && lane == 7) prefetch_l2(p.progress + env0 + 16);
+        else if (FUSED && lane == 8) prefetch_l2(p.reset + env0);
+        else if (FUSED && lane == 9) prefetch_l2(p.reset + env0 + 16);
+        else if (FUSED && lane == 10 && p.ep_return) prefetch_l2(p.ep_return + env0);
+    }
     // touch both ends of the per-DOF constant tables so that their constant-cache lines are fetched now, not in the
     // middle of the math (the result only feeds a never-true predicate)
     const float warm = p.lo[0] + p.lo[D - 1] + p.hi[0] + p.hi[D - 1] + p.rinv[0] + p.rinv[D - 1] + p.dt + p.tgt[0];
@@ -128,6 +159,13 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     asm volatile("griddepcontrol.wait;" ::: "memory");
     TK_STAMP(0);
     if (warm == -1.2345e-30f && p.dbg_ts) p.dbg_ts[0] = 0;
+    // First-wave stagger.  CTAs of the first wave all start at once, so without this every SM runs load-all / math-all /
+    // store-all phases in lockstep and HBM idles during the math; later CTAs start as slots free up and are staggered
+    // by construction.  Resident slot s (~ blockIdx / #SMs) of the first wave waits s * stagger_cycles.
+    if (p.stagger_cycles > 0 && blockIdx.x < static_cast<unsigned>(p.stagger_ctas)) {
+        const long long until = clock64() + static_cast<long long>(blockIdx.x / p.sm_count) * p.stagger_cycles;
+        while (clock64() < until) __nanosleep(32);
+    }
     if (bulk) {
         if (lane == 0) {
             fence_proxy_async_smem();      // the init (generic proxy) must be visible to the bulk-copy engine (async proxy)

@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--pdl", default="1")
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--kernel", default="post", choices=["post", "pre"])
+    ap.add_argument("--sweep", default="", help="ENV_VAR=v1,v2,... : one line per value (developer knobs of the kernels)")
     args = ap.parse_args()
     peak, _ = B.measured_peak_gbs()
     bpe = B.HUMANOID_BYTES_PER_ENV if args.task == "humanoid" else B.GOGORO_BYTES_PER_ENV
@@ -48,6 +49,17 @@ def main():
             gbs = n * pre_bytes / (us * 1e-6) / 1e9
             print(json.dumps({"task": args.task, "kernel": "pre_physics", "envs": n, "us_per_step": round(us, 2),
                               "GBps": round(gbs, 1), "frac": round(gbs / peak, 4), "sets": sets}), flush=True)
+        return
+    if args.sweep:
+        key, vals = args.sweep.split("=")
+        for n in [int(x) for x in args.envs.split(",")]:
+            for v in vals.split(","):
+                os.environ[key] = v
+                r = G._kernel_bench(torch, args.task, n, "cuda:0", args.steps, args.warmup, seed=5)
+                us = 1e3 * r["ms_total"] / args.steps
+                gbs = n * bpe / (us * 1e-6) / 1e9
+                print(json.dumps({"task": args.task, "envs": n, key: v, "us_per_step": round(us, 2),
+                                  "GBps": round(gbs, 1), "frac": round(gbs / peak, 4), "sets": r["sets"]}), flush=True)
         return
     for n in [int(x) for x in args.envs.split(",")]:
         for tile in [int(x) for x in args.pdl.split(",")]:
