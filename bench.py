@@ -29,6 +29,11 @@ if ROOT not in sys.path:
 
 HUMANOID_BYTES_PER_ENV = 924     # 456 B read + 468 B written per env-step, fused post-physics
 GOGORO_BYTES_PER_ENV = 172       # 192 B with supplied noise, 172 B with in-kernel RNG
+# SURVEY.md 8(f) N1, 8-channel x 20-frame Gogoro variant: fused kernel 780 B read (root 52, 6 scalars 32,
+# progress/reset 16, command ring 80, 19 noisy frames 608) + 705 B written (obs row 640, clean frame 32, command 4, reward 4,
+# reset/progress 16, timeout 1, speed 4, yaw command 4); finalize kernel 16 B read + 8 B written
+GOGORO_PAPER_BYTES_PER_ENV = 1509
+BYTES_PER_ENV = {"humanoid": HUMANOID_BYTES_PER_ENV, "gogoro": GOGORO_BYTES_PER_ENV, "gogoro_paper": GOGORO_PAPER_BYTES_PER_ENV}
 L2_BYTES = 126 * 1024 * 1024
 METRIC = "env-steps/sec (obs+reward+reset)"
 

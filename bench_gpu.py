@@ -59,6 +59,36 @@ def _make_gogoro(n, seed, device, env_off=0):
     return env, st
 
 
+def _make_gogoro_paper(n, seed, device, env_off=0):
+    """8-channel x 20-frame Gogoro variant; ~2 % of the envs beyond the fall threshold per step."""
+    import torch
+    from thormang_isaacgym_b200 import config as tcfg
+    from thormang_isaacgym_b200 import synthetic as syn
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.gogoro_realistic_turning_sim_paper import Gogoro as GogoroPaper
+    st = syn.gogoro_paper_state(n, seed=seed, fallen_frac=0.02)
+    cfg = tcfg.gogoro_paper_cfg(n, seed=1234)
+    cfg["env"]["envIdOffset"] = env_off
+    cfg["env"]["resetOnInit"] = False
+    names = ["steering_joint", "rear_wheel_joint"] + [f"j{i}" for i in range(37)]
+    sim = FakeSim(n, 39, device, num_sensor_floats=0, dof_names=names)
+    sim.load_state(st)
+    cfg["sim_backend"] = sim
+    dev_index = torch.device(device).index or 0
+    env = GogoroPaper(cfg, device, f"cuda:{dev_index}", -1, True)
+    for name in ("yaw_command", "curent_command", "curent_speed", "steer_offsets", "curent_speed_offset",
+                 "curent_imu_x_offset", "steer_delay", "command_history", "progress_buf", "reset_buf", "thormang_pose"):
+        getattr(env, name).copy_(st[name].to(device))
+    env.buffer_obs_ring.copy_(st["buffer_obs"].to(device))
+    env.command_ring.copy_(st["buffer_obs"][:, :, 6].to(device))
+    env.obs_buf.copy_(st["buffer_obs_noisy"].flatten(start_dim=1).to(device))
+    return env, st
+
+
+_MAKERS = {"humanoid": _make_humanoid, "gogoro": _make_gogoro, "gogoro_paper": _make_gogoro_paper}
+_LAUNCHES_PER_STEP = {"humanoid": 1, "gogoro": 1, "gogoro_paper": 2}   # the paper variant: fused kernel + reward finalize
+
+
 def _rotating_sets(n, bytes_per_env):
     per_set = n * bytes_per_env
     return max(3, int(math.ceil(2.2 * B.L2_BYTES / per_set)))
@@ -90,9 +120,10 @@ def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, b
                   graph=False):
     """Fused post-physics kernel over rotating state sets.  Returns dict(ms_total, launches, sets, window).
     graph=True: one pass over the sets is captured in a CUDA graph and replayed (steps is rounded to whole passes)."""
-    bpe = B.HUMANOID_BYTES_PER_ENV if task == "humanoid" else B.GOGORO_BYTES_PER_ENV
+    bpe = B.BYTES_PER_ENV[task]
     sets = _rotating_sets(n, bpe)
-    make = _make_humanoid if task == "humanoid" else _make_gogoro
+    make = _MAKERS[task]
+    per_step = _LAUNCHES_PER_STEP[task]
     envs = [make(n, seed + 17 * s, device, env_off)[0] for s in range(sets)]
 
     if graph:
@@ -108,7 +139,7 @@ def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, b
 
         def replay(i):
             g.replay()
-            return sets
+            return sets * per_step
         ms, launches, window = _time_steps(torch, replay, passes, max(1, warmup // sets), barrier)
         del envs
         return {"ms_total": ms, "launches": launches, "sets": sets, "window": window, "steps": passes * sets}
@@ -118,7 +149,7 @@ def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, b
         extra = 0
         if horizon_hook is not None and (i + 1) % HORIZON == 0:
             extra = horizon_hook(envs)
-        return 1 + extra
+        return per_step + extra
 
     ms, launches, window = _time_steps(torch, step, steps, warmup, barrier)
     del envs
@@ -329,11 +360,15 @@ def run_gpu_arm(args, rank, world):
                                     ("humanoid_1048576", "humanoid", 1048576, False),
                                     ("config3_gogoro_65536", "gogoro", 65536, False),
                                     ("config3_gogoro_65536_cuda_graph", "gogoro", 65536, True),
-                                    ("gogoro_4194304", "gogoro", 4194304, False)):
+                                    ("gogoro_4194304", "gogoro", 4194304, False),
+                                    ("n1_gogoro_paper_4096", "gogoro_paper", 4096, False),
+                                    ("n1_gogoro_paper_65536", "gogoro_paper", 65536, False),
+                                    ("n1_gogoro_paper_262144", "gogoro_paper", 262144, False),
+                                    ("n1_gogoro_paper_1048576", "gogoro_paper", 1048576, False)):
                 k = 300 if m <= 262144 else 60
                 r = _kernel_bench(torch, t, m, device, k, 20, seed=77, graph=gr)
                 k = r["steps"]
-                b = B.HUMANOID_BYTES_PER_ENV if t == "humanoid" else B.GOGORO_BYTES_PER_ENV
+                b = B.BYTES_PER_ENV[t]
                 gbs = m * b / (r["ms_total"] / k * 1e-3) / 1e9
                 extras[label] = {"env_steps_per_s": m * k / (r["ms_total"] * 1e-3), "us_per_step": 1e3 * r["ms_total"] / k,
                                  "achieved_GBps": gbs, "frac_of_peak": gbs / peak, "rotating_sets": r["sets"]}

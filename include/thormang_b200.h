@@ -297,6 +297,133 @@ int tk_gogoro_stats(TkGogoro* h, double* stats_out, int32_t accumulate, void* st
 int tk_gogoro_philox_noise(TkGogoro* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* steer_unit,
                            float* sensor_unit, float* reset_unit, float* speed_unit, float* yaw_unit, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Gogoro scooter, 8-channel x 20-frame history variant -- the configuration of the paper runs
+ * (isaacgymenvs/tasks/gogoro_realistic_turning_sim_paper.py, cfg/task/Gogoro_paper.yaml); SURVEY.md 8(f) row N1.
+ * The file is not registered in isaacgymenvs/tasks/__init__.py; its class is also called Gogoro.
+ *
+ * Storage differs from the reference's two shift-copied [N,20,8] buffers (:114-115, :502-506):
+ *   obs_buf [N,160]        = buffer_obs_noisy, time-ordered (oldest frame first), shifted IN PLACE by one frame per step
+ *                            (the reference's obs_buf is a flatten() view of buffer_obs_noisy as well, :545);
+ *   buffer_obs_ring [N,20,8] = the clean frames as a ring: the frame of step t sits in slot t % 20 (device-side tick);
+ *                            tk_gogoro_paper_clean_frames materialises the reference's time-ordered buffer_obs;
+ *   command_ring [N,20]    = channel 6 of the clean frames (the reward's act_buff, :509), same ring.
+ * ------------------------------------------------------------------------------------------ */
+
+typedef struct TkGogoroPaperParams {
+    int32_t device;
+    int32_t num_envs;
+    int32_t num_dof;                 /* 39 for scooter_V13.urdf */
+    int32_t steering_joint;          /* dof_name_to_id['steering_joint'], :360 */
+    int32_t rear_wheel_joint;        /* dof_name_to_id['rear_wheel_joint'], :376 */
+    int32_t max_episode_length;      /* cfg["env"]["max_steps"], :47 */
+    int32_t speed_freq_update;       /* :78 */
+    int32_t yaw_freq_update;         /* :79 */
+    int32_t buff_size;               /* 20, :112 */
+    int32_t delay_width;             /* command_delay[1]: width of command_history, :93 (3..8) */
+    int32_t use_steer_delay;         /* USE_STEER_DELAY, :31: per-env tap -steer_delay (:355) instead of the fixed -3 (:357) */
+    int32_t reserved;
+    float max_steering;              /* 0.5, :86 */
+    float start_speed;               /* 1.3 with DEBUG_START_SPEED (:26,638-641), 0 = off */
+    /* [lo,hi] pairs of cfg["noises"], :55-80; double for the same reason as in TkGogoroParams */
+    double imu_filter_noise[2];
+    double imu_noise[2];
+    double speed_sensor_noise[2];
+    double speed_sensor_offset[2];
+    double imu_x_offset[2];
+    double steering_offset[2];
+    double command_delay[2];
+    double speed_range[2];
+} TkGogoroPaperParams;
+
+typedef struct TkGogoroPaperBuffers {
+    float* root_tensor;              /* [N,13] simulator-owned */
+    float* state_dof;                /* [N*D,2] simulator-owned */
+    float* obs_buf;                  /* [N,160], 16-byte aligned */
+    float* buffer_obs_ring;          /* [N,20,8], 16-byte aligned */
+    float* command_ring;             /* [N,20], 16-byte aligned */
+    float* rew_buf;                  /* [N] */
+    int64_t* reset_buf;              /* [N] */
+    int64_t* progress_buf;           /* [N] */
+    uint8_t* timeout_buf;            /* [N] bool, may be NULL */
+    float* yaw_command;              /* [N] :81 */
+    float* curent_command;           /* [N] :90 */
+    float* curent_speed;             /* [N] :88 */
+    float* steer_offsets;            /* [N] :91 */
+    float* curent_speed_offset;      /* [N] :96 */
+    float* curent_imu_x_offset;      /* [N] :97 */
+    float* speed_no_noise;           /* [N] :100 */
+    int64_t* steer_delay;            /* [N] :92 */
+    float* command_history;          /* [N,delay_width] :93 */
+    const float* thormang_pose;      /* [N,D] */
+    const float* root_reset_tensor;  /* [N,13] :155-156 */
+    float* dof_pos_command;          /* [N,D] persistent position-target tensor (:359-360) */
+    float* dof_speed_command;        /* [N,D] persistent velocity-target tensor (:375-376) */
+    float* episode_return;           /* [N], may be NULL */
+} TkGogoroPaperBuffers;
+
+/* U(0,1) draws of one step, addressed by env id (mode TK_NOISE_DENSE), or drawn in-kernel (TK_NOISE_PHILOX), or absent
+ * (TK_NOISE_NONE: every draw = 0.5).  sensor_unit [N,6] in draw order: 2 x imu_filter (:525), 2 x imu_noise (:527),
+ * speed noise (:528), imu_filter (:531).  reset_unit [N,5]: speed (:562), steer_delay (:563), steer_offsets (:564),
+ * speed-sensor offset (:566), imu_x offset (:655).  speed_unit [N] (:407), yaw_unit [N] (:410). */
+typedef struct TkGogoroPaperNoise {
+    int32_t mode;
+    int32_t reserved;
+    const float* sensor_unit;
+    const float* reset_unit;
+    const float* speed_unit;
+    const float* yaw_unit;
+    uint64_t seed;
+    uint64_t step;
+    int64_t env_id_offset;
+} TkGogoroPaperNoise;
+
+typedef struct TkGogoroPaper TkGogoroPaper;
+
+int tk_gogoro_paper_create(const TkGogoroPaperParams* params, TkGogoroPaper** out);
+int tk_gogoro_paper_destroy(TkGogoroPaper* h);
+int tk_gogoro_paper_bind(TkGogoroPaper* h, const TkGogoroPaperBuffers* buffers);
+
+/* pre_physics_step (:342-378): clamp, direct steer command, delay line, the two live target columns. */
+int tk_gogoro_paper_pre_physics(TkGogoroPaper* h, const float* actions, int32_t zero_fill, void* stream);
+
+/* compute_gogoro_observations (:770-807) on the current state -> obs_out [N,8] (clean); nothing else is written. */
+int tk_gogoro_paper_compute_observations(TkGogoroPaper* h, float* obs_out, void* stream);
+
+/* compute_obs_rwd (:490-545) except the cross-env term of the reward; MUST be followed by
+ * tk_gogoro_paper_finalize_reward on the same stream. */
+int tk_gogoro_paper_compute_obs_rwd(TkGogoroPaper* h, const TkGogoroPaperNoise* noise, void* stream);
+
+/* post_physics_step (:382-412) + vec_task.py:345 as ONE fused kernel, except the cross-env term of the reward;
+ * MUST be followed by tk_gogoro_paper_finalize_reward on the same stream. */
+int tk_gogoro_paper_post_physics(TkGogoroPaper* h, const TkGogoroPaperNoise* noise, void* stream);
+
+/* reward7 = 1 - mean over ALL envs and frame pairs of diff(act_buff / 0.5)^2 (:747) couples every env.
+ * sums_out[2] (device, fp64) = {sum of squared differences, number of differences} of the step just computed on THIS
+ * GPU: the payload of the per-step all-reduce in range-sharded multi-GPU runs. */
+int tk_gogoro_paper_diff_sums(TkGogoroPaper* h, double* sums_out, void* stream);
+
+/* Second (small) kernel of a step: rew_buf += 0.2 * reward7, clip at 0 (:760), fall penalty -1 (:761), episode return;
+ * clears the accumulators and advances the frame ring.  sums = the all-reduced pair, or NULL on a single GPU. */
+int tk_gogoro_paper_finalize_reward(TkGogoroPaper* h, const double* sums, void* stream);
+
+/* reset_idx (:599-688 with randomize :557-566 and generate_spawn_r :570-587), PhysX property calls left out.
+ * env_ids[k] int64, unit [k,5]. */
+int tk_gogoro_paper_reset_idx(TkGogoroPaper* h, const int64_t* env_ids, int32_t k, const float* unit, void* stream);
+
+/* The reference's buffer_obs: clean frames in time order, frames_out [N,20,8] (16-byte aligned). */
+int tk_gogoro_paper_clean_frames(TkGogoroPaper* h, float* frames_out, void* stream);
+
+int tk_gogoro_paper_advance_epoch(TkGogoroPaper* h, void* stream);
+
+/* stats: sum reward, #reset, #timeout, sum episode_return of reset envs, sum episode length of reset envs,
+ * sum |tilt|, sum |yaw error|, N */
+int tk_gogoro_paper_stats(TkGogoroPaper* h, double* stats_out, int32_t accumulate, void* stream);
+
+/* Materialise the PHILOX draws of one step: sensor_unit [N,6], reset_unit [N,5], speed_unit [N], yaw_unit [N]. */
+int tk_gogoro_paper_philox_noise(TkGogoroPaper* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* sensor_unit,
+                                 float* reset_unit, float* speed_unit, float* yaw_unit, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -38,6 +38,11 @@ LIFT_TABLE: Dict[str, Iterable[str]] = {
         "shortest_angle_distance",        # gogoro_new.py:687-689
         "compute_gogoro_observations",    # gogoro_new.py:692-723
     ),
+    "isaacgymenvs/tasks/gogoro_realistic_turning_sim_paper.py": (   # SURVEY 8(f) N1, the 8-channel x 20-frame variant
+        "compute_gogoro_reward",          # :713-762
+        "shortest_angle_distance",        # :765-767
+        "compute_gogoro_observations",    # :770-807
+    ),
 }
 
 _PRELUDE = (
@@ -113,3 +118,7 @@ def ant() -> ModuleType:
 
 def gogoro() -> ModuleType:
     return lift("isaacgymenvs/tasks/gogoro_new.py")
+
+
+def gogoro_paper() -> ModuleType:
+    return lift("isaacgymenvs/tasks/gogoro_realistic_turning_sim_paper.py")

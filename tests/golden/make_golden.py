@@ -2,7 +2,7 @@
 
     python tests/golden/make_golden.py
 
-* ``humanoid_jit.npz`` / ``gogoro_jit.npz``: inputs and outputs of the reference's own
+* ``humanoid_jit.npz`` / ``gogoro_jit.npz`` / ``ant_jit.npz`` / ``gogoro_paper_jit.npz``: inputs and outputs of the reference's own
   ``@torch.jit.script`` functions, lifted by source from /root/reference
   (oracle/lift_reference.py), on seeded synthetic states + hand-built edge rows.
 * ``poselib_quat.npz``: outputs of the reference's in-tree quaternion library
@@ -188,6 +188,40 @@ def ant_golden(n_rand=96):
     print("ant_jit.npz", n, "rows; resets", int(reset_out.sum()))
 
 
+def gogoro_paper_golden(n_rand=96):
+    """gogoro_realistic_turning_sim_paper.py JIT functions: observations [N,8], reward over [N,20,8]."""
+    ref = L.gogoro_paper()
+    st = syn.gogoro_paper_state(n_rand, seed=4245)
+    root = st["root_tensor"]
+    base = root[0].clone()
+    edge = []
+    for roll in (0.3799, 0.3801, -0.3801, 0.0):
+        r = base.clone(); r[3:7] = _euler_q(roll, 0.0, 0.5); edge.append(r)          # around max_tilt = 0.38
+    for yaw in (math.pi - 1e-4, -math.pi + 1e-4, 0.0, -1e-4):
+        r = base.clone(); r[3:7] = _euler_q(0.05, 0.01, yaw); edge.append(r)         # yaw wrap
+    for pitch in (math.pi / 2, -math.pi / 2):
+        r = base.clone(); r[3:7] = _euler_q(0.1, pitch, 0.3); edge.append(r)         # gimbal
+    edge = torch.stack(edge)
+    ne = edge.shape[0]
+    n = n_rand + ne
+    root = torch.cat([root, edge])
+    desired = torch.cat([st["yaw_command"], torch.tensor([0.5, 0.5, 0.5, 0.5, -math.pi + 1e-4, math.pi - 1e-4,
+                                                           math.pi, 3.0, 0.3, 0.3])[:ne]])
+    cmd = torch.cat([st["curent_command"], torch.tensor([0.5, -0.5, 0.0, 0.25, 0.1, 0.2, 0.3, 0.4, -0.1, -0.2])[:ne]])
+    delay = torch.cat([st["steer_delay"], torch.tensor([0, 1, 2, 3, 4, 0, 1, 2, 3, 4])[:ne]])
+    progress = torch.cat([st["progress_buf"], torch.tensor([3597, 3598, 3599, 3600, 0, 299, 300, 301, 3598, 3599])[:ne]])
+    obs = ref.compute_gogoro_observations(root.clone(), desired.clone(), cmd.clone(), (delay.clone() - 0) / (5 - 0))
+    ext = syn.gogoro_paper_state(ne, seed=97)
+    frames = torch.cat([st["buffer_obs"], ext["buffer_obs"]])
+    frames = torch.cat([frames[:, 1:], obs.unsqueeze(1)], dim=1)                     # the push of :502-503
+    rew, reset = ref.compute_gogoro_reward(act_buff=frames[:, :, 6], curent_obs=frames, progress_buf=progress,
+                                           max_episode_length=torch.tensor(3600), yaw_update_freq=torch.tensor(300))
+    np.savez_compressed(os.path.join(HERE, "gogoro_paper_jit.npz"), **_np(dict(
+        root_tensor=root, desired_yaw=desired, curent_command=cmd, steer_delay=delay, progress_buf=progress,
+        frames=frames, obs=obs, rew=rew, reset=reset, n_rand=n_rand)))
+    print("gogoro_paper_jit.npz", n, "rows; resets", int(reset.sum()), "reward range", float(rew.min()), float(rew.max()))
+
+
 def poselib_golden(n=256):
     path = os.path.join(L.REFERENCE_ROOT, "isaacgymenvs/tasks/amp/poselib/poselib/core/rotation3d.py")
     spec = importlib.util.spec_from_file_location("_ref_rotation3d", path)
@@ -210,4 +244,5 @@ if __name__ == "__main__":
     humanoid_golden()
     gogoro_golden()
     ant_golden()
+    gogoro_paper_golden()
     poselib_golden()

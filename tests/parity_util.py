@@ -155,3 +155,44 @@ def make_ant_pair(n, seed=1234, device="cuda:0", state=None, asset=None, **env_o
     orc.prev_potentials = state["prev_potentials"].clone()
     orc.randomize_buf = torch.zeros(n, dtype=torch.long)
     return env, orc, state
+
+
+def gogoro_paper_frame_close(got, want, what="frame", noisy=False):
+    """[N,8] frames: roll, yaw, d_roll, d_yaw, speed, delta_yaw, command, delay.  Noisy frames are normalised
+    (angles / pi, :534-538), so the angle tolerance shrinks with them and the wrap period becomes 2."""
+    if not noisy:
+        close(got[:, [2, 3, 4, 6, 7]], want[:, [2, 3, 4, 6, 7]], what=what)
+        angle_close(got[:, [0, 1, 5]], want[:, [0, 1, 5]], what=what + "[angles]")
+    else:
+        close(got[:, [1, 2, 3, 4, 6, 7]], want[:, [1, 2, 3, 4, 6, 7]], what=what)
+        angle_close(got[:, [0, 5]] * math.pi, want[:, [0, 5]] * math.pi, atol=ANGLE_ATOL + 2e-6, what=what + "[angles/pi]")
+
+
+def make_gogoro_paper_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
+    """(cuda task, cpu oracle, state) of the 8x20 Gogoro variant from one synthetic snapshot."""
+    from oracle import gogoro_paper_oracle as gp
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.gogoro_realistic_turning_sim_paper import Gogoro as GogoroPaper
+    state = state or syn.gogoro_paper_state(n, seed=seed)
+    cfg = tcfg.gogoro_paper_cfg(n, seed=seed)
+    cfg["env"].update(env_over)
+    cfg["env"]["resetOnInit"] = False
+    names = ["steering_joint", "rear_wheel_joint"] + [f"j{i}" for i in range(37)]
+    sim = FakeSim(n, 39, device, num_sensor_floats=0, dof_names=names)
+    sim.load_state(state)
+    cfg["sim_backend"] = sim
+    env = GogoroPaper(cfg, device, device, -1, True)
+    consts = gp.GogoroPaperConsts.from_cfg(cfg, steering_joint=0, rear_wheel_joint=1)
+    orc = gp.GogoroPaperOracle(consts, state["root_tensor"].clone(), state["state_dof"].clone(), state["thormang_pose"].clone())
+    for name in ("yaw_command", "curent_command", "curent_speed", "steer_offsets", "curent_speed_offset",
+                 "curent_imu_x_offset", "steer_delay", "command_history", "progress_buf", "reset_buf", "thormang_pose"):
+        getattr(env, name).copy_(state[name].to(device))
+        setattr(orc, name, state[name].clone())
+    orc.buffer_obs = state["buffer_obs"].clone()
+    orc.buffer_obs_noisy = state["buffer_obs_noisy"].clone()
+    orc.obs_buf = orc.buffer_obs_noisy.flatten(start_dim=1)
+    # device tick is 0: ring slot t holds the frame of time index t
+    env.buffer_obs_ring.copy_(state["buffer_obs"].to(device))
+    env.command_ring.copy_(state["buffer_obs"][:, :, 6].to(device))
+    env.obs_buf.copy_(state["buffer_obs_noisy"].flatten(start_dim=1).to(device))
+    return env, orc, state

@@ -151,3 +151,56 @@ def test_ant_golden(golden_dir):
     assert torch.equal(reset, g["reset_out"])
     torch.testing.assert_close(rew, g["rew"], rtol=RTOL, atol=ATOL)
     assert float((g["obs"][:, 12:20] > 0.99).sum()) > 0, "fixture must exercise the joints-at-limit term"
+
+
+def test_gogoro_paper_golden(golden_dir):
+    """8-channel x 20-frame Gogoro variant against gogoro_realistic_turning_sim_paper.py's JIT functions."""
+    from oracle import gogoro_paper_oracle as gp
+    g = _load(golden_dir, "gogoro_paper_jit.npz")
+    obs = gp.paper_observations(g["root_tensor"].clone(), g["desired_yaw"].clone(), g["curent_command"].clone(),
+                                (g["steer_delay"].clone() - 0) / (5 - 0))
+    lin = [2, 3, 4, 6, 7]
+    torch.testing.assert_close(obs[:, lin], g["obs"][:, lin], rtol=RTOL, atol=ATOL)
+    assert _wrap_close(obs[:, [0, 1, 5]], g["obs"][:, [0, 1, 5]], 4e-6)
+    rew, reset = gp.paper_reward(g["frames"][:, :, 6], g["frames"], g["progress_buf"], 3600)
+    assert torch.equal(reset, g["reset"]) and reset.dtype == torch.int64
+    torch.testing.assert_close(rew, g["rew"], rtol=RTOL, atol=ATOL)
+    assert float(rew.min()) == -1.0 and float(rew[rew >= 0].max()) <= 0.45 + 0.1 + 0.35 + 2.0 + 0.2 + 1e-6
+
+
+def test_gogoro_paper_oracle_step_semantics():
+    """Method-level restatement: frame shift, reset zeroing, delay-line tap, command resampling on the hit set."""
+    from oracle import gogoro_paper_oracle as gp
+    from thormang_isaacgym_b200 import synthetic as syn
+    n = 64
+    st = syn.gogoro_paper_state(n, seed=5)
+    orc = gp.GogoroPaperOracle(gp.GogoroPaperConsts(), st["root_tensor"].clone(), st["state_dof"].clone(),
+                               st["thormang_pose"].clone())
+    for name in ("yaw_command", "curent_command", "curent_speed", "steer_offsets", "curent_speed_offset",
+                 "curent_imu_x_offset", "steer_delay", "command_history", "progress_buf", "reset_buf"):
+        setattr(orc, name, st[name].clone())
+    orc.buffer_obs, orc.buffer_obs_noisy = st["buffer_obs"].clone(), st["buffer_obs_noisy"].clone()
+    orc.reset_buf[:] = 0
+    orc.reset_buf[[3, 17]] = 1
+    orc.progress_buf[:] = 10
+    orc.progress_buf[5] = 299
+    nz = syn.gogoro_paper_noise(n, seed=1)
+    hist_before = orc.command_history.clone()
+    orc.pre_physics_step(st["actions"])
+    cmd = torch.clamp(st["actions"][:, 0], -1, 1) * 0.5
+    assert torch.equal(orc.command_history[:, -1], cmd) and torch.equal(orc.command_history[:, :-1], hist_before[:, 1:])
+    assert torch.equal(orc.dof_pos_command[:, 0], orc.command_history[:, -3])
+    old_noisy = orc.buffer_obs_noisy.clone()
+    ids, sp, yw = orc.post_physics_step(nz["sensor_unit"], nz["reset_unit"][[3, 17]], nz["speed_unit"][:1], nz["yaw_unit"])
+    assert ids.tolist() == [3, 17] and sp.tolist() == [5] and yw.tolist() == [5]
+    keep = [i for i in range(n) if i not in (3, 17)]
+    nzy = orc.buffer_obs_noisy
+    assert torch.equal(nzy[keep, :-1][..., [0, 2, 3, 4, 5, 6, 7]], old_noisy[keep, 1:][..., [0, 2, 3, 4, 5, 6, 7]])   # one-frame shift
+    assert float(nzy[[3, 17], :-1].abs().max()) == 0.0                                 # reset zeroes the history
+    assert float(nzy[:, :, 1].abs().max()) == 0.0                                      # :544
+    assert orc.obs_buf.shape == (n, 160) and orc.obs_buf.data_ptr() == nzy.data_ptr()  # flatten() view, :545
+    assert torch.equal(orc.root_tensor[3, 3:7], torch.tensor([0.0, 0.0, 0.0, 1.0]))
+    assert float(orc.root_tensor[3, 7]) == float(np.float32(1.3)) and float(orc.root_tensor[3, 8]) == 0.0
+    assert int(orc.progress_buf[3]) == 0 and float(orc.yaw_command[3]) == 0.0
+    want_speed = 5.0 + nz["speed_unit"][0] * (20.0 - 5.0)
+    assert torch.equal(orc.curent_speed[5], want_speed)

@@ -83,3 +83,23 @@ def test_ant_bit_exact(n):
     rg = ao.ant_reward(got[0], st["reset_buf"], st["progress_buf"], st["actions"], 0.1, 0.5, got[1], got[2], 0.005, 0.05,
                        0.1, 0.31, -2.0, 1000.0)
     assert torch.equal(rw[0], rg[0]) and torch.equal(rw[1], rg[1])
+
+
+@pytest.mark.parametrize("n", [1, 33, 4096])
+def test_gogoro_paper_bit_exact(n):
+    """gogoro_realistic_turning_sim_paper.py:713-807."""
+    from oracle import gogoro_paper_oracle as gp
+    ref = L.gogoro_paper()
+    st = syn.gogoro_paper_state(n, seed=177 + n)
+    delay = (st["steer_delay"].clone() - 0) / (5 - 0)
+    want = ref.compute_gogoro_observations(st["root_tensor"].clone(), st["yaw_command"].clone(),
+                                           st["curent_command"].clone(), delay.clone())
+    got = gp.paper_observations(st["root_tensor"].clone(), st["yaw_command"].clone(), st["curent_command"].clone(), delay)
+    assert torch.equal(want, got)
+    frames = torch.cat([st["buffer_obs"][:, 1:], want.unsqueeze(1)], dim=1)
+    rw = ref.compute_gogoro_reward(act_buff=frames[:, :, 6], curent_obs=frames, progress_buf=st["progress_buf"],
+                                   max_episode_length=torch.tensor(3600), yaw_update_freq=torch.tensor(300))
+    rg = gp.paper_reward(frames[:, :, 6], frames, st["progress_buf"], 3600)
+    assert torch.equal(rw[0], rg[0]) and torch.equal(rw[1], rg[1])
+    a, b = syn._u(syn._gen(3), (256,), -7.0, 7.0), syn._u(syn._gen(4), (256,), -7.0, 7.0)
+    assert torch.equal(ref.shortest_angle_distance(a, b), gp.shortest_angle_distance(a, b))

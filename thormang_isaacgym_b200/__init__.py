@@ -16,7 +16,8 @@ def make(seed: int, task: str, num_envs: int, sim_device: str = "cuda:0", rl_dev
     """isaacgymenvs/__init__.py:14-55: build the named task with the stock cfg (or ``cfg``)."""
     from .tasks import isaacgym_task_map
     if cfg is None:
-        cfg = {"Humanoid": config.humanoid_cfg, "Gogoro": config.gogoro_cfg, "Ant": config.ant_cfg}[task](num_envs, seed)
+        cfg = {"Humanoid": config.humanoid_cfg, "Gogoro": config.gogoro_cfg, "Ant": config.ant_cfg,
+               "GogoroPaper": config.gogoro_paper_cfg}[task](num_envs, seed)
     else:
         cfg["env"]["numEnvs"] = num_envs
     return isaacgym_task_map[task](cfg, rl_device, sim_device, graphics_device_id, headless,

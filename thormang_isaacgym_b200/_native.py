@@ -68,6 +68,31 @@ class GogoroNoise(C.Structure):
     _fields_ = [("reset", ResetNoise), ("sensor_unit", _p), ("speed_unit", _p), ("yaw_unit", _p)]
 
 
+class GogoroPaperParams(C.Structure):
+    _fields_ = [
+        ("device", _i32), ("num_envs", _i32), ("num_dof", _i32), ("steering_joint", _i32),
+        ("rear_wheel_joint", _i32), ("max_episode_length", _i32), ("speed_freq_update", _i32),
+        ("yaw_freq_update", _i32), ("buff_size", _i32), ("delay_width", _i32), ("use_steer_delay", _i32),
+        ("reserved", _i32), ("max_steering", _f), ("start_speed", _f),
+        ("imu_filter_noise", _d * 2), ("imu_noise", _d * 2), ("speed_sensor_noise", _d * 2),
+        ("speed_sensor_offset", _d * 2), ("imu_x_offset", _d * 2), ("steering_offset", _d * 2),
+        ("command_delay", _d * 2), ("speed_range", _d * 2),
+    ]
+
+
+class GogoroPaperBuffers(C.Structure):
+    _fields_ = [(name, _p) for name in (
+        "root_tensor", "state_dof", "obs_buf", "buffer_obs_ring", "command_ring", "rew_buf", "reset_buf",
+        "progress_buf", "timeout_buf", "yaw_command", "curent_command", "curent_speed", "steer_offsets",
+        "curent_speed_offset", "curent_imu_x_offset", "speed_no_noise", "steer_delay", "command_history",
+        "thormang_pose", "root_reset_tensor", "dof_pos_command", "dof_speed_command", "episode_return")]
+
+
+class GogoroPaperNoise(C.Structure):
+    _fields_ = [("mode", _i32), ("reserved", _i32), ("sensor_unit", _p), ("reset_unit", _p), ("speed_unit", _p),
+                ("yaw_unit", _p), ("seed", _u64), ("step", _u64), ("env_id_offset", _i64)]
+
+
 # every symbol include/thormang_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "tk_last_error": (C.c_char_p, []),
@@ -98,6 +123,20 @@ SYMBOLS = {
     "tk_gogoro_post_physics": (C.c_int, [_p, C.POINTER(GogoroNoise), _p]),
     "tk_gogoro_stats": (C.c_int, [_p, _p, _i32, _p]),
     "tk_gogoro_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p, _p, _p, _p, _p]),
+    "tk_gogoro_paper_create": (C.c_int, [C.POINTER(GogoroPaperParams), C.POINTER(_p)]),
+    "tk_gogoro_paper_destroy": (C.c_int, [_p]),
+    "tk_gogoro_paper_bind": (C.c_int, [_p, C.POINTER(GogoroPaperBuffers)]),
+    "tk_gogoro_paper_pre_physics": (C.c_int, [_p, _p, _i32, _p]),
+    "tk_gogoro_paper_compute_observations": (C.c_int, [_p, _p, _p]),
+    "tk_gogoro_paper_compute_obs_rwd": (C.c_int, [_p, C.POINTER(GogoroPaperNoise), _p]),
+    "tk_gogoro_paper_post_physics": (C.c_int, [_p, C.POINTER(GogoroPaperNoise), _p]),
+    "tk_gogoro_paper_diff_sums": (C.c_int, [_p, _p, _p]),
+    "tk_gogoro_paper_finalize_reward": (C.c_int, [_p, _p, _p]),
+    "tk_gogoro_paper_reset_idx": (C.c_int, [_p, _p, _i32, _p, _p]),
+    "tk_gogoro_paper_clean_frames": (C.c_int, [_p, _p, _p]),
+    "tk_gogoro_paper_advance_epoch": (C.c_int, [_p, _p]),
+    "tk_gogoro_paper_stats": (C.c_int, [_p, _p, _i32, _p]),
+    "tk_gogoro_paper_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p, _p, _p, _p]),
 }
 
 _lib = None

@@ -72,3 +72,24 @@ def gogoro_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
         "joints_pos": dict(GOGORO_JOINTS_POS),
         "task": {"randomize": False, "randomization_params": {}},
     })
+
+
+def gogoro_paper_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
+    """cfg/task/Gogoro_paper.yaml:5-58 (+ joints_pos :62-93, same riding pose as Gogoro.yaml)."""
+    return copy.deepcopy({
+        "name": "Gogoro",
+        "physics_engine": "physx",
+        "seed": seed,
+        "env": {"numEnvs": num_envs, "max_steps": 3600},
+        "sim": {"dt": 0.03, "up_axis": "z", "use_gpu_pipeline": True, "gravity": [0.0, 0.0, -9.81], "substeps": 3},
+        "noises": {
+            "imu_filter_noise": [-0.003, 0.003], "imu_noise": [-0.003, 0.003], "speed_sensor_offset": [-0.3, 0.3],
+            "speed_sensor_noise": [0, 0.3], "seat_offset_x_range": [-0.1, 0.1], "seat_offset_y_range": [-0.1, 0.1],
+            "seat_offset_z_range": [-0.05, 0.05], "imu_x_offset": [-0.02, 0.02], "spawn_x_angle": [-0.02, 0.02],
+            "steering_action_noise": [-0.05, 0.05], "steering_offset": [-0.05, 0.05], "command_delay": [0, 5],
+            "steering_damping_range": [50, 1000], "IK_noise_amplitude": [0, 3], "speed_range": [5.0, 20.0],
+            "speed_freq_update": 300, "yaw_freq_update": 300,
+        },
+        "joints_pos": dict(GOGORO_JOINTS_POS),
+        "task": {"randomize": False, "randomization_params": {}},
+    })

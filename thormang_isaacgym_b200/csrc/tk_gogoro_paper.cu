@@ -1,0 +1,816 @@
+// Gogoro scooter, 8-channel x 20-frame history variant ("paper" configuration) for B200 (sm_100a) -- SURVEY 8(f) row N1.
+//
+// Replaces, behind the C ABI of include/thormang_b200.h, the TorchScript functions and method bodies of
+// /root/reference/isaacgymenvs/tasks/gogoro_realistic_turning_sim_paper.py:
+//   pre_physics_step :342-378, post_physics_step :382-412, compute_obs_rwd :490-545, randomize :557-566,
+//   generate_spawn_r :570-587, reset_idx :599-688, compute_gogoro_reward :713-762, shortest_angle_distance :765-767,
+//   compute_gogoro_observations :770-807.
+//
+// Layout.  The reference keeps two [N,20,8] frame buffers and shift-copies both every step (2 x 1280 B/env) before
+// flattening the noisy one into obs_buf.  Here
+//   * obs_buf [N,160] IS the noisy buffer, time-ordered (the reference's obs_buf is a flatten() VIEW of it too, :545);
+//     it is shifted in place by one frame per step: 608 B read + 640 B written per env, the minimum for handing a
+//     contiguous time-ordered [N,160] row to the policy;
+//   * the clean frames live in a true ring [N,20,8] (one 32-byte row written per step, slot = tick % 20, the tick is
+//     a device-side counter so that captured CUDA graphs replay correctly) and the clean command channel, the only
+//     clean history the reward reads (act_buff = buffer_obs[:,:,6]), in a compact ring [N,20] (80 B read, 4 B written).
+// ~1.46 KB / env-step in total.
+//
+// reward7 (:747) is a mean over EVERY env and frame pair: the fused kernel writes the per-env part of the reward and
+// adds each tile's sum of squared command differences to 256 fp64 accumulators; a small second kernel
+// (paper_finalize_kernel, 24 B/env) folds the global mean in, clips, restores the fall penalty and bumps the tick.
+// In range-sharded multi-GPU runs the two sums are all-reduced between the two kernels (the one real exchange step of
+// this variant).
+#include "tk_common.cuh"
+
+#include <new>
+
+namespace tk {
+namespace gpaper {
+
+constexpr int kRoot = 13;
+constexpr int kCh = 8;
+constexpr int kBuf = 20;
+constexpr int kObs = kCh * kBuf;       // 160
+constexpr int kChunks = kObs / 4;      // float4 chunks per obs row
+constexpr int kSensorNoise = 6;
+constexpr int kResetNoise = 5;
+constexpr int kMaxDelayW = 8;
+constexpr int kTile = 32;
+constexpr float kMaxTilt = 0.38f;      // :724
+
+struct KParams {
+    float* root;
+    float* state_dof;
+    float* obs_buf;
+    float* clean_ring;
+    float* cmd_ring;
+    float* rew;
+    long long* reset;
+    long long* progress;
+    uint8_t* timeout;
+    float* yaw_command;
+    float* curent_command;
+    float* curent_speed;
+    float* steer_offsets;
+    float* curent_speed_offset;
+    float* curent_imu_x_offset;
+    float* speed_no_noise;
+    long long* steer_delay;
+    float* command_history;
+    const float* thormang_pose;
+    const float* root_reset;
+    float* pos_cmd;
+    float* vel_cmd;
+    float* ep_return;
+    double* partials;              // [kStatSlots, TK_STATS]
+    double* diff_slots;            // [kStatSlots] sums of squared command differences of the current step
+    unsigned long long* tick;      // completed compute_obs_rwd calls (ring slot = tick % 20)
+    unsigned int* done_ctr;
+    const float* reset_unit;
+    const float* sensor_unit;
+    const float* speed_unit;
+    const float* yaw_unit;
+    unsigned long long seed, step;
+    unsigned long long* step_dev;
+    long long env_off;
+    int noise_mode;
+    int n, num_dof, steering_joint, rear_wheel_joint, max_episode_length, speed_freq, yaw_freq;
+    int delay_w, use_delay;
+    int vec_ok;
+    float max_steering, start_speed;
+    float delay_lo, delay_span;    // (float)command_delay[0], (float)(command_delay[1] - command_delay[0])
+    // (float)lo, (float)(hi - lo) with the span formed in double (get_randoms :549-550)
+    float imu_filter[2], imu[2], speed_sensor[2], speed_off[2], imu_x[2], steer_off[2], delay[2], speed[2];
+};
+
+enum { kStreamSensorA = 16, kStreamSensorB = 17, kStreamResetA = 18, kStreamResetB = 19 };
+
+__device__ __forceinline__ float uniform_of(const float* pair, float u) { return pair[0] + u * pair[1]; }   // get_randoms
+
+// compute_gogoro_observations :770-807
+__device__ __forceinline__ void observe(const float* r, float desired_yaw, float command, float delay_norm, float* o) {
+    Q4 q{r[3], r[4], r[5], r[6]};
+    float roll, yaw;
+    euler_roll_yaw_ref(q, &roll, &yaw);                                             // :775
+    V3 lin = quat_rotate_ref<-1>(q, V3{r[7], r[8], r[9]});                          // :777
+    V3 ang = quat_rotate_ref<-1>(q, V3{r[10], r[11], r[12]});                       // :778
+    roll = (roll > kPi) ? roll - kTwoPi : roll;                                     // :783
+    roll = (roll < -kPi) ? roll + kTwoPi : roll;                                    // :784
+    yaw = (yaw > kPi) ? yaw - kTwoPi : yaw;                                         // :786
+    yaw = (yaw < -kPi) ? yaw + kTwoPi : yaw;                                        // :787
+    const float delta = floor_mod_two_pi_near(desired_yaw - yaw + kPi) - kPi;       // :789, :767
+    o[0] = roll; o[1] = yaw; o[2] = ang.x; o[3] = ang.z; o[4] = lin.x; o[5] = delta; o[6] = command; o[7] = delay_norm;
+}
+
+// compute_gogoro_reward :713-762 without the reward7 term (added by paper_finalize_kernel); *felt_out = fall mask
+__device__ __forceinline__ float reward_partial(const float* o, bool* felt_out) {
+    const float tilt = o[0], dtilt = o[2], yaw_e = o[5];
+    const float tilt_err = fminf(fmaxf(tilt / kMaxTilt, -1.0f), 1.0f);              // :725-726
+    const float yaw_err = fminf(fmaxf(yaw_e / kPi, -1.0f), 1.0f);                   // :728-729
+    const float dtilt_err = fminf(fmaxf(dtilt / 0.3f, -1.0f), 1.0f);                // :731-732
+    const float reward1 = 1.0f - yaw_err * yaw_err;                                 // :737
+    const float reward2 = 1.0f - tilt_err * tilt_err;                               // :738
+    const float reward4 = 1.0f - dtilt_err * dtilt_err;                             // :739
+    const float tilt_w = 1.0f - tanhf(50.0f * (tilt_err * tilt_err));               // :742
+    const float dtilt_w = 1.0f - tanhf(50.0f * (dtilt_err * dtilt_err));            // :743
+    const float a_last = o[6] / 0.5f;                                               // :722
+    const float reward5 = 1.0f - ((a_last * a_last) * (tilt_w * dtilt_w));          // :745
+    *felt_out = fabsf(tilt) >= kMaxTilt;                                            // :757
+    return reward1 * 0.45f + reward2 * 0.1f + reward4 * 0.35f + reward5 * 2.0f;     // :753 (first four terms, same order)
+}
+
+// randomize :557-566 + reset_idx :599-688 for env `ne`, executed by ONE thread (rare, divergent).  u = the 5 unit draws.
+// Writes the global state except obs_buf (the caller's shift phase writes the zero frames); returns the new root row.
+__device__ __forceinline__ void reset_env(const KParams& p, long long ne, const float* u, float* r, long long* delay_out,
+                                          float* imu_x_out, float* speed_off_out) {
+    p.curent_speed[ne] = uniform_of(p.speed, u[0]);                                 // :562
+    const long long delay = static_cast<long long>(uniform_of(p.delay, u[1]));      // :563 (.to(torch.long) truncates)
+    p.steer_delay[ne] = delay;
+    p.steer_offsets[ne] = uniform_of(p.steer_off, u[2]);                            // :564
+    const float so = uniform_of(p.speed_off, u[3]);                                 // :566
+    p.curent_speed_offset[ne] = so;
+    const float ix = uniform_of(p.imu_x, u[4]);                                     // :655
+    p.curent_imu_x_offset[ne] = ix;
+#pragma unroll
+    for (int c = 0; c < kRoot; ++c) r[c] = p.root_reset[ne * kRoot + c];            // :618
+    r[2] = 0.03f;                                                                   // :619
+    r[3] = 0.0f; r[4] = 0.0f; r[5] = 0.0f; r[6] = 1.0f;                             // :573-575,635: euler (0,0,0) -> identity, exactly
+#pragma unroll
+    for (int c = 7; c < kRoot; ++c) r[c] = 0.0f;                                    // :636
+    if (p.start_speed != 0.0f) { r[7] = p.start_speed * 1.0f; r[8] = p.start_speed * 0.0f; }   // :638-641, cos(0), sin(0)
+#pragma unroll
+    for (int c = 0; c < kRoot; ++c) p.root[ne * kRoot + c] = r[c];                  // :645
+    float2* ds = reinterpret_cast<float2*>(p.state_dof) + ne * p.num_dof;
+    for (int j = 0; j < p.num_dof; ++j) ds[j] = make_float2(p.thormang_pose[ne * p.num_dof + j], 0.0f);   // :647-648
+    float4* cr = reinterpret_cast<float4*>(p.clean_ring + ne * kObs);
+    for (int j = 0; j < kChunks; ++j) cr[j] = make_float4(0.f, 0.f, 0.f, 0.f);      // :681
+    float4* cm = reinterpret_cast<float4*>(p.cmd_ring + ne * kBuf);
+#pragma unroll
+    for (int j = 0; j < kBuf / 4; ++j) cm[j] = make_float4(0.f, 0.f, 0.f, 0.f);     // :681 (channel 6 of the clean frames)
+    for (int j = 0; j < p.delay_w; ++j) p.command_history[ne * p.delay_w + j] = 0.0f;   // :686
+    p.curent_command[ne] = 0.0f;                                                    // :683
+    p.yaw_command[ne] = 0.0f;                                                       // :685 (spawn_yaw_tgt = 0, :571)
+    *delay_out = delay; *imu_x_out = ix; *speed_off_out = so;
+}
+
+struct Smem {
+    alignas(128) float frames[kTile * kObs];  // the tile's [32,160] obs rows AFTER the shift (20 KB): loaded one frame ahead
+    alignas(16) float root[kTile * kRoot];
+    alignas(16) float cmd[kTile * kBuf];
+    alignas(8) uint64_t bar;
+};
+
+// MODE 0: fused post_physics_step; 1: compute_obs_rwd only; 2: observations only (obs_out = clean [N,8], nothing else written)
+template <int MODE>
+__global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant__ KParams p, float* __restrict__ obs_out) {
+    __shared__ Smem s;
+    const int lane = threadIdx.x;
+    const int env0 = blockIdx.x * kTile;
+    const int nt = min(kTile, p.n - env0);
+    const long long n = env0 + lane;
+    const bool valid = lane < nt;
+    const bool philox = p.noise_mode == TK_NOISE_PHILOX;
+    const unsigned long long step_now = philox ? effective_step(p.step, p.step_dev) : 0ull;
+    const int slot = static_cast<int>(*p.tick % kBuf);            // ring slot written by this step
+
+    float* obs_tile = p.obs_buf + static_cast<size_t>(env0) * kObs;
+    constexpr uint32_t kShiftBytes = (kTile * kObs - kCh) * 4;       // 20448: the tile minus its first frame
+    const bool bulk = p.vec_ok && nt == kTile;
+    if (bulk) {
+        if (lane == 0) {
+            mbar_init(&s.bar, 1);
+            fence_proxy_async_smem();
+            mbar_expect_tx(&s.bar, (kRoot + (MODE != 2 ? kBuf : 0)) * kTile * 4 + (MODE != 2 ? kShiftBytes : 0));
+        }
+        __syncwarp();
+        // In-place shift of the tile's noisy frames by one frame (:505-506) as ONE bulk copy: the tile's 20 KB are read
+        // starting one frame (32 B) into it, so env e's frames 1..19 land where its frames 0..18 belong; the slot of its
+        // frame 19 receives the next env's frame 0 and is overwritten with the fresh frame below.  The whole tile goes
+        // back with one bulk store after the mbarrier wait, i.e. after every byte of it has been read.
+        if (lane == 0 && MODE != 2) bulk_load(s.frames, obs_tile + kCh, kShiftBytes, &s.bar);
+        else if (lane == 1) bulk_load(s.root, p.root + static_cast<size_t>(env0) * kRoot, kTile * kRoot * 4, &s.bar);
+        else if (lane == 2 && MODE != 2) bulk_load(s.cmd, p.cmd_ring + static_cast<size_t>(env0) * kBuf, kTile * kBuf * 4, &s.bar);
+    } else {
+        for (int i = lane; i < nt * kRoot; i += kTile) s.root[i] = p.root[static_cast<size_t>(env0) * kRoot + i];
+        if (MODE != 2) {
+            for (int i = lane; i < nt * kBuf; i += kTile) s.cmd[i] = p.cmd_ring[static_cast<size_t>(env0) * kBuf + i];
+            for (int i = lane; i < nt * kObs - kCh; i += kTile) s.frames[i] = obs_tile[i + kCh];
+        }
+    }
+
+    long long prog = 0, delay = 0;
+    bool do_reset = false;
+    float yaw_cmd = 0.f, cur_cmd = 0.f, imu_x = 0.f, speed_off = 0.f;
+    if (valid) {
+        yaw_cmd = p.yaw_command[n];
+        cur_cmd = p.curent_command[n];
+        delay = p.steer_delay[n];
+        if (MODE != 2) { imu_x = p.curent_imu_x_offset[n]; speed_off = p.curent_speed_offset[n]; prog = p.progress[n]; }
+        if (MODE == 0) {
+            prog += 1;                                                              // :384
+            do_reset = p.reset[n] != 0;                                             // :385
+            if (do_reset) prog = 0;                                                 // :678
+        }
+    }
+    __syncwarp();
+    if (bulk) mbar_wait(&s.bar, 0);
+
+    float st_len = 0.f, st_tilt = 0.f, st_yaw = 0.f;
+    double dsum = 0.0;
+    bool out_reset = false, out_timeout = false;
+    if (valid) {
+        float r[kRoot];
+#pragma unroll
+        for (int c = 0; c < kRoot; ++c) r[c] = s.root[lane * kRoot + c];
+        float un[kSensorNoise];
+        if (MODE != 2) {
+            if (philox) {
+                Philox4 a = philox_env(p.seed, step_now, p.env_off + n, kStreamSensorA);
+                Philox4 b = philox_env(p.seed, step_now, p.env_off + n, kStreamSensorB);
+                un[0] = u01(a.x); un[1] = u01(a.y); un[2] = u01(a.z); un[3] = u01(a.w); un[4] = u01(b.x); un[5] = u01(b.y);
+            } else {
+#pragma unroll
+                for (int c = 0; c < kSensorNoise; ++c) un[c] = p.sensor_unit ? p.sensor_unit[n * kSensorNoise + c] : 0.5f;
+            }
+        }
+        if (MODE == 0 && do_reset) {
+            float u[kResetNoise];
+            if (philox) {
+                Philox4 a = philox_env(p.seed, step_now, p.env_off + n, kStreamResetA);
+                Philox4 b = philox_env(p.seed, step_now, p.env_off + n, kStreamResetB);
+                u[0] = u01(a.x); u[1] = u01(a.y); u[2] = u01(a.z); u[3] = u01(a.w); u[4] = u01(b.x);
+            } else {
+#pragma unroll
+                for (int c = 0; c < kResetNoise; ++c) u[c] = p.reset_unit ? p.reset_unit[n * kResetNoise + c] : 0.5f;
+            }
+            reset_env(p, n, u, r, &delay, &imu_x, &speed_off);
+            cur_cmd = 0.0f; yaw_cmd = 0.0f;
+            if (p.ep_return) p.ep_return[n] = 0.0f;
+        }
+
+        float o[kCh];
+        const float delay_norm = (static_cast<float>(delay) - p.delay_lo) / p.delay_span;       // :497
+        observe(r, yaw_cmd, cur_cmd, delay_norm, o);                                // :494-499
+        if (MODE == 2) {
+#pragma unroll
+            for (int c = 0; c < kCh; ++c) obs_out[n * kCh + c] = o[c];
+        } else {
+            // clean frame -> ring slot (:502-503), command channel -> compact ring
+            float4* cr = reinterpret_cast<float4*>(p.clean_ring + n * kObs + slot * kCh);
+            cr[0] = make_float4(o[0], o[1], o[2], o[3]);
+            cr[1] = make_float4(o[4], o[5], o[6], o[7]);
+            p.cmd_ring[n * kBuf + slot] = o[6];
+            // time-ordered command history: t = 0..18 from the ring as it was before this step, t = 19 = o[6]
+            float prev_cmd = 0.0f, acc = 0.0f;
+            if (!do_reset) {
+                int t_slot = slot + 1;
+                if (t_slot == kBuf) t_slot = 0;
+                float a0 = s.cmd[lane * kBuf + t_slot] / 0.5f;                      // :722
+#pragma unroll 1
+                for (int t = 1; t < kBuf - 1; ++t) {
+                    if (++t_slot == kBuf) t_slot = 0;
+                    const float a1 = s.cmd[lane * kBuf + t_slot] / 0.5f;
+                    const float d = a1 - a0;
+                    acc += d * d;                                                   // :747 diff(...)**2
+                    a0 = a1;
+                }
+                prev_cmd = a0 * 0.5f;                                               // buffer_obs[:,-2,6] (exact: power of two)
+                const float d = o[6] / 0.5f - a0;
+                acc += d * d;
+            } else {
+                const float d = o[6] / 0.5f;                                        // zero history, new command 0 after reset
+                acc = d * d;
+            }
+            dsum = static_cast<double>(acc);
+            bool felt;
+            const float partial = reward_partial(o, &felt);                         // :508-514
+            const bool finished = prog >= p.max_episode_length - 1;                 // :755
+            out_reset = felt || finished;                                           // :758-759
+            p.rew[n] = felt ? -INFINITY : partial;                                  // sentinel, resolved by paper_finalize_kernel
+            p.reset[n] = out_reset ? 1 : 0;
+            p.speed_no_noise[n] = o[4];                                             // :521
+            // sensor-noise model on the noisy copy :525-544
+            float z[kCh];
+            z[0] = o[0] + uniform_of(p.imu_filter, un[0]);                          // :525
+            z[0] = z[0] + imu_x;                                                    // :526
+            z[2] = o[2] + uniform_of(p.imu, un[2]);                                 // :527
+            z[3] = o[3] + uniform_of(p.imu, un[3]);
+            z[4] = o[4] + uniform_of(p.speed_sensor, un[4]);                        // :528
+            z[4] = z[4] + speed_off;                                                // :529
+            z[4] = (z[4] < 0.0f) ? 0.0f : z[4];                                     // :530
+            z[5] = o[5] + uniform_of(p.imu_filter, un[5]);                          // :531
+            z[0] = z[0] / kPi;                                                      // :534
+            z[2] = z[2] / 3.0f; z[3] = z[3] / 3.0f;                                 // :535
+            z[4] = z[4] / 5.0f;                                                     // :536
+            z[5] = z[5] / kPi;                                                      // :537
+            z[6] = o[6] / p.max_steering;                                           // :538
+            const float dc = prev_cmd - o[6];
+            z[2] = z[2] + dc;                                                       // :541
+            z[0] = z[0] + dc * 0.3f;                                                // :542
+            z[1] = 0.0f;                                                            // :544
+            z[7] = o[7];
+            float4* fr = reinterpret_cast<float4*>(s.frames + lane * kObs);
+            if (do_reset) {                                                         // :680,682: the history is gone
+#pragma unroll 1
+                for (int j = 0; j < kChunks - 2; ++j) fr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            fr[kChunks - 2] = make_float4(z[0], z[1], z[2], z[3]);
+            fr[kChunks - 1] = make_float4(z[4], z[5], z[6], z[7]);
+            st_tilt = fabsf(o[0]); st_yaw = fabsf(o[5]);
+        }
+        if (MODE == 0) {
+            p.progress[n] = prog;
+            // command resampling :393-412
+            const bool do_speed = prog == p.speed_freq, do_yaw = prog == p.yaw_freq;
+            if (do_speed || do_yaw) {
+                float su = 0.5f, yu = 0.5f;
+                if (philox) {
+                    Philox4 b = philox_env(p.seed, step_now, p.env_off + n, kStreamSensorB);
+                    su = u01(b.z); yu = u01(b.w);
+                } else {
+                    if (p.speed_unit) su = p.speed_unit[n];
+                    if (p.yaw_unit) yu = p.yaw_unit[n];
+                }
+                if (do_speed) p.curent_speed[n] = uniform_of(p.speed, su);          // :407
+                if (do_yaw) yaw_cmd = -kPi + yu * kTwoPi;                           // :410
+            }
+            yaw_cmd = (yaw_cmd > kPi) ? yaw_cmd - kTwoPi : yaw_cmd;                 // :411
+            yaw_cmd = (yaw_cmd < -kPi) ? yaw_cmd + kTwoPi : yaw_cmd;                // :412
+            p.yaw_command[n] = yaw_cmd;
+            out_timeout = (prog >= p.max_episode_length - 1) && out_reset;          // vec_task.py:345
+            if (p.timeout) p.timeout[n] = out_timeout ? 1 : 0;
+            if (out_reset) st_len = static_cast<float>(prog);
+        }
+    }
+    if (MODE == 2) return;
+
+    // tile sums: squared command differences (reward7) and the episode statistics that do not need the final reward
+    dsum = warp_sum(dsum);
+    const unsigned m_reset = __ballot_sync(0xffffffffu, out_reset);
+    const unsigned m_to = __ballot_sync(0xffffffffu, out_timeout);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
+        st_tilt += __shfl_xor_sync(0xffffffffu, st_tilt, o);
+        st_yaw += __shfl_xor_sync(0xffffffffu, st_yaw, o);
+    }
+    const int row = blockIdx.x & (kStatSlots - 1);
+    if (lane == 0) atomicAdd(p.diff_slots + row, dsum);
+    if (MODE == 0) {
+        double* pr = p.partials + static_cast<size_t>(row) * TK_STATS;
+        if (lane == 1) atomicAdd(pr + 1, static_cast<double>(__popc(m_reset)));
+        else if (lane == 2) atomicAdd(pr + 2, static_cast<double>(__popc(m_to)));
+        else if (lane == 4) atomicAdd(pr + 4, static_cast<double>(st_len));
+        else if (lane == 5) atomicAdd(pr + 5, static_cast<double>(st_tilt));
+        else if (lane == 6) atomicAdd(pr + 6, static_cast<double>(st_yaw));
+        else if (lane == 7) atomicAdd(pr + 7, static_cast<double>(nt));
+    }
+    __syncwarp();
+
+    // the shifted tile + fresh frames -> obs_buf
+    if (bulk) {
+        fence_proxy_async_smem();          // fresh frames were written through the generic proxy
+        __syncwarp();
+        if (lane == 0) {
+            bulk_store(obs_tile, s.frames, kTile * kObs * 4);
+            bulk_commit();
+            bulk_wait_read<0>();           // shared memory must stay alive until the engine has read it
+        }
+    } else {
+        __syncwarp();
+        for (int i = lane; i < nt * kObs; i += kTile) obs_tile[i] = s.frames[i];
+    }
+}
+
+// reward7 (:747) folded in, clip (:760), fall penalty (:761), episode return; the last CTA clears the difference
+// accumulators and bumps the tick.  sums = {sum of squared differences, number of differences} all-reduced over the
+// ranks, or NULL: this GPU's accumulators and n * 19.
+__global__ void __launch_bounds__(256) paper_finalize_kernel(const __grid_constant__ KParams p, const double* __restrict__ sums) {
+    __shared__ double red[8];
+    __shared__ float add_s;
+    __shared__ bool last_s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    double v = (tid < kStatSlots) ? p.diff_slots[tid] : 0.0;
+    v = warp_sum(v);
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    if (tid == 0) {
+        double S = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) S += red[w];
+        double cnt = static_cast<double>(p.n) * (kBuf - 1);
+        if (sums) { S = sums[0]; cnt = sums[1]; }
+        const float mean = static_cast<float>(S / cnt);
+        const float reward7 = 1.0f - mean;                                          // :747
+        add_s = reward7 * 0.2f;                                                     // :753 last term
+    }
+    __syncthreads();
+    const float add = add_s;
+    float st_rew = 0.f, st_ret = 0.f;
+    for (long long n = static_cast<long long>(blockIdx.x) * blockDim.x + tid; n < p.n; n += static_cast<long long>(gridDim.x) * blockDim.x) {
+        float r = p.rew[n];
+        if (r == -INFINITY) r = -1.0f;                                              // :761
+        else r = fmaxf(r + add, 0.0f);                                              // :753, :760
+        p.rew[n] = r;
+        st_rew += r;
+        if (p.ep_return) {
+            const float ret = p.ep_return[n] + r;
+            p.ep_return[n] = ret;
+            if (p.reset[n] != 0) st_ret += ret;
+        }
+    }
+    double a = warp_sum(static_cast<double>(st_rew)), b = warp_sum(static_cast<double>(st_ret));
+    if (lane == 0) {
+        double* pr = p.partials + static_cast<size_t>((blockIdx.x * 8 + warp) & (kStatSlots - 1)) * TK_STATS;
+        atomicAdd(pr + 0, a);
+        atomicAdd(pr + 3, b);
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) last_s = atomicAdd(p.done_ctr, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (last_s) {
+        if (tid < kStatSlots) p.diff_slots[tid] = 0.0;
+        if (tid == 0) { *p.tick += 1ull; *p.done_ctr = 0u; }
+    }
+}
+
+// {sum of squared command differences, number of differences} of the step just computed -> out[2] (all-reduce payload)
+__global__ void __launch_bounds__(256) paper_diff_sums_kernel(const double* __restrict__ slots, int n, double* __restrict__ out) {
+    __shared__ double red[8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    double v = (tid < kStatSlots) ? slots[tid] : 0.0;
+    v = warp_sum(v);
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    if (tid == 0) {
+        double S = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) S += red[w];
+        out[0] = S;
+        out[1] = static_cast<double>(n) * (kBuf - 1);
+    }
+}
+
+// pre_physics_step :342-378, one env per thread
+__global__ void __launch_bounds__(256) paper_pre_kernel(const __grid_constant__ KParams p, const float* __restrict__ actions,
+                                                         int zero_fill) {
+    const long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (zero_fill) {   // fresh torch.zeros targets of :359,375: flat coalesced fill by the whole grid
+        const long long total = static_cast<long long>(p.n) * p.num_dof;
+        for (long long i = n; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) { p.pos_cmd[i] = 0.0f; p.vel_cmd[i] = 0.0f; }
+        return;
+    }
+    if (n >= p.n) return;
+    const float a = fminf(fmaxf(actions[n], -1.0f), 1.0f);                          // :344 (actions[:,0], one action)
+    const float cmd = a * p.max_steering;                                           // :345
+    p.curent_command[n] = cmd;
+    float h[kMaxDelayW];
+    float* hist = p.command_history + n * p.delay_w;
+#pragma unroll
+    for (int i = 0; i < kMaxDelayW; ++i) h[i] = (i + 1 < p.delay_w) ? hist[i + 1] : cmd;   // :352-353
+    int tap = p.delay_w - 3;                                                        // :357
+    if (p.use_delay) {                                                              // :355: column -steer_delay, -0 = column 0
+        const long long d = p.steer_delay[n];
+        tap = (d <= 0 || d > p.delay_w) ? 0 : static_cast<int>(p.delay_w - d);
+    }
+    float applied = 0.0f;
+#pragma unroll
+    for (int i = 0; i < kMaxDelayW; ++i) {
+        if (i < p.delay_w) hist[i] = h[i];
+        if (i == tap) applied = h[i];
+    }
+    p.pos_cmd[n * p.num_dof + p.steering_joint] = applied;                          // :360
+    p.vel_cmd[n * p.num_dof + p.rear_wheel_joint] = p.curent_speed[n];              // :376
+}
+
+// reset_idx :599-688 for an explicit id list, one thread per listed env
+__global__ void paper_reset_idx_kernel(const __grid_constant__ KParams p, const long long* __restrict__ ids, int k,
+                                       const float* __restrict__ unit) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= k) return;
+    const long long ne = ids[i];
+    if (ne < 0 || ne >= p.n) return;
+    float u[kResetNoise], r[kRoot], f0, f1;
+    long long d;
+#pragma unroll
+    for (int c = 0; c < kResetNoise; ++c) u[c] = unit[static_cast<size_t>(i) * kResetNoise + c];
+    reset_env(p, ne, u, r, &d, &f0, &f1);
+    p.progress[ne] = 0;                                                             // :678
+    p.reset[ne] = 0;                                                                // :679
+    float4* ob = reinterpret_cast<float4*>(p.obs_buf + ne * kObs);
+    for (int j = 0; j < kChunks; ++j) ob[j] = make_float4(0.f, 0.f, 0.f, 0.f);      // :680,682
+    p.speed_no_noise[ne] = 0.0f;                                                    // :688
+}
+
+// time-ordered copy of the clean ring: out[n, t, :] = ring[n, (tick + t) % 20, :] (the reference's buffer_obs)
+__global__ void paper_frames_kernel(const float* __restrict__ ring, const unsigned long long* __restrict__ tick, int n,
+                                    float* __restrict__ out) {
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;    // float4 chunk
+    if (i >= static_cast<long long>(n) * kChunks) return;
+    const long long e = i / kChunks;
+    const int k = static_cast<int>(i - e * kChunks);
+    const int first = static_cast<int>(*tick % kBuf);
+    int src = k + 2 * first;
+    if (src >= kChunks) src -= kChunks;
+    reinterpret_cast<float4*>(out)[i] = reinterpret_cast<const float4*>(ring)[e * kChunks + src];
+}
+
+__global__ void paper_philox_kernel(int n, unsigned long long seed, unsigned long long step, long long env_off,
+                                    const unsigned long long* __restrict__ epoch, float* sensor, float* reset_unit,
+                                    float* speed, float* yaw) {
+    step = effective_step(step, epoch);
+    const long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    Philox4 a = philox_env(seed, step, env_off + e, kStreamSensorA), b = philox_env(seed, step, env_off + e, kStreamSensorB);
+    if (sensor) {
+        float* o = sensor + e * kSensorNoise;
+        o[0] = u01(a.x); o[1] = u01(a.y); o[2] = u01(a.z); o[3] = u01(a.w); o[4] = u01(b.x); o[5] = u01(b.y);
+    }
+    if (speed) speed[e] = u01(b.z);
+    if (yaw) yaw[e] = u01(b.w);
+    if (reset_unit) {
+        Philox4 c = philox_env(seed, step, env_off + e, kStreamResetA), d = philox_env(seed, step, env_off + e, kStreamResetB);
+        float* o = reset_unit + e * kResetNoise;
+        o[0] = u01(c.x); o[1] = u01(c.y); o[2] = u01(c.z); o[3] = u01(c.w); o[4] = u01(d.x);
+    }
+}
+
+__global__ void paper_stats_finalize_kernel(double* __restrict__ partials, int rows, double* __restrict__ out, int accumulate) {
+    const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (k >= TK_STATS) return;
+    double acc = 0.0;
+    for (int r = lane; r < rows; r += 32) {
+        acc += partials[static_cast<size_t>(r) * TK_STATS + k];
+        partials[static_cast<size_t>(r) * TK_STATS + k] = 0.0;
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) out[k] = accumulate ? out[k] + acc : acc;
+}
+
+}  // namespace gpaper
+}  // namespace tk
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+using namespace tk;
+using namespace tk::gpaper;
+
+struct TkGogoroPaper {
+    TkGogoroPaperParams params;
+    TkGogoroPaperBuffers buf;
+    bool bound;
+    int tiles;
+    int finalize_grid;
+    double* partials;
+    double* diff_slots;
+    unsigned long long* tick;
+    unsigned int* done_ctr;
+    unsigned long long* step_dev;
+    bool ran;
+};
+
+static void pair_uniform(const double* in, float* out) { out[0] = static_cast<float>(in[0]); out[1] = static_cast<float>(in[1] - in[0]); }
+
+static void fill_kparams(const TkGogoroPaper* h, KParams& k) {
+    const TkGogoroPaperParams& P = h->params;
+    const TkGogoroPaperBuffers& B = h->buf;
+    k.root = B.root_tensor; k.state_dof = B.state_dof; k.obs_buf = B.obs_buf; k.clean_ring = B.buffer_obs_ring;
+    k.cmd_ring = B.command_ring; k.rew = B.rew_buf;
+    k.reset = reinterpret_cast<long long*>(B.reset_buf); k.progress = reinterpret_cast<long long*>(B.progress_buf);
+    k.timeout = B.timeout_buf; k.yaw_command = B.yaw_command; k.curent_command = B.curent_command;
+    k.curent_speed = B.curent_speed; k.steer_offsets = B.steer_offsets; k.curent_speed_offset = B.curent_speed_offset;
+    k.curent_imu_x_offset = B.curent_imu_x_offset; k.speed_no_noise = B.speed_no_noise;
+    k.steer_delay = reinterpret_cast<long long*>(B.steer_delay); k.command_history = B.command_history;
+    k.thormang_pose = B.thormang_pose; k.root_reset = B.root_reset_tensor; k.pos_cmd = B.dof_pos_command;
+    k.vel_cmd = B.dof_speed_command; k.ep_return = B.episode_return;
+    k.partials = h->partials; k.diff_slots = h->diff_slots; k.tick = h->tick; k.done_ctr = h->done_ctr;
+    k.reset_unit = nullptr; k.sensor_unit = nullptr; k.speed_unit = nullptr; k.yaw_unit = nullptr;
+    k.seed = 0; k.step = 0; k.step_dev = h->step_dev; k.env_off = 0; k.noise_mode = TK_NOISE_NONE;
+    k.n = P.num_envs; k.num_dof = P.num_dof; k.steering_joint = P.steering_joint; k.rear_wheel_joint = P.rear_wheel_joint;
+    k.max_episode_length = P.max_episode_length; k.speed_freq = P.speed_freq_update; k.yaw_freq = P.yaw_freq_update;
+    k.delay_w = P.delay_width; k.use_delay = P.use_steer_delay;
+    k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.command_ring, 16);
+    k.max_steering = P.max_steering; k.start_speed = P.start_speed;
+    k.delay_lo = static_cast<float>(P.command_delay[0]);
+    k.delay_span = static_cast<float>(P.command_delay[1] - P.command_delay[0]);
+    pair_uniform(P.imu_filter_noise, k.imu_filter); pair_uniform(P.imu_noise, k.imu);
+    pair_uniform(P.speed_sensor_noise, k.speed_sensor); pair_uniform(P.speed_sensor_offset, k.speed_off);
+    pair_uniform(P.imu_x_offset, k.imu_x); pair_uniform(P.steering_offset, k.steer_off);
+    pair_uniform(P.command_delay, k.delay); pair_uniform(P.speed_range, k.speed);
+}
+
+static int check_bound(const TkGogoroPaper* h) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_REQUIRE(h->bound, TK_ERR_UNBOUND, "tk_gogoro_paper_bind was not called");
+    return TK_OK;
+}
+
+static int set_noise(KParams& k, const TkGogoroPaperNoise* nz) {
+    TK_REQUIRE(nz != nullptr, TK_ERR_INVALID, "null noise descriptor");
+    TK_REQUIRE(nz->mode == TK_NOISE_NONE || nz->mode == TK_NOISE_DENSE || nz->mode == TK_NOISE_PHILOX, TK_ERR_INVALID,
+               "noise mode %d: this variant takes TK_NOISE_NONE, TK_NOISE_DENSE (row n = env n) or TK_NOISE_PHILOX", nz->mode);
+    k.noise_mode = nz->mode;
+    if (nz->mode == TK_NOISE_DENSE) {
+        k.reset_unit = nz->reset_unit; k.sensor_unit = nz->sensor_unit; k.speed_unit = nz->speed_unit; k.yaw_unit = nz->yaw_unit;
+    }
+    k.seed = nz->seed; k.step = nz->step; k.env_off = nz->env_id_offset;
+    return TK_OK;
+}
+
+extern "C" {
+
+int tk_gogoro_paper_create(const TkGogoroPaperParams* params, TkGogoroPaper** out) {
+    TK_REQUIRE(params && out, TK_ERR_INVALID, "null argument");
+    TK_REQUIRE(params->num_envs > 0, TK_ERR_INVALID, "num_envs must be positive (got %d)", params->num_envs);
+    TK_REQUIRE(params->num_dof > 0 && params->num_dof <= 4096, TK_ERR_INVALID, "bad num_dof %d", params->num_dof);
+    TK_REQUIRE(params->steering_joint >= 0 && params->steering_joint < params->num_dof && params->rear_wheel_joint >= 0 &&
+                   params->rear_wheel_joint < params->num_dof,
+               TK_ERR_INVALID, "joint index out of range");
+    TK_REQUIRE(params->buff_size == kBuf, TK_ERR_INVALID, "buff_size must be %d (got %d)", kBuf, params->buff_size);
+    TK_REQUIRE(params->delay_width >= 3 && params->delay_width <= kMaxDelayW, TK_ERR_INVALID,
+               "delay_width (command_delay[1]) must be in 3..%d (got %d)", kMaxDelayW, params->delay_width);
+    TK_REQUIRE(params->command_delay[1] != params->command_delay[0], TK_ERR_INVALID, "empty command_delay range");
+    TK_CUDA(cudaSetDevice(params->device));
+    TkGogoroPaper* h = new (std::nothrow) TkGogoroPaper();
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "out of host memory");
+    h->params = *params;
+    h->bound = false; h->ran = false;
+    h->tiles = (params->num_envs + kTile - 1) / kTile;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, params->device);
+    const int want = (params->num_envs + 255) / 256;
+    h->finalize_grid = want < sms * 4 ? want : sms * 4;
+    h->partials = nullptr; h->diff_slots = nullptr; h->tick = nullptr; h->done_ctr = nullptr; h->step_dev = nullptr;
+    cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
+    if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * kStatSlots);
+    if (e == cudaSuccess) e = cudaMalloc(&h->diff_slots, sizeof(double) * kStatSlots);
+    if (e == cudaSuccess) e = cudaMemset(h->diff_slots, 0, sizeof(double) * kStatSlots);
+    if (e == cudaSuccess) e = cudaMalloc(&h->tick, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(h->tick, 0, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&h->done_ctr, sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMemset(h->done_ctr, 0, sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMalloc(&h->step_dev, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(h->step_dev, 0, sizeof(unsigned long long));
+    if (e != cudaSuccess) {
+        cudaFree(h->partials); cudaFree(h->diff_slots); cudaFree(h->tick); cudaFree(h->done_ctr); cudaFree(h->step_dev);
+        delete h;
+        return cuda_fail(e, "tk_gogoro_paper_create");
+    }
+    *out = h;
+    return TK_OK;
+}
+
+int tk_gogoro_paper_destroy(TkGogoroPaper* h) {
+    if (!h) return TK_OK;
+    cudaSetDevice(h->params.device);
+    cudaFree(h->partials); cudaFree(h->diff_slots); cudaFree(h->tick); cudaFree(h->done_ctr); cudaFree(h->step_dev);
+    delete h;
+    return TK_OK;
+}
+
+int tk_gogoro_paper_bind(TkGogoroPaper* h, const TkGogoroPaperBuffers* b) {
+    TK_REQUIRE(h && b, TK_ERR_INVALID, "null argument");
+    const void* req[] = {b->root_tensor, b->state_dof, b->obs_buf, b->buffer_obs_ring, b->command_ring, b->rew_buf, b->reset_buf,
+                         b->progress_buf, b->yaw_command, b->curent_command, b->curent_speed, b->steer_offsets,
+                         b->curent_speed_offset, b->curent_imu_x_offset, b->speed_no_noise, b->steer_delay, b->command_history,
+                         b->thormang_pose, b->root_reset_tensor, b->dof_pos_command, b->dof_speed_command};
+    const char* names[] = {"root_tensor", "state_dof", "obs_buf", "buffer_obs_ring", "command_ring", "rew_buf", "reset_buf",
+                           "progress_buf", "yaw_command", "curent_command", "curent_speed", "steer_offsets",
+                           "curent_speed_offset", "curent_imu_x_offset", "speed_no_noise", "steer_delay", "command_history",
+                           "thormang_pose", "root_reset_tensor", "dof_pos_command", "dof_speed_command"};
+    for (unsigned i = 0; i < sizeof(req) / sizeof(req[0]); ++i) {
+        TK_REQUIRE(req[i] != nullptr, TK_ERR_UNBOUND, "buffer %s is NULL", names[i]);
+        TK_REQUIRE(aligned_to(req[i], 4), TK_ERR_ALIGN, "buffer %s is not 4-byte aligned", names[i]);
+    }
+    TK_REQUIRE(aligned_to(b->reset_buf, 8) && aligned_to(b->progress_buf, 8) && aligned_to(b->steer_delay, 8), TK_ERR_ALIGN,
+               "int64 buffers must be 8-byte aligned");
+    TK_REQUIRE(aligned_to(b->state_dof, 8), TK_ERR_ALIGN, "state_dof must be 8-byte aligned ((pos,vel) pairs)");
+    TK_REQUIRE(aligned_to(b->obs_buf, 16) && aligned_to(b->buffer_obs_ring, 16) && aligned_to(b->command_ring, 16), TK_ERR_ALIGN,
+               "obs_buf, buffer_obs_ring and command_ring must be 16-byte aligned (frames move as 128-bit chunks)");
+    h->buf = *b;
+    h->bound = true;
+    return TK_OK;
+}
+
+int tk_gogoro_paper_pre_physics(TkGogoroPaper* h, const float* actions, int32_t zero_fill, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(actions != nullptr, TK_ERR_INVALID, "null actions");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    KParams k; fill_kparams(h, k);
+    if (zero_fill) {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->params.device);
+        const long long want = (static_cast<long long>(k.n) * k.num_dof + 255) / 256;
+        const int zb = static_cast<int>(want < static_cast<long long>(sms) * 8 ? (want < 1 ? 1 : want) : static_cast<long long>(sms) * 8);
+        paper_pre_kernel<<<zb, 256, 0, st>>>(k, actions, 1);
+    }
+    paper_pre_kernel<<<(k.n + 255) / 256, 256, 0, st>>>(k, actions, 0);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_paper_compute_observations(TkGogoroPaper* h, float* obs_out, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(obs_out != nullptr, TK_ERR_INVALID, "null obs_out");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    paper_tile_kernel<2><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, obs_out);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_paper_compute_obs_rwd(TkGogoroPaper* h, const TkGogoroPaperNoise* noise, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    if (int rc = set_noise(k, noise)) return rc;
+    paper_tile_kernel<1><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, nullptr);
+    TK_CUDA(cudaGetLastError());
+    h->ran = true;
+    return TK_OK;
+}
+
+int tk_gogoro_paper_post_physics(TkGogoroPaper* h, const TkGogoroPaperNoise* noise, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    if (int rc = set_noise(k, noise)) return rc;
+    paper_tile_kernel<0><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, nullptr);
+    TK_CUDA(cudaGetLastError());
+    h->ran = true;
+    return TK_OK;
+}
+
+int tk_gogoro_paper_diff_sums(TkGogoroPaper* h, double* sums_out, void* stream) {
+    TK_REQUIRE(h && sums_out, TK_ERR_INVALID, "null argument");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    paper_diff_sums_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(h->diff_slots, h->params.num_envs, sums_out);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_paper_finalize_reward(TkGogoroPaper* h, const double* sums, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    paper_finalize_kernel<<<h->finalize_grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(k, sums);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_paper_reset_idx(TkGogoroPaper* h, const int64_t* env_ids, int32_t kcount, const float* unit, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    if (kcount == 0) return TK_OK;
+    TK_REQUIRE(kcount > 0 && env_ids && unit, TK_ERR_INVALID, "bad reset_idx arguments");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    paper_reset_idx_kernel<<<(kcount + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        k, reinterpret_cast<const long long*>(env_ids), kcount, unit);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_paper_clean_frames(TkGogoroPaper* h, float* frames_out, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(frames_out != nullptr && aligned_to(frames_out, 16), TK_ERR_INVALID, "frames_out must be a 16-byte aligned pointer");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    const long long chunks = static_cast<long long>(h->params.num_envs) * kChunks;
+    paper_frames_kernel<<<static_cast<int>((chunks + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        h->buf.buffer_obs_ring, h->tick, h->params.num_envs, frames_out);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_paper_advance_epoch(TkGogoroPaper* h, void* stream) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    advance_epoch_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(h->step_dev);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_paper_stats(TkGogoroPaper* h, double* stats_out, int32_t accumulate, void* stream) {
+    TK_REQUIRE(h && stats_out, TK_ERR_INVALID, "null argument");
+    TK_REQUIRE(h->ran, TK_ERR_INVALID, "tk_gogoro_paper_post_physics has not run yet");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    paper_stats_finalize_kernel<<<1, TK_STATS * 32, 0, static_cast<cudaStream_t>(stream)>>>(h->partials, kStatSlots, stats_out,
+                                                                                          accumulate);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_gogoro_paper_philox_noise(TkGogoroPaper* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* sensor_unit,
+                                 float* reset_unit, float* speed_unit, float* yaw_unit, void* stream) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    paper_philox_kernel<<<(h->params.num_envs + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        h->params.num_envs, seed, step, env_id_offset, h->step_dev, sensor_unit, reset_unit, speed_unit, yaw_unit);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+}  // extern "C"

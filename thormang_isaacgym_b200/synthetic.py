@@ -171,3 +171,48 @@ def gogoro_noise(n: int, seed: int, device="cpu") -> Dict[str, torch.Tensor]:
                reset_unit=reset_unit, speed_unit=torch.rand((n,), generator=g),
                yaw_unit=torch.rand((n,), generator=g))
     return {k: v.to(device) for k, v in out.items()}
+
+
+def gogoro_paper_state(n: int, seed: int = 1234, device="cpu", num_dof: int = GOGORO_DOF, max_steps: int = 3600,
+                       fallen_frac=None) -> Dict[str, torch.Tensor]:
+    """One post-physics snapshot for ``n`` scooters of the 8-channel x 20-frame variant: the
+    ``gogoro_state`` distributions plus the delay line, the per-env offsets and 20 frames of clean / noisy history
+    (time-ordered; channel 6 of the clean frames is the command history the reward differentiates)."""
+    base = gogoro_state(n, seed=seed, num_dof=num_dof)
+    g = _gen(seed + 4001)
+    if fallen_frac is not None:    # control the share of envs beyond the 0.38 rad fall threshold
+        roll = torch.where(torch.rand((n,), generator=g) < fallen_frac, _u(g, (n,), 0.4, 0.6), _n(g, (n,), 0.1).clamp(-0.3, 0.3))
+        yaw = _u(g, (n,), -math.pi, math.pi)
+        base["root_tensor"][:, 3:7] = _euler_to_quat(roll, _n(g, (n,), 0.03), yaw)
+    progress = torch.randint(0, max_steps, (n,), generator=g, dtype=torch.int64)
+    forced = torch.rand((n,), generator=g) < 0.02
+    ladder = torch.tensor([298, 299, 300, max_steps - 3, max_steps - 2, max_steps - 1], dtype=torch.int64)
+    progress = torch.where(forced, ladder[torch.arange(n) % 6], progress)
+    clean = torch.empty((n, 20, 8), dtype=torch.float32)
+    clean[:, :, 0] = _n(g, (n, 20), 0.15)
+    clean[:, :, 1] = _u(g, (n, 20), -math.pi, math.pi)
+    clean[:, :, 2:4] = _n(g, (n, 20, 2), 0.5)
+    clean[:, :, 4] = _u(g, (n, 20), 4.0, 13.0)
+    clean[:, :, 5] = _u(g, (n, 20), -math.pi, math.pi)
+    clean[:, :, 6] = _u(g, (n, 20), -0.5, 0.5)
+    delay = torch.randint(0, 5, (n,), generator=g, dtype=torch.int64)
+    clean[:, :, 7] = (delay.float() / 5.0).unsqueeze(1)
+    noisy = clean + _n(g, (n, 20, 8), 0.01)
+    noisy[:, :, 1] = 0.0
+    out = dict(
+        root_tensor=base["root_tensor"], state_dof=base["state_dof"], thormang_pose=base["thormang_pose"],
+        progress_buf=progress, reset_buf=base["reset_buf"], yaw_command=base["yaw_command"],
+        curent_command=base["curent_command"], curent_speed=_u(g, (n,), 5.0, 20.0), steer_offsets=_u(g, (n,), -0.05, 0.05),
+        curent_speed_offset=_u(g, (n,), -0.3, 0.3), curent_imu_x_offset=_u(g, (n,), -0.02, 0.02),
+        steer_delay=delay, command_history=_u(g, (n, 5), -0.5, 0.5),
+        buffer_obs=clean, buffer_obs_noisy=noisy, actions=_u(g, (n, 1), -1.5, 1.5),
+    )
+    return {k: v.to(device) for k, v in out.items()}
+
+
+def gogoro_paper_noise(n: int, seed: int, device="cpu") -> Dict[str, torch.Tensor]:
+    """U(0,1) draws of one step of the paper variant, addressed by env id: sensors [N,6], reset [N,5], speed [N], yaw [N]."""
+    g = _gen(seed + 1993)
+    out = dict(sensor_unit=torch.rand((n, 6), generator=g), reset_unit=torch.rand((n, 5), generator=g),
+               speed_unit=torch.rand((n,), generator=g), yaw_unit=torch.rand((n,), generator=g))
+    return {k: v.to(device) for k, v in out.items()}

@@ -28,7 +28,7 @@ def main():
     ap.add_argument("--sweep", default="", help="ENV_VAR=v1,v2,... : one line per value (developer knobs of the kernels)")
     args = ap.parse_args()
     peak, _ = B.measured_peak_gbs()
-    bpe = B.HUMANOID_BYTES_PER_ENV if args.task == "humanoid" else B.GOGORO_BYTES_PER_ENV
+    bpe = B.BYTES_PER_ENV[args.task]
     if args.kernel == "pre":
         pre_bytes = 252 if args.task == "humanoid" else 48
         for n in [int(x) for x in args.envs.split(",")]:
