@@ -23,6 +23,7 @@
 // this variant).
 #include "tk_common.cuh"
 
+#include <cstdlib>
 #include <new>
 
 namespace tk {
@@ -64,8 +65,8 @@ struct KParams {
     float* vel_cmd;
     float* ep_return;
     double* partials;              // [kStatSlots, TK_STATS]
-    double* diff_slots;            // [kStatSlots] sums of squared command differences of the current step
-    unsigned long long* tick;      // completed compute_obs_rwd calls (ring slot = tick % 20)
+    double* diff_slots;            // [2, kStatSlots] sums of squared command differences, set = tick & 1
+    unsigned long long* tick;      // [0] completed steps (ring slot = tick % 20); [1] tick of the fused kernel that ran last
     unsigned int* done_ctr;
     const float* reset_unit;
     const float* sensor_unit;
@@ -78,6 +79,8 @@ struct KParams {
     int n, num_dof, steering_joint, rear_wheel_joint, max_episode_length, speed_freq, yaw_freq;
     int delay_w, use_delay;
     int vec_ok;
+    int stagger_cycles, stagger_ctas, sm_count;   // first-wave stagger, see paper_tile_kernel
+    int fin_vec_ok;                // rew_buf / episode_return / reset_buf 16-byte aligned: 128-bit accesses in the finalize kernel
     float max_steering, start_speed;
     float delay_lo, delay_span;    // (float)command_delay[0], (float)(command_delay[1] - command_delay[0])
     // (float)lo, (float)(hi - lo) with the span formed in double (get_randoms :549-550)
@@ -171,15 +174,25 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
     const long long n = env0 + lane;
     const bool valid = lane < nt;
     const bool philox = p.noise_mode == TK_NOISE_PHILOX;
-    const unsigned long long step_now = philox ? effective_step(p.step, p.step_dev) : 0ull;
-    const int slot = static_cast<int>(*p.tick % kBuf);            // ring slot written by this step
-
     float* obs_tile = p.obs_buf + static_cast<size_t>(env0) * kObs;
     constexpr uint32_t kShiftBytes = (kTile * kObs - kCh) * 4;       // 20448: the tile minus its first frame
     const bool bulk = p.vec_ok && nt == kTile;
+    // programmatic dependent launch (no-ops without the launch attribute): this CTA may become resident while the
+    // previous kernel of the stream drains; nothing of global memory is touched before griddepcontrol.wait
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (bulk && lane == 0) mbar_init(&s.bar, 1);
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    // First-wave stagger (same finding as in the Humanoid kernel): the CTAs of the first wave start together, so every SM
+    // would run load-all / math-all / store-all in lockstep; resident slot s of the first wave waits s * stagger_cycles.
+    if (MODE == 0 && p.stagger_cycles > 0 && blockIdx.x < static_cast<unsigned>(p.stagger_ctas)) {
+        const long long until = clock64() + static_cast<long long>(blockIdx.x / p.sm_count) * p.stagger_cycles;
+        while (clock64() < until) __nanosleep(32);
+    }
+    const unsigned long long step_now = philox ? effective_step(p.step, p.step_dev) : 0ull;
+    const unsigned long long tick = p.tick[0];
+    const int slot = static_cast<int>(tick % kBuf);               // ring slot written by this step
     if (bulk) {
         if (lane == 0) {
-            mbar_init(&s.bar, 1);
             fence_proxy_async_smem();
             mbar_expect_tx(&s.bar, (kRoot + (MODE != 2 ? kBuf : 0)) * kTile * 4 + (MODE != 2 ? kShiftBytes : 0));
         }
@@ -356,7 +369,8 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
         st_yaw += __shfl_xor_sync(0xffffffffu, st_yaw, o);
     }
     const int row = blockIdx.x & (kStatSlots - 1);
-    if (lane == 0) atomicAdd(p.diff_slots + row, dsum);
+    if (lane == 0) atomicAdd(p.diff_slots + (tick & 1ull) * kStatSlots + row, dsum);
+    if (blockIdx.x == 0 && lane == 0) p.tick[1] = tick;           // tells the finalize kernel which accumulator set is live
     if (MODE == 0) {
         double* pr = p.partials + static_cast<size_t>(row) * TK_STATS;
         if (lane == 1) atomicAdd(pr + 1, static_cast<double>(__popc(m_reset)));
@@ -383,15 +397,43 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
     }
 }
 
-// reward7 (:747) folded in, clip (:760), fall penalty (:761), episode return; the last CTA clears the difference
-// accumulators and bumps the tick.  sums = {sum of squared differences, number of differences} all-reduced over the
-// ranks, or NULL: this GPU's accumulators and n * 19.
+// Second kernel of a step: reward7 (:747) folded in, clip (:760), fall penalty (:761), episode return.  Four envs per
+// thread (128-bit accesses), every per-env load is issued before the 256 accumulators are summed.  sums = {sum of
+// squared differences, number of differences} all-reduced over the ranks, or NULL: this GPU's accumulators and n * 19.
+// No atomics on the control path: the fused kernel publishes its tick in tick[1]; block 0 advances tick[0] (only the
+// NEXT fused kernel reads it) and clears the accumulator set that kernel will add to.
 __global__ void __launch_bounds__(256) paper_finalize_kernel(const __grid_constant__ KParams p, const double* __restrict__ sums) {
     __shared__ double red[8];
     __shared__ float add_s;
-    __shared__ bool last_s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    double v = (tid < kStatSlots) ? p.diff_slots[tid] : 0.0;
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const long long n0 = (static_cast<long long>(blockIdx.x) * blockDim.x + tid) * 4;
+    const bool any = n0 < p.n;
+    const bool full = n0 + 3 < p.n && p.fin_vec_ok;
+    float r[4] = {0.f, 0.f, 0.f, 0.f}, ret[4] = {0.f, 0.f, 0.f, 0.f};
+    long long rs[4] = {0, 0, 0, 0};
+    if (full) {
+        const float4 v = *reinterpret_cast<const float4*>(p.rew + n0);
+        r[0] = v.x; r[1] = v.y; r[2] = v.z; r[3] = v.w;
+        if (p.ep_return) {
+            const float4 e = *reinterpret_cast<const float4*>(p.ep_return + n0);
+            ret[0] = e.x; ret[1] = e.y; ret[2] = e.z; ret[3] = e.w;
+            const longlong2 a = *reinterpret_cast<const longlong2*>(p.reset + n0);
+            const longlong2 b = *reinterpret_cast<const longlong2*>(p.reset + n0 + 2);
+            rs[0] = a.x; rs[1] = a.y; rs[2] = b.x; rs[3] = b.y;
+        }
+    } else if (any) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (n0 + c < p.n) {
+                r[c] = p.rew[n0 + c];
+                if (p.ep_return) { ret[c] = p.ep_return[n0 + c]; rs[c] = p.reset[n0 + c]; }
+            }
+    }
+    const unsigned long long t = p.tick[1];
+    const double* slots = p.diff_slots + (t & 1ull) * kStatSlots;
+    double v = (tid < kStatSlots) ? slots[tid] : 0.0;
     v = warp_sum(v);
     if (lane == 0) red[warp] = v;
     __syncthreads();
@@ -408,38 +450,44 @@ __global__ void __launch_bounds__(256) paper_finalize_kernel(const __grid_consta
     __syncthreads();
     const float add = add_s;
     float st_rew = 0.f, st_ret = 0.f;
-    for (long long n = static_cast<long long>(blockIdx.x) * blockDim.x + tid; n < p.n; n += static_cast<long long>(gridDim.x) * blockDim.x) {
-        float r = p.rew[n];
-        if (r == -INFINITY) r = -1.0f;                                              // :761
-        else r = fmaxf(r + add, 0.0f);                                              // :753, :760
-        p.rew[n] = r;
-        st_rew += r;
-        if (p.ep_return) {
-            const float ret = p.ep_return[n] + r;
-            p.ep_return[n] = ret;
-            if (p.reset[n] != 0) st_ret += ret;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        if (n0 + c < p.n) {
+            r[c] = (r[c] == -INFINITY) ? -1.0f : fmaxf(r[c] + add, 0.0f);          // :761 | :753, :760
+            st_rew += r[c];
+            ret[c] += r[c];
+            if (rs[c] != 0) st_ret += ret[c];
         }
     }
-    double a = warp_sum(static_cast<double>(st_rew)), b = warp_sum(static_cast<double>(st_ret));
+    if (full) {
+        *reinterpret_cast<float4*>(p.rew + n0) = make_float4(r[0], r[1], r[2], r[3]);
+        if (p.ep_return) *reinterpret_cast<float4*>(p.ep_return + n0) = make_float4(ret[0], ret[1], ret[2], ret[3]);
+    } else if (any) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            if (n0 + c < p.n) {
+                p.rew[n0 + c] = r[c];
+                if (p.ep_return) p.ep_return[n0 + c] = ret[c];
+            }
+    }
+    const double a = warp_sum(static_cast<double>(st_rew)), b = warp_sum(static_cast<double>(st_ret));
     if (lane == 0) {
         double* pr = p.partials + static_cast<size_t>((blockIdx.x * 8 + warp) & (kStatSlots - 1)) * TK_STATS;
         atomicAdd(pr + 0, a);
-        atomicAdd(pr + 3, b);
+        if (p.ep_return) atomicAdd(pr + 3, b);
     }
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) last_s = atomicAdd(p.done_ctr, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (last_s) {
-        if (tid < kStatSlots) p.diff_slots[tid] = 0.0;
-        if (tid == 0) { *p.tick += 1ull; *p.done_ctr = 0u; }
+    if (blockIdx.x == 0) {
+        p.diff_slots[((t + 1ull) & 1ull) * kStatSlots + tid] = 0.0;   // blockDim.x == kStatSlots
+        if (tid == 0) p.tick[0] = t + 1ull;
     }
 }
 
 // {sum of squared command differences, number of differences} of the step just computed -> out[2] (all-reduce payload)
-__global__ void __launch_bounds__(256) paper_diff_sums_kernel(const double* __restrict__ slots, int n, double* __restrict__ out) {
+__global__ void __launch_bounds__(256) paper_diff_sums_kernel(const double* __restrict__ slots2, const unsigned long long* __restrict__ tick,
+                                                               int n, double* __restrict__ out) {
     __shared__ double red[8];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const double* slots = slots2 + (tick[1] & 1ull) * kStatSlots;
     double v = (tid < kStatSlots) ? slots[tid] : 0.0;
     v = warp_sum(v);
     if (lane == 0) red[warp] = v;
@@ -570,6 +618,8 @@ struct TkGogoroPaper {
     unsigned int* done_ctr;
     unsigned long long* step_dev;
     bool ran;
+    int stagger_cycles, stagger_slots, sm_count;
+    int use_pdl;      // programmatic dependent launch of the two step kernels (TK_GOGORO_PAPER_PDL=0 disables)
 };
 
 static void pair_uniform(const double* in, float* out) { out[0] = static_cast<float>(in[0]); out[1] = static_cast<float>(in[1] - in[0]); }
@@ -593,6 +643,8 @@ static void fill_kparams(const TkGogoroPaper* h, KParams& k) {
     k.max_episode_length = P.max_episode_length; k.speed_freq = P.speed_freq_update; k.yaw_freq = P.yaw_freq_update;
     k.delay_w = P.delay_width; k.use_delay = P.use_steer_delay;
     k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.command_ring, 16);
+    k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count;
+    k.fin_vec_ok = aligned_to(B.rew_buf, 16) && aligned_to(B.reset_buf, 16) && (!B.episode_return || aligned_to(B.episode_return, 16));
     k.max_steering = P.max_steering; k.start_speed = P.start_speed;
     k.delay_lo = static_cast<float>(P.command_delay[0]);
     k.delay_span = static_cast<float>(P.command_delay[1] - P.command_delay[0]);
@@ -638,18 +690,28 @@ int tk_gogoro_paper_create(const TkGogoroPaperParams* params, TkGogoroPaper** ou
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "out of host memory");
     h->params = *params;
     h->bound = false; h->ran = false;
+    h->use_pdl = 1;
+    if (const char* env = getenv("TK_GOGORO_PAPER_PDL")) h->use_pdl = atoi(env) != 0;
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, params->device);
-    const int want = (params->num_envs + 255) / 256;
-    h->finalize_grid = want < sms * 4 ? want : sms * 4;
+    h->sm_count = sms; h->stagger_cycles = 1000; h->stagger_slots = 8;   // 800..1200 cycles measured the same (-2.6 us at 65536..262144 envs)
+    {
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, paper_tile_kernel<0>, kTile, 0) == cudaSuccess && occ > 0) h->stagger_slots = occ;
+        else cudaGetLastError();
+    }
+    if (const char* env = getenv("TK_GOGORO_PAPER_STAGGER")) h->stagger_cycles = atoi(env);
+    if (const char* env = getenv("TK_GOGORO_PAPER_STAGGER_SLOTS")) h->stagger_slots = atoi(env);
+    (void)sms;
+    h->finalize_grid = (params->num_envs + 1023) / 1024;            // four envs per thread, 256 threads
     h->partials = nullptr; h->diff_slots = nullptr; h->tick = nullptr; h->done_ctr = nullptr; h->step_dev = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * kStatSlots);
-    if (e == cudaSuccess) e = cudaMalloc(&h->diff_slots, sizeof(double) * kStatSlots);
-    if (e == cudaSuccess) e = cudaMemset(h->diff_slots, 0, sizeof(double) * kStatSlots);
-    if (e == cudaSuccess) e = cudaMalloc(&h->tick, sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMemset(h->tick, 0, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&h->diff_slots, sizeof(double) * 2 * kStatSlots);
+    if (e == cudaSuccess) e = cudaMemset(h->diff_slots, 0, sizeof(double) * 2 * kStatSlots);
+    if (e == cudaSuccess) e = cudaMalloc(&h->tick, 2 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(h->tick, 0, 2 * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&h->done_ctr, sizeof(unsigned int));
     if (e == cudaSuccess) e = cudaMemset(h->done_ctr, 0, sizeof(unsigned int));
     if (e == cudaSuccess) e = cudaMalloc(&h->step_dev, sizeof(unsigned long long));
@@ -739,7 +801,19 @@ int tk_gogoro_paper_post_physics(TkGogoroPaper* h, const TkGogoroPaperNoise* noi
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
     if (int rc = set_noise(k, noise)) return rc;
-    paper_tile_kernel<0><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, nullptr);
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(h->tiles);
+        cfg.blockDim = dim3(kTile);
+        cfg.stream = static_cast<cudaStream_t>(stream);
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = h->use_pdl;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        float* no_out = nullptr;
+        cudaLaunchKernelEx(&cfg, paper_tile_kernel<0>, k, no_out);
+    }
     TK_CUDA(cudaGetLastError());
     h->ran = true;
     return TK_OK;
@@ -748,7 +822,7 @@ int tk_gogoro_paper_post_physics(TkGogoroPaper* h, const TkGogoroPaperNoise* noi
 int tk_gogoro_paper_diff_sums(TkGogoroPaper* h, double* sums_out, void* stream) {
     TK_REQUIRE(h && sums_out, TK_ERR_INVALID, "null argument");
     TK_CUDA(cudaSetDevice(h->params.device));
-    paper_diff_sums_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(h->diff_slots, h->params.num_envs, sums_out);
+    paper_diff_sums_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(h->diff_slots, h->tick, h->params.num_envs, sums_out);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
@@ -757,7 +831,18 @@ int tk_gogoro_paper_finalize_reward(TkGogoroPaper* h, const double* sums, void* 
     if (int rc = check_bound(h)) return rc;
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
-    paper_finalize_kernel<<<h->finalize_grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(k, sums);
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(h->finalize_grid);
+        cfg.blockDim = dim3(256);
+        cfg.stream = static_cast<cudaStream_t>(stream);
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = h->use_pdl;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        cudaLaunchKernelEx(&cfg, paper_finalize_kernel, k, sums);
+    }
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
