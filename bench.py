@@ -33,7 +33,10 @@ GOGORO_BYTES_PER_ENV = 172       # 192 B with supplied noise, 17
 # progress/reset 16, command ring 80, 19 noisy frames 608) + 705 B written (obs row 640, clean frame 32, command 4, reward 4,
 # reset/progress 16, timeout 1, speed 4, yaw command 4); finalize kernel 16 B read + 8 B written
 GOGORO_PAPER_BYTES_PER_ENV = 1509
-BYTES_PER_ENV = {"humanoid": HUMANOID_BYTES_PER_ENV, "gogoro": GOGORO_BYTES_PER_ENV, "gogoro_paper": GOGORO_PAPER_BYTES_PER_ENV}
+# SURVEY.md 8(f) N2 Anymal: reads root 52 + dof_state 96 + torques 48 + contact 156 + commands 12 + progress 8 +
+# reset 8; writes obs 244 + reward 4 + reset 8 + progress 8 + timeout 1
+ANYMAL_BYTES_PER_ENV = 645
+BYTES_PER_ENV = {"anymal": ANYMAL_BYTES_PER_ENV, "humanoid": HUMANOID_BYTES_PER_ENV, "gogoro": GOGORO_BYTES_PER_ENV, "gogoro_paper": GOGORO_PAPER_BYTES_PER_ENV}
 L2_BYTES = 126 * 1024 * 1024
 METRIC = "env-steps/sec (obs+reward+reset)"
 

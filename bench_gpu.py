@@ -85,8 +85,28 @@ def _make_gogoro_paper(n, seed, device, env_off=0):
     return env, st
 
 
-_MAKERS = {"humanoid": _make_humanoid, "gogoro": _make_gogoro, "gogoro_paper": _make_gogoro_paper}
-_LAUNCHES_PER_STEP = {"humanoid": 1, "gogoro": 1, "gogoro_paper": 2}   # the paper variant: fused kernel + reward finalize
+def _make_anymal(n, seed, device, env_off=0):
+    import torch
+    from thormang_isaacgym_b200 import config as tcfg
+    from thormang_isaacgym_b200 import synthetic as syn
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.anymal import Anymal
+    st = syn.anymal_state(n, seed=seed, contact_frac=0.01)
+    cfg = tcfg.anymal_cfg(n, seed=1234)
+    cfg["env"]["envIdOffset"] = env_off
+    cfg["env"]["resetOnInit"] = False
+    sim = FakeSim(n, 12, device, num_sensor_floats=0, dof_names=list(tcfg.ANYMAL_DOF_NAMES), num_bodies=13)
+    sim.load_state(st)
+    cfg["sim_backend"] = sim
+    dev_index = torch.device(device).index or 0
+    env = Anymal(cfg, device, f"cuda:{dev_index}", -1, True)
+    for name in ("commands", "actions", "progress_buf", "reset_buf"):
+        getattr(env, name).copy_(st[name].to(device))
+    return env, st
+
+
+_MAKERS = {"anymal": _make_anymal, "humanoid": _make_humanoid, "gogoro": _make_gogoro, "gogoro_paper": _make_gogoro_paper}
+_LAUNCHES_PER_STEP = {"anymal": 1, "humanoid": 1, "gogoro": 1, "gogoro_paper": 2}   # the paper variant: fused kernel + reward finalize
 
 
 def _rotating_sets(n, bytes_per_env):
@@ -361,6 +381,8 @@ def run_gpu_arm(args, rank, world):
                                     ("config3_gogoro_65536", "gogoro", 65536, False),
                                     ("config3_gogoro_65536_cuda_graph", "gogoro", 65536, True),
                                     ("gogoro_4194304", "gogoro", 4194304, False),
+                                    ("n2_anymal_65536", "anymal", 65536, False),
+                                    ("n2_anymal_1048576", "anymal", 1048576, False),
                                     ("n1_gogoro_paper_4096", "gogoro_paper", 4096, False),
                                     ("n1_gogoro_paper_65536", "gogoro_paper", 65536, False),
                                     ("n1_gogoro_paper_262144", "gogoro_paper", 262144, False),

@@ -424,6 +424,92 @@ int tk_gogoro_paper_stats(TkGogoroPaper* h, double* stats_out, int32_t accumulat
 int tk_gogoro_paper_philox_noise(TkGogoroPaper* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* sensor_unit,
                                  float* reset_unit, float* speed_unit, float* yaw_unit, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Anymal  (isaacgymenvs/tasks/anymal.py, cfg/task/Anymal.yaml) -- SURVEY.md 8(f) row N2: the canonical
+ * `targets = action_scale * actions + default_dof_pos` PD-target write (:229-232) and contact-force termination
+ * (:359-362).  This fork's copy: 61 observations via compute_anymal_observations_V2 (:399-431), 12 DOFs, 13 bodies.
+ * ------------------------------------------------------------------------------------------ */
+
+typedef struct TkAnymalParams {
+    int32_t device;
+    int32_t num_envs;
+    int32_t num_dof;                 /* 12 (:84) */
+    int32_t num_bodies;              /* 13: base + 4 x (HIP, THIGH, SHANK), :192,206-213 */
+    int32_t max_episode_length;      /* int(episodeLength_s / dt + 0.5), :92 */
+    int32_t base_index;              /* :215,226 */
+    int32_t num_knee;                /* len(knee_indices), :212-213 */
+    int32_t knee_indices[8];         /* rigid-body indices of the THIGH bodies, :223-224 */
+    int32_t reserved;
+    float dof_pos_scale;             /* :48 */
+    float dof_vel_scale;             /* :49 */
+    float action_scale;              /* :50 */
+    float clip_actions;              /* vec_task.py:108 */
+    /* python doubles: the reference multiplies the reward scales by dt in double (:96-97) before torch rounds to fp32 */
+    double dt;
+    double rew_lin_vel_xy;           /* :53 */
+    double rew_ang_vel_z;            /* :54 */
+    double rew_torque;               /* :55 */
+    double command_x_range[2];       /* :62 */
+    double command_y_range[2];       /* :63 */
+    double command_yaw_range[2];     /* :64 */
+    /* rows of replicated [N,*] tensors (identical for every env) */
+    float default_dof_pos[12];       /* :131-136 */
+    float base_init_state[13];       /* :72-78,140-141 */
+    float gravity_vec[3];            /* :142 */
+} TkAnymalParams;
+
+typedef struct TkAnymalBuffers {
+    float* root_states;              /* [N,13] simulator-owned */
+    float* dof_state;                /* [N*12,2] simulator-owned */
+    const float* torques;            /* [N,12] dof-force tensor, :125 */
+    const float* contact_forces;     /* [N,13,3] net contact forces, :124 */
+    float* commands;                 /* [N,3] :127 */
+    float* actions;                  /* [N,12] self.actions */
+    float* obs_buf;                  /* [N,61] */
+    float* rew_buf;                  /* [N] */
+    int64_t* reset_buf;              /* [N] */
+    int64_t* progress_buf;           /* [N] */
+    uint8_t* timeout_buf;            /* [N] bool, may be NULL */
+    float* episode_return;           /* [N], may be NULL */
+} TkAnymalBuffers;
+
+/* U(0,1) draws of reset_idx (:288-289,305-307), addressed by env id (TK_NOISE_DENSE), drawn in-kernel
+ * (TK_NOISE_PHILOX) or absent (TK_NOISE_NONE: 0.5): unit_pos [N,12], unit_vel [N,12], unit_cmd [N,3] = x, y, yaw. */
+typedef struct TkAnymalNoise {
+    int32_t mode;
+    int32_t reserved;
+    const float* unit_pos;
+    const float* unit_vel;
+    const float* unit_cmd;
+    uint64_t seed;
+    uint64_t step;
+    int64_t env_id_offset;
+} TkAnymalNoise;
+
+typedef struct TkAnymal TkAnymal;
+
+int tk_anymal_create(const TkAnymalParams* params, TkAnymal** out);
+int tk_anymal_destroy(TkAnymal* h);
+int tk_anymal_bind(TkAnymal* h, const TkAnymalBuffers* buffers);
+
+/* Anymal.pre_physics_step (:229-232) with the action clamp of vec_task.py:327 (when clip != 0): bound actions = clamp(in);
+ * targets_out[N,12] = action_scale * actions + default_dof_pos (the tensor handed to set_dof_position_target_tensor). */
+int tk_anymal_pre_physics(TkAnymal* h, const float* actions_in, float* targets_out, int32_t clip, void* stream);
+/* compute_observations (:262-283) = compute_anymal_observations_V2 (:399-431): writes obs_buf. */
+int tk_anymal_compute_observations(TkAnymal* h, void* stream);
+/* compute_reward (:244-259) = compute_anymal_reward (:323-372): writes rew_buf, reset_buf. */
+int tk_anymal_compute_reward(TkAnymal* h, void* stream);
+/* reset_idx (:285-311): env_ids[k] int64, unit_pos / unit_vel [k,12], unit_cmd [k,3]. */
+int tk_anymal_reset_idx(TkAnymal* h, const int64_t* env_ids, int32_t k, const float* unit_pos, const float* unit_vel,
+                        const float* unit_cmd, void* stream);
+/* post_physics_step (:234-242) + vec_task.py:345 as ONE fused kernel. */
+int tk_anymal_post_physics(TkAnymal* h, const TkAnymalNoise* noise, void* stream);
+int tk_anymal_advance_epoch(TkAnymal* h, void* stream);
+/* stats: sum reward, #reset, #timeout, sum episode_return / length of reset envs, sum lin-vel error, sum ang-vel error, N */
+int tk_anymal_stats(TkAnymal* h, double* stats_out, int32_t accumulate, void* stream);
+int tk_anymal_philox_noise(TkAnymal* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* unit_pos, float* unit_vel,
+                           float* unit_cmd, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -33,6 +33,11 @@ LIFT_TABLE: Dict[str, Iterable[str]] = {
         "compute_ant_reward",             # ant.py:318-364
         "compute_ant_observations",       # ant.py:367-408
     ),
+    "isaacgymenvs/tasks/anymal.py": (
+        "compute_anymal_reward",           # anymal.py:323-372
+        "compute_reward",                  # anymal.py:375-396
+        "compute_anymal_observations_V2",  # anymal.py:399-431
+    ),
     "isaacgymenvs/tasks/gogoro_new.py": (
         "compute_gogoro_reward",          # gogoro_new.py:645-684
         "shortest_angle_distance",        # gogoro_new.py:687-689
@@ -122,3 +127,7 @@ def gogoro() -> ModuleType:
 
 def gogoro_paper() -> ModuleType:
     return lift("isaacgymenvs/tasks/gogoro_realistic_turning_sim_paper.py")
+
+
+def anymal() -> ModuleType:
+    return lift("isaacgymenvs/tasks/anymal.py")

@@ -222,6 +222,38 @@ def gogoro_paper_golden(n_rand=96):
     print("gogoro_paper_jit.npz", n, "rows; resets", int(reset.sum()), "reward range", float(rew.min()), float(rew.max()))
 
 
+def anymal_golden(n_rand=96):
+    """anymal.py JIT functions: observations [N,61], reward / reset incl. contact norms around 1 N."""
+    from oracle import anymal_oracle as ao
+    ref = L.anymal()
+    st = syn.anymal_state(n_rand, seed=4246, contact_frac=0.3)
+    cf = st["contact_forces"]
+    one = float(np.float32(1.0))
+    up, dn = float(np.nextafter(np.float32(1.0), np.float32(2))), float(np.nextafter(np.float32(1.0), np.float32(0)))
+    for i, (body, val) in enumerate([(0, one), (0, up), (0, dn), (2, up), (5, one), (11, up), (3, 500.0), (12, 500.0)]):
+        cf[i] = 0.0
+        cf[i, body, 2] = val                                  # exactly at / one ulp around the threshold; feet do not count
+    progress = st["progress_buf"].clone()
+    progress[8:12] = torch.tensor([2497, 2498, 2499, 2500])
+    c = ao.AnymalConsts()
+    n = n_rand
+    d = 12
+    dof_pos = st["dof_state"].view(n, d, 2)[..., 0]
+    dof_vel = st["dof_state"].view(n, d, 2)[..., 1]
+    default = torch.tensor([0.03, 0.4, -0.8, 0.03, -0.4, 0.8, -0.03, 0.4, -0.8, -0.03, -0.4, 0.8]).repeat(n, 1)
+    grav = torch.tensor([0.0, 0.0, -1.0]).repeat(n, 1)
+    obs = ref.compute_anymal_observations_V2(st["root_states"], st["commands"], st["torques"], cf, dof_pos, default, dof_vel,
+                                             grav, st["actions"], 2.0, 0.25, 1.0, 0.05)
+    knee = torch.tensor([2, 5, 8, 11])
+    rew, reset = ref.compute_anymal_reward(st["root_states"], st["commands"], st["torques"], cf, knee, progress,
+                                           c.rew_scales(), 0, c.max_episode_length)
+    np.savez_compressed(os.path.join(HERE, "anymal_jit.npz"), **_np(dict(
+        root_states=st["root_states"], dof_state=st["dof_state"], torques=st["torques"], contact_forces=cf,
+        commands=st["commands"], actions=st["actions"], progress_buf=progress, default_dof_pos=default[0],
+        obs=obs, rew=rew, reset=reset.to(torch.int64))))
+    print("anymal_jit.npz", n, "rows; resets", int(reset.sum()), "reward max", float(rew.max()))
+
+
 def poselib_golden(n=256):
     path = os.path.join(L.REFERENCE_ROOT, "isaacgymenvs/tasks/amp/poselib/poselib/core/rotation3d.py")
     spec = importlib.util.spec_from_file_location("_ref_rotation3d", path)
@@ -245,4 +277,5 @@ if __name__ == "__main__":
     gogoro_golden()
     ant_golden()
     gogoro_paper_golden()
+    anymal_golden()
     poselib_golden()

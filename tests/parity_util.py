@@ -196,3 +196,31 @@ def make_gogoro_paper_pair(n, seed=1234, device="cuda:0", state=None, **env_over
     env.command_ring.copy_(state["buffer_obs"][:, :, 6].to(device))
     env.obs_buf.copy_(state["buffer_obs_noisy"].flatten(start_dim=1).to(device))
     return env, orc, state
+
+
+def make_anymal_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
+    """(cuda Anymal task, cpu AnymalOracle, state) from one synthetic snapshot."""
+    from oracle import anymal_oracle as ao
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.anymal import Anymal
+    state = state or syn.anymal_state(n, seed=seed)
+    cfg = tcfg.anymal_cfg(n, seed=seed)
+    cfg["env"].update(env_over)
+    cfg["env"]["resetOnInit"] = False
+    sim = FakeSim(n, 12, device, num_sensor_floats=0, dof_names=list(tcfg.ANYMAL_DOF_NAMES), num_bodies=13)
+    sim.load_state(state)
+    cfg["sim_backend"] = sim
+    env = Anymal(cfg, device, device, -1, True)
+    for name in ("commands", "actions", "progress_buf", "reset_buf"):
+        getattr(env, name).copy_(state[name].to(device))
+    consts = ao.AnymalConsts.from_cfg(cfg)
+    default_row = torch.tensor([cfg["env"]["defaultJointAngles"][k] for k in tcfg.ANYMAL_DOF_NAMES])
+    b = cfg["env"]["baseInitState"]
+    orc = ao.AnymalOracle(consts, state["root_states"].clone(), state["dof_state"].clone(), state["torques"].clone(),
+                          state["contact_forces"].clone(), default_row,
+                          torch.tensor(b["pos"] + b["rot"] + b["vLinear"] + b["vAngular"]))
+    orc.commands = state["commands"].clone()
+    orc.actions = state["actions"].clone()
+    orc.progress_buf = state["progress_buf"].clone()
+    orc.reset_buf = state["reset_buf"].clone()
+    return env, orc, state

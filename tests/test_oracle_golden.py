@@ -204,3 +204,25 @@ def test_gogoro_paper_oracle_step_semantics():
     assert int(orc.progress_buf[3]) == 0 and float(orc.yaw_command[3]) == 0.0
     want_speed = 5.0 + nz["speed_unit"][0] * (20.0 - 5.0)
     assert torch.equal(orc.curent_speed[5], want_speed)
+
+
+def test_anymal_golden(golden_dir):
+    """Anymal against anymal.py's own JIT functions; contact norms exactly at / 1 ulp around 1 N."""
+    from oracle import anymal_oracle as ao
+    g = _load(golden_dir, "anymal_jit.npz")
+    n, d = g["root_states"].shape[0], 12
+    c = ao.AnymalConsts()
+    dof_pos = g["dof_state"].view(n, d, 2)[..., 0]
+    dof_vel = g["dof_state"].view(n, d, 2)[..., 1]
+    obs = ao.anymal_observations(g["root_states"], g["commands"], g["torques"], g["contact_forces"], dof_pos,
+                                 g["default_dof_pos"].repeat(n, 1), dof_vel, torch.tensor([0.0, 0.0, -1.0]).repeat(n, 1),
+                                 1.0, 0.05)
+    torch.testing.assert_close(obs, g["obs"], rtol=RTOL, atol=ATOL)
+    rew, reset = ao.anymal_reward(g["root_states"], g["commands"], g["torques"], g["contact_forces"],
+                                  torch.tensor([2, 5, 8, 11]), g["progress_buf"], c.rew_scales(), 0, c.max_episode_length)
+    assert torch.equal(reset.to(torch.int64), g["reset"])
+    torch.testing.assert_close(rew, g["rew"], rtol=RTOL, atol=ATOL)
+    # rows 0..7: base at 1 N (no reset: strict >), base 1 ulp above (reset), 1 ulp below (no), thigh above (reset),
+    # thigh at 1 N (no), thigh above (reset), two foot contacts of 500 N (never a reset)
+    assert g["reset"][:8].tolist() == [0, 1, 0, 1, 0, 1, 0, 0]
+    assert g["reset"][8:12].tolist()[2:] == [1, 1] and c.max_episode_length == 2500

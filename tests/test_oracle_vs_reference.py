@@ -103,3 +103,34 @@ def test_gogoro_paper_bit_exact(n):
     assert torch.equal(rw[0], rg[0]) and torch.equal(rw[1], rg[1])
     a, b = syn._u(syn._gen(3), (256,), -7.0, 7.0), syn._u(syn._gen(4), (256,), -7.0, 7.0)
     assert torch.equal(ref.shortest_angle_distance(a, b), gp.shortest_angle_distance(a, b))
+
+
+@pytest.mark.parametrize("n", [1, 33, 4096])
+def test_anymal_bit_exact(n):
+    """anymal.py:323-431."""
+    from oracle import anymal_oracle as ao
+    ref = L.anymal()
+    st = syn.anymal_state(n, seed=700 + n, contact_frac=0.2)
+    c = ao.AnymalConsts()
+    d = 12
+    dof_pos = st["dof_state"].view(n, d, 2)[..., 0]
+    dof_vel = st["dof_state"].view(n, d, 2)[..., 1]
+    default = torch.tensor([0.03, 0.4, -0.8, 0.03, -0.4, 0.8, -0.03, 0.4, -0.8, -0.03, -0.4, 0.8]).repeat(n, 1)
+    grav = torch.tensor([0.0, 0.0, -1.0]).repeat(n, 1)
+    want = ref.compute_anymal_observations_V2(st["root_states"], st["commands"], st["torques"], st["contact_forces"], dof_pos,
+                                              default, dof_vel, grav, st["actions"], 2.0, 0.25, 1.0, 0.05)
+    got = ao.anymal_observations(st["root_states"], st["commands"], st["torques"], st["contact_forces"], dof_pos, default,
+                                 dof_vel, grav, 1.0, 0.05)
+    assert torch.equal(want, got)
+    knee = torch.tensor([2, 5, 8, 11])
+    rw = ref.compute_anymal_reward(st["root_states"], st["commands"], st["torques"], st["contact_forces"], knee,
+                                   st["progress_buf"], c.rew_scales(), 0, c.max_episode_length)
+    rg = ao.anymal_reward(st["root_states"], st["commands"], st["torques"], st["contact_forces"], knee, st["progress_buf"],
+                          c.rew_scales(), 0, c.max_episode_length)
+    assert torch.equal(rw[0], rg[0]) and torch.equal(rw[1], rg[1])
+    if n >= 33:
+        b, t = max(1, n // 64), 64 if n >= 64 else n
+        m = b * t
+        lin, ang = got[:m, 0:3].reshape(b, t, 3), got[:m, 3:6].reshape(b, t, 3)
+        tq, cmd = st["torques"][:m].reshape(b, t, 12), st["commands"][:m].reshape(b, t, 3)
+        assert torch.equal(ref.compute_reward(lin, ang, tq, cmd, c.rew_scales()), ao.anymal_wm_reward(lin, ang, tq, cmd, c.rew_scales()))

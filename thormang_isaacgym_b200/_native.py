@@ -93,6 +93,28 @@ class GogoroPaperNoise(C.Structure):
                 ("yaw_unit", _p), ("seed", _u64), ("step", _u64), ("env_id_offset", _i64)]
 
 
+class AnymalParams(C.Structure):
+    _fields_ = [
+        ("device", _i32), ("num_envs", _i32), ("num_dof", _i32), ("num_bodies", _i32), ("max_episode_length", _i32),
+        ("base_index", _i32), ("num_knee", _i32), ("knee_indices", _i32 * 8), ("reserved", _i32),
+        ("dof_pos_scale", _f), ("dof_vel_scale", _f), ("action_scale", _f), ("clip_actions", _f),
+        ("dt", _d), ("rew_lin_vel_xy", _d), ("rew_ang_vel_z", _d), ("rew_torque", _d),
+        ("command_x_range", _d * 2), ("command_y_range", _d * 2), ("command_yaw_range", _d * 2),
+        ("default_dof_pos", _f * 12), ("base_init_state", _f * 13), ("gravity_vec", _f * 3),
+    ]
+
+
+class AnymalBuffers(C.Structure):
+    _fields_ = [(name, _p) for name in (
+        "root_states", "dof_state", "torques", "contact_forces", "commands", "actions", "obs_buf", "rew_buf",
+        "reset_buf", "progress_buf", "timeout_buf", "episode_return")]
+
+
+class AnymalNoise(C.Structure):
+    _fields_ = [("mode", _i32), ("reserved", _i32), ("unit_pos", _p), ("unit_vel", _p), ("unit_cmd", _p),
+                ("seed", _u64), ("step", _u64), ("env_id_offset", _i64)]
+
+
 # every symbol include/thormang_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "tk_last_error": (C.c_char_p, []),
@@ -137,6 +159,17 @@ SYMBOLS = {
     "tk_gogoro_paper_advance_epoch": (C.c_int, [_p, _p]),
     "tk_gogoro_paper_stats": (C.c_int, [_p, _p, _i32, _p]),
     "tk_gogoro_paper_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p, _p, _p, _p]),
+    "tk_anymal_create": (C.c_int, [C.POINTER(AnymalParams), C.POINTER(_p)]),
+    "tk_anymal_destroy": (C.c_int, [_p]),
+    "tk_anymal_bind": (C.c_int, [_p, C.POINTER(AnymalBuffers)]),
+    "tk_anymal_pre_physics": (C.c_int, [_p, _p, _p, _i32, _p]),
+    "tk_anymal_compute_observations": (C.c_int, [_p, _p]),
+    "tk_anymal_compute_reward": (C.c_int, [_p, _p]),
+    "tk_anymal_reset_idx": (C.c_int, [_p, _p, _i32, _p, _p, _p, _p]),
+    "tk_anymal_post_physics": (C.c_int, [_p, C.POINTER(AnymalNoise), _p]),
+    "tk_anymal_advance_epoch": (C.c_int, [_p, _p]),
+    "tk_anymal_stats": (C.c_int, [_p, _p, _i32, _p]),
+    "tk_anymal_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p, _p, _p]),
 }
 
 _lib = None

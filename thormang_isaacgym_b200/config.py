@@ -93,3 +93,33 @@ def gogoro_paper_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
         "joints_pos": dict(GOGORO_JOINTS_POS),
         "task": {"randomize": False, "randomization_params": {}},
     })
+
+
+ANYMAL_DOF_NAMES = ["LF_HAA", "LF_HFE", "LF_KFE", "LH_HAA", "LH_HFE", "LH_KFE", "RF_HAA", "RF_HFE", "RF_KFE",
+                    "RH_HAA", "RH_HFE", "RH_KFE"]      # DOF order of anymal_c/urdf/anymal.urdf
+
+
+def anymal_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
+    """cfg/task/Anymal.yaml:6-64,80-84."""
+    return copy.deepcopy({
+        "name": "Anymal",
+        "physics_engine": "physx",
+        "seed": seed,
+        "env": {
+            "numEnvs": num_envs, "envSpacing": 4.0, "clipObservations": 5.0, "clipActions": 1.0,
+            "plane": {"staticFriction": 1.0, "dynamicFriction": 1.0, "restitution": 0.0},
+            "baseInitState": {"pos": [0.0, 0.0, 0.62], "rot": [0.0, 0.0, 0.0, 1.0], "vLinear": [0.0, 0.0, 0.0],
+                              "vAngular": [0.0, 0.0, 0.0]},
+            "randomCommandVelocityRanges": {"linear_x": [-2.0, 2.0], "linear_y": [-1.0, 1.0], "yaw": [-1.0, 1.0]},
+            "control": {"stiffness": 85.0, "damping": 2.0, "actionScale": 0.5, "controlFrequencyInv": 1},
+            "defaultJointAngles": {"LF_HAA": 0.03, "LH_HAA": 0.03, "RF_HAA": -0.03, "RH_HAA": -0.03,
+                                   "LF_HFE": 0.4, "LH_HFE": -0.4, "RF_HFE": 0.4, "RH_HFE": -0.4,
+                                   "LF_KFE": -0.8, "LH_KFE": 0.8, "RF_KFE": -0.8, "RH_KFE": 0.8},
+            "urdfAsset": {"collapseFixedJoints": True, "fixBaseLink": False, "defaultDofDriveMode": 4},
+            "learn": {"linearVelocityXYRewardScale": 1.0, "angularVelocityZRewardScale": 0.5,
+                      "torqueRewardScale": -0.000025, "linearVelocityScale": 2.0, "angularVelocityScale": 0.25,
+                      "dofPositionScale": 1.0, "dofVelocityScale": 0.05, "episodeLength_s": 50},
+        },
+        "sim": {"dt": 0.02, "substeps": 2, "up_axis": "z", "use_gpu_pipeline": True, "gravity": [0.0, 0.0, -9.81]},
+        "task": {"randomize": False, "randomization_params": {}},
+    })

@@ -25,9 +25,12 @@ import torch
 class FakeSim:
     def __init__(self, num_envs: int, num_dof: int, device, num_sensor_floats: int = 12,
                  dof_names: Optional[List[str]] = None, asset: Optional[Dict[str, torch.Tensor]] = None,
-                 physics: Optional[Callable[["FakeSim"], None]] = None, slab: bool = False):
+                 physics: Optional[Callable[["FakeSim"], None]] = None, slab: bool = False, num_bodies: int = 0):
         self.num_envs, self.num_dof, self.device = num_envs, num_dof, torch.device(device)
         f = dict(dtype=torch.float32, device=self.device)
+        # net contact forces [N*bodies, 3] (anymal.py:113,124), only for tasks that read them
+        self.num_bodies = num_bodies
+        self.net_contact_force = torch.zeros((num_envs * num_bodies, 3), **f) if num_bodies else None
         self.state_slab = None
         self.actions_view = None
         if slab:
@@ -66,6 +69,8 @@ class FakeSim:
     def acquire_dof_state_tensor(self): return self.dof_state
     def acquire_dof_force_tensor(self): return self.dof_force
     def acquire_force_sensor_tensor(self): return self.force_sensor
+    def acquire_net_contact_force_tensor(self): return self.net_contact_force
+    def refresh_net_contact_force_tensor(self): return True
     def refresh_actor_root_state_tensor(self): return True
     def refresh_dof_state_tensor(self): return True
     def refresh_dof_force_tensor(self): return True
@@ -97,7 +102,9 @@ class FakeSim:
     def load_state(self, state: Dict[str, torch.Tensor]):
         """Copy a synthetic snapshot (thormang_isaacgym_b200.synthetic) into the sim buffers."""
         alias = {"root_states": "root_states", "root_tensor": "root_states", "dof_state": "dof_state",
-                 "state_dof": "dof_state", "dof_force": "dof_force", "sensors": "force_sensor"}
+                 "state_dof": "dof_state", "dof_force": "dof_force", "sensors": "force_sensor",
+                 "torques": "dof_force", "contact_forces": "net_contact_force"}
         for key, attr in alias.items():
             if key in state:
-                getattr(self, attr).copy_(state[key].to(self.device))
+                dst = getattr(self, attr)
+                dst.copy_(state[key].to(self.device).reshape(dst.shape))

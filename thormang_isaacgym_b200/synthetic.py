@@ -216,3 +216,45 @@ def gogoro_paper_noise(n: int, seed: int, device="cpu") -> Dict[str, torch.Tenso
     out = dict(sensor_unit=torch.rand((n, 6), generator=g), reset_unit=torch.rand((n, 5), generator=g),
                speed_unit=torch.rand((n,), generator=g), yaw_unit=torch.rand((n,), generator=g))
     return {k: v.to(device) for k, v in out.items()}
+
+
+def anymal_state(n: int, seed: int = 1234, device="cpu", contact_frac: float = 0.02) -> Dict[str, torch.Tensor]:
+    """One post-physics snapshot for ``n`` ANYmals: 12 DOFs, 13 bodies.  ~``contact_frac`` of the envs
+    carry a base / thigh contact force above the 1 N termination threshold; feet (shank) contacts are common."""
+    g = _gen(seed)
+    root = torch.empty((n, 13), dtype=torch.float32)
+    root[:, 0:2] = _u(g, (n, 2), -20.0, 20.0)
+    root[:, 2] = _u(g, (n,), 0.4, 0.7)
+    root[:, 3:7] = _euler_to_quat(_n(g, (n,), 0.1), _n(g, (n,), 0.1), _u(g, (n,), -math.pi, math.pi))
+    root[:, 7:10] = _n(g, (n, 3), 1.0)
+    root[:, 10:13] = _n(g, (n, 3), 0.7)
+    contact = torch.zeros((n, 13, 3), dtype=torch.float32)
+    feet = [3, 6, 9, 12]
+    contact[:, feet, 2] = torch.where(torch.rand((n, 4), generator=g) < 0.6, _u(g, (n, 4), 20.0, 200.0), torch.zeros(n, 4))
+    contact[:, feet, 0:2] = _n(g, (n, 4, 2), 5.0) * (contact[:, feet, 2:3] > 0)
+    bad_body = torch.tensor([0, 2, 5, 8, 11])[torch.randint(0, 5, (n,), generator=g)]
+    hit = torch.rand((n,), generator=g) < contact_frac
+    mag = torch.where(torch.rand((n,), generator=g) < 0.5, _u(g, (n,), 0.5, 1.5), _u(g, (n,), 1.5, 80.0))   # both sides of 1 N
+    dirv = torch.randn((n, 3), generator=g)
+    dirv = dirv / dirv.norm(dim=-1, keepdim=True)
+    idx = torch.nonzero(hit).flatten()
+    contact[idx, bad_body[idx]] = dirv[idx] * mag[idx].unsqueeze(-1)
+    progress = torch.randint(0, 2500, (n,), generator=g, dtype=torch.int64)
+    forced = torch.rand((n,), generator=g) < 0.02
+    ladder = torch.tensor([2497, 2498, 2499, 2500], dtype=torch.int64)
+    progress = torch.where(forced, ladder[torch.arange(n) % 4], progress)
+    out = dict(
+        root_states=root, dof_state=torch.stack([_n(g, (n * 12,), 0.5), _n(g, (n * 12,), 3.0)], dim=-1),
+        torques=_n(g, (n, 12), 20.0), contact_forces=contact,
+        commands=torch.stack([_u(g, (n,), -2.0, 2.0), _u(g, (n,), -1.0, 1.0), _u(g, (n,), -1.0, 1.0)], dim=-1),
+        actions=_u(g, (n, 12), -1.5, 1.5), progress_buf=progress,
+        reset_buf=(torch.rand((n,), generator=g) < 0.01).to(torch.int64),
+    )
+    return {k: v.to(device) for k, v in out.items()}
+
+
+def anymal_reset_noise(n: int, seed: int, device="cpu"):
+    """U(0,1) draws of Anymal.reset_idx addressed by env id: positions [N,12], velocities [N,12], commands [N,3]."""
+    g = _gen(seed + 313)
+    return tuple(t.to(device) for t in (torch.rand((n, 12), generator=g), torch.rand((n, 12), generator=g),
+                                        torch.rand((n, 3), generator=g)))

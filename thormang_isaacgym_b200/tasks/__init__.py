@@ -1,5 +1,6 @@
 """Task registry, same shape as ``isaacgymenvs/tasks/__init__.py:54-78`` for the hot-path tasks."""
 from .ant import Ant
+from .anymal import Anymal
 from .gogoro_new import Gogoro
 from .gogoro_realistic_turning_sim_paper import Gogoro as GogoroPaper
 from .humanoid import Humanoid
@@ -7,6 +8,7 @@ from .humanoid import Humanoid
 isaacgym_task_map = {
     "Humanoid": Humanoid,
     "Ant": Ant,
+    "Anymal": Anymal,
     "Gogoro": Gogoro,
     "GogoroPaper": GogoroPaper,   # gogoro_realistic_turning_sim_paper.py::Gogoro (unregistered in the reference)
 }
