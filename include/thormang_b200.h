@@ -510,6 +510,40 @@ int tk_anymal_stats(TkAnymal* h, double* stats_out, int32_t accumulate, void* st
 int tk_anymal_philox_noise(TkAnymal* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* unit_pos, float* unit_vel,
                            float* unit_cmd, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * VecTask.step prologue / epilogue (isaacgymenvs/tasks/base/vec_task.py:323-327,347-353) and the non-physical
+ * domain-randomisation lambdas of apply_randomizations (:576-646) -- SURVEY.md 8(f) row N4.
+ * ------------------------------------------------------------------------------------------ */
+
+/* One entry of dr_randomizations['observations' | 'actions'] AFTER the schedule scaling of :592-634 (host arithmetic).
+ * gaussian: range = [mu, var], range_correlated = [mu_corr, var_corr] (:591-592);
+ * uniform:  range = [lo, hi],  range_correlated = [lo_corr, hi_corr]  (:624-625). */
+typedef struct TkNoiseLambda {
+    int32_t distribution;            /* 0 none, 1 gaussian, 2 uniform */
+    int32_t operation;               /* 0 additive (operator.add), 1 scaling (operator.mul), :582 */
+    double range[2];
+    double range_correlated[2];
+} TkNoiseLambda;
+
+/* ONE pass over a tensor of `count` floats: x' = op(x, (corr * a_corr + b_corr) + unit * a + b)  (noise_lambda, :612-620 /
+ * :635-641), y = clamp(x', +-clip).  noisy_out (may alias `in`: what `self.obs_buf = noise_lambda(self.obs_buf)` rebinds
+ * to) and clamped_out (obs_dict["obs"] / action_tensor; e.g. slot t of a [horizon, N, obs] rollout buffer) may each be
+ * NULL.  corr: the persistent N(0,1) draw params['corr'] or NULL (= 0).  unit: N(0,1) / U(0,1) draws of this call, or NULL:
+ * in-kernel Philox keyed by (seed, step, (elem_offset + i) / 4); elem_offset (a multiple of 4) is the global index of
+ * element 0 in range-sharded runs.  lambda NULL or distribution 0: clamp copy only.  clip = INFINITY: no clamp. */
+int tk_step_noise_clamp(const float* in, int64_t count, const TkNoiseLambda* lambda, const float* corr, const float* unit,
+                        uint64_t seed, uint64_t step, int64_t elem_offset, float clip, float* noisy_out, float* clamped_out,
+                        void* stream);
+/* The unit draws tk_step_noise_clamp makes in Philox mode (parity checks). */
+int tk_step_noise_units(int64_t count, int32_t distribution, uint64_t seed, uint64_t step, int64_t elem_offset, float* unit_out,
+                        void* stream);
+
+/* Second destination of the Humanoid / Ant obs tile: every tk_humanoid_post_physics / _compute_observations after this call
+ * also stores the [N,obs] rows at obs_copy (16-byte aligned; NULL switches it off) straight from the kernel's shared-memory
+ * tile -- slot t of an rl_games [horizon, N, obs] rollout buffer when clipObservations is inf and no observation noise is
+ * configured (Humanoid.yaml), which removes the clamp copy of vec_task.py:353 and the rollout copy after it. */
+int tk_humanoid_set_obs_copy(TkHumanoid* h, float* obs_copy);
+
 #ifdef __cplusplus
 }
 #endif

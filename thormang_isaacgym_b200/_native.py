@@ -115,6 +115,10 @@ class AnymalNoise(C.Structure):
                 ("seed", _u64), ("step", _u64), ("env_id_offset", _i64)]
 
 
+class NoiseLambda(C.Structure):
+    _fields_ = [("distribution", _i32), ("operation", _i32), ("range", _d * 2), ("range_correlated", _d * 2)]
+
+
 # every symbol include/thormang_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "tk_last_error": (C.c_char_p, []),
@@ -170,6 +174,9 @@ SYMBOLS = {
     "tk_anymal_advance_epoch": (C.c_int, [_p, _p]),
     "tk_anymal_stats": (C.c_int, [_p, _p, _i32, _p]),
     "tk_anymal_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p, _p, _p]),
+    "tk_step_noise_clamp": (C.c_int, [_p, _i64, C.POINTER(NoiseLambda), _p, _p, _u64, _u64, _i64, _f, _p, _p, _p]),
+    "tk_step_noise_units": (C.c_int, [_i64, _i32, _u64, _u64, _i64, _p, _p]),
+    "tk_humanoid_set_obs_copy": (C.c_int, [_p, _p]),
 }
 
 _lib = None

@@ -58,6 +58,7 @@ struct KParams {
     const float* sensors;
     float* actions;
     float* obs;
+    float* obs2;                // optional second destination of the obs tile (tk_humanoid_set_obs_copy)
     float* rew;
     long long* reset;
     long long* progress;
@@ -429,6 +430,7 @@ struct TkHumanoid {
     int* tile_counts;     // [tiles]
     int* tile_base;       // [tiles]
     int last_grid;
+    float* obs_copy;      // tk_humanoid_set_obs_copy
     int use_pdl;          // programmatic dependent launch (TK_HUMANOID_PDL=0 disables)
     int stagger_cycles;   // TK_HUMANOID_STAGGER (SM cycles per resident slot), see the kernel
     int stagger_slots;    // TK_HUMANOID_STAGGER_SLOTS
@@ -464,7 +466,7 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     const TkHumanoidParams& P = h->params;
     const TkHumanoidBuffers& B = h->buf;
     k.root = B.root_states; k.dof_state = B.dof_state; k.dof_force = B.dof_force; k.sensors = B.sensors;
-    k.actions = B.actions; k.obs = B.obs_buf; k.rew = B.rew_buf;
+    k.actions = B.actions; k.obs = B.obs_buf; k.obs2 = h->obs_copy; k.rew = B.rew_buf;
     k.reset = reinterpret_cast<long long*>(B.reset_buf); k.progress = reinterpret_cast<long long*>(B.progress_buf);
     k.timeout = B.timeout_buf; k.randomize = reinterpret_cast<long long*>(B.randomize_buf);
     k.pot = B.potentials; k.prev_pot = B.prev_potentials; k.up_vec = B.up_vec; k.heading_vec = B.heading_vec;
@@ -515,6 +517,7 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     h->bound = false;
     h->dbg_ts = nullptr;
     h->use_pdl = 1;
+    h->obs_copy = nullptr;
     if (const char* env = getenv("TK_HUMANOID_PDL")) h->use_pdl = atoi(env) != 0;
     // First-wave stagger (see the kernel): 500 SM cycles per resident slot; anything in 400..700 measured the same
     // (B200: 16.5 -> 14.0 us at 65536 envs, 25.4 -> 23.0 us at 131072).  The slot count is the kernel's real occupancy.
@@ -714,6 +717,13 @@ int tk_humanoid_philox_noise(TkHumanoid* h, uint64_t seed, uint64_t step, int64_
 int tk_debug_humanoid_timeline(TkHumanoid* h, long long* device_buffer) {
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
     h->dbg_ts = device_buffer;
+    return TK_OK;
+}
+
+int tk_humanoid_set_obs_copy(TkHumanoid* h, float* obs_copy) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_REQUIRE(aligned_to(obs_copy, 16), TK_ERR_ALIGN, "obs_copy must be 16-byte aligned");
+    h->obs_copy = obs_copy;
     return TK_OK;
 }
 

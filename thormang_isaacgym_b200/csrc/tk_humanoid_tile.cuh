@@ -372,10 +372,13 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     if (bulk) {
         if (lane == 0) {
             bulk_store(dst, buf, WT::kOut * 4);
+            // second destination of the same tile (tk_humanoid_set_obs_copy): e.g. slot t of a [horizon, N, obs] rollout buffer
+            if (p.obs2) bulk_store(p.obs2 + static_cast<size_t>(env0) * OBS, buf, WT::kOut * 4);
             bulk_commit();
         }
     } else {
         warp_copy(dst, buf, nt * OBS, lane);
+        if (p.obs2) warp_copy(p.obs2 + static_cast<size_t>(env0) * OBS, buf, nt * OBS, lane);
     }
 
     // ---- statistics partials: one row per tile, fixed reduction order -> deterministic

@@ -11,8 +11,9 @@ randomisation through PhysX property setters (:538-768).  The simulator is injec
 (``cfg["sim_backend"]``) or replaced by the fake-sim shim.
 """
 import abc
+import ctypes
 from dataclasses import dataclass
-from typing import Any, Dict, Tuple
+from typing import Any, Dict, Optional, Tuple
 
 import numpy as np
 import torch
@@ -103,6 +104,8 @@ class VecTask(Env):
         self.allocate_buffers()
         self.obs_dict = {}
         self._clip_in_kernel = False
+        self._rollout, self._rollout_t, self._slot_filled_by_kernel = None, 0, False
+        self.first_randomization, self.last_step, self.last_rand_step = True, -1, -1
 
     def allocate_buffers(self):
         """vec_task.py:254-277: same names, shapes, dtypes and initial values."""
@@ -144,30 +147,153 @@ class VecTask(Env):
     @abc.abstractmethod
     def post_physics_step(self): ...
 
+    # ---- step prologue / epilogue as one fused kernel each -----------------------------------------
+    def _noise_clamp(self, tensor, which, clip, noisy_out, clamped_out, unit=None):
+        """``clamp(noise_lambda(tensor), +-clip)`` of vec_task.py:323-327 / :347-353 in ONE pass (csrc/tk_epilogue.cu).
+        ``which``: 'observations' | 'actions'.  ``unit``: the draws of this call (tests); in-kernel Philox otherwise."""
+        from ... import _native as nat
+        params = self.dr_randomizations.get(which)
+        lam, corr = None, None
+        if params:
+            lam = params["_lambda"]
+            corr = params.get("corr")
+            if corr is None:                       # drawn on first use and kept until the next randomisation (:613-616)
+                corr = torch.randn_like(tensor)
+                params["corr"] = corr
+        self._epilogue_calls = getattr(self, "_epilogue_calls", 0) + 1
+        nat.check(nat.lib().tk_step_noise_clamp(
+            nat.ptr(tensor), tensor.numel(), None if lam is None else ctypes.byref(lam), nat.ptr(corr), nat.ptr(unit),
+            int(self.cfg.get("seed", 0)) & 0xFFFFFFFFFFFFFFFF, (self._epilogue_calls << 1) | (which == "actions"),
+            int(self.cfg["env"].get("envIdOffset", 0)) * tensor.shape[-1], float(clip), nat.ptr(noisy_out),
+            nat.ptr(clamped_out), nat.current_stream_ptr(self.device)), "tk_step_noise_clamp")
+
+    def set_rollout_buffer(self, buf: Optional[torch.Tensor]):
+        """``buf`` [horizon, N, num_obs] on the sim device: every ``step`` writes ``obs_dict["obs"]`` straight into slot
+        ``t`` (t = 0, 1, ... wrapping at the horizon) -- rl_games' rollout tensor filled by the kernels instead of a clamp
+        copy (vec_task.py:353) plus a copy into the experience buffer.  None switches it off."""
+        if buf is not None and (buf.dim() != 3 or buf.shape[1:] != (self.num_envs, self.num_obs) or not buf.is_contiguous()
+                                or buf.dtype != torch.float or str(buf.device) != str(self.device)):
+            raise ValueError(f"rollout buffer must be a contiguous float [horizon, {self.num_envs}, {self.num_obs}] tensor on {self.device}")
+        self._rollout, self._rollout_t = buf, 0
+
+    def _obs_copy_hook(self, dst):
+        """Tasks whose fused kernel can store its obs tile to a second destination override this and return True."""
+        return False
+
     def _clipped_obs(self):
-        # clamp(+-inf) is the identity: skip the extra full-obs copy the reference makes (vec_task.py:353)
-        if np.isinf(self.clip_obs):
+        """vec_task.py:347-353: observation noise lambda + clamp (+ the rollout slot) in one pass."""
+        rollout = getattr(self, "_rollout", None)
+        noisy = bool(self.dr_randomizations.get("observations"))
+        if rollout is not None:
+            slot = rollout[self._rollout_t]
+            if not self._slot_filled_by_kernel:
+                self._noise_clamp(self.obs_buf, "observations", self.clip_obs, self.obs_buf if noisy else None, slot)
+            self._rollout_t = (self._rollout_t + 1) % rollout.shape[0]
+            return slot.to(self.rl_device)
+        if not noisy and np.isinf(self.clip_obs):
+            # clamp(+-inf) is the identity: skip the extra full-obs copy the reference makes (vec_task.py:353)
             return self.obs_buf.to(self.rl_device)
-        return torch.clamp(self.obs_buf, -self.clip_obs, self.clip_obs).to(self.rl_device)
+        out = torch.empty_like(self.obs_buf)
+        self._noise_clamp(self.obs_buf, "observations", self.clip_obs, self.obs_buf if noisy else None, out)
+        return out.to(self.rl_device)
 
     def step(self, actions: torch.Tensor):
-        """vec_task.py:313-359 without the DR lambdas and render()."""
-        if self.fuses_action_clip:
+        """vec_task.py:313-359 without render(); the DR lambdas and clamps run as fused kernels."""
+        if self.dr_randomizations.get("actions"):                                    # vec_task.py:323-327
+            a = actions.to(self.device, dtype=torch.float).contiguous()
+            action_tensor = torch.empty_like(a)
+            self._noise_clamp(a, "actions", self.clip_actions, None, action_tensor)
+            self.pre_physics_step(action_tensor)
+        elif self.fuses_action_clip:
             self._clip_in_kernel = True
             self.pre_physics_step(actions)
             self._clip_in_kernel = False
         else:
-            action_tensor = actions if np.isinf(self.clip_actions) else torch.clamp(actions, -self.clip_actions, self.clip_actions)
+            action_tensor = actions
+            if not np.isinf(self.clip_actions):
+                action_tensor = torch.empty_like(actions)
+                self._noise_clamp(actions.contiguous(), "actions", self.clip_actions, None, action_tensor)
             self.pre_physics_step(action_tensor)
         for _ in range(self.control_freq_inv):
             self.sim.simulate()
+        # the fused kernel stores its obs tile into the rollout slot as well when nothing has to be applied to it
+        rollout = getattr(self, "_rollout", None)
+        self._slot_filled_by_kernel = False
+        if rollout is not None and np.isinf(self.clip_obs) and not self.dr_randomizations.get("observations"):
+            self._slot_filled_by_kernel = self._obs_copy_hook(rollout[self._rollout_t])
         # post_physics_step also fills timeout_buf (vec_task.py:345) inside the fused kernel
         self.post_physics_step()
+        if self._slot_filled_by_kernel:
+            self._obs_copy_hook(None)
         self.extras["time_outs"] = self.timeout_buf.to(self.rl_device)
         self.obs_dict["obs"] = self._clipped_obs()
         if self.num_states > 0:
             self.obs_dict["states"] = self.get_state()
         return self.obs_dict, self.rew_buf.to(self.rl_device), self.reset_buf.to(self.rl_device), self.extras
+
+    def apply_randomizations(self, dr_params):
+        """vec_task.py:538-646, the NON-PHYSICAL part: the observation / action noise lambdas (gaussian | uniform,
+        additive | scaling, linear | constant schedule, correlated component).  Same ``dr_randomizations`` entries as the
+        reference ('mu', 'var', 'mu_corr', 'var_corr' | 'lo', 'hi', 'lo_corr', 'hi_corr', 'noise_lambda'); the lambda is
+        one fused kernel.  The PhysX property setters (:648-768) are out of scope."""
+        from ... import _native as nat
+        rand_freq = dr_params.get("frequency", 1)                                    # :547
+        self.last_step = int(getattr(self.sim, "frame_count", self.last_step + 1))   # :553 gym.get_frame_count
+        if self.first_randomization:
+            do_nonenv_randomize = True                                               # :555
+        else:
+            do_nonenv_randomize = (self.last_step - self.last_rand_step) >= rand_freq    # :558
+        if do_nonenv_randomize:
+            self.last_rand_step = self.last_step                                     # :565
+        for name in ("observations", "actions"):                                     # :576
+            if name not in dr_params or not do_nonenv_randomize:
+                continue
+            prm = dr_params[name]
+            dist, op_type = prm["distribution"], prm["operation"]
+            sched_type = prm["schedule"] if "schedule" in prm else None
+            sched_step = prm["schedule_steps"] if "schedule" in prm else None
+            if sched_type == "linear":
+                sched_scaling = 1.0 / sched_step * min(self.last_step, sched_step)   # :585-586
+            elif sched_type == "constant":
+                sched_scaling = 0 if self.last_step < sched_step else 1              # :588
+            else:
+                sched_scaling = 1
+            a, b = prm["range"]
+            a_corr, b_corr = prm.get("range_correlated", [0., 0.])
+            if dist == "gaussian":                                                   # a = mu, b = var
+                if op_type == "additive":
+                    a, b, a_corr, b_corr = a * sched_scaling, b * sched_scaling, a_corr * sched_scaling, b_corr * sched_scaling
+                elif op_type == "scaling":
+                    b = b * sched_scaling
+                    a = a * sched_scaling + 1.0 * (1.0 - sched_scaling)
+                    b_corr = b_corr * sched_scaling
+                    a_corr = a_corr * sched_scaling + 1.0 * (1.0 - sched_scaling)
+                entry = {"mu": a, "var": b, "mu_corr": a_corr, "var_corr": b_corr}
+            elif dist == "uniform":                                                  # a = lo, b = hi
+                if op_type == "additive":
+                    a, b, a_corr, b_corr = a * sched_scaling, b * sched_scaling, a_corr * sched_scaling, b_corr * sched_scaling
+                elif op_type == "scaling":
+                    a = a * sched_scaling + 1.0 * (1.0 - sched_scaling)
+                    b = b * sched_scaling + 1.0 * (1.0 - sched_scaling)
+                    a_corr = a_corr * sched_scaling + 1.0 * (1.0 - sched_scaling)
+                    b_corr = b_corr * sched_scaling + 1.0 * (1.0 - sched_scaling)
+                entry = {"lo": a, "hi": b, "lo_corr": a_corr, "hi_corr": b_corr}
+            else:
+                raise ValueError(f"unknown distribution {dist!r}")
+            lam = nat.NoiseLambda()
+            lam.distribution = 1 if dist == "gaussian" else 2
+            lam.operation = 0 if op_type == "additive" else 1
+            lam.range[0], lam.range[1] = float(a), float(b)
+            lam.range_correlated[0], lam.range_correlated[1] = float(a_corr), float(b_corr)
+            entry["_lambda"] = lam
+
+            def noise_lambda(tensor, param_name=name):                               # :612-620 / :635-641
+                out = torch.empty_like(tensor)
+                self._noise_clamp(tensor.contiguous(), param_name, float("inf"), out, None)
+                return out
+            entry["noise_lambda"] = noise_lambda
+            self.dr_randomizations[name] = entry
+        self.first_randomization = False
 
     def zero_actions(self) -> torch.Tensor:
         return torch.zeros([self.num_envs, self.num_actions], dtype=torch.float32, device=self.rl_device)

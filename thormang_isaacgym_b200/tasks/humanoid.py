@@ -187,6 +187,11 @@ class Humanoid(VecTask):
             setattr(b, name, nat.ptr(t))
         nat.check(self._lib.tk_humanoid_bind(self._handle, C.byref(b)), "tk_humanoid_bind")
 
+    def _obs_copy_hook(self, dst):
+        """N4: the fused kernel stores its obs tile to ``dst`` too (a rollout slot); None switches the copy off."""
+        nat.check(self._lib.tk_humanoid_set_obs_copy(self._handle, nat.ptr(dst)), "tk_humanoid_set_obs_copy")
+        return True
+
     def rebind(self):
         """Call after replacing any buffer attribute (e.g. ``env.reset_buf = ...``) by a new tensor."""
         self._bind()
