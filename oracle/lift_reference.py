@@ -38,6 +38,11 @@ LIFT_TABLE: Dict[str, Iterable[str]] = {
         "compute_reward",                  # anymal.py:375-396
         "compute_anymal_observations_V2",  # anymal.py:399-431
     ),
+    "isaacgymenvs/tasks/MA_OP3.py": (
+        "compute_objective_reward",        # MA_OP3.py:496-547
+        "compute_op3_reward",              # MA_OP3.py:550-658
+        "compute_op3_observations",        # MA_OP3.py:662-708
+    ),
     "isaacgymenvs/tasks/gogoro_new.py": (
         "compute_gogoro_reward",          # gogoro_new.py:645-684
         "shortest_angle_distance",        # gogoro_new.py:687-689
@@ -131,3 +136,7 @@ def gogoro_paper() -> ModuleType:
 
 def anymal() -> ModuleType:
     return lift("isaacgymenvs/tasks/anymal.py")
+
+
+def ma_op3() -> ModuleType:
+    return lift("isaacgymenvs/tasks/MA_OP3.py")

@@ -258,3 +258,78 @@ def anymal_reset_noise(n: int, seed: int, device="cpu"):
     g = _gen(seed + 313)
     return tuple(t.to(device) for t in (torch.rand((n, 12), generator=g), torch.rand((n, 12), generator=g),
                                         torch.rand((n, 3), generator=g)))
+
+
+OP3_DOF = 22
+OP3_AGENTS = 2
+OP3_BODIES = 25          # rigid bodies of one OP3 in the synthetic layout (the URDF is not in the reference tree)
+OP3_FEET = (10, 11, 16, 17)      # the four "*ank*" links of one robot (MA_OP3.py:237-238), actor-local
+OP3_GRIPPERS = (20, 24)          # the two "*gr*" links (:241-242), actor-local: [left, right]
+
+
+def ma_op3_body_indices():
+    """(feet [2,4], grippers [2,2]) into ``contact_forces.view(N, -1, 3)``: agent a's bodies start at a * OP3_BODIES."""
+    feet = torch.tensor([[a * OP3_BODIES + b for b in OP3_FEET] for a in range(OP3_AGENTS)], dtype=torch.long)
+    grip = torch.tensor([[a * OP3_BODIES + b for b in OP3_GRIPPERS] for a in range(OP3_AGENTS)], dtype=torch.long)
+    return feet, grip
+
+
+def ma_op3_state(n: int, seed: int = 1234, device="cpu", far_frac: float = 0.03) -> Dict[str, torch.Tensor]:
+    """One post-physics snapshot for ``n`` MA_OP3 envs: two 22-DOF OP3 + one table per env,
+    2 * 25 + 1 rigid bodies.  A few percent of the robots are tilted past up_proj 0.90 or further than 0.40 m from the
+    table, a few tables are tilted / below 0.25 m; foot forces straddle the 0.1 / 1.1 / 450 N thresholds, gripper forces
+    the 0.1 / 400 N ones; progress counters are forced onto 0 and the episode end (3012)."""
+    g = _gen(seed)
+    a, d, nb = OP3_AGENTS, OP3_DOF, OP3_AGENTS * OP3_BODIES + 1
+    root = torch.zeros((n, 3, 13), dtype=torch.float32)
+    base = torch.tensor([[-0.31, 0.0, 0.27], [0.30, 0.0, 0.27], [0.0, 0.0, 0.30]])
+    origin = torch.cat([_u(g, (n, 1, 2), -2.0, 2.0), torch.zeros(n, 1, 1)], dim=-1)
+    spread = torch.where(torch.rand((n, 3, 1), generator=g) < far_frac, torch.tensor(0.12), torch.tensor(0.03))
+    root[:, :, 0:3] = base + origin + _n(g, (n, 3, 3)) * spread
+    tilt = torch.where(torch.rand((n, 3), generator=g) < 0.02, torch.tensor(0.5), torch.tensor(0.08))
+    for k in range(3):
+        root[:, k, 3:7] = _euler_to_quat(_n(g, (n,)) * tilt[:, k], _n(g, (n,)) * tilt[:, k], _u(g, (n,), -math.pi, math.pi))
+    root[:, :, 7:10] = _n(g, (n, 3, 3), 0.5)
+    root[:, :, 10:13] = _n(g, (n, 3, 3), 1.0)
+    contact = torch.zeros((n, nb, 3), dtype=torch.float32)
+    feet, grip = ma_op3_body_indices()
+    for i in range(a):
+        fz = torch.where(torch.rand((n, 4), generator=g) < 0.5, _u(g, (n, 4), 0.0, 2.0), _u(g, (n, 4), 2.0, 60.0))
+        fz = torch.where(torch.rand((n, 4), generator=g) < 0.03, _u(g, (n, 4), 430.0, 470.0), fz)
+        fz = torch.where(torch.rand((n, 4), generator=g) < 0.35, torch.zeros(n, 4), fz)
+        contact[:, feet[i], 2] = fz
+        contact[:, feet[i], 0:2] = _n(g, (n, 4, 2), 5.0) * (fz.unsqueeze(-1) > 0)
+        gx = torch.where(torch.rand((n, 2), generator=g) < 0.02, _u(g, (n, 2), 0.0, 30.0), torch.zeros(n, 2))
+        gx = torch.where(torch.rand((n, 2), generator=g) < 0.005, _u(g, (n, 2), 390.0, 410.0), gx)
+        contact[:, grip[i], 0] = gx
+        contact[:, grip[i], 1:3] = _n(g, (n, 2, 2), 1.0) * (gx.unsqueeze(-1) > 0)
+    other = torch.rand((n, nb), generator=g) < 0.05
+    contact += (_n(g, (n, nb, 3), 10.0) * other.unsqueeze(-1)) * (contact.abs().sum(-1, keepdim=True) == 0)
+    cmd_y = torch.where(torch.rand((n,), generator=g) < 0.1, _u(g, (n,), 0.0, 0.2), _u(g, (n,), 0.0, 10.0))
+    progress = torch.randint(1, 3012, (n,), generator=g, dtype=torch.int64)
+    forced = torch.rand((n,), generator=g) < 0.03
+    ladder = torch.tensor([0, 3010, 3011, 3012, 3013, 1], dtype=torch.int64)
+    progress = torch.where(forced, ladder[torch.arange(n) % 6], progress)
+    air = torch.where(torch.rand((n, a, 4), generator=g) < 0.3, torch.zeros(n, a, 4), _u(g, (n, a, 4), 0.0, 1.2))
+    # potentials of the previous step: the same closed form on slightly displaced positions (dt = 0.0166)
+    goal, target = torch.tensor([0.0, -10.0, 0.0]), torch.tensor([0.0, 10.0, 0.0])
+    prev_pos = root[:, 0:2, 0:3] + _n(g, (n, 2, 3), 0.004)
+    to_goal = goal - prev_pos
+    to_goal[..., 2] = 0.0
+    pot = -to_goal.norm(dim=-1) / 0.0166
+    tpot = -(target - (root[:, 2, 0:3] + _n(g, (n, 3), 0.004))).norm(dim=-1) / 0.0166
+    out = dict(
+        root_states=root.view(n * 3, 13), dof_state=torch.stack([_n(g, (n * a * d,), 0.5), _n(g, (n * a * d,), 3.0)], dim=-1),
+        torques=_n(g, (n, a, d), 2.0), prev_torques=_n(g, (n, a, d), 2.0), contact_forces=contact,
+        commands=torch.stack([torch.zeros(n), cmd_y, torch.zeros(n)], dim=-1),
+        actions=_u(g, (n, a, d), -1.5, 1.5), last_actions=_u(g, (n, a, d), -1.0, 1.0),
+        feet_air_time=air, last_contacts=torch.rand((n, a, 4), generator=g) < 0.5,
+        potentials=pot, prev_potentials=pot + _n(g, (n, a), 0.3), table_potentials=tpot, progress_buf=progress,
+        reset_buf=(torch.rand((n,), generator=g) < 0.01).to(torch.int64),
+    )
+    return {k: v.to(device) for k, v in out.items()}
+
+
+def ma_op3_reset_noise(n: int, seed: int, device="cpu") -> torch.Tensor:
+    """U(0,1) draws of MA_OP3.reset_idx addressed by env id: commands [N,3] (x, y, yaw)."""
+    return torch.rand((n, 3), generator=_gen(seed + 717)).to(device)
