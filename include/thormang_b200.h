@@ -511,6 +511,116 @@ int tk_anymal_philox_noise(TkAnymal* h, uint64_t seed, uint64_t step, int64_t en
                            float* unit_cmd, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * MA_OP3  (isaacgymenvs/tasks/MA_OP3.py, cfg/task/MA_OP3.yaml) -- SURVEY.md 8(f) row N3: two 22-DOF ROBOTIS OP3
+ * humanoids and one table per env; tensors are [N, agents, ...].  compute_op3_observations (:662-708),
+ * compute_op3_reward (:550-658), compute_objective_reward (:496-547), the five contact terms (:319-358),
+ * compute_observations (:411-438), compute_reward (:360-409), reset_idx (:440-489).  The reference's step hooks are
+ * stubs (:309-317): the fused step is the anymal.py:229-242 ordering around those methods, with prev_torques /
+ * last_actions (read at :373,:384; never assigned / only zeroed in the reference) refreshed at the end of the step.
+ * ------------------------------------------------------------------------------------------ */
+
+#define TK_OP3_AGENTS 2
+#define TK_OP3_DOF 22
+#define TK_OP3_OBS 88
+#define TK_OP3_MAX_FEET 8
+#define TK_OP3_MAX_GRIPPERS 4
+
+typedef struct TkOp3Params {
+    int32_t device;
+    int32_t num_envs;
+    int32_t num_agents;              /* 2 (MA_OP3.yaml numAgents) */
+    int32_t num_dof;                 /* 22 per robot (:208) */
+    int32_t num_bodies_total;        /* rigid bodies per env = dim 1 of contact_forces.view(N, -1, 3), :114 */
+    int32_t max_episode_length;      /* int(episodeLength_s / dt + 0.5), :69 */
+    int32_t num_feet;                /* len(feet_names), :237-238 */
+    int32_t num_grippers;            /* len(gripper_names) >= 2, :241-242; [0] = left, [1] = right (:347-348) */
+    int32_t feet_indices[TK_OP3_AGENTS][TK_OP3_MAX_FEET];          /* into dim 1 of contact_forces, :294-296 */
+    int32_t gripper_indices[TK_OP3_AGENTS][TK_OP3_MAX_GRIPPERS];   /* :300-302 */
+    float lin_vel_scale;             /* :18 */
+    float ang_vel_scale;             /* :19 */
+    float dof_pos_scale;             /* :20 */
+    float dof_vel_scale;             /* :21 */
+    float action_scale;              /* :22 */
+    float clip_actions;
+    /* python doubles: the reward scales are multiplied by dt in double (:80-81) before torch rounds to fp32 */
+    double dt;
+    double rew_torque, rew_up, rew_air_time, rew_syns_hip, rew_no_fly, rew_stand, rew_action_rate;   /* :25-35 */
+    double command_x_range[2];       /* :42 */
+    double command_y_range[2];       /* :43 */
+    double command_yaw_range[2];     /* :44 */
+    /* rows of replicated [N,*] tensors (identical for every env) */
+    float default_dof_pos[TK_OP3_DOF];   /* :126-129 */
+    float inv_start_rot[4];          /* :143 */
+    float gravity_vec[3];            /* :132 */
+    float up_vec[3];                 /* :139 (vec1 of both reward functions) */
+    float targets[3];                /* :144 */
+    float goal_pos[3];               /* :100 */
+} TkOp3Params;
+
+typedef struct TkOp3Buffers {
+    float* root_states;              /* [N,3,13] simulator-owned: robot 0, robot 1, table (:98) */
+    const float* initial_root_states;/* [N,3,13] (:99-100) */
+    float* dof_state;                /* [N,2,22,2] simulator-owned (:109-111) */
+    const float* torques;            /* [N,2,22] dof-force tensor (:115) */
+    float* prev_torques;             /* [N,2,22] (:373) */
+    const float* contact_forces;     /* [N,bodies,3] (:114) */
+    float* commands;                 /* [N,3] (:117) */
+    float* actions;                  /* [N,2,22] */
+    float* last_actions;             /* [N,2,22] (:137) */
+    float* feet_air_time;            /* [N,2,F] (:134) */
+    uint8_t* last_contacts;          /* [N,2,F] bool (:135) */
+    float* potentials;               /* [N,2] (:145) */
+    float* prev_potentials;          /* [N,2] (:146) */
+    float* table_potentials;         /* [N] (:106) */
+    float* prev_table_potentials;    /* [N] (:107) */
+    float* obs_buf;                  /* [N,2,88] */
+    float* rew_buf;                  /* [N,2] */
+    int64_t* reset_buf;              /* [N] */
+    int64_t* progress_buf;           /* [N] */
+    uint8_t* timeout_buf;            /* [N] bool, may be NULL */
+    float* episode_return;           /* [N] (sum over both agents), may be NULL */
+} TkOp3Buffers;
+
+/* U(0,1) draws of reset_idx (:472-474): unit_cmd [N,3] = x, y, yaw addressed by env id (TK_NOISE_DENSE), drawn in-kernel
+ * (TK_NOISE_PHILOX) or absent (TK_NOISE_NONE: 0.5). */
+typedef struct TkOp3Noise {
+    int32_t mode;
+    int32_t reserved;
+    const float* unit_cmd;
+    uint64_t seed;
+    uint64_t step;
+    int64_t env_id_offset;
+} TkOp3Noise;
+
+typedef struct TkOp3 TkOp3;
+
+int tk_ma_op3_create(const TkOp3Params* params, TkOp3** out);
+int tk_ma_op3_destroy(TkOp3* h);
+int tk_ma_op3_bind(TkOp3* h, const TkOp3Buffers* buffers);
+/* Un-stubbed pre_physics_step (:309-310 is `pass`; anymal.py:229-232 + clamp vec_task.py:327): actions = clamp(in),
+ * targets_out[N,2,22] = action_scale * actions + default_dof_pos. */
+int tk_ma_op3_pre_physics(TkOp3* h, const float* actions_in, float* targets_out, int32_t clip, void* stream);
+/* _reward_gripper_contact_hold (:346-358) reduces over ALL envs.  This call counts, into the handle's device array
+ * int64[agents][2] (pointer returned through counts_dev), the envs whose left / right gripper x-force exceeds 0.1.
+ * A sharded run all-reduces (SUM) that array over ranks before the reward kernel -- the one exchange step of this path.
+ * tk_ma_op3_compute_reward / tk_ma_op3_post_physics read it; they MUST follow this call on the same stream. */
+int tk_ma_op3_grip_counts(TkOp3* h, int64_t** counts_dev, void* stream);
+/* compute_observations (:411-438): obs_buf, potentials, prev_potentials, prev_table_potentials. */
+int tk_ma_op3_compute_observations(TkOp3* h, void* stream);
+/* compute_reward (:360-409): rew_buf, reset_buf, feet_air_time, last_contacts. */
+int tk_ma_op3_compute_reward(TkOp3* h, void* stream);
+/* reset_idx (:440-489): env_ids[k] int64, unit_cmd [k,3]. */
+int tk_ma_op3_reset_idx(TkOp3* h, const int64_t* env_ids, int32_t k, const float* unit_cmd, void* stream);
+/* progress += 1, reset prologue, compute_observations, compute_reward, prev_torques / last_actions refresh and the
+ * timeout line (multi_vec_task.py:193) as ONE fused kernel. */
+int tk_ma_op3_post_physics(TkOp3* h, const TkOp3Noise* noise, void* stream);
+int tk_ma_op3_advance_epoch(TkOp3* h, void* stream);
+/* stats: sum reward (both agents), #reset, #timeout, sum episode_return / length of reset envs, sum agent-0 / agent-1
+ * distance to the table, N */
+int tk_ma_op3_stats(TkOp3* h, double* stats_out, int32_t accumulate, void* stream);
+int tk_ma_op3_philox_noise(TkOp3* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* unit_cmd, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * VecTask.step prologue / epilogue (isaacgymenvs/tasks/base/vec_task.py:323-327,347-353) and the non-physical
  * domain-randomisation lambdas of apply_randomizations (:576-646) -- SURVEY.md 8(f) row N4.
  * ------------------------------------------------------------------------------------------ */

@@ -254,6 +254,34 @@ def anymal_golden(n_rand=96):
     print("anymal_jit.npz", n, "rows; resets", int(reset.sum()), "reward max", float(rew.max()))
 
 
+def ma_op3_golden(n=96):
+    """MA_OP3.py JIT functions run through the method bodies of compute_observations / compute_reward:
+    rows forced onto the 0.90 / 0.95 / 0.98 up-projection, 0.40 m table distance, 0.25 m table height and
+    episode-length thresholds; exactly one env holds each gripper (the batch-global hold term is 1)."""
+    from oracle import ma_op3_oracle as mo
+    ref = L.ma_op3()
+    st = syn.ma_op3_state(n, seed=5151)
+    root = st["root_states"].view(n, 3, 13)
+    root[0, 2, 2] = 0.25                                     # table height exactly at the threshold (not < 0.25)
+    root[1, 2, 2] = float(np.nextafter(np.float32(0.25), np.float32(0)))
+    root[2, 0, 0:3] = root[2, 2, 0:3] + torch.tensor([0.4, 0.0, 0.0])       # agent 0 at ~0.40 m from the table
+    root[3, 1, 0:3] = root[3, 2, 0:3] + torch.tensor([0.0, 0.41, 0.0])
+    st["progress_buf"][4:10] = torch.tensor([0, 1, 3011, 3012, 3013, 0])
+    st["reset_buf"][9] = 1                                   # cleared by the episode_lengths == 0 line (:656)
+    feet, grip = syn.ma_op3_body_indices()
+    cf = st["contact_forces"]
+    cf[:, grip.flatten(), 0] = 0.0
+    cf[11, grip[0, 0], 0] = 0.5; cf[12, grip[0, 1], 0] = 0.7          # agent 0: exactly one env per gripper -> hold = 1
+    cf[13, grip[1, 0], 0] = 0.5; cf[14, grip[1, 0], 0] = 0.5; cf[15, grip[1, 1], 0] = 0.9   # agent 1: two left holds -> 0
+    o = mo.oracle_from_state(st)
+    out = mo.run_jit_level(o, ref.compute_op3_observations, ref.compute_op3_reward, ref.compute_objective_reward)
+    np.savez_compressed(os.path.join(HERE, "ma_op3_jit.npz"), **_np({**{k: v for k, v in st.items()},
+                                                                      **{"out_" + k: v for k, v in out.items()},
+                                                                      "grip_counts": mo.grip_counts(cf, grip)}))
+    print("ma_op3_jit.npz", n, "rows; resets", int(out["reset"].sum()), "reward max", float(out["rew"].max()),
+          "grip counts", mo.grip_counts(cf, grip).tolist())
+
+
 def poselib_golden(n=256):
     path = os.path.join(L.REFERENCE_ROOT, "isaacgymenvs/tasks/amp/poselib/poselib/core/rotation3d.py")
     spec = importlib.util.spec_from_file_location("_ref_rotation3d", path)
@@ -278,4 +306,5 @@ if __name__ == "__main__":
     ant_golden()
     gogoro_paper_golden()
     anymal_golden()
+    ma_op3_golden()
     poselib_golden()

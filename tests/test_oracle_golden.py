@@ -226,3 +226,20 @@ def test_anymal_golden(golden_dir):
     # thigh at 1 N (no), thigh above (reset), two foot contacts of 500 N (never a reset)
     assert g["reset"][:8].tolist() == [0, 1, 0, 1, 0, 1, 0, 0]
     assert g["reset"][8:12].tolist()[2:] == [1, 1] and c.max_episode_length == 2500
+
+
+def test_ma_op3_golden(golden_dir):
+    """MA_OP3 against MA_OP3.py's own JIT functions; threshold rows and the batch-global hold term."""
+    from oracle import ma_op3_oracle as mo
+    g = _load(golden_dir, "ma_op3_jit.npz")
+    st = {k: v for k, v in g.items() if not k.startswith("out_") and k != "grip_counts"}
+    o = mo.oracle_from_state(st)
+    assert torch.equal(mo.grip_counts(o.contact_forces, o.gripper_indices), g["grip_counts"])
+    assert bool(o._reward_gripper_contact_hold(0)) and not bool(o._reward_gripper_contact_hold(1))
+    out = mo.run_jit_level(o)
+    for k, v in out.items():
+        w = g["out_" + k]
+        if v.is_floating_point():
+            assert torch.allclose(v, w, rtol=RTOL, atol=ATOL), k
+        else:
+            assert torch.equal(v, w), k

@@ -134,3 +134,16 @@ def test_anymal_bit_exact(n):
         lin, ang = got[:m, 0:3].reshape(b, t, 3), got[:m, 3:6].reshape(b, t, 3)
         tq, cmd = st["torques"][:m].reshape(b, t, 12), st["commands"][:m].reshape(b, t, 3)
         assert torch.equal(ref.compute_reward(lin, ang, tq, cmd, c.rew_scales()), ao.anymal_wm_reward(lin, ang, tq, cmd, c.rew_scales()))
+
+
+@pytest.mark.parametrize("n", [1, 33, 4096])
+def test_ma_op3_bit_exact(n):
+    """MA_OP3.py:496-708 through the method bodies of compute_observations / compute_reward."""
+    from oracle import ma_op3_oracle as mo
+    ref = L.ma_op3()
+    st = syn.ma_op3_state(n, seed=900 + n)
+    got = mo.run_jit_level(mo.oracle_from_state(st))
+    want = mo.run_jit_level(mo.oracle_from_state(st), ref.compute_op3_observations, ref.compute_op3_reward,
+                            ref.compute_objective_reward)
+    for k in want:
+        assert torch.equal(want[k], got[k]), k
