@@ -579,6 +579,7 @@ typedef struct TkOp3Buffers {
     int64_t* progress_buf;           /* [N] */
     uint8_t* timeout_buf;            /* [N] bool, may be NULL */
     float* episode_return;           /* [N] (sum over both agents), may be NULL */
+    int64_t* grip_counts;            /* [agents,2] batch-global gripper counts (:351-352), see tk_ma_op3_grip_counts */
 } TkOp3Buffers;
 
 /* U(0,1) draws of reset_idx (:472-474): unit_cmd [N,3] = x, y, yaw addressed by env id (TK_NOISE_DENSE), drawn in-kernel
@@ -600,11 +601,11 @@ int tk_ma_op3_bind(TkOp3* h, const TkOp3Buffers* buffers);
 /* Un-stubbed pre_physics_step (:309-310 is `pass`; anymal.py:229-232 + clamp vec_task.py:327): actions = clamp(in),
  * targets_out[N,2,22] = action_scale * actions + default_dof_pos. */
 int tk_ma_op3_pre_physics(TkOp3* h, const float* actions_in, float* targets_out, int32_t clip, void* stream);
-/* _reward_gripper_contact_hold (:346-358) reduces over ALL envs.  This call counts, into the handle's device array
- * int64[agents][2] (pointer returned through counts_dev), the envs whose left / right gripper x-force exceeds 0.1.
- * A sharded run all-reduces (SUM) that array over ranks before the reward kernel -- the one exchange step of this path.
- * tk_ma_op3_compute_reward / tk_ma_op3_post_physics read it; they MUST follow this call on the same stream. */
-int tk_ma_op3_grip_counts(TkOp3* h, int64_t** counts_dev, void* stream);
+/* _reward_gripper_contact_hold (:346-358) reduces over ALL envs.  This call counts, into the bound grip_counts array
+ * (int64 [agents,2]), the envs whose left / right gripper x-force exceeds 0.1.  A sharded run all-reduces (SUM) that
+ * array over ranks before the reward kernel -- the one exchange step of this path.  tk_ma_op3_compute_reward /
+ * tk_ma_op3_post_physics read it; they MUST follow this call on the same stream. */
+int tk_ma_op3_grip_counts(TkOp3* h, void* stream);
 /* compute_observations (:411-438): obs_buf, potentials, prev_potentials, prev_table_potentials. */
 int tk_ma_op3_compute_observations(TkOp3* h, void* stream);
 /* compute_reward (:360-409): rew_buf, reset_buf, feet_air_time, last_contacts. */

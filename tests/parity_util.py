@@ -224,3 +224,38 @@ def make_anymal_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
     orc.progress_buf = state["progress_buf"].clone()
     orc.reset_buf = state["reset_buf"].clone()
     return env, orc, state
+
+
+OP3_STATE_NAMES = ("prev_torques", "commands", "actions", "last_actions", "feet_air_time", "last_contacts", "potentials",
+                   "prev_potentials", "table_potentials", "progress_buf", "reset_buf")
+
+
+def make_ma_op3_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
+    """(cuda MA_OP3 task, cpu MAOP3Oracle, state) from one synthetic snapshot."""
+    from oracle import ma_op3_oracle as mo
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.MA_OP3 import MA_OP3
+    state = state or syn.ma_op3_state(n, seed=seed)
+    cfg = tcfg.ma_op3_cfg(n, seed=seed)
+    cfg["env"].update(env_over)
+    cfg["env"]["resetOnInit"] = False
+    nb = state["contact_forces"].numel() // (n * 3)
+    sim = FakeSim(n, 44, device, num_sensor_floats=0, dof_names=list(tcfg.OP3_DOF_NAMES), num_bodies=nb, actors_per_env=3)
+    init = state.get("initial_root_states")
+    if init is None:
+        # a distinct "spawn" snapshot so that reset writes are visible: the initial pose of MA_OP3.py:221-231 per env
+        init = torch.zeros(n, 3, 13)
+        init[:, :, 0:3] = torch.tensor([[-0.31, 0.0, 0.27], [0.30, 0.0, 0.27], [0.0, 0.0, 0.30]])
+        init[:, :, 0:2] += state["root_states"].view(n, 3, 13)[:, 2:3, 0:2] * 0.5
+        init[:, :, 6] = 1.0
+    sim.load_state({"root_states": init.view(n * 3, 13)})
+    cfg["sim_backend"] = sim
+    env = MA_OP3(cfg, device, device, -1, True)           # initial_root_states := clone of the spawn snapshot (:99-100)
+    sim.load_state(state)
+    for name in OP3_STATE_NAMES:
+        getattr(env, name).copy_(state[name].to(device))
+    feet, grip = syn.ma_op3_body_indices()
+    st = dict(state)
+    st["initial_root_states"] = init.clone()
+    orc = mo.oracle_from_state(st, consts=mo.OP3Consts.from_cfg(cfg), feet=feet, grip=grip)
+    return env, orc, state

@@ -1,0 +1,119 @@
+"""GPU parity of MA_OP3 (two OP3 humanoids + table, ``[N, agents, ...]`` tensors) against the CPU
+oracle (oracle/ma_op3_oracle.py, pinned bit-for-bit to MA_OP3.py's JIT functions).
+
+Bar: reset / progress / timeout / last_contacts masks and the gripper counts bit-exact; reset-state writes exact; fp32
+observations, potentials, air times and rewards within 1e-5 relative (tests/parity_util.py).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import parity_util as U
+from thormang_isaacgym_b200 import synthetic as syn
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _reward_close(got, want, what):
+    # rewards are sums of O(1) terms (alive 2, foot-force excess up to tens) minus small penalties and a progress term
+    # (potential differences of ~600-magnitude values, ulp 6e-5, times 5): the absolute floor is that cancellation
+    U.close(got, want, rtol=U.RTOL, atol=2e-5, what=what)
+
+
+def _check_obs_side(env, orc, tag):
+    U.close(env.obs_buf, orc.obs_buf, what=f"{tag} obs")
+    U.close(env.potentials, orc.potentials, what=f"{tag} potentials")
+    U.close(env.prev_potentials, orc.prev_potentials, what=f"{tag} prev_potentials")
+    U.close(env.prev_table_potentials, orc.prev_table_potentials, what=f"{tag} prev_table_potentials")
+
+
+def _check_reward_side(env, orc, tag):
+    _reward_close(env.rew_buf, orc.rew_buf, f"{tag} rew")
+    U.exact(env.reset_buf, orc.reset_buf, f"{tag} reset")
+    U.exact(env.last_contacts, orc.last_contacts, f"{tag} last_contacts")
+    U.close(env.feet_air_time, orc.feet_air_time, what=f"{tag} feet_air_time")
+
+
+@pytest.mark.parametrize("n", [1, 31, 32, 33, 1000, 4096])
+def test_observations_and_reward_split(n):
+    env, orc, st = U.make_ma_op3_pair(n, seed=100 + n)
+    env.compute_observations()
+    env.compute_reward()
+    orc.compute_observations()
+    orc.compute_reward()
+    torch.cuda.synchronize()
+    _check_obs_side(env, orc, f"n={n}")
+    _check_reward_side(env, orc, f"n={n}")
+
+
+def test_golden_vectors(golden_dir):
+    from oracle import ma_op3_oracle as mo
+    z = np.load(os.path.join(golden_dir, "ma_op3_jit.npz"))
+    g = {k: torch.from_numpy(z[k]) for k in z.files}
+    n = g["progress_buf"].shape[0]
+    st = {k: v for k, v in g.items() if not k.startswith("out_") and k != "grip_counts"}
+    env, orc, _ = U.make_ma_op3_pair(n, seed=1, state=st)
+    env.compute_observations()
+    env.compute_reward()
+    torch.cuda.synchronize()
+    U.exact(env.grip_count_buf, g["grip_counts"], "golden grip counts (agent 0 holds, agent 1 does not)")
+    U.close(env.obs_buf, g["out_obs"], what="golden obs")
+    U.close(env.potentials, g["out_potentials"], what="golden potentials")
+    _reward_close(env.rew_buf, g["out_rew"], "golden reward")
+    U.exact(env.reset_buf, g["out_reset"], "golden reset (0.25 m / 0.40 m / 0.90 thresholds, episode_lengths == 0 line)")
+    U.exact(env.last_contacts, g["out_last_contacts"], "golden last_contacts")
+    U.close(env.feet_air_time, g["out_feet_air_time"], what="golden feet_air_time")
+
+
+@pytest.mark.parametrize("clip", [False, True])
+def test_pre_physics(clip):
+    n = 1000
+    env, orc, st = U.make_ma_op3_pair(n, seed=7)
+    env._clip_in_kernel = clip
+    env.pre_physics_step(st["actions"].to(DEV))
+    env._clip_in_kernel = False
+    orc.pre_physics_step(st["actions"], clip=clip)
+    torch.cuda.synchronize()
+    U.exact(env.actions, orc.actions, "actions")
+    U.exact(env.pd_targets, orc.pd_targets, "PD targets")
+    assert env.sim.dof_position_target.data_ptr() == env.pd_targets.data_ptr()
+
+
+def test_reset_idx():
+    n = 300
+    env, orc, st = U.make_ma_op3_pair(n, seed=9)
+    ids = torch.tensor([0, 5, 31, 32, 33, 299])
+    uc = syn.ma_op3_reset_noise(n, seed=4)[:len(ids)]
+    env.reset_idx(ids.to(DEV), uc.to(DEV))
+    orc.reset_idx(ids, uc)
+    torch.cuda.synchronize()
+    for name in ("root_states", "dof_state", "commands", "progress_buf", "reset_buf", "potentials", "prev_potentials",
+                 "table_potentials", "prev_table_potentials", "last_actions", "feet_air_time"):
+        U.exact(getattr(env, name), getattr(orc, name), name)
+
+
+@pytest.mark.parametrize("n", [1, 33, 1000, 4096, 65536])
+def test_fused_post_physics(n):
+    env, orc, st = U.make_ma_op3_pair(n, seed=500 + n)
+    uc = syn.ma_op3_reset_noise(n, seed=n)
+    ids = orc.reset_buf.nonzero(as_tuple=False).squeeze(-1)
+    env.post_physics_step(uc.to(DEV))
+    got_ids = orc.post_physics_step(uc[ids])
+    torch.cuda.synchronize()
+    assert torch.equal(got_ids, ids)
+    if n >= 1000:
+        assert len(ids) > 0 and int(orc.reset_buf.sum()) > 0
+    U.exact(env.reset_buf, orc.reset_buf, "reset_buf")
+    U.exact(env.progress_buf, orc.progress_buf, "progress_buf")
+    U.exact(env.timeout_buf, orc.timeout_buf.bool(), "timeout_buf")
+    U.exact(env.root_states, orc.root_states, "root_states (reset writes)")
+    U.exact(env.dof_state, orc.dof_state, "dof_state (reset writes)")
+    U.exact(env.commands, orc.commands, "commands")
+    U.exact(env.table_potentials, orc.table_potentials, "table_potentials")
+    U.exact(env.prev_torques, orc.prev_torques, "prev_torques (end-of-step refresh)")
+    U.exact(env.last_actions, orc.last_actions, "last_actions (end-of-step refresh)")
+    _check_obs_side(env, orc, "fused")
+    _check_reward_side(env, orc, "fused")

@@ -17,7 +17,7 @@ def make(seed: int, task: str, num_envs: int, sim_device: str = "cuda:0", rl_dev
     from .tasks import isaacgym_task_map
     if cfg is None:
         cfg = {"Humanoid": config.humanoid_cfg, "Gogoro": config.gogoro_cfg, "Ant": config.ant_cfg,
-               "GogoroPaper": config.gogoro_paper_cfg, "Anymal": config.anymal_cfg}[task](num_envs, seed)
+               "GogoroPaper": config.gogoro_paper_cfg, "Anymal": config.anymal_cfg, "MA_OP3": config.ma_op3_cfg}[task](num_envs, seed)
     else:
         cfg["env"]["numEnvs"] = num_envs
     return isaacgym_task_map[task](cfg, rl_device, sim_device, graphics_device_id, headless,

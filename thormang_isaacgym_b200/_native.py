@@ -115,6 +115,37 @@ class AnymalNoise(C.Structure):
                 ("seed", _u64), ("step", _u64), ("env_id_offset", _i64)]
 
 
+OP3_AGENTS, OP3_DOF, OP3_OBS, OP3_MAX_FEET, OP3_MAX_GRIPPERS = 2, 22, 88, 8, 4
+
+
+class Op3Params(C.Structure):
+    _fields_ = [
+        ("device", _i32), ("num_envs", _i32), ("num_agents", _i32), ("num_dof", _i32), ("num_bodies_total", _i32),
+        ("max_episode_length", _i32), ("num_feet", _i32), ("num_grippers", _i32),
+        ("feet_indices", (_i32 * OP3_MAX_FEET) * OP3_AGENTS), ("gripper_indices", (_i32 * OP3_MAX_GRIPPERS) * OP3_AGENTS),
+        ("lin_vel_scale", _f), ("ang_vel_scale", _f), ("dof_pos_scale", _f), ("dof_vel_scale", _f), ("action_scale", _f),
+        ("clip_actions", _f),
+        ("dt", _d), ("rew_torque", _d), ("rew_up", _d), ("rew_air_time", _d), ("rew_syns_hip", _d), ("rew_no_fly", _d),
+        ("rew_stand", _d), ("rew_action_rate", _d),
+        ("command_x_range", _d * 2), ("command_y_range", _d * 2), ("command_yaw_range", _d * 2),
+        ("default_dof_pos", _f * OP3_DOF), ("inv_start_rot", _f * 4), ("gravity_vec", _f * 3), ("up_vec", _f * 3),
+        ("targets", _f * 3), ("goal_pos", _f * 3),
+    ]
+
+
+class Op3Buffers(C.Structure):
+    _fields_ = [(name, _p) for name in (
+        "root_states", "initial_root_states", "dof_state", "torques", "prev_torques", "contact_forces", "commands",
+        "actions", "last_actions", "feet_air_time", "last_contacts", "potentials", "prev_potentials", "table_potentials",
+        "prev_table_potentials", "obs_buf", "rew_buf", "reset_buf", "progress_buf", "timeout_buf", "episode_return",
+        "grip_counts")]
+
+
+class Op3Noise(C.Structure):
+    _fields_ = [("mode", _i32), ("reserved", _i32), ("unit_cmd", _p), ("seed", _u64), ("step", _u64),
+                ("env_id_offset", _i64)]
+
+
 class NoiseLambda(C.Structure):
     _fields_ = [("distribution", _i32), ("operation", _i32), ("range", _d * 2), ("range_correlated", _d * 2)]
 
@@ -174,6 +205,18 @@ SYMBOLS = {
     "tk_anymal_advance_epoch": (C.c_int, [_p, _p]),
     "tk_anymal_stats": (C.c_int, [_p, _p, _i32, _p]),
     "tk_anymal_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p, _p, _p]),
+    "tk_ma_op3_create": (C.c_int, [C.POINTER(Op3Params), C.POINTER(_p)]),
+    "tk_ma_op3_destroy": (C.c_int, [_p]),
+    "tk_ma_op3_bind": (C.c_int, [_p, C.POINTER(Op3Buffers)]),
+    "tk_ma_op3_pre_physics": (C.c_int, [_p, _p, _p, _i32, _p]),
+    "tk_ma_op3_grip_counts": (C.c_int, [_p, _p]),
+    "tk_ma_op3_compute_observations": (C.c_int, [_p, _p]),
+    "tk_ma_op3_compute_reward": (C.c_int, [_p, _p]),
+    "tk_ma_op3_reset_idx": (C.c_int, [_p, _p, _i32, _p, _p]),
+    "tk_ma_op3_post_physics": (C.c_int, [_p, C.POINTER(Op3Noise), _p]),
+    "tk_ma_op3_advance_epoch": (C.c_int, [_p, _p]),
+    "tk_ma_op3_stats": (C.c_int, [_p, _p, _i32, _p]),
+    "tk_ma_op3_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p]),
     "tk_step_noise_clamp": (C.c_int, [_p, _i64, C.POINTER(NoiseLambda), _p, _p, _u64, _u64, _i64, _f, _p, _p, _p]),
     "tk_step_noise_units": (C.c_int, [_i64, _i32, _u64, _u64, _i64, _p, _p]),
     "tk_humanoid_set_obs_copy": (C.c_int, [_p, _p]),

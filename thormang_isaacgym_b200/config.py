@@ -123,3 +123,41 @@ def anymal_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
         "sim": {"dt": 0.02, "substeps": 2, "up_axis": "z", "use_gpu_pipeline": True, "gravity": [0.0, 0.0, -9.81]},
         "task": {"randomize": False, "randomization_params": {}},
     })
+
+
+OP3_DOF_NAMES = ["head_pan", "head_tilt", "l_hip_yaw", "l_hip_roll", "l_hip_pitch", "l_knee", "l_ank_pitch", "l_ank_roll",
+                 "l_sho_pitch", "l_sho_roll", "l_el", "l_gr", "r_hip_yaw", "r_hip_roll", "r_hip_pitch", "r_knee",
+                 "r_ank_pitch", "r_ank_roll", "r_sho_pitch", "r_sho_roll", "r_el", "r_gr"]   # MA_OP3.yaml defaultJointAngles order
+
+
+def ma_op3_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
+    """cfg/task/MA_OP3.yaml."""
+    angles = {k: 0.0 for k in OP3_DOF_NAMES}
+    angles.update({"l_hip_pitch": -0.95, "l_knee": 1.49, "l_ank_pitch": -0.0, "l_gr": -0.0, "r_hip_pitch": 0.95,
+                   "r_knee": -1.49, "r_sho_roll": -0.0, "r_el": -0.0})
+    return copy.deepcopy({
+        "name": "MA_OP3",
+        "physics_engine": "physx",
+        "isMultiAgent": True,
+        "seed": seed,
+        "env": {
+            "numEnvs": num_envs, "numAgents": 2, "envSpacing": 1.0, "episodeLength": 1000, "clipObservations": 5.0,
+            "clipActions": 1.0, "staticFriction": 1.0, "dynamicFriction": 1.0, "restitution": 0.0, "enableDebugVis": False,
+            "baseInitState": {"pos": [0.0, 0.0, 0.255], "rot": [0.0, 0.0, 0.0, 1.0], "vLinear": [0.0, 0.0, 0.0],
+                              "vAngular": [0.0, 0.0, 0.0]},
+            "randomCommandVelocityRanges": {"linear_x": [0.0, 0.0], "linear_y": [0.0, 10.0], "yaw": [0.0, 0.0],
+                                            "heading": [-3.14, 3.14]},
+            "control": {"stiffness": 1000.0, "damping": 200.0, "actionScale": 1.0, "powerScale": 0.1, "controlFrequencyInv": 1},
+            "defaultJointAngles": angles,
+            "urdfAsset": {"collapseFixedJoints": True, "fixBaseLink": False, "defaultDofDriveMode": 4},
+            "learn": {"linearVelocityXYRewardScale": 1.0, "angularVelocityZRewardScale": 0.5, "torqueRewardScale": -0.000025,
+                      "headingScale": 1, "upScale": 0.1, "actionRateRewardScale": -0.01, "hipRewardScale": -0.0,
+                      "jointAccRewardScale": -0.0005, "standRewardScale": -0, "noflyRewardScale": 0.5,
+                      "feetAirTimeRewardScale": 0.5, "syncronizeHipRewardScale": -0.00025, "linearVelocityScale": 3.0,
+                      "angularVelocityScale": 0.25, "dofPositionScale": 1.0, "dofVelocityScale": 0.01,
+                      "episodeLength_s": 50, "pushInterval_s": 15},
+            "color": [[1.0, 0.2, 0.2], [0.23, 0.50, 0.92]],
+        },
+        "sim": {"dt": 0.0166, "substeps": 2, "up_axis": "z", "use_gpu_pipeline": True, "gravity": [0.0, 0.0, -9.81]},
+        "task": {"randomize": False, "randomization_params": {}},
+    })

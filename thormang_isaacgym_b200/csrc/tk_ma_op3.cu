@@ -1,0 +1,742 @@
+// MA_OP3 env-step hot path for B200 (sm_100a) -- SURVEY 8(f) row N3 (two OP3 humanoids + one table per env).
+//
+// Replaces, behind the C ABI of include/thormang_b200.h, the TorchScript functions and method bodies of
+// /root/reference/isaacgymenvs/tasks/MA_OP3.py: compute_op3_observations :662-708, compute_op3_reward :550-658,
+// compute_objective_reward :496-547, the contact terms :319-358, compute_observations :411-438, compute_reward :360-409,
+// reset_idx :440-489.  The reference's step hooks are stubs (:309-317); the fused step is the anymal.py:229-242 ordering
+// around those methods (oracle/ma_op3_oracle.py states the assumptions).
+//
+// One CTA = 2 warps = 32 consecutive envs; warp a owns agent a, lane e owns env e.  The six [N,2,*] arrays arrive as
+// cp.async.bulk (TMA) tile copies on one mbarrier (a 32-env tile of every array starts 16-byte aligned); the 4 foot
+// contact rows an agent needs are gathered straight from global memory (12 of the env's 51 body rows are ever read).
+// Each (env, agent) observation row is assembled as float4 groups in a padded shared-memory row (stride 100 words:
+// conflict-free 128-bit stores) and leaves as one 352-byte bulk store; prev_torques / last_actions are refreshed by
+// bulk-storing the torque / action tiles that are already in shared memory.  Warp 1 hands its reward and reset bits
+// to warp 0 through shared memory for the table ("objective") terms.
+//
+// Algorithmic bytes / env-step (F = 4 feet): reads root 156 + dof 352 + torques 176 + prev_torques 176 + actions 176 +
+// last_actions 176 + foot contacts 96 + gripper x-forces 16 + commands 12 + potentials 8 + table potential 4 +
+// air time 32 + last contacts 8 + progress 8 + reset 8 = 1404; writes obs 704 + prev_torques 176 + last_actions 176 +
+// rew 8 + reset 8 + progress 8 + potentials 16 + prev table potential 4 + air time 32 + last contacts 8 + timeout 1
+// = 1141  =>  2545 B.
+#include "tk_common.cuh"
+
+#include <cstdlib>
+#include <new>
+
+namespace tk {
+namespace op3 {
+
+constexpr int kA = TK_OP3_AGENTS;
+constexpr int kRoot = 13;
+constexpr int kActors = 3;
+constexpr int kDof = TK_OP3_DOF;
+constexpr int kObs = TK_OP3_OBS;
+constexpr int kObsPad = 100;             // padded obs row (words): 100 mod 32 = 4 -> conflict-free float4 stores
+constexpr int kTile = 32;
+constexpr int kThreads = kTile * kA;
+constexpr int kMaxFeet = TK_OP3_MAX_FEET;
+
+struct KParams {
+    float* root;
+    const float* init_root;
+    float* dof_state;
+    const float* torques;
+    float* prev_torques;
+    const float* contact;
+    float* commands;
+    float* actions;
+    float* last_actions;
+    float* air_time;
+    uint8_t* last_contacts;
+    float* potentials;
+    float* prev_potentials;
+    float* table_pot;
+    float* prev_table_pot;
+    float* obs;
+    float* rew;
+    long long* reset;
+    long long* progress;
+    uint8_t* timeout;
+    float* ep_return;
+    double* partials;
+    const unsigned long long* grip_counts;   // [agents][2]
+    const float* unit_cmd;
+    unsigned long long seed, step;
+    unsigned long long* step_dev;
+    long long env_off;
+    int noise_mode;
+    int n, nb, max_episode_length, num_feet;
+    int feet[kA][kMaxFeet];
+    int grip[kA][2];
+    int vec_ok;
+    float lin_vel_scale, ang_vel_scale, dof_pos_scale, dof_vel_scale, action_scale, clip_actions, dt;
+    float k_torque, k_up, k_air, k_syns, k_nofly, k_stand, k_rate;     // (float)(scale * dt), MA_OP3.py:80-81
+    float cmd_x[2], cmd_y[2], cmd_yaw[2];   // lo, (hi - lo) formed in double
+    float default_dof_pos[kDof];
+    float inv_start_rot[4], gravity[3], up[3], targets[3], goal[3];
+};
+
+enum { kStreamCmd = 48 };
+
+__device__ __forceinline__ float rand_float(float lo, float span, float u) { return span * u + lo; }   // torch_rand_float
+// torch.norm(dim=1) of two elements
+__device__ __forceinline__ float norm2_ref(float x, float y) { return sqrtf(fmaf(y, y, x * x)); }
+
+struct Smem {
+    alignas(128) float obs[kTile * kA * kObsPad];
+    alignas(16) float root[kTile * kActors * kRoot];
+    alignas(16) float dof[kTile * kA * kDof * 2];
+    alignas(16) float tq[kTile * kA * kDof];
+    alignas(16) float ptq[kTile * kA * kDof];
+    alignas(16) float act[kTile * kA * kDof];
+    alignas(16) float lact[kTile * kA * kDof];
+    float x_rew[kTile];
+    float x_dist[kTile];
+    int x_flag[kTile];
+    alignas(8) uint64_t bar;
+};
+
+// MODE 0: fused post_physics_step; 1: compute_observations; 2: compute_reward
+template <int MODE>
+__global__ void __launch_bounds__(kThreads) op3_tile_kernel(const __grid_constant__ KParams p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem& s = *reinterpret_cast<Smem*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, a = tid >> 5;
+    const int env0 = blockIdx.x * kTile;
+    const int nt = min(kTile, p.n - env0);
+    const long long n = env0 + lane;
+    const bool valid = lane < nt;
+    const bool bulk = p.vec_ok && nt == kTile;
+    const size_t e0 = static_cast<size_t>(env0);
+    constexpr bool kNeedTq = MODE != 1, kNeedDof = true, kNeedAct = true;
+    constexpr uint32_t kRootB = kTile * kActors * kRoot * 4, kDofB = kTile * kA * kDof * 2 * 4, kRowB = kTile * kA * kDof * 4;
+    if (bulk && tid == 0) {
+        mbar_init(&s.bar, 1);
+        fence_proxy_async_smem();
+    }
+    __syncthreads();
+    if (bulk) {
+        if (tid == 0) {
+            mbar_expect_tx(&s.bar, kRootB + kDofB + kRowB + (kNeedTq ? 3 * kRowB : 0));
+            bulk_load(s.dof, p.dof_state + e0 * kA * kDof * 2, kDofB, &s.bar);
+            bulk_load(s.root, p.root + e0 * kActors * kRoot, kRootB, &s.bar);
+            bulk_load(s.act, p.actions + e0 * kA * kDof, kRowB, &s.bar);
+            if (kNeedTq) {
+                bulk_load(s.tq, p.torques + e0 * kA * kDof, kRowB, &s.bar);
+                bulk_load(s.ptq, p.prev_torques + e0 * kA * kDof, kRowB, &s.bar);
+                bulk_load(s.lact, p.last_actions + e0 * kA * kDof, kRowB, &s.bar);
+            }
+        }
+    } else {
+        for (int i = tid; i < nt * kActors * kRoot; i += kThreads) s.root[i] = p.root[e0 * kActors * kRoot + i];
+        for (int i = tid; i < nt * kA * kDof * 2; i += kThreads) s.dof[i] = p.dof_state[e0 * kA * kDof * 2 + i];
+        for (int i = tid; i < nt * kA * kDof; i += kThreads) {
+            s.act[i] = p.actions[e0 * kA * kDof + i];
+            if (kNeedTq) {
+                s.tq[i] = p.torques[e0 * kA * kDof + i];
+                s.ptq[i] = p.prev_torques[e0 * kA * kDof + i];
+                s.lact[i] = p.last_actions[e0 * kA * kDof + i];
+            }
+        }
+    }
+    // ---- per-env scalars and the foot contact rows: issued before the tile wait ----
+    long long prog = 0, rb = 0;
+    bool do_reset = false;
+    float cmd[3] = {0.f, 0.f, 0.f}, pot_old = 0.f, ppot_old = 0.f, tpot = 0.f, ptpot = 0.f, ret_old = 0.f;
+    float cf[kMaxFeet][3], air[kMaxFeet];
+    bool lastc[kMaxFeet];
+    const int nf = p.num_feet;
+    if (valid) {
+        if (MODE != 1) prog = p.progress[n];
+        if (MODE == 0) {
+            prog += 1;
+            do_reset = p.reset[n] != 0;
+            if (do_reset) prog = 0;                                                 // :488
+            if (a == 0 && p.ep_return) ret_old = p.ep_return[n];
+        } else if (MODE == 2) {
+            rb = p.reset[n];
+        }
+#pragma unroll
+        for (int c = 0; c < 3; ++c) cmd[c] = p.commands[n * 3 + c];
+        pot_old = p.potentials[n * kA + a];
+        if (MODE == 2) ppot_old = p.prev_potentials[n * kA + a];
+        tpot = p.table_pot[n];
+        if (MODE == 2) ptpot = p.prev_table_pot[n];
+        if (MODE != 1) {
+#pragma unroll
+            for (int f = 0; f < kMaxFeet; ++f) {
+                if (f < nf) {
+                    const float* row = p.contact + (static_cast<size_t>(n) * p.nb + p.feet[a][f]) * 3;
+                    cf[f][0] = row[0]; cf[f][1] = row[1]; cf[f][2] = row[2];
+                    air[f] = p.air_time[(n * kA + a) * nf + f];
+                    lastc[f] = p.last_contacts[(n * kA + a) * nf + f] != 0;
+                }
+            }
+        }
+    }
+    if (bulk) mbar_wait(&s.bar, 0);
+    else __syncthreads();
+
+    float my_rew = 0.f, my_dist = 0.f;
+    int my_flag = 0;                        // bit 0: up_proj < 0.90, bit 1: distance to the table > 0.40
+    float tb[kRoot];
+    float pot_new = pot_old, ppot_new = ppot_old;
+    if (valid) {
+        float r[kRoot];
+        const int row = lane * kA + a;
+#pragma unroll
+        for (int c = 0; c < kRoot; ++c) r[c] = s.root[(lane * kActors + a) * kRoot + c];
+#pragma unroll
+        for (int c = 0; c < kRoot; ++c) tb[c] = s.root[(lane * kActors + 2) * kRoot + c];
+        float2* dofp = reinterpret_cast<float2*>(s.dof) + row * kDof;
+        const float* act = s.act + row * kDof;
+        bool zero_last = false;
+        if (MODE == 0 && do_reset) {                                                // reset_idx :440-489, this env's lanes
+            float2* gd = reinterpret_cast<float2*>(p.dof_state) + (n * kA + a) * kDof;
+#pragma unroll
+            for (int j = 0; j < kDof; ++j) {
+                const float2 pv = make_float2(p.default_dof_pos[j] + 0.0f, 0.0f);   // :456-457 (offsets are zeros)
+                dofp[j] = pv;
+                gd[j] = pv;
+            }
+            const float* ir = p.init_root + static_cast<size_t>(n) * kActors * kRoot;
+#pragma unroll
+            for (int c = 0; c < kRoot; ++c) {                                       // :468-470
+                r[c] = ir[a * kRoot + c];
+                tb[c] = ir[2 * kRoot + c];
+                p.root[(n * kActors + a) * kRoot + c] = r[c];
+                if (a == 0) p.root[(n * kActors + 2) * kRoot + c] = tb[c];
+            }
+            float uc[3] = {0.5f, 0.5f, 0.5f};
+            if (p.noise_mode == TK_NOISE_PHILOX) {
+                Philox4 d = philox_env(p.seed, effective_step(p.step, p.step_dev), p.env_off + n, kStreamCmd);
+                uc[0] = u01(d.x); uc[1] = u01(d.y); uc[2] = u01(d.z);
+            } else if (p.noise_mode == TK_NOISE_DENSE && p.unit_cmd) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) uc[c] = p.unit_cmd[n * 3 + c];
+            }
+            cmd[0] = rand_float(p.cmd_x[0], p.cmd_x[1], uc[0]);                     // :472
+            cmd[1] = rand_float(p.cmd_y[0], p.cmd_y[1], uc[1]);                     // :473
+            cmd[2] = rand_float(p.cmd_yaw[0], p.cmd_yaw[1], uc[2]);                 // :474
+            pot_old = -norm3_ref(V3{p.goal[0] - r[0], p.goal[1] - r[1], 0.0f}) / p.dt;      // :476-479
+            tpot = -norm3_ref(V3{p.targets[0] - tb[0], p.targets[1] - tb[1], 0.0f}) / p.dt; // :481-484
+            if (a == 0) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) p.commands[n * 3 + c] = cmd[c];
+                p.table_pot[n] = tpot;
+            }
+            zero_last = true;                                                       // :486
+#pragma unroll
+            for (int f = 0; f < kMaxFeet; ++f) air[f] = 0.0f;                       // :487
+        }
+        const Q4 q{r[3], r[4], r[5], r[6]};
+        const V3 ang_raw = quat_rotate_ref<-1>(q, V3{r[10], r[11], r[12]});         // :579 / :693 before scaling
+        if (MODE != 2) {                                                            // compute_observations :411-438
+            ppot_new = pot_old;                                                     // :688
+            pot_new = -norm3_ref(V3{p.goal[0] - r[0], p.goal[1] - r[1], 0.0f}) / p.dt;      // :680-689
+            if (a == 0) ptpot = -norm3_ref(V3{p.targets[0] - tb[0], p.targets[1] - tb[1], p.targets[2] - tb[2]}) / p.dt;   // :418-419
+            const V3 lin = quat_rotate_ref<-1>(q, V3{r[7], r[8], r[9]});            // :692
+            const V3 g = quat_rotate_ref<1>(q, V3{p.gravity[0], p.gravity[1], p.gravity[2]});   // :694
+            float4* o = reinterpret_cast<float4*>(s.obs + row * kObsPad);
+            float v[kObs];
+            v[0] = lin.x * p.lin_vel_scale; v[1] = lin.y * p.lin_vel_scale; v[2] = lin.z * p.lin_vel_scale;
+            v[3] = ang_raw.x * p.ang_vel_scale; v[4] = ang_raw.y * p.ang_vel_scale; v[5] = ang_raw.z * p.ang_vel_scale;
+            v[6] = g.x; v[7] = g.y; v[8] = g.z;
+#pragma unroll
+            for (int j = 0; j < kDof; ++j) {
+                const float2 pv = dofp[j];
+                v[9 + j] = (pv.x - p.default_dof_pos[j]) * p.dof_pos_scale;         // :695
+                v[31 + j] = pv.y * p.dof_vel_scale;
+                v[53 + j] = act[j];
+            }
+#pragma unroll
+            for (int c = 0; c < 10; ++c) v[75 + c] = tb[c];                         // object pose + linvel
+            v[85] = p.targets[0]; v[86] = p.targets[1]; v[87] = p.targets[2];
+#pragma unroll
+            for (int c = 0; c < kObs / 4; ++c) o[c] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+            p.potentials[n * kA + a] = pot_new;
+            p.prev_potentials[n * kA + a] = ppot_new;
+            if (a == 0) p.prev_table_pot[n] = ptpot;
+        }
+        if (MODE != 1) {                                                            // compute_reward :360-409, this agent
+            const float pot_r = (MODE == 2) ? pot_old : pot_new, ppot_r = (MODE == 2) ? ppot_old : ppot_new;
+            const bool moving = norm2_ref(cmd[0], cmd[1]) > 0.1f, still = norm2_ref(cmd[0], cmd[1]) < 0.1f;
+            // _reward_air_time :319-329, _reward_feet_contact_forces :331-334, _reward_no_fly :336-340
+            float air_sum = 0.0f, step_sum = 0.0f;
+            int touching = 0;
+#pragma unroll
+            for (int f = 0; f < kMaxFeet; ++f) {
+                if (f < nf) {
+                    const bool contact = cf[f][2] > 1.1f;
+                    const bool filt = contact || lastc[f];
+                    const bool first = (air[f] > 0.0f) && filt;
+                    const float t = air[f] + p.dt;
+                    air_sum += (t - 0.5f) * (first ? 1.0f : 0.0f);
+                    const float t2 = t * (filt ? 0.0f : 1.0f);
+                    p.air_time[(n * kA + a) * nf + f] = t2;
+                    p.last_contacts[(n * kA + a) * nf + f] = contact ? 1 : 0;
+                    step_sum += fmaxf(norm3_ref(V3{cf[f][0], cf[f][1], cf[f][2]}) - 450.0f, 0.0f);
+                    touching += cf[f][2] > 0.1f ? 1 : 0;
+                }
+            }
+            const float rew_airtime = (air_sum * (moving ? 1.0f : 0.0f)) * p.k_air;
+            const float rew_no_fly = (touching == 1 ? 1.0f : 0.0f) * p.k_nofly;
+            // _reward_gripper_contact_hold :346-358: batch-global counts (tk_ma_op3_grip_counts, all-reduced when sharded)
+            const float hold = (p.grip_counts[a * 2] == 1ull && p.grip_counts[a * 2 + 1] == 1ull) ? 1.0f : 0.0f;
+            // compute_op3_reward :550-658
+            const Q4 torso = quat_mul_ref(q, Q4{p.inv_start_rot[0], p.inv_start_rot[1], p.inv_start_rot[2], p.inv_start_rot[3]});   // :593
+            const float up_proj = quat_rotate_ref<1>(torso, V3{p.up[0], p.up[1], p.up[2]}).z;    // :601-602
+            const float rew_up = up_proj > 0.95f ? 0.0f + p.k_up : 0.0f;           // :605-606
+            const float progress_reward = (pot_r - ppot_r) * 5.0f;                  // :612
+            const float* tqr = s.tq + row * kDof;
+            const float* ptqr = s.ptq + row * kDof;
+            const float* lar = s.lact + row * kDof;
+            float tsum = 0.0f, legsum = 0.0f, ratesum = 0.0f, standsum = 0.0f;
+#pragma unroll
+            for (int j = 0; j < kDof; ++j) {
+                tsum += fabsf(ptqr[j] - tqr[j]);                                    // :619
+                const float dev = fabsf(dofp[j].x - p.default_dof_pos[j]);
+                standsum += dev;                                                    // :630
+                if ((j >= 2 && j <= 7) || (j >= 11 && j <= 17) || j == 21) legsum += dev;   // :622-623
+                const float la = zero_last ? 0.0f : lar[j];
+                const float da = la - act[j];
+                ratesum += da * da;                                                 // :627
+            }
+            const float rew_torque = tsum * p.k_torque;
+            const float rew_syns = legsum * p.k_syns;                               // :624
+            const float rew_action_rate = ratesum * p.k_rate;
+            const float rew_stand_still = (standsum * (still ? 1.0f : 0.0f)) * p.k_stand;
+            const float dz = p.targets[2] - ang_raw.z;
+            const float rew_ang_vel_z = expf(-(dz * dz) / 0.1f) * 0.1f;             // :632-633
+            my_dist = norm3_ref(V3{r[0] - tb[0], r[1] - tb[1], r[2] - tb[2]});      // :644
+            const float rew_distobject = expf(-my_dist / 0.32f) * 0.5f;             // :645
+            float total = progress_reward + 2.0f;                                   // :648-649, left to right (rew_orient is -0)
+            total += rew_torque; total += rew_up; total += rew_airtime; total += rew_ang_vel_z; total += step_sum;
+            total += rew_no_fly; total += rew_stand_still; total += rew_action_rate; total += rew_syns;
+            total += rew_distobject; total += hold;
+            my_rew = fmaxf(total, 0.0f);                                            // :650
+            my_flag = (up_proj < 0.90f ? 1 : 0) | (my_dist > 0.40f ? 2 : 0);        // :654-655
+        }
+    }
+    if (MODE == 1) {
+        __syncthreads();
+    } else {
+        if (a == 1) { s.x_rew[lane] = my_rew; s.x_dist[lane] = my_dist; s.x_flag[lane] = my_flag; }
+        __syncthreads();
+    }
+    float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_d0 = 0.f, st_d1 = 0.f;
+    bool out_reset = false, out_timeout = false;
+    if (MODE != 1 && a == 0 && valid) {
+        const float rew1 = s.x_rew[lane];
+        const int flag1 = s.x_flag[lane];
+        // reset_buf through the two compute_op3_reward calls (:653-656) ...
+        long long rv = rb;
+        const bool over = prog >= p.max_episode_length;
+        if (over) rv = 1;
+        if (my_flag) rv = 1;
+        if (prog == 0) rv = 0;
+        if (over) rv = 1;
+        if (flag1) rv = 1;
+        if (prog == 0) rv = 0;
+        // ... and compute_objective_reward :496-547
+        const Q4 tq{tb[3], tb[4], tb[5], tb[6]};
+        const float tup = quat_rotate_ref<1>(tq, V3{p.up[0], p.up[1], p.up[2]}).z;  // :528-529
+        const float rew_up = tup > 0.98f ? 0.0f + 0.1f : 0.0f;                      // :532-533
+        const float hz = tb[2] - 0.29f;
+        const float rew_h = (hz * hz) * -0.001f;                                    // :536
+        const float dist_rew = (tpot - ptpot) * 5.0f;                               // :540
+        const float r0 = ((my_rew + dist_rew) + rew_up) + rew_h;                    // :542
+        const float r1 = ((rew1 + dist_rew) + rew_up) + rew_h;
+        if (tup < 0.90f) rv = 1;                                                    // :544
+        if (tb[2] < 0.25f) rv = 1;                                                  // :545
+        *reinterpret_cast<float2*>(p.rew + n * kA) = make_float2(r0, r1);
+        p.reset[n] = rv;
+        out_reset = rv != 0;
+        st_rew = r0 + r1; st_d0 = my_dist; st_d1 = s.x_dist[lane];
+        if (MODE == 0) {
+            p.progress[n] = prog;
+            out_timeout = (prog >= p.max_episode_length - 1) && out_reset;          // multi_vec_task.py:193
+            if (p.timeout) p.timeout[n] = out_timeout ? 1 : 0;
+            if (p.ep_return) {
+                const float ret = (do_reset ? 0.0f : ret_old) + (r0 + r1);
+                if (out_reset) st_ret = ret;
+                p.ep_return[n] = ret;
+            }
+            if (out_reset) st_len = static_cast<float>(prog);
+        }
+    }
+    if (MODE == 0 && a == 0) {
+        const unsigned m_reset = __ballot_sync(0xffffffffu, out_reset), m_to = __ballot_sync(0xffffffffu, out_timeout);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            st_rew += __shfl_xor_sync(0xffffffffu, st_rew, o);
+            st_ret += __shfl_xor_sync(0xffffffffu, st_ret, o);
+            st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
+            st_d0 += __shfl_xor_sync(0xffffffffu, st_d0, o);
+            st_d1 += __shfl_xor_sync(0xffffffffu, st_d1, o);
+        }
+        double* pr = p.partials + static_cast<size_t>(blockIdx.x & (kStatSlots - 1)) * TK_STATS;
+        const float vals[TK_STATS] = {st_rew, static_cast<float>(__popc(m_reset)), static_cast<float>(__popc(m_to)), st_ret,
+                                      st_len, st_d0, st_d1, static_cast<float>(nt)};
+        if (lane < TK_STATS) atomicAdd(pr + lane, static_cast<double>(vals[lane]));
+    }
+    // ---- stores: one 352-byte bulk store per (env, agent) obs row; prev_torques / last_actions from the resident tiles ----
+    if (bulk) {
+        if (MODE != 2) {
+            fence_proxy_async_smem();
+            bulk_store(p.obs + (e0 * kA + lane * kA + a) * kObs, s.obs + (lane * kA + a) * kObsPad, kObs * 4);
+        }
+        if (MODE == 0 && tid == 0) {
+            bulk_store(p.prev_torques + e0 * kA * kDof, s.tq, kRowB);                // end-of-step refresh (see header)
+            bulk_store(p.last_actions + e0 * kA * kDof, s.act, kRowB);
+        }
+        if (MODE != 2 || tid == 0) {
+            bulk_commit();
+            bulk_wait_read<0>();
+        }
+    } else {
+        if (MODE != 2)
+            for (int i = tid; i < nt * kA * kObs; i += kThreads) p.obs[e0 * kA * kObs + i] = s.obs[(i / kObs) * kObsPad + i % kObs];
+        if (MODE == 0)
+            for (int i = tid; i < nt * kA * kDof; i += kThreads) {
+                p.prev_torques[e0 * kA * kDof + i] = s.tq[i];
+                p.last_actions[e0 * kA * kDof + i] = s.act[i];
+            }
+    }
+}
+
+// un-stubbed pre_physics_step (anymal.py:229-232 + clamp vec_task.py:327): flat stream over N*2*22 floats
+__global__ void __launch_bounds__(256) op3_pre_kernel(const __grid_constant__ KParams p, const float* __restrict__ actions_in,
+                                                       float* __restrict__ targets, int clip) {
+    const long long total = static_cast<long long>(p.n) * kA * kDof;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        float a = actions_in[i];
+        if (clip) a = fminf(fmaxf(a, -p.clip_actions), p.clip_actions);
+        p.actions[i] = a;
+        targets[i] = p.action_scale * a + p.default_dof_pos[i % kDof];
+    }
+}
+
+// _reward_gripper_contact_hold :351-352: how many envs press the left / right gripper (x force > 0.1), per agent
+__global__ void __launch_bounds__(256) op3_grip_count_kernel(const __grid_constant__ KParams p, unsigned long long* __restrict__ counts) {
+    int c[kA * 2] = {0, 0, 0, 0};
+    for (long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; e < p.n;
+         e += static_cast<long long>(gridDim.x) * blockDim.x) {
+#pragma unroll
+        for (int k = 0; k < kA * 2; ++k)
+            c[k] += p.contact[(static_cast<size_t>(e) * p.nb + p.grip[k >> 1][k & 1]) * 3] > 0.1f ? 1 : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < kA * 2; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c[k] += __shfl_xor_sync(0xffffffffu, c[k], o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < kA * 2; ++k)
+            if (c[k]) atomicAdd(counts + k, static_cast<unsigned long long>(c[k]));
+    }
+}
+
+// reset_idx :440-489 for an explicit id list
+__global__ void op3_reset_idx_kernel(const __grid_constant__ KParams p, const long long* __restrict__ ids, int k,
+                                     const float* __restrict__ unit_cmd) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= k) return;
+    const long long ne = ids[i];
+    if (ne < 0 || ne >= p.n) return;
+    float2* gd = reinterpret_cast<float2*>(p.dof_state) + ne * kA * kDof;
+    for (int j = 0; j < kA * kDof; ++j) gd[j] = make_float2(p.default_dof_pos[j % kDof] + 0.0f, 0.0f);     // :456-457
+    const float* ir = p.init_root + static_cast<size_t>(ne) * kActors * kRoot;
+    for (int c = 0; c < kActors * kRoot; ++c) p.root[ne * kActors * kRoot + c] = ir[c];                   // :468-470
+    p.commands[ne * 3 + 0] = rand_float(p.cmd_x[0], p.cmd_x[1], unit_cmd[static_cast<size_t>(i) * 3 + 0]);
+    p.commands[ne * 3 + 1] = rand_float(p.cmd_y[0], p.cmd_y[1], unit_cmd[static_cast<size_t>(i) * 3 + 1]);
+    p.commands[ne * 3 + 2] = rand_float(p.cmd_yaw[0], p.cmd_yaw[1], unit_cmd[static_cast<size_t>(i) * 3 + 2]);
+    for (int a = 0; a < kA; ++a) {
+        const float pot = -norm3_ref(V3{p.goal[0] - ir[a * kRoot], p.goal[1] - ir[a * kRoot + 1], 0.0f}) / p.dt;   // :476-479
+        p.prev_potentials[ne * kA + a] = pot;
+        p.potentials[ne * kA + a] = pot;
+        for (int j = 0; j < kDof; ++j) p.last_actions[(ne * kA + a) * kDof + j] = 0.0f;                   // :486
+        for (int f = 0; f < p.num_feet; ++f) p.air_time[(ne * kA + a) * p.num_feet + f] = 0.0f;          // :487
+    }
+    const float tpot = -norm3_ref(V3{p.targets[0] - ir[2 * kRoot], p.targets[1] - ir[2 * kRoot + 1], 0.0f}) / p.dt;   // :481-484
+    p.prev_table_pot[ne] = tpot;
+    p.table_pot[ne] = tpot;
+    p.progress[ne] = 0;                                                             // :488
+    p.reset[ne] = 0;                                                                // :489
+}
+
+__global__ void op3_philox_kernel(int n, unsigned long long seed, unsigned long long step, long long env_off,
+                                  const unsigned long long* __restrict__ epoch, float* uc) {
+    step = effective_step(step, epoch);
+    const long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    Philox4 d = philox_env(seed, step, env_off + e, kStreamCmd);
+    uc[e * 3] = u01(d.x); uc[e * 3 + 1] = u01(d.y); uc[e * 3 + 2] = u01(d.z);
+}
+
+__global__ void op3_stats_finalize_kernel(double* __restrict__ partials, int rows, double* __restrict__ out, int accumulate) {
+    const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (k >= TK_STATS) return;
+    double acc = 0.0;
+    for (int r = lane; r < rows; r += 32) {
+        acc += partials[static_cast<size_t>(r) * TK_STATS + k];
+        partials[static_cast<size_t>(r) * TK_STATS + k] = 0.0;
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) out[k] = accumulate ? out[k] + acc : acc;
+}
+
+}  // namespace op3
+}  // namespace tk
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+using namespace tk;
+using namespace tk::op3;
+
+struct TkOp3 {
+    TkOp3Params params;
+    TkOp3Buffers buf;
+    bool bound, ran, counted;
+    int tiles, sm_count;
+    double* partials;
+    unsigned long long* step_dev;
+};
+
+static void fill_kparams(const TkOp3* h, KParams& k) {
+    const TkOp3Params& P = h->params;
+    const TkOp3Buffers& B = h->buf;
+    k.root = B.root_states; k.init_root = B.initial_root_states; k.dof_state = B.dof_state; k.torques = B.torques;
+    k.prev_torques = B.prev_torques; k.contact = B.contact_forces; k.commands = B.commands; k.actions = B.actions;
+    k.last_actions = B.last_actions; k.air_time = B.feet_air_time; k.last_contacts = B.last_contacts;
+    k.potentials = B.potentials; k.prev_potentials = B.prev_potentials; k.table_pot = B.table_potentials;
+    k.prev_table_pot = B.prev_table_potentials; k.obs = B.obs_buf; k.rew = B.rew_buf;
+    k.reset = reinterpret_cast<long long*>(B.reset_buf); k.progress = reinterpret_cast<long long*>(B.progress_buf);
+    k.timeout = B.timeout_buf; k.ep_return = B.episode_return; k.partials = h->partials;
+    k.grip_counts = reinterpret_cast<const unsigned long long*>(B.grip_counts);
+    k.unit_cmd = nullptr; k.seed = 0; k.step = 0; k.step_dev = h->step_dev; k.env_off = 0; k.noise_mode = TK_NOISE_NONE;
+    k.n = P.num_envs; k.nb = P.num_bodies_total; k.max_episode_length = P.max_episode_length; k.num_feet = P.num_feet;
+    for (int a = 0; a < kA; ++a) {
+        for (int f = 0; f < kMaxFeet; ++f) k.feet[a][f] = P.feet_indices[a][f];
+        k.grip[a][0] = P.gripper_indices[a][0]; k.grip[a][1] = P.gripper_indices[a][1];
+    }
+    k.vec_ok = aligned_to(B.root_states, 16) && aligned_to(B.dof_state, 16) && aligned_to(B.torques, 16) &&
+               aligned_to(B.prev_torques, 16) && aligned_to(B.actions, 16) && aligned_to(B.last_actions, 16) &&
+               aligned_to(B.obs_buf, 16);
+    k.lin_vel_scale = P.lin_vel_scale; k.ang_vel_scale = P.ang_vel_scale; k.dof_pos_scale = P.dof_pos_scale;
+    k.dof_vel_scale = P.dof_vel_scale; k.action_scale = P.action_scale; k.clip_actions = P.clip_actions;
+    k.dt = static_cast<float>(P.dt);
+    k.k_torque = static_cast<float>(P.rew_torque * P.dt); k.k_up = static_cast<float>(P.rew_up * P.dt);
+    k.k_air = static_cast<float>(P.rew_air_time * P.dt); k.k_syns = static_cast<float>(P.rew_syns_hip * P.dt);
+    k.k_nofly = static_cast<float>(P.rew_no_fly * P.dt); k.k_stand = static_cast<float>(P.rew_stand * P.dt);
+    k.k_rate = static_cast<float>(P.rew_action_rate * P.dt);
+    k.cmd_x[0] = static_cast<float>(P.command_x_range[0]); k.cmd_x[1] = static_cast<float>(P.command_x_range[1] - P.command_x_range[0]);
+    k.cmd_y[0] = static_cast<float>(P.command_y_range[0]); k.cmd_y[1] = static_cast<float>(P.command_y_range[1] - P.command_y_range[0]);
+    k.cmd_yaw[0] = static_cast<float>(P.command_yaw_range[0]);
+    k.cmd_yaw[1] = static_cast<float>(P.command_yaw_range[1] - P.command_yaw_range[0]);
+    for (int j = 0; j < kDof; ++j) k.default_dof_pos[j] = P.default_dof_pos[j];
+    for (int c = 0; c < 4; ++c) k.inv_start_rot[c] = P.inv_start_rot[c];
+    for (int c = 0; c < 3; ++c) {
+        k.gravity[c] = P.gravity_vec[c]; k.up[c] = P.up_vec[c]; k.targets[c] = P.targets[c]; k.goal[c] = P.goal_pos[c];
+    }
+}
+
+static int check_bound(const TkOp3* h) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_REQUIRE(h->bound, TK_ERR_UNBOUND, "tk_ma_op3_bind was not called");
+    return TK_OK;
+}
+
+template <int MODE>
+static cudaError_t launch_tile(const TkOp3* h, const KParams& k, cudaStream_t st) {
+    static bool opted = false;
+    if (!opted) {
+        cudaError_t e = cudaFuncSetAttribute(op3_tile_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(sizeof(Smem)));
+        if (e != cudaSuccess) return e;
+        opted = true;
+    }
+    op3_tile_kernel<MODE><<<h->tiles, kThreads, sizeof(Smem), st>>>(k);
+    return cudaGetLastError();
+}
+
+static int count_grips(TkOp3* h, const KParams& k, cudaStream_t st) {
+    unsigned long long* counts = reinterpret_cast<unsigned long long*>(h->buf.grip_counts);
+    TK_CUDA(cudaMemsetAsync(counts, 0, sizeof(unsigned long long) * kA * 2, st));
+    int blocks = (k.n + 255) / 256;
+    if (blocks > h->sm_count * 8) blocks = h->sm_count * 8;
+    op3_grip_count_kernel<<<blocks, 256, 0, st>>>(k, counts);
+    TK_CUDA(cudaGetLastError());
+    h->counted = true;
+    return TK_OK;
+}
+
+extern "C" {
+
+int tk_ma_op3_create(const TkOp3Params* params, TkOp3** out) {
+    TK_REQUIRE(params && out, TK_ERR_INVALID, "null argument");
+    TK_REQUIRE(params->num_envs > 0, TK_ERR_INVALID, "num_envs must be positive (got %d)", params->num_envs);
+    TK_REQUIRE(params->num_agents == kA && params->num_dof == kDof, TK_ERR_INVALID,
+               "this build serves the 2-agent / 22-DOF OP3 of MA_OP3.py (got %d agents, %d DOFs)", params->num_agents,
+               params->num_dof);
+    TK_REQUIRE(params->num_feet >= 0 && params->num_feet <= kMaxFeet, TK_ERR_INVALID, "bad num_feet %d", params->num_feet);
+    TK_REQUIRE(params->num_grippers >= 2 && params->num_grippers <= TK_OP3_MAX_GRIPPERS, TK_ERR_INVALID,
+               "num_grippers must be 2..%d (got %d): _reward_gripper_contact_hold reads grippers [0] and [1]",
+               TK_OP3_MAX_GRIPPERS, params->num_grippers);
+    TK_REQUIRE(params->num_bodies_total > 0, TK_ERR_INVALID, "num_bodies_total must be positive");
+    for (int a = 0; a < kA; ++a) {
+        for (int f = 0; f < params->num_feet; ++f)
+            TK_REQUIRE(params->feet_indices[a][f] >= 0 && params->feet_indices[a][f] < params->num_bodies_total, TK_ERR_INVALID,
+                       "feet index out of range");
+        for (int g = 0; g < 2; ++g)
+            TK_REQUIRE(params->gripper_indices[a][g] >= 0 && params->gripper_indices[a][g] < params->num_bodies_total,
+                       TK_ERR_INVALID, "gripper index out of range");
+    }
+    TK_CUDA(cudaSetDevice(params->device));
+    TkOp3* h = new (std::nothrow) TkOp3();
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "out of host memory");
+    h->params = *params;
+    h->bound = false; h->ran = false; h->counted = false;
+    h->tiles = (params->num_envs + kTile - 1) / kTile;
+    h->sm_count = 148;
+    cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, params->device);
+    h->partials = nullptr; h->step_dev = nullptr;
+    cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
+    if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * kStatSlots);
+    if (e == cudaSuccess) e = cudaMalloc(&h->step_dev, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(h->step_dev, 0, sizeof(unsigned long long));
+    if (e != cudaSuccess) {
+        cudaFree(h->partials); cudaFree(h->step_dev);
+        delete h;
+        return cuda_fail(e, "tk_ma_op3_create");
+    }
+    *out = h;
+    return TK_OK;
+}
+
+int tk_ma_op3_destroy(TkOp3* h) {
+    if (!h) return TK_OK;
+    cudaSetDevice(h->params.device);
+    cudaFree(h->partials); cudaFree(h->step_dev);
+    delete h;
+    return TK_OK;
+}
+
+int tk_ma_op3_bind(TkOp3* h, const TkOp3Buffers* b) {
+    TK_REQUIRE(h && b, TK_ERR_INVALID, "null argument");
+    const void* req[] = {b->root_states, b->initial_root_states, b->dof_state, b->torques, b->prev_torques, b->contact_forces,
+                         b->commands, b->actions, b->last_actions, b->feet_air_time, b->potentials, b->prev_potentials,
+                         b->table_potentials, b->prev_table_potentials, b->obs_buf, b->rew_buf, b->reset_buf, b->progress_buf};
+    const char* names[] = {"root_states", "initial_root_states", "dof_state", "torques", "prev_torques", "contact_forces",
+                           "commands", "actions", "last_actions", "feet_air_time", "potentials", "prev_potentials",
+                           "table_potentials", "prev_table_potentials", "obs_buf", "rew_buf", "reset_buf", "progress_buf"};
+    for (unsigned i = 0; i < sizeof(req) / sizeof(req[0]); ++i) {
+        TK_REQUIRE(req[i] != nullptr, TK_ERR_UNBOUND, "buffer %s is NULL", names[i]);
+        TK_REQUIRE(aligned_to(req[i], 4), TK_ERR_ALIGN, "buffer %s is not 4-byte aligned", names[i]);
+    }
+    TK_REQUIRE(b->last_contacts != nullptr, TK_ERR_UNBOUND, "buffer last_contacts is NULL");
+    TK_REQUIRE(b->grip_counts != nullptr && aligned_to(b->grip_counts, 8), TK_ERR_UNBOUND, "buffer grip_counts is NULL or misaligned");
+    TK_REQUIRE(aligned_to(b->reset_buf, 8) && aligned_to(b->progress_buf, 8), TK_ERR_ALIGN, "int64 buffers must be 8-byte aligned");
+    TK_REQUIRE(aligned_to(b->dof_state, 8) && aligned_to(b->rew_buf, 8), TK_ERR_ALIGN,
+               "dof_state ((pos,vel) pairs) and rew_buf ([N,2] rows) must be 8-byte aligned");
+    h->buf = *b;
+    h->bound = true;
+    return TK_OK;
+}
+
+int tk_ma_op3_pre_physics(TkOp3* h, const float* actions_in, float* targets_out, int32_t clip, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(actions_in && targets_out, TK_ERR_INVALID, "null argument");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    const long long total = static_cast<long long>(k.n) * kA * kDof;
+    long long blocks = (total + 255) / 256;
+    if (blocks > static_cast<long long>(h->sm_count) * 16) blocks = static_cast<long long>(h->sm_count) * 16;
+    op3_pre_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(k, actions_in, targets_out, clip);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_ma_op3_grip_counts(TkOp3* h, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    return count_grips(h, k, static_cast<cudaStream_t>(stream));
+}
+
+int tk_ma_op3_compute_observations(TkOp3* h, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    TK_CUDA(launch_tile<1>(h, k, static_cast<cudaStream_t>(stream)));
+    return TK_OK;
+}
+
+int tk_ma_op3_compute_reward(TkOp3* h, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(h->counted, TK_ERR_INVALID, "tk_ma_op3_grip_counts must run before tk_ma_op3_compute_reward");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    TK_CUDA(launch_tile<2>(h, k, static_cast<cudaStream_t>(stream)));
+    return TK_OK;
+}
+
+int tk_ma_op3_reset_idx(TkOp3* h, const int64_t* env_ids, int32_t kcount, const float* unit_cmd, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    if (kcount == 0) return TK_OK;
+    TK_REQUIRE(kcount > 0 && env_ids && unit_cmd, TK_ERR_INVALID, "bad reset_idx arguments");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    op3_reset_idx_kernel<<<(kcount + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        k, reinterpret_cast<const long long*>(env_ids), kcount, unit_cmd);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_ma_op3_post_physics(TkOp3* h, const TkOp3Noise* noise, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(noise != nullptr, TK_ERR_INVALID, "null noise descriptor");
+    TK_REQUIRE(noise->mode == TK_NOISE_NONE || noise->mode == TK_NOISE_DENSE || noise->mode == TK_NOISE_PHILOX, TK_ERR_INVALID,
+               "noise mode %d: MA_OP3 takes TK_NOISE_NONE, TK_NOISE_DENSE (row n = env n) or TK_NOISE_PHILOX", noise->mode);
+    TK_REQUIRE(h->counted, TK_ERR_INVALID, "tk_ma_op3_grip_counts must run before tk_ma_op3_post_physics");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    k.noise_mode = noise->mode;
+    if (noise->mode == TK_NOISE_DENSE) k.unit_cmd = noise->unit_cmd;
+    k.seed = noise->seed; k.step = noise->step; k.env_off = noise->env_id_offset;
+    TK_CUDA(launch_tile<0>(h, k, static_cast<cudaStream_t>(stream)));
+    h->ran = true;
+    return TK_OK;
+}
+
+int tk_ma_op3_advance_epoch(TkOp3* h, void* stream) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    advance_epoch_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(h->step_dev);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_ma_op3_stats(TkOp3* h, double* stats_out, int32_t accumulate, void* stream) {
+    TK_REQUIRE(h && stats_out, TK_ERR_INVALID, "null argument");
+    TK_REQUIRE(h->ran, TK_ERR_INVALID, "tk_ma_op3_post_physics has not run yet");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    op3_stats_finalize_kernel<<<1, TK_STATS * 32, 0, static_cast<cudaStream_t>(stream)>>>(h->partials, kStatSlots, stats_out, accumulate);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int tk_ma_op3_philox_noise(TkOp3* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* unit_cmd, void* stream) {
+    TK_REQUIRE(h != nullptr && unit_cmd != nullptr, TK_ERR_INVALID, "null argument");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    op3_philox_kernel<<<(h->params.num_envs + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        h->params.num_envs, seed, step, env_id_offset, h->step_dev, unit_cmd);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+}  // extern "C"

@@ -25,8 +25,10 @@ import torch
 class FakeSim:
     def __init__(self, num_envs: int, num_dof: int, device, num_sensor_floats: int = 12,
                  dof_names: Optional[List[str]] = None, asset: Optional[Dict[str, torch.Tensor]] = None,
-                 physics: Optional[Callable[["FakeSim"], None]] = None, slab: bool = False, num_bodies: int = 0):
+                 physics: Optional[Callable[["FakeSim"], None]] = None, slab: bool = False, num_bodies: int = 0,
+                 actors_per_env: int = 1):
         self.num_envs, self.num_dof, self.device = num_envs, num_dof, torch.device(device)
+        self.actors_per_env = actors_per_env
         f = dict(dtype=torch.float32, device=self.device)
         # net contact forces [N*bodies, 3] (anymal.py:113,124), only for tasks that read them
         self.num_bodies = num_bodies
@@ -51,7 +53,8 @@ class FakeSim:
             self.actions_view = cut(4, (num_envs, num_dof))
             self.slab_layout = dict(zip(("root_states", "dof_state", "dof_force", "sensors", "actions"), zip(offs, sizes)))
         else:
-            self.root_states = torch.zeros((num_envs, 13), **f)
+            # actors_per_env > 1 (MA_OP3.py:78-98: two robots + a table): [N * actors, 13], num_dof = DOFs per env
+            self.root_states = torch.zeros((num_envs * actors_per_env, 13), **f)
             self.dof_state = torch.zeros((num_envs * num_dof, 2), **f)
             self.dof_force = torch.zeros((num_envs, num_dof), **f)
             self.force_sensor = torch.zeros((num_envs, num_sensor_floats), **f)
