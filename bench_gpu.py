@@ -105,8 +105,31 @@ def _make_anymal(n, seed, device, env_off=0):
     return env, st
 
 
-_MAKERS = {"anymal": _make_anymal, "humanoid": _make_humanoid, "gogoro": _make_gogoro, "gogoro_paper": _make_gogoro_paper}
-_LAUNCHES_PER_STEP = {"anymal": 1, "humanoid": 1, "gogoro": 1, "gogoro_paper": 2}   # the paper variant: fused kernel + reward finalize
+def _make_ma_op3(n, seed, device, env_off=0):
+    """MA_OP3: two OP3 + table per env, 51 rigid bodies; ~1 % of the envs in reset per step."""
+    import torch
+    from thormang_isaacgym_b200 import config as tcfg
+    from thormang_isaacgym_b200 import synthetic as syn
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.MA_OP3 import MA_OP3
+    st = syn.ma_op3_state(n, seed=seed)
+    cfg = tcfg.ma_op3_cfg(n, seed=1234)
+    cfg["env"]["envIdOffset"] = env_off
+    cfg["env"]["resetOnInit"] = False
+    nb = st["contact_forces"].shape[1]
+    sim = FakeSim(n, 44, device, num_sensor_floats=0, dof_names=list(tcfg.OP3_DOF_NAMES), num_bodies=nb, actors_per_env=3)
+    sim.load_state(st)
+    cfg["sim_backend"] = sim
+    dev_index = torch.device(device).index or 0
+    env = MA_OP3(cfg, device, f"cuda:{dev_index}", -1, True)
+    for name in ("prev_torques", "commands", "actions", "last_actions", "feet_air_time", "last_contacts", "potentials",
+                 "prev_potentials", "table_potentials", "progress_buf", "reset_buf"):
+        getattr(env, name).copy_(st[name].to(device))
+    return env, st
+
+
+_MAKERS = {"ma_op3": _make_ma_op3, "anymal": _make_anymal, "humanoid": _make_humanoid, "gogoro": _make_gogoro, "gogoro_paper": _make_gogoro_paper}
+_LAUNCHES_PER_STEP = {"ma_op3": 2, "anymal": 1, "humanoid": 1, "gogoro": 1, "gogoro_paper": 2}   # the paper variant: fused kernel + reward finalize
 
 
 def _rotating_sets(n, bytes_per_env):
@@ -383,6 +406,8 @@ def run_gpu_arm(args, rank, world):
                                     ("gogoro_4194304", "gogoro", 4194304, False),
                                     ("n2_anymal_65536", "anymal", 65536, False),
                                     ("n2_anymal_1048576", "anymal", 1048576, False),
+                                    ("n3_ma_op3_65536", "ma_op3", 65536, False),
+                                    ("n3_ma_op3_524288", "ma_op3", 524288, False),
                                     ("n1_gogoro_paper_4096", "gogoro_paper", 4096, False),
                                     ("n1_gogoro_paper_65536", "gogoro_paper", 65536, False),
                                     ("n1_gogoro_paper_262144", "gogoro_paper", 262144, False),

@@ -613,8 +613,13 @@ int tk_ma_op3_compute_reward(TkOp3* h, void* stream);
 /* reset_idx (:440-489): env_ids[k] int64, unit_cmd [k,3]. */
 int tk_ma_op3_reset_idx(TkOp3* h, const int64_t* env_ids, int32_t k, const float* unit_cmd, void* stream);
 /* progress += 1, reset prologue, compute_observations, compute_reward, prev_torques / last_actions refresh and the
- * timeout line (multi_vec_task.py:193) as ONE fused kernel. */
+ * timeout line (multi_vec_task.py:193) as ONE fused kernel.  The kernel also counts the gripper contacts of :351-352
+ * into grip_counts (no pre-pass) and writes rewards with _reward_gripper_contact_hold = 0; it MUST be followed by
+ * tk_ma_op3_finalize_reward on the same stream -- after an all-reduce (SUM) of grip_counts when the envs are sharded. */
 int tk_ma_op3_post_physics(TkOp3* h, const TkOp3Noise* noise, void* stream);
+/* Adds the batch-global hold term (:346-358, :648-650) to the rewards of the agents whose counts are exactly (1, 1);
+ * a grid that exits immediately otherwise. */
+int tk_ma_op3_finalize_reward(TkOp3* h, void* stream);
 int tk_ma_op3_advance_epoch(TkOp3* h, void* stream);
 /* stats: sum reward (both agents), #reset, #timeout, sum episode_return / length of reset envs, sum agent-0 / agent-1
  * distance to the table, N */

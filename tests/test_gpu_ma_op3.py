@@ -117,3 +117,98 @@ def test_fused_post_physics(n):
     U.exact(env.last_actions, orc.last_actions, "last_actions (end-of-step refresh)")
     _check_obs_side(env, orc, "fused")
     _check_reward_side(env, orc, "fused")
+
+
+def _one_holder_state(n, seed):
+    """Exactly one env presses each gripper of agent 0 (hold term = 1); agent 1 has two left presses (0)."""
+    st = syn.ma_op3_state(n, seed=seed)
+    _, grip = syn.ma_op3_body_indices()
+    cf = st["contact_forces"]
+    cf[:, grip.flatten(), 0] = 0.0
+    cf[n // 3, grip[0, 0], 0] = 0.5
+    cf[n // 2, grip[0, 1], 0] = 0.7
+    cf[1, grip[1, 0], 0] = 0.5
+    cf[n - 1, grip[1, 0], 0] = 0.5
+    cf[2, grip[1, 1], 0] = 0.9
+    return st
+
+
+@pytest.mark.parametrize("n", [40, 4096])
+def test_fused_hold_term(n):
+    """_reward_gripper_contact_hold (:346-358) is a batch-global 0/1: counted inside the fused kernel, added by finalize."""
+    st = _one_holder_state(n, seed=77)
+    env, orc, _ = U.make_ma_op3_pair(n, seed=77, state=st)
+    uc = syn.ma_op3_reset_noise(n, seed=5)
+    ids = orc.reset_buf.nonzero(as_tuple=False).squeeze(-1)
+    env.post_physics_step(uc.to(DEV))
+    orc.post_physics_step(uc[ids])
+    torch.cuda.synchronize()
+    assert env.grip_count_buf.tolist() == [[1, 1], [2, 1]]
+    _check_reward_side(env, orc, "hold")
+    s = env.episode_statistics().cpu()
+    assert abs(float(s[0]) - float(env.rew_buf.double().sum())) < 1e-3 * n
+    assert abs(float(env.episode_return.double().sum()) - float(env.rew_buf.double().sum())) < 1e-3 * n
+
+
+def test_philox_mode_and_rollout():
+    n = 2048
+    env, orc, st = U.make_ma_op3_pair(n, seed=21)
+    g = torch.Generator().manual_seed(3)
+    for step in range(6):
+        a = torch.rand((n, 2, 22), generator=g) * 3 - 1.5
+        env._clip_in_kernel = True
+        env.pre_physics_step(a.to(DEV))
+        env._clip_in_kernel = False
+        orc.pre_physics_step(a, clip=True)
+        uc = env.philox_noise().cpu()
+        ids = orc.reset_buf.nonzero(as_tuple=False).squeeze(-1)
+        env.post_physics_step()                        # in-kernel Philox
+        orc.post_physics_step(uc[ids])
+        torch.cuda.synchronize()
+        U.exact(env.reset_buf, orc.reset_buf, f"step {step} reset_buf")
+        U.exact(env.progress_buf, orc.progress_buf, f"step {step} progress_buf")
+        U.exact(env.dof_state, orc.dof_state, f"step {step} dof_state")
+        U.exact(env.commands, orc.commands, f"step {step} commands")
+        U.exact(env.pd_targets, orc.pd_targets, f"step {step} targets")
+        _check_obs_side(env, orc, f"step {step}")
+        _check_reward_side(env, orc, f"step {step}")
+
+
+def test_step_api_and_statistics():
+    import thormang_isaacgym_b200 as pkg
+    env = pkg.make(seed=3, task="MA_OP3", num_envs=128, sim_device=DEV, rl_device=DEV)
+    obs_d, rew, reset, extras = env.step(env.zero_actions())
+    assert obs_d["obs"].shape == (128, 2, 88) and rew.shape == (128, 2) and reset.dtype == torch.int64
+    assert float(obs_d["obs"].abs().max()) <= 5.0                         # clipObservations, MA_OP3.yaml
+    assert extras["time_outs"].dtype == torch.bool
+    s = env.episode_statistics().cpu()
+    assert int(s[7]) == 128 and abs(float(s[0]) - float(env.rew_buf.double().sum())) < 1e-4
+
+
+def test_unaligned_and_sharded():
+    """Two shards (cut not a multiple of 32) with the gripper counts summed across them == the unsharded run."""
+    n = 4096 + 17
+    st = _one_holder_state(n, seed=33)
+    uc = syn.ma_op3_reset_noise(n, seed=34)
+    full, _, _ = U.make_ma_op3_pair(n, seed=33, state=st)
+    full.post_physics_step(uc.to(DEV))
+    cut = 1000
+    parts = []
+    for sl in (slice(0, cut), slice(cut, n)):
+        m = sl.stop - sl.start
+        sub = {}
+        for k, v in st.items():
+            per = v.shape[0] // n
+            sub[k] = v[sl.start * per:sl.stop * per].clone()
+        sub["initial_root_states"] = full.initial_root_states[sl].cpu().clone()
+        env, _, _ = U.make_ma_op3_pair(m, seed=33, state=sub)
+        env.launch_post_physics(uc[sl].to(DEV))
+        parts.append(env)
+    total = parts[0].grip_count_buf + parts[1].grip_count_buf      # what the NCCL all-reduce does (gripAllReduce)
+    for env in parts:
+        env.grip_count_buf.copy_(total)
+        env.finalize_reward()
+    torch.cuda.synchronize()
+    assert total.tolist() == [[1, 1], [2, 1]] and full.grip_count_buf.tolist() == [[1, 1], [2, 1]]
+    for name in ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "commands", "feet_air_time", "potentials"):
+        U.exact(torch.cat([getattr(p, name) for p in parts]), getattr(full, name), "sharded " + name)

@@ -214,6 +214,7 @@ SYMBOLS = {
     "tk_ma_op3_compute_reward": (C.c_int, [_p, _p]),
     "tk_ma_op3_reset_idx": (C.c_int, [_p, _p, _i32, _p, _p]),
     "tk_ma_op3_post_physics": (C.c_int, [_p, C.POINTER(Op3Noise), _p]),
+    "tk_ma_op3_finalize_reward": (C.c_int, [_p, _p]),
     "tk_ma_op3_advance_epoch": (C.c_int, [_p, _p]),
     "tk_ma_op3_stats": (C.c_int, [_p, _p, _i32, _p]),
     "tk_ma_op3_philox_noise": (C.c_int, [_p, _u64, _u64, _i64, _p, _p]),

@@ -6,13 +6,16 @@
 // reset_idx :440-489.  The reference's step hooks are stubs (:309-317); the fused step is the anymal.py:229-242 ordering
 // around those methods (oracle/ma_op3_oracle.py states the assumptions).
 //
-// One CTA = 2 warps = 32 consecutive envs; warp a owns agent a, lane e owns env e.  The six [N,2,*] arrays arrive as
-// cp.async.bulk (TMA) tile copies on one mbarrier (a 32-env tile of every array starts 16-byte aligned); the 4 foot
-// contact rows an agent needs are gathered straight from global memory (12 of the env's 51 body rows are ever read).
-// Each (env, agent) observation row is assembled as float4 groups in a padded shared-memory row (stride 100 words:
-// conflict-free 128-bit stores) and leaves as one 352-byte bulk store; prev_torques / last_actions are refreshed by
-// bulk-storing the torque / action tiles that are already in shared memory.  Warp 1 hands its reward and reset bits
-// to warp 0 through shared memory for the table ("objective") terms.
+// One CTA = 2 warps = 32 consecutive envs; warp a owns agent a, lane e owns env e.  root / dof_state / torques / actions
+// arrive as cp.async.bulk (TMA) tile copies on one mbarrier (a 32-env tile of every array starts 16-byte aligned): 27 KB
+// of shared memory per CTA, so 6 CTAs (register-limited) are resident per SM.  Each lane reads its own prev_torques /
+// last_actions rows (88 contiguous bytes) and the 4 foot contact rows an agent needs straight from global memory, issued
+// before the tile wait (12 of the env's 51 body rows are ever read).  An (env, agent) observation row is built in
+// registers and leaves as 22 streaming 128-bit stores (352-byte rows, 16-byte aligned; sectors complete in L2);
+// prev_torques / last_actions are refreshed by bulk-storing the torque / action tiles that are already in shared
+// memory.  Warp 1 hands its reward and reset bits to warp 0 through shared memory for the table ("objective") terms.
+// (v1 staged padded obs rows and all six tiles in shared memory: 64 KB, 3 CTAs per SM, 44 % of HBM peak, stalled on the
+// tile wait -- profiles/r01_n3_ma_op3_tile_kernel_262144_v1.json.)
 //
 // Algorithmic bytes / env-step (F = 4 feet): reads root 156 + dof 352 + torques 176 + prev_torques 176 + actions 176 +
 // last_actions 176 + foot contacts 96 + gripper x-forces 16 + commands 12 + potentials 8 + table potential 4 +
@@ -32,7 +35,6 @@ constexpr int kRoot = 13;
 constexpr int kActors = 3;
 constexpr int kDof = TK_OP3_DOF;
 constexpr int kObs = TK_OP3_OBS;
-constexpr int kObsPad = 100;             // padded obs row (words): 100 mod 32 = 4 -> conflict-free float4 stores
 constexpr int kTile = 32;
 constexpr int kThreads = kTile * kA;
 constexpr int kMaxFeet = TK_OP3_MAX_FEET;
@@ -60,7 +62,8 @@ struct KParams {
     uint8_t* timeout;
     float* ep_return;
     double* partials;
-    const unsigned long long* grip_counts;   // [agents][2]
+    unsigned long long* grip_counts;         // [agents][2]
+    float* pre_rew;                          // [N,2] un-clipped per-agent totals before the hold term (fused step only)
     const float* unit_cmd;
     unsigned long long seed, step;
     unsigned long long* step_dev;
@@ -84,13 +87,10 @@ __device__ __forceinline__ float rand_float(float lo, float span, float u) { ret
 __device__ __forceinline__ float norm2_ref(float x, float y) { return sqrtf(fmaf(y, y, x * x)); }
 
 struct Smem {
-    alignas(128) float obs[kTile * kA * kObsPad];
-    alignas(16) float root[kTile * kActors * kRoot];
+    alignas(128) float root[kTile * kActors * kRoot];
     alignas(16) float dof[kTile * kA * kDof * 2];
     alignas(16) float tq[kTile * kA * kDof];
-    alignas(16) float ptq[kTile * kA * kDof];
     alignas(16) float act[kTile * kA * kDof];
-    alignas(16) float lact[kTile * kA * kDof];
     float x_rew[kTile];
     float x_dist[kTile];
     int x_flag[kTile];
@@ -118,26 +118,18 @@ __global__ void __launch_bounds__(kThreads) op3_tile_kernel(const __grid_constan
     __syncthreads();
     if (bulk) {
         if (tid == 0) {
-            mbar_expect_tx(&s.bar, kRootB + kDofB + kRowB + (kNeedTq ? 3 * kRowB : 0));
+            mbar_expect_tx(&s.bar, kRootB + kDofB + kRowB + (kNeedTq ? kRowB : 0));
             bulk_load(s.dof, p.dof_state + e0 * kA * kDof * 2, kDofB, &s.bar);
             bulk_load(s.root, p.root + e0 * kActors * kRoot, kRootB, &s.bar);
             bulk_load(s.act, p.actions + e0 * kA * kDof, kRowB, &s.bar);
-            if (kNeedTq) {
-                bulk_load(s.tq, p.torques + e0 * kA * kDof, kRowB, &s.bar);
-                bulk_load(s.ptq, p.prev_torques + e0 * kA * kDof, kRowB, &s.bar);
-                bulk_load(s.lact, p.last_actions + e0 * kA * kDof, kRowB, &s.bar);
-            }
+            if (kNeedTq) bulk_load(s.tq, p.torques + e0 * kA * kDof, kRowB, &s.bar);
         }
     } else {
         for (int i = tid; i < nt * kActors * kRoot; i += kThreads) s.root[i] = p.root[e0 * kActors * kRoot + i];
         for (int i = tid; i < nt * kA * kDof * 2; i += kThreads) s.dof[i] = p.dof_state[e0 * kA * kDof * 2 + i];
         for (int i = tid; i < nt * kA * kDof; i += kThreads) {
             s.act[i] = p.actions[e0 * kA * kDof + i];
-            if (kNeedTq) {
-                s.tq[i] = p.torques[e0 * kA * kDof + i];
-                s.ptq[i] = p.prev_torques[e0 * kA * kDof + i];
-                s.lact[i] = p.last_actions[e0 * kA * kDof + i];
-            }
+            if (kNeedTq) s.tq[i] = p.torques[e0 * kA * kDof + i];
         }
     }
     // ---- per-env scalars and the foot contact rows: issued before the tile wait ----
@@ -146,6 +138,8 @@ __global__ void __launch_bounds__(kThreads) op3_tile_kernel(const __grid_constan
     float cmd[3] = {0.f, 0.f, 0.f}, pot_old = 0.f, ppot_old = 0.f, tpot = 0.f, ptpot = 0.f, ret_old = 0.f;
     float cf[kMaxFeet][3], air[kMaxFeet];
     bool lastc[kMaxFeet];
+    float2 ptq2[kDof / 2], la2[kDof / 2];       // this (env, agent)'s prev_torques / last_actions rows, straight from global
+    float gx0 = 0.f, gx1 = 0.f;                 // x contact force on this agent's left / right gripper
     const int nf = p.num_feet;
     if (valid) {
         if (MODE != 1) prog = p.progress[n];
@@ -164,6 +158,14 @@ __global__ void __launch_bounds__(kThreads) op3_tile_kernel(const __grid_constan
         tpot = p.table_pot[n];
         if (MODE == 2) ptpot = p.prev_table_pot[n];
         if (MODE != 1) {
+            const float2* gp = reinterpret_cast<const float2*>(p.prev_torques) + (n * kA + a) * (kDof / 2);
+            const float2* gl = reinterpret_cast<const float2*>(p.last_actions) + (n * kA + a) * (kDof / 2);
+#pragma unroll
+            for (int j = 0; j < kDof / 2; ++j) { ptq2[j] = gp[j]; la2[j] = gl[j]; }
+            if (MODE == 0) {
+                gx0 = p.contact[(static_cast<size_t>(n) * p.nb + p.grip[a][0]) * 3];
+                gx1 = p.contact[(static_cast<size_t>(n) * p.nb + p.grip[a][1]) * 3];
+            }
 #pragma unroll
             for (int f = 0; f < kMaxFeet; ++f) {
                 if (f < nf) {
@@ -238,7 +240,7 @@ __global__ void __launch_bounds__(kThreads) op3_tile_kernel(const __grid_constan
             if (a == 0) ptpot = -norm3_ref(V3{p.targets[0] - tb[0], p.targets[1] - tb[1], p.targets[2] - tb[2]}) / p.dt;   // :418-419
             const V3 lin = quat_rotate_ref<-1>(q, V3{r[7], r[8], r[9]});            // :692
             const V3 g = quat_rotate_ref<1>(q, V3{p.gravity[0], p.gravity[1], p.gravity[2]});   // :694
-            float4* o = reinterpret_cast<float4*>(s.obs + row * kObsPad);
+            float4* o = reinterpret_cast<float4*>(p.obs + (static_cast<size_t>(n) * kA + a) * kObs);   // 352-byte rows, 16-byte aligned
             float v[kObs];
             v[0] = lin.x * p.lin_vel_scale; v[1] = lin.y * p.lin_vel_scale; v[2] = lin.z * p.lin_vel_scale;
             v[3] = ang_raw.x * p.ang_vel_scale; v[4] = ang_raw.y * p.ang_vel_scale; v[5] = ang_raw.z * p.ang_vel_scale;
@@ -254,7 +256,7 @@ __global__ void __launch_bounds__(kThreads) op3_tile_kernel(const __grid_constan
             for (int c = 0; c < 10; ++c) v[75 + c] = tb[c];                         // object pose + linvel
             v[85] = p.targets[0]; v[86] = p.targets[1]; v[87] = p.targets[2];
 #pragma unroll
-            for (int c = 0; c < kObs / 4; ++c) o[c] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+            for (int c = 0; c < kObs / 4; ++c) __stcs(o + c, make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]));
             p.potentials[n * kA + a] = pot_new;
             p.prev_potentials[n * kA + a] = ppot_new;
             if (a == 0) p.prev_table_pot[n] = ptpot;
@@ -283,15 +285,17 @@ __global__ void __launch_bounds__(kThreads) op3_tile_kernel(const __grid_constan
             const float rew_airtime = (air_sum * (moving ? 1.0f : 0.0f)) * p.k_air;
             const float rew_no_fly = (touching == 1 ? 1.0f : 0.0f) * p.k_nofly;
             // _reward_gripper_contact_hold :346-358: batch-global counts (tk_ma_op3_grip_counts, all-reduced when sharded)
-            const float hold = (p.grip_counts[a * 2] == 1ull && p.grip_counts[a * 2 + 1] == 1ull) ? 1.0f : 0.0f;
+            // The fused step counts while it runs and assumes hold = 0; op3_finalize_kernel adds the term afterwards in the
+            // (one env in the whole batch) case where it is 1.  compute_reward (MODE 2) reads the counts of the pre-pass.
+            const float hold = (MODE == 2 && p.grip_counts[a * 2] == 1ull && p.grip_counts[a * 2 + 1] == 1ull) ? 1.0f : 0.0f;
             // compute_op3_reward :550-658
             const Q4 torso = quat_mul_ref(q, Q4{p.inv_start_rot[0], p.inv_start_rot[1], p.inv_start_rot[2], p.inv_start_rot[3]});   // :593
             const float up_proj = quat_rotate_ref<1>(torso, V3{p.up[0], p.up[1], p.up[2]}).z;    // :601-602
             const float rew_up = up_proj > 0.95f ? 0.0f + p.k_up : 0.0f;           // :605-606
             const float progress_reward = (pot_r - ppot_r) * 5.0f;                  // :612
             const float* tqr = s.tq + row * kDof;
-            const float* ptqr = s.ptq + row * kDof;
-            const float* lar = s.lact + row * kDof;
+            const float* ptqr = reinterpret_cast<const float*>(ptq2);
+            const float* lar = reinterpret_cast<const float*>(la2);
             float tsum = 0.0f, legsum = 0.0f, ratesum = 0.0f, standsum = 0.0f;
 #pragma unroll
             for (int j = 0; j < kDof; ++j) {
@@ -314,10 +318,17 @@ __global__ void __launch_bounds__(kThreads) op3_tile_kernel(const __grid_constan
             float total = progress_reward + 2.0f;                                   // :648-649, left to right (rew_orient is -0)
             total += rew_torque; total += rew_up; total += rew_airtime; total += rew_ang_vel_z; total += step_sum;
             total += rew_no_fly; total += rew_stand_still; total += rew_action_rate; total += rew_syns;
-            total += rew_distobject; total += hold;
+            total += rew_distobject;
+            if (MODE == 0) p.pre_rew[n * kA + a] = total;
+            total += hold;
             my_rew = fmaxf(total, 0.0f);                                            // :650
             my_flag = (up_proj < 0.90f ? 1 : 0) | (my_dist > 0.40f ? 2 : 0);        // :654-655
         }
+    }
+    if (MODE == 0) {                                                                // :351-352, this tile's share
+        const unsigned m0 = __ballot_sync(0xffffffffu, valid && gx0 > 0.1f), m1 = __ballot_sync(0xffffffffu, valid && gx1 > 0.1f);
+        if (lane == 0 && m0) atomicAdd(p.grip_counts + a * 2, static_cast<unsigned long long>(__popc(m0)));
+        if (lane == 0 && m1) atomicAdd(p.grip_counts + a * 2 + 1, static_cast<unsigned long long>(__popc(m1)));
     }
     if (MODE == 1) {
         __syncthreads();
@@ -383,21 +394,13 @@ __global__ void __launch_bounds__(kThreads) op3_tile_kernel(const __grid_constan
     }
     // ---- stores: one 352-byte bulk store per (env, agent) obs row; prev_torques / last_actions from the resident tiles ----
     if (bulk) {
-        if (MODE != 2) {
-            fence_proxy_async_smem();
-            bulk_store(p.obs + (e0 * kA + lane * kA + a) * kObs, s.obs + (lane * kA + a) * kObsPad, kObs * 4);
-        }
         if (MODE == 0 && tid == 0) {
             bulk_store(p.prev_torques + e0 * kA * kDof, s.tq, kRowB);                // end-of-step refresh (see header)
             bulk_store(p.last_actions + e0 * kA * kDof, s.act, kRowB);
-        }
-        if (MODE != 2 || tid == 0) {
             bulk_commit();
             bulk_wait_read<0>();
         }
     } else {
-        if (MODE != 2)
-            for (int i = tid; i < nt * kA * kObs; i += kThreads) p.obs[e0 * kA * kObs + i] = s.obs[(i / kObs) * kObsPad + i % kObs];
         if (MODE == 0)
             for (int i = tid; i < nt * kA * kDof; i += kThreads) {
                 p.prev_torques[e0 * kA * kDof + i] = s.tq[i];
@@ -437,6 +440,48 @@ __global__ void __launch_bounds__(256) op3_grip_count_kernel(const __grid_consta
 #pragma unroll
         for (int k = 0; k < kA * 2; ++k)
             if (c[k]) atomicAdd(counts + k, static_cast<unsigned long long>(c[k]));
+    }
+}
+
+// Second half of the fused step: add _reward_gripper_contact_hold (:346-358) where the batch-global counts say it is 1.
+// Exits at once otherwise (the common case: exactly one env of the whole batch must press each gripper).
+__global__ void __launch_bounds__(256) op3_finalize_kernel(const __grid_constant__ KParams p) {
+    const bool h0 = p.grip_counts[0] == 1ull && p.grip_counts[1] == 1ull, h1 = p.grip_counts[2] == 1ull && p.grip_counts[3] == 1ull;
+    if (!h0 && !h1) return;
+    float d_rew = 0.f, d_ret = 0.f;
+    for (long long n = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; n < p.n;
+         n += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const float* tb = p.root + (n * kActors + 2) * kRoot;
+        const float tup = quat_rotate_ref<1>(Q4{tb[3], tb[4], tb[5], tb[6]}, V3{p.up[0], p.up[1], p.up[2]}).z;
+        const float rew_up = tup > 0.98f ? 0.0f + 0.1f : 0.0f;
+        const float hz = tb[2] - 0.29f;
+        const float rew_h = (hz * hz) * -0.001f;
+        const float dist_rew = (p.table_pot[n] - p.prev_table_pot[n]) * 5.0f;
+        float delta = 0.f;
+#pragma unroll
+        for (int a = 0; a < kA; ++a) {
+            if (a == 0 ? h0 : h1) {
+                const float agent = fmaxf(p.pre_rew[n * kA + a] + 1.0f, 0.0f);      // :648-650 with rew_gripper_hold = 1
+                const float r = ((agent + dist_rew) + rew_up) + rew_h;              // :542
+                delta += r - p.rew[n * kA + a];
+                p.rew[n * kA + a] = r;
+            }
+        }
+        d_rew += delta;
+        if (p.ep_return) {
+            p.ep_return[n] += delta;
+            if (p.reset[n] != 0) d_ret += delta;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        d_rew += __shfl_xor_sync(0xffffffffu, d_rew, o);
+        d_ret += __shfl_xor_sync(0xffffffffu, d_ret, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        double* pr = p.partials + static_cast<size_t>(blockIdx.x & (kStatSlots - 1)) * TK_STATS;
+        atomicAdd(pr + 0, static_cast<double>(d_rew));
+        atomicAdd(pr + 3, static_cast<double>(d_ret));
     }
 }
 
@@ -505,6 +550,7 @@ struct TkOp3 {
     int tiles, sm_count;
     double* partials;
     unsigned long long* step_dev;
+    float* pre_rew;
 };
 
 static void fill_kparams(const TkOp3* h, KParams& k) {
@@ -517,7 +563,7 @@ static void fill_kparams(const TkOp3* h, KParams& k) {
     k.prev_table_pot = B.prev_table_potentials; k.obs = B.obs_buf; k.rew = B.rew_buf;
     k.reset = reinterpret_cast<long long*>(B.reset_buf); k.progress = reinterpret_cast<long long*>(B.progress_buf);
     k.timeout = B.timeout_buf; k.ep_return = B.episode_return; k.partials = h->partials;
-    k.grip_counts = reinterpret_cast<const unsigned long long*>(B.grip_counts);
+    k.grip_counts = reinterpret_cast<unsigned long long*>(B.grip_counts); k.pre_rew = h->pre_rew;
     k.unit_cmd = nullptr; k.seed = 0; k.step = 0; k.step_dev = h->step_dev; k.env_off = 0; k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs; k.nb = P.num_bodies_total; k.max_episode_length = P.max_episode_length; k.num_feet = P.num_feet;
     for (int a = 0; a < kA; ++a) {
@@ -604,13 +650,14 @@ int tk_ma_op3_create(const TkOp3Params* params, TkOp3** out) {
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->sm_count = 148;
     cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, params->device);
-    h->partials = nullptr; h->step_dev = nullptr;
+    h->partials = nullptr; h->step_dev = nullptr; h->pre_rew = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMalloc(&h->step_dev, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemset(h->step_dev, 0, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&h->pre_rew, sizeof(float) * kA * static_cast<size_t>(params->num_envs));
     if (e != cudaSuccess) {
-        cudaFree(h->partials); cudaFree(h->step_dev);
+        cudaFree(h->partials); cudaFree(h->step_dev); cudaFree(h->pre_rew);
         delete h;
         return cuda_fail(e, "tk_ma_op3_create");
     }
@@ -621,7 +668,7 @@ int tk_ma_op3_create(const TkOp3Params* params, TkOp3** out) {
 int tk_ma_op3_destroy(TkOp3* h) {
     if (!h) return TK_OK;
     cudaSetDevice(h->params.device);
-    cudaFree(h->partials); cudaFree(h->step_dev);
+    cudaFree(h->partials); cudaFree(h->step_dev); cudaFree(h->pre_rew);
     delete h;
     return TK_OK;
 }
@@ -641,8 +688,10 @@ int tk_ma_op3_bind(TkOp3* h, const TkOp3Buffers* b) {
     TK_REQUIRE(b->last_contacts != nullptr, TK_ERR_UNBOUND, "buffer last_contacts is NULL");
     TK_REQUIRE(b->grip_counts != nullptr && aligned_to(b->grip_counts, 8), TK_ERR_UNBOUND, "buffer grip_counts is NULL or misaligned");
     TK_REQUIRE(aligned_to(b->reset_buf, 8) && aligned_to(b->progress_buf, 8), TK_ERR_ALIGN, "int64 buffers must be 8-byte aligned");
-    TK_REQUIRE(aligned_to(b->dof_state, 8) && aligned_to(b->rew_buf, 8), TK_ERR_ALIGN,
-               "dof_state ((pos,vel) pairs) and rew_buf ([N,2] rows) must be 8-byte aligned");
+    TK_REQUIRE(aligned_to(b->dof_state, 8) && aligned_to(b->rew_buf, 8) && aligned_to(b->prev_torques, 8) &&
+               aligned_to(b->last_actions, 8), TK_ERR_ALIGN,
+               "dof_state, rew_buf, prev_torques and last_actions are accessed as 8-byte pairs");
+    TK_REQUIRE(aligned_to(b->obs_buf, 16), TK_ERR_ALIGN, "obs_buf rows are written as 128-bit stores: 16-byte alignment");
     h->buf = *b;
     h->bound = true;
     return TK_OK;
@@ -702,14 +751,27 @@ int tk_ma_op3_post_physics(TkOp3* h, const TkOp3Noise* noise, void* stream) {
     TK_REQUIRE(noise != nullptr, TK_ERR_INVALID, "null noise descriptor");
     TK_REQUIRE(noise->mode == TK_NOISE_NONE || noise->mode == TK_NOISE_DENSE || noise->mode == TK_NOISE_PHILOX, TK_ERR_INVALID,
                "noise mode %d: MA_OP3 takes TK_NOISE_NONE, TK_NOISE_DENSE (row n = env n) or TK_NOISE_PHILOX", noise->mode);
-    TK_REQUIRE(h->counted, TK_ERR_INVALID, "tk_ma_op3_grip_counts must run before tk_ma_op3_post_physics");
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
+    TK_CUDA(cudaMemsetAsync(k.grip_counts, 0, sizeof(unsigned long long) * kA * 2, static_cast<cudaStream_t>(stream)));
+    h->counted = true;
     k.noise_mode = noise->mode;
     if (noise->mode == TK_NOISE_DENSE) k.unit_cmd = noise->unit_cmd;
     k.seed = noise->seed; k.step = noise->step; k.env_off = noise->env_id_offset;
     TK_CUDA(launch_tile<0>(h, k, static_cast<cudaStream_t>(stream)));
     h->ran = true;
+    return TK_OK;
+}
+
+int tk_ma_op3_finalize_reward(TkOp3* h, void* stream) {
+    if (int rc = check_bound(h)) return rc;
+    TK_REQUIRE(h->ran, TK_ERR_INVALID, "tk_ma_op3_post_physics has not run yet");
+    TK_CUDA(cudaSetDevice(h->params.device));
+    KParams k; fill_kparams(h, k);
+    int blocks = (k.n + 255) / 256;
+    if (blocks > h->sm_count * 8) blocks = h->sm_count * 8;
+    op3_finalize_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
+    TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
 

@@ -247,10 +247,13 @@ class MA_OP3(VecTask):
     def grip_counts(self) -> torch.Tensor:
         """int64 [agents, 2] (device): envs pressing the left / right gripper (:351-352), summed over ranks when sharded."""
         nat.check(self._lib.tk_ma_op3_grip_counts(self._handle, self._stream()), "tk_ma_op3_grip_counts")
+        self._all_reduce_counts()
+        return self.grip_count_buf
+
+    def _all_reduce_counts(self):
         if self.grip_all_reduce and torch.distributed.is_available() and torch.distributed.is_initialized() \
                 and torch.distributed.get_world_size() > 1:
             torch.distributed.all_reduce(self.grip_count_buf)        # the one exchange step of this path (NCCL, 32 bytes)
-        return self.grip_count_buf
 
     def compute_observations(self):
         """:411-438."""
@@ -276,10 +279,20 @@ class MA_OP3(VecTask):
                   "tk_ma_op3_reset_idx")
 
     def post_physics_step(self, unit_cmd: Optional[torch.Tensor] = None):
+        self.launch_post_physics(unit_cmd)
+        self._all_reduce_counts()
+        self.finalize_reward()
+
+    def finalize_reward(self):
+        """Second half of the step: the batch-global hold term, after ``grip_count_buf`` holds the GLOBAL counts."""
+        nat.check(self._lib.tk_ma_op3_finalize_reward(self._handle, self._stream()), "tk_ma_op3_finalize_reward")
+
+    def launch_post_physics(self, unit_cmd: Optional[torch.Tensor] = None):
         """progress += 1, reset, compute_observations, compute_reward, prev_torques / last_actions refresh and the timeout
-        line (multi_vec_task.py:193): the count kernel + ONE fused kernel.  ``unit_cmd`` [N,3] is addressed by env id;
-        in-kernel Philox noise when omitted."""
-        self.grip_counts()
+        line (multi_vec_task.py:193): ONE fused kernel that also counts the gripper contacts, then (after the all-reduce
+        of the four counts in a sharded run) a finalize grid that adds the batch-global hold term -- it exits at once
+        unless exactly one env presses each gripper.  ``unit_cmd`` [N,3] is addressed by env id; in-kernel Philox noise
+        when omitted."""
         if unit_cmd is None:
             nz = self._philox_noise
             nz.seed, nz.step, nz.env_id_offset = self.noise_seed, self.step_count, self.env_id_offset
