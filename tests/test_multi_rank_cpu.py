@@ -102,3 +102,66 @@ def test_two_rank_sharding_and_allreduce(tmp_path):
         assert got[1] == full_stats[1] and got[2] == full_stats[2] and got[4] == full_stats[4]
         assert p["stats"]["env_steps"] == total
         assert abs(p["stats"]["mean_reward"] - float(full.rew_buf.double().mean())) < 1e-9
+
+
+def _op3_state(total):
+    """One env of the whole batch presses each gripper of agent 0 (one per shard): only the all-reduced counts give 1."""
+    from thormang_isaacgym_b200 import synthetic as syn
+    st = syn.ma_op3_state(total, seed=4321)
+    _, grip = syn.ma_op3_body_indices()
+    cf = st["contact_forces"]
+    cf[:, grip.flatten(), 0] = 0.0
+    cf[3, grip[0, 0], 0] = 0.5                 # rank 0's shard
+    cf[total - 2, grip[0, 1], 0] = 0.7         # rank 1's shard
+    cf[5, grip[1, 0], 0] = 0.5
+    cf[total - 5, grip[1, 0], 0] = 0.5         # agent 1: two left presses over the two shards -> 0
+    cf[6, grip[1, 1], 0] = 0.5
+    return st
+
+
+def _op3_shard(st, total, lo, hi):
+    from oracle import ma_op3_oracle as mo
+    sub = {}
+    for k, v in st.items():
+        per = v.shape[0] // total
+        sub[k] = v[lo * per:hi * per].clone()
+    return mo.oracle_from_state(sub)
+
+
+def _op3_worker(rank, world, port, total, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    from oracle import ma_op3_oracle as mo
+    lo, hi = par.shard_range(total, rank, world)
+    orc = _op3_shard(_op3_state(total), total, lo, hi)
+    counts = mo.grip_counts(orc.contact_forces, orc.gripper_indices)       # what the fused kernel counts on this rank
+    local = counts.clone()
+    dist.all_reduce(counts)                                                 # MA_OP3._all_reduce_counts (SUM, 32 bytes)
+    orc.global_grip_counts = counts
+    orc.compute_observations()
+    orc.compute_reward()
+    torch.save({"rew": orc.rew_buf, "reset": orc.reset_buf, "local": local, "global": counts},
+               os.path.join(out_dir, f"op3_rank{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_ma_op3_grip_count_exchange(tmp_path):
+    """MA_OP3 is the one path with a real exchange step: _reward_gripper_contact_hold reduces over all
+    envs (MA_OP3.py:346-358), so a sharded run must all-reduce the four counts before the reward."""
+    total, world = 257, 2
+    port = _free_port()
+    mp.spawn(_op3_worker, args=(world, port, total, str(tmp_path)), nprocs=world, join=True)
+    full = _op3_shard(_op3_state(total), total, 0, total)
+    full.compute_observations()
+    full.compute_reward()
+    parts = [torch.load(os.path.join(str(tmp_path), f"op3_rank{r}.pt"), weights_only=False) for r in range(world)]
+    assert parts[0]["local"].tolist() == [[1, 0], [1, 1]] and parts[1]["local"].tolist() == [[0, 1], [1, 0]]
+    for p in parts:
+        assert p["global"].tolist() == [[1, 1], [2, 1]]
+    torch.testing.assert_close(torch.cat([p["rew"] for p in parts]), full.rew_buf, rtol=1e-6, atol=1e-6)
+    assert torch.equal(torch.cat([p["reset"] for p in parts]), full.reset_buf)
+    # without the exchange rank-local counts would give agent 0 no hold term at all: the +1 is visible in the rewards
+    assert float((full.rew_buf[:, 0] > 0).float().mean()) > 0.5
