@@ -98,8 +98,12 @@ struct Smem {
 };
 
 // MODE 0: fused post_physics_step; 1: compute_observations; 2: compute_reward
+#ifndef TK_OP3_MIN_CTAS
+#define TK_OP3_MIN_CTAS 6        // resident CTAs per SM the register allocation targets (developer knob)
+#endif
+
 template <int MODE>
-__global__ void __launch_bounds__(kThreads) op3_tile_kernel(const __grid_constant__ KParams p) {
+__global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(const __grid_constant__ KParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem& s = *reinterpret_cast<Smem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, a = tid >> 5;
