@@ -113,7 +113,10 @@ __global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(con
     const bool valid = lane < nt;
     const bool bulk = p.vec_ok && nt == kTile;
     const size_t e0 = static_cast<size_t>(env0);
-    constexpr bool kNeedTq = MODE != 1, kNeedDof = true, kNeedAct = true;
+    constexpr bool kNeedTq = MODE != 1;
+    // the finalize grid that follows (programmatic dependent launch) may be scheduled as soon as every CTA got here; it
+    // still waits for this grid's completion and memory flush in its own griddepcontrol.wait
+    if (MODE == 0) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     constexpr uint32_t kRootB = kTile * kActors * kRoot * 4, kDofB = kTile * kA * kDof * 2 * 4, kRowB = kTile * kA * kDof * 4;
     if (bulk && tid == 0) {
         mbar_init(&s.bar, 1);
@@ -455,6 +458,7 @@ __global__ void __launch_bounds__(256) op3_grip_count_kernel(const __grid_consta
 // Second half of the fused step: add _reward_gripper_contact_hold (:346-358) where the batch-global counts say it is 1.
 // Exits at once otherwise (the common case: exactly one env of the whole batch must press each gripper).
 __global__ void __launch_bounds__(256) op3_finalize_kernel(const __grid_constant__ KParams p) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const bool h0 = p.grip_counts[0] == 1ull && p.grip_counts[1] == 1ull, h1 = p.grip_counts[2] == 1ull && p.grip_counts[3] == 1ull;
     if (!h0 && !h1) return;
     float d_rew = 0.f, d_ret = 0.f;
@@ -779,8 +783,16 @@ int tk_ma_op3_finalize_reward(TkOp3* h, void* stream) {
     KParams k; fill_kparams(h, k);
     int blocks = (k.n + 255) / 256;
     if (blocks > h->sm_count * 8) blocks = h->sm_count * 8;
-    op3_finalize_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
-    TK_CUDA(cudaGetLastError());
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(blocks);
+    cfg.blockDim = dim3(256);
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    TK_CUDA(cudaLaunchKernelEx(&cfg, op3_finalize_kernel, k));
     return TK_OK;
 }
 
