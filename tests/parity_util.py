@@ -230,8 +230,9 @@ OP3_STATE_NAMES = ("prev_torques", "commands", "actions", "last_actions", "feet_
                    "prev_potentials", "table_potentials", "progress_buf", "reset_buf")
 
 
-def make_ma_op3_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
-    """(cuda MA_OP3 task, cpu MAOP3Oracle, state) from one synthetic snapshot."""
+def make_ma_op3_pair(n, seed=1234, device="cuda:0", state=None, feet=None, **env_over):
+    """(cuda MA_OP3 task, cpu MAOP3Oracle, state) from one synthetic snapshot.  ``feet``: [2][F] body
+    indices replacing the four "*ank*" links (exercises the run-time foot count of the kernel)."""
     from oracle import ma_op3_oracle as mo
     from thormang_isaacgym_b200.sim.fake_sim import FakeSim
     from thormang_isaacgym_b200.tasks.MA_OP3 import MA_OP3
@@ -239,6 +240,12 @@ def make_ma_op3_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
     cfg = tcfg.ma_op3_cfg(n, seed=seed)
     cfg["env"].update(env_over)
     cfg["env"]["resetOnInit"] = False
+    if feet is not None:
+        cfg["env"]["feetIndices"] = [list(map(int, f)) for f in feet]
+        nf = len(feet[0])
+        state = dict(state)
+        state["feet_air_time"] = state["feet_air_time"][:, :, :1].repeat(1, 1, nf).contiguous()
+        state["last_contacts"] = state["last_contacts"][:, :, :1].repeat(1, 1, nf).contiguous()
     nb = state["contact_forces"].numel() // (n * 3)
     sim = FakeSim(n, 44, device, num_sensor_floats=0, dof_names=list(tcfg.OP3_DOF_NAMES), num_bodies=nb, actors_per_env=3)
     init = state.get("initial_root_states")
@@ -254,7 +261,8 @@ def make_ma_op3_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
     sim.load_state(state)
     for name in OP3_STATE_NAMES:
         getattr(env, name).copy_(state[name].to(device))
-    feet, grip = syn.ma_op3_body_indices()
+    default_feet, grip = syn.ma_op3_body_indices()
+    feet = default_feet if feet is None else torch.tensor(cfg["env"]["feetIndices"], dtype=torch.long)
     st = dict(state)
     st["initial_root_states"] = init.clone()
     orc = mo.oracle_from_state(st, consts=mo.OP3Consts.from_cfg(cfg), feet=feet, grip=grip)

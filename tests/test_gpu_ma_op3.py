@@ -212,3 +212,19 @@ def test_unaligned_and_sharded():
     assert total.tolist() == [[1, 1], [2, 1]] and full.grip_count_buf.tolist() == [[1, 1], [2, 1]]
     for name in ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "commands", "feet_air_time", "potentials"):
         U.exact(torch.cat([getattr(p, name) for p in parts]), getattr(full, name), "sharded " + name)
+
+
+@pytest.mark.parametrize("feet", [[[10, 11, 16], [35, 36, 41]], [[10, 11, 16, 17, 3, 4], [35, 36, 41, 42, 28, 29]]])
+def test_runtime_foot_count(feet):
+    """The kernel is specialised for the OP3's four "*ank*" links; any other count takes the run-time path."""
+    n = 1000
+    env, orc, st = U.make_ma_op3_pair(n, seed=61, feet=feet)
+    assert env.feet_air_time.shape == (n, 2, len(feet[0]))
+    uc = syn.ma_op3_reset_noise(n, seed=8)
+    ids = orc.reset_buf.nonzero(as_tuple=False).squeeze(-1)
+    env.post_physics_step(uc.to(DEV))
+    orc.post_physics_step(uc[ids])
+    torch.cuda.synchronize()
+    _check_obs_side(env, orc, "nf")
+    _check_reward_side(env, orc, "nf")
+    U.exact(env.progress_buf, orc.progress_buf, "progress_buf")

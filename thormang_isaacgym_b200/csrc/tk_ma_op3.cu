@@ -102,7 +102,8 @@ struct Smem {
 #define TK_OP3_MIN_CTAS 6        // resident CTAs per SM the register allocation targets (developer knob)
 #endif
 
-template <int MODE>
+// NF > 0: number of feet known at compile time (4 for the OP3 of MA_OP3.py:237-238); NF = 0: p.num_feet at run time
+template <int MODE, int NF>
 __global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(const __grid_constant__ KParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem& s = *reinterpret_cast<Smem*>(smem_raw);
@@ -147,7 +148,7 @@ __global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(con
     bool lastc[kMaxFeet];
     float2 ptq2[kDof / 2], la2[kDof / 2];       // this (env, agent)'s prev_torques / last_actions rows, straight from global
     float gx0 = 0.f, gx1 = 0.f;                 // x contact force on this agent's left / right gripper
-    const int nf = p.num_feet;
+    const int nf = NF > 0 ? NF : p.num_feet;
     if (valid) {
         if (MODE != 1) prog = p.progress[n];
         if (MODE == 0) {
@@ -610,17 +611,22 @@ static int check_bound(const TkOp3* h) {
     return TK_OK;
 }
 
-template <int MODE>
-static cudaError_t launch_tile(const TkOp3* h, const KParams& k, cudaStream_t st) {
+template <int MODE, int NF>
+static cudaError_t launch_tile_nf(const TkOp3* h, const KParams& k, cudaStream_t st) {
     static bool opted = false;
     if (!opted) {
-        cudaError_t e = cudaFuncSetAttribute(op3_tile_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(op3_tile_kernel<MODE, NF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              static_cast<int>(sizeof(Smem)));
         if (e != cudaSuccess) return e;
         opted = true;
     }
-    op3_tile_kernel<MODE><<<h->tiles, kThreads, sizeof(Smem), st>>>(k);
+    op3_tile_kernel<MODE, NF><<<h->tiles, kThreads, sizeof(Smem), st>>>(k);
     return cudaGetLastError();
+}
+
+template <int MODE>
+static cudaError_t launch_tile(const TkOp3* h, const KParams& k, cudaStream_t st) {
+    return k.num_feet == 4 ? launch_tile_nf<MODE, 4>(h, k, st) : launch_tile_nf<MODE, 0>(h, k, st);
 }
 
 static int count_grips(TkOp3* h, const KParams& k, cudaStream_t st) {
