@@ -59,7 +59,7 @@ def _make_gogoro(n, seed, device, env_off=0):
     return env, st
 
 
-def _make_gogoro_paper(n, seed, device, env_off=0):
+def _make_gogoro_paper(n, seed, device, env_off=0, world_reduce=False):
     """8-channel x 20-frame Gogoro variant; ~2 % of the envs beyond the fall threshold per step."""
     import torch
     from thormang_isaacgym_b200 import config as tcfg
@@ -70,6 +70,8 @@ def _make_gogoro_paper(n, seed, device, env_off=0):
     cfg = tcfg.gogoro_paper_cfg(n, seed=1234)
     cfg["env"]["envIdOffset"] = env_off
     cfg["env"]["resetOnInit"] = False
+    if world_reduce:
+        cfg["env"]["worldReduce"] = True      # :747 cross-env mean: diff sums -> NCCL all-reduce -> finalize, every step
     names = ["steering_joint", "rear_wheel_joint"] + [f"j{i}" for i in range(37)]
     sim = FakeSim(n, 39, device, num_sensor_floats=0, dof_names=names)
     sim.load_state(st)
@@ -105,7 +107,7 @@ def _make_anymal(n, seed, device, env_off=0):
     return env, st
 
 
-def _make_ma_op3(n, seed, device, env_off=0):
+def _make_ma_op3(n, seed, device, env_off=0, grip_all_reduce=False):
     """MA_OP3: two OP3 + table per env, 51 rigid bodies; ~1 % of the envs in reset per step."""
     import torch
     from thormang_isaacgym_b200 import config as tcfg
@@ -116,6 +118,7 @@ def _make_ma_op3(n, seed, device, env_off=0):
     cfg = tcfg.ma_op3_cfg(n, seed=1234)
     cfg["env"]["envIdOffset"] = env_off
     cfg["env"]["resetOnInit"] = False
+    cfg["env"]["gripAllReduce"] = bool(grip_all_reduce)   # MA_OP3.py:346-358 batch-global counts: int64[4] all-reduce per step
     nb = st["contact_forces"].shape[1]
     sim = FakeSim(n, 44, device, num_sensor_floats=0, dof_names=list(tcfg.OP3_DOF_NAMES), num_bodies=nb, actors_per_env=3)
     sim.load_state(st)
@@ -137,14 +140,18 @@ def _rotating_sets(n, bytes_per_env):
     return max(3, int(math.ceil(2.2 * B.L2_BYTES / per_set)))
 
 
-def _time_steps(torch, step_fn, steps, warmup, barrier=None):
+def _time_steps(torch, step_fn, steps, warmup, barrier=None, after_warmup=None):
     """W untimed steps, then exactly K steps between two events on the launching stream.
-    step_fn(i) returns the number of kernels of ours it launched.  Returns (ms, launches, (t0, t1))."""
+    step_fn(i) returns the number of kernels of ours it launched.  Returns (ms, launches, (t0, t1)).
+    after_warmup() runs between the warm-up and the barrier (outside the timed region)."""
     for i in range(warmup):
         step_fn(i)
+    if after_warmup is not None:
+        after_warmup()
     torch.cuda.synchronize()
     if barrier:
         barrier()
+        torch.cuda.synchronize()      # the barrier's own NCCL kernel has drained before the first event is recorded
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     ev0.record()
@@ -160,14 +167,16 @@ def _time_steps(torch, step_fn, steps, warmup, barrier=None):
 
 
 def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, barrier=None, horizon_hook=None,
-                  graph=False):
+                  graph=False, horizon=HORIZON, cfg_patch=None):
     """Fused post-physics kernel over rotating state sets.  Returns dict(ms_total, launches, sets, window).
-    graph=True: one pass over the sets is captured in a CUDA graph and replayed (steps is rounded to whole passes)."""
+    graph=True: one pass over the sets is captured in a CUDA graph and replayed (steps is rounded to whole passes).
+    horizon_hook(env, steps_since_last_finalize) fires after every `horizon`-th TIMED step (warm-up steps do not count;
+    the statistics partials of every set are discarded after the warm-up, outside the timed region)."""
     bpe = B.BYTES_PER_ENV[task]
     sets = _rotating_sets(n, bpe)
     make = _MAKERS[task]
     per_step = _LAUNCHES_PER_STEP[task]
-    envs = [make(n, seed + 17 * s, device, env_off)[0] for s in range(sets)]
+    envs = [make(n, seed + 17 * s, device, env_off, **(cfg_patch or {}))[0] for s in range(sets)]
 
     if graph:
         for e in envs:
@@ -187,14 +196,27 @@ def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, b
         del envs
         return {"ms_total": ms, "launches": launches, "sets": sets, "window": window, "steps": passes * sets}
 
+    since = [0] * sets          # steps of each set since its statistics were last finalized
+
+    def after_warmup():
+        if horizon_hook is not None:
+            for e in envs:
+                e.episode_statistics()      # finalize + zero the partials: the timed region starts from empty statistics
+            for k in range(sets):
+                since[k] = 0
+
     def step(i):
-        envs[i % sets].post_physics_step()
+        k = i % sets
+        envs[k].post_physics_step()
+        since[k] += 1
         extra = 0
-        if horizon_hook is not None and (i + 1) % HORIZON == 0:
-            extra = horizon_hook(envs)
+        t = i - warmup                      # index inside the timed region
+        if horizon_hook is not None and t >= 0 and (t + 1) % horizon == 0:
+            extra = horizon_hook(envs[k], since[k])
+            since[k] = 0
         return per_step + extra
 
-    ms, launches, window = _time_steps(torch, step, steps, warmup, barrier)
+    ms, launches, window = _time_steps(torch, step, steps, warmup, barrier, after_warmup)
     del envs
     return {"ms_total": ms, "launches": launches, "sets": sets, "window": window, "steps": steps}
 
@@ -289,6 +311,88 @@ def _step_loop_bench(torch, n, device, horizon, reps, graph=False):
             "note": "pre (252 B/env) + post (924 B/env) on ONE state set: L2-resident at this size, not an HBM number"}
 
 
+def _multi_gpu_diag(torch, dist, task, n, device, rank, world, local_rank, barrier, steps):
+    """N > 1 only, outside the headline timing.  (1) per-step CUDA-event times of the first `steps` steps after a barrier,
+    per rank: separates a barrier tail / clock ramp at the head of the window from a steady-state loss.  (2) the two
+    IN-STEP exchanges of the path family, timed with their NCCL all-reduce inside every step and checked against the
+    sum of the per-rank values: the paper variant's cross-env reward mean (gogoro_realistic_turning_sim_paper.py:747) and
+    MA_OP3's batch-global gripper counts (MA_OP3.py:346-358)."""
+    out = {}
+    # ---- (1) per-step profile of the headline workload
+    bpe = B.BYTES_PER_ENV[task]
+    sets = _rotating_sets(n, bpe)
+    envs = [_MAKERS[task](n, 99 + 17 * k + 1000 * rank, device, rank * n)[0] for k in range(sets)]
+    for i in range(6):
+        envs[i % sets].post_physics_step()
+    torch.cuda.synchronize()
+    barrier()
+    torch.cuda.synchronize()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    evs[0].record()
+    for i in range(steps):
+        envs[i % sets].post_physics_step()
+        evs[i + 1].record()
+    torch.cuda.synchronize()
+    per = torch.tensor([evs[i].elapsed_time(evs[i + 1]) * 1e3 for i in range(steps)], device=device, dtype=torch.float64)
+    allp = [torch.zeros_like(per) for _ in range(world)]
+    dist.all_gather(allp, per)
+    out["per_step_us_after_barrier"] = {
+        "note": "an event after EVERY step (this serialises consecutive launches: slower than the headline loop, "
+                "which records two events in all); first rows = head of the window",
+        "per_rank": [[round(float(v), 2) for v in t.tolist()] for t in allp]}
+    del envs
+
+    # ---- (2) in-step exchanges
+    def timed(make_kwargs, tk, m, k_steps):
+        r = _kernel_bench(torch, tk, m, device, k_steps, 10, seed=555 + 1000 * rank, env_off=rank * m, barrier=barrier,
+                          cfg_patch=make_kwargs)
+        t = torch.tensor([r["ms_total"]], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        return {"us_per_step": 1e3 * ms / k_steps, "env_steps_per_s": m * world * k_steps / (ms * 1e-3), "envs_per_gpu": m}
+
+    m = 65536
+    try:
+        with_x = timed({"world_reduce": True}, "gogoro_paper", m, 60)
+        no_x = timed({}, "gogoro_paper", m, 60)
+        env = _make_gogoro_paper(m, 4242 + rank, device, rank * m, world_reduce=True)[0]
+        env.post_physics_step()
+        torch.cuda.synchronize()
+        mine = env.diff_sums.clone()
+        every = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        same = all(torch.equal(every[0], e) for e in every)
+        out["paper_cross_env_mean"] = {**with_x, "us_per_step_without_exchange": no_x["us_per_step"],
+                                       "collective": "NCCL SUM all-reduce of 2 x fp64 between the fused kernel and the finalize grid, every step",
+                                       "reduced_sums_identical_on_all_ranks": bool(same), "reduced_sums": every[0].tolist()}
+        del env
+    except Exception as exc:
+        out["paper_cross_env_mean"] = {"error": repr(exc)}
+    try:
+        with_x = timed({"grip_all_reduce": True}, "ma_op3", m, 60)
+        no_x = timed({}, "ma_op3", m, 60)
+        twin = _make_ma_op3(m, 4343 + rank, device, rank * m, grip_all_reduce=False)[0]
+        twin.launch_post_physics()                  # same state, no exchange: this rank's own counts
+        local = twin.grip_count_buf.clone()
+        want = local.clone()
+        dist.all_reduce(want)                       # what the step's exchange must produce
+        env = _make_ma_op3(m, 4343 + rank, device, rank * m, grip_all_reduce=True)[0]
+        env.post_physics_step()
+        torch.cuda.synchronize()
+        del twin
+        ok = torch.equal(env.grip_count_buf.view(-1), want.view(-1))
+        okt = torch.tensor([1 if ok else 0], device=device, dtype=torch.int32)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        out["ma_op3_grip_counts"] = {**with_x, "us_per_step_without_exchange": no_x["us_per_step"],
+                                     "collective": "NCCL SUM all-reduce of int64[4] between the fused kernel and the finalize grid, every step",
+                                     "global_counts_equal_sum_of_rank_counts": bool(okt.item()),
+                                     "global_counts": want.view(-1).tolist(), "rank0_counts": local.view(-1).tolist()}
+        del env
+    except Exception as exc:
+        out["ma_op3_grip_counts"] = {"error": repr(exc)}
+    return out
+
+
 def run_gpu_arm(args, rank, world):
     import torch
     if not torch.cuda.is_available():
@@ -313,31 +417,53 @@ def run_gpu_arm(args, rank, world):
         sampler.start()
     windows = []
 
-    # ---- episode statistics: finalize per state set on device, one 8 x fp64 NCCL all-reduce per horizon (side stream)
+    # ---- episode statistics: finalize on device, one 8 x fp64 NCCL all-reduce per horizon (side stream).
+    # The hook is keyed on the TIMED step index and horizon = min(32, steps), so it fires inside every timed region
+    # (the driver's --steps 20 included); the partials of every state set are discarded after the warm-up.
     from thormang_isaacgym_b200.parallel import EpisodeStatsReducer
     reducer = EpisodeStatsReducer(device)
+    horizon = max(1, min(HORIZON, args.steps))
+    hook_log = {"launches": 0, "expected_env_steps": None}
 
-    hook_calls = [0]
-
-    def horizon_hook(envs):
+    def horizon_hook(env, steps_since):
         # what a training loop does once per rollout horizon: finalize the episode statistics of the env on device
         # (one tiny kernel) and all-reduce the 8 doubles on a side stream.  The rotating state sets exist only to defeat
-        # the L2, so one set is finalized per horizon (each set every len(envs) horizons), like a single real env.
-        e = envs[hook_calls[0] % len(envs)]
-        hook_calls[0] += 1
-        reducer.launch(e.episode_statistics())      # side stream; NCCL all-reduce when world > 1
+        # the L2: the set that has just stepped is finalized; it has run `steps_since` steps since its last finalize,
+        # identically on every rank, which fixes the env-step count the reduced vector must carry.
+        reducer.launch(env.episode_statistics())      # side stream; NCCL all-reduce when world > 1
+        hook_log["launches"] += 1
+        hook_log["expected_env_steps"] = float(world) * n * steps_since
         return 1
 
     res = _kernel_bench(torch, task, n, device, args.steps, max(args.warmup, 3), seed=1234 + 1000 * rank, env_off=rank * n,
-                        barrier=barrier, horizon_hook=None if os.environ.get("TK_BENCH_NO_HOOK") else horizon_hook)
+                        barrier=barrier, horizon_hook=None if os.environ.get("TK_BENCH_NO_HOOK") else horizon_hook,
+                        horizon=horizon)
     windows.append(res["window"])
     ms_local = res["ms_total"]
     ms_t = torch.tensor([ms_local], device=device, dtype=torch.float64)
+    per_rank_ms = [ms_local]
     if dist:
+        gathered = [torch.zeros_like(ms_t) for _ in range(world)]
+        dist.all_gather(gathered, ms_t)
+        per_rank_ms = [float(g.item()) for g in gathered]
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
     ms_total = float(ms_t.item())
     value = n * world * args.steps / (ms_total * 1e-3)
     ms_per_step = ms_total / args.steps
+
+    # the collective must have run, and the reduced vector must carry world x n x (steps since the set's last finalize)
+    stats_last = reducer.result()
+    stats_ran = hook_log["launches"]
+    stats_ok = stats_ran > 0 and abs(stats_last["env_steps"] - hook_log["expected_env_steps"]) < 0.5
+    if dist:
+        ok_t = torch.tensor([1 if stats_ok else 0], device=device, dtype=torch.int32)
+        dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
+        stats_ok = bool(ok_t.item())
+
+    multi = None
+    if dist and not os.environ.get("TK_BENCH_NO_DIAG"):
+        multi = _multi_gpu_diag(torch, dist, task, n, device, rank, world, local_rank, barrier, args.steps)
+        multi["per_rank_ms_total"] = per_rank_ms
 
     # ---- end-to-end through the public API with host buffers
     e2e = None
@@ -353,10 +479,6 @@ def run_gpu_arm(args, rank, world):
                "path": "HostBridge: pinned host state slab -> one H2D -> Humanoid.post_physics_step() -> one D2H of the "
                        "obs|rew|reset slab, range-sharded into chunks on separate streams so PCIe copies overlap the kernels"}
 
-    stats_last = reducer.result()
-    # self-check of the collective: every rank contributes the same number of env-steps per finalize
-    local_steps = float(n * HORIZON)
-    stats_ok = (args.steps < HORIZON) or abs(stats_last["env_steps"] - world * local_steps) < 0.5
     sampler.stop()
     clocks = sampler.summary(windows)
     if rank != 0:
@@ -381,9 +503,17 @@ def run_gpu_arm(args, rank, world):
         "e2e": e2e,
         "gpu_launches": res["launches"],
         "clocks": clocks,
-        "stats_allreduce": {"per": f"{HORIZON} steps", "payload_bytes": 64, "backend": "nccl" if dist else "none (1 GPU)", "sum_over_ranks_ok": bool(stats_ok),
+        "stats_allreduce": {"per": f"{horizon} timed steps", "payload_bytes": 64, "launched_in_timed_region": stats_ran,
+                            "backend": "nccl" if dist else "none (1 GPU: finalize kernel + side-stream copy, no collective)",
+                            "expected_env_steps": hook_log["expected_env_steps"],
+                            "sum_over_ranks_ok": bool(stats_ok) if dist else None,
+                            "local_sum_ok": bool(stats_ok) if not dist else None,
+                            "check": "reduced env_steps == world x envs_per_gpu x steps since the finalized set's last "
+                                     "finalize, on every rank (MIN over ranks); fails when no all-reduce ran",
                             "last": stats_last},
     }
+    if multi is not None:
+        line["multi_gpu"] = multi
 
     if world == 1 and not args.no_cpu_baseline:
         v, ms_cpu, done, threads = B.time_cpu(task, n, 1234, 400, 3, budget_s=args.cpu_seconds)

@@ -32,10 +32,35 @@ def close(got, want, rtol=RTOL, atol=ATOL, what=""):
                              f"got {got[tuple(idx)].item():.9g} want {want[tuple(idx)].item():.9g}; max err {err.max().item():.3g}")
 
 
-def angle_close(got, want, atol=ANGLE_ATOL, what=""):
+PI_F32 = float(np.float32(math.pi))          # 3.14159274...: the largest magnitude fp32 atan2 / a +-2*pi wrap can return
+CUT_TOL = 1e-4
+
+
+TWO_PI_F32 = float(np.float32(2 * math.pi))
+
+
+def angle_close(got, want, atol=ANGLE_ATOL, what="", bound=PI_F32, cut_tol=CUT_TOL, lo=None, flip_ok=None):
+    """Angles agree modulo 2*pi within atol, AND (the modulo is only legitimate next to the cut)
+    * every output lies in [lo, bound] (default [-pi_f32, pi_f32]; bound=None for channels whose range is open), and
+    * got and want pick different representatives (|got - want| > pi) only where the reference value itself sits within
+      cut_tol of an end of the range (or where ``flip_ok`` says the cut of an upstream angle is near) -- a kernel
+      returning yaw + 2*pi away from the cut fails."""
     got, want = got.detach().cpu().double(), want.detach().cpu().double()
     d = torch.remainder(got - want + math.pi, 2 * math.pi) - math.pi
     assert float(d.abs().max()) <= atol, f"{what}: max angular error {float(d.abs().max()):.3g}"
+    flipped = (got - want).abs() > math.pi
+    allowed = torch.zeros_like(flipped) if flip_ok is None else flip_ok.detach().cpu().bool().expand_as(flipped)
+    if bound is not None:
+        lo = -bound if lo is None else lo
+        eps = 2.0 ** -22 * max(abs(bound), abs(lo), 1.0)
+        over = (got > bound + eps) | (got < lo - eps)
+        assert not bool(over.any()), f"{what}: {int(over.sum())} outputs outside [{lo:.7g}, {bound:.7g}], e.g. {float(got[over][0]):.9g}"
+        allowed = allowed | ((want - bound).abs() <= cut_tol) | ((want - lo).abs() <= cut_tol)
+    elif flip_ok is None:
+        return                      # open range and no knowledge of the upstream cut: modulo comparison only
+    off_cut = flipped & ~allowed
+    assert not bool(off_cut.any()), (f"{what}: {int(off_cut.sum())} values differ from the reference by 2*pi away from "
+                                     f"the cut, e.g. got {float(got[off_cut][0]):.9g} want {float(want[off_cut][0]):.9g}")
 
 
 def exact(got, want, what=""):
@@ -59,7 +84,9 @@ def humanoid_obs_close(got, want, what="obs"):
 def gogoro_obs_close(got, want, what="obs", noisy=False):
     lin = [1, 2, 5] if noisy else [1, 2, 3, 5]
     close(got[:, lin], want[:, lin], what=what)
-    angle_close(got[:, [0, 4]], want[:, [0, 4]], what=what + "[angles]")
+    # noisy rows carry N(0, sigma) on both angle channels: their range is open and the cut of the clean angle is not
+    # visible in them (the clean rows of the same step are compared through buffer_obs with the range check on)
+    angle_close(got[:, [0, 4]], want[:, [0, 4]], what=what + "[angles]", bound=None if noisy else PI_F32)
     if noisy:   # channel 3 = round(delta_yaw): exact unless delta_yaw sits within the angle tolerance of k + 0.5
         g, w = got[:, 3].cpu(), want[:, 3].cpu()
         assert float((g - w).abs().max()) <= 1.0 and float((g != w).float().mean()) < 1e-3, what + "[round]"
@@ -121,9 +148,14 @@ ANT_ANGLE_COLS = [7, 8, 9]
 
 
 def ant_obs_close(got, want, what="obs"):
+    """ant.py:395-400 concatenates yaw, roll (get_euler_xyz: [0, 2*pi], cut at 0 / 2*pi) and the raw angle_to_target
+    (atan2 - yaw, open range) WITHOUT normalize_angle: the representative may flip only where yaw / roll sit at their cut."""
     rest = [c for c in range(got.shape[1]) if c not in ANT_ANGLE_COLS]
     close(got[:, rest], want[:, rest], what=what)
-    angle_close(got[:, ANT_ANGLE_COLS], want[:, ANT_ANGLE_COLS], what=what + "[angles]")
+    angle_close(got[:, [7, 8]], want[:, [7, 8]], what=what + "[yaw, roll]", lo=0.0, bound=TWO_PI_F32)
+    wy = want[:, 7].detach().cpu().double()
+    yaw_at_cut = (wy <= CUT_TOL) | (wy >= TWO_PI_F32 - CUT_TOL)
+    angle_close(got[:, 9], want[:, 9], what=what + "[angle_to_target]", bound=None, flip_ok=yaw_at_cut)
 
 
 def make_ant_pair(n, seed=1234, device="cuda:0", state=None, asset=None, **env_over):
@@ -165,7 +197,8 @@ def gogoro_paper_frame_close(got, want, what="frame", noisy=False):
         angle_close(got[:, [0, 1, 5]], want[:, [0, 1, 5]], what=what + "[angles]")
     else:
         close(got[:, [1, 2, 3, 4, 6, 7]], want[:, [1, 2, 3, 4, 6, 7]], what=what)
-        angle_close(got[:, [0, 5]] * math.pi, want[:, [0, 5]] * math.pi, atol=ANGLE_ATOL + 2e-6, what=what + "[angles/pi]")
+        angle_close(got[:, [0, 5]] * math.pi, want[:, [0, 5]] * math.pi, atol=ANGLE_ATOL + 2e-6, what=what + "[angles/pi]",
+                    bound=None)      # noise + offsets added after the wrap (:525-538): open range
 
 
 def make_gogoro_paper_pair(n, seed=1234, device="cuda:0", state=None, **env_over):

@@ -64,7 +64,7 @@ def test_golden_vectors(golden_dir):
     U.close(wm, g["wm_reward"], atol=1e-4, what="wm reward vs golden")   # potentials difference of ~6e4-sized terms / 6e4
 
 
-@pytest.mark.parametrize("n", [1, 33, 128, 257, 4096])
+@pytest.mark.parametrize("n", [1, 33, 128, 257, 4096, 16384, 131072])   # 16384 / 131072: BASELINE configs 2 and 4
 @pytest.mark.parametrize("mode", ["compact", "dense", "philox"])
 def test_fused_post_physics(n, mode):
     from thormang_isaacgym_b200 import _native as nat
@@ -105,6 +105,57 @@ def test_fused_post_physics(n, mode):
                          orc.obs_buf[:, 11].double().sum(), n], dtype=torch.float64)
     keep = [0, 1, 2, 4, 5, 6, 7]
     U.close(stats[keep], want[keep], rtol=1e-5, atol=1e-3, what="episode statistics")
+
+
+@pytest.mark.parametrize("mode", ["compact", "philox"])
+def test_fused_every_env_of_a_tile_resets(mode):
+    """All 32 envs of tile 1 (and a few of tiles 0 and 3) reset in one step: the kernel writes reset rows to global memory
+    while the bulk load of the same rows is in flight and patches the staged copy afterwards (tk_humanoid_tile.cuh); the
+    result must be the reference's reset -> observe order for every one of them, noise row k <-> k-th reset env."""
+    n = 160
+    env, orc, st = U.make_humanoid_pair(n, seed=404)
+    st["reset_buf"][:] = 0
+    st["reset_buf"][32:64] = 1
+    for i in (0, 5, 31, 96, 97, 98, 99, 100, 127):
+        st["reset_buf"][i] = 1
+    env.reset_buf.copy_(st["reset_buf"].to(DEV)); orc.reset_buf = st["reset_buf"].clone()
+    ids = orc.reset_buf.nonzero().flatten()
+    if mode == "compact":
+        ua, ub = syn.humanoid_reset_noise(len(ids), seed=11)
+        env.post_physics_step(ua.to(DEV), ub.to(DEV))
+    else:
+        pa, pb = env.philox_noise()
+        ua, ub = pa.cpu()[ids], pb.cpu()[ids]
+        env.post_physics_step()
+    orc.post_physics_step(ua, ub)
+    _check_obs_outputs(env, orc)
+    for name in ("reset_buf", "progress_buf", "dof_state", "root_states"):
+        U.exact(getattr(env, name), getattr(orc, name), name)
+    U.close(env.rew_buf, orc.rew_buf, what="rew_buf")
+    assert int((env.progress_buf[32:64] == 0).sum()) == 32
+
+
+def test_angle_to_target_beyond_pi():
+    """angle_to_target = atan2(..) - yaw spans (-3*pi, pi] before normalize_angle (humanoid.py:400-405).  With the target
+    BEHIND the robots (targets = (-1000, 0, 0), so atan2 ~ +-pi) every row has |angle_to_target| in (pi, 3*pi): the
+    kernel's +-2*pi wrap must land in [-pi, pi] and agree with atan2(sin, cos) -- checked with the range assertion on."""
+    n = 2048
+    env, orc, st = U.make_humanoid_pair(n, seed=31)
+    # pos.z above / below the target height so that atan2 sits on both sides of the cut, yaw uniform in [0, 2*pi)
+    env.targets[:] = torch.tensor([-1000.0, 0.0, 1.0], device=DEV)
+    orc.targets[:] = torch.tensor([-1000.0, 0.0, 1.0])
+    env._lib.tk_humanoid_destroy(env._handle)
+    env._create_native()
+    env.compute_observations()
+    orc.compute_observations()
+    from oracle import isaac_helpers as ih
+    q = ih.quat_mul(orc.root_states[:, 3:7], orc.inv_start_rot)
+    _, _, yaw = ih.get_euler_xyz(q)
+    raw = torch.atan2(orc.targets[:, 2] - orc.root_states[:, 2], orc.targets[:, 0] - orc.root_states[:, 0]) - yaw
+    frac = float(((raw.abs() > np.pi) & (raw.abs() < 3 * np.pi)).float().mean())
+    assert frac > 0.45, f"only {frac:.2f} of the rows exercise the wide range"
+    _check_obs_outputs(env, orc)
+    assert float(env.obs_buf[:, 9].abs().max()) <= U.PI_F32 * (1 + 2.0 ** -22)
 
 
 def test_pre_physics_and_reset_idx():

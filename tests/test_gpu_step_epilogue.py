@@ -169,3 +169,63 @@ def test_step_with_noise_and_clamp_anymal():
     U.exact(clean, want_noisy, "obs_buf holds the noisy observations (vec_task.py:349)")
     U.exact(buf[0], want_clamped, "rollout slot holds clamp(noisy obs)")
     assert float(buf[0].abs().max()) <= 5.0 and obs_d["obs"].data_ptr() == buf[0].data_ptr()
+
+
+def test_reset_done_after_kernel_filled_slot():
+    """A step that let the fused kernel fill the rollout slot must not leak into reset()/reset_done(): those return a
+    clamp of obs_buf (vec_task.py:386,400) and never touch or advance the rollout buffer."""
+    n, horizon = 256, 4
+    env, orc, st = U.make_humanoid_pair(n, seed=9)
+    buf = torch.full((horizon, n, 110), float("nan"), device=DEV)
+    env.set_rollout_buffer(buf)
+    env.step(torch.rand((n, 21), device=DEV) * 2 - 1)
+    torch.cuda.synchronize()
+    assert env._rollout_t == 1
+    obs_d, done = env.reset_done()
+    torch.cuda.synchronize()
+    U.exact(obs_d["obs"], env.obs_buf, "reset_done returns obs_buf")
+    assert env._rollout_t == 1 and bool(torch.isnan(buf[1]).all())          # slot 1 untouched, index not advanced
+    obs_d = env.reset()
+    U.exact(obs_d["obs"], env.obs_buf, "reset returns obs_buf")
+    assert env._rollout_t == 1
+    obs_d, *_ = env.step(torch.rand((n, 21), device=DEV) * 2 - 1)
+    torch.cuda.synchronize()
+    U.exact(buf[1], env.obs_buf, "the next step fills slot 1")
+    assert obs_d["obs"].data_ptr() == buf[1].data_ptr()
+
+
+def test_reset_is_clamp_only_under_observation_noise():
+    """reset()/reset_done() only clamp (vec_task.py:386,400): no noise lambda, no Philox call consumed, obs_buf unchanged."""
+    n = 300
+    env, orc, st = U.make_anymal_pair(n, seed=10)
+    env.apply_randomizations({"frequency": 1000, "observations": dict(GAUSS_SCALE)})
+    env.obs_buf.copy_(torch.randn((n, 61), device=DEV) * 4)                 # some entries beyond clipObservations = 5
+    before = env.obs_buf.clone()
+    calls = getattr(env, "_epilogue_calls", 0)
+    obs_d = env.reset()
+    torch.cuda.synchronize()
+    U.exact(env.obs_buf, before, "obs_buf untouched by reset()")
+    U.exact(obs_d["obs"], torch.clamp(before, -5.0, 5.0), "reset() = clamp(obs_buf)")
+    assert getattr(env, "_epilogue_calls", 0) == calls
+
+
+def test_fake_sim_counts_frames_for_the_dr_schedule():
+    """apply_randomizations reads gym.get_frame_count (vec_task.py:553): FakeSim.simulate() counts sim frames."""
+    env, _, _ = U.make_humanoid_pair(64, seed=3)
+    f0 = env.sim.frame_count
+    for _ in range(3):
+        env.step(torch.zeros((64, 21), device=DEV))
+    assert env.sim.frame_count == f0 + 3 * env.control_freq_inv
+    env.apply_randomizations({"frequency": 2, "observations": dict(GAUSS)})
+    assert env.last_step == env.sim.frame_count
+
+
+def test_non_fused_clip_path_accepts_host_and_double_actions():
+    """Gogoro (finite clipActions, no fused clip): actions arriving on the CPU / as float64 are moved and cast before
+    the clamp kernel sees a pointer (the reference's torch.clamp works on any device / dtype)."""
+    n = 200
+    env, orc, st = U.make_gogoro_pair(n, seed=12)
+    a = (torch.rand((n, 1), dtype=torch.float64) * 3 - 1.5)                 # host, fp64
+    env.step(a)
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(env.obs_buf).all())

@@ -24,7 +24,10 @@ def test_shard_range_partitions_exactly():
         par.shard_range(10, 2, 2)
     cfg = {"env": {"numEnvs": 1048576}}
     par.shard_cfg(cfg, 3, 8)
-    assert cfg["env"] == {"numEnvs": 131072, "envIdOffset": 393216}
+    # world > 1 also switches the two in-step exchanges on (MA_OP3 gripper counts, paper variants' cross-env mean)
+    assert cfg["env"] == {"numEnvs": 131072, "envIdOffset": 393216, "gripAllReduce": True, "worldReduce": True}
+    one = par.shard_cfg({"env": {"numEnvs": 4096}}, 0, 1)
+    assert one["env"] == {"numEnvs": 4096, "envIdOffset": 0}
 
 
 def _free_port():
@@ -165,3 +168,31 @@ def test_two_rank_ma_op3_grip_count_exchange(tmp_path):
     assert torch.equal(torch.cat([p["reset"] for p in parts]), full.reset_buf)
     # without the exchange rank-local counts would give agent 0 no hold term at all: the +1 is visible in the rewards
     assert float((full.rew_buf[:, 0] > 0).float().mean()) > 0.5
+
+
+def _init_worker(rank, world, port, out_dir):
+    os.environ.update({"MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "RANK": str(rank), "WORLD_SIZE": str(world),
+                       "LOCAL_RANK": str(rank)})
+    r, w, device, seed = par.init_multi_gpu(seed=40)         # what make(multi_gpu=True) calls (train.py:74-82)
+    from thormang_isaacgym_b200 import config as tcfg
+    cfg = par.shard_cfg(tcfg.humanoid_cfg(1001, seed=40), r, w)
+    t = torch.tensor([cfg["env"]["numEnvs"]], dtype=torch.int64)
+    dist.all_reduce(t)                                       # the group init_multi_gpu created is usable
+    torch.save({"rank": r, "world": w, "device": device, "seed": seed, "env": {k: cfg["env"][k] for k in
+               ("numEnvs", "envIdOffset", "gripAllReduce", "worldReduce")}, "total": int(t)},
+               os.path.join(out_dir, f"init{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_make_multi_gpu_host_logic(tmp_path):
+    """make(multi_gpu=True) = LOCAL_RANK -> device, seed + rank (train.py:74-82) + range sharding by global env id."""
+    world = 2
+    port = _free_port()
+    mp.spawn(_init_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    got = [torch.load(os.path.join(str(tmp_path), f"init{r}.pt"), weights_only=False) for r in range(world)]
+    assert [g["device"] for g in got] == ["cuda:0", "cuda:1"]
+    assert [g["seed"] for g in got] == [40, 41]
+    assert got[0]["env"] == {"numEnvs": 501, "envIdOffset": 0, "gripAllReduce": True, "worldReduce": True}
+    assert got[1]["env"] == {"numEnvs": 500, "envIdOffset": 501, "gripAllReduce": True, "worldReduce": True}
+    assert all(g["total"] == 1001 and g["world"] == 2 for g in got)

@@ -29,19 +29,34 @@ def test_header_symbols_exported(built_lib):
 
 
 def test_struct_layouts_match_header(built_lib):
-    """sizeof of the ctypes mirrors == sizeof in C (compiled with gcc from the header)."""
+    """Every struct of include/thormang_b200.h has a ctypes mirror in _native.py with the same sizeof and the same
+    offsetof for every field (compiled with gcc from the header): all 16 structs of the boundary, found by parsing the
+    header, so that a struct added there without a mirror fails here."""
     import subprocess
     import tempfile
     from thormang_isaacgym_b200 import _native as nat
-    src = ('#include <stdio.h>\n#include "thormang_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu\\n", '
-           'sizeof(TkHumanoidParams), sizeof(TkHumanoidBuffers), sizeof(TkResetNoise), sizeof(TkGogoroParams), '
-           'sizeof(TkGogoroBuffers), sizeof(TkGogoroNoise)); return 0;}\n')
+    header = open(os.path.join(ROOT, "include", "thormang_b200.h")).read()
+    names = re.findall(r"^typedef struct (Tk\w+) \{", header, re.M)
+    assert len(names) == 16, names
+    lines = []
+    for name in names:
+        mirror = getattr(nat, name[2:])                       # TkHumanoidParams -> nat.HumanoidParams
+        lines.append(f'printf("{name} %zu", sizeof({name}));')
+        for field, _ in mirror._fields_:
+            lines.append(f'printf(" %zu", offsetof({name}, {field}));')
+        lines.append('printf("\\n");')
+    src = '#include <stdio.h>\n#include <stddef.h>\n#include "thormang_b200.h"\nint main(){\n' + "\n".join(lines) + "\nreturn 0;}\n"
     with tempfile.TemporaryDirectory() as d:
         open(os.path.join(d, "s.c"), "w").write(src)
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), os.path.join(d, "s.c"), "-o", os.path.join(d, "s")])
-        sizes = [int(x) for x in subprocess.check_output([os.path.join(d, "s")]).split()]
-    mirrors = [nat.HumanoidParams, nat.HumanoidBuffers, nat.ResetNoise, nat.GogoroParams, nat.GogoroBuffers, nat.GogoroNoise]
-    assert sizes == [C.sizeof(m) for m in mirrors]
+        out = subprocess.check_output([os.path.join(d, "s")]).decode().splitlines()
+    assert len(out) == len(names)
+    for row in out:
+        name, size, *offs = row.split()
+        mirror = getattr(nat, name[2:])
+        assert int(size) == C.sizeof(mirror), f"{name}: sizeof {size} in C vs {C.sizeof(mirror)} in ctypes"
+        got = [getattr(mirror, f).offset for f, _ in mirror._fields_]
+        assert [int(o) for o in offs] == got, f"{name}: field offsets differ"
 
 
 def test_no_cpu_fallback():

@@ -40,8 +40,8 @@ static inline bool aligned_to(const void* p, size_t a) { return (reinterpret_cas
 // ---------------------------------------------------------------------------------------------
 // constants (fp32 values of the python doubles the reference passes to torch)
 // ---------------------------------------------------------------------------------------------
-__device__ __host__ constexpr float kPi = 3.14159265358979323846f;        // (float)np.pi
-__device__ __host__ constexpr float kTwoPi = 6.28318530717958647692f;     // (float)(2*np.pi)
+constexpr float kPi = 3.14159265358979323846f;        // (float)np.pi
+constexpr float kTwoPi = 6.28318530717958647692f;     // (float)(2*np.pi)
 
 // ---------------------------------------------------------------------------------------------
 // PTX wrappers: cache-hinted vector access, bulk (TMA) copies, mbarrier

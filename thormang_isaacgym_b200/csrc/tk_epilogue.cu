@@ -36,8 +36,9 @@ __device__ __forceinline__ float apply_one(float x, const Lambda& l, float corr,
 }
 
 // one thread = four consecutive elements.  unit: supplied draws (N(0,1) for gaussian, U(0,1) for uniform) or NULL = Philox
-// keyed by (seed, step, element index / 4).  noisy_out / clamped_out may be NULL or alias `in`.
-__global__ void __launch_bounds__(256) noise_clamp_kernel(const float* __restrict__ in, long long count, Lambda l,
+// keyed by (seed, step, element index / 4).  noisy_out / clamped_out may be NULL or alias `in` (obs_buf in place): `in` is
+// therefore NOT __restrict__ / read-only-path qualified; each thread reads its four elements before it writes them.
+__global__ void __launch_bounds__(256) noise_clamp_kernel(const float* in, long long count, Lambda l,
                                                           const float* __restrict__ corr, const float* __restrict__ unit,
                                                           unsigned long long seed, unsigned long long step,
                                                           const unsigned long long* __restrict__ epoch, long long elem_off,

@@ -5,7 +5,10 @@ range ``[r * N/W, (r+1) * N/W)`` of every state and output tensor, task constant
 in-kernel Philox noise is keyed by the GLOBAL env id (``cfg["env"]["envIdOffset"]``), so results do
 not depend on W.  The only collective is a SUM all-reduce of the 8 x fp64 episode-statistics vector
 (64 bytes, latency-bound), issued once per rollout horizon on a side stream so that it never sits on
-the step's critical path.  The reference has no collective at all (``multi_gpu`` only picks the device
+the step's critical path.  Two members of the task family have a cross-env reward term and therefore one more,
+IN-STEP, exchange each (a 16- / 32-byte all-reduce between the fused kernel and its finalize grid): the Gogoro paper
+variants (``worldReduce``) and MA_OP3 (``gripAllReduce``); ``shard_cfg`` switches both on.  The reference has no
+collective at all (``multi_gpu`` only picks the device
 and offsets the seed: train.py:74-82); parity for the reduced vector is defined against the
 single-process sum.
 
@@ -30,11 +33,39 @@ def shard_range(total_envs: int, rank: int, world: int) -> Tuple[int, int]:
 
 
 def shard_cfg(cfg: dict, rank: int, world: int) -> dict:
-    """Rewrite ``cfg["env"]["numEnvs"]`` / ``envIdOffset`` in place for this rank's shard (global numEnvs in)."""
+    """Rewrite ``cfg["env"]["numEnvs"]`` / ``envIdOffset`` in place for this rank's shard (global numEnvs in).
+
+    With ``world > 1`` the two in-step exchanges of the task family are switched on as well, so that rewards do not
+    depend on ``world``: MA_OP3's batch-global gripper counts (``gripAllReduce``, MA_OP3.py:346-358) and the paper
+    variants' cross-env reward mean (``worldReduce``, gogoro_realistic_turning_sim_paper.py:747).  Tasks without a
+    cross-env term ignore the keys."""
     lo, hi = shard_range(cfg["env"]["numEnvs"], rank, world)
     cfg["env"]["numEnvs"] = hi - lo
     cfg["env"]["envIdOffset"] = lo
+    if world > 1:
+        cfg["env"].setdefault("gripAllReduce", True)
+        cfg["env"].setdefault("worldReduce", True)
     return cfg
+
+
+def init_multi_gpu(seed: int = 0):
+    """What ``train.py:74-82`` does for ``multi_gpu=True``: pick ``cuda:LOCAL_RANK`` and offset the seed by the rank
+    -- plus the process group the stats / in-step all-reduces need.  Returns (rank, world, device string, seed)."""
+    import os
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    device = f"cuda:{local_rank}"
+    if world > 1 and dist.is_available() and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if torch.cuda.is_available():
+            torch.cuda.set_device(local_rank)
+            dist.init_process_group("nccl", device_id=torch.device(device))
+        else:                                   # CPU tests of the host logic (gloo); tasks themselves need CUDA
+            dist.init_process_group("gloo")
+    return rank, world, device, seed + rank     # train.py:80-82: cfg.seed += rank
 
 
 class EpisodeStatsReducer:

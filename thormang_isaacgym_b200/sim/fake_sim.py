@@ -66,6 +66,7 @@ class FakeSim:
         self.dof_position_target = None
         self.dof_velocity_target = None
         self.dt = None
+        self.frame_count = 0
 
     # -- tensor API -------------------------------------------------------------------------
     def acquire_actor_root_state_tensor(self): return self.root_states
@@ -96,8 +97,11 @@ class FakeSim:
     def set_dof_velocity_target_tensor(self, t): self.dof_velocity_target = t; return True
 
     def simulate(self):
+        self.frame_count += 1                            # gym.get_frame_count (vec_task.py:553): one per sim frame
         if self.physics is not None:
             self.physics(self)
+
+    def get_frame_count(self): return self.frame_count
 
     def fetch_results(self, wait=True): return True
 

@@ -104,7 +104,7 @@ class VecTask(Env):
         self.allocate_buffers()
         self.obs_dict = {}
         self._clip_in_kernel = False
-        self._rollout, self._rollout_t, self._slot_filled_by_kernel = None, 0, False
+        self._rollout, self._rollout_t = None, 0
         self.first_randomization, self.last_step, self.last_rand_step = True, -1, -1
 
     def allocate_buffers(self):
@@ -180,13 +180,14 @@ class VecTask(Env):
         """Tasks whose fused kernel can store its obs tile to a second destination override this and return True."""
         return False
 
-    def _clipped_obs(self):
-        """vec_task.py:347-353: observation noise lambda + clamp (+ the rollout slot) in one pass."""
+    def _clipped_obs(self, filled_by_kernel: bool = False):
+        """vec_task.py:347-353, called by ``step`` only: observation noise lambda + clamp (+ the rollout slot) in one pass.
+        ``filled_by_kernel``: the fused post-physics kernel of THIS step has already stored its obs tile into the slot."""
         rollout = getattr(self, "_rollout", None)
         noisy = bool(self.dr_randomizations.get("observations"))
         if rollout is not None:
             slot = rollout[self._rollout_t]
-            if not self._slot_filled_by_kernel:
+            if not filled_by_kernel:
                 self._noise_clamp(self.obs_buf, "observations", self.clip_obs, self.obs_buf if noisy else None, slot)
             self._rollout_t = (self._rollout_t + 1) % rollout.shape[0]
             return slot.to(self.rl_device)
@@ -195,6 +196,17 @@ class VecTask(Env):
             return self.obs_buf.to(self.rl_device)
         out = torch.empty_like(self.obs_buf)
         self._noise_clamp(self.obs_buf, "observations", self.clip_obs, self.obs_buf if noisy else None, out)
+        return out.to(self.rl_device)
+
+    def _clamped_obs_only(self):
+        """vec_task.py:386 / :400 (``reset`` / ``reset_done``): clamp only -- no noise lambda, no rollout slot."""
+        if np.isinf(self.clip_obs):
+            return self.obs_buf.to(self.rl_device)
+        from ... import _native as nat
+        out = torch.empty_like(self.obs_buf)
+        nat.check(nat.lib().tk_step_noise_clamp(
+            nat.ptr(self.obs_buf), self.obs_buf.numel(), None, None, None, 0, 0, 0, float(self.clip_obs), None,
+            nat.ptr(out), nat.current_stream_ptr(self.device)), "tk_step_noise_clamp")
         return out.to(self.rl_device)
 
     def step(self, actions: torch.Tensor):
@@ -211,22 +223,23 @@ class VecTask(Env):
         else:
             action_tensor = actions
             if not np.isinf(self.clip_actions):
-                action_tensor = torch.empty_like(actions)
-                self._noise_clamp(actions.contiguous(), "actions", self.clip_actions, None, action_tensor)
+                a = actions.to(self.device, dtype=torch.float).contiguous()      # the kernel takes a device fp32 pointer
+                action_tensor = torch.empty_like(a)
+                self._noise_clamp(a, "actions", self.clip_actions, None, action_tensor)
             self.pre_physics_step(action_tensor)
         for _ in range(self.control_freq_inv):
             self.sim.simulate()
         # the fused kernel stores its obs tile into the rollout slot as well when nothing has to be applied to it
         rollout = getattr(self, "_rollout", None)
-        self._slot_filled_by_kernel = False
+        filled = False                      # local to this step: reset()/reset_done() never see a stale flag
         if rollout is not None and np.isinf(self.clip_obs) and not self.dr_randomizations.get("observations"):
-            self._slot_filled_by_kernel = self._obs_copy_hook(rollout[self._rollout_t])
+            filled = self._obs_copy_hook(rollout[self._rollout_t])
         # post_physics_step also fills timeout_buf (vec_task.py:345) inside the fused kernel
         self.post_physics_step()
-        if self._slot_filled_by_kernel:
+        if filled:
             self._obs_copy_hook(None)
         self.extras["time_outs"] = self.timeout_buf.to(self.rl_device)
-        self.obs_dict["obs"] = self._clipped_obs()
+        self.obs_dict["obs"] = self._clipped_obs(filled)
         if self.num_states > 0:
             self.obs_dict["states"] = self.get_state()
         return self.obs_dict, self.rew_buf.to(self.rl_device), self.reset_buf.to(self.rl_device), self.extras
@@ -238,7 +251,7 @@ class VecTask(Env):
         one fused kernel.  The PhysX property setters (:648-768) are out of scope."""
         from ... import _native as nat
         rand_freq = dr_params.get("frequency", 1)                                    # :547
-        self.last_step = int(getattr(self.sim, "frame_count", self.last_step + 1))   # :553 gym.get_frame_count
+        self.last_step = int(getattr(self.sim, "frame_count", self.last_step + 1))   # :553 gym.get_frame_count (FakeSim counts simulate() calls)
         if self.first_randomization:
             do_nonenv_randomize = True                                               # :555
         else:
@@ -302,7 +315,7 @@ class VecTask(Env):
         pass
 
     def reset(self):
-        self.obs_dict["obs"] = self._clipped_obs()
+        self.obs_dict["obs"] = self._clamped_obs_only()                              # vec_task.py:386
         if self.num_states > 0:
             self.obs_dict["states"] = self.get_state()
         return self.obs_dict
@@ -311,7 +324,7 @@ class VecTask(Env):
         done_env_ids = self.reset_buf.nonzero(as_tuple=False).flatten()
         if len(done_env_ids) > 0:
             self.reset_idx(done_env_ids)
-        self.obs_dict["obs"] = self._clipped_obs()
+        self.obs_dict["obs"] = self._clamped_obs_only()                              # vec_task.py:400
         if self.num_states > 0:
             self.obs_dict["states"] = self.get_state()
         return self.obs_dict, done_env_ids

@@ -29,6 +29,13 @@ def main():
     args = ap.parse_args()
     peak, _ = B.measured_peak_gbs()
     bpe = B.BYTES_PER_ENV[args.task]
+    # clock ramp: the first measurement of a fresh process reads ~20 % slow (seen at 16384 envs: 9.9 vs 8.3 us)
+    w = torch.empty(64 << 20, device="cuda:0")
+    t_end = __import__("time").perf_counter() + 0.5
+    while __import__("time").perf_counter() < t_end:
+        w.mul_(1.0001)
+        torch.cuda.synchronize()
+    del w
     if args.kernel == "pre":
         pre_bytes = 252 if args.task == "humanoid" else 48
         for n in [int(x) for x in args.envs.split(",")]:
