@@ -159,6 +159,7 @@ def _time_steps(torch, step_fn, steps, warmup, barrier=None, after_warmup=None):
     for i in range(steps):
         launches += step_fn(warmup + i)
     ev1.record()
+    _time_steps.last_host_enqueue_ms = (time.perf_counter() - t0) * 1e3   # host time to enqueue the K steps (diagnostic)
     torch.cuda.synchronize()
     t1 = time.perf_counter()
     if barrier:
@@ -184,8 +185,11 @@ def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, b
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
+            # every replay draws fresh in-kernel noise: one epoch bump per task object, all of them ahead of the steps so
+            # that the step kernels follow one another directly (programmatic-launch edges between consecutive kernel nodes)
             for e in envs:
                 e.advance_noise_epoch()
+            for e in envs:
                 e.post_physics_step()
         passes = max(1, steps // sets)
 
@@ -200,6 +204,7 @@ def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, b
 
     def after_warmup():
         if horizon_hook is not None:
+            horizon_hook(envs[0], 0, warm=True)   # first use of the side stream / the fp64 all-reduce happens untimed
             for e in envs:
                 e.episode_statistics()      # finalize + zero the partials: the timed region starts from empty statistics
             for k in range(sets):
@@ -218,7 +223,8 @@ def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, b
 
     ms, launches, window = _time_steps(torch, step, steps, warmup, barrier, after_warmup)
     del envs
-    return {"ms_total": ms, "launches": launches, "sets": sets, "window": window, "steps": steps}
+    return {"ms_total": ms, "launches": launches, "sets": sets, "window": window, "steps": steps,
+            "host_enqueue_ms": _time_steps.last_host_enqueue_ms}
 
 
 def _e2e_bench(torch, n, device, steps, chunks, env_off, barrier=None):
@@ -325,8 +331,9 @@ def _multi_gpu_diag(torch, dist, task, n, device, rank, world, local_rank, barri
     for i in range(6):
         envs[i % sets].post_physics_step()
     torch.cuda.synchronize()
-    barrier()
-    torch.cuda.synchronize()
+    if barrier:
+        barrier()
+        torch.cuda.synchronize()
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
     evs[0].record()
     for i in range(steps):
@@ -335,12 +342,17 @@ def _multi_gpu_diag(torch, dist, task, n, device, rank, world, local_rank, barri
     torch.cuda.synchronize()
     per = torch.tensor([evs[i].elapsed_time(evs[i + 1]) * 1e3 for i in range(steps)], device=device, dtype=torch.float64)
     allp = [torch.zeros_like(per) for _ in range(world)]
-    dist.all_gather(allp, per)
+    if dist:
+        dist.all_gather(allp, per)
+    else:
+        allp = [per]
     out["per_step_us_after_barrier"] = {
         "note": "an event after EVERY step (this serialises consecutive launches: slower than the headline loop, "
                 "which records two events in all); first rows = head of the window",
         "per_rank": [[round(float(v), 2) for v in t.tolist()] for t in allp]}
     del envs
+    if not dist:
+        return out
 
     # ---- (2) in-step exchanges
     def timed(make_kwargs, tk, m, k_steps):
@@ -425,12 +437,15 @@ def run_gpu_arm(args, rank, world):
     horizon = max(1, min(HORIZON, args.steps))
     hook_log = {"launches": 0, "expected_env_steps": None}
 
-    def horizon_hook(env, steps_since):
+    def horizon_hook(env, steps_since, warm=False):
         # what a training loop does once per rollout horizon: finalize the episode statistics of the env on device
         # (one tiny kernel) and all-reduce the 8 doubles on a side stream.  The rotating state sets exist only to defeat
         # the L2: the set that has just stepped is finalized; it has run `steps_since` steps since its last finalize,
         # identically on every rank, which fixes the env-step count the reduced vector must carry.
         reducer.launch(env.episode_statistics())      # side stream; NCCL all-reduce when world > 1
+        if warm:
+            reducer.result()
+            return 1
         hook_log["launches"] += 1
         hook_log["expected_env_steps"] = float(world) * n * steps_since
         return 1
@@ -461,9 +476,10 @@ def run_gpu_arm(args, rank, world):
         stats_ok = bool(ok_t.item())
 
     multi = None
-    if dist and not os.environ.get("TK_BENCH_NO_DIAG"):
+    if not os.environ.get("TK_BENCH_NO_DIAG"):
         multi = _multi_gpu_diag(torch, dist, task, n, device, rank, world, local_rank, barrier, args.steps)
         multi["per_rank_ms_total"] = per_rank_ms
+        multi["rank0_host_enqueue_ms"] = res.get("host_enqueue_ms")
 
     # ---- end-to-end through the public API with host buffers
     e2e = None

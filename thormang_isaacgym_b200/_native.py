@@ -256,6 +256,17 @@ def ptr(t) -> int:
     return 0 if t is None else t.data_ptr()
 
 
+_device_index = {}
+
+
 def current_stream_ptr(device) -> int:
+    """cudaStream_t of torch's CURRENT stream on ``device`` ('cuda:1' | torch.device | int), as an integer.
+    Goes through the raw getter (no torch.cuda.Stream object is built): this sits on the per-step launch path."""
     import torch
-    return torch.cuda.current_stream(device).cuda_stream
+    idx = _device_index.get(device)
+    if idx is None:
+        d = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        idx = d.index if d.index is not None else torch.cuda.current_device()
+        if d.index is not None:             # 'cuda' without an index follows the current device: never cached
+            _device_index[device] = idx
+    return torch._C._cuda_getCurrentRawStream(idx)

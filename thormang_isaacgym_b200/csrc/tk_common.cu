@@ -24,6 +24,15 @@ const char* last_error() { return g_error; }
 
 __global__ void advance_epoch_kernel(unsigned long long* epoch) { *epoch += 1ull; }
 
+// Launch-floor probe: the shell of the fused kernels (programmatic dependent launch, dynamic shared memory of the
+// same size, one 4-byte store per CTA when `sink` is given) with nothing in between.
+__global__ void launch_floor_kernel(int* sink) {
+    extern __shared__ float pad[];
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (sink && threadIdx.x == 0) sink[blockIdx.x] = static_cast<int>(blockIdx.x) + (pad == nullptr);
+}
+
 }  // namespace tk
 
 extern "C" {
@@ -38,6 +47,26 @@ int tk_device_info(int device, int* sm_count, int* cc_major, int* cc_minor) {
     if (sm_count) *sm_count = prop.multiProcessorCount;
     if (cc_major) *cc_major = prop.major;
     if (cc_minor) *cc_minor = prop.minor;
+    return TK_OK;
+}
+
+// developer / bench probe, not part of the public header: one launch of an empty kernel with the launch shape of the
+// fused kernels, so that bench.py can print the launch + drain floor of this box next to the small-grid numbers
+int tk_debug_launch_floor(int grid, int block, int smem_bytes, int pdl, int* sink, void* stream) {
+    TK_REQUIRE(grid > 0 && block > 0 && smem_bytes >= 0, TK_ERR_INVALID, "bad launch shape");
+    if (smem_bytes > 48 * 1024)
+        TK_CUDA(cudaFuncSetAttribute(tk::launch_floor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = smem_bytes;
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    TK_CUDA(cudaLaunchKernelEx(&cfg, tk::launch_floor_kernel, sink));
     return TK_OK;
 }
 

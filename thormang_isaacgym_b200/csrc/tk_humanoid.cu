@@ -92,6 +92,7 @@ struct KParams {
     long long* dbg_ts;          // developer timeline probe (tools/tile_timeline.py); NULL in normal use
     int stagger_cycles;         // first-wave stagger: resident slot s of an SM delays its bulk loads by s * cycles (0 = off)
     int stagger_ctas;           // CTAs of the first wave (resident CTAs per SM x SMs)
+    int stagger_free;           // the first `stagger_free` resident slots of every SM start at once (fills the memory pipe), the rest are spaced
     int sm_count;
     int prefetch;               // L2 prefetch of the tile inputs ahead of griddepcontrol.wait
 };
@@ -148,6 +149,61 @@ __device__ __forceinline__ Head torso_math(const float* r, const KParams& p) {
     return h;
 }
 
+// The same arithmetic cut into four independent pieces, one per warp of the four-warp tile kernel
+// (tk_humanoid_quad.cuh); every piece re-derives the torso quaternion (9 multiplies) and evaluates its columns with
+// exactly the expressions of torso_math, so the two kernels agree bit for bit.
+struct HeadA { float height, up_proj, heading_proj, pot; V3 up, heading; };
+template <int VARIANT>
+__device__ __forceinline__ HeadA torso_part_a(const float* r, const KParams& p) {     // potentials, up / heading projections
+    HeadA h;
+    V3 pos{r[0], r[1], r[2]};
+    Q4 q{r[3], r[4], r[5], r[6]};
+    V3 tt{p.tgt[0] - pos.x, p.tgt[1] - pos.y, 0.0f};              // :391-392
+    float nrm = norm3_ref(tt);
+    h.pot = (-nrm) / p.dt;                                        // :395
+    float nclamp = fmaxf(nrm, 1e-9f);
+    V3 td{tt.x / nclamp, tt.y / nclamp, tt.z / nclamp};
+    Q4 tq = quat_mul_ref(q, Q4{p.isr[0], p.isr[1], p.isr[2], p.isr[3]});
+    h.up = quat_rotate_ref<1>(tq, V3{p.b1[0], p.b1[1], p.b1[2]});
+    h.heading = quat_rotate_ref<1>(tq, V3{p.b0[0], p.b0[1], p.b0[2]});
+    h.up_proj = h.up.z;
+    h.heading_proj = dot_ref(h.heading, td);
+    h.height = pos.z;
+    return h;
+}
+template <int VARIANT>
+__device__ __forceinline__ void torso_part_b(const float* r, const KParams& p, float* c1to6) {   // local velocities
+    Q4 q{r[3], r[4], r[5], r[6]};
+    Q4 tq = quat_mul_ref(q, Q4{p.isr[0], p.isr[1], p.isr[2], p.isr[3]});
+    V3 vel_loc = quat_rotate_ref<-1>(tq, V3{r[7], r[8], r[9]});
+    V3 angvel_loc = quat_rotate_ref<-1>(tq, V3{r[10], r[11], r[12]});
+    c1to6[0] = vel_loc.x; c1to6[1] = vel_loc.y; c1to6[2] = vel_loc.z;
+    if (VARIANT == kVarAnt) {
+        c1to6[3] = angvel_loc.x; c1to6[4] = angvel_loc.y; c1to6[5] = angvel_loc.z;
+    } else {
+        c1to6[3] = angvel_loc.x * p.ang_vel_scale; c1to6[4] = angvel_loc.y * p.ang_vel_scale; c1to6[5] = angvel_loc.z * p.ang_vel_scale;
+    }
+}
+template <int VARIANT>
+__device__ __forceinline__ void torso_part_c(const float* r, const KParams& p, float* yaw_out, float* roll_out) {   // columns 7, 8
+    Q4 q{r[3], r[4], r[5], r[6]};
+    Q4 tq = quat_mul_ref(q, Q4{p.isr[0], p.isr[1], p.isr[2], p.isr[3]});
+    float roll, yaw;
+    euler_roll_yaw_ref(tq, &roll, &yaw);
+    *yaw_out = (VARIANT == kVarAnt) ? yaw : normalize_angle_fast(yaw);
+    *roll_out = (VARIANT == kVarAnt) ? roll : normalize_angle_fast(roll);
+}
+template <int VARIANT>
+__device__ __forceinline__ float torso_part_d(const float* r, const KParams& p) {                // column 9: angle_to_target
+    Q4 q{r[3], r[4], r[5], r[6]};
+    Q4 tq = quat_mul_ref(q, Q4{p.isr[0], p.isr[1], p.isr[2], p.isr[3]});
+    float roll, yaw;
+    euler_roll_yaw_ref(tq, &roll, &yaw);                          // roll is dead here: the compiler drops its atan2
+    float walk = atan2f(p.tgt[2] - r[2], p.tgt[0] - r[0]);        // z and x, sic (compute_rot)
+    float att = walk - yaw;
+    return (VARIANT == kVarAnt) ? att : normalize_angle_fast(att);
+}
+
 // unscale (humanoid.py:406): (2x - hi - lo) / (hi - lo).  The numerator is formed exactly as the reference does;
 // the division is a multiplication by the host-rounded reciprocal (<= 1.5 ulp from the IEEE quotient, i.e. 2e-7
 // relative: far inside the 1e-5 parity tolerance, and no threshold of the live reward reads these columns).
@@ -158,6 +214,7 @@ __device__ __forceinline__ float unscale_ref(float x, float lo, float hi) { retu
 }  // namespace tk
 
 #include "tk_humanoid_tile.cuh"
+#include "tk_humanoid_quad.cuh"
 
 namespace tk {
 namespace humanoid {
@@ -434,13 +491,18 @@ struct TkHumanoid {
     int use_pdl;          // programmatic dependent launch (TK_HUMANOID_PDL=0 disables)
     int stagger_cycles;   // TK_HUMANOID_STAGGER (SM cycles per resident slot), see the kernel
     int stagger_slots;    // TK_HUMANOID_STAGGER_SLOTS
+    int stagger_free;     // TK_HUMANOID_STAGGER_FREE
     int smem_pad;         // TK_HUMANOID_SMEM_PAD: extra dynamic shared memory per CTA (caps the resident CTAs per SM)
     int prefetch;         // TK_HUMANOID_PREFETCH: L2 prefetch ahead of griddepcontrol.wait (default: small grids only)
     int sm_count;
+    int quad;             // TK_HUMANOID_QUAD: four-warp tile kernel (tk_humanoid_quad.cuh) 1 | one-warp kernel 0; default by grid size
     unsigned long long* step_dev;
     long long* dbg_ts;
 };
 
+// the four-warp kernel runs while the whole grid is resident at once (7 CTAs / SM: up to 33152 envs on 148 SMs); measured
+// B200, us / step, four-warp vs one-warp: 6.7 / 8.3 at 16384 envs, 9.3 / 9.9 at 32768, 15.0 / 13.3 at 65536, 25.9 / 22.6 at 131072
+static constexpr int kQuadMaxTilesPerSm = 7;
 static constexpr int kD = HumanoidSpec::D;
 static constexpr int kDAnt = AntSpec::D;
 
@@ -450,14 +512,19 @@ static void launch_tile(const TkHumanoid* h, const KParams& k, cudaStream_t st) 
     // drains; the kernel itself executes griddepcontrol.wait before it touches global memory, so stream order is kept.
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(h->tiles);
-    cfg.blockDim = dim3(kTile);
-    cfg.dynamicSmemBytes = h->smem_pad;
+    cfg.blockDim = dim3(h->quad ? kQuadThreads : kTile);
+    cfg.dynamicSmemBytes = h->quad ? 0 : h->smem_pad;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = h->use_pdl ? 1 : 0;
+    if (h->quad) {      // thin / medium grids: four warps per tile (tk_humanoid_quad.cuh)
+        if (h->variant == kVarAnt) cudaLaunchKernelEx(&cfg, humanoid_quad_kernel<AntSpec, FUSED>, k);
+        else cudaLaunchKernelEx(&cfg, humanoid_quad_kernel<HumanoidSpec, FUSED>, k);
+        return;
+    }
     if (h->variant == kVarAnt) cudaLaunchKernelEx(&cfg, humanoid_warp_kernel<AntSpec, FUSED>, k);
     else cudaLaunchKernelEx(&cfg, humanoid_warp_kernel<HumanoidSpec, FUSED>, k);
 }
@@ -473,7 +540,7 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     k.init_root = B.initial_root_states; k.init_dof_pos = B.initial_dof_pos; k.ep_return = B.episode_return;
     k.partials = h->partials; k.tile_rank_base = h->tile_base; k.dbg_ts = h->dbg_ts; k.step_dev = h->step_dev;
     k.prefetch = h->prefetch;
-    k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count;
+    k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count; k.stagger_free = h->stagger_free;
     k.unit_a = nullptr; k.unit_b = nullptr; k.noise_rows = 0; k.seed = 0; k.step = 0; k.env_off = 0;
     k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs;
@@ -535,6 +602,8 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     if (const char* env = getenv("TK_HUMANOID_PREFETCH")) h->prefetch = atoi(env);
     if (const char* env = getenv("TK_HUMANOID_STAGGER")) h->stagger_cycles = atoi(env);
     if (const char* env = getenv("TK_HUMANOID_STAGGER_SLOTS")) h->stagger_slots = atoi(env);
+    h->stagger_free = 0;
+    if (const char* env = getenv("TK_HUMANOID_STAGGER_FREE")) h->stagger_free = atoi(env);
     if (const char* env = getenv("TK_HUMANOID_SMEM_PAD")) {
         h->smem_pad = atoi(env);
         cudaFuncSetAttribute(humanoid_warp_kernel<HumanoidSpec, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_pad);
@@ -544,6 +613,20 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     // L2 prefetch ahead of griddepcontrol.wait pays only while the whole grid is resident at once and thin (measured:
     // 10.1 -> 8.3 us at 16384 envs, but +1.8 us at 65536 where it re-synchronises the staggered first wave)
     if (h->prefetch < 0) h->prefetch = (h->tiles <= 4 * h->sm_count) ? 2 : 0;
+    // four-warp tiles while the grid is at most a few waves deep, one-warp tiles (most bytes in flight per SM) beyond
+    h->quad = (h->tiles <= kQuadMaxTilesPerSm * h->sm_count) ? 1 : 0;
+    if (const char* env = getenv("TK_HUMANOID_QUAD")) h->quad = atoi(env) != 0;
+    // the four-warp kernel only runs single-wave grids, where spacing the CTAs merely delays them (6.5 us with 0 cycles,
+    // 6.8 with 500, 7.4 with 1000 at 16384 envs)
+    if (h->quad && !getenv("TK_HUMANOID_STAGGER")) h->stagger_cycles = 0;
+    if (h->quad && !getenv("TK_HUMANOID_STAGGER_SLOTS")) {      // the stagger counts the resident CTAs of the kernel that runs
+        int occ = 0;
+        cudaError_t oe = (params->variant == kVarAnt)
+            ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, humanoid_quad_kernel<AntSpec, true>, kQuadThreads, 0)
+            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, humanoid_quad_kernel<HumanoidSpec, true>, kQuadThreads, 0);
+        if (oe == cudaSuccess && occ > 0) h->stagger_slots = occ;
+        else cudaGetLastError();
+    }
     h->last_grid = 0;
     h->partials = nullptr; h->tile_counts = nullptr; h->tile_base = nullptr; h->step_dev = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);

@@ -57,14 +57,17 @@ __device__ __forceinline__ void warp_copy(float* dst, const float* src, int cnt,
 // reset_idx :253-279 for env `ne` (lane = DOF): draws the noise, writes the new (pos, vel) pairs and the initial root
 // row to GLOBAL memory and returns this lane's values so that the caller can patch its staged copy.
 // `rank` = index of this env among the envs being reset (COMPACT noise rows follow the reference's nonzero() order).
+// split in two so that a tile with several flagged envs can request ALL their rows first (one DRAM round trip, not one
+// per env) and only then draw the noise and write
+template <int D>
+__device__ __forceinline__ void reset_env_fetch(const KParams& p, int ne, int lane, float* idp, float* rv) {
+    *idp = (lane < D) ? p.init_dof_pos[static_cast<size_t>(ne) * D + lane] : 0.0f;
+    *rv = (lane < kRoot) ? p.init_root[static_cast<size_t>(ne) * kRoot + lane] : 0.0f;   // :265-267 root row <- initial_root_states
+}
 template <int D>   // reset_idx of humanoid.py:253-279 and ant.py:247-271 (identical bodies)
-__device__ __forceinline__ void reset_env_values(const KParams& p, int ne, int rank, int lane, float2* pv_out, float* root_out) {
+__device__ __forceinline__ void reset_env_apply(const KParams& p, int ne, int rank, int lane, float idp, float rv, float2* pv_out) {
     const long long row = (p.noise_mode == TK_NOISE_COMPACT) ? rank : ne;
     float2 pv = make_float2(0.0f, 0.0f);
-    float rv = 0.0f;
-    // both global reads are requested before the noise is computed
-    const float idp = (lane < D) ? p.init_dof_pos[static_cast<size_t>(ne) * D + lane] : 0.0f;
-    if (lane < kRoot) rv = p.init_root[static_cast<size_t>(ne) * kRoot + lane];    // :265-267 root row <- initial_root_states
     if (lane < D) {
         const int j = lane;
         float ua = 0.5f, ub = 0.5f;
@@ -85,6 +88,12 @@ __device__ __forceinline__ void reset_env_values(const KParams& p, int ne, int r
     }
     if (lane < kRoot) p.root[static_cast<size_t>(ne) * kRoot + lane] = rv;
     *pv_out = pv;
+}
+template <int D>
+__device__ __forceinline__ void reset_env_values(const KParams& p, int ne, int rank, int lane, float2* pv_out, float* root_out) {
+    float idp, rv;
+    reset_env_fetch<D>(p, ne, lane, &idp, &rv);    // both global reads are requested before the noise is computed
+    reset_env_apply<D>(p, ne, rank, lane, idp, rv, pv_out);
     *root_out = rv;
 }
 
@@ -163,7 +172,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     // store-all phases in lockstep and HBM idles during the math; later CTAs start as slots free up and are staggered
     // by construction.  Resident slot s (~ blockIdx / #SMs) of the first wave waits s * stagger_cycles.
     if (p.stagger_cycles > 0 && blockIdx.x < static_cast<unsigned>(p.stagger_ctas)) {
-        const long long until = clock64() + static_cast<long long>(blockIdx.x / p.sm_count) * p.stagger_cycles;
+        const long long until = clock64() + static_cast<long long>(max(0, static_cast<int>(blockIdx.x / p.sm_count) - p.stagger_free)) * p.stagger_cycles;
         while (clock64() < until) __nanosleep(32);
     }
     if (bulk) {
@@ -205,7 +214,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     // ---- reset prologue (rare): reset_idx :253-279 for this tile's flagged envs, lane = DOF.  The new state does not
     // depend on the staged tile, so for the first kPre flagged envs it is computed and written to global memory WHILE
     // the bulk loads are still in flight; only the patch of the staged copy waits for them.
-    constexpr int kPre = 2;
+    constexpr int kPre = 4;                // 1 % of the envs resetting: 0.4 % of the tiles have 3+ resets, 0.003 % have 5+
     unsigned reset_bits = 0;
     int rank0 = 0;
     float2 pre_pv[kPre];
@@ -214,13 +223,27 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
         reset_bits = __ballot_sync(0xffffffffu, do_reset);
         if (reset_bits) {
             rank0 = (p.noise_mode == TK_NOISE_COMPACT) ? p.tile_rank_base[blockIdx.x] : 0;
+            // the rows of ALL (up to kPre) flagged envs are requested first: one DRAM round trip instead of one per env
+            // (tiles with 3-4 resets used to finish them one after the other behind the wait and were the last ~1 us of
+            // every launch: tools/tile_timeline.py prints the stragglers)
+            float idp[kPre];
             unsigned bits = reset_bits;
+#pragma unroll
+            for (int q = 0; q < kPre; ++q) {
+                idp[q] = 0.0f; pre_root[q] = 0.0f;
+                if (bits) {
+                    const int e = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    reset_env_fetch<D>(p, env0 + e, lane, &idp[q], &pre_root[q]);
+                }
+            }
+            bits = reset_bits;
 #pragma unroll
             for (int q = 0; q < kPre; ++q) {
                 if (bits) {
                     const int e = __ffs(bits) - 1;
                     bits &= bits - 1;
-                    reset_env_values<D>(p, env0 + e, rank0 + q, lane, &pre_pv[q], &pre_root[q]);
+                    reset_env_apply<D>(p, env0 + e, rank0 + q, lane, idp[q], pre_root[q], &pre_pv[q]);
                 }
             }
         }

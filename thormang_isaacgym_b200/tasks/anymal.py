@@ -202,7 +202,7 @@ class Anymal(VecTask):
                           unit_cmd: Optional[torch.Tensor] = None):
         """:234-242 + vec_task.py:345 as one fused kernel.  Supplied draws are addressed by env id ([N, ...]);
         in-kernel Philox noise when none is given."""
-        stream = torch.cuda.current_stream(self._torch_device).cuda_stream
+        stream = nat.current_stream_ptr(self._torch_device)
         if unit_pos is None and unit_vel is None and unit_cmd is None:
             nz = self._philox_noise
             nz.seed, nz.step, nz.env_id_offset = self.noise_seed, self.step_count, self.env_id_offset

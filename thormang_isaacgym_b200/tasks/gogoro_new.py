@@ -249,7 +249,7 @@ class Gogoro(VecTask):
             nz = self._philox_noise
             nz.reset.seed, nz.reset.step, nz.reset.env_id_offset = self.noise_seed, self.step_count, self.env_id_offset
             rc = self._post_physics(self._handle, self._philox_noise_ref,
-                                    torch.cuda.current_stream(self._torch_device).cuda_stream)
+                                    nat.current_stream_ptr(self._torch_device))
             if rc:
                 nat.check(rc, "tk_gogoro_post_physics")
             self.step_count += 1

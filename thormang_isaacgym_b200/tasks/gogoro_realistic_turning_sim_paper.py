@@ -260,7 +260,7 @@ class Gogoro(VecTask):
     def _finalize(self, stream=None):
         """Second kernel of a step: the cross-env reward term (:747), with the all-reduce when range-sharded."""
         if stream is None:
-            stream = torch.cuda.current_stream(self._torch_device).cuda_stream
+            stream = nat.current_stream_ptr(self._torch_device)
         sums = 0
         if self._world_group is not None:
             import torch.distributed as dist
@@ -302,7 +302,7 @@ class Gogoro(VecTask):
         env id ([N, ...] tensors); in-kernel Philox noise when none is given."""
         keep = []
         nz = self._noise(sensor_unit, reset_unit, speed_unit, yaw_unit, keep)
-        stream = torch.cuda.current_stream(self._torch_device).cuda_stream
+        stream = nat.current_stream_ptr(self._torch_device)
         rc = self._post_physics(self._handle, nz, stream)
         if rc:
             nat.check(rc, "tk_gogoro_paper_post_physics")

@@ -168,6 +168,7 @@ class Humanoid(VecTask):
         self._noise = nat.ResetNoise()
         self._noise.seed, self._noise.env_id_offset = self.noise_seed, self.env_id_offset
         self._noise_ref = C.byref(self._noise)
+        self._noise_is_philox = False
         self._bind()
 
     def _bind(self):
@@ -251,15 +252,21 @@ class Humanoid(VecTask):
                           noise_mode: Optional[int] = None):
         """humanoid.py:287-296 + vec_task.py:345 as one fused kernel."""
         noise = self._noise                     # one struct per task object: nothing is allocated per step
-        if unit_pos is not None:
-            unit_pos, unit_vel = unit_pos.contiguous(), unit_vel.contiguous()
-            noise.mode = nat.NOISE_COMPACT if noise_mode is None else noise_mode
-            noise.unit_a, noise.unit_b, noise.rows = nat.ptr(unit_pos), nat.ptr(unit_vel), unit_pos.shape[0]
+        if unit_pos is None and noise_mode is None:
+            if not self._noise_is_philox:       # the default path touches only what changes from step to step
+                noise.mode, noise.unit_a, noise.unit_b, noise.rows = nat.NOISE_PHILOX, None, None, 0
+                self._noise_is_philox = True
         else:
-            noise.mode = nat.NOISE_PHILOX if noise_mode is None else noise_mode
-            noise.unit_a, noise.unit_b, noise.rows = None, None, 0
+            self._noise_is_philox = False
+            if unit_pos is not None:
+                unit_pos, unit_vel = unit_pos.contiguous(), unit_vel.contiguous()
+                noise.mode = nat.NOISE_COMPACT if noise_mode is None else noise_mode
+                noise.unit_a, noise.unit_b, noise.rows = nat.ptr(unit_pos), nat.ptr(unit_vel), unit_pos.shape[0]
+            else:
+                noise.mode = noise_mode
+                noise.unit_a, noise.unit_b, noise.rows = None, None, 0
         noise.seed, noise.step, noise.env_id_offset = self.noise_seed, self.step_count, self.env_id_offset
-        rc = self._post_physics(self._handle, self._noise_ref, torch.cuda.current_stream(self._torch_device).cuda_stream)
+        rc = self._post_physics(self._handle, self._noise_ref, nat.current_stream_ptr(self._torch_device))
         if rc:
             nat.check(rc, "tk_humanoid_post_physics")
         self.step_count += 1

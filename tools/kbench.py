@@ -25,6 +25,8 @@ def main():
     ap.add_argument("--pdl", default="1")
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--kernel", default="post", choices=["post", "pre"])
+    ap.add_argument("--graph", action="store_true", help="capture one pass over the state sets in a CUDA graph and replay it")
+    ap.add_argument("--host", action="store_true", help="host cost of one post_physics_step() call (no GPU wait in between)")
     ap.add_argument("--sweep", default="", help="ENV_VAR=v1,v2,... : one line per value (developer knobs of the kernels)")
     args = ap.parse_args()
     peak, _ = B.measured_peak_gbs()
@@ -57,15 +59,29 @@ def main():
             print(json.dumps({"task": args.task, "kernel": "pre_physics", "envs": n, "us_per_step": round(us, 2),
                               "GBps": round(gbs, 1), "frac": round(gbs / peak, 4), "sets": sets}), flush=True)
         return
+    if args.host:
+        import time
+        env = G._MAKERS[args.task](32, 5, "cuda:0")[0]
+        for _ in range(200):
+            env.post_physics_step()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(5000):
+            env.post_physics_step()
+        t1 = time.perf_counter()
+        torch.cuda.synchronize()
+        print(json.dumps({"task": args.task, "host_us_per_call": round((t1 - t0) / 5000 * 1e6, 2),
+                          "note": "32 envs: the GPU side is the empty-launch floor, the loop is bound by the host call"}), flush=True)
+        return
     if args.sweep:
         key, vals = args.sweep.split("=")
         for n in [int(x) for x in args.envs.split(",")]:
             for v in vals.split(","):
                 os.environ[key] = v
-                r = G._kernel_bench(torch, args.task, n, "cuda:0", args.steps, args.warmup, seed=5)
-                us = 1e3 * r["ms_total"] / args.steps
+                r = G._kernel_bench(torch, args.task, n, "cuda:0", args.steps, args.warmup, seed=5, graph=args.graph)
+                us = 1e3 * r["ms_total"] / r["steps"]
                 gbs = n * bpe / (us * 1e-6) / 1e9
-                print(json.dumps({"task": args.task, "envs": n, key: v, "us_per_step": round(us, 2),
+                print(json.dumps({"task": args.task, "envs": n, "graph": args.graph, key: v, "us_per_step": round(us, 2),
                                   "GBps": round(gbs, 1), "frac": round(gbs / peak, 4), "sets": r["sets"]}), flush=True)
         return
     for n in [int(x) for x in args.envs.split(",")]:

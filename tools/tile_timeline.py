@@ -32,6 +32,7 @@ lib.tk_debug_humanoid_timeline(e._handle, C.c_void_p(buf.data_ptr()))
 for o in envs[4:] + envs[:3]:
     o.post_physics_step()
 torch.cuda.synchronize()
+e_reset_before = e.reset_buf.clone().cpu()
 e.post_physics_step()
 torch.cuda.synchronize()
 t = buf.cpu().double()
@@ -44,3 +45,27 @@ for i, nm in enumerate(names):
 d = t[:, 1:7] - t[:, 0:6]
 for i, nm in enumerate(["issue", "scalar wait", "bulk wait", "reset+reg read", "math+STS", "store"]):
     print(f"  phase {nm:14s} median {d[:, i].median()/1e3:6.2f}  mean {d[:, i].mean()/1e3:6.2f}  p95 {d[:, i].quantile(0.95)/1e3:6.2f} us")
+
+# bandwidth over time: a tile's 13.9 KB of loads are counted when its bulk load has landed, its 14.1 KB obs tile when the
+# bulk store has been read out of shared memory (the per-env scalars ride along): where is HBM idle -- head, middle, tail?
+w = 1024.0                                   # ns per bucket
+landed = ((t[:, 3] - t0) / w).long()
+stored = ((t[:, 6] - t0) / w).long()
+nb = int(stored.max()) + 1
+ld = torch.bincount(landed, minlength=nb).double() * (109 * 32 * 4 + 32 * 28)
+stv = torch.bincount(stored, minlength=nb).double() * (110 * 32 * 4 + 32 * 29)
+print("bucket(us)  loaded MB  stored MB  GB/s")
+for b in range(nb):
+    print(f"{b * w / 1e3:6.2f}    {ld[b] / 1e6:8.2f}  {stv[b] / 1e6:8.2f}  {(ld[b] + stv[b]) / w:8.0f}")
+
+# the stragglers: the ten tiles that finish last, with their stamps (us after the first start) and reset counts
+rb = e_reset_before.view(-1, 32).sum(1) if e_reset_before.numel() % 32 == 0 else None
+order = torch.argsort(t[:, 6], descending=True)[:10]
+print("last tiles: blockIdx  resets | start issue scal bulk regs math done")
+for i in order.tolist():
+    row = " ".join(f"{(t[i, k] - t0) / 1e3:6.2f}" for k in range(7))
+    print(f"  {i:6d}  {int(rb[i]) if rb is not None else -1:3d} | {row}")
+first = torch.argsort(t[:, 6])[:5]
+for i in first.tolist():
+    row = " ".join(f"{(t[i, k] - t0) / 1e3:6.2f}" for k in range(7))
+    print(f"  first {i:6d}  {int(rb[i]) if rb is not None else -1:3d} | {row}")
