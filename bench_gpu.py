@@ -136,6 +136,8 @@ _LAUNCHES_PER_STEP = {"ma_op3": 2, "anymal": 1, "humanoid": 1, "gogoro": 1, "gog
 
 
 def _rotating_sets(n, bytes_per_env):
+    if os.environ.get("TK_BENCH_SETS"):           # developer knob (tools/kbench.py): L2-resident vs HBM-cold comparisons
+        return int(os.environ["TK_BENCH_SETS"])
     per_set = n * bytes_per_env
     return max(3, int(math.ceil(2.2 * B.L2_BYTES / per_set)))
 

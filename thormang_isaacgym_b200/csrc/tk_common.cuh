@@ -250,8 +250,10 @@ __device__ __host__ __forceinline__ Philox4 philox_env(uint64_t seed, uint64_t s
 // graph draws fresh noise.  (A per-launch device counter was tried first: one same-address RED per CTA cost 20 % of
 // the kernel time at 32768 CTAs.)
 // ---------------------------------------------------------------------------------------------
+// `epoch` may be NULL: a handle whose epoch was never advanced passes NULL, so that eager launches neither read global
+// memory for it nor make their first Philox block wait on that read.
 __device__ __forceinline__ unsigned long long effective_step(unsigned long long step, const unsigned long long* epoch) {
-    return step + (*epoch << 32);
+    return epoch ? step + (*epoch << 32) : step;
 }
 __global__ void advance_epoch_kernel(unsigned long long* epoch);
 

@@ -6,10 +6,13 @@
 //   reset_idx :505-590 (+ randomize :474-482, generate_spawn_r :485-492, euler_to_quaternion :496-502),
 //   compute_gogoro_observations :692-723, shortest_angle_distance :687-689, compute_gogoro_reward :645-684.
 //
-// 192 B / env-step of algorithmic traffic (172 B with in-kernel Philox noise).  One warp = one CTA = 32 consecutive
-// envs, lane e owns env e.  The AoS rows that are not a multiple of 16 bytes (root 52 B, action history 20 B, supplied
+// 192 B / env-step of algorithmic traffic (172 B with in-kernel Philox noise).  One CTA = four warps = 128 consecutive
+// envs, thread e owns env e.  The AoS rows that are not a multiple of 16 bytes (root 52 B, action history 20 B, supplied
 // sensor noise 20 B, the two 24 B obs rows) move as cp.async.bulk (TMA) tile copies through shared memory (row strides
 // 13 / 5 / 6 words: conflict-free or 2-way), everything else is a coalesced 4/8-byte access per lane.
+// 128-env CTAs, not 32: a B200 dispatches ~0.85 CTA / ns (tools/launch_floor.py: an EMPTY 2048-CTA grid takes 2.4 us, a
+// 4096-CTA grid 4.8 us), so with one warp per CTA the 65536-env launch spent 2.4 us and the 4 M-env launch 153 us --
+// more than its 113 us of HBM time -- on CTA dispatch alone.
 #include "tk_common.cuh"
 
 #include <new>
@@ -22,7 +25,7 @@ constexpr int kObs = 6;
 constexpr int kHist = 5;
 constexpr int kSensorNoise = 5;
 constexpr int kResetNoise = 10;
-constexpr int kTile = 32;      // envs per CTA == one warp (tile slices of every array are 16-byte aligned bulk-copy operands)
+constexpr int kTile = 128;     // envs per CTA (tile slices of every array are 16-byte aligned bulk-copy operands)
 constexpr int kWarps = kTile / 32;
 
 struct KParams {
@@ -61,6 +64,7 @@ struct KParams {
     int noise_mode;
     int n, num_dof, steering_joint, rear_wheel_joint, max_episode_length, speed_freq, yaw_freq;
     int vec_ok;
+    long long* dbg_ts;            // developer timeline probe (tools/tile_timeline.py --task gogoro); NULL in normal use
     float max_steering, max_steering_change;
     // (float)lo / (float)mean, (float)(hi - lo) / (float)std with the span formed in double (get_randoms :466-467)
     float imu_filter[2], imu[2], speed_sensor[2], steer_action[2], speed[2], seat_x[2], seat_y[2], seat_z[2], seat_xr[2],
@@ -88,6 +92,40 @@ __device__ __forceinline__ MiscNoise philox_misc_noise(unsigned long long seed, 
     Philox4 b = philox_env(seed, step, env, kStreamMisc);
     float2 n = normal_pair(b.x, b.y);
     return MiscNoise{n.x, n.y, u01(b.z), u01(b.w)};
+}
+// The reset draws run in a handful of warps per launch, i.e. from a cold instruction cache: the three Philox blocks and the
+// three Box-Muller pairs go through ONE out-of-line copy each (3 KB of code instead of 10 KB fetched on the critical path
+// of the tiles that hold a reset -- those tiles set the length of a small launch).
+__device__ __noinline__ Philox4 philox_env_cold(unsigned long long seed, unsigned long long step, long long env, unsigned stream_id) {
+    unsigned k0 = static_cast<unsigned>(seed), k1 = static_cast<unsigned>(seed >> 32);
+    const unsigned long long hi = (step << 8) | stream_id;
+    Philox4 c{static_cast<unsigned>(env), static_cast<unsigned>(static_cast<unsigned long long>(env) >> 32), static_cast<unsigned>(hi),
+              static_cast<unsigned>(hi >> 32)};
+#pragma unroll 1
+    for (int r = 0; r < 10; ++r) {
+        const unsigned hi0 = mulhi32(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const unsigned hi1 = mulhi32(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = Philox4{hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0};
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return c;
+}
+__device__ __noinline__ float2 normal_pair_cold(unsigned a, unsigned b) { return normal_pair(a, b); }
+// Warp-collective: lanes 0 / 1 / 2 evaluate the three blocks (streams ResetU / ResetN0 / ResetN1) side by side and the ten
+// values are broadcast -- one Philox block + one Box-Muller pair deep instead of three of each.  Same functions, same
+// bits as philox_reset_noise.
+__device__ __forceinline__ void philox_reset_noise_cold(unsigned long long seed, unsigned long long step, long long env, int lane,
+                                                        float* u) {
+    const unsigned sid = kStreamResetU + static_cast<unsigned>(min(lane, 2));
+    const Philox4 blk = philox_env_cold(seed, step, env, sid);
+    const float2 pa = normal_pair_cold(blk.x, blk.y), pb = normal_pair_cold(blk.z, blk.w);
+    const unsigned full = 0xffffffffu;
+    u[0] = __shfl_sync(full, u01(blk.x), 0); u[2] = __shfl_sync(full, u01(blk.y), 0);
+    u[3] = __shfl_sync(full, u01(blk.z), 0); u[4] = __shfl_sync(full, u01(blk.w), 0);
+    u[1] = __shfl_sync(full, pa.x, 1); u[5] = __shfl_sync(full, pa.y, 1);
+    u[6] = __shfl_sync(full, pb.x, 1); u[7] = __shfl_sync(full, pb.y, 1);
+    u[8] = __shfl_sync(full, pa.x, 2); u[9] = __shfl_sync(full, pa.y, 2);
 }
 __device__ __forceinline__ void philox_reset_noise(unsigned long long seed, unsigned long long step, long long env, float* u) {
     Philox4 a = philox_env(seed, step, env, kStreamResetU);
@@ -205,6 +243,91 @@ __device__ __forceinline__ void tile_store(float* dst, const float* src, int cnt
     }
 }
 
+// reset_idx :505-590 for env `ne` of the fused kernel, executed by ONE WARP (lane-cooperative; the single-thread
+// reset_env above serves the explicit-id-list entry point).  Every lane holds the same 10 unit draws `u`, so every lane
+// derives the same scalars with the expressions of reset_env; the rows are spread over the lanes -- lane j the (pos, vel)
+// pair of DOF j, j + 32, ..., lanes 0..12 the root row, lanes 0..14 one per-env scalar each -- and ALL global reads are
+// requested before any of them is consumed: one memory round trip (~1 us) where the single thread walked 39 + 13 + 5
+// rows one after the other (~3 us, and the tiles that held a reset set the length of the whole launch).
+// Returns the new root value of column `lane` (lanes 0..12) for the patch of the staged tile.
+struct ResetScalars { float yaw_cmd, imu_off; };
+struct ResetRows { float pose0, pose1, rv; };
+// the rows a reset reads, requested as early as possible (they depend on the env id only): the noise draws are computed
+// under their round trip
+__device__ __forceinline__ ResetRows reset_env_fetch(const KParams& p, long long ne, int lane) {
+    const int d = p.num_dof;
+    ResetRows r;
+    r.pose0 = (lane < d) ? p.thormang_pose[ne * d + lane] : 0.0f;
+    r.pose1 = (lane + 32 < d) ? p.thormang_pose[ne * d + lane + 32] : 0.0f;
+    r.rv = (lane < kRoot) ? p.root_reset[ne * kRoot + lane] : 0.0f;                 // :518
+    return r;
+}
+__device__ __forceinline__ float reset_env_warp(const KParams& p, long long ne, const float* u, int lane, const ResetRows& rows,
+                                                ResetScalars* out) {
+    const int d = p.num_dof;
+    const float pose0 = rows.pose0, pose1 = rows.pose1;
+    float rv = rows.rv;
+    const float initial_target = (u[3] * 2.0f - 1.0f) * kPi;                        // :486
+    const float initial_rot = initial_target + (-1.57f + u[4] * static_cast<float>(1.57 - (-1.57)));   // :487
+    const float half = initial_rot / 2.0f;
+    float sy, cy;
+    sincosf(half, &sy, &cy);
+    const float sr = 0.0f, cr = 1.0f, sp = 0.0f, cp = 1.0f;                         // sin/cos of roll/2 = pitch/2 = 0
+    const float qx = sr * cp * cy - cr * sp * sy;                                   // :497-500
+    const float qy = cr * sp * cy + sr * cp * sy;
+    const float qz = cr * cp * sy - sr * sp * cy;
+    const float qw = cr * cp * cy + sr * sp * sy;
+    float cfgv[5];
+    cfgv[0] = normal_of(p.seat_x, u[5]);                                            // :554
+    cfgv[1] = normal_of(p.seat_y, u[6]);                                            // :555
+    cfgv[2] = normal_of(p.seat_z, u[7]);                                            // :556
+    cfgv[3] = normal_of(p.seat_xr, u[8]);                                           // :557
+    cfgv[4] = normal_of(p.steer_off, u[9]);                                         // :559
+    // root row: [0:3] <- root_reset (z <- 0.03 :537), [3:7] <- spawn quaternion :519, [7:13] <- 0 :520
+    rv = (lane == 2) ? 0.03f : rv;
+    rv = (lane == 3) ? qx : rv; rv = (lane == 4) ? qy : rv; rv = (lane == 5) ? qz : rv; rv = (lane == 6) ? qw : rv;
+    rv = (lane >= 7) ? 0.0f : rv;
+    if (lane < kRoot) p.root[ne * kRoot + lane] = rv;                               // :547
+    float2* ds = reinterpret_cast<float2*>(p.state_dof) + ne * d;
+    if (lane < d) ds[lane] = make_float2(pose0, 0.0f);                              // :549-550
+    if (lane + 32 < d) ds[lane + 32] = make_float2(pose1, 0.0f);
+    for (int j = lane + 64; j < d; j += 32) ds[j] = make_float2(p.thormang_pose[ne * d + j], 0.0f);
+    // per-env scalars, one lane each
+    float sv = 0.0f;
+    float* sp_ = nullptr;
+    switch (lane) {
+        case 0: sp_ = p.curent_speed + ne; sv = uniform_of(p.speed, u[0]); break;           // :479
+        case 1: sp_ = p.curent_speed_offset + ne; sv = uniform_of(p.speed_off, u[2]); break;   // :482 (:481 is overwritten at :575, dead)
+        case 2: case 3: case 4: case 5: case 6: sp_ = p.config_vector + ne * 5 + (lane - 2); break;
+        case 7: sp_ = p.imu_offsets + ne; sv = cfgv[3]; break;                              // :574
+        case 8: sp_ = p.steer_offsets + ne; sv = cfgv[4]; break;                            // :575
+        case 9: sp_ = p.curent_command + ne; break;                                         // :587
+        case 10: case 11: case 12: case 13: case 14: sp_ = p.action_history + ne * kHist + (lane - 10); break;   // :590
+        default: break;
+    }
+    if (lane >= 2 && lane <= 6) {
+        sv = cfgv[0];
+        sv = (lane == 3) ? cfgv[1] : sv; sv = (lane == 4) ? cfgv[2] : sv; sv = (lane == 5) ? cfgv[3] : sv; sv = (lane == 6) ? cfgv[4] : sv;
+    }
+    if (sp_) *sp_ = sv;
+    out->yaw_cmd = initial_target;                                                  // :589
+    out->imu_off = cfgv[3];
+    return rv;
+}
+
+// the 10 unit draws of one reset (same value in every lane of the calling warp)
+__device__ __forceinline__ void reset_units(const KParams& p, long long ne, long long row, bool philox, unsigned long long step_now,
+                                            int lane, float* u) {
+    if (philox) {
+        philox_reset_noise_cold(p.seed, step_now, p.env_off + ne, lane, u);
+    } else {
+#pragma unroll
+        for (int c = 0; c < kResetNoise; ++c)
+            u[c] = (p.noise_mode != TK_NOISE_NONE && row < p.reset_rows) ? p.reset_unit[row * kResetNoise + c]
+                                                                         : ((c == 0 || (c >= 2 && c <= 4)) ? 0.5f : 0.0f);
+    }
+}
+
 // MODE 0: fused post_physics_step; 1: compute_obs_rwd only; 2: observations only (obs_out = clean [N,6])
 template <int MODE>
 __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constant__ KParams p, float* __restrict__ obs_out) {
@@ -216,20 +339,32 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
     const bool valid = tid < nt;
     const bool vec = p.vec_ok != 0;
     const bool philox = p.noise_mode == TK_NOISE_PHILOX;
-    // programmatic dependent launch (no-ops without the launch attribute)
+    long long* ts = p.dbg_ts ? p.dbg_ts + static_cast<size_t>(blockIdx.x) * 8 : nullptr;
+#define TK_GSTAMP(i) do { if (ts && tid == 0) { long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g) :: "memory"); ts[i] = g; } } while (0)
+    // programmatic dependent launch (no-ops without the launch attribute): everything up to griddepcontrol.wait touches
+    // no global memory and may overlap the drain of the previous kernel in the stream
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const bool use_noise = (MODE != 2) && !philox && p.sensor_unit != nullptr;
+    const bool bulk = vec && nt == kTile;
+    if (bulk && tid == 0) {
+        mbar_init(&s.bar, 1);
+        fence_proxy_async_smem();
+    }
+    // The sensor noise of this step is a pure function of (seed, step, global env id): with a NULL epoch (eager launches)
+    // it is computed right here, under the previous kernel's drain; with a device-side epoch (CUDA-graph replays) the one
+    // global word it needs is requested first thing after the wait and the block is computed under the tile's round trip.
+    StepNoise sn;
+#pragma unroll
+    for (int c = 0; c < kSensorNoise; ++c) sn.sensor[c] = 0.0f;
+    const bool early_noise = (MODE != 2) && philox && p.step_dev == nullptr;
+    if (early_noise) sn = philox_sensor_noise(p.seed, p.step, p.env_off + n);
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    TK_GSTAMP(0);
     const unsigned long long step_now = philox ? effective_step(p.step, p.step_dev) : 0ull;
 
     // full, 16-byte aligned tile: the bulk-copy (TMA) engine moves root / history / noise rows in and both obs rows out
-    const bool use_noise = (MODE != 2) && !philox && p.sensor_unit != nullptr;
-    const bool bulk = vec && nt == kTile;
     if (bulk) {
-        if (tid == 0) {
-            mbar_init(&s.bar, 1);
-            fence_proxy_async_smem();
-            mbar_expect_tx(&s.bar, (kRoot + (MODE != 2 ? kHist : 0) + (use_noise ? kSensorNoise : 0)) * kTile * 4);
-        }
+        if (tid == 0) mbar_expect_tx(&s.bar, (kRoot + (MODE != 2 ? kHist : 0) + (use_noise ? kSensorNoise : 0)) * kTile * 4);
         __syncwarp();
         if (tid == 0) bulk_load(s.root, p.root + static_cast<size_t>(env0) * kRoot, kTile * kRoot * 4, &s.bar);
         else if (tid == 1 && MODE != 2) bulk_load(s.hist, p.action_history + static_cast<size_t>(env0) * kHist, kTile * kHist * 4, &s.bar);
@@ -252,19 +387,80 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         if (MODE != 2) imu_off = p.imu_offsets[n];
         if (MODE == 0 && p.ep_return) ret_old = p.ep_return[n];
         if (MODE != 2) prog = p.progress[n];
-        if (MODE == 0) {
-            prog += 1;                                                              // :375
-            do_reset = p.reset[n] != 0;                                             // :377
-            if (do_reset) prog = 0;                                                 // :583
-            do_speed = prog == p.speed_freq;                                        // :384 (after the reset)
+        if (MODE == 0) do_reset = p.reset[n] != 0;                                  // :377
+    }
+    if (MODE != 2 && philox && !early_noise && valid) sn = philox_sensor_noise(p.seed, step_now, p.env_off + n);
+    if (MODE == 0 && valid) {
+        prog += 1;                                                                  // :375
+        if (do_reset) prog = 0;                                                     // :583
+        do_speed = prog == p.speed_freq;                                            // :384 (after the reset)
+    }
+    unsigned reset_bits = 0;
+    if (MODE == 0) {
+        reset_bits = __ballot_sync(0xffffffffu, do_reset);
+        const unsigned b1 = __ballot_sync(0xffffffffu, do_speed);
+        if (lane == 0) { s.ballots[0][warp] = reset_bits; s.ballots[1][warp] = b1; }
+    }
+    TK_GSTAMP(1);
+    __syncthreads();                       // ballots, mbarrier init, cooperative copies visible to the whole CTA
+
+    // ---- reset prologue (rare): this warp's flagged envs, lane-cooperative, BEFORE the tile is waited for -- the new
+    // state does not depend on the staged rows; only the patch of the staged copy comes after the wait
+    constexpr int kPre = 2;
+    float pre_root[kPre];
+    bool hist_zero = false;
+    if (MODE == 0 && reset_bits) {
+        int rank = 0;
+        if (p.noise_mode == TK_NOISE_COMPACT) {
+            rank = p.tile_base_reset[blockIdx.x];
+            for (int w = 0; w < warp; ++w) rank += __popc(s.ballots[0][w]);
+        }
+        unsigned bits = reset_bits;
+#pragma unroll
+        for (int q = 0; q < kPre; ++q) {
+            pre_root[q] = 0.0f;
+            if (bits) {
+                const int e = __ffs(bits) - 1;
+                bits &= bits - 1;
+                const long long ne = env0 + warp * 32 + e;
+                float u[kResetNoise];
+                const ResetRows rows = reset_env_fetch(p, ne, lane);
+                reset_units(p, ne, (p.noise_mode == TK_NOISE_COMPACT) ? rank + q : ne, philox, step_now, lane, u);
+                ResetScalars rs;
+                pre_root[q] = reset_env_warp(p, ne, u, lane, rows, &rs);
+                if (lane == e) { yaw_cmd = rs.yaw_cmd; imu_off = rs.imu_off; cur_cmd = 0.0f; hist_zero = true; }   // :589,574,587,590
+            }
         }
     }
-    if (MODE == 0) {
-        unsigned b0 = __ballot_sync(0xffffffffu, do_reset), b1 = __ballot_sync(0xffffffffu, do_speed);
-        if (lane == 0) { s.ballots[0][warp] = b0; s.ballots[1][warp] = b1; }
-    }
-    __syncthreads();
+    TK_GSTAMP(2);
     if (bulk) mbar_wait(&s.bar, 0);        // bulk loads landed
+    if (MODE == 0 && reset_bits) {         // patch the staged rows of the envs that were reset
+        int rank = 0;
+        if (p.noise_mode == TK_NOISE_COMPACT) {
+            rank = p.tile_base_reset[blockIdx.x];
+            for (int w = 0; w < warp; ++w) rank += __popc(s.ballots[0][w]);
+        }
+        unsigned bits = reset_bits;
+        for (int q = 0; bits; ++q) {
+            const int e = __ffs(bits) - 1;
+            bits &= bits - 1;
+            float rv;
+            if (q < kPre) {
+                rv = (q == 0) ? pre_root[0] : pre_root[kPre - 1];
+            } else {                       // more than kPre resets in one warp: the rest after the wait
+                const long long ne = env0 + warp * 32 + e;
+                float u[kResetNoise];
+                const ResetRows rows = reset_env_fetch(p, ne, lane);
+                reset_units(p, ne, (p.noise_mode == TK_NOISE_COMPACT) ? rank + q : ne, philox, step_now, lane, u);
+                ResetScalars rs;
+                rv = reset_env_warp(p, ne, u, lane, rows, &rs);
+                if (lane == e) { yaw_cmd = rs.yaw_cmd; imu_off = rs.imu_off; cur_cmd = 0.0f; hist_zero = true; }
+            }
+            if (lane < kRoot) s.root[(warp * 32 + e) * kRoot + lane] = rv;
+        }
+        __syncwarp();
+    }
+    TK_GSTAMP(3);
 
     float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_tilt = 0.f, st_yaw = 0.f;
     bool out_reset = false, out_timeout = false;
@@ -272,40 +468,13 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         float r[kRoot], hist[kHist];
 #pragma unroll
         for (int c = 0; c < kRoot; ++c) r[c] = s.root[tid * kRoot + c];
-        StepNoise sn;
         if (MODE != 2) {
 #pragma unroll
-            for (int c = 0; c < kHist; ++c) hist[c] = s.hist[tid * kHist + c];
-            if (philox) {
-                sn = philox_sensor_noise(p.seed, step_now, p.env_off + n);
-            } else {
+            for (int c = 0; c < kHist; ++c) hist[c] = hist_zero ? 0.0f : s.hist[tid * kHist + c];
+            if (!philox) {
 #pragma unroll
                 for (int c = 0; c < kSensorNoise; ++c) sn.sensor[c] = p.sensor_unit ? s.noise[tid * kSensorNoise + c] : 0.0f;
             }
-        }
-        if (MODE == 0 && do_reset) {
-            float u[kResetNoise];
-            if (philox) {
-                philox_reset_noise(p.seed, step_now, p.env_off + n, u);
-            } else {
-                long long row = n;
-                if (p.noise_mode == TK_NOISE_COMPACT) {
-                    int rank = p.tile_base_reset[blockIdx.x];
-                    for (int w = 0; w < warp; ++w) rank += __popc(s.ballots[0][w]);
-                    rank += __popc(s.ballots[0][warp] & ((1u << lane) - 1u));
-                    row = rank;
-                }
-#pragma unroll
-                for (int c = 0; c < kResetNoise; ++c)
-                    u[c] = (p.noise_mode != TK_NOISE_NONE && row < p.reset_rows) ? p.reset_unit[row * kResetNoise + c]
-                                                                                 : ((c == 0 || (c >= 2 && c <= 4)) ? 0.5f : 0.0f);
-            }
-            reset_env(p, n, u, r, &yaw_cmd);
-            imu_off = normal_of(p.seat_xr, u[8]);                                   // :557,574 (what reset_env just stored)
-            cur_cmd = 0.0f;                                                         // :587
-            p.curent_command[n] = 0.0f;
-#pragma unroll
-            for (int c = 0; c < kHist; ++c) { hist[c] = 0.0f; p.action_history[n * kHist + c] = 0.0f; }   // :590
         }
 
         float o[kObs];
@@ -375,6 +544,7 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         }
     }
 
+    TK_GSTAMP(4);
     if (MODE == 0) {
         const unsigned m_reset = __ballot_sync(0xffffffffu, out_reset);
         const unsigned m_to = __ballot_sync(0xffffffffu, out_timeout);
@@ -395,6 +565,7 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
     }
     fence_proxy_async_smem();              // obs rows written via the generic proxy, read by the bulk-copy engine
     __syncthreads();
+    TK_GSTAMP(5);
     if (MODE == 0 && tid < TK_STATS) {
         double acc = 0.0;
 #pragma unroll
@@ -402,16 +573,19 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         // running sum since the last tk_*_stats (slot scheme: tk_common.cuh)
         atomicAdd(p.partials + static_cast<size_t>(blockIdx.x & (kStatSlots - 1)) * TK_STATS + tid, acc);
     }
+    TK_GSTAMP(7);
     float* out_clean = (MODE == 2) ? obs_out + static_cast<size_t>(env0) * kObs : p.buffer_obs + static_cast<size_t>(env0) * kObs;
     const bool bulk_out = bulk && (MODE != 2 || (reinterpret_cast<uintptr_t>(obs_out) & 15) == 0);
     if (bulk_out) {
         if (tid == 0) bulk_store(out_clean, s.clean, kTile * kObs * 4);
-        if (tid == 1 && MODE != 2) bulk_store(p.obs_buf + static_cast<size_t>(env0) * kObs, s.noisy, kTile * kObs * 4);
-        if (tid < 2) { bulk_commit(); bulk_wait_read<0>(); }   // shared memory must stay alive until the engine has read it
+        if (tid == 32 && MODE != 2) bulk_store(p.obs_buf + static_cast<size_t>(env0) * kObs, s.noisy, kTile * kObs * 4);
+        if (tid == 0 || (tid == 32 && MODE != 2)) { bulk_commit(); bulk_wait_read<0>(); }   // shared memory must stay alive until the engine has read it
     } else {
         tile_store(out_clean, s.clean, nt * kObs, false, tid);
         if (MODE != 2) tile_store(p.obs_buf + static_cast<size_t>(env0) * kObs, s.noisy, nt * kObs, false, tid);
     }
+    TK_GSTAMP(6);
+#undef TK_GSTAMP
 }
 
 // per-tile counts of the two COMPACT predicates: reset != 0 ; reset == 0 && progress + 1 == speed_freq
@@ -584,6 +758,8 @@ struct TkGogoro {
     int* bases;    // [2, tiles]
     int last_grid;
     unsigned long long* step_dev;
+    bool epoch_used;      // tk_gogoro_advance_epoch was called: the kernels must read the device-side epoch (NULL otherwise)
+    long long* dbg_ts;
 };
 
 static void pair_uniform(const double* in, float* out) { out[0] = static_cast<float>(in[0]); out[1] = static_cast<float>(in[1] - in[0]); }
@@ -601,7 +777,7 @@ static void fill_kparams(const TkGogoro* h, KParams& k) {
     k.vel_cmd = B.dof_speed_command; k.ep_return = B.episode_return;
     k.partials = h->partials; k.tile_base_reset = h->bases; k.tile_base_speed = h->bases + h->tiles;
     k.reset_unit = nullptr; k.sensor_unit = nullptr; k.speed_unit = nullptr; k.yaw_unit = nullptr; k.reset_rows = 0;
-    k.seed = 0; k.step = 0; k.env_off = 0; k.noise_mode = TK_NOISE_NONE; k.step_dev = h->step_dev;
+    k.seed = 0; k.step = 0; k.env_off = 0; k.noise_mode = TK_NOISE_NONE; k.step_dev = h->epoch_used ? h->step_dev : nullptr; k.dbg_ts = h->dbg_ts;
     k.n = P.num_envs; k.num_dof = P.num_dof; k.steering_joint = P.steering_joint; k.rear_wheel_joint = P.rear_wheel_joint;
     k.max_episode_length = P.max_episode_length; k.speed_freq = P.speed_freq_update; k.yaw_freq = P.yaw_freq_update;
     k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.action_history, 16) && aligned_to(B.obs_buf, 16) &&
@@ -636,6 +812,8 @@ int tk_gogoro_create(const TkGogoroParams* params, TkGogoro** out) {
     h->bound = false;
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->last_grid = 0;
+    h->dbg_ts = nullptr;
+    h->epoch_used = false;
     h->partials = nullptr; h->counts = nullptr; h->bases = nullptr; h->step_dev = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMalloc(&h->counts, sizeof(int) * 2 * h->tiles);
@@ -791,9 +969,17 @@ int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream
     return TK_OK;
 }
 
+// developer probe, not part of the public header: per-tile globaltimer stamps [tiles, 8] (tools/tile_timeline.py --task gogoro)
+int tk_debug_gogoro_timeline(TkGogoro* h, long long* device_buffer) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    h->dbg_ts = device_buffer;
+    return TK_OK;
+}
+
 int tk_gogoro_advance_epoch(TkGogoro* h, void* stream) {
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
     TK_CUDA(cudaSetDevice(h->params.device));
+    h->epoch_used = true;
     advance_epoch_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(h->step_dev);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
@@ -814,7 +1000,8 @@ int tk_gogoro_philox_noise(TkGogoro* h, uint64_t seed, uint64_t step, int64_t en
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
     TK_CUDA(cudaSetDevice(h->params.device));
     gogoro_philox_kernel<<<(h->params.num_envs + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        h->params.num_envs, seed, step, env_id_offset, h->step_dev, steer_unit, sensor_unit, reset_unit, speed_unit, yaw_unit);
+        h->params.num_envs, seed, step, env_id_offset, h->epoch_used ? h->step_dev : nullptr, steer_unit, sensor_unit, reset_unit,
+        speed_unit, yaw_unit);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }

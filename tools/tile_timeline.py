@@ -16,28 +16,48 @@ from thormang_isaacgym_b200 import _native as nat  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--envs", type=int, default=16384)
+ap.add_argument("--task", default="humanoid", choices=["humanoid", "gogoro"])
 a = ap.parse_args()
 n = a.envs
-envs = [G._make_humanoid(n, 10 + s, "cuda:0")[0] for s in range(8)]
+envs = [G._MAKERS[a.task](n, 10 + s, "cuda:0")[0] for s in range(8)]
 lib = nat.lib()
-lib.tk_debug_humanoid_timeline.argtypes = [C.c_void_p, C.c_void_p]
-tiles = (n + 31) // 32
-for e in envs:
-    e.post_physics_step()
+probe = lib.tk_debug_humanoid_timeline if a.task == "humanoid" else lib.tk_debug_gogoro_timeline
+probe.argtypes = [C.c_void_p, C.c_void_p]
+tile_envs = 32 if a.task == "humanoid" else 128
+tiles = (n + tile_envs - 1) // tile_envs
+for _ in range(6):          # past the transient: the synthetic state's fallen envs are reset by the first steps
+    for e in envs:
+        e.post_physics_step()
 torch.cuda.synchronize()
 buf = torch.zeros((tiles, 8), dtype=torch.int64, device="cuda:0")
 e = envs[3]
-lib.tk_debug_humanoid_timeline(e._handle, C.c_void_p(buf.data_ptr()))
+probe(e._handle, C.c_void_p(buf.data_ptr()))
 # flush L2 with the other sets, then the probed launch
 for o in envs[4:] + envs[:3]:
     o.post_physics_step()
 torch.cuda.synchronize()
 e_reset_before = e.reset_buf.clone().cpu()
+# the probed launch sits in the middle of a back-to-back stream of launches (programmatic dependent launch in play);
+# the launch behind it is probed as well: the distance between "every tile of A has finished" and "the first tile of B has
+# passed griddepcontrol.wait" is the launch-to-launch gap that no tile stamp of a single launch can see
+buf_b = torch.zeros((tiles, 8), dtype=torch.int64, device="cuda:0")
+eb = envs[4]
+probe(eb._handle, C.c_void_p(buf_b.data_ptr()))
+envs[1].post_physics_step()
+envs[2].post_physics_step()
 e.post_physics_step()
+eb.post_physics_step()
+envs[5].post_physics_step()
 torch.cuda.synchronize()
 t = buf.cpu().double()
+tb = buf_b.cpu().double()
+print(f"launch A: first wait release -> last tile done {(t[:, 6].max() - t[:, 0].min()) / 1e3:.2f} us; "
+      f"gap to launch B's first wait release {(tb[:, 0].min() - t[:, 6].max()) / 1e3:.2f} us; "
+      f"B's first release -> last done {(tb[:, 6].max() - tb[:, 0].min()) / 1e3:.2f} us; "
+      f"A start -> B start {(tb[:, 0].min() - t[:, 0].min()) / 1e3:.2f} us")
 t0 = t[:, 0].min()
 names = ["start", "scalars issued", "scalars landed", "bulk landed", "inputs in regs", "math+STS done", "store read done"]
+print(f"envs flagged for reset in the probed step: {int((e_reset_before != 0).sum())} of {n}")
 print(f"tiles {tiles}; kernel span {(t[:, 6].max() - t0) / 1e3:.2f} us")
 for i, nm in enumerate(names):
     col = t[:, i] - t0
@@ -46,6 +66,20 @@ d = t[:, 1:7] - t[:, 0:6]
 for i, nm in enumerate(["issue", "scalar wait", "bulk wait", "reset+reg read", "math+STS", "store"]):
     print(f"  phase {nm:14s} median {d[:, i].median()/1e3:6.2f}  mean {d[:, i].mean()/1e3:6.2f}  p95 {d[:, i].quantile(0.95)/1e3:6.2f} us")
 
+# the stragglers: the ten tiles that finish last, with their stamps (us after the first start) and reset counts
+rb = e_reset_before.view(-1, tile_envs).sum(1) if e_reset_before.numel() % tile_envs == 0 else None
+order = torch.argsort(t[:, 6], descending=True)[:10]
+print("last tiles: blockIdx  resets | start issue scal bulk regs math done")
+for i in order.tolist():
+    row = " ".join(f"{(t[i, k] - t0) / 1e3:6.2f}" for k in range(8))
+    print(f"  {i:6d}  {int(rb[i]) if rb is not None else -1:3d} | {row}")
+first = torch.argsort(t[:, 6])[:5]
+for i in first.tolist():
+    row = " ".join(f"{(t[i, k] - t0) / 1e3:6.2f}" for k in range(7))
+    print(f"  first {i:6d}  {int(rb[i]) if rb is not None else -1:3d} | {row}")
+
+if a.task != "humanoid":
+    sys.exit(0)
 # bandwidth over time: a tile's 13.9 KB of loads are counted when its bulk load has landed, its 14.1 KB obs tile when the
 # bulk store has been read out of shared memory (the per-env scalars ride along): where is HBM idle -- head, middle, tail?
 w = 1024.0                                   # ns per bucket
@@ -58,14 +92,3 @@ print("bucket(us)  loaded MB  stored MB  GB/s")
 for b in range(nb):
     print(f"{b * w / 1e3:6.2f}    {ld[b] / 1e6:8.2f}  {stv[b] / 1e6:8.2f}  {(ld[b] + stv[b]) / w:8.0f}")
 
-# the stragglers: the ten tiles that finish last, with their stamps (us after the first start) and reset counts
-rb = e_reset_before.view(-1, 32).sum(1) if e_reset_before.numel() % 32 == 0 else None
-order = torch.argsort(t[:, 6], descending=True)[:10]
-print("last tiles: blockIdx  resets | start issue scal bulk regs math done")
-for i in order.tolist():
-    row = " ".join(f"{(t[i, k] - t0) / 1e3:6.2f}" for k in range(7))
-    print(f"  {i:6d}  {int(rb[i]) if rb is not None else -1:3d} | {row}")
-first = torch.argsort(t[:, 6])[:5]
-for i in first.tolist():
-    row = " ".join(f"{(t[i, k] - t0) / 1e3:6.2f}" for k in range(7))
-    print(f"  first {i:6d}  {int(rb[i]) if rb is not None else -1:3d} | {row}")
