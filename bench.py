@@ -218,6 +218,42 @@ def time_cpu(task, n, seed, steps, warmup, budget_s=None):
     return n * len(times) / total, 1e3 * total / len(times), len(times), torch.get_num_threads()
 
 
+def cpu_config1(n=4096, warmup=5, reps=50):
+    """BASELINE config 1 as SURVEY 8(d) specifies it: Humanoid compute_observations + compute_reward (humanoid.py:219-251,
+    323-417; no reset_idx) on `n` synthetic env states, CPU torch, TorchScript-compiled like the reference; all host
+    threads AND one thread; `warmup` warm-ups, median of `reps`.  The functions are the pinned port in oracle/ (bit-for-bit
+    equal to the reference's own JIT functions, tests/test_oracle_vs_reference.py) -- /root/reference does not exist on
+    the GPU box."""
+    import torch
+    from oracle import humanoid_oracle as ho
+    from thormang_isaacgym_b200 import config as tcfg
+    from thormang_isaacgym_b200 import synthetic as syn
+    asset = syn.humanoid_asset()
+    st = syn.humanoid_state(n, seed=1234, asset=asset)
+    orc = ho.HumanoidOracle(ho.HumanoidConsts.from_cfg(tcfg.humanoid_cfg(n, seed=1234)), st["root_states"], st["dof_state"],
+                            st["dof_force"], st["sensors"], asset["dof_limits_lower"], asset["dof_limits_upper"],
+                            asset["motor_efforts"], jit=True)
+    orc.actions, orc.progress_buf, orc.reset_buf, orc.potentials = st["actions"], st["progress_buf"], st["reset_buf"], st["potentials"]
+    out = {"envs": n, "what": "compute_observations + compute_reward (no reset), CPU torch " + torch.__version__,
+           "kind": "port (oracle/, pinned bit-for-bit to the reference's JIT functions)", "warmup": warmup, "reps": reps,
+           "torch": torch.__version__, "parallel_info": torch.__config__.parallel_info().strip().splitlines()[:8]}
+    before = torch.get_num_threads()
+    for label, threads in (("all_threads", os.cpu_count() or 1), ("single_thread", 1)):
+        torch.set_num_threads(threads)
+        for _ in range(warmup):
+            orc.compute_observations(); orc.compute_reward()
+        times = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            orc.compute_observations(); orc.compute_reward()
+            times.append(time.perf_counter() - t0)
+        med = statistics.median(times)
+        out[label] = {"threads": torch.get_num_threads(), "median_ms": 1e3 * med, "env_steps_per_s": n / med,
+                      "min_ms": 1e3 * min(times)}
+    torch.set_num_threads(before)
+    return out
+
+
 def run_reference_arm(args, rank, world):
     """--impl reference: rank 0 alone times the CPU path on the same workload, bounded sample per step."""
     if rank != 0:

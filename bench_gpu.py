@@ -185,22 +185,27 @@ def _kernel_bench(torch, task, n, device, steps, warmup, seed=1234, env_off=0, b
         for e in envs:
             e.post_physics_step()
         torch.cuda.synchronize()
+        # one captured graph = one rollout horizon (>= 32 steps, whole passes over the state sets), like a training loop
+        # that captures its horizon: ONE noise-epoch bump per task object per replay, all of them ahead of the steps so that
+        # the step kernels follow one another directly (programmatic-launch edges between consecutive kernel nodes); every
+        # captured launch carries its own host step number, the epoch makes every replay draw fresh noise
+        per_graph = max(1, -(-HORIZON // sets))
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
-            # every replay draws fresh in-kernel noise: one epoch bump per task object, all of them ahead of the steps so
-            # that the step kernels follow one another directly (programmatic-launch edges between consecutive kernel nodes)
             for e in envs:
                 e.advance_noise_epoch()
-            for e in envs:
-                e.post_physics_step()
-        passes = max(1, steps // sets)
+            for _ in range(per_graph):
+                for e in envs:
+                    e.post_physics_step()
+        per_replay = per_graph * sets
+        replays = max(1, steps // per_replay)
 
         def replay(i):
             g.replay()
-            return sets * per_step
-        ms, launches, window = _time_steps(torch, replay, passes, max(1, warmup // sets), barrier)
+            return per_replay * per_step + sets
+        ms, launches, window = _time_steps(torch, replay, replays, max(1, warmup // per_replay), barrier)
         del envs
-        return {"ms_total": ms, "launches": launches, "sets": sets, "window": window, "steps": passes * sets}
+        return {"ms_total": ms, "launches": launches, "sets": sets, "window": window, "steps": replays * per_replay}
 
     since = [0] * sets          # steps of each set since its statistics were last finalized
 
@@ -286,6 +291,68 @@ def _pcie_probe(torch, device, mb=64):
             host2.copy_(dev2, non_blocking=True)
     torch.cuda.synchronize()
     out["duplex_GBps_per_direction"] = 5 * host.numel() / (time.perf_counter() - t0) / 1e9
+    return out
+
+
+def _launch_floor(torch, device):
+    """Launch + drain floor of this box next to the small-grid numbers: an EMPTY kernel with the launch shape of the fused
+    kernels (programmatic dependent launch, same CTA count / size / shared memory), back to back on one stream -- through
+    the same ctypes call path (host-bound: ~3 us per call) and replayed from a CUDA graph (the GPU-side floor, which
+    grows with the CTA count: a B200 dispatches ~0.85 CTA per ns)."""
+    import ctypes as C
+    from thormang_isaacgym_b200 import _native as nat
+    fn = nat.lib().tk_debug_launch_floor
+    fn.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    fn.restype = C.c_int
+    out = {}
+    for label, grid, block, smem in (("humanoid_16384_quad_512x128", 512, 128, 28 * 1024), ("humanoid_65536_2048x32", 2048, 32, 14 * 1024),
+                                     ("humanoid_131072_4096x32", 4096, 32, 14 * 1024), ("gogoro_65536_512x128", 512, 128, 18 * 1024)):
+        sink = torch.zeros(grid, dtype=torch.int32, device=device)
+
+        def eager(i):
+            fn(grid, block, smem, 1, sink.data_ptr(), nat.current_stream_ptr(device))
+            return 1
+        ms, _, _ = _time_steps(torch, eager, 1000, 50)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(50):
+                fn(grid, block, smem, 1, sink.data_ptr(), nat.current_stream_ptr(device))
+        msg, _, _ = _time_steps(torch, lambda i: (g.replay(), 50)[1], 20, 2)
+        out[label] = {"us_per_launch_eager": 1e3 * ms / 1000, "us_per_launch_cuda_graph": 1e3 * msg / (20 * 50)}
+    return out
+
+
+def _l2_resident(torch, task, m, device, peak):
+    """The same kernel over TWO state sets only (both L2-resident, translations hot): what a training loop that steps ONE
+    env object sees between launches.  The headline extras rotate 20-26 sets to force every byte from HBM, which also makes
+    every launch start from cold TLB / L2 state; the difference between the two lines is that artefact."""
+    os.environ["TK_BENCH_SETS"] = "2"
+    try:
+        r = _kernel_bench(torch, task, m, device, 300, 20, seed=78)
+    finally:
+        del os.environ["TK_BENCH_SETS"]
+    us = 1e3 * r["ms_total"] / r["steps"]
+    gbs = m * B.BYTES_PER_ENV[task] / (us * 1e-6) / 1e9
+    return {"us_per_step": us, "env_steps_per_s": m / (us * 1e-6), "achieved_GBps": gbs, "frac_of_peak": gbs / peak,
+            "rotating_sets": 2, "note": "L2-resident: not an HBM number"}
+
+
+def _config1(torch, device):
+    """BASELINE config 1 (Humanoid compute_observations + compute_reward, 4096 envs): the CPU torch path as SURVEY 8(d)
+    specifies it (all threads and one thread, 5 warm-ups, median of 50) and the same two method calls on the GPU."""
+    out = {"cpu": B.cpu_config1(4096, 5, 50)}
+    env, _ = _make_humanoid(4096, 4096, device)
+
+    def pair(i):
+        env.compute_observations()
+        env.compute_reward(env.actions)
+        return 2
+    ms, _, _ = _time_steps(torch, pair, 400, 20)
+    us = 1e3 * ms / 400
+    out["gpu_split_methods"] = {"us_per_call_pair": us, "env_steps_per_s": 4096 / (us * 1e-6), "launches": 2,
+                                "note": "compute_observations() + compute_reward() through the method-level C-ABI entry "
+                                        "points (two launches, one L2-resident state set: launch-bound at this size)"}
+    out["gpu_over_cpu_all_threads"] = out["gpu_split_methods"]["env_steps_per_s"] / out["cpu"]["all_threads"]["env_steps_per_s"]
     return out
 
 
@@ -545,6 +612,7 @@ def run_gpu_arm(args, rank, world):
         try:
             for label, t, m, gr in (("config2_humanoid_16384", "humanoid", 16384, False),
                                     ("config2_humanoid_16384_cuda_graph", "humanoid", 16384, True),
+                                    ("humanoid_32768", "humanoid", 32768, False),
                                     ("humanoid_65536", "humanoid", 65536, False),
                                     ("humanoid_65536_cuda_graph", "humanoid", 65536, True),
                                     ("humanoid_262144", "humanoid", 262144, False),
@@ -567,6 +635,10 @@ def run_gpu_arm(args, rank, world):
                 gbs = m * b / (r["ms_total"] / k * 1e-3) / 1e9
                 extras[label] = {"env_steps_per_s": m * k / (r["ms_total"] * 1e-3), "us_per_step": 1e3 * r["ms_total"] / k,
                                  "achieved_GBps": gbs, "frac_of_peak": gbs / peak, "rotating_sets": r["sets"]}
+            extras["launch_floor"] = _launch_floor(torch, device)
+            extras["config3_gogoro_65536_l2_resident"] = _l2_resident(torch, "gogoro", 65536, device, peak)
+            extras["config2_humanoid_16384_l2_resident"] = _l2_resident(torch, "humanoid", 16384, device, peak)
+            extras["config1_humanoid_4096"] = _config1(torch, device)
             extras["config5_step_loop_131072x32"] = _step_loop_bench(torch, 131072, device, 32, 8)
             extras["config5_step_loop_4096x32_cuda_graph"] = _step_loop_bench(torch, 4096, device, 32, 20, graph=True)
             extras["config5_step_loop_4096x32"] = _step_loop_bench(torch, 4096, device, 32, 20)
