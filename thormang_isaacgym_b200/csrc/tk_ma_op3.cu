@@ -36,7 +36,7 @@ constexpr int kActors = 3;
 constexpr int kDof = TK_OP3_DOF;
 constexpr int kObs = TK_OP3_OBS;
 constexpr int kTile = 32;
-constexpr int kThreads = kTile * kA;
+constexpr int kRows = kTile * kA;            // (env, agent) rows of a tile
 constexpr int kMaxFeet = TK_OP3_MAX_FEET;
 
 struct KParams {
@@ -91,53 +91,94 @@ struct Smem {
     alignas(16) float dof[kTile * kA * kDof * 2];
     alignas(16) float tq[kTile * kA * kDof];
     alignas(16) float act[kTile * kA * kDof];
-    float x_rew[kTile];
-    float x_dist[kTile];
-    int x_flag[kTile];
+    alignas(16) float ptq[kTile * kA * kDof];     // prev_torques / last_actions tiles: bulk-loaded like the others.  Per-lane
+    alignas(16) float la[kTile * kA * kDof];      // row reads straight from global (88 B rows, 176 B lane stride) lived on L1
+                                                  // sector reuse: the step time followed the L1 size left by the shared-memory
+                                                  // carve-out (336 us with 60 KB of L1, 400 us with 28 KB, 524288 envs)
     alignas(8) uint64_t bar;
 };
 
+// obs row piece c (columns 4c .. 4c+3) is complete after iteration `obs_piece_ready(c)` of the per-DOF loop (-1: before it):
+// columns 0..8 head, 9..30 dof_pos (j = col - 9), 31..52 dof_vel (j = col - 31), 53..74 actions (j = col - 53), 75..87 table
+__host__ __device__ constexpr int obs_col_ready(int col) {
+    return col < 9 ? -1 : col < 31 ? col - 9 : col < 53 ? col - 31 : col < 75 ? col - 53 : -1;
+}
+__host__ __device__ constexpr int obs_piece_ready(int c) {
+    int r = -1;
+    for (int k = 0; k < 4; ++k) r = obs_col_ready(4 * c + k) > r ? obs_col_ready(4 * c + k) : r;
+    return r;
+}
+
 // MODE 0: fused post_physics_step; 1: compute_observations; 2: compute_reward
 #ifndef TK_OP3_MIN_CTAS
-#define TK_OP3_MIN_CTAS 6        // resident CTAs per SM the register allocation targets (developer knob)
+#define TK_OP3_MIN_CTAS 5        // resident CTAs per SM the register allocation targets (developer knob)
 #endif
+
+template <int MODE> __host__ __device__ constexpr int threads_of() { return MODE == 0 ? 2 * kRows : kRows; }
+
+// compute_observations :411-438 / compute_op3_observations :662-708 for one (env, agent) row: potentials bookkeeping
+__device__ __forceinline__ void potentials_step(const KParams& p, long long n, int a, const float* r, const float* tb,
+                                                float pot_old, float& pot_new, float& ppot_new, float& ptpot) {
+    ppot_new = pot_old;                                                             // :688
+    pot_new = -norm3_ref(V3{p.goal[0] - r[0], p.goal[1] - r[1], 0.0f}) / p.dt;      // :680-689
+    p.potentials[n * kA + a] = pot_new;
+    p.prev_potentials[n * kA + a] = ppot_new;
+    if (a == 0) {
+        ptpot = -norm3_ref(V3{p.targets[0] - tb[0], p.targets[1] - tb[1], p.targets[2] - tb[2]}) / p.dt;   // :418-419
+        p.prev_table_pot[n] = ptpot;
+    }
+}
 
 // NF > 0: number of feet known at compile time (4 for the OP3 of MA_OP3.py:237-238); NF = 0: p.num_feet at run time
 template <int MODE, int NF>
-__global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(const __grid_constant__ KParams p) {
+__global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_kernel(const __grid_constant__ KParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem& s = *reinterpret_cast<Smem*>(smem_raw);
-    const int tid = threadIdx.x, lane = tid & 31, a = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
+    // thread -> ((env, agent) row, role): rows are consecutive over the lanes of a warp (lane = 2 * env + agent within the
+    // warp's 16 envs), so a lane's row of the torque / action tiles starts 88 B after its neighbour's and its dof_state row
+    // 176 B after: 64-bit / 128-bit shared loads of those rows touch every bank once per phase (no conflicts), and the two
+    // agents of an env sit in neighbouring lanes (the table terms need both: one shuffle, no barrier).  In the fused step
+    // threads 0..63 build the observation rows and threads 64..127 the rewards / resets of the same 64 rows.
+    const int row = tid & (kRows - 1), le = row >> 1, a = row & 1;
+    const bool role_rew = MODE == 2 || (MODE == 0 && tid >= kRows);
+    const bool role_obs = !role_rew;
     const int env0 = blockIdx.x * kTile;
     const int nt = min(kTile, p.n - env0);
-    const long long n = env0 + lane;
-    const bool valid = lane < nt;
+    const long long n = env0 + le;
+    const bool valid = le < nt;
     const bool bulk = p.vec_ok && nt == kTile;
     const size_t e0 = static_cast<size_t>(env0);
     constexpr bool kNeedTq = MODE != 1;
+    constexpr int kThreads = threads_of<MODE>();
     // the finalize grid that follows (programmatic dependent launch) may be scheduled as soon as every CTA got here; it
     // still waits for this grid's completion and memory flush in its own griddepcontrol.wait
     if (MODE == 0) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     constexpr uint32_t kRootB = kTile * kActors * kRoot * 4, kDofB = kTile * kA * kDof * 2 * 4, kRowB = kTile * kA * kDof * 4;
-    if (bulk && tid == 0) {
-        mbar_init(&s.bar, 1);
-        fence_proxy_async_smem();
-    }
-    __syncthreads();
     if (bulk) {
-        if (tid == 0) {
-            mbar_expect_tx(&s.bar, kRootB + kDofB + kRowB + (kNeedTq ? kRowB : 0));
+        if (tid == 0) {                                 // the issuing thread needs no barrier between init and use
+            mbar_init(&s.bar, 1);
+            fence_proxy_async_smem();
+            mbar_expect_tx(&s.bar, kRootB + kDofB + kRowB + (kNeedTq ? 3 * kRowB : 0));
             bulk_load(s.dof, p.dof_state + e0 * kA * kDof * 2, kDofB, &s.bar);
             bulk_load(s.root, p.root + e0 * kActors * kRoot, kRootB, &s.bar);
             bulk_load(s.act, p.actions + e0 * kA * kDof, kRowB, &s.bar);
-            if (kNeedTq) bulk_load(s.tq, p.torques + e0 * kA * kDof, kRowB, &s.bar);
+            if (kNeedTq) {
+                bulk_load(s.tq, p.torques + e0 * kA * kDof, kRowB, &s.bar);
+                bulk_load(s.ptq, p.prev_torques + e0 * kA * kDof, kRowB, &s.bar);
+                bulk_load(s.la, p.last_actions + e0 * kA * kDof, kRowB, &s.bar);
+            }
         }
     } else {
         for (int i = tid; i < nt * kActors * kRoot; i += kThreads) s.root[i] = p.root[e0 * kActors * kRoot + i];
         for (int i = tid; i < nt * kA * kDof * 2; i += kThreads) s.dof[i] = p.dof_state[e0 * kA * kDof * 2 + i];
         for (int i = tid; i < nt * kA * kDof; i += kThreads) {
             s.act[i] = p.actions[e0 * kA * kDof + i];
-            if (kNeedTq) s.tq[i] = p.torques[e0 * kA * kDof + i];
+            if (kNeedTq) {
+                s.tq[i] = p.torques[e0 * kA * kDof + i];
+                s.ptq[i] = p.prev_torques[e0 * kA * kDof + i];
+                s.la[i] = p.last_actions[e0 * kA * kDof + i];
+            }
         }
     }
     // ---- per-env scalars and the foot contact rows: issued before the tile wait ----
@@ -146,30 +187,24 @@ __global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(con
     float cmd[3] = {0.f, 0.f, 0.f}, pot_old = 0.f, ppot_old = 0.f, tpot = 0.f, ptpot = 0.f, ret_old = 0.f;
     float cf[kMaxFeet][3], air[kMaxFeet];
     bool lastc[kMaxFeet];
-    float2 ptq2[kDof / 2], la2[kDof / 2];       // this (env, agent)'s prev_torques / last_actions rows, straight from global
     float gx0 = 0.f, gx1 = 0.f;                 // x contact force on this agent's left / right gripper
     const int nf = NF > 0 ? NF : p.num_feet;
     if (valid) {
-        if (MODE != 1) prog = p.progress[n];
-        if (MODE == 0) {
-            prog += 1;
-            do_reset = p.reset[n] != 0;
-            if (do_reset) prog = 0;                                                 // :488
-            if (a == 0 && p.ep_return) ret_old = p.ep_return[n];
-        } else if (MODE == 2) {
-            rb = p.reset[n];
-        }
+        if (MODE == 0) do_reset = p.reset[n] != 0;
+        if (role_rew || MODE == 1) pot_old = p.potentials[n * kA + a];
+        if (role_rew) {
+            prog = p.progress[n];
+            if (MODE == 0) {
+                prog += 1;
+                if (a == 0 && p.ep_return) ret_old = p.ep_return[n];
+            } else {
+                rb = p.reset[n];
+            }
 #pragma unroll
-        for (int c = 0; c < 3; ++c) cmd[c] = p.commands[n * 3 + c];
-        pot_old = p.potentials[n * kA + a];
-        if (MODE == 2) ppot_old = p.prev_potentials[n * kA + a];
-        tpot = p.table_pot[n];
-        if (MODE == 2) ptpot = p.prev_table_pot[n];
-        if (MODE != 1) {
-            const float2* gp = reinterpret_cast<const float2*>(p.prev_torques) + (n * kA + a) * (kDof / 2);
-            const float2* gl = reinterpret_cast<const float2*>(p.last_actions) + (n * kA + a) * (kDof / 2);
-#pragma unroll
-            for (int j = 0; j < kDof / 2; ++j) { ptq2[j] = gp[j]; la2[j] = gl[j]; }
+            for (int c = 0; c < 3; ++c) cmd[c] = p.commands[n * 3 + c];
+            if (MODE == 2) ppot_old = p.prev_potentials[n * kA + a];
+            tpot = p.table_pot[n];
+            if (MODE == 2) ptpot = p.prev_table_pot[n];
             if (MODE == 0) {
                 gx0 = p.contact[(static_cast<size_t>(n) * p.nb + p.grip[a][0]) * 3];
                 gx1 = p.contact[(static_cast<size_t>(n) * p.nb + p.grip[a][1]) * 3];
@@ -177,14 +212,20 @@ __global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(con
 #pragma unroll
             for (int f = 0; f < kMaxFeet; ++f) {
                 if (f < nf) {
-                    const float* row = p.contact + (static_cast<size_t>(n) * p.nb + p.feet[a][f]) * 3;
-                    cf[f][0] = row[0]; cf[f][1] = row[1]; cf[f][2] = row[2];
+                    const float* crow = p.contact + (static_cast<size_t>(n) * p.nb + p.feet[a][f]) * 3;
+                    cf[f][0] = crow[0]; cf[f][1] = crow[1]; cf[f][2] = crow[2];
                     air[f] = p.air_time[(n * kA + a) * nf + f];
                     lastc[f] = p.last_contacts[(n * kA + a) * nf + f] != 0;
                 }
             }
         }
     }
+    // Every thread has its reset flag in hand before any thread of the CTA can write reset_buf (the reward lanes do, at the
+    // end): the barrier orders the two roles; it also publishes the mbarrier.  The other loads above stay in flight.
+    // (__syncthreads_or takes the flag as an operand, so the load has landed when the thread arrives.)
+    if (MODE == 0) (void)__syncthreads_or(do_reset ? 1 : 0);
+    else __syncthreads();
+    if (MODE == 0 && do_reset) prog = 0;                                            // :488
     // A resetting env takes its robot / table rows from initial_root_states (:468-470): those global loads are issued
     // here, under the tile wait, instead of in the middle of the compute phase (18 % of the stall samples in the v3 profile).
     float r[kRoot], tb[kRoot];
@@ -198,59 +239,30 @@ __global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(con
 
     float my_rew = 0.f, my_dist = 0.f;
     int my_flag = 0;                        // bit 0: up_proj < 0.90, bit 1: distance to the table > 0.40
-    float pot_new = pot_old, ppot_new = ppot_old;
     if (valid) {
-        const int row = lane * kA + a;
         if (!(MODE == 0 && do_reset)) {
 #pragma unroll
-            for (int c = 0; c < kRoot; ++c) r[c] = s.root[(lane * kActors + a) * kRoot + c];
+            for (int c = 0; c < kRoot; ++c) r[c] = s.root[((le * kActors) + a) * kRoot + c];
 #pragma unroll
-            for (int c = 0; c < kRoot; ++c) tb[c] = s.root[(lane * kActors + 2) * kRoot + c];
+            for (int c = 0; c < kRoot; ++c) tb[c] = s.root[((le * kActors) + 2) * kRoot + c];
         }
-        float2* dofp = reinterpret_cast<float2*>(s.dof) + row * kDof;
-        const float* act = s.act + row * kDof;
-        bool zero_last = false;
-        if (MODE == 0 && do_reset) {                                                // reset_idx :440-489, this env's lanes
-            float2* gd = reinterpret_cast<float2*>(p.dof_state) + (n * kA + a) * kDof;
-#pragma unroll
-            for (int j = 0; j < kDof; ++j) {
-                const float2 pv = make_float2(p.default_dof_pos[j] + 0.0f, 0.0f);   // :456-457 (offsets are zeros)
-                dofp[j] = pv;
-                gd[j] = pv;
-            }
-#pragma unroll
-            for (int c = 0; c < kRoot; ++c) {                                       // :468-470 (rows preloaded above)
-                p.root[(n * kActors + a) * kRoot + c] = r[c];
-                if (a == 0) p.root[(n * kActors + 2) * kRoot + c] = tb[c];
-            }
-            float uc[3] = {0.5f, 0.5f, 0.5f};
-            if (p.noise_mode == TK_NOISE_PHILOX) {
-                Philox4 d = philox_env(p.seed, effective_step(p.step, p.step_dev), p.env_off + n, kStreamCmd);
-                uc[0] = u01(d.x); uc[1] = u01(d.y); uc[2] = u01(d.z);
-            } else if (p.noise_mode == TK_NOISE_DENSE && p.unit_cmd) {
-#pragma unroll
-                for (int c = 0; c < 3; ++c) uc[c] = p.unit_cmd[n * 3 + c];
-            }
-            cmd[0] = rand_float(p.cmd_x[0], p.cmd_x[1], uc[0]);                     // :472
-            cmd[1] = rand_float(p.cmd_y[0], p.cmd_y[1], uc[1]);                     // :473
-            cmd[2] = rand_float(p.cmd_yaw[0], p.cmd_yaw[1], uc[2]);                 // :474
-            pot_old = -norm3_ref(V3{p.goal[0] - r[0], p.goal[1] - r[1], 0.0f}) / p.dt;      // :476-479
-            tpot = -norm3_ref(V3{p.targets[0] - tb[0], p.targets[1] - tb[1], 0.0f}) / p.dt; // :481-484
-            if (a == 0) {
-#pragma unroll
-                for (int c = 0; c < 3; ++c) p.commands[n * 3 + c] = cmd[c];
-                p.table_pot[n] = tpot;
-            }
-            zero_last = true;                                                       // :486
-#pragma unroll
-            for (int f = 0; f < kMaxFeet; ++f) air[f] = 0.0f;                       // :487
-        }
+        const float4* dof4 = reinterpret_cast<const float4*>(s.dof) + row * (kDof / 2);    // (pos_j, vel_j, pos_j+1, vel_j+1)
+        const float2* act2 = reinterpret_cast<const float2*>(s.act) + row * (kDof / 2);
+        const bool rst = MODE == 0 && do_reset;
         const Q4 q{r[3], r[4], r[5], r[6]};
         const V3 ang_raw = quat_rotate_ref<-1>(q, V3{r[10], r[11], r[12]});         // :579 / :693 before scaling
-        if (MODE != 2) {                                                            // compute_observations :411-438
-            ppot_new = pot_old;                                                     // :688
-            pot_new = -norm3_ref(V3{p.goal[0] - r[0], p.goal[1] - r[1], 0.0f}) / p.dt;      // :680-689
-            if (a == 0) ptpot = -norm3_ref(V3{p.targets[0] - tb[0], p.targets[1] - tb[1], p.targets[2] - tb[2]}) / p.dt;   // :418-419
+        if (role_obs) {                                                             // compute_observations :411-438
+            if (rst) {
+#pragma unroll
+                for (int c = 0; c < kRoot; ++c) {                                   // :468-470 (rows preloaded above)
+                    p.root[(n * kActors + a) * kRoot + c] = r[c];
+                    if (a == 0) p.root[(n * kActors + 2) * kRoot + c] = tb[c];
+                }
+            }
+            if (MODE == 1) {
+                float pot_new, ppot_new;
+                potentials_step(p, n, a, r, tb, pot_old, pot_new, ppot_new, ptpot);
+            }
             const V3 lin = quat_rotate_ref<-1>(q, V3{r[7], r[8], r[9]});            // :692
             const V3 g = quat_rotate_ref<1>(q, V3{p.gravity[0], p.gravity[1], p.gravity[2]});   // :694
             float4* o = reinterpret_cast<float4*>(p.obs + (static_cast<size_t>(n) * kA + a) * kObs);   // 352-byte rows, 16-byte aligned
@@ -259,23 +271,60 @@ __global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(con
             v[3] = ang_raw.x * p.ang_vel_scale; v[4] = ang_raw.y * p.ang_vel_scale; v[5] = ang_raw.z * p.ang_vel_scale;
             v[6] = g.x; v[7] = g.y; v[8] = g.z;
 #pragma unroll
-            for (int j = 0; j < kDof; ++j) {
-                const float2 pv = dofp[j];
-                v[9 + j] = (pv.x - p.default_dof_pos[j]) * p.dof_pos_scale;         // :695
-                v[31 + j] = pv.y * p.dof_vel_scale;
-                v[53 + j] = act[j];
-            }
-#pragma unroll
             for (int c = 0; c < 10; ++c) v[75 + c] = tb[c];                         // object pose + linvel
             v[85] = p.targets[0]; v[86] = p.targets[1]; v[87] = p.targets[2];
+            // Every 128-bit piece of the row is stored as soon as its four columns exist (obs_piece_ready: the j at which
+            // the last of them is produced), not after the whole row: the row never sits in 88 registers.
 #pragma unroll
-            for (int c = 0; c < kObs / 4; ++c) __stcs(o + c, make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]));
-            p.potentials[n * kA + a] = pot_new;
-            p.prev_potentials[n * kA + a] = ppot_new;
-            if (a == 0) p.prev_table_pot[n] = ptpot;
-        }
-        if (MODE != 1) {                                                            // compute_reward :360-409, this agent
-            const float pot_r = (MODE == 2) ? pot_old : pot_new, ppot_r = (MODE == 2) ? ppot_old : ppot_new;
+            for (int c = 0; c < kObs / 4; ++c)
+                if (obs_piece_ready(c) < 0) __stcs(o + c, make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]));
+#pragma unroll
+            for (int jj = 0; jj < kDof / 2; ++jj) {
+                float4 d = dof4[jj];
+                const float2 ac = act2[jj];
+                if (rst) d = make_float4(p.default_dof_pos[2 * jj] + 0.0f, 0.0f, p.default_dof_pos[2 * jj + 1] + 0.0f, 0.0f);   // :456-457
+                v[9 + 2 * jj] = (d.x - p.default_dof_pos[2 * jj]) * p.dof_pos_scale;                // :695
+                v[10 + 2 * jj] = (d.z - p.default_dof_pos[2 * jj + 1]) * p.dof_pos_scale;
+                v[31 + 2 * jj] = d.y * p.dof_vel_scale;
+                v[32 + 2 * jj] = d.w * p.dof_vel_scale;
+                v[53 + 2 * jj] = ac.x;
+                v[54 + 2 * jj] = ac.y;
+#pragma unroll
+                for (int c = 0; c < kObs / 4; ++c)
+                    if (obs_piece_ready(c) >= 0 && (obs_piece_ready(c) >> 1) == jj)
+                        __stcs(o + c, make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]));
+            }
+        } else {                                                                    // compute_reward :360-409, this agent
+            bool zero_last = false;
+            if (rst) {                                                              // reset_idx :440-489, this env's lanes
+                float4* gd = reinterpret_cast<float4*>(p.dof_state) + (n * kA + a) * (kDof / 2);
+#pragma unroll
+                for (int jj = 0; jj < kDof / 2; ++jj)                               // :456-457 (offsets are zeros)
+                    gd[jj] = make_float4(p.default_dof_pos[2 * jj] + 0.0f, 0.0f, p.default_dof_pos[2 * jj + 1] + 0.0f, 0.0f);
+                float uc[3] = {0.5f, 0.5f, 0.5f};
+                if (p.noise_mode == TK_NOISE_PHILOX) {
+                    Philox4 d = philox_env(p.seed, effective_step(p.step, p.step_dev), p.env_off + n, kStreamCmd);
+                    uc[0] = u01(d.x); uc[1] = u01(d.y); uc[2] = u01(d.z);
+                } else if (p.noise_mode == TK_NOISE_DENSE && p.unit_cmd) {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) uc[c] = p.unit_cmd[n * 3 + c];
+                }
+                cmd[0] = rand_float(p.cmd_x[0], p.cmd_x[1], uc[0]);                 // :472
+                cmd[1] = rand_float(p.cmd_y[0], p.cmd_y[1], uc[1]);                 // :473
+                cmd[2] = rand_float(p.cmd_yaw[0], p.cmd_yaw[1], uc[2]);             // :474
+                pot_old = -norm3_ref(V3{p.goal[0] - r[0], p.goal[1] - r[1], 0.0f}) / p.dt;      // :476-479
+                tpot = -norm3_ref(V3{p.targets[0] - tb[0], p.targets[1] - tb[1], 0.0f}) / p.dt; // :481-484
+                if (a == 0) {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) p.commands[n * 3 + c] = cmd[c];
+                    p.table_pot[n] = tpot;
+                }
+                zero_last = true;                                                   // :486
+#pragma unroll
+                for (int f = 0; f < kMaxFeet; ++f) air[f] = 0.0f;                   // :487
+            }
+            float pot_r = pot_old, ppot_r = ppot_old;
+            if (MODE == 0) potentials_step(p, n, a, r, tb, pot_old, pot_r, ppot_r, ptpot);
             const bool moving = norm2_ref(cmd[0], cmd[1]) > 0.1f, still = norm2_ref(cmd[0], cmd[1]) < 0.1f;
             // _reward_air_time :319-329, _reward_feet_contact_forces :331-334, _reward_no_fly :336-340
             float air_sum = 0.0f, step_sum = 0.0f;
@@ -306,19 +355,28 @@ __global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(con
             const float up_proj = quat_rotate_ref<1>(torso, V3{p.up[0], p.up[1], p.up[2]}).z;    // :601-602
             const float rew_up = up_proj > 0.95f ? 0.0f + p.k_up : 0.0f;           // :605-606
             const float progress_reward = (pot_r - ppot_r) * 5.0f;                  // :612
-            const float* tqr = s.tq + row * kDof;
-            const float* ptqr = reinterpret_cast<const float*>(ptq2);
-            const float* lar = reinterpret_cast<const float*>(la2);
+            const float2* tq2 = reinterpret_cast<const float2*>(s.tq) + row * (kDof / 2);
+            const float2* ptq2 = reinterpret_cast<const float2*>(s.ptq) + row * (kDof / 2);
+            const float2* la2 = reinterpret_cast<const float2*>(s.la) + row * (kDof / 2);
             float tsum = 0.0f, legsum = 0.0f, ratesum = 0.0f, standsum = 0.0f;
 #pragma unroll
-            for (int j = 0; j < kDof; ++j) {
-                tsum += fabsf(ptqr[j] - tqr[j]);                                    // :619
-                const float dev = fabsf(dofp[j].x - p.default_dof_pos[j]);
-                standsum += dev;                                                    // :630
-                if ((j >= 2 && j <= 7) || (j >= 11 && j <= 17) || j == 21) legsum += dev;   // :622-623
-                const float la = zero_last ? 0.0f : lar[j];
-                const float da = la - act[j];
-                ratesum += da * da;                                                 // :627
+            for (int jj = 0; jj < kDof / 2; ++jj) {
+                const float4 d = dof4[jj];
+                const float2 t = tq2[jj], pt = ptq2[jj], ac = act2[jj];
+                float2 l = la2[jj];
+                if (zero_last) l = make_float2(0.0f, 0.0f);
+                const float px[2] = {rst ? p.default_dof_pos[2 * jj] + 0.0f : d.x, rst ? p.default_dof_pos[2 * jj + 1] + 0.0f : d.z};
+                const float tv[2] = {t.x, t.y}, ptv[2] = {pt.x, pt.y}, av[2] = {ac.x, ac.y}, lv[2] = {l.x, l.y};
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int j = 2 * jj + h;
+                    tsum += fabsf(ptv[h] - tv[h]);                                  // :619
+                    const float dev = fabsf(px[h] - p.default_dof_pos[j]);
+                    standsum += dev;                                                // :630
+                    if ((j >= 2 && j <= 7) || (j >= 11 && j <= 17) || j == 21) legsum += dev;   // :622-623
+                    const float da = lv[h] - av[h];
+                    ratesum += da * da;                                             // :627
+                }
             }
             const float rew_torque = tsum * p.k_torque;
             const float rew_syns = legsum * p.k_syns;                               // :624
@@ -338,74 +396,75 @@ __global__ void __launch_bounds__(kThreads, TK_OP3_MIN_CTAS) op3_tile_kernel(con
             my_flag = (up_proj < 0.90f ? 1 : 0) | (my_dist > 0.40f ? 2 : 0);        // :654-655
         }
     }
-    if (MODE == 0) {                                                                // :351-352, this tile's share
-        const unsigned m0 = __ballot_sync(0xffffffffu, valid && gx0 > 0.1f), m1 = __ballot_sync(0xffffffffu, valid && gx1 > 0.1f);
-        if (lane == 0 && m0) atomicAdd(p.grip_counts + a * 2, static_cast<unsigned long long>(__popc(m0)));
-        if (lane == 0 && m1) atomicAdd(p.grip_counts + a * 2 + 1, static_cast<unsigned long long>(__popc(m1)));
-    }
-    if (MODE == 1) {
-        __syncthreads();
-    } else {
-        if (a == 1) { s.x_rew[lane] = my_rew; s.x_dist[lane] = my_dist; s.x_flag[lane] = my_flag; }
-        __syncthreads();
-    }
-    float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_d0 = 0.f, st_d1 = 0.f;
-    bool out_reset = false, out_timeout = false;
-    if (MODE != 1 && a == 0 && valid) {
-        const float rew1 = s.x_rew[lane];
-        const int flag1 = s.x_flag[lane];
-        // reset_buf through the two compute_op3_reward calls (:653-656) ...
-        long long rv = rb;
-        const bool over = prog >= p.max_episode_length;
-        if (over) rv = 1;
-        if (my_flag) rv = 1;
-        if (prog == 0) rv = 0;
-        if (over) rv = 1;
-        if (flag1) rv = 1;
-        if (prog == 0) rv = 0;
-        // ... and compute_objective_reward :496-547
-        const Q4 tq{tb[3], tb[4], tb[5], tb[6]};
-        const float tup = quat_rotate_ref<1>(tq, V3{p.up[0], p.up[1], p.up[2]}).z;  // :528-529
-        const float rew_up = tup > 0.98f ? 0.0f + 0.1f : 0.0f;                      // :532-533
-        const float hz = tb[2] - 0.29f;
-        const float rew_h = (hz * hz) * -0.001f;                                    // :536
-        const float dist_rew = (tpot - ptpot) * 5.0f;                               // :540
-        const float r0 = ((my_rew + dist_rew) + rew_up) + rew_h;                    // :542
-        const float r1 = ((rew1 + dist_rew) + rew_up) + rew_h;
-        if (tup < 0.90f) rv = 1;                                                    // :544
-        if (tb[2] < 0.25f) rv = 1;                                                  // :545
-        *reinterpret_cast<float2*>(p.rew + n * kA) = make_float2(r0, r1);
-        p.reset[n] = rv;
-        out_reset = rv != 0;
-        st_rew = r0 + r1; st_d0 = my_dist; st_d1 = s.x_dist[lane];
-        if (MODE == 0) {
-            p.progress[n] = prog;
-            out_timeout = (prog >= p.max_episode_length - 1) && out_reset;          // multi_vec_task.py:193
-            if (p.timeout) p.timeout[n] = out_timeout ? 1 : 0;
-            if (p.ep_return) {
-                const float ret = (do_reset ? 0.0f : ret_old) + (r0 + r1);
-                if (out_reset) st_ret = ret;
-                p.ep_return[n] = ret;
+    if (role_rew) {                                     // warp-uniform: whole warps of reward lanes from here on
+        if (MODE == 0) {                                                            // :351-352, this warp's share
+            const unsigned m0 = __ballot_sync(0xffffffffu, valid && gx0 > 0.1f), m1 = __ballot_sync(0xffffffffu, valid && gx1 > 0.1f);
+            if (lane < 4) {                             // lane = agent * 2 + gripper; agent a sits in the lanes of parity a
+                const unsigned m = ((lane & 1) ? m1 : m0) & ((lane >> 1) ? 0xaaaaaaaau : 0x55555555u);
+                if (m) atomicAdd(p.grip_counts + lane, static_cast<unsigned long long>(__popc(m)));
             }
-            if (out_reset) st_len = static_cast<float>(prog);
         }
-    }
-    if (MODE == 0 && a == 0) {
-        const unsigned m_reset = __ballot_sync(0xffffffffu, out_reset), m_to = __ballot_sync(0xffffffffu, out_timeout);
+        // the other agent of this env sits in the neighbouring lane
+        const float rew1 = __shfl_xor_sync(0xffffffffu, my_rew, 1), dist1 = __shfl_xor_sync(0xffffffffu, my_dist, 1);
+        const int flag1 = __shfl_xor_sync(0xffffffffu, my_flag, 1);
+        float st_rew = 0.f, st_ret = 0.f, st_len = 0.f, st_d0 = 0.f, st_d1 = 0.f;
+        bool out_reset = false, out_timeout = false;
+        if (a == 0 && valid) {
+            // reset_buf through the two compute_op3_reward calls (:653-656) ...
+            long long rv = rb;
+            const bool over = prog >= p.max_episode_length;
+            if (over) rv = 1;
+            if (my_flag) rv = 1;
+            if (prog == 0) rv = 0;
+            if (over) rv = 1;
+            if (flag1) rv = 1;
+            if (prog == 0) rv = 0;
+            // ... and compute_objective_reward :496-547
+            const Q4 tq{tb[3], tb[4], tb[5], tb[6]};
+            const float tup = quat_rotate_ref<1>(tq, V3{p.up[0], p.up[1], p.up[2]}).z;  // :528-529
+            const float rew_up = tup > 0.98f ? 0.0f + 0.1f : 0.0f;                      // :532-533
+            const float hz = tb[2] - 0.29f;
+            const float rew_h = (hz * hz) * -0.001f;                                    // :536
+            const float dist_rew = (tpot - ptpot) * 5.0f;                               // :540
+            const float r0 = ((my_rew + dist_rew) + rew_up) + rew_h;                    // :542
+            const float r1 = ((rew1 + dist_rew) + rew_up) + rew_h;
+            if (tup < 0.90f) rv = 1;                                                    // :544
+            if (tb[2] < 0.25f) rv = 1;                                                  // :545
+            *reinterpret_cast<float2*>(p.rew + n * kA) = make_float2(r0, r1);
+            p.reset[n] = rv;
+            out_reset = rv != 0;
+            st_rew = r0 + r1; st_d0 = my_dist; st_d1 = dist1;
+            if (MODE == 0) {
+                p.progress[n] = prog;
+                out_timeout = (prog >= p.max_episode_length - 1) && out_reset;          // multi_vec_task.py:193
+                if (p.timeout) p.timeout[n] = out_timeout ? 1 : 0;
+                if (p.ep_return) {
+                    const float ret = (do_reset ? 0.0f : ret_old) + (r0 + r1);
+                    if (out_reset) st_ret = ret;
+                    p.ep_return[n] = ret;
+                }
+                if (out_reset) st_len = static_cast<float>(prog);
+            }
+        }
+        if (MODE == 0) {
+            const unsigned m_reset = __ballot_sync(0xffffffffu, out_reset), m_to = __ballot_sync(0xffffffffu, out_timeout);
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            st_rew += __shfl_xor_sync(0xffffffffu, st_rew, o);
-            st_ret += __shfl_xor_sync(0xffffffffu, st_ret, o);
-            st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
-            st_d0 += __shfl_xor_sync(0xffffffffu, st_d0, o);
-            st_d1 += __shfl_xor_sync(0xffffffffu, st_d1, o);
+            for (int o = 16; o > 0; o >>= 1) {
+                st_rew += __shfl_xor_sync(0xffffffffu, st_rew, o);
+                st_ret += __shfl_xor_sync(0xffffffffu, st_ret, o);
+                st_len += __shfl_xor_sync(0xffffffffu, st_len, o);
+                st_d0 += __shfl_xor_sync(0xffffffffu, st_d0, o);
+                st_d1 += __shfl_xor_sync(0xffffffffu, st_d1, o);
+            }
+            const int warp_envs = min(max(nt - ((row >> 5) * (kTile / 2)), 0), kTile / 2);
+            double* pr = p.partials + static_cast<size_t>(blockIdx.x & (kStatSlots - 1)) * TK_STATS;
+            const float vals[TK_STATS] = {st_rew, static_cast<float>(__popc(m_reset)), static_cast<float>(__popc(m_to)), st_ret,
+                                          st_len, st_d0, st_d1, static_cast<float>(warp_envs)};
+            if (lane < TK_STATS) atomicAdd(pr + lane, static_cast<double>(vals[lane]));
         }
-        double* pr = p.partials + static_cast<size_t>(blockIdx.x & (kStatSlots - 1)) * TK_STATS;
-        const float vals[TK_STATS] = {st_rew, static_cast<float>(__popc(m_reset)), static_cast<float>(__popc(m_to)), st_ret,
-                                      st_len, st_d0, st_d1, static_cast<float>(nt)};
-        if (lane < TK_STATS) atomicAdd(pr + lane, static_cast<double>(vals[lane]));
     }
-    // ---- stores: one 352-byte bulk store per (env, agent) obs row; prev_torques / last_actions from the resident tiles ----
+    // ---- prev_torques / last_actions are refreshed from the torque / action tiles that are resident (TMA wrote them; no
+    //      thread modifies them), by the thread that issued the loads ----
     if (bulk) {
         if (MODE == 0 && tid == 0) {
             bulk_store(p.prev_torques + e0 * kA * kDof, s.tq, kRowB);                // end-of-step refresh (see header)
@@ -614,13 +673,15 @@ static int check_bound(const TkOp3* h) {
 template <int MODE, int NF>
 static cudaError_t launch_tile_nf(const TkOp3* h, const KParams& k, cudaStream_t st) {
     static bool opted = false;
+    static int pad = 0;      // TK_OP3_SMEM_PAD (developer knob): extra dynamic shared memory per CTA = fewer resident CTAs per SM
     if (!opted) {
+        if (const char* env = getenv("TK_OP3_SMEM_PAD")) pad = atoi(env);
         cudaError_t e = cudaFuncSetAttribute(op3_tile_kernel<MODE, NF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             static_cast<int>(sizeof(Smem)));
+                                             static_cast<int>(sizeof(Smem)) + pad);
         if (e != cudaSuccess) return e;
         opted = true;
     }
-    op3_tile_kernel<MODE, NF><<<h->tiles, kThreads, sizeof(Smem), st>>>(k);
+    op3_tile_kernel<MODE, NF><<<h->tiles, threads_of<MODE>(), sizeof(Smem) + pad, st>>>(k);
     return cudaGetLastError();
 }
 
