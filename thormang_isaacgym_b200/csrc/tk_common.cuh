@@ -55,6 +55,22 @@ __device__ __forceinline__ float4 ldg_stream4(const float* p) {
 // same through the coherent path, evict-first: for arrays this kernel may also write (root_states, dof_state)
 __device__ __forceinline__ float4 ld_stream4(const float* p) { return __ldcs(reinterpret_cast<const float4*>(p)); }
 __device__ __forceinline__ void stg_stream4(float* p, float4 v) { __stcs(reinterpret_cast<float4*>(p), v); }
+// One whole 32-byte sector per lane in one request (sm_100 has 256-bit global accesses: STG.E.EF.ENL2.256); p 32-byte aligned
+__device__ __forceinline__ void stg_stream8(float* p, const float* v) {
+    asm volatile("st.global.cs.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
+                 "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+}
+// A 12-byte row at a 4-byte aligned address as one 64-bit and one 32-bit load (two requests instead of three)
+__device__ __forceinline__ void ldg_row3(const float* row, float& x, float& y, float& z) {
+    if ((reinterpret_cast<uintptr_t>(row) & 4u) == 0) {
+        const float2 t = *reinterpret_cast<const float2*>(row);
+        x = t.x; y = t.y; z = row[2];
+    } else {
+        x = row[0];
+        const float2 t = *reinterpret_cast<const float2*>(row + 1);
+        y = t.x; z = t.y;
+    }
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 

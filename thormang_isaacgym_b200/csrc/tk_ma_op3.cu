@@ -35,7 +35,11 @@ constexpr int kRoot = 13;
 constexpr int kActors = 3;
 constexpr int kDof = TK_OP3_DOF;
 constexpr int kObs = TK_OP3_OBS;
-constexpr int kTile = 32;
+#ifndef TK_OP3_TILE
+#define TK_OP3_TILE 16          // envs per CTA (16 or 32): one warp of observation lanes + one of reward lanes per 16 envs
+#endif
+constexpr int kTile = TK_OP3_TILE;
+constexpr int kMaxContactTileBytes = 24 * 1024;     // a tile's whole contact block is staged when it is at most this big
 constexpr int kRows = kTile * kA;            // (env, agent) rows of a tile
 constexpr int kMaxFeet = TK_OP3_MAX_FEET;
 
@@ -72,12 +76,15 @@ struct KParams {
     int n, nb, max_episode_length, num_feet;
     int feet[kA][kMaxFeet];
     int grip[kA][2];
-    int vec_ok;
+    int vec_ok;                              // 16-byte aligned tile arrays: cp.async.bulk tile copies
+    int contact_tile;                        // the tile's contact_forces block [kTile, nb, 3] is bulk-copied as well
+    int obs32, vec_feet, contact8;           // 32-byte aligned obs rows; 16-/4-byte aligned air_time / last_contacts; 8-byte contact
     float lin_vel_scale, ang_vel_scale, dof_pos_scale, dof_vel_scale, action_scale, clip_actions, dt;
     float k_torque, k_up, k_air, k_syns, k_nofly, k_stand, k_rate;     // (float)(scale * dt), MA_OP3.py:80-81
     float cmd_x[2], cmd_y[2], cmd_yaw[2];   // lo, (hi - lo) formed in double
     float default_dof_pos[kDof];
     float inv_start_rot[4], gravity[3], up[3], targets[3], goal[3];
+    long long* dbg_ts;                       // developer timeline probe (tools/op3_timeline.py): [tiles, 4 warps, 8]; NULL in normal use
 };
 
 enum { kStreamCmd = 48 };
@@ -103,15 +110,23 @@ struct Smem {
 __host__ __device__ constexpr int obs_col_ready(int col) {
     return col < 9 ? -1 : col < 31 ? col - 9 : col < 53 ? col - 31 : col < 75 ? col - 53 : -1;
 }
-__host__ __device__ constexpr int obs_piece_ready(int c) {
+__host__ __device__ constexpr int obs_piece_ready(int c) {      // piece = 8 columns = one 32-byte sector of the row
     int r = -1;
-    for (int k = 0; k < 4; ++k) r = obs_col_ready(4 * c + k) > r ? obs_col_ready(4 * c + k) : r;
+    for (int k = 0; k < 8; ++k) r = obs_col_ready(8 * c + k) > r ? obs_col_ready(8 * c + k) : r;
     return r;
+}
+__device__ __forceinline__ void store_obs_piece(float* row, int c, const float* v, bool obs32) {
+    if (obs32) {
+        stg_stream8(row + 8 * c, v + 8 * c);
+    } else {
+        stg_stream4(row + 8 * c, make_float4(v[8 * c], v[8 * c + 1], v[8 * c + 2], v[8 * c + 3]));
+        stg_stream4(row + 8 * c + 4, make_float4(v[8 * c + 4], v[8 * c + 5], v[8 * c + 6], v[8 * c + 7]));
+    }
 }
 
 // MODE 0: fused post_physics_step; 1: compute_observations; 2: compute_reward
 #ifndef TK_OP3_MIN_CTAS
-#define TK_OP3_MIN_CTAS 5        // resident CTAs per SM the register allocation targets (developer knob)
+#define TK_OP3_MIN_CTAS (TK_OP3_TILE == 16 ? 7 : 3)        // resident CTAs per SM the register allocation targets (developer knob)
 #endif
 
 template <int MODE> __host__ __device__ constexpr int threads_of() { return MODE == 0 ? 2 * kRows : kRows; }
@@ -154,12 +169,23 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
     // the finalize grid that follows (programmatic dependent launch) may be scheduled as soon as every CTA got here; it
     // still waits for this grid's completion and memory flush in its own griddepcontrol.wait
     if (MODE == 0) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    long long* ts = (MODE == 0 && p.dbg_ts) ? p.dbg_ts + (static_cast<size_t>(blockIdx.x) * 4 + (tid >> 5)) * 8 : nullptr;
+#define TK_OSTAMP(i) do { if (ts && lane == 0) { long long g_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_) :: "memory"); ts[i] = g_; } } while (0)
+    TK_OSTAMP(0);
     constexpr uint32_t kRootB = kTile * kActors * kRoot * 4, kDofB = kTile * kA * kDof * 2 * 4, kRowB = kTile * kA * kDof * 4;
+    // The feet / gripper rows an env needs are 12 of its nb = 51 contact rows, 12 bytes each at a 612-byte stride: fetched by
+    // the lanes they cost one 64-byte DRAM atom per row (768 B per env, more than the 612-byte block) and, worse, one L1 miss
+    // per row and lane -- the reward warps spent 6 us of their 12 us just getting those loads accepted.  The block comes
+    // with the other tiles instead.
+    float* s_contact = reinterpret_cast<float*>(smem_raw + sizeof(Smem));
+    const bool ctile = kNeedTq && bulk && p.contact_tile;
+    const uint32_t contact_bytes = static_cast<uint32_t>(kTile) * static_cast<uint32_t>(p.nb) * 12u;
     if (bulk) {
         if (tid == 0) {                                 // the issuing thread needs no barrier between init and use
             mbar_init(&s.bar, 1);
             fence_proxy_async_smem();
-            mbar_expect_tx(&s.bar, kRootB + kDofB + kRowB + (kNeedTq ? 3 * kRowB : 0));
+            mbar_expect_tx(&s.bar, kRootB + kDofB + kRowB + (kNeedTq ? 3 * kRowB : 0) + (ctile ? contact_bytes : 0u));
+            if (ctile) bulk_load(s_contact, p.contact + e0 * p.nb * 3, contact_bytes, &s.bar);
             bulk_load(s.dof, p.dof_state + e0 * kA * kDof * 2, kDofB, &s.bar);
             bulk_load(s.root, p.root + e0 * kActors * kRoot, kRootB, &s.bar);
             bulk_load(s.act, p.actions + e0 * kA * kDof, kRowB, &s.bar);
@@ -182,50 +208,63 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
         }
     }
     // ---- per-env scalars and the foot contact rows: issued before the tile wait ----
-    long long prog = 0, rb = 0;
+    long long prog = 0, rb = 0, reset_raw = 0;
     bool do_reset = false;
     float cmd[3] = {0.f, 0.f, 0.f}, pot_old = 0.f, ppot_old = 0.f, tpot = 0.f, ptpot = 0.f, ret_old = 0.f;
     float cf[kMaxFeet][3], air[kMaxFeet];
-    bool lastc[kMaxFeet];
+    unsigned lc_raw = 0;                        // last_contacts of this lane's feet: the four bytes as loaded (four-foot build),
+                                                // else one bit per foot
     float gx0 = 0.f, gx1 = 0.f;                 // x contact force on this agent's left / right gripper
     const int nf = NF > 0 ? NF : p.num_feet;
+    const bool feet_vec = NF == 4 && p.vec_feet;
     if (valid) {
-        if (MODE == 0) do_reset = p.reset[n] != 0;
+        if (MODE != 1) reset_raw = p.reset[n];
         if (role_rew || MODE == 1) pot_old = p.potentials[n * kA + a];
         if (role_rew) {
             prog = p.progress[n];
-            if (MODE == 0) {
-                prog += 1;
-                if (a == 0 && p.ep_return) ret_old = p.ep_return[n];
-            } else {
-                rb = p.reset[n];
-            }
 #pragma unroll
             for (int c = 0; c < 3; ++c) cmd[c] = p.commands[n * 3 + c];
             if (MODE == 2) ppot_old = p.prev_potentials[n * kA + a];
             tpot = p.table_pot[n];
             if (MODE == 2) ptpot = p.prev_table_pot[n];
-            if (MODE == 0) {
+            if (MODE == 0 && !ctile) {
                 gx0 = p.contact[(static_cast<size_t>(n) * p.nb + p.grip[a][0]) * 3];
                 gx1 = p.contact[(static_cast<size_t>(n) * p.nb + p.grip[a][1]) * 3];
+            }
+            if (feet_vec) {                             // this lane's four feet: one 128-bit and one 32-bit load
+                const float4 at = *reinterpret_cast<const float4*>(p.air_time + (n * kA + a) * 4);
+                lc_raw = *reinterpret_cast<const unsigned*>(p.last_contacts + (n * kA + a) * 4);
+                air[0] = at.x; air[1] = at.y; air[2] = at.z; air[3] = at.w;
             }
 #pragma unroll
             for (int f = 0; f < kMaxFeet; ++f) {
                 if (f < nf) {
-                    const float* crow = p.contact + (static_cast<size_t>(n) * p.nb + p.feet[a][f]) * 3;
-                    cf[f][0] = crow[0]; cf[f][1] = crow[1]; cf[f][2] = crow[2];
-                    air[f] = p.air_time[(n * kA + a) * nf + f];
-                    lastc[f] = p.last_contacts[(n * kA + a) * nf + f] != 0;
+                    if (!ctile) {
+                        const float* crow = p.contact + (static_cast<size_t>(n) * p.nb + p.feet[a][f]) * 3;
+                        if (p.contact8) ldg_row3(crow, cf[f][0], cf[f][1], cf[f][2]);
+                        else { cf[f][0] = crow[0]; cf[f][1] = crow[1]; cf[f][2] = crow[2]; }
+                    }
+                    if (!feet_vec) {
+                        air[f] = p.air_time[(n * kA + a) * nf + f];
+                        lc_raw |= (p.last_contacts[(n * kA + a) * nf + f] != 0 ? 1u : 0u) << f;
+                    }
                 }
             }
         }
     }
     // Every thread has its reset flag in hand before any thread of the CTA can write reset_buf (the reward lanes do, at the
     // end): the barrier orders the two roles; it also publishes the mbarrier.  The other loads above stay in flight.
-    // (__syncthreads_or takes the flag as an operand, so the load has landed when the thread arrives.)
-    if (MODE == 0) (void)__syncthreads_or(do_reset ? 1 : 0);
+    // (__syncthreads_or takes the flag as an operand, so the load has landed when the thread arrives.)  Nothing that was
+    // loaded above may be looked at before this point: the compiler otherwise turns loaded values into predicates as soon as
+    // it can (prog + 1, gx > 0.1, flag != 0 ...), and every such use is a full memory latency in front of the loads behind it
+    // (7 us from kernel entry to the barrier in the first build of this layout).  The empty asm statements pin that order.
+    asm volatile("" : "+l"(reset_raw) :: "memory");
+    TK_OSTAMP(1);
+    if (MODE == 0) (void)__syncthreads_or(reset_raw != 0 ? 1 : 0);
     else __syncthreads();
-    if (MODE == 0 && do_reset) prog = 0;                                            // :488
+    TK_OSTAMP(2);
+    do_reset = MODE == 0 && reset_raw != 0;
+    rb = reset_raw;
     // A resetting env takes its robot / table rows from initial_root_states (:468-470): those global loads are issued
     // here, under the tile wait, instead of in the middle of the compute phase (18 % of the stall samples in the v3 profile).
     float r[kRoot], tb[kRoot];
@@ -236,6 +275,35 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
     }
     if (bulk) mbar_wait(&s.bar, 0);
     else __syncthreads();
+    TK_OSTAMP(3);
+    if (role_rew) {
+        if (ctile && valid) {
+            const float* cb = s_contact + static_cast<size_t>(le) * p.nb * 3;
+            if (MODE == 0) { gx0 = cb[p.grip[a][0] * 3]; gx1 = cb[p.grip[a][1] * 3]; }
+#pragma unroll
+            for (int f = 0; f < kMaxFeet; ++f) {
+                if (f < nf) {
+                    const float* crow = cb + p.feet[a][f] * 3;
+                    cf[f][0] = crow[0]; cf[f][1] = crow[1]; cf[f][2] = crow[2];
+                }
+            }
+        }
+        asm volatile("" : "+l"(prog), "+f"(gx0), "+f"(gx1), "+r"(lc_raw), "+f"(pot_old), "+f"(tpot));
+#pragma unroll
+        for (int f = 0; f < kMaxFeet; ++f)
+            if (f < nf) asm volatile("" : "+f"(cf[f][0]), "+f"(cf[f][1]), "+f"(cf[f][2]), "+f"(air[f]));
+        if (MODE == 0) {
+            prog = do_reset ? 0 : prog + 1;                                         // :488
+            // the episode return is only needed at the very end: its load rides under the row math
+            if (valid && a == 0 && p.ep_return) ret_old = p.ep_return[n];
+            // :351-352, this warp's share of the batch-global gripper counts (the two forces die here)
+            const unsigned m0 = __ballot_sync(0xffffffffu, valid && gx0 > 0.1f), m1 = __ballot_sync(0xffffffffu, valid && gx1 > 0.1f);
+            if (lane < 4) {                             // lane = agent * 2 + gripper; agent a sits in the lanes of parity a
+                const unsigned m = ((lane & 1) ? m1 : m0) & ((lane >> 1) ? 0xaaaaaaaau : 0x55555555u);
+                if (m) atomicAdd(p.grip_counts + lane, static_cast<unsigned long long>(__popc(m)));
+            }
+        }
+    }
 
     float my_rew = 0.f, my_dist = 0.f;
     int my_flag = 0;                        // bit 0: up_proj < 0.90, bit 1: distance to the table > 0.40
@@ -265,7 +333,7 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
             }
             const V3 lin = quat_rotate_ref<-1>(q, V3{r[7], r[8], r[9]});            // :692
             const V3 g = quat_rotate_ref<1>(q, V3{p.gravity[0], p.gravity[1], p.gravity[2]});   // :694
-            float4* o = reinterpret_cast<float4*>(p.obs + (static_cast<size_t>(n) * kA + a) * kObs);   // 352-byte rows, 16-byte aligned
+            float* o = p.obs + (static_cast<size_t>(n) * kA + a) * kObs;            // 352-byte rows = 11 sectors
             float v[kObs];
             v[0] = lin.x * p.lin_vel_scale; v[1] = lin.y * p.lin_vel_scale; v[2] = lin.z * p.lin_vel_scale;
             v[3] = ang_raw.x * p.ang_vel_scale; v[4] = ang_raw.y * p.ang_vel_scale; v[5] = ang_raw.z * p.ang_vel_scale;
@@ -273,11 +341,12 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
 #pragma unroll
             for (int c = 0; c < 10; ++c) v[75 + c] = tb[c];                         // object pose + linvel
             v[85] = p.targets[0]; v[86] = p.targets[1]; v[87] = p.targets[2];
-            // Every 128-bit piece of the row is stored as soon as its four columns exist (obs_piece_ready: the j at which
-            // the last of them is produced), not after the whole row: the row never sits in 88 registers.
+            // Every 32-byte piece of the row is stored as soon as its eight columns exist (obs_piece_ready: the j at which
+            // the last of them is produced), not after the whole row: the row never sits in 88 registers.  One 256-bit
+            // store per piece: a lane's row costs the L1 11 sector writes, not 22 half-sector ones.
 #pragma unroll
-            for (int c = 0; c < kObs / 4; ++c)
-                if (obs_piece_ready(c) < 0) __stcs(o + c, make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]));
+            for (int c = 0; c < kObs / 8; ++c)
+                if (obs_piece_ready(c) < 0) store_obs_piece(o, c, v, p.obs32);
 #pragma unroll
             for (int jj = 0; jj < kDof / 2; ++jj) {
                 float4 d = dof4[jj];
@@ -290,9 +359,8 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
                 v[53 + 2 * jj] = ac.x;
                 v[54 + 2 * jj] = ac.y;
 #pragma unroll
-                for (int c = 0; c < kObs / 4; ++c)
-                    if (obs_piece_ready(c) >= 0 && (obs_piece_ready(c) >> 1) == jj)
-                        __stcs(o + c, make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]));
+                for (int c = 0; c < kObs / 8; ++c)
+                    if (obs_piece_ready(c) >= 0 && (obs_piece_ready(c) >> 1) == jj) store_obs_piece(o, c, v, p.obs32);
             }
         } else {                                                                    // compute_reward :360-409, this agent
             bool zero_last = false;
@@ -328,21 +396,31 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
             const bool moving = norm2_ref(cmd[0], cmd[1]) > 0.1f, still = norm2_ref(cmd[0], cmd[1]) < 0.1f;
             // _reward_air_time :319-329, _reward_feet_contact_forces :331-334, _reward_no_fly :336-340
             float air_sum = 0.0f, step_sum = 0.0f;
+            unsigned lc_new = 0;
             int touching = 0;
 #pragma unroll
             for (int f = 0; f < kMaxFeet; ++f) {
                 if (f < nf) {
                     const bool contact = cf[f][2] > 1.1f;
-                    const bool filt = contact || lastc[f];
+                    const bool filt = contact || (feet_vec ? ((lc_raw >> (8 * (f & 3))) & 0xffu) : ((lc_raw >> f) & 1u)) != 0;
                     const bool first = (air[f] > 0.0f) && filt;
                     const float t = air[f] + p.dt;
                     air_sum += (t - 0.5f) * (first ? 1.0f : 0.0f);
                     const float t2 = t * (filt ? 0.0f : 1.0f);
-                    p.air_time[(n * kA + a) * nf + f] = t2;
-                    p.last_contacts[(n * kA + a) * nf + f] = contact ? 1 : 0;
+                    if (feet_vec) {
+                        air[f] = t2;
+                        lc_new |= (contact ? 1u : 0u) << (8 * (f & 3));
+                    } else {
+                        p.air_time[(n * kA + a) * nf + f] = t2;
+                        p.last_contacts[(n * kA + a) * nf + f] = contact ? 1 : 0;
+                    }
                     step_sum += fmaxf(norm3_ref(V3{cf[f][0], cf[f][1], cf[f][2]}) - 450.0f, 0.0f);
                     touching += cf[f][2] > 0.1f ? 1 : 0;
                 }
+            }
+            if (feet_vec) {
+                *reinterpret_cast<float4*>(p.air_time + (n * kA + a) * 4) = make_float4(air[0], air[1], air[2], air[3]);
+                *reinterpret_cast<unsigned*>(p.last_contacts + (n * kA + a) * 4) = lc_new;
             }
             const float rew_airtime = (air_sum * (moving ? 1.0f : 0.0f)) * p.k_air;
             const float rew_no_fly = (touching == 1 ? 1.0f : 0.0f) * p.k_nofly;
@@ -396,14 +474,8 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
             my_flag = (up_proj < 0.90f ? 1 : 0) | (my_dist > 0.40f ? 2 : 0);        // :654-655
         }
     }
+    TK_OSTAMP(4);
     if (role_rew) {                                     // warp-uniform: whole warps of reward lanes from here on
-        if (MODE == 0) {                                                            // :351-352, this warp's share
-            const unsigned m0 = __ballot_sync(0xffffffffu, valid && gx0 > 0.1f), m1 = __ballot_sync(0xffffffffu, valid && gx1 > 0.1f);
-            if (lane < 4) {                             // lane = agent * 2 + gripper; agent a sits in the lanes of parity a
-                const unsigned m = ((lane & 1) ? m1 : m0) & ((lane >> 1) ? 0xaaaaaaaau : 0x55555555u);
-                if (m) atomicAdd(p.grip_counts + lane, static_cast<unsigned long long>(__popc(m)));
-            }
-        }
         // the other agent of this env sits in the neighbouring lane
         const float rew1 = __shfl_xor_sync(0xffffffffu, my_rew, 1), dist1 = __shfl_xor_sync(0xffffffffu, my_dist, 1);
         const int flag1 = __shfl_xor_sync(0xffffffffu, my_flag, 1);
@@ -456,13 +528,14 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
                 st_d0 += __shfl_xor_sync(0xffffffffu, st_d0, o);
                 st_d1 += __shfl_xor_sync(0xffffffffu, st_d1, o);
             }
-            const int warp_envs = min(max(nt - ((row >> 5) * (kTile / 2)), 0), kTile / 2);
+            const int warp_envs = min(max(nt - (row >> 5) * 16, 0), 16);      // a warp = 16 envs x 2 agents
             double* pr = p.partials + static_cast<size_t>(blockIdx.x & (kStatSlots - 1)) * TK_STATS;
             const float vals[TK_STATS] = {st_rew, static_cast<float>(__popc(m_reset)), static_cast<float>(__popc(m_to)), st_ret,
                                           st_len, st_d0, st_d1, static_cast<float>(warp_envs)};
             if (lane < TK_STATS) atomicAdd(pr + lane, static_cast<double>(vals[lane]));
         }
     }
+    TK_OSTAMP(5);
     // ---- prev_torques / last_actions are refreshed from the torque / action tiles that are resident (TMA wrote them; no
     //      thread modifies them), by the thread that issued the loads ----
     if (bulk) {
@@ -479,6 +552,8 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
                 p.last_actions[e0 * kA * kDof + i] = s.act[i];
             }
     }
+    TK_OSTAMP(6);
+#undef TK_OSTAMP
 }
 
 // un-stubbed pre_physics_step (anymal.py:229-232 + clamp vec_task.py:327): flat stream over N*2*22 floats
@@ -624,6 +699,7 @@ struct TkOp3 {
     double* partials;
     unsigned long long* step_dev;
     float* pre_rew;
+    long long* dbg_ts;
 };
 
 static void fill_kparams(const TkOp3* h, KParams& k) {
@@ -637,6 +713,7 @@ static void fill_kparams(const TkOp3* h, KParams& k) {
     k.reset = reinterpret_cast<long long*>(B.reset_buf); k.progress = reinterpret_cast<long long*>(B.progress_buf);
     k.timeout = B.timeout_buf; k.ep_return = B.episode_return; k.partials = h->partials;
     k.grip_counts = reinterpret_cast<unsigned long long*>(B.grip_counts); k.pre_rew = h->pre_rew;
+    k.dbg_ts = h->dbg_ts;
     k.unit_cmd = nullptr; k.seed = 0; k.step = 0; k.step_dev = h->step_dev; k.env_off = 0; k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs; k.nb = P.num_bodies_total; k.max_episode_length = P.max_episode_length; k.num_feet = P.num_feet;
     for (int a = 0; a < kA; ++a) {
@@ -646,6 +723,10 @@ static void fill_kparams(const TkOp3* h, KParams& k) {
     k.vec_ok = aligned_to(B.root_states, 16) && aligned_to(B.dof_state, 16) && aligned_to(B.torques, 16) &&
                aligned_to(B.prev_torques, 16) && aligned_to(B.actions, 16) && aligned_to(B.last_actions, 16) &&
                aligned_to(B.obs_buf, 16);
+    k.obs32 = aligned_to(B.obs_buf, 32);
+    k.vec_feet = aligned_to(B.feet_air_time, 16) && aligned_to(B.last_contacts, 4);
+    k.contact8 = aligned_to(B.contact_forces, 8);
+    k.contact_tile = aligned_to(B.contact_forces, 16) && static_cast<long long>(kTile) * P.num_bodies_total * 12 <= kMaxContactTileBytes;
     k.lin_vel_scale = P.lin_vel_scale; k.ang_vel_scale = P.ang_vel_scale; k.dof_pos_scale = P.dof_pos_scale;
     k.dof_vel_scale = P.dof_vel_scale; k.action_scale = P.action_scale; k.clip_actions = P.clip_actions;
     k.dt = static_cast<float>(P.dt);
@@ -672,16 +753,19 @@ static int check_bound(const TkOp3* h) {
 
 template <int MODE, int NF>
 static cudaError_t launch_tile_nf(const TkOp3* h, const KParams& k, cudaStream_t st) {
-    static bool opted = false;
-    static int pad = 0;      // TK_OP3_SMEM_PAD (developer knob): extra dynamic shared memory per CTA = fewer resident CTAs per SM
-    if (!opted) {
-        if (const char* env = getenv("TK_OP3_SMEM_PAD")) pad = atoi(env);
-        cudaError_t e = cudaFuncSetAttribute(op3_tile_kernel<MODE, NF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             static_cast<int>(sizeof(Smem)) + pad);
-        if (e != cudaSuccess) return e;
-        opted = true;
+    static int opted = 0;    // dynamic shared memory this instantiation has been opted in for
+    static int pad = -1;     // TK_OP3_SMEM_PAD (developer knob): extra dynamic shared memory per CTA = fewer resident CTAs per SM
+    if (pad < 0) {
+        const char* env = getenv("TK_OP3_SMEM_PAD");
+        pad = env ? atoi(env) : 0;
     }
-    op3_tile_kernel<MODE, NF><<<h->tiles, threads_of<MODE>(), sizeof(Smem) + pad, st>>>(k);
+    const int bytes = static_cast<int>(sizeof(Smem)) + pad + ((MODE != 1 && k.contact_tile) ? kTile * k.nb * 12 : 0);
+    if (bytes > opted) {
+        cudaError_t e = cudaFuncSetAttribute(op3_tile_kernel<MODE, NF>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e != cudaSuccess) return e;
+        opted = bytes;
+    }
+    op3_tile_kernel<MODE, NF><<<h->tiles, threads_of<MODE>(), bytes, st>>>(k);
     return cudaGetLastError();
 }
 
@@ -730,7 +814,7 @@ int tk_ma_op3_create(const TkOp3Params* params, TkOp3** out) {
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->sm_count = 148;
     cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, params->device);
-    h->partials = nullptr; h->step_dev = nullptr; h->pre_rew = nullptr;
+    h->partials = nullptr; h->step_dev = nullptr; h->pre_rew = nullptr; h->dbg_ts = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMalloc(&h->step_dev, sizeof(unsigned long long));
@@ -860,6 +944,13 @@ int tk_ma_op3_finalize_reward(TkOp3* h, void* stream) {
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     TK_CUDA(cudaLaunchKernelEx(&cfg, op3_finalize_kernel, k));
+    return TK_OK;
+}
+
+// developer probe, not part of the public header: per-warp globaltimer stamps [tiles, 4, 8] (tools/op3_timeline.py)
+int tk_debug_ma_op3_timeline(TkOp3* h, long long* device_buffer) {
+    TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
+    h->dbg_ts = device_buffer;
     return TK_OK;
 }
 
