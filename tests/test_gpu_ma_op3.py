@@ -228,3 +228,35 @@ def test_runtime_foot_count(feet):
     _check_obs_side(env, orc, "nf")
     _check_reward_side(env, orc, "nf")
     U.exact(env.progress_buf, orc.progress_buf, "progress_buf")
+
+
+def _shifted(t, elems):
+    """The same data at an address `elems` elements past a 512-byte aligned allocation."""
+    buf = torch.empty(t.numel() + 64, dtype=t.dtype, device=t.device)
+    v = buf[elems:elems + t.numel()].view(t.shape)
+    v.copy_(t)
+    return v
+
+
+@pytest.mark.parametrize("shift", [
+    {"obs_buf": 4, "contact_forces": 2, "feet_air_time": 1},        # 16-byte obs rows, 8-byte contact rows, scalar feet path
+    {"contact_forces": 1, "last_contacts": 1},                       # 4-byte contact rows
+    {"root_states": 1, "torques": 2, "contact_forces": 4},          # no bulk tile copies at all; contact block still 16-byte aligned
+], ids=["obs16_contact8_feet4", "contact4_lastc1", "no_bulk"])
+def test_alignment_fallbacks(shift):
+    """Every vector / bulk-copy path has a fallback chosen from the bound addresses: same results from shifted buffers."""
+    n = 1000 + 7
+    env, orc, st = U.make_ma_op3_pair(n, seed=71)
+    for name, k in shift.items():
+        setattr(env, name, _shifted(getattr(env, name), k))
+    env.rebind()
+    uc = syn.ma_op3_reset_noise(n, seed=9)
+    for step in range(2):
+        ids = orc.reset_buf.nonzero(as_tuple=False).squeeze(-1)
+        env.post_physics_step(uc.to(DEV))
+        orc.post_physics_step(uc[ids])
+        torch.cuda.synchronize()
+        _check_obs_side(env, orc, f"shifted step {step}")
+        _check_reward_side(env, orc, f"shifted step {step}")
+        U.exact(env.progress_buf, orc.progress_buf, "progress_buf")
+        U.exact(env.feet_air_time, orc.feet_air_time, "feet_air_time")

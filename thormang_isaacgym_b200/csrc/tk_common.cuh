@@ -60,6 +60,14 @@ __device__ __forceinline__ void stg_stream8(float* p, const float* v) {
     asm volatile("st.global.cs.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
                  "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
 }
+// 128-bit shared load the compiler may not narrow: a lane that uses two of the four words would otherwise get two 32-bit
+// loads, and rows that are conflict-free as 128-bit accesses (odd multiples of 16 bytes apart) are 4-way conflicted as words
+__device__ __forceinline__ float4 lds128(const float4* p) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(p))));
+    return v;
+}
 // A 12-byte row at a 4-byte aligned address as one 64-bit and one 32-bit load (two requests instead of three)
 __device__ __forceinline__ void ldg_row3(const float* row, float& x, float& y, float& z) {
     if ((reinterpret_cast<uintptr_t>(row) & 4u) == 0) {

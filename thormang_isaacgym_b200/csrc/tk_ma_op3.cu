@@ -349,7 +349,7 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
                 if (obs_piece_ready(c) < 0) store_obs_piece(o, c, v, p.obs32);
 #pragma unroll
             for (int jj = 0; jj < kDof / 2; ++jj) {
-                float4 d = dof4[jj];
+                float4 d = lds128(dof4 + jj);
                 const float2 ac = act2[jj];
                 if (rst) d = make_float4(p.default_dof_pos[2 * jj] + 0.0f, 0.0f, p.default_dof_pos[2 * jj + 1] + 0.0f, 0.0f);   // :456-457
                 v[9 + 2 * jj] = (d.x - p.default_dof_pos[2 * jj]) * p.dof_pos_scale;                // :695
@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
             float tsum = 0.0f, legsum = 0.0f, ratesum = 0.0f, standsum = 0.0f;
 #pragma unroll
             for (int jj = 0; jj < kDof / 2; ++jj) {
-                const float4 d = dof4[jj];
+                const float4 d = lds128(dof4 + jj);                                  // only the positions are used here
                 const float2 t = tq2[jj], pt = ptq2[jj], ac = act2[jj];
                 float2 l = la2[jj];
                 if (zero_last) l = make_float2(0.0f, 0.0f);
