@@ -310,6 +310,19 @@ int tk_gogoro_philox_noise(TkGogoro* h, uint64_t seed, uint64_t step, int64_t en
  *   command_ring [N,20]    = channel 6 of the clean frames (the reward's act_buff, :509), same ring.
  * ------------------------------------------------------------------------------------------ */
 
+/* The sibling file isaacgymenvs/tasks/gogoro_realistic_turning.py (same class name, buffers and step skeleton; saved with
+ * DEBUG = False) is served by the same entry points with variant = TK_GOGORO_PAPER_VARIANT_TURNING:
+ *   pre_physics_step :345-383  steering target = delayed command + steer_offsets (:365);
+ *   compute_obs_rwd  :480-547  no command-change correction of the newest noisy frame;
+ *   compute_gogoro_reward :713-765  3/(1+200 yaw^2) + 1/(1+100 tilt^2) + 10 * 1 + 2/(1+100 dtilt^2) + 10 (1 - |mean(act_buff)|),
+ *                    the mean taken over every env and all 20 frames (tk_gogoro_paper_diff_sums then returns
+ *                    {sum of the command ring, N * 20});
+ *   generate_spawn_r :572-588, reset_idx :601-686  random spawn yaw / roll / yaw target: reset_unit has 8 columns,
+ *                    5 = yaw target (:573), 6 = yaw offset (:574), 7 = roll (:575).
+ * Set use_steer_delay = 1 for the file as saved (USE_STEER_DELAY = not DEBUG, :31). */
+#define TK_GOGORO_PAPER_VARIANT_PAPER 0
+#define TK_GOGORO_PAPER_VARIANT_TURNING 1
+
 typedef struct TkGogoroPaperParams {
     int32_t device;
     int32_t num_envs;
@@ -322,7 +335,7 @@ typedef struct TkGogoroPaperParams {
     int32_t buff_size;               /* 20, :112 */
     int32_t delay_width;             /* command_delay[1]: width of command_history, :93 (3..8) */
     int32_t use_steer_delay;         /* USE_STEER_DELAY, :31: per-env tap -steer_delay (:355) instead of the fixed -3 (:357) */
-    int32_t reserved;
+    int32_t variant;                 /* TK_GOGORO_PAPER_VARIANT_PAPER (0) | TK_GOGORO_PAPER_VARIANT_TURNING */
     float max_steering;              /* 0.5, :86 */
     float start_speed;               /* 1.3 with DEBUG_START_SPEED (:26,638-641), 0 = off */
     /* [lo,hi] pairs of cfg["noises"], :55-80; double for the same reason as in TkGogoroParams */

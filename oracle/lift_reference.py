@@ -53,6 +53,11 @@ LIFT_TABLE: Dict[str, Iterable[str]] = {
         "shortest_angle_distance",        # :765-767
         "compute_gogoro_observations",    # :770-807
     ),
+    "isaacgymenvs/tasks/gogoro_realistic_turning.py": (             # SURVEY 8(f) N1, the rational-reward sibling
+        "compute_gogoro_reward",          # :713-765
+        "shortest_angle_distance",        # :768-770
+        "compute_gogoro_observations",    # :773-810
+    ),
 }
 
 _PRELUDE = (
@@ -132,6 +137,10 @@ def gogoro() -> ModuleType:
 
 def gogoro_paper() -> ModuleType:
     return lift("isaacgymenvs/tasks/gogoro_realistic_turning_sim_paper.py")
+
+
+def gogoro_turning() -> ModuleType:
+    return lift("isaacgymenvs/tasks/gogoro_realistic_turning.py")
 
 
 def anymal() -> ModuleType:

@@ -2,7 +2,7 @@
 
     python tests/golden/make_golden.py
 
-* ``humanoid_jit.npz`` / ``gogoro_jit.npz`` / ``ant_jit.npz`` / ``gogoro_paper_jit.npz``: inputs and outputs of the reference's own
+* ``humanoid_jit.npz`` / ``gogoro_jit.npz`` / ``ant_jit.npz`` / ``gogoro_paper_jit.npz`` / ``gogoro_turning_jit.npz``: inputs and outputs of the reference's own
   ``@torch.jit.script`` functions, lifted by source from /root/reference
   (oracle/lift_reference.py), on seeded synthetic states + hand-built edge rows.
 * ``poselib_quat.npz``: outputs of the reference's in-tree quaternion library
@@ -222,6 +222,42 @@ def gogoro_paper_golden(n_rand=96):
     print("gogoro_paper_jit.npz", n, "rows; resets", int(reset.sum()), "reward range", float(rew.min()), float(rew.max()))
 
 
+def gogoro_turning_golden(n_rand=96):
+    """gogoro_realistic_turning.py JIT functions (SURVEY 8(f) N1 sibling): same observation function as the paper file,
+    the rational reward with the all-env ``mean(act_buff)`` term over [N,20,8]."""
+    ref = L.gogoro_turning()
+    st = syn.gogoro_paper_state(n_rand, seed=5245)
+    root = st["root_tensor"]
+    base = root[0].clone()
+    edge = []
+    for roll in (0.3799, 0.3801, -0.3801, 0.0):
+        r = base.clone(); r[3:7] = _euler_q(roll, 0.0, -0.7); edge.append(r)         # around max_tilt = 0.38
+    for yaw in (math.pi - 1e-4, -math.pi + 1e-4, 0.0, -1e-4):
+        r = base.clone(); r[3:7] = _euler_q(-0.05, 0.02, yaw); edge.append(r)        # yaw wrap
+    for wx in (0.999, 1.001, -1.5):                                                  # dtilt clamp at +-1 (:728-729)
+        r = base.clone(); r[3:7] = _euler_q(0.0, 0.0, 0.0); r[10:13] = torch.tensor([wx, 0.0, 0.1]); edge.append(r)
+    edge = torch.stack(edge)
+    ne = edge.shape[0]
+    n = n_rand + ne
+    root = torch.cat([root, edge])
+    desired = torch.cat([st["yaw_command"], torch.tensor([0.5, 0.5, 0.5, 0.5, -math.pi + 1e-4, math.pi - 1e-4,
+                                                           math.pi, 3.0, 0.3, 0.3, 0.0])[:ne]])
+    cmd = torch.cat([st["curent_command"], torch.tensor([0.5, -0.5, 0.0, 0.25, 0.1, 0.2, 0.3, 0.4, -0.1, -0.2, 0.0])[:ne]])
+    delay = torch.cat([st["steer_delay"], torch.tensor([0, 1, 2, 3, 4, 0, 1, 2, 3, 4, 0])[:ne]])
+    progress = torch.cat([st["progress_buf"], torch.tensor([3597, 3598, 3599, 3600, 0, 299, 300, 301, 3598, 3599, 7])[:ne]])
+    obs = ref.compute_gogoro_observations(root.clone(), desired.clone(), cmd.clone(), (delay.clone() - 0) / (5 - 0))
+    ext = syn.gogoro_paper_state(ne, seed=98)
+    frames = torch.cat([st["buffer_obs"], ext["buffer_obs"]])
+    frames[:, :, 6] += 0.07                                                          # a command mean away from zero
+    frames = torch.cat([frames[:, 1:], obs.unsqueeze(1)], dim=1)                     # the push of :495-496
+    rew, reset = ref.compute_gogoro_reward(act_buff=frames[:, :, 6], curent_obs=frames, progress_buf=progress,
+                                           max_episode_length=torch.tensor(3600), yaw_update_freq=torch.tensor(300))
+    np.savez_compressed(os.path.join(HERE, "gogoro_turning_jit.npz"), **_np(dict(
+        root_tensor=root, desired_yaw=desired, curent_command=cmd, steer_delay=delay, progress_buf=progress,
+        frames=frames, obs=obs, rew=rew, reset=reset, n_rand=n_rand)))
+    print("gogoro_turning_jit.npz", n, "rows; resets", int(reset.sum()), "reward range", float(rew.min()), float(rew.max()))
+
+
 def anymal_golden(n_rand=96):
     """anymal.py JIT functions: observations [N,61], reward / reset incl. contact norms around 1 N."""
     from oracle import anymal_oracle as ao
@@ -305,6 +341,7 @@ if __name__ == "__main__":
     gogoro_golden()
     ant_golden()
     gogoro_paper_golden()
+    gogoro_turning_golden()
     anymal_golden()
     ma_op3_golden()
     poselib_golden()

@@ -201,11 +201,17 @@ def gogoro_paper_frame_close(got, want, what="frame", noisy=False):
                     bound=None)      # noise + offsets added after the wrap (:525-538): open range
 
 
-def make_gogoro_paper_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
-    """(cuda task, cpu oracle, state) of the 8x20 Gogoro variant from one synthetic snapshot."""
+def make_gogoro_paper_pair(n, seed=1234, device="cuda:0", state=None, turning=False, **env_over):
+    """(cuda task, cpu oracle, state) of the 8x20 Gogoro variant from one synthetic snapshot (SURVEY 8f N1);
+    ``turning``: the gogoro_realistic_turning.py sibling (task ``GogoroTurning``, oracle ``GogoroTurningOracle``)."""
     from oracle import gogoro_paper_oracle as gp
     from thormang_isaacgym_b200.sim.fake_sim import FakeSim
-    from thormang_isaacgym_b200.tasks.gogoro_realistic_turning_sim_paper import Gogoro as GogoroPaper
+    if turning:
+        from oracle import gogoro_turning_oracle as gt
+        from thormang_isaacgym_b200.tasks.gogoro_realistic_turning import Gogoro as GogoroPaper
+        env_over.setdefault("useSteerDelay", True)
+    else:
+        from thormang_isaacgym_b200.tasks.gogoro_realistic_turning_sim_paper import Gogoro as GogoroPaper
     state = state or syn.gogoro_paper_state(n, seed=seed)
     cfg = tcfg.gogoro_paper_cfg(n, seed=seed)
     cfg["env"].update(env_over)
@@ -216,7 +222,8 @@ def make_gogoro_paper_pair(n, seed=1234, device="cuda:0", state=None, **env_over
     cfg["sim_backend"] = sim
     env = GogoroPaper(cfg, device, device, -1, True)
     consts = gp.GogoroPaperConsts.from_cfg(cfg, steering_joint=0, rear_wheel_joint=1)
-    orc = gp.GogoroPaperOracle(consts, state["root_tensor"].clone(), state["state_dof"].clone(), state["thormang_pose"].clone())
+    orc_cls = gt.GogoroTurningOracle if turning else gp.GogoroPaperOracle
+    orc = orc_cls(consts, state["root_tensor"].clone(), state["state_dof"].clone(), state["thormang_pose"].clone())
     for name in ("yaw_command", "curent_command", "curent_speed", "steer_offsets", "curent_speed_offset",
                  "curent_imu_x_offset", "steer_delay", "command_history", "progress_buf", "reset_buf", "thormang_pose"):
         getattr(env, name).copy_(state[name].to(device))

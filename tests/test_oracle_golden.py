@@ -206,6 +206,60 @@ def test_gogoro_paper_oracle_step_semantics():
     assert torch.equal(orc.curent_speed[5], want_speed)
 
 
+def test_gogoro_turning_golden(golden_dir):
+    """gogoro_realistic_turning.py (the rational-reward sibling of the paper file) against its own JIT functions."""
+    from oracle import gogoro_turning_oracle as gt
+    g = _load(golden_dir, "gogoro_turning_jit.npz")
+    obs = gt.paper_observations(g["root_tensor"].clone(), g["desired_yaw"].clone(), g["curent_command"].clone(),
+                                (g["steer_delay"].clone() - 0) / (5 - 0))
+    lin = [2, 3, 4, 6, 7]
+    torch.testing.assert_close(obs[:, lin], g["obs"][:, lin], rtol=RTOL, atol=ATOL)
+    assert _wrap_close(obs[:, [0, 1, 5]], g["obs"][:, [0, 1, 5]], 4e-6)
+    rew, reset = gt.turning_reward(g["frames"][:, :, 6], g["frames"], g["progress_buf"], 3600)
+    assert torch.equal(reset, g["reset"]) and reset.dtype == torch.int64
+    torch.testing.assert_close(rew, g["rew"], rtol=RTOL, atol=ATOL)
+    mean_term = 10.0 * (1.0 - abs(float(g["frames"][:, :, 6].mean())))
+    assert 9.0 < mean_term < 9.5, "fixture must put the all-env command mean away from zero"
+    assert float(rew.min()) == -1.0 and float(rew[rew >= 0].min()) >= 10.0 + mean_term - 1e-4      # reward3 == 1 always
+    assert float(rew.max()) <= 3.0 + 1.0 + 10.0 + 2.0 + mean_term + 1e-4
+
+
+def test_gogoro_turning_oracle_step_semantics():
+    """What the sibling file changes: steering target + offsets on the per-env tap, random spawn, no correction terms."""
+    from oracle import gogoro_turning_oracle as gt
+    from thormang_isaacgym_b200 import synthetic as syn
+    n = 64
+    st = syn.gogoro_paper_state(n, seed=6)
+    orc = gt.GogoroTurningOracle(gt.turning_consts(), st["root_tensor"].clone(), st["state_dof"].clone(),
+                                 st["thormang_pose"].clone())
+    for name in ("yaw_command", "curent_command", "curent_speed", "steer_offsets", "curent_speed_offset",
+                 "curent_imu_x_offset", "steer_delay", "command_history", "progress_buf", "reset_buf"):
+        setattr(orc, name, st[name].clone())
+    orc.buffer_obs, orc.buffer_obs_noisy = st["buffer_obs"].clone(), st["buffer_obs_noisy"].clone()
+    orc.reset_buf[:] = 0
+    orc.reset_buf[[3, 17]] = 1
+    orc.progress_buf[:] = 10
+    nz = syn.gogoro_paper_noise(n, seed=1, reset_cols=gt.RESET_NOISE_COLS)
+    orc.pre_physics_step(st["actions"])
+    tap = orc.command_history[torch.arange(n), -orc.steer_delay]
+    assert torch.equal(orc.dof_pos_command[:, 0], tap + orc.steer_offsets)            # :360, :365
+    ids, _, _ = orc.post_physics_step(nz["sensor_unit"], nz["reset_unit"][[3, 17]], nz["speed_unit"][:0], nz["yaw_unit"])
+    assert ids.tolist() == [3, 17]
+    u = nz["reset_unit"][[3, 17]]
+    tgt = (u[:, 5] * 2 - 1) * np.pi
+    assert torch.equal(orc.yaw_command[[3, 17]], tgt)                                 # :573, :683 (|tgt| <= pi: no wrap)
+    q = orc.root_tensor[[3, 17], 3:7]
+    torch.testing.assert_close(q.norm(dim=-1), torch.ones(2), rtol=1e-6, atol=1e-6)
+    rot = tgt + (-np.pi + u[:, 6] * (2 * np.pi))
+    torch.testing.assert_close(orc.root_tensor[[3, 17], 7], 1.3 * torch.cos(rot), rtol=1e-6, atol=1e-6)
+    nzy = orc.buffer_obs_noisy
+    assert float(nzy[[3, 17], :-1].abs().max()) == 0.0 and float(nzy[:, :, 1].abs().max()) == 0.0
+    # no command-change correction (the paper file's :541-542): channel 2 of the fresh noisy frame = (d_roll + noise) / 3
+    keep = [i for i in range(n) if i not in (3, 17)]
+    want2 = (orc.buffer_obs[keep, -1, 2] + (-0.003 + nz["sensor_unit"][keep, 2] * 0.006)) / 3.0
+    torch.testing.assert_close(nzy[keep, -1, 2], want2, rtol=1e-6, atol=1e-7)
+
+
 def test_anymal_golden(golden_dir):
     """Anymal against anymal.py's own JIT functions; contact norms exactly at / 1 ulp around 1 N."""
     from oracle import anymal_oracle as ao

@@ -106,6 +106,27 @@ def test_gogoro_paper_bit_exact(n):
 
 
 @pytest.mark.parametrize("n", [1, 33, 4096])
+def test_gogoro_turning_bit_exact(n):
+    """SURVEY 8(f) N1 sibling: gogoro_realistic_turning.py:713-810 (rational reward, all-env mean of the command history)."""
+    from oracle import gogoro_turning_oracle as gt
+    ref = L.gogoro_turning()
+    st = syn.gogoro_paper_state(n, seed=277 + n)
+    delay = (st["steer_delay"].clone() - 0) / (5 - 0)
+    want = ref.compute_gogoro_observations(st["root_tensor"].clone(), st["yaw_command"].clone(),
+                                           st["curent_command"].clone(), delay.clone())
+    got = gt.paper_observations(st["root_tensor"].clone(), st["yaw_command"].clone(), st["curent_command"].clone(), delay)
+    assert torch.equal(want, got)
+    frames = torch.cat([st["buffer_obs"][:, 1:], want.unsqueeze(1)], dim=1)
+    frames[:, :, 6] += 0.05
+    rw = ref.compute_gogoro_reward(act_buff=frames[:, :, 6], curent_obs=frames, progress_buf=st["progress_buf"],
+                                   max_episode_length=torch.tensor(3600), yaw_update_freq=torch.tensor(300))
+    rg = gt.turning_reward(frames[:, :, 6], frames, st["progress_buf"], 3600)
+    assert torch.equal(rw[0], rg[0]) and torch.equal(rw[1], rg[1])
+    a, b = syn._u(syn._gen(5), (256,), -7.0, 7.0), syn._u(syn._gen(6), (256,), -7.0, 7.0)
+    assert torch.equal(ref.shortest_angle_distance(a, b), gt.shortest_angle_distance(a, b))
+
+
+@pytest.mark.parametrize("n", [1, 33, 4096])
 def test_anymal_bit_exact(n):
     """anymal.py:323-431."""
     from oracle import anymal_oracle as ao

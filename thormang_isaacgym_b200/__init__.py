@@ -23,10 +23,8 @@ def make(seed: int, task: str, num_envs: int, sim_device: str = "cuda:0", rl_dev
     ``seed`` so that results do not depend on the number of ranks."""
     from .tasks import isaacgym_task_map
     makers = {"Humanoid": config.humanoid_cfg, "Gogoro": config.gogoro_cfg, "Ant": config.ant_cfg,
-              "GogoroPaper": config.gogoro_paper_cfg, "Anymal": config.anymal_cfg, "MA_OP3": config.ma_op3_cfg}
-    for extra in ("gogoro_turning_cfg",):
-        if hasattr(config, extra):
-            makers["GogoroTurning"] = getattr(config, extra)
+              "GogoroPaper": config.gogoro_paper_cfg, "GogoroTurning": config.gogoro_turning_cfg,
+              "Anymal": config.anymal_cfg, "MA_OP3": config.ma_op3_cfg}
     if cfg is None:
         cfg = makers[task](num_envs, seed)
     else:

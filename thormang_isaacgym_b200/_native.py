@@ -68,12 +68,15 @@ class GogoroNoise(C.Structure):
     _fields_ = [("reset", ResetNoise), ("sensor_unit", _p), ("speed_unit", _p), ("yaw_unit", _p)]
 
 
+GOGORO_PAPER_VARIANT_PAPER, GOGORO_PAPER_VARIANT_TURNING = 0, 1
+
+
 class GogoroPaperParams(C.Structure):
     _fields_ = [
         ("device", _i32), ("num_envs", _i32), ("num_dof", _i32), ("steering_joint", _i32),
         ("rear_wheel_joint", _i32), ("max_episode_length", _i32), ("speed_freq_update", _i32),
         ("yaw_freq_update", _i32), ("buff_size", _i32), ("delay_width", _i32), ("use_steer_delay", _i32),
-        ("reserved", _i32), ("max_steering", _f), ("start_speed", _f),
+        ("variant", _i32), ("max_steering", _f), ("start_speed", _f),
         ("imu_filter_noise", _d * 2), ("imu_noise", _d * 2), ("speed_sensor_noise", _d * 2),
         ("speed_sensor_offset", _d * 2), ("imu_x_offset", _d * 2), ("steering_offset", _d * 2),
         ("command_delay", _d * 2), ("speed_range", _d * 2),

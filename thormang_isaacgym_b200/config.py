@@ -95,6 +95,12 @@ def gogoro_paper_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
     })
 
 
+def gogoro_turning_cfg(num_envs: int = 4096, seed: int = 0) -> dict:
+    """``tasks/gogoro_realistic_turning.py`` reads the same cfg keys as the paper file (:44-84) and has no yaml of its own:
+    cfg/task/Gogoro_paper.yaml values."""
+    return gogoro_paper_cfg(num_envs, seed)
+
+
 ANYMAL_DOF_NAMES = ["LF_HAA", "LF_HFE", "LF_KFE", "LH_HAA", "LH_HFE", "LH_KFE", "RF_HAA", "RF_HFE", "RF_KFE",
                     "RH_HAA", "RH_HFE", "RH_KFE"]      # DOF order of anymal_c/urdf/anymal.urdf
 

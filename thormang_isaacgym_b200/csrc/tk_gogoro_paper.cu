@@ -21,6 +21,13 @@
 // (paper_finalize_kernel, 24 B/env) folds the global mean in, clips, restores the fall penalty and bumps the tick.
 // In range-sharded multi-GPU runs the two sums are all-reduced between the two kernels (the one real exchange step of
 // this variant).
+//
+// TK_GOGORO_PAPER_VARIANT_TURNING selects the sibling file /root/reference/isaacgymenvs/tasks/gogoro_realistic_turning.py
+// (same class, same buffers; module flags DEBUG = False, hence USE_STEER_DELAY = True): steering target = delayed command +
+// steer_offsets (:365), random spawn yaw / roll / yaw target (:573-577), no command-change correction of the noisy frame
+// (the paper file's :540-542 are absent), and the rational reward of :713-765 whose cross-env term is
+// reward5 = 1 - |mean(act_buff)| (:742, a mean over every env and all 20 frames): the same two-kernel scheme with the sum
+// of the command ring in place of the squared differences.  reward3 (:738-741) compares min with min: identically 1.
 #include "tk_common.cuh"
 
 #include <cstdlib>
@@ -35,7 +42,9 @@ constexpr int kBuf = 20;
 constexpr int kObs = kCh * kBuf;       // 160
 constexpr int kChunks = kObs / 4;      // float4 chunks per obs row
 constexpr int kSensorNoise = 6;
-constexpr int kResetNoise = 5;
+constexpr int kResetNoise = 5;         // paper file: speed, delay, steer offset, speed-sensor offset, imu_x offset
+constexpr int kResetNoiseTurning = 8;  // + spawn yaw target (:573), spawn yaw offset (:574), spawn roll (:575)
+constexpr int kPaper = TK_GOGORO_PAPER_VARIANT_PAPER, kTurning = TK_GOGORO_PAPER_VARIANT_TURNING;
 constexpr int kMaxDelayW = 8;
 constexpr int kTile = 32;
 constexpr float kMaxTilt = 0.38f;      // :724
@@ -78,6 +87,7 @@ struct KParams {
     int noise_mode;
     int n, num_dof, steering_joint, rear_wheel_joint, max_episode_length, speed_freq, yaw_freq;
     int delay_w, use_delay;
+    int variant;                   // kPaper | kTurning
     int vec_ok;
     int stagger_cycles, stagger_ctas, sm_count;   // first-wave stagger, see paper_tile_kernel
     int fin_vec_ok;                // rew_buf / episode_return / reset_buf 16-byte aligned: 128-bit accesses in the finalize kernel
@@ -123,10 +133,26 @@ __device__ __forceinline__ float reward_partial(const float* o, bool* felt_out) 
     return reward1 * 0.45f + reward2 * 0.1f + reward4 * 0.35f + reward5 * 2.0f;     // :753 (first four terms, same order)
 }
 
+// gogoro_realistic_turning.py compute_gogoro_reward :713-765 without the reward5 term (added by paper_finalize_kernel)
+__device__ __forceinline__ float reward_partial_turning(const float* o, bool* felt_out) {
+    const float tilt = o[0], dtilt = o[2], yaw_e = o[5];
+    const float tilt_err = fminf(fmaxf(tilt / kMaxTilt, -1.0f), 1.0f);              // :722-723
+    const float yaw_err = fminf(fmaxf(yaw_e / kPi, -1.0f), 1.0f);                   // :725-726
+    const float dtilt_err = fminf(fmaxf(dtilt, -1.0f), 1.0f);                       // :728-729
+    const float reward1 = 1.0f / (1.0f + (yaw_err * yaw_err) * 200.0f);             // :734
+    const float reward2 = 1.0f / (1.0f + (tilt_err * tilt_err) * 100.0f);           // :735
+    const float reward4 = 1.0f / (1.0f + (dtilt_err * dtilt_err) * 100.0f);         // :736
+    const float reward3 = 1.0f / (1.0f + (0.0f * 0.0f) * 500.0f);                   // :738-741: min_ - "max_" (also a min) = 0
+    *felt_out = fabsf(tilt) >= kMaxTilt;                                            // :756
+    return ((reward1 * 3.0f + reward2 * 1.0f) + reward3 * 10.0f) + reward4 * 2.0f;  // :744 (first four terms, same order)
+}
+
 // randomize :557-566 + reset_idx :599-688 for env `ne`, executed by ONE thread (rare, divergent).  u = the 5 unit draws.
 // Writes the global state except obs_buf (the caller's shift phase writes the zero frames); returns the new root row.
+// VAR = kTurning: gogoro_realistic_turning.py randomize :559-568, generate_spawn_r :572-588, reset_idx :601-686 (u = 8 draws)
+template <int VAR>
 __device__ __forceinline__ void reset_env(const KParams& p, long long ne, const float* u, float* r, long long* delay_out,
-                                          float* imu_x_out, float* speed_off_out) {
+                                          float* imu_x_out, float* speed_off_out, float* yaw_tgt_out) {
     p.curent_speed[ne] = uniform_of(p.speed, u[0]);                                 // :562
     const long long delay = static_cast<long long>(uniform_of(p.delay, u[1]));      // :563 (.to(torch.long) truncates)
     p.steer_delay[ne] = delay;
@@ -138,10 +164,31 @@ __device__ __forceinline__ void reset_env(const KParams& p, long long ne, const 
 #pragma unroll
     for (int c = 0; c < kRoot; ++c) r[c] = p.root_reset[ne * kRoot + c];            // :618
     r[2] = 0.03f;                                                                   // :619
-    r[3] = 0.0f; r[4] = 0.0f; r[5] = 0.0f; r[6] = 1.0f;                             // :573-575,635: euler (0,0,0) -> identity, exactly
+    float yaw_tgt = 0.0f;                                                           // :571 (paper file)
 #pragma unroll
     for (int c = 7; c < kRoot; ++c) r[c] = 0.0f;                                    // :636
-    if (p.start_speed != 0.0f) { r[7] = p.start_speed * 1.0f; r[8] = p.start_speed * 0.0f; }   // :638-641, cos(0), sin(0)
+    if (VAR == kTurning) {
+        yaw_tgt = (u[5] * 2.0f - 1.0f) * kPi;                                       // :573
+        const float yaw_noise_pair[2] = {-kPi, kTwoPi};
+        const float initial_rot = yaw_tgt + uniform_of(yaw_noise_pair, u[6]);       // :574 get_randoms(n, [-pi, pi])
+        const float roll = (u[7] * 2.0f - 1.0f) * 0.1f;                             // :575
+        float sr, cr, sy, cy;
+        sincosf(roll / 2.0f, &sr, &cr);
+        sincosf(initial_rot / 2.0f, &sy, &cy);
+        const float sp = 0.0f, cp = 1.0f;                                           // pitch = 0
+        r[3] = sr * cp * cy - cr * sp * sy;                                         // :593-597
+        r[4] = cr * sp * cy + sr * cp * sy;
+        r[5] = cr * cp * sy - sr * sp * cy;
+        r[6] = cr * cp * cy + sr * sp * sy;
+        if (p.start_speed != 0.0f) {                                                // :636-639
+            float si, ci;
+            sincosf(initial_rot, &si, &ci);
+            r[7] = p.start_speed * ci; r[8] = p.start_speed * si;
+        }
+    } else {
+        r[3] = 0.0f; r[4] = 0.0f; r[5] = 0.0f; r[6] = 1.0f;                         // :573-575,635: euler (0,0,0) -> identity, exactly
+        if (p.start_speed != 0.0f) { r[7] = p.start_speed * 1.0f; r[8] = p.start_speed * 0.0f; }   // :638-641, cos(0), sin(0)
+    }
 #pragma unroll
     for (int c = 0; c < kRoot; ++c) p.root[ne * kRoot + c] = r[c];                  // :645
     float2* ds = reinterpret_cast<float2*>(p.state_dof) + ne * p.num_dof;
@@ -153,8 +200,8 @@ __device__ __forceinline__ void reset_env(const KParams& p, long long ne, const 
     for (int j = 0; j < kBuf / 4; ++j) cm[j] = make_float4(0.f, 0.f, 0.f, 0.f);     // :681 (channel 6 of the clean frames)
     for (int j = 0; j < p.delay_w; ++j) p.command_history[ne * p.delay_w + j] = 0.0f;   // :686
     p.curent_command[ne] = 0.0f;                                                    // :683
-    p.yaw_command[ne] = 0.0f;                                                       // :685 (spawn_yaw_tgt = 0, :571)
-    *delay_out = delay; *imu_x_out = ix; *speed_off_out = so;
+    p.yaw_command[ne] = yaw_tgt;                                                    // :685 (spawn_yaw_tgt)
+    *delay_out = delay; *imu_x_out = ix; *speed_off_out = so; *yaw_tgt_out = yaw_tgt;
 }
 
 struct Smem {
@@ -165,7 +212,7 @@ struct Smem {
 };
 
 // MODE 0: fused post_physics_step; 1: compute_obs_rwd only; 2: observations only (obs_out = clean [N,8], nothing else written)
-template <int MODE>
+template <int MODE, int VAR>
 __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant__ KParams p, float* __restrict__ obs_out) {
     __shared__ Smem s;
     const int lane = threadIdx.x;
@@ -248,17 +295,19 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
             }
         }
         if (MODE == 0 && do_reset) {
-            float u[kResetNoise];
+            constexpr int kCols = VAR == kTurning ? kResetNoiseTurning : kResetNoise;
+            float u[kResetNoiseTurning];
             if (philox) {
                 Philox4 a = philox_env(p.seed, step_now, p.env_off + n, kStreamResetA);
                 Philox4 b = philox_env(p.seed, step_now, p.env_off + n, kStreamResetB);
                 u[0] = u01(a.x); u[1] = u01(a.y); u[2] = u01(a.z); u[3] = u01(a.w); u[4] = u01(b.x);
+                u[5] = u01(b.y); u[6] = u01(b.z); u[7] = u01(b.w);
             } else {
 #pragma unroll
-                for (int c = 0; c < kResetNoise; ++c) u[c] = p.reset_unit ? p.reset_unit[n * kResetNoise + c] : 0.5f;
+                for (int c = 0; c < kCols; ++c) u[c] = p.reset_unit ? p.reset_unit[n * kCols + c] : 0.5f;
             }
-            reset_env(p, n, u, r, &delay, &imu_x, &speed_off);
-            cur_cmd = 0.0f; yaw_cmd = 0.0f;
+            reset_env<VAR>(p, n, u, r, &delay, &imu_x, &speed_off, &yaw_cmd);
+            cur_cmd = 0.0f;
             if (p.ep_return) p.ep_return[n] = 0.0f;
         }
 
@@ -276,7 +325,14 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
             p.cmd_ring[n * kBuf + slot] = o[6];
             // time-ordered command history: t = 0..18 from the ring as it was before this step, t = 19 = o[6]
             float prev_cmd = 0.0f, acc = 0.0f;
-            if (!do_reset) {
+            if (VAR == kTurning) {                      // sum of act_buff = the ring with this step's command in its slot (:742)
+                acc = o[6];
+                if (!do_reset) {
+#pragma unroll 1
+                    for (int t = 0; t < kBuf; ++t)
+                        if (t != slot) acc += s.cmd[lane * kBuf + t];
+                }
+            } else if (!do_reset) {
                 int t_slot = slot + 1;
                 if (t_slot == kBuf) t_slot = 0;
                 float a0 = s.cmd[lane * kBuf + t_slot] / 0.5f;                      // :722
@@ -297,7 +353,7 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
             }
             dsum = static_cast<double>(acc);
             bool felt;
-            const float partial = reward_partial(o, &felt);                         // :508-514
+            const float partial = VAR == kTurning ? reward_partial_turning(o, &felt) : reward_partial(o, &felt);   // :508-514
             const bool finished = prog >= p.max_episode_length - 1;                 // :755
             out_reset = felt || finished;                                           // :758-759
             p.rew[n] = felt ? -INFINITY : partial;                                  // sentinel, resolved by paper_finalize_kernel
@@ -318,9 +374,11 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
             z[4] = z[4] / 5.0f;                                                     // :536
             z[5] = z[5] / kPi;                                                      // :537
             z[6] = o[6] / p.max_steering;                                           // :538
-            const float dc = prev_cmd - o[6];
-            z[2] = z[2] + dc;                                                       // :541
-            z[0] = z[0] + dc * 0.3f;                                                // :542
+            if (VAR == kPaper) {
+                const float dc = prev_cmd - o[6];
+                z[2] = z[2] + dc;                                                   // :541
+                z[0] = z[0] + dc * 0.3f;                                            // :542
+            }
             z[1] = 0.0f;                                                            // :544
             z[7] = o[7];
             float4* fr = reinterpret_cast<float4*>(s.frames + lane * kObs);
@@ -441,11 +499,16 @@ __global__ void __launch_bounds__(256) paper_finalize_kernel(const __grid_consta
         double S = 0.0;
 #pragma unroll
         for (int w = 0; w < 8; ++w) S += red[w];
-        double cnt = static_cast<double>(p.n) * (kBuf - 1);
+        double cnt = static_cast<double>(p.n) * (p.variant == kTurning ? kBuf : kBuf - 1);
         if (sums) { S = sums[0]; cnt = sums[1]; }
         const float mean = static_cast<float>(S / cnt);
-        const float reward7 = 1.0f - mean;                                          // :747
-        add_s = reward7 * 0.2f;                                                     // :753 last term
+        if (p.variant == kTurning) {
+            const float reward5 = 1.0f - fabsf(mean);                               // gogoro_realistic_turning.py:742
+            add_s = reward5 * 10.0f;                                                // :744 last term
+        } else {
+            const float reward7 = 1.0f - mean;                                      // :747
+            add_s = reward7 * 0.2f;                                                 // :753 last term
+        }
     }
     __syncthreads();
     const float add = add_s;
@@ -484,7 +547,7 @@ __global__ void __launch_bounds__(256) paper_finalize_kernel(const __grid_consta
 
 // {sum of squared command differences, number of differences} of the step just computed -> out[2] (all-reduce payload)
 __global__ void __launch_bounds__(256) paper_diff_sums_kernel(const double* __restrict__ slots2, const unsigned long long* __restrict__ tick,
-                                                               int n, double* __restrict__ out) {
+                                                               int n, int per_env, double* __restrict__ out) {
     __shared__ double red[8];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const double* slots = slots2 + (tick[1] & 1ull) * kStatSlots;
@@ -497,7 +560,7 @@ __global__ void __launch_bounds__(256) paper_diff_sums_kernel(const double* __re
 #pragma unroll
         for (int w = 0; w < 8; ++w) S += red[w];
         out[0] = S;
-        out[1] = static_cast<double>(n) * (kBuf - 1);
+        out[1] = static_cast<double>(n) * per_env;
     }
 }
 
@@ -529,6 +592,7 @@ __global__ void __launch_bounds__(256) paper_pre_kernel(const __grid_constant__ 
         if (i < p.delay_w) hist[i] = h[i];
         if (i == tap) applied = h[i];
     }
+    if (p.variant == kTurning) applied = applied + p.steer_offsets[n];              // gogoro_realistic_turning.py:365
     p.pos_cmd[n * p.num_dof + p.steering_joint] = applied;                          // :360
     p.vel_cmd[n * p.num_dof + p.rear_wheel_joint] = p.curent_speed[n];              // :376
 }
@@ -540,11 +604,13 @@ __global__ void paper_reset_idx_kernel(const __grid_constant__ KParams p, const 
     if (i >= k) return;
     const long long ne = ids[i];
     if (ne < 0 || ne >= p.n) return;
-    float u[kResetNoise], r[kRoot], f0, f1;
+    float u[kResetNoiseTurning], r[kRoot], f0, f1, f2;
     long long d;
+    const int cols = p.variant == kTurning ? kResetNoiseTurning : kResetNoise;
 #pragma unroll
-    for (int c = 0; c < kResetNoise; ++c) u[c] = unit[static_cast<size_t>(i) * kResetNoise + c];
-    reset_env(p, ne, u, r, &d, &f0, &f1);
+    for (int c = 0; c < kResetNoiseTurning; ++c) u[c] = c < cols ? unit[static_cast<size_t>(i) * cols + c] : 0.5f;
+    if (p.variant == kTurning) reset_env<kTurning>(p, ne, u, r, &d, &f0, &f1, &f2);
+    else reset_env<kPaper>(p, ne, u, r, &d, &f0, &f1, &f2);
     p.progress[ne] = 0;                                                             // :678
     p.reset[ne] = 0;                                                                // :679
     float4* ob = reinterpret_cast<float4*>(p.obs_buf + ne * kObs);
@@ -567,7 +633,7 @@ __global__ void paper_frames_kernel(const float* __restrict__ ring, const unsign
 
 __global__ void paper_philox_kernel(int n, unsigned long long seed, unsigned long long step, long long env_off,
                                     const unsigned long long* __restrict__ epoch, float* sensor, float* reset_unit,
-                                    float* speed, float* yaw) {
+                                    float* speed, float* yaw, int reset_cols) {
     step = effective_step(step, epoch);
     const long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (e >= n) return;
@@ -580,8 +646,9 @@ __global__ void paper_philox_kernel(int n, unsigned long long seed, unsigned lon
     if (yaw) yaw[e] = u01(b.w);
     if (reset_unit) {
         Philox4 c = philox_env(seed, step, env_off + e, kStreamResetA), d = philox_env(seed, step, env_off + e, kStreamResetB);
-        float* o = reset_unit + e * kResetNoise;
+        float* o = reset_unit + e * reset_cols;
         o[0] = u01(c.x); o[1] = u01(c.y); o[2] = u01(c.z); o[3] = u01(c.w); o[4] = u01(d.x);
+        if (reset_cols == kResetNoiseTurning) { o[5] = u01(d.y); o[6] = u01(d.z); o[7] = u01(d.w); }
     }
 }
 
@@ -641,7 +708,7 @@ static void fill_kparams(const TkGogoroPaper* h, KParams& k) {
     k.seed = 0; k.step = 0; k.step_dev = h->step_dev; k.env_off = 0; k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs; k.num_dof = P.num_dof; k.steering_joint = P.steering_joint; k.rear_wheel_joint = P.rear_wheel_joint;
     k.max_episode_length = P.max_episode_length; k.speed_freq = P.speed_freq_update; k.yaw_freq = P.yaw_freq_update;
-    k.delay_w = P.delay_width; k.use_delay = P.use_steer_delay;
+    k.delay_w = P.delay_width; k.use_delay = P.use_steer_delay; k.variant = P.variant;
     k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.command_ring, 16);
     k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count;
     k.fin_vec_ok = aligned_to(B.rew_buf, 16) && aligned_to(B.reset_buf, 16) && (!B.episode_return || aligned_to(B.episode_return, 16));
@@ -685,6 +752,8 @@ int tk_gogoro_paper_create(const TkGogoroPaperParams* params, TkGogoroPaper** ou
     TK_REQUIRE(params->delay_width >= 3 && params->delay_width <= kMaxDelayW, TK_ERR_INVALID,
                "delay_width (command_delay[1]) must be in 3..%d (got %d)", kMaxDelayW, params->delay_width);
     TK_REQUIRE(params->command_delay[1] != params->command_delay[0], TK_ERR_INVALID, "empty command_delay range");
+    TK_REQUIRE(params->variant == kPaper || params->variant == kTurning, TK_ERR_INVALID,
+               "variant %d: TK_GOGORO_PAPER_VARIANT_PAPER or TK_GOGORO_PAPER_VARIANT_TURNING", params->variant);
     TK_CUDA(cudaSetDevice(params->device));
     TkGogoroPaper* h = new (std::nothrow) TkGogoroPaper();
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "out of host memory");
@@ -698,7 +767,7 @@ int tk_gogoro_paper_create(const TkGogoroPaperParams* params, TkGogoroPaper** ou
     h->sm_count = sms; h->stagger_cycles = 1000; h->stagger_slots = 8;   // 800..1200 cycles measured the same (-2.6 us at 65536..262144 envs)
     {
         int occ = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, paper_tile_kernel<0>, kTile, 0) == cudaSuccess && occ > 0) h->stagger_slots = occ;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, paper_tile_kernel<0, kPaper>, kTile, 0) == cudaSuccess && occ > 0) h->stagger_slots = occ;
         else cudaGetLastError();
     }
     if (const char* env = getenv("TK_GOGORO_PAPER_STAGGER")) h->stagger_cycles = atoi(env);
@@ -780,7 +849,7 @@ int tk_gogoro_paper_compute_observations(TkGogoroPaper* h, float* obs_out, void*
     TK_REQUIRE(obs_out != nullptr, TK_ERR_INVALID, "null obs_out");
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
-    paper_tile_kernel<2><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, obs_out);
+    paper_tile_kernel<2, kPaper><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, obs_out);   // same in both files
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
@@ -790,7 +859,8 @@ int tk_gogoro_paper_compute_obs_rwd(TkGogoroPaper* h, const TkGogoroPaperNoise* 
     TK_CUDA(cudaSetDevice(h->params.device));
     KParams k; fill_kparams(h, k);
     if (int rc = set_noise(k, noise)) return rc;
-    paper_tile_kernel<1><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, nullptr);
+    if (k.variant == kTurning) paper_tile_kernel<1, kTurning><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, nullptr);
+    else paper_tile_kernel<1, kPaper><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, nullptr);
     TK_CUDA(cudaGetLastError());
     h->ran = true;
     return TK_OK;
@@ -812,7 +882,8 @@ int tk_gogoro_paper_post_physics(TkGogoroPaper* h, const TkGogoroPaperNoise* noi
         cfg.attrs = attr;
         cfg.numAttrs = 1;
         float* no_out = nullptr;
-        cudaLaunchKernelEx(&cfg, paper_tile_kernel<0>, k, no_out);
+        if (k.variant == kTurning) cudaLaunchKernelEx(&cfg, paper_tile_kernel<0, kTurning>, k, no_out);
+        else cudaLaunchKernelEx(&cfg, paper_tile_kernel<0, kPaper>, k, no_out);
     }
     TK_CUDA(cudaGetLastError());
     h->ran = true;
@@ -822,7 +893,8 @@ int tk_gogoro_paper_post_physics(TkGogoroPaper* h, const TkGogoroPaperNoise* noi
 int tk_gogoro_paper_diff_sums(TkGogoroPaper* h, double* sums_out, void* stream) {
     TK_REQUIRE(h && sums_out, TK_ERR_INVALID, "null argument");
     TK_CUDA(cudaSetDevice(h->params.device));
-    paper_diff_sums_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(h->diff_slots, h->tick, h->params.num_envs, sums_out);
+    paper_diff_sums_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        h->diff_slots, h->tick, h->params.num_envs, h->params.variant == kTurning ? kBuf : kBuf - 1, sums_out);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
@@ -893,7 +965,8 @@ int tk_gogoro_paper_philox_noise(TkGogoroPaper* h, uint64_t seed, uint64_t step,
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
     TK_CUDA(cudaSetDevice(h->params.device));
     paper_philox_kernel<<<(h->params.num_envs + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        h->params.num_envs, seed, step, env_id_offset, h->step_dev, sensor_unit, reset_unit, speed_unit, yaw_unit);
+        h->params.num_envs, seed, step, env_id_offset, h->step_dev, sensor_unit, reset_unit, speed_unit, yaw_unit,
+        h->params.variant == kTurning ? kResetNoiseTurning : kResetNoise);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }

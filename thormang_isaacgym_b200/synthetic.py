@@ -210,10 +210,11 @@ def gogoro_paper_state(n: int, seed: int = 1234, device="cpu", num_dof: int = GO
     return {k: v.to(device) for k, v in out.items()}
 
 
-def gogoro_paper_noise(n: int, seed: int, device="cpu") -> Dict[str, torch.Tensor]:
-    """U(0,1) draws of one step of the paper variant, addressed by env id: sensors [N,6], reset [N,5], speed [N], yaw [N]."""
+def gogoro_paper_noise(n: int, seed: int, device="cpu", reset_cols: int = 5) -> Dict[str, torch.Tensor]:
+    """U(0,1) draws of one step of the paper variant, addressed by env id: sensors [N,6], reset [N,5] (8 columns for the
+    gogoro_realistic_turning.py sibling), speed [N], yaw [N]."""
     g = _gen(seed + 1993)
-    out = dict(sensor_unit=torch.rand((n, 6), generator=g), reset_unit=torch.rand((n, 5), generator=g),
+    out = dict(sensor_unit=torch.rand((n, 6), generator=g), reset_unit=torch.rand((n, reset_cols), generator=g),
                speed_unit=torch.rand((n,), generator=g), yaw_unit=torch.rand((n,), generator=g))
     return {k: v.to(device) for k, v in out.items()}
 

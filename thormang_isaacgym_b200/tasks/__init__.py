@@ -2,6 +2,7 @@
 from .ant import Ant
 from .anymal import Anymal
 from .gogoro_new import Gogoro
+from .gogoro_realistic_turning import Gogoro as GogoroTurning
 from .gogoro_realistic_turning_sim_paper import Gogoro as GogoroPaper
 from .humanoid import Humanoid
 from .MA_OP3 import MA_OP3
@@ -13,4 +14,5 @@ isaacgym_task_map = {
     "Gogoro": Gogoro,
     "MA_OP3": MA_OP3,
     "GogoroPaper": GogoroPaper,   # gogoro_realistic_turning_sim_paper.py::Gogoro (unregistered in the reference)
+    "GogoroTurning": GogoroTurning,   # gogoro_realistic_turning.py::Gogoro (unregistered in the reference)
 }

@@ -36,6 +36,10 @@ SENSOR_NOISE_COLS = 6
 
 
 class Gogoro(VecTask):
+    # what tasks/gogoro_realistic_turning.py (the sibling reference file, same class) changes
+    VARIANT = nat.GOGORO_PAPER_VARIANT_PAPER
+    RESET_NOISE_COLS = RESET_NOISE_COLS
+    USE_STEER_DELAY_DEFAULT = False            # USE_STEER_DELAY = not DEBUG, :31, with DEBUG = True as saved (:22)
 
     def __init__(self, cfg, rl_device, sim_device, graphics_device_id, headless,
                  virtual_screen_capture=False, force_render=False):
@@ -63,7 +67,7 @@ class Gogoro(VecTask):
         self.steering_offset = nz["steering_offset"]
         self.command_delay = nz["command_delay"]
         self.min_speed, self.max_speed, self.max_steering = 0.0, 10.0, 0.5        # :84-86
-        self.use_steer_delay = bool(cfg["env"].get("useSteerDelay", False))       # USE_STEER_DELAY = not DEBUG, :31
+        self.use_steer_delay = bool(cfg["env"].get("useSteerDelay", self.USE_STEER_DELAY_DEFAULT))       # USE_STEER_DELAY = not DEBUG, :31
         self.start_speed = float(cfg["env"].get("startSpeed", 1.3))               # DEBUG_START_SPEED, :26,638
         self.buff_size = BUFF
         cfg["env"]["numObservations"] = NUM_CH * self.buff_size                   # :117
@@ -151,6 +155,7 @@ class Gogoro(VecTask):
         p.speed_freq_update, p.yaw_freq_update = int(self.speed_freq_update), int(self.yaw_freq_update)
         p.buff_size, p.delay_width = self.buff_size, int(self.command_delay[1])
         p.use_steer_delay = 1 if self.use_steer_delay else 0
+        p.variant = self.VARIANT
         p.max_steering, p.start_speed = self.max_steering, self.start_speed
         for name, pair in (("imu_filter_noise", self.imu_filter_noise), ("imu_noise", self.imu_noise),
                            ("speed_sensor_noise", self.speed_sensor_noise),
@@ -285,12 +290,12 @@ class Gogoro(VecTask):
         self.curent_step += 1
 
     def reset_idx(self, env_ids: torch.Tensor, unit: Optional[torch.Tensor] = None):
-        """:599-688.  ``unit`` [K,5] U(0,1) draws in reference order (drawn with torch.rand when omitted)."""
+        """:599-688.  ``unit`` [K,RESET_NOISE_COLS] U(0,1) draws in reference order (drawn with torch.rand when omitted)."""
         k = len(env_ids)
         if k == 0:
             return
         if unit is None:
-            unit = torch.rand((k, RESET_NOISE_COLS), device=self.device)
+            unit = torch.rand((k, self.RESET_NOISE_COLS), device=self.device)
         ids = env_ids.to(device=self.device, dtype=torch.long).contiguous()
         unit = unit.to(self.device, dtype=torch.float).contiguous()
         nat.check(self._lib.tk_gogoro_paper_reset_idx(self._handle, nat.ptr(ids), k, nat.ptr(unit), self._stream()),
@@ -314,7 +319,7 @@ class Gogoro(VecTask):
         """Materialise the in-kernel draws of ``step``: dict(sensor_unit, reset_unit, speed_unit, yaw_unit)."""
         n, dev = self.n_envs, self.device
         out = dict(sensor_unit=torch.empty((n, SENSOR_NOISE_COLS), device=dev),
-                   reset_unit=torch.empty((n, RESET_NOISE_COLS), device=dev),
+                   reset_unit=torch.empty((n, self.RESET_NOISE_COLS), device=dev),
                    speed_unit=torch.empty(n, device=dev), yaw_unit=torch.empty(n, device=dev))
         nat.check(self._lib.tk_gogoro_paper_philox_noise(
             self._handle, self.noise_seed, self.step_count if step is None else step, self.env_id_offset,
