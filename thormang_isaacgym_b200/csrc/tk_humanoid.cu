@@ -7,15 +7,19 @@
 //
 // Data layout in HBM is Isaac Gym's (AoS): root_states [N,13], dof_state [N*D,2], dof_force [N,D],
 // sensors [N,12], actions [N,D], obs_buf [N,110].  The fused post-physics kernel is a pure
-// streaming kernel (924 B / env-step, ~0.3 flop/B): one CTA owns a tile of T consecutive
-// envs, whose slice of EVERY array is one contiguous, 16-byte aligned byte range (tk_humanoid_tile.cuh).
+// streaming kernel (924 B / env-step, ~0.3 flop/B): one CTA owns a tile of 32 consecutive
+// envs, whose slice of EVERY array is one contiguous, 16-byte aligned byte range.
 //   * the tile's inputs arrive as five cp.async.bulk (TMA) global->shared copies on one mbarrier;
-//   * scaled copies (96 of the 110 columns) go shared->shared into the image of the tile's obs rows;
-//   * the 14 columns that need the torso math are computed one env per thread from the
-//     shared-memory copy of the root rows (stride 13 words: bank-conflict free);
-//   * the finished [T,110] tile leaves as ONE cp.async.bulk (TMA) shared->global store;
-//   * per-task constants (limits, 1/range, efforts) are staged once in shared memory;
-//   * per-env flags/potentials/reward are coalesced 4/8-byte accesses, one env per thread.
+//   * lane e pulls ITS env's inputs out of the staged tile into registers (conflict-free row strides), computes the
+//     96 scaled copies and the torso math, and writes its obs row IN PLACE over the staging area;
+//   * the finished [32,110] tile leaves as ONE cp.async.bulk (TMA) shared->global store;
+//   * per-task constants (limits, 1/range, efforts) ride in the __grid_constant__ parameter block and are read as
+//     constant-bank operands with compile-time indices: not staged in shared memory;
+//   * per-env flags/potentials/reward are coalesced 4/8-byte accesses, one env per lane.
+// Two kernels share that tile layout: humanoid_warp_kernel (tk_humanoid_tile.cuh; one warp per tile, 12 CTAs / SM:
+// the bandwidth shape for grids of several waves) and humanoid_quad_kernel (tk_humanoid_quad.cuh; four warps per tile
+// with the torso math split over the warps and column-parallel copies: the latency shape for single-wave grids).
+// launch_tile() picks by tiles-per-SM.
 // No tensor cores: nothing on this path is a contraction.
 #include "tk_common.cuh"
 
