@@ -15,6 +15,7 @@
 // more than its 113 us of HBM time -- on CTA dispatch alone.
 #include "tk_common.cuh"
 
+#include <cstdlib>
 #include <new>
 
 namespace tk {
@@ -64,6 +65,8 @@ struct KParams {
     int noise_mode;
     int n, num_dof, steering_joint, rear_wheel_joint, max_episode_length, speed_freq, yaw_freq;
     int vec_ok;
+    int prefetch;                 // L2 prefetch of the tile inputs ahead of griddepcontrol.wait (thin grids, host decides)
+    int dbg_reset;                // developer ablation mask (TK_GOGORO_DBG_RESET): 1 no resets, 2 no scalar stores, 4 no row fetch/stores, 8 no Philox
     long long* dbg_ts;            // developer timeline probe (tools/tile_timeline.py --task gogoro); NULL in normal use
     float max_steering, max_steering_change;
     // (float)lo / (float)mean, (float)(hi - lo) / (float)std with the span formed in double (get_randoms :466-467)
@@ -262,11 +265,11 @@ __device__ __forceinline__ ResetRows reset_env_fetch(const KParams& p, long long
     r.rv = (lane < kRoot) ? p.root_reset[ne * kRoot + lane] : 0.0f;                 // :518
     return r;
 }
-__device__ __forceinline__ float reset_env_warp(const KParams& p, long long ne, const float* u, int lane, const ResetRows& rows,
-                                                ResetScalars* out) {
-    const int d = p.num_dof;
-    const float pose0 = rows.pose0, pose1 = rows.pose1;
-    float rv = rows.rv;
+// Part 1: everything of reset_idx that does not depend on the fetched rows -- the per-env scalars, the spawn quaternion.
+// Returns the new root value of column `lane` for lanes 2..12 (z, quaternion, zero velocities); columns 0 / 1 (x, y) come
+// from root_reset and are filled in by reset_env_rows.  compute_gogoro_observations reads no position column (:696-699),
+// so the staged tile is patched with this value alone and the row fetch stays off the tile's critical path.
+__device__ __forceinline__ float reset_env_scalars(const KParams& p, long long ne, const float* u, int lane, ResetScalars* out) {
     const float initial_target = (u[3] * 2.0f - 1.0f) * kPi;                        // :486
     const float initial_rot = initial_target + (-1.57f + u[4] * static_cast<float>(1.57 - (-1.57)));   // :487
     const float half = initial_rot / 2.0f;
@@ -284,14 +287,9 @@ __device__ __forceinline__ float reset_env_warp(const KParams& p, long long ne, 
     cfgv[3] = normal_of(p.seat_xr, u[8]);                                           // :557
     cfgv[4] = normal_of(p.steer_off, u[9]);                                         // :559
     // root row: [0:3] <- root_reset (z <- 0.03 :537), [3:7] <- spawn quaternion :519, [7:13] <- 0 :520
+    float rv = 0.0f;
     rv = (lane == 2) ? 0.03f : rv;
     rv = (lane == 3) ? qx : rv; rv = (lane == 4) ? qy : rv; rv = (lane == 5) ? qz : rv; rv = (lane == 6) ? qw : rv;
-    rv = (lane >= 7) ? 0.0f : rv;
-    if (lane < kRoot) p.root[ne * kRoot + lane] = rv;                               // :547
-    float2* ds = reinterpret_cast<float2*>(p.state_dof) + ne * d;
-    if (lane < d) ds[lane] = make_float2(pose0, 0.0f);                              // :549-550
-    if (lane + 32 < d) ds[lane + 32] = make_float2(pose1, 0.0f);
-    for (int j = lane + 64; j < d; j += 32) ds[j] = make_float2(p.thormang_pose[ne * d + j], 0.0f);
     // per-env scalars, one lane each
     float sv = 0.0f;
     float* sp_ = nullptr;
@@ -309,16 +307,30 @@ __device__ __forceinline__ float reset_env_warp(const KParams& p, long long ne, 
         sv = cfgv[0];
         sv = (lane == 3) ? cfgv[1] : sv; sv = (lane == 4) ? cfgv[2] : sv; sv = (lane == 5) ? cfgv[3] : sv; sv = (lane == 6) ? cfgv[4] : sv;
     }
-    if (sp_) *sp_ = sv;
+    if (sp_ && !(p.dbg_reset & 2)) *sp_ = sv;
     out->yaw_cmd = initial_target;                                                  // :589
     out->imu_off = cfgv[3];
     return rv;
+}
+// Part 2: the two row writes that consume the fetched rows (root :547, the 39 locked joints :549-550).  Nothing in the
+// step reads them back, so the fused kernel issues them at its very end, when the fetch has long landed.
+__device__ __forceinline__ void reset_env_rows(const KParams& p, long long ne, int lane, const ResetRows& rows, float rv_fixed) {
+    const int d = p.num_dof;
+    const float rv = (lane < 2) ? rows.rv : rv_fixed;
+    if (lane < kRoot) p.root[ne * kRoot + lane] = rv;                               // :547
+    float2* ds = reinterpret_cast<float2*>(p.state_dof) + ne * d;
+    if (lane < d) ds[lane] = make_float2(rows.pose0, 0.0f);                         // :549-550
+    if (lane + 32 < d) ds[lane + 32] = make_float2(rows.pose1, 0.0f);
+    for (int j = lane + 64; j < d; j += 32) ds[j] = make_float2(p.thormang_pose[ne * d + j], 0.0f);
 }
 
 // the 10 unit draws of one reset (same value in every lane of the calling warp)
 __device__ __forceinline__ void reset_units(const KParams& p, long long ne, long long row, bool philox, unsigned long long step_now,
                                             int lane, float* u) {
-    if (philox) {
+    if (philox && (p.dbg_reset & 8)) {
+#pragma unroll
+        for (int c = 0; c < kResetNoise; ++c) u[c] = 0.25f;
+    } else if (philox) {
         philox_reset_noise_cold(p.seed, step_now, p.env_off + ne, lane, u);
     } else {
 #pragma unroll
@@ -328,9 +340,55 @@ __device__ __forceinline__ void reset_units(const KParams& p, long long ne, long
     }
 }
 
+// SPEC variant (thin grids, in-kernel Philox): every thread evaluates the reset of ITS OWN env speculatively -- the draws are a
+// pure function of (seed, step, global env id) -- ahead of griddepcontrol.wait (eager launches) or under the tile's round trip
+// (CUDA-graph replays, where the epoch word must be read first).  A lone warp walking the ~500 dependent instructions of
+// three Philox blocks, three Box-Muller pairs and a sincosf takes 1.5-2.5 us, and in the lazy scheme that walk sat between
+// "reset flag landed" and "math may start" of exactly the tiles that end a thin launch (tools/tile_timeline.py: 61 resets in
+// 65536 envs made the launch 5.4 us long instead of 3.3 us; with resets disabled the step took 5.8 us instead of 8.4 us).
+// Same functions, same bits as philox_reset_noise / reset_env_scalars.
+struct SpecReset { float speed, speed_off, cfg[5], qx, qy, qz, qw, yaw_target; };
+__device__ __forceinline__ SpecReset spec_reset(const KParams& p, unsigned long long step_now, long long env_global) {
+    float u[kResetNoise];
+    philox_reset_noise(p.seed, step_now, env_global, u);
+    SpecReset r;
+    r.speed = uniform_of(p.speed, u[0]);                                            // :479
+    r.speed_off = uniform_of(p.speed_off, u[2]);                                    // :482
+    const float initial_target = (u[3] * 2.0f - 1.0f) * kPi;                        // :486
+    const float initial_rot = initial_target + (-1.57f + u[4] * static_cast<float>(1.57 - (-1.57)));   // :487
+    const float half = initial_rot / 2.0f;
+    float sy, cy;
+    sincosf(half, &sy, &cy);
+    const float sr = 0.0f, cr = 1.0f, sp = 0.0f, cp = 1.0f;
+    r.qx = sr * cp * cy - cr * sp * sy;                                             // :497-500
+    r.qy = cr * sp * cy + sr * cp * sy;
+    r.qz = cr * cp * sy - sr * sp * cy;
+    r.qw = cr * cp * cy + sr * sp * sy;
+    r.cfg[0] = normal_of(p.seat_x, u[5]);                                           // :554
+    r.cfg[1] = normal_of(p.seat_y, u[6]);                                           // :555
+    r.cfg[2] = normal_of(p.seat_z, u[7]);                                           // :556
+    r.cfg[3] = normal_of(p.seat_xr, u[8]);                                          // :557
+    r.cfg[4] = normal_of(p.steer_off, u[9]);                                        // :559
+    r.yaw_target = initial_target;
+    return r;
+}
+// the per-env scalars of reset_idx, written by the env's own thread from its speculative values
+__device__ __forceinline__ void spec_reset_store(const KParams& p, long long ne, const SpecReset& r) {
+    p.curent_speed[ne] = r.speed;                                                   // :479
+    p.curent_speed_offset[ne] = r.speed_off;                                        // :482
+#pragma unroll
+    for (int c = 0; c < 5; ++c) p.config_vector[ne * 5 + c] = r.cfg[c];
+    p.imu_offsets[ne] = r.cfg[3];                                                   // :574
+    p.steer_offsets[ne] = r.cfg[4];                                                 // :575
+    p.curent_command[ne] = 0.0f;                                                    // :587
+#pragma unroll
+    for (int c = 0; c < kHist; ++c) p.action_history[ne * kHist + c] = 0.0f;        // :590
+}
+
 // MODE 0: fused post_physics_step; 1: compute_obs_rwd only; 2: observations only (obs_out = clean [N,6])
-template <int MODE>
+template <int MODE, bool SPEC = false>
 __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constant__ KParams p, float* __restrict__ obs_out) {
+    static_assert(!SPEC || MODE == 0, "the speculative reset belongs to the fused step");
     __shared__ Smem s;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int env0 = blockIdx.x * kTile;
@@ -350,17 +408,67 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         mbar_init(&s.bar, 1);
         fence_proxy_async_smem();
     }
-    // The sensor noise of this step is a pure function of (seed, step, global env id): with a NULL epoch (eager launches)
-    // it is computed right here, under the previous kernel's drain; with a device-side epoch (CUDA-graph replays) the one
-    // global word it needs is requested first thing after the wait and the block is computed under the tile's round trip.
+    // The sensor noise of this step is a pure function of (seed, step, global env id): it is computed right here, under the
+    // previous kernel's drain.
     StepNoise sn;
 #pragma unroll
     for (int c = 0; c < kSensorNoise; ++c) sn.sensor[c] = 0.0f;
-    const bool early_noise = (MODE != 2) && philox && p.step_dev == nullptr;
-    if (early_noise) sn = philox_sensor_noise(p.seed, p.step, p.env_off + n);
+    // L2 prefetch of the tile's inputs ahead of the dependency wait (thin grids; a hint: nothing is consumed, L2 is the
+    // point of coherence, stream order is intact).  With the state sets of bench.py rotating over > 2x the L2 -- more than
+    // the 256 MB the TLB reaches -- the first touch of a tile costs a page walk plus a DRAM round trip (2.3 us from the
+    // wait to the first scalar, 1.3 us when L2-resident: tools/tile_timeline.py --task gogoro --sets 26); both move under
+    // the previous kernel's tail.
+    if (p.prefetch && bulk) {
+        if (tid == 0) bulk_prefetch_l2(p.root + static_cast<size_t>(env0) * kRoot, kTile * kRoot * 4);
+        else if (tid == 1 && MODE != 2) bulk_prefetch_l2(p.action_history + static_cast<size_t>(env0) * kHist, kTile * kHist * 4);
+        else if (tid == 2 && use_noise) bulk_prefetch_l2(p.sensor_unit + static_cast<size_t>(env0) * kSensorNoise, kTile * kSensorNoise * 4);
+        else if (warp == 1) {               // the six per-env scalar arrays: 4 + 4 + 4 + 4 + 8 + 8 lines of 128 bytes
+            const char* a = nullptr;
+            const int l = lane;
+            if (l < 4) a = reinterpret_cast<const char*>(p.yaw_command + env0) + 128 * l;
+            else if (l < 8) a = reinterpret_cast<const char*>(p.curent_command + env0) + 128 * (l - 4);
+            else if (l < 12) a = (MODE != 2) ? reinterpret_cast<const char*>(p.imu_offsets + env0) + 128 * (l - 8) : nullptr;
+            else if (l < 16) a = (MODE == 0 && p.ep_return) ? reinterpret_cast<const char*>(p.ep_return + env0) + 128 * (l - 12) : nullptr;
+            else if (l < 24) a = (MODE != 2) ? reinterpret_cast<const char*>(p.progress + env0) + 128 * (l - 16) : nullptr;
+            else a = (MODE == 0) ? reinterpret_cast<const char*>(p.reset + env0) + 128 * (l - 24) : nullptr;
+            if (a) prefetch_l2(a);
+        } else if (warp == 2 && MODE == 0) {
+            // one line of every array the tile writes or (on a reset) reads late: not for the data, for the TRANSLATION --
+            // a first touch of a page the TLB has dropped is a page walk of several dependent DRAM reads (~2 us measured
+            // on the reset rows), and a store that misses holds back the completion of the whole grid
+            const void* a = nullptr;
+            switch (lane) {
+                case 0: a = p.thormang_pose + static_cast<size_t>(env0) * p.num_dof; break;
+                case 1: a = p.root_reset + static_cast<size_t>(env0) * kRoot; break;
+                case 2: a = p.state_dof + static_cast<size_t>(env0) * p.num_dof * 2; break;
+                case 3: a = p.obs_buf + static_cast<size_t>(env0) * kObs; break;
+                case 4: a = p.buffer_obs + static_cast<size_t>(env0) * kObs; break;
+                case 5: a = p.rew + env0; break;
+                case 6: a = p.timeout ? p.timeout + env0 : nullptr; break;
+                case 7: a = p.curent_speed + env0; break;             // the arrays only a reset / a resample writes
+                case 8: a = p.curent_speed_offset + env0; break;
+                case 9: a = p.config_vector + static_cast<size_t>(env0) * 5; break;
+                case 10: a = p.steer_offsets + env0; break;
+                default: break;
+            }
+            if (a) prefetch_l2(a);
+        }
+    }
+    // The noise epoch (CUDA-graph replays) is read AHEAD of the wait as well: the word is written only by
+    // tk_gogoro_advance_epoch's single-thread kernel, a plain launch that never triggers its dependents early -- whatever
+    // follows it in the stream starts after it has completed, and this grid starts no earlier than its own predecessor.
+    const bool early_noise = (MODE != 2) && philox;
+    unsigned long long step_now = p.step;
+    if (early_noise && p.step_dev) {
+        unsigned long long ep;
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(ep) : "l"(p.step_dev) : "memory");
+        step_now = p.step + (ep << 32);
+    }
+    if (early_noise) sn = philox_sensor_noise(p.seed, step_now, p.env_off + n);
+    SpecReset spec;
+    if (SPEC && early_noise) spec = spec_reset(p, step_now, p.env_off + n);
     asm volatile("griddepcontrol.wait;" ::: "memory");
     TK_GSTAMP(0);
-    const unsigned long long step_now = philox ? effective_step(p.step, p.step_dev) : 0ull;
 
     // full, 16-byte aligned tile: the bulk-copy (TMA) engine moves root / history / noise rows in and both obs rows out
     if (bulk) {
@@ -387,9 +495,8 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         if (MODE != 2) imu_off = p.imu_offsets[n];
         if (MODE == 0 && p.ep_return) ret_old = p.ep_return[n];
         if (MODE != 2) prog = p.progress[n];
-        if (MODE == 0) do_reset = p.reset[n] != 0;                                  // :377
+        if (MODE == 0) do_reset = p.reset[n] != 0 && !(p.dbg_reset & 1);            // :377
     }
-    if (MODE != 2 && philox && !early_noise && valid) sn = philox_sensor_noise(p.seed, step_now, p.env_off + n);
     if (MODE == 0 && valid) {
         prog += 1;                                                                  // :375
         if (do_reset) prog = 0;                                                     // :583
@@ -408,8 +515,25 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
     // state does not depend on the staged rows; only the patch of the staged copy comes after the wait
     constexpr int kPre = 2;
     float pre_root[kPre];
+    ResetRows pre_rows[kPre];
+    int pre_env[kPre];
     bool hist_zero = false;
-    if (MODE == 0 && reset_bits) {
+    if (SPEC && reset_bits) {              // only the rows are fetched here; everything else is already in registers
+        unsigned bits = reset_bits;
+#pragma unroll
+        for (int q = 0; q < kPre; ++q) {
+            pre_root[q] = 0.0f;
+            pre_env[q] = -1;
+            pre_rows[q] = ResetRows{0.0f, 0.0f, 0.0f};
+            if (bits) {
+                pre_env[q] = __ffs(bits) - 1;
+                bits &= bits - 1;
+                pre_rows[q] = reset_env_fetch(p, env0 + warp * 32 + pre_env[q], lane);
+            }
+        }
+        if (do_reset) { yaw_cmd = spec.yaw_target; imu_off = spec.cfg[3]; cur_cmd = 0.0f; hist_zero = true; }   // :589,574,587,590
+    }
+    if (!SPEC && MODE == 0 && reset_bits) {
         int rank = 0;
         if (p.noise_mode == TK_NOISE_COMPACT) {
             rank = p.tile_base_reset[blockIdx.x];
@@ -419,22 +543,29 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
 #pragma unroll
         for (int q = 0; q < kPre; ++q) {
             pre_root[q] = 0.0f;
+            pre_env[q] = -1;
+            pre_rows[q] = ResetRows{0.0f, 0.0f, 0.0f};
             if (bits) {
                 const int e = __ffs(bits) - 1;
                 bits &= bits - 1;
                 const long long ne = env0 + warp * 32 + e;
                 float u[kResetNoise];
-                const ResetRows rows = reset_env_fetch(p, ne, lane);
+                pre_env[q] = e;
                 reset_units(p, ne, (p.noise_mode == TK_NOISE_COMPACT) ? rank + q : ne, philox, step_now, lane, u);
                 ResetScalars rs;
-                pre_root[q] = reset_env_warp(p, ne, u, lane, rows, &rs);
+                pre_root[q] = reset_env_scalars(p, ne, u, lane, &rs);
                 if (lane == e) { yaw_cmd = rs.yaw_cmd; imu_off = rs.imu_off; cur_cmd = 0.0f; hist_zero = true; }   // :589,574,587,590
             }
         }
+        // the rows reset_env_rows writes back at the end of the kernel: requested AFTER the out-of-line Philox calls (a
+        // value in flight cannot live across a call: it would be waited for and spilled)
+#pragma unroll
+        for (int q = 0; q < kPre; ++q)
+            if (pre_env[q] >= 0 && !(p.dbg_reset & 4)) pre_rows[q] = reset_env_fetch(p, env0 + warp * 32 + pre_env[q], lane);
     }
     TK_GSTAMP(2);
     if (bulk) mbar_wait(&s.bar, 0);        // bulk loads landed
-    if (MODE == 0 && reset_bits) {         // patch the staged rows of the envs that were reset
+    if (!SPEC && MODE == 0 && reset_bits) {         // patch the staged rows of the envs that were reset
         int rank = 0;
         if (p.noise_mode == TK_NOISE_COMPACT) {
             rank = p.tile_base_reset[blockIdx.x];
@@ -453,10 +584,12 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
                 const ResetRows rows = reset_env_fetch(p, ne, lane);
                 reset_units(p, ne, (p.noise_mode == TK_NOISE_COMPACT) ? rank + q : ne, philox, step_now, lane, u);
                 ResetScalars rs;
-                rv = reset_env_warp(p, ne, u, lane, rows, &rs);
+                rv = reset_env_scalars(p, ne, u, lane, &rs);
+                reset_env_rows(p, ne, lane, rows, rv);
                 if (lane == e) { yaw_cmd = rs.yaw_cmd; imu_off = rs.imu_off; cur_cmd = 0.0f; hist_zero = true; }
             }
-            if (lane < kRoot) s.root[(warp * 32 + e) * kRoot + lane] = rv;
+            // columns 2..12 only: x / y of the staged row are not read by the observation (and for q < kPre not known yet)
+            if (lane >= 2 && lane < kRoot) s.root[(warp * 32 + e) * kRoot + lane] = rv;
         }
         __syncwarp();
     }
@@ -468,6 +601,11 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         float r[kRoot], hist[kHist];
 #pragma unroll
         for (int c = 0; c < kRoot; ++c) r[c] = s.root[tid * kRoot + c];
+        if (SPEC && do_reset) {             // the new root row (:518-520): position columns are not read by the observation
+            r[3] = spec.qx; r[4] = spec.qy; r[5] = spec.qz; r[6] = spec.qw;
+#pragma unroll
+            for (int c = 7; c < kRoot; ++c) r[c] = 0.0f;
+        }
         if (MODE != 2) {
 #pragma unroll
             for (int c = 0; c < kHist; ++c) hist[c] = hist_zero ? 0.0f : s.hist[tid * kHist + c];
@@ -579,11 +717,36 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
     if (bulk_out) {
         if (tid == 0) bulk_store(out_clean, s.clean, kTile * kObs * 4);
         if (tid == 32 && MODE != 2) bulk_store(p.obs_buf + static_cast<size_t>(env0) * kObs, s.noisy, kTile * kObs * 4);
-        if (tid == 0 || (tid == 32 && MODE != 2)) { bulk_commit(); bulk_wait_read<0>(); }   // shared memory must stay alive until the engine has read it
+        if (tid == 0 || (tid == 32 && MODE != 2)) bulk_commit();
     } else {
         tile_store(out_clean, s.clean, nt * kObs, false, tid);
         if (MODE != 2) tile_store(p.obs_buf + static_cast<size_t>(env0) * kObs, s.noisy, nt * kObs, false, tid);
     }
+    if (SPEC && reset_bits) {              // per-env scalars by the env's own thread, rows warp-cooperatively (lane e holds env e's quaternion)
+        if (do_reset) spec_reset_store(p, n, spec);
+        unsigned bits = reset_bits;
+        for (int q = 0; bits; ++q) {
+            const int e = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const float qx = __shfl_sync(0xffffffffu, spec.qx, e), qy = __shfl_sync(0xffffffffu, spec.qy, e);
+            const float qz = __shfl_sync(0xffffffffu, spec.qz, e), qw = __shfl_sync(0xffffffffu, spec.qw, e);
+            float rv = 0.0f;
+            rv = (lane == 2) ? 0.03f : rv;                                          // :537
+            rv = (lane == 3) ? qx : rv; rv = (lane == 4) ? qy : rv; rv = (lane == 5) ? qz : rv; rv = (lane == 6) ? qw : rv;
+            const long long ne = env0 + warp * 32 + e;
+            ResetRows rows;
+            if (q == 0) rows = pre_rows[0];
+            else if (q == 1) rows = pre_rows[kPre - 1];
+            else rows = reset_env_fetch(p, ne, lane);                               // more than kPre resets in one warp
+            reset_env_rows(p, ne, lane, rows, rv);
+        }
+    }
+    if (!SPEC && MODE == 0 && reset_bits) {         // the deferred row writes of this warp's first kPre resets
+#pragma unroll
+        for (int q = 0; q < kPre; ++q)
+            if (pre_env[q] >= 0 && !(p.dbg_reset & 4)) reset_env_rows(p, env0 + warp * 32 + pre_env[q], lane, pre_rows[q], pre_root[q]);
+    }
+    if (bulk_out && (tid == 0 || (tid == 32 && MODE != 2))) bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
     TK_GSTAMP(6);
 #undef TK_GSTAMP
 }
@@ -760,6 +923,7 @@ struct TkGogoro {
     unsigned long long* step_dev;
     bool epoch_used;      // tk_gogoro_advance_epoch was called: the kernels must read the device-side epoch (NULL otherwise)
     long long* dbg_ts;
+    int prefetch;         // TK_GOGORO_PREFETCH: L2 prefetch ahead of griddepcontrol.wait (default: thin grids only)
 };
 
 static void pair_uniform(const double* in, float* out) { out[0] = static_cast<float>(in[0]); out[1] = static_cast<float>(in[1] - in[0]); }
@@ -782,6 +946,8 @@ static void fill_kparams(const TkGogoro* h, KParams& k) {
     k.max_episode_length = P.max_episode_length; k.speed_freq = P.speed_freq_update; k.yaw_freq = P.yaw_freq_update;
     k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.action_history, 16) && aligned_to(B.obs_buf, 16) &&
                aligned_to(B.buffer_obs, 16);
+    k.prefetch = h->prefetch;
+    { const char* env = getenv("TK_GOGORO_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
     k.max_steering = P.max_steering; k.max_steering_change = P.max_steering_change;
     pair_normal(P.imu_filter_noise, k.imu_filter); pair_normal(P.imu_noise, k.imu); pair_normal(P.speed_sensor_noise, k.speed_sensor);
     pair_normal(P.steering_action_noise, k.steer_action); pair_uniform(P.speed_range, k.speed);
@@ -814,6 +980,13 @@ int tk_gogoro_create(const TkGogoroParams* params, TkGogoro** out) {
     h->last_grid = 0;
     h->dbg_ts = nullptr;
     h->epoch_used = false;
+    {   // the prefetch pays while the whole grid is resident at once (the CTAs sit at the wait while the previous kernel
+        // drains); on deep grids it would only double the requests of a bandwidth-bound stream
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, params->device);
+        h->prefetch = (h->tiles <= 4 * sms) ? 1 : 0;
+        if (const char* env = getenv("TK_GOGORO_PREFETCH")) h->prefetch = atoi(env);
+    }
     h->partials = nullptr; h->counts = nullptr; h->bases = nullptr; h->step_dev = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMalloc(&h->counts, sizeof(int) * 2 * h->tiles);
@@ -962,7 +1135,11 @@ int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream
         cfg.attrs = attr;
         cfg.numAttrs = 1;
         float* no_out = nullptr;
-        cudaLaunchKernelEx(&cfg, gogoro_tile_kernel<0>, k, no_out);
+        // thin grids with in-kernel noise: the speculative-reset variant (see spec_reset); TK_GOGORO_SPEC=0/1 overrides
+        bool spec = mode == TK_NOISE_PHILOX && h->prefetch != 0;
+        if (const char* env = getenv("TK_GOGORO_SPEC")) spec = mode == TK_NOISE_PHILOX && atoi(env) != 0;
+        if (spec) cudaLaunchKernelEx(&cfg, gogoro_tile_kernel<0, true>, k, no_out);
+        else cudaLaunchKernelEx(&cfg, gogoro_tile_kernel<0, false>, k, no_out);
     }
     TK_CUDA(cudaGetLastError());
     h->last_grid = kStatSlots;

@@ -17,9 +17,10 @@ from thormang_isaacgym_b200 import _native as nat  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--envs", type=int, default=16384)
 ap.add_argument("--task", default="humanoid", choices=["humanoid", "gogoro"])
+ap.add_argument("--sets", type=int, default=8, help="state sets rotated (8 x 15 MB stays L2-resident; bench.py rotates > 2x L2)")
 a = ap.parse_args()
 n = a.envs
-envs = [G._MAKERS[a.task](n, 10 + s, "cuda:0")[0] for s in range(8)]
+envs = [G._MAKERS[a.task](n, 10 + s, "cuda:0")[0] for s in range(max(3, a.sets))]
 lib = nat.lib()
 probe = lib.tk_debug_humanoid_timeline if a.task == "humanoid" else lib.tk_debug_gogoro_timeline
 probe.argtypes = [C.c_void_p, C.c_void_p]
@@ -30,10 +31,12 @@ for _ in range(6):          # past the transient: the synthetic state's fallen e
         e.post_physics_step()
 torch.cuda.synchronize()
 buf = torch.zeros((tiles, 8), dtype=torch.int64, device="cuda:0")
-e = envs[3]
+ia, ib = (3, 4) if len(envs) >= 6 else (0, 1)
+e = envs[ia]
 probe(e._handle, C.c_void_p(buf.data_ptr()))
-# flush L2 with the other sets, then the probed launch
-for o in envs[4:] + envs[:3]:
+others = [o for k, o in enumerate(envs) if k not in (ia, ib)]
+# flush L2 with the other sets (when there are enough of them), then the probed launch
+for o in others:
     o.post_physics_step()
 torch.cuda.synchronize()
 e_reset_before = e.reset_buf.clone().cpu()
@@ -41,13 +44,13 @@ e_reset_before = e.reset_buf.clone().cpu()
 # the launch behind it is probed as well: the distance between "every tile of A has finished" and "the first tile of B has
 # passed griddepcontrol.wait" is the launch-to-launch gap that no tile stamp of a single launch can see
 buf_b = torch.zeros((tiles, 8), dtype=torch.int64, device="cuda:0")
-eb = envs[4]
+eb = envs[ib]
 probe(eb._handle, C.c_void_p(buf_b.data_ptr()))
-envs[1].post_physics_step()
-envs[2].post_physics_step()
+for o in others:       # the probed sets were touched longest ago: HBM-cold when --sets is large
+    o.post_physics_step()
 e.post_physics_step()
 eb.post_physics_step()
-envs[5].post_physics_step()
+others[0].post_physics_step()
 torch.cuda.synchronize()
 t = buf.cpu().double()
 tb = buf_b.cpu().double()
@@ -57,13 +60,17 @@ print(f"launch A: first wait release -> last tile done {(t[:, 6].max() - t[:, 0]
       f"A start -> B start {(tb[:, 0].min() - t[:, 0].min()) / 1e3:.2f} us")
 t0 = t[:, 0].min()
 names = ["start", "scalars issued", "scalars landed", "bulk landed", "inputs in regs", "math+STS done", "store read done"]
+phases = ["issue", "scalar wait", "bulk wait", "reset+reg read", "math+STS", "store"]
+if a.task == "gogoro":      # tk_gogoro.cu stamps: 0 wait released, 1 scalars landed + ballots, 2 reset prologue, 3 tile landed + patched, 4 math done, 5 CTA barrier, 6 stores read
+    names = ["start", "scalars landed", "reset prologue", "tile landed", "math done", "cta barrier", "store read done"]
+    phases = ["scalar round trip", "reset prologue", "tile wait", "math", "barrier", "store"]
 print(f"envs flagged for reset in the probed step: {int((e_reset_before != 0).sum())} of {n}")
 print(f"tiles {tiles}; kernel span {(t[:, 6].max() - t0) / 1e3:.2f} us")
 for i, nm in enumerate(names):
     col = t[:, i] - t0
     print(f"{nm:18s} min {col.min()/1e3:7.2f}  median {col.median()/1e3:7.2f}  max {col.max()/1e3:7.2f} us")
 d = t[:, 1:7] - t[:, 0:6]
-for i, nm in enumerate(["issue", "scalar wait", "bulk wait", "reset+reg read", "math+STS", "store"]):
+for i, nm in enumerate(phases):
     print(f"  phase {nm:14s} median {d[:, i].median()/1e3:6.2f}  mean {d[:, i].mean()/1e3:6.2f}  p95 {d[:, i].quantile(0.95)/1e3:6.2f} us")
 
 # the stragglers: the ten tiles that finish last, with their stamps (us after the first start) and reset counts
