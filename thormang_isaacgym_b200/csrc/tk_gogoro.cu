@@ -984,7 +984,9 @@ int tk_gogoro_create(const TkGogoroParams* params, TkGogoro** out) {
         // drains); on deep grids it would only double the requests of a bandwidth-bound stream
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, params->device);
-        h->prefetch = (h->tiles <= 4 * sms) ? 1 : 0;
+        // measured (HBM-cold, prefetch + speculative reset on / off): 65536 envs 6.2 / 8.4 us, 131072 7.1 / 9.8, 262144 13.5 / 14.7,
+        // 1048576 47.6 / 40.0 -- the switch sits at two waves of resident CTAs
+        h->prefetch = (h->tiles <= 16 * sms) ? 1 : 0;
         if (const char* env = getenv("TK_GOGORO_PREFETCH")) h->prefetch = atoi(env);
     }
     h->partials = nullptr; h->counts = nullptr; h->bases = nullptr; h->step_dev = nullptr;

@@ -96,9 +96,12 @@ struct KParams {
     long long* dbg_ts;          // developer timeline probe (tools/tile_timeline.py); NULL in normal use
     int stagger_cycles;         // first-wave stagger: resident slot s of an SM delays its bulk loads by s * cycles (0 = off)
     int stagger_ctas;           // CTAs of the first wave (resident CTAs per SM x SMs)
+    int prefetch_ctas;          // prefetch mode 2: the CTAs (lowest block ids = first resident slots of every SM) that prefetch
     int stagger_free;           // the first `stagger_free` resident slots of every SM start at once (fills the memory pipe), the rest are spaced
     int sm_count;
     int prefetch;               // L2 prefetch of the tile inputs ahead of griddepcontrol.wait
+    int warm;                   // warm_ahead_of_wait (tk_humanoid_tile.cuh): 1 translations, 2 initial rows of the tile
+    int dbg_reset;              // developer ablation (TK_HUMANOID_DBG_RESET=1): reset flags ignored
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -498,6 +501,7 @@ struct TkHumanoid {
     int stagger_free;     // TK_HUMANOID_STAGGER_FREE
     int smem_pad;         // TK_HUMANOID_SMEM_PAD: extra dynamic shared memory per CTA (caps the resident CTAs per SM)
     int prefetch;         // TK_HUMANOID_PREFETCH: L2 prefetch ahead of griddepcontrol.wait (default: small grids only)
+    int warm;             // TK_HUMANOID_WARM: see KParams::warm
     int sm_count;
     int quad;             // TK_HUMANOID_QUAD: four-warp tile kernel (tk_humanoid_quad.cuh) 1 | one-warp kernel 0; default by grid size
     unsigned long long* step_dev;
@@ -544,7 +548,11 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     k.init_root = B.initial_root_states; k.init_dof_pos = B.initial_dof_pos; k.ep_return = B.episode_return;
     k.partials = h->partials; k.tile_rank_base = h->tile_base; k.dbg_ts = h->dbg_ts; k.step_dev = h->step_dev;
     k.prefetch = h->prefetch;
+    k.warm = h->warm;
+    { const char* env = getenv("TK_HUMANOID_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
     k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count; k.stagger_free = h->stagger_free;
+    k.prefetch_ctas = k.stagger_ctas;
+    if (const char* env = getenv("TK_HUMANOID_PREFETCH_SLOTS")) k.prefetch_ctas = atoi(env) * h->sm_count;
     k.unit_a = nullptr; k.unit_b = nullptr; k.noise_rows = 0; k.seed = 0; k.step = 0; k.env_off = 0;
     k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs;
@@ -620,6 +628,8 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     // four-warp tiles while the grid is at most a few waves deep, one-warp tiles (most bytes in flight per SM) beyond
     h->quad = (h->tiles <= kQuadMaxTilesPerSm * h->sm_count) ? 1 : 0;
     if (const char* env = getenv("TK_HUMANOID_QUAD")) h->quad = atoi(env) != 0;
+    h->warm = 0;          // measured: no gain at 16384 envs (6.55 vs 6.58 / 7.09 us with 1 / 3), -3 % at 32768, +8 % at 65536
+    if (const char* env = getenv("TK_HUMANOID_WARM")) h->warm = atoi(env);
     // the four-warp kernel only runs single-wave grids, where spacing the CTAs merely delays them (6.5 us with 0 cycles,
     // 6.8 with 500, 7.4 with 1000 at 16384 envs)
     if (h->quad && !getenv("TK_HUMANOID_STAGGER")) h->stagger_cycles = 0;

@@ -104,6 +104,8 @@ __global__ void __launch_bounds__(kQuadThreads, TK_HUMANOID_QUAD_MIN_CTAS) human
         }
     }
     const float warm = p.dt + p.tgt[0] + p.isr[3] + p.b0[0] + p.b1[2] + p.termination_height;   // constant-bank lines of the torso math
+    if (bulk && warp >= 2) warm_ahead_of_wait<D, OBS>(p, env0, tid - 64, FUSED);
+    const unsigned long long step_now = FUSED ? step_ahead_of_wait(p) : 0ull;
 
     asm volatile("griddepcontrol.wait;" ::: "memory");
     TK_QSTAMP(0);
@@ -144,7 +146,7 @@ __global__ void __launch_bounds__(kQuadThreads, TK_HUMANOID_QUAD_MIN_CTAS) human
             pot_old = p.pot[n];
             if (FUSED) {
                 prog = p.progress[n] + 1;                         // humanoid.py:288
-                do_reset = p.reset[n] != 0;                       // :291
+                do_reset = p.reset[n] != 0 && !p.dbg_reset;                       // :291
                 if (p.ep_return) ret_old = p.ep_return[n];
                 if (p.randomize) p.randomize[n] += 1;             // :289
             }
@@ -171,7 +173,7 @@ __global__ void __launch_bounds__(kQuadThreads, TK_HUMANOID_QUAD_MIN_CTAS) human
             bits &= bits - 1;
             if (q == warp) {
                 pre_e = e;
-                reset_env_values<D>(p, env0 + e, rank0 + q, lane, &pre_pv, &pre_root);
+                reset_env_values<D>(p, env0 + e, rank0 + q, lane, &pre_pv, &pre_root, step_now);
             }
         }
     }
@@ -191,7 +193,7 @@ __global__ void __launch_bounds__(kQuadThreads, TK_HUMANOID_QUAD_MIN_CTAS) human
             if (q >= 4 && (q & 3) == warp) {   // more than four resets in one tile: the rest after the wait
                 float2 pv;
                 float rv;
-                reset_env_values<D>(p, env0 + e, rank0 + q, lane, &pv, &rv);
+                reset_env_values<D>(p, env0 + e, rank0 + q, lane, &pv, &rv, step_now);
                 if (lane < D) reinterpret_cast<float2*>(in + WT::oDof)[e * D + lane] = pv;
                 if (lane < kRoot) in[WT::oRoot + e * kRoot + lane] = rv;
             }

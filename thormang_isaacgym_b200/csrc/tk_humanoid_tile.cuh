@@ -65,14 +65,15 @@ __device__ __forceinline__ void reset_env_fetch(const KParams& p, int ne, int la
     *rv = (lane < kRoot) ? p.init_root[static_cast<size_t>(ne) * kRoot + lane] : 0.0f;   // :265-267 root row <- initial_root_states
 }
 template <int D>   // reset_idx of humanoid.py:253-279 and ant.py:247-271 (identical bodies)
-__device__ __forceinline__ void reset_env_apply(const KParams& p, int ne, int rank, int lane, float idp, float rv, float2* pv_out) {
+__device__ __forceinline__ void reset_env_apply(const KParams& p, int ne, int rank, int lane, float idp, float rv, float2* pv_out,
+                                                unsigned long long step_now) {
     const long long row = (p.noise_mode == TK_NOISE_COMPACT) ? rank : ne;
     float2 pv = make_float2(0.0f, 0.0f);
     if (lane < D) {
         const int j = lane;
         float ua = 0.5f, ub = 0.5f;
         if (p.noise_mode == TK_NOISE_PHILOX) {
-            Philox4 r = philox_env(p.seed, effective_step(p.step, p.step_dev), p.env_off + ne, static_cast<uint32_t>(j >> 1));
+            Philox4 r = philox_env(p.seed, step_now, p.env_off + ne, static_cast<uint32_t>(j >> 1));
             ua = u01((j & 1) ? r.z : r.x);
             ub = u01((j & 1) ? r.w : r.y);
         } else if (p.noise_mode != TK_NOISE_NONE && row < p.noise_rows) {
@@ -90,19 +91,67 @@ __device__ __forceinline__ void reset_env_apply(const KParams& p, int ne, int ra
     *pv_out = pv;
 }
 template <int D>
-__device__ __forceinline__ void reset_env_values(const KParams& p, int ne, int rank, int lane, float2* pv_out, float* root_out) {
+__device__ __forceinline__ void reset_env_values(const KParams& p, int ne, int rank, int lane, float2* pv_out, float* root_out,
+                                                 unsigned long long step_now) {
     float idp, rv;
     reset_env_fetch<D>(p, ne, lane, &idp, &rv);    // both global reads are requested before the noise is computed
-    reset_env_apply<D>(p, ne, rank, lane, idp, rv, pv_out);
+    reset_env_apply<D>(p, ne, rank, lane, idp, rv, pv_out, step_now);
     *root_out = rv;
+}
+
+// The Philox step of this launch, resolved AHEAD of griddepcontrol.wait: the device-side noise epoch (CUDA-graph replays) is
+// written only by tk_humanoid_advance_epoch's single-thread kernel, a plain launch that never triggers its dependents
+// early -- whatever follows it in the stream starts after it has completed, and this grid starts no earlier than its own
+// predecessor.  (Read inside the reset path it was a dependent DRAM round trip on exactly the tiles that end a thin launch.)
+__device__ __forceinline__ unsigned long long step_ahead_of_wait(const KParams& p) {
+    unsigned long long step_now = p.step;
+    if (p.noise_mode == TK_NOISE_PHILOX && p.step_dev) {
+        unsigned long long ep;
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(ep) : "l"(p.step_dev) : "memory");
+        step_now = p.step + (ep << 32);
+    }
+    return step_now;
+}
+// Ahead of the wait as well (p.warm, host decides by grid shape): bit 0 -- one line of every array a reset reads late or the
+// tile writes, not for the data but for the TRANSLATION (bench.py rotates its state sets over more than the 256 MB the TLB
+// reaches: the first touch of a page is a walk of several dependent DRAM reads, and a store that misses holds back the
+// completion of the grid); bit 1 -- the tile's rows of initial_dof_pos / initial_root_states in full (+136 B / env of
+// reads: thin grids only, where the launch is bound by the life of its slowest tile -- one holding a reset -- not by bytes).
+template <int D, int OBS>
+__device__ __forceinline__ void warm_ahead_of_wait(const KParams& p, int env0, int t, bool fused) {
+    if (!p.warm) return;
+    if (p.warm & 2) {
+        constexpr int kDofLines = (kTile * D * 4 + 127) / 128, kRootLines = (kTile * kRoot * 4 + 127) / 128;
+        if (fused && t < kDofLines) prefetch_l2(reinterpret_cast<const char*>(p.init_dof_pos + static_cast<size_t>(env0) * D) + 128 * t);
+        if (fused && t < kRootLines) prefetch_l2(reinterpret_cast<const char*>(p.init_root + static_cast<size_t>(env0) * kRoot) + 128 * t);
+    }
+    if (p.warm & 1) {
+        const void* a = nullptr;
+        switch (t) {
+            case 16: a = fused ? p.init_dof_pos + static_cast<size_t>(env0) * D : nullptr; break;
+            case 17: a = fused ? p.init_root + static_cast<size_t>(env0) * kRoot : nullptr; break;
+            case 18: a = p.obs + static_cast<size_t>(env0) * OBS; break;
+            case 19: a = fused ? p.rew + env0 : nullptr; break;
+            case 20: a = p.prev_pot + env0; break;
+            case 21: a = (fused && p.timeout) ? p.timeout + env0 : nullptr; break;
+            case 22: a = p.obs2 ? p.obs2 + static_cast<size_t>(env0) * OBS : nullptr; break;
+            default: break;
+        }
+        if (a) prefetch_l2(a);
+    }
 }
 
 #ifndef TK_HUMANOID_MIN_CTAS
 #define TK_HUMANOID_MIN_CTAS 12
 #endif
 
+#ifdef TK_HUMANOID_MAXNREG      // developer knob: a register cap instead of a CTA-count bound (the two cannot be combined)
+#define TK_HUMANOID_BOUNDS __maxnreg__(TK_HUMANOID_MAXNREG)
+#else
+#define TK_HUMANOID_BOUNDS __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS)
+#endif
 template <class S, bool FUSED>
-__global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_kernel(const __grid_constant__ KParams p) {
+__global__ void TK_HUMANOID_BOUNDS humanoid_warp_kernel(const __grid_constant__ KParams p) {
     using L = S;
     using WT = WarpTile<S>;
     constexpr int D = S::D;
@@ -141,7 +190,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
         else if (lane == 2) bulk_prefetch_l2(g_act, kTile * D * 4);
         else if (lane == 3) bulk_prefetch_l2(g_root, kTile * kRoot * 4);
         else if (lane == 4) bulk_prefetch_l2(g_sens, kTile * kSensor * 4);
-    } else if (bulk && p.prefetch == 2 && blockIdx.x < static_cast<unsigned>(p.stagger_ctas)) {
+    } else if (bulk && p.prefetch == 2 && blockIdx.x < static_cast<unsigned>(p.prefetch_ctas)) {
         // through the load/store unit, one 128-byte line per instruction, first-wave CTAs only (later CTAs start
         // after the dependency has resolved: a prefetch would only add requests)
         auto pf = [&](const float* base, int bytes) {
@@ -164,6 +213,8 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
     // touch both ends of the per-DOF constant tables so that their constant-cache lines are fetched now, not in the
     // middle of the math (the result only feeds a never-true predicate)
     const float warm = p.lo[0] + p.lo[D - 1] + p.hi[0] + p.hi[D - 1] + p.rinv[0] + p.rinv[D - 1] + p.dt + p.tgt[0];
+    if (bulk) warm_ahead_of_wait<D, OBS>(p, env0, lane, FUSED);
+    const unsigned long long step_now = FUSED ? step_ahead_of_wait(p) : 0ull;
     // everything above (parameter fetch, address arithmetic, mbarrier init) may overlap the drain of the previous kernel
     asm volatile("griddepcontrol.wait;" ::: "memory");
     TK_STAMP(0);
@@ -204,7 +255,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
         pot_old = p.pot[n];
         if (FUSED) {
             prog = p.progress[n] + 1;                              // humanoid.py:288
-            do_reset = p.reset[n] != 0;                            // :291
+            do_reset = p.reset[n] != 0 && !p.dbg_reset;                            // :291
             if (p.ep_return) ret_old = p.ep_return[n];
             if (p.randomize) p.randomize[n] += 1;                  // :289
         }
@@ -243,7 +294,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
                 if (bits) {
                     const int e = __ffs(bits) - 1;
                     bits &= bits - 1;
-                    reset_env_apply<D>(p, env0 + e, rank0 + q, lane, idp[q], pre_root[q], &pre_pv[q]);
+                    reset_env_apply<D>(p, env0 + e, rank0 + q, lane, idp[q], pre_root[q], &pre_pv[q], step_now);
                 }
             }
         }
@@ -269,7 +320,7 @@ __global__ void __launch_bounds__(kTile, TK_HUMANOID_MIN_CTAS) humanoid_warp_ker
             bits &= bits - 1;
             float2 pv;
             float rv;
-            reset_env_values<D>(p, env0 + e, rank0 + q, lane, &pv, &rv);
+            reset_env_values<D>(p, env0 + e, rank0 + q, lane, &pv, &rv, step_now);
             if (lane < D) reinterpret_cast<float2*>(buf + WT::oDof)[e * D + lane] = pv;
             if (lane < kRoot) buf[WT::oRoot + e * kRoot + lane] = rv;
         }
