@@ -49,6 +49,7 @@ struct KParams {
     int n, max_episode_length, base_index, num_knee;
     int knee[kMaxKnee];
     int vec_ok;
+    int dbg_reset;     // developer ablation (TK_ANYMAL_DBG_RESET=1): reset flags ignored
     float dof_pos_scale, dof_vel_scale, action_scale, clip_actions;
     float k_lin, k_ang, k_torque;           // (float)(scale * dt), anymal.py:96-97
     float cmd_x[2], cmd_y[2], cmd_yaw[2];   // lo, (hi - lo) formed in double
@@ -110,7 +111,7 @@ __global__ void __launch_bounds__(kTile) anymal_tile_kernel(const __grid_constan
         prog = p.progress[n];
         if (MODE == 0) {
             prog += 1;                                                              // :235
-            do_reset = p.reset[n] != 0;                                             // :237
+            do_reset = p.reset[n] != 0 && !p.dbg_reset;                             // :237
             if (do_reset) prog = 0;                                                 // :309
             if (p.ep_return) ret_old = p.ep_return[n];
         }
@@ -346,6 +347,7 @@ static void fill_kparams(const TkAnymal* h, KParams& k) {
     k.env_off = 0; k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs; k.max_episode_length = P.max_episode_length; k.base_index = P.base_index; k.num_knee = P.num_knee;
     for (int i = 0; i < kMaxKnee; ++i) k.knee[i] = P.knee_indices[i];
+    { const char* env = getenv("TK_ANYMAL_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
     k.vec_ok = aligned_to(B.root_states, 16) && aligned_to(B.dof_state, 16) && aligned_to(B.torques, 16) &&
                aligned_to(B.contact_forces, 16) && aligned_to(B.commands, 16) && aligned_to(B.obs_buf, 16);
     k.dof_pos_scale = P.dof_pos_scale; k.dof_vel_scale = P.dof_vel_scale; k.action_scale = P.action_scale;

@@ -89,6 +89,8 @@ struct KParams {
     int delay_w, use_delay;
     int variant;                   // kPaper | kTurning
     int vec_ok;
+    int spec;          // speculative reset draws ahead of the wait (thin grids; TK_PAPER_SPEC overrides)
+    int dbg_reset;     // developer ablation (TK_PAPER_DBG_RESET=1): reset flags ignored
     int stagger_cycles, stagger_ctas, sm_count;   // first-wave stagger, see paper_tile_kernel
     int fin_vec_ok;                // rew_buf / episode_return / reset_buf 16-byte aligned: 128-bit accesses in the finalize kernel
     float max_steering, start_speed;
@@ -150,7 +152,10 @@ __device__ __forceinline__ float reward_partial_turning(const float* o, bool* fe
 // randomize :557-566 + reset_idx :599-688 for env `ne`, executed by ONE thread (rare, divergent).  u = the 5 unit draws.
 // Writes the global state except obs_buf (the caller's shift phase writes the zero frames); returns the new root row.
 // VAR = kTurning: gogoro_realistic_turning.py randomize :559-568, generate_spawn_r :572-588, reset_idx :601-686 (u = 8 draws)
-template <int VAR>
+// ROWS = false (fused kernel): only what the env's own observation depends on -- scalars, quaternion, velocities; the row
+// traffic (root_reset -> root, thormang_pose -> state_dof, ring / delay-line zeroing) is done warp-cooperatively at the end
+// of the kernel by reset_rows_warp.  The observation reads no position column (:775-778), so r[0..1] stay as staged.
+template <int VAR, bool ROWS = true>
 __device__ __forceinline__ void reset_env(const KParams& p, long long ne, const float* u, float* r, long long* delay_out,
                                           float* imu_x_out, float* speed_off_out, float* yaw_tgt_out) {
     p.curent_speed[ne] = uniform_of(p.speed, u[0]);                                 // :562
@@ -161,8 +166,10 @@ __device__ __forceinline__ void reset_env(const KParams& p, long long ne, const 
     p.curent_speed_offset[ne] = so;
     const float ix = uniform_of(p.imu_x, u[4]);                                     // :655
     p.curent_imu_x_offset[ne] = ix;
+    if (ROWS) {
 #pragma unroll
-    for (int c = 0; c < kRoot; ++c) r[c] = p.root_reset[ne * kRoot + c];            // :618
+        for (int c = 0; c < kRoot; ++c) r[c] = p.root_reset[ne * kRoot + c];        // :618
+    }
     r[2] = 0.03f;                                                                   // :619
     float yaw_tgt = 0.0f;                                                           // :571 (paper file)
 #pragma unroll
@@ -189,19 +196,41 @@ __device__ __forceinline__ void reset_env(const KParams& p, long long ne, const 
         r[3] = 0.0f; r[4] = 0.0f; r[5] = 0.0f; r[6] = 1.0f;                         // :573-575,635: euler (0,0,0) -> identity, exactly
         if (p.start_speed != 0.0f) { r[7] = p.start_speed * 1.0f; r[8] = p.start_speed * 0.0f; }   // :638-641, cos(0), sin(0)
     }
+    if (ROWS) {
 #pragma unroll
-    for (int c = 0; c < kRoot; ++c) p.root[ne * kRoot + c] = r[c];                  // :645
-    float2* ds = reinterpret_cast<float2*>(p.state_dof) + ne * p.num_dof;
-    for (int j = 0; j < p.num_dof; ++j) ds[j] = make_float2(p.thormang_pose[ne * p.num_dof + j], 0.0f);   // :647-648
-    float4* cr = reinterpret_cast<float4*>(p.clean_ring + ne * kObs);
-    for (int j = 0; j < kChunks; ++j) cr[j] = make_float4(0.f, 0.f, 0.f, 0.f);      // :681
-    float4* cm = reinterpret_cast<float4*>(p.cmd_ring + ne * kBuf);
+        for (int c = 0; c < kRoot; ++c) p.root[ne * kRoot + c] = r[c];              // :645
+        float2* ds = reinterpret_cast<float2*>(p.state_dof) + ne * p.num_dof;
+        for (int j = 0; j < p.num_dof; ++j) ds[j] = make_float2(p.thormang_pose[ne * p.num_dof + j], 0.0f);   // :647-648
+        float4* cr = reinterpret_cast<float4*>(p.clean_ring + ne * kObs);
+        for (int j = 0; j < kChunks; ++j) cr[j] = make_float4(0.f, 0.f, 0.f, 0.f);  // :681
+        float4* cm = reinterpret_cast<float4*>(p.cmd_ring + ne * kBuf);
 #pragma unroll
-    for (int j = 0; j < kBuf / 4; ++j) cm[j] = make_float4(0.f, 0.f, 0.f, 0.f);     // :681 (channel 6 of the clean frames)
-    for (int j = 0; j < p.delay_w; ++j) p.command_history[ne * p.delay_w + j] = 0.0f;   // :686
+        for (int j = 0; j < kBuf / 4; ++j) cm[j] = make_float4(0.f, 0.f, 0.f, 0.f); // :681 (channel 6 of the clean frames)
+        for (int j = 0; j < p.delay_w; ++j) p.command_history[ne * p.delay_w + j] = 0.0f;   // :686
+    }
     p.curent_command[ne] = 0.0f;                                                    // :683
     p.yaw_command[ne] = yaw_tgt;                                                    // :685 (spawn_yaw_tgt)
     *delay_out = delay; *imu_x_out = ix; *speed_off_out = so; *yaw_tgt_out = yaw_tgt;
+}
+
+// The row traffic of one reset, by a whole warp at the end of the fused kernel (the single thread walked 13 + 39 dependent
+// load -> store pairs and 47 zero stores in the middle of its tile's math: 3.5 us of a 27 us launch at 65536 envs).  q6 = the
+// env's new quaternion and planar velocity (columns 3..8), broadcast from its lane by the caller.  The ring slot and the
+// command-ring entry this step has just written (after the reset, as in the reference: :681 then :502-503) are left alone.
+__device__ __forceinline__ void reset_rows_warp(const KParams& p, long long ne, int lane, const float* q6, int slot) {
+    float rv = 0.0f;
+    if (lane < 2) rv = p.root_reset[ne * kRoot + lane];                             // :618
+    rv = (lane == 2) ? 0.03f : rv;                                                  // :619
+#pragma unroll
+    for (int c = 0; c < 6; ++c) rv = (lane == 3 + c) ? q6[c] : rv;                  // :635-641
+    if (lane < kRoot) p.root[ne * kRoot + lane] = rv;                               // :645 (columns 9..12 <- 0, :636)
+    float2* ds = reinterpret_cast<float2*>(p.state_dof) + ne * p.num_dof;
+    for (int j = lane; j < p.num_dof; j += 32) ds[j] = make_float2(p.thormang_pose[ne * p.num_dof + j], 0.0f);   // :647-648
+    float4* cr = reinterpret_cast<float4*>(p.clean_ring + ne * kObs);
+    for (int j = lane; j < kChunks; j += 32)
+        if ((j >> 1) != slot) cr[j] = make_float4(0.f, 0.f, 0.f, 0.f);              // :681
+    if (lane < kBuf && lane != slot) p.cmd_ring[ne * kBuf + lane] = 0.0f;           // :681 (channel 6 of the clean frames)
+    for (int j = lane; j < p.delay_w; j += 32) p.command_history[ne * p.delay_w + j] = 0.0f;   // :686
 }
 
 struct Smem {
@@ -228,6 +257,34 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
     // previous kernel of the stream drains; nothing of global memory is touched before griddepcontrol.wait
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (bulk && lane == 0) mbar_init(&s.bar, 1);
+    // Ahead of the wait: everything that is a pure function of (seed, step, global env id).  The noise epoch of CUDA-graph
+    // replays is written only by tk_gogoro_paper_advance_epoch's single-thread kernel, a plain launch that never triggers its
+    // dependents early (see tk_gogoro.cu).  Sensor draws always; the reset draws speculatively for EVERY env on thin grids
+    // (p.spec), where the launch is as long as its slowest tile -- one that holds a reset.
+    unsigned long long step_now = p.step;
+    if (philox && p.step_dev) {
+        unsigned long long ep;
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(ep) : "l"(p.step_dev) : "memory");
+        step_now = p.step + (ep << 32);
+    }
+    float un[kSensorNoise];
+    float su_b = 0.5f, yu_b = 0.5f;        // the two resample uniforms ride in the second sensor block
+#pragma unroll
+    for (int c = 0; c < kSensorNoise; ++c) un[c] = 0.5f;
+    if (MODE != 2 && philox) {
+        Philox4 a = philox_env(p.seed, step_now, p.env_off + n, kStreamSensorA);
+        Philox4 b = philox_env(p.seed, step_now, p.env_off + n, kStreamSensorB);
+        un[0] = u01(a.x); un[1] = u01(a.y); un[2] = u01(a.z); un[3] = u01(a.w); un[4] = u01(b.x); un[5] = u01(b.y);
+        su_b = u01(b.z); yu_b = u01(b.w);
+    }
+    float u_spec[kResetNoiseTurning];
+    const bool spec = MODE == 0 && philox && p.spec != 0;
+    if (spec) {
+        Philox4 a = philox_env(p.seed, step_now, p.env_off + n, kStreamResetA);
+        Philox4 b = philox_env(p.seed, step_now, p.env_off + n, kStreamResetB);
+        u_spec[0] = u01(a.x); u_spec[1] = u01(a.y); u_spec[2] = u01(a.z); u_spec[3] = u01(a.w); u_spec[4] = u01(b.x);
+        u_spec[5] = u01(b.y); u_spec[6] = u01(b.z); u_spec[7] = u01(b.w);
+    }
     asm volatile("griddepcontrol.wait;" ::: "memory");
     // First-wave stagger (same finding as in the Humanoid kernel): the CTAs of the first wave start together, so every SM
     // would run load-all / math-all / store-all in lockstep; resident slot s of the first wave waits s * stagger_cycles.
@@ -235,7 +292,6 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
         const long long until = clock64() + static_cast<long long>(blockIdx.x / p.sm_count) * p.stagger_cycles;
         while (clock64() < until) __nanosleep(32);
     }
-    const unsigned long long step_now = philox ? effective_step(p.step, p.step_dev) : 0ull;
     const unsigned long long tick = p.tick[0];
     const int slot = static_cast<int>(tick % kBuf);               // ring slot written by this step
     if (bulk) {
@@ -269,7 +325,7 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
         if (MODE != 2) { imu_x = p.curent_imu_x_offset[n]; speed_off = p.curent_speed_offset[n]; prog = p.progress[n]; }
         if (MODE == 0) {
             prog += 1;                                                              // :384
-            do_reset = p.reset[n] != 0;                                             // :385
+            do_reset = p.reset[n] != 0 && !p.dbg_reset;                             // :385
             if (do_reset) prog = 0;                                                 // :678
         }
     }
@@ -277,27 +333,24 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
     if (bulk) mbar_wait(&s.bar, 0);
 
     float st_len = 0.f, st_tilt = 0.f, st_yaw = 0.f;
+    float reset_q6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // new quaternion + planar velocity of a reset env, for reset_rows_warp
     double dsum = 0.0;
     bool out_reset = false, out_timeout = false;
     if (valid) {
         float r[kRoot];
 #pragma unroll
         for (int c = 0; c < kRoot; ++c) r[c] = s.root[lane * kRoot + c];
-        float un[kSensorNoise];
-        if (MODE != 2) {
-            if (philox) {
-                Philox4 a = philox_env(p.seed, step_now, p.env_off + n, kStreamSensorA);
-                Philox4 b = philox_env(p.seed, step_now, p.env_off + n, kStreamSensorB);
-                un[0] = u01(a.x); un[1] = u01(a.y); un[2] = u01(a.z); un[3] = u01(a.w); un[4] = u01(b.x); un[5] = u01(b.y);
-            } else {
+        if (MODE != 2 && !philox) {
 #pragma unroll
-                for (int c = 0; c < kSensorNoise; ++c) un[c] = p.sensor_unit ? p.sensor_unit[n * kSensorNoise + c] : 0.5f;
-            }
+            for (int c = 0; c < kSensorNoise; ++c) un[c] = p.sensor_unit ? p.sensor_unit[n * kSensorNoise + c] : 0.5f;
         }
         if (MODE == 0 && do_reset) {
             constexpr int kCols = VAR == kTurning ? kResetNoiseTurning : kResetNoise;
             float u[kResetNoiseTurning];
-            if (philox) {
+            if (spec) {
+#pragma unroll
+                for (int c = 0; c < kResetNoiseTurning; ++c) u[c] = u_spec[c];
+            } else if (philox) {
                 Philox4 a = philox_env(p.seed, step_now, p.env_off + n, kStreamResetA);
                 Philox4 b = philox_env(p.seed, step_now, p.env_off + n, kStreamResetB);
                 u[0] = u01(a.x); u[1] = u01(a.y); u[2] = u01(a.z); u[3] = u01(a.w); u[4] = u01(b.x);
@@ -306,7 +359,9 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
 #pragma unroll
                 for (int c = 0; c < kCols; ++c) u[c] = p.reset_unit ? p.reset_unit[n * kCols + c] : 0.5f;
             }
-            reset_env<VAR>(p, n, u, r, &delay, &imu_x, &speed_off, &yaw_cmd);
+            reset_env<VAR, false>(p, n, u, r, &delay, &imu_x, &speed_off, &yaw_cmd);
+#pragma unroll
+            for (int c = 0; c < 6; ++c) reset_q6[c] = r[3 + c];
             cur_cmd = 0.0f;
             if (p.ep_return) p.ep_return[n] = 0.0f;
         }
@@ -397,8 +452,7 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
             if (do_speed || do_yaw) {
                 float su = 0.5f, yu = 0.5f;
                 if (philox) {
-                    Philox4 b = philox_env(p.seed, step_now, p.env_off + n, kStreamSensorB);
-                    su = u01(b.z); yu = u01(b.w);
+                    su = su_b; yu = yu_b;
                 } else {
                     if (p.speed_unit) su = p.speed_unit[n];
                     if (p.yaw_unit) yu = p.yaw_unit[n];
@@ -447,12 +501,23 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
         if (lane == 0) {
             bulk_store(obs_tile, s.frames, kTile * kObs * 4);
             bulk_commit();
-            bulk_wait_read<0>();           // shared memory must stay alive until the engine has read it
         }
     } else {
         __syncwarp();
         for (int i = lane; i < nt * kObs; i += kTile) obs_tile[i] = s.frames[i];
     }
+    if (MODE == 0) {                       // the row traffic of this tile's resets, off every env's critical path
+        unsigned bits = __ballot_sync(0xffffffffu, do_reset);
+        while (bits) {
+            const int e = __ffs(bits) - 1;
+            bits &= bits - 1;
+            float q6[6];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) q6[c] = __shfl_sync(0xffffffffu, reset_q6[c], e);
+            reset_rows_warp(p, static_cast<long long>(env0) + e, lane, q6, slot);
+        }
+    }
+    if (bulk && lane == 0) bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
 }
 
 // Second kernel of a step: reward7 (:747) folded in, clip (:760), fall penalty (:761), episode return.  Four envs per
@@ -709,8 +774,11 @@ static void fill_kparams(const TkGogoroPaper* h, KParams& k) {
     k.n = P.num_envs; k.num_dof = P.num_dof; k.steering_joint = P.steering_joint; k.rear_wheel_joint = P.rear_wheel_joint;
     k.max_episode_length = P.max_episode_length; k.speed_freq = P.speed_freq_update; k.yaw_freq = P.yaw_freq_update;
     k.delay_w = P.delay_width; k.use_delay = P.use_steer_delay; k.variant = P.variant;
+    { const char* env = getenv("TK_PAPER_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
     k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.command_ring, 16);
     k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count;
+    k.spec = (h->tiles <= 16 * h->sm_count) ? 1 : 0;
+    if (const char* env = getenv("TK_PAPER_SPEC")) k.spec = atoi(env);
     k.fin_vec_ok = aligned_to(B.rew_buf, 16) && aligned_to(B.reset_buf, 16) && (!B.episode_return || aligned_to(B.episode_return, 16));
     k.max_steering = P.max_steering; k.start_speed = P.start_speed;
     k.delay_lo = static_cast<float>(P.command_delay[0]);
