@@ -49,6 +49,7 @@ struct KParams {
     int n, max_episode_length, base_index, num_knee;
     int knee[kMaxKnee];
     int vec_ok;
+    int stagger_cycles, stagger_ctas, sm_count;   // first-wave stagger (same finding as in the Humanoid kernel)
     int dbg_reset;     // developer ablation (TK_ANYMAL_DBG_RESET=1): reset flags ignored
     float dof_pos_scale, dof_vel_scale, action_scale, clip_actions;
     float k_lin, k_ang, k_torque;           // (float)(scale * dt), anymal.py:96-97
@@ -85,6 +86,12 @@ __global__ void __launch_bounds__(kTile) anymal_tile_kernel(const __grid_constan
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (bulk && lane == 0) mbar_init(&s.bar, 1);
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    // First-wave stagger: the CTAs of the first wave start together, so every SM would run load-all / math-all / store-all
+    // in lockstep and HBM would idle during the math; resident slot s of the first wave waits s * stagger_cycles.
+    if (MODE == 0 && p.stagger_cycles > 0 && blockIdx.x < static_cast<unsigned>(p.stagger_ctas)) {
+        const long long until = clock64() + static_cast<long long>(blockIdx.x / p.sm_count) * p.stagger_cycles;
+        while (clock64() < until) __nanosleep(32);
+    }
     const size_t e0 = static_cast<size_t>(env0);
     if (bulk) {
         if (lane == 0) {
@@ -331,7 +338,7 @@ struct TkAnymal {
     TkAnymalParams params;
     TkAnymalBuffers buf;
     bool bound, ran;
-    int tiles, use_pdl, sm_count;
+    int tiles, use_pdl, sm_count, stagger_cycles, stagger_slots;
     double* partials;
     unsigned long long* step_dev;
 };
@@ -347,6 +354,7 @@ static void fill_kparams(const TkAnymal* h, KParams& k) {
     k.env_off = 0; k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs; k.max_episode_length = P.max_episode_length; k.base_index = P.base_index; k.num_knee = P.num_knee;
     for (int i = 0; i < kMaxKnee; ++i) k.knee[i] = P.knee_indices[i];
+    k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count;
     { const char* env = getenv("TK_ANYMAL_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
     k.vec_ok = aligned_to(B.root_states, 16) && aligned_to(B.dof_state, 16) && aligned_to(B.torques, 16) &&
                aligned_to(B.contact_forces, 16) && aligned_to(B.commands, 16) && aligned_to(B.obs_buf, 16);
@@ -405,6 +413,14 @@ int tk_anymal_create(const TkAnymalParams* params, TkAnymal** out) {
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->sm_count = 148;
     cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, params->device);
+    h->stagger_cycles = 500; h->stagger_slots = 11;
+    {
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, anymal_tile_kernel<0>, kTile, 0) == cudaSuccess && occ > 0) h->stagger_slots = occ;
+        else cudaGetLastError();
+    }
+    if (h->tiles <= h->sm_count * 2) h->stagger_cycles = 0;      // a thin single wave is only delayed by it
+    if (const char* env = getenv("TK_ANYMAL_STAGGER")) h->stagger_cycles = atoi(env);
     h->partials = nullptr; h->step_dev = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * kStatSlots);

@@ -77,6 +77,7 @@ struct KParams {
     int feet[kA][kMaxFeet];
     int grip[kA][2];
     int vec_ok;                              // 16-byte aligned tile arrays: cp.async.bulk tile copies
+    int stagger_cycles, stagger_ctas, sm_count;   // first-wave stagger (same finding as in the Humanoid kernel)
     int contact_tile;                        // the tile's contact_forces block [kTile, nb, 3] is bulk-copied as well
     int obs32, vec_feet, contact8;           // 32-byte aligned obs rows; 16-/4-byte aligned air_time / last_contacts; 8-byte contact
     float lin_vel_scale, ang_vel_scale, dof_pos_scale, dof_vel_scale, action_scale, clip_actions, dt;
@@ -172,6 +173,12 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
     long long* ts = (MODE == 0 && p.dbg_ts) ? p.dbg_ts + (static_cast<size_t>(blockIdx.x) * 4 + (tid >> 5)) * 8 : nullptr;
 #define TK_OSTAMP(i) do { if (ts && lane == 0) { long long g_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_) :: "memory"); ts[i] = g_; } } while (0)
     TK_OSTAMP(0);
+    // First-wave stagger: the CTAs of the first wave start together, so every SM would run load-all / math-all / store-all
+    // in lockstep and HBM would idle during the math; resident slot s of the first wave waits s * stagger_cycles.
+    if (MODE == 0 && p.stagger_cycles > 0 && blockIdx.x < static_cast<unsigned>(p.stagger_ctas)) {
+        const long long until = clock64() + static_cast<long long>(blockIdx.x / p.sm_count) * p.stagger_cycles;
+        while (clock64() < until) __nanosleep(32);
+    }
     constexpr uint32_t kRootB = kTile * kActors * kRoot * 4, kDofB = kTile * kA * kDof * 2 * 4, kRowB = kTile * kA * kDof * 4;
     // The feet / gripper rows an env needs are 12 of its nb = 51 contact rows, 12 bytes each at a 612-byte stride: fetched by
     // the lanes they cost one 64-byte DRAM atom per row (768 B per env, more than the 612-byte block) and, worse, one L1 miss
@@ -765,7 +772,24 @@ static cudaError_t launch_tile_nf(const TkOp3* h, const KParams& k, cudaStream_t
         if (e != cudaSuccess) return e;
         opted = bytes;
     }
-    op3_tile_kernel<MODE, NF><<<h->tiles, threads_of<MODE>(), bytes, st>>>(k);
+    KParams kk = k;
+    kk.stagger_cycles = 0; kk.stagger_ctas = 0; kk.sm_count = h->sm_count;
+    if (MODE == 0) {
+        static int slots = -1, cycles = -1;
+        if (slots < 0) {
+            int occ = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, op3_tile_kernel<MODE, NF>, threads_of<MODE>(), bytes) != cudaSuccess || occ <= 0) {
+                cudaGetLastError();
+                occ = 6;
+            }
+            slots = occ;
+            const char* env = getenv("TK_OP3_STAGGER");
+            cycles = env ? atoi(env) : 0;      // measured: no effect at 65536 .. 524288 envs (16-env tiles: many waves)
+        }
+        kk.stagger_ctas = slots * h->sm_count;
+        kk.stagger_cycles = (h->tiles <= 2 * h->sm_count) ? 0 : cycles;      // a thin single wave is only delayed by it
+    }
+    op3_tile_kernel<MODE, NF><<<h->tiles, threads_of<MODE>(), bytes, st>>>(kk);
     return cudaGetLastError();
 }
 
