@@ -262,7 +262,7 @@ def _e2e_bench(torch, n, device, steps, chunks, env_off, barrier=None):
     b0 = bridge.bridges[0]
     assert torch.equal(b0.host_out["reset_buf"], b0.env.reset_buf.cpu()), "e2e read-back mismatch"
     return {"seconds": t1 - t0, "h2d": bridge.h2d_bytes, "d2h": bridge.d2h_bytes, "chunks": chunks,
-            "launches": steps * chunks, "window": (t0, t1)}
+            "launches": steps * chunks, "window": (t0, t1), "placement": bridge.placement}
 
 
 def _pcie_probe(torch, device, mb=64):
@@ -292,6 +292,46 @@ def _pcie_probe(torch, device, mb=64):
     torch.cuda.synchronize()
     out["duplex_GBps_per_direction"] = 5 * host.numel() / (time.perf_counter() - t0) / 1e9
     return out
+
+
+def _pcie_probe_concurrent(torch, dist, device, world, barrier, mb=64, reps=8):
+    """What the BOX gives when all N ranks copy at once (N > 1): every rank, after a barrier, drives both directions of its
+    own PCIe link from pinned slabs placed like the e2e path places them (host_io.near_gpu).  The e2e line can at best
+    move its h2d + d2h bytes at this rate: if the per-GPU figure drops as N grows the ceiling is the host side of the box
+    (memory / root complex shared by the GPUs), not host_io.py."""
+    from thormang_isaacgym_b200.host_io import near_gpu
+    place = {}
+    with near_gpu(torch.device(device).index or 0, place):
+        host = torch.empty(mb * 1024 * 1024, dtype=torch.uint8, pin_memory=True)
+        host2 = torch.empty(mb * 1024 * 1024, dtype=torch.uint8, pin_memory=True)
+    dev, dev2 = torch.empty_like(host, device=device), torch.empty_like(host, device=device)
+    s1, s2 = torch.cuda.Stream(device=device), torch.cuda.Stream(device=device)
+    for _ in range(2):
+        with torch.cuda.stream(s1):
+            dev.copy_(host, non_blocking=True)
+        with torch.cuda.stream(s2):
+            host2.copy_(dev2, non_blocking=True)
+    torch.cuda.synchronize()
+    if barrier:
+        barrier()
+        torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        with torch.cuda.stream(s1):
+            dev.copy_(host, non_blocking=True)
+        with torch.cuda.stream(s2):
+            host2.copy_(dev2, non_blocking=True)
+    torch.cuda.synchronize()
+    mine = reps * host.numel() / (time.perf_counter() - t0) / 1e9
+    t = torch.tensor([mine], device=device, dtype=torch.float64)
+    every = [torch.zeros_like(t) for _ in range(world)]
+    if dist:
+        dist.all_gather(every, t)
+    else:
+        every = [t]
+    per = [float(x.item()) for x in every]
+    return {"duplex_GBps_per_direction_per_rank": [round(v, 2) for v in per], "sum_over_ranks_GBps_per_direction": round(sum(per), 2),
+            "ranks_copying_at_once": world, "mb_per_copy": mb, "pinned_placement": place}
 
 
 def _launch_floor(torch, device):
@@ -548,6 +588,11 @@ def run_gpu_arm(args, rank, world):
     if not os.environ.get("TK_BENCH_NO_DIAG"):
         multi = _multi_gpu_diag(torch, dist, task, n, device, rank, world, local_rank, barrier, args.steps)
         multi["per_rank_ms_total"] = per_rank_ms
+        if dist:
+            try:
+                multi["pcie_concurrent"] = _pcie_probe_concurrent(torch, dist, device, world, barrier)
+            except Exception as exc:
+                multi["pcie_concurrent"] = {"error": repr(exc)}
         multi["rank0_host_enqueue_ms"] = res.get("host_enqueue_ms")
 
     # ---- end-to-end through the public API with host buffers
@@ -560,10 +605,25 @@ def run_gpu_arm(args, rank, world):
             dist.all_reduce(sec, op=dist.ReduceOp.MAX)
         e2e = {"value": n * world * args.e2e_steps / float(sec.item()), "unit": "env-steps/s",
                "h2d_bytes_per_step": r["h2d"] * world, "d2h_bytes_per_step": r["d2h"] * world,
-               "steps": args.e2e_steps, "chunks_per_gpu": r["chunks"],
+               "steps": args.e2e_steps, "chunks_per_gpu": r["chunks"], "pinned_placement_rank0": r["placement"],
+               "GBps_per_direction_per_gpu": (r["h2d"] + r["d2h"]) / 2 * args.e2e_steps / float(sec.item()) / 1e9,
                "path": "HostBridge: pinned host state slab -> one H2D -> Humanoid.post_physics_step() -> one D2H of the "
                        "obs|rew|reset slab, range-sharded into chunks on separate streams so PCIe copies overlap the kernels"}
 
+    if dist and multi is not None and e2e is not None:
+        # the same e2e path with 1 and 4 chunks per GPU (the headline uses --e2e-chunks): does finer pipelining help or hurt
+        # once N ranks share the host side of the box?
+        sweep = {}
+        for ch in (1, 4):
+            try:
+                r2 = _e2e_bench(torch, n, device, max(10, args.e2e_steps // 2), ch, rank * n, barrier)
+                sec2 = torch.tensor([r2["seconds"]], device=device, dtype=torch.float64)
+                dist.all_reduce(sec2, op=dist.ReduceOp.MAX)
+                sweep[f"chunks_{r2['chunks']}"] = n * world * max(10, args.e2e_steps // 2) / float(sec2.item())
+            except Exception as exc:
+                sweep[f"chunks_{ch}"] = repr(exc)
+        sweep[f"chunks_{e2e['chunks_per_gpu']}_headline"] = e2e["value"]
+        multi["e2e_env_steps_per_s_by_chunks"] = sweep
     sampler.stop()
     clocks = sampler.summary(windows)
     if rank != 0:

@@ -19,6 +19,9 @@ from typing import Callable, Dict, List
 
 import torch
 
+import contextlib
+import os
+
 HUMANOID_INPUTS = ("root_states", "dof_state", "dof_force", "sensors", "actions")
 HUMANOID_OUTPUTS = ("obs_buf", "rew_buf", "reset_buf")
 
@@ -36,6 +39,53 @@ def make_humanoid_for_host(n: int, device, env_id_offset: int = 0, seed: int = 0
     cfg["sim_backend"] = FakeSim(n, 21, device, num_sensor_floats=12, asset=humanoid_asset(), slab=True)
     dev = torch.device(device)
     return Humanoid(cfg, str(dev), f"cuda:{dev.index or 0}", -1, True)
+
+
+def gpu_local_cpus(device_index: int):
+    """CPUs of the NUMA node the GPU hangs off (NVML), or None when the box does not say (no NVML, one node, a VM that
+    hides the topology).  Returns (cpu list, numa node or None)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        words = (os.cpu_count() + 63) // 64
+        try:      # node scope where the driver offers it, else the plain affinity mask
+            mask = pynvml.nvmlDeviceGetCpuAffinityWithinScope(h, words, pynvml.NVML_AFFINITY_SCOPE_NODE)
+        except Exception:
+            mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1]
+        node = None
+        try:
+            node = int(pynvml.nvmlDeviceGetNumaNodeId(h))
+        except Exception:
+            pass
+        return (cpus or None), node
+    except Exception:
+        return None, None
+
+
+@contextlib.contextmanager
+def near_gpu(device_index: int, report: dict = None):
+    """Run the enclosed allocations on the CPUs next to the GPU: pinned slabs are placed on the NUMA node of the thread
+    that allocates them, and a slab on the far socket crosses the inter-socket link on every copy.  The affinity of the
+    process is restored on exit (the env-step path itself is not CPU-bound)."""
+    old = None
+    cpus, node = gpu_local_cpus(device_index)
+    try:
+        if cpus and hasattr(os, "sched_setaffinity"):
+            old = os.sched_getaffinity(0)
+            usable = sorted(set(cpus) & set(old)) or None
+            if usable and set(usable) != set(old):
+                os.sched_setaffinity(0, usable)
+            else:
+                old = None
+        if report is not None:
+            report.update({"gpu": device_index, "numa_node": node, "gpu_local_cpus": len(cpus) if cpus else None,
+                           "affinity_narrowed_for_allocation": old is not None})
+        yield
+    finally:
+        if old is not None:
+            os.sched_setaffinity(0, old)
 
 
 class HostBridge:
@@ -102,7 +152,11 @@ class ChunkedHostBridge:
     def __init__(self, make_env: Callable[[int, int], object], n: int, chunks: int):
         assert n % chunks == 0, "env count must divide into the chunks"
         self.per = n // chunks
-        self.bridges: List[HostBridge] = [HostBridge(make_env(self.per, c * self.per)) for c in range(chunks)]
+        self.placement: dict = {}
+        envs = [make_env(self.per, c * self.per) for c in range(chunks)]
+        dev = torch.device(envs[0].device)
+        with near_gpu(dev.index or 0, self.placement):      # pinned slabs on the GPU's own NUMA node
+            self.bridges: List[HostBridge] = [HostBridge(e) for e in envs]
         self.h2d_bytes = sum(b.h2d_bytes for b in self.bridges)
         self.d2h_bytes = sum(b.d2h_bytes for b in self.bridges)
 
