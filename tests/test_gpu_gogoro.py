@@ -203,3 +203,25 @@ def test_cuda_graph_replay_matches_eager():
     for name in ("obs_buf", "buffer_obs", "rew_buf", "reset_buf", "progress_buf", "root_tensor", "curent_command",
                  "action_history", "yaw_command", "curent_speed", "dof_pos_command"):
         U.exact(getattr(env_b, name), getattr(env_a, name), f"graph vs eager: {name}")
+
+
+@pytest.mark.parametrize("n", [4099, 65536])
+def test_speculative_reset_matches_lazy_reset(n, monkeypatch):
+    """Thin grids draw every env's reset speculatively ahead of the dependency wait (gogoro_tile_kernel<0, true>); deep grids
+    draw lazily, warp-cooperatively, for the flagged envs only.  Same Philox streams, same expressions: every state tensor
+    must agree bit for bit after three steps with resets (also more than two per warp, and a ragged last tile)."""
+    st = syn.gogoro_state(n, seed=77)
+    for i in (0, 1, 2, 3, 31, 32, 127, 128, n - 1):
+        st["reset_buf"][i] = 1
+    outs = []
+    for spec in ("0", "1"):
+        monkeypatch.setenv("TK_GOGORO_SPEC", spec)          # read at every launch
+        env, _, _ = U.make_gogoro_pair(n, state={k: v.clone() for k, v in st.items()})
+        for _ in range(3):
+            env.post_physics_step()
+        torch.cuda.synchronize()
+        outs.append({k: getattr(env, k).clone() for k in (
+            "obs_buf", "buffer_obs", "rew_buf", "reset_buf", "progress_buf", "yaw_command", "curent_command", "curent_speed",
+            "curent_speed_offset", "steer_offsets", "imu_offsets", "config_vector", "action_history", "root_tensor", "state_dof")})
+    for k in outs[0]:
+        assert torch.equal(outs[0][k], outs[1][k]), f"{k}: speculative reset differs from the lazy reset"

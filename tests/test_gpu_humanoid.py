@@ -410,3 +410,23 @@ def test_stats_reducer_cuda_path_single_rank_nccl():
         assert out["num_reset"] == int((env.reset_buf != 0).sum())
     finally:
         dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n", [4103, 16384])
+def test_quad_kernel_matches_warp_kernel(n, monkeypatch):
+    """The two tile kernels of the fused step (one warp per tile | four warps per tile, picked by grid size) are the same
+    arithmetic cut differently: every output must agree bit for bit, resets and Philox noise included (3 steps)."""
+    outs = []
+    for quad in ("0", "1"):
+        monkeypatch.setenv("TK_HUMANOID_QUAD", quad)        # read when the handle is created
+        env, _, st = U.make_humanoid_pair(n, seed=99)
+        for i in (0, 31, 32, 33, n - 1):
+            st["reset_buf"][i] = 1
+        env.reset_buf.copy_(st["reset_buf"].to(DEV))
+        for _ in range(3):
+            env.post_physics_step()
+        torch.cuda.synchronize()
+        outs.append({k: getattr(env, k).clone() for k in ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "timeout_buf",
+                                                           "potentials", "prev_potentials", "dof_state", "root_states")})
+    for k in outs[0]:
+        assert torch.equal(outs[0][k], outs[1][k]), f"{k}: four-warp kernel differs from the one-warp kernel"

@@ -6,16 +6,18 @@
 // reset_idx :440-489.  The reference's step hooks are stubs (:309-317); the fused step is the anymal.py:229-242 ordering
 // around those methods (oracle/ma_op3_oracle.py states the assumptions).
 //
-// One CTA = 2 warps = 32 consecutive envs; warp a owns agent a, lane e owns env e.  root / dof_state / torques / actions
-// arrive as cp.async.bulk (TMA) tile copies on one mbarrier (a 32-env tile of every array starts 16-byte aligned): 27 KB
-// of shared memory per CTA, so 6 CTAs (register-limited) are resident per SM.  Each lane reads its own prev_torques /
-// last_actions rows (88 contiguous bytes) and the 4 foot contact rows an agent needs straight from global memory, issued
-// before the tile wait (12 of the env's 51 body rows are ever read).  An (env, agent) observation row is built in
-// registers and leaves as 22 streaming 128-bit stores (352-byte rows, 16-byte aligned; sectors complete in L2);
-// prev_torques / last_actions are refreshed by bulk-storing the torque / action tiles that are already in shared
-// memory.  Warp 1 hands its reward and reset bits to warp 0 through shared memory for the table ("objective") terms.
-// (v1 staged padded obs rows and all six tiles in shared memory: 64 KB, 3 CTAs per SM, 44 % of HBM peak, stalled on the
-// tile wait -- profiles/r01_n3_ma_op3_tile_kernel_262144_v1.json.)
+// One CTA = one tile of 16 consecutive envs = 32 (env, agent) rows.  The fused step runs 64 threads per CTA: lanes 0..31 build
+// the 32 observation rows, lanes 32..63 the rewards / reset bits of the same rows (row = 2 * env + agent, so a lane's row of
+// the torque / action tiles starts 88 B after its neighbour's and its dof_state row 176 B after: the 64- and 128-bit shared
+// loads touch every bank once per phase, and the two agents of an env sit in neighbouring lanes -- the table terms need
+// both: one shuffle, no barrier).  root / dof_state / torques / prev_torques / actions / last_actions AND the tile's whole
+// contact block (16 x 51 x 12 B) arrive as cp.async.bulk (TMA) tile copies on one mbarrier; per-env scalars are requested
+// by the lanes before the tile wait.  An observation row is built in registers and leaves as 11 streaming 256-bit stores
+// (352-byte rows; 128-bit stores when the base is only 16-byte aligned); prev_torques / last_actions are refreshed by
+// bulk-storing the torque / action tiles already resident in shared memory.  7 CTAs per SM (register target).
+// History: v1 staged padded obs rows and all six tiles (64 KB, 3 CTAs / SM): 46 % of HBM peak, stalled on the tile wait;
+// v3 (warp per agent, stride-88 row reads: 58 % of the shared wavefronts conflicted, 166 registers): 62 %; this layout: 82 %
+// at 524288 envs (profiles/r02_n3_ma_op3_tile_kernel_524288.json).
 //
 // Algorithmic bytes / env-step (F = 4 feet): reads root 156 + dof 352 + torques 176 + prev_torques 176 + actions 176 +
 // last_actions 176 + foot contacts 96 + gripper x-forces 16 + commands 12 + potentials 8 + table potential 4 +
