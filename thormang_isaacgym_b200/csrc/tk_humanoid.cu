@@ -102,6 +102,7 @@ struct KParams {
     int prefetch;               // L2 prefetch of the tile inputs ahead of griddepcontrol.wait
     int warm;                   // warm_ahead_of_wait (tk_humanoid_tile.cuh): 1 translations, 2 initial rows of the tile
     int dbg_reset;              // developer ablation (TK_HUMANOID_DBG_RESET=1): reset flags ignored
+    int coop_store;             // developer knob (TK_HUMANOID_COOP_STORE=1): four-warp kernel stores its obs tile with STG.128
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -550,6 +551,7 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     k.prefetch = h->prefetch;
     k.warm = h->warm;
     { const char* env = getenv("TK_HUMANOID_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
+    { const char* env = getenv("TK_HUMANOID_COOP_STORE"); k.coop_store = env ? atoi(env) : 0; }
     k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count; k.stagger_free = h->stagger_free;
     k.prefetch_ctas = k.stagger_ctas;
     if (const char* env = getenv("TK_HUMANOID_PREFETCH_SLOTS")) k.prefetch_ctas = atoi(env) * h->sm_count;

@@ -317,7 +317,12 @@ __global__ void __launch_bounds__(kQuadThreads, TK_HUMANOID_QUAD_MIN_CTAS) human
 
     // ---- obs tile -> global
     float* dst = p.obs + static_cast<size_t>(env0) * OBS;
-    if (bulk) {
+    if (bulk && p.coop_store) {
+        // developer knob (TK_HUMANOID_COOP_STORE): the obs tile leaves as 128-bit stores of all 128 threads instead of one bulk store
+        const float4* o4 = reinterpret_cast<const float4*>(out);
+        for (int i = tid; i < WT::kOut / 4; i += kQuadThreads) stg_stream4(dst + 4 * i, o4[i]);
+        if (p.obs2) for (int i = tid; i < WT::kOut / 4; i += kQuadThreads) stg_stream4(p.obs2 + static_cast<size_t>(env0) * OBS + 4 * i, o4[i]);
+    } else if (bulk) {
         if (tid == 0) {
             bulk_store(dst, out, WT::kOut * 4);
             // second destination of the same tile (tk_humanoid_set_obs_copy): e.g. slot t of a [horizon, N, obs] rollout buffer
@@ -354,7 +359,7 @@ __global__ void __launch_bounds__(kQuadThreads, TK_HUMANOID_QUAD_MIN_CTAS) human
             atomicAdd(p.partials + static_cast<size_t>(blockIdx.x & (kStatSlots - 1)) * TK_STATS + lane, static_cast<double>(v));
         }
     }
-    if (bulk && tid == 0) bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
+    if (bulk && !p.coop_store && tid == 0) bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
     TK_QSTAMP(6);
 #undef TK_QSTAMP
 }
