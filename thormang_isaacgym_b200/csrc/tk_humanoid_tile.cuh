@@ -265,6 +265,13 @@ __global__ void TK_HUMANOID_BOUNDS humanoid_warp_kernel(const __grid_constant__ 
     // ---- reset prologue (rare): reset_idx :253-279 for this tile's flagged envs, lane = DOF.  The new state does not
     // depend on the staged tile, so for the first kPre flagged envs it is computed and written to global memory WHILE
     // the bulk loads are still in flight; only the patch of the staged copy waits for them.
+    // Why the overlap of these global writes with the in-flight bulk load of the SAME rows is benign: (1) the bulk copy may
+    // deliver the old or the new bytes of a flagged env's rows into shared memory, or a mix -- and exactly those staged rows
+    // (all D (pos, vel) pairs and all 13 root columns of every flagged env) are overwritten after the mbarrier wait with the
+    // values that were written to global memory, so nothing downstream ever reads what the copy delivered for them; (2) the
+    // rows of an env belong to ONE tile, no other CTA of this launch reads or writes them; (3) the next launch is ordered
+    // behind this one by the stream (griddepcontrol.wait).  tests: test_fused_every_env_of_a_tile_resets (all 32 envs of a
+    // tile flagged, COMPACT and Philox noise), test_quad_kernel_matches_warp_kernel.
     constexpr int kPre = 4;                // 1 % of the envs resetting: 0.4 % of the tiles have 3+ resets, 0.003 % have 5+
     unsigned reset_bits = 0;
     int rank0 = 0;

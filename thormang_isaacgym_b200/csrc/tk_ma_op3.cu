@@ -374,10 +374,11 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
         } else {                                                                    // compute_reward :360-409, this agent
             bool zero_last = false;
             if (rst) {                                                              // reset_idx :440-489, this env's lanes
-                float4* gd = reinterpret_cast<float4*>(p.dof_state) + (n * kA + a) * (kDof / 2);
+                // 64-bit stores: tk_ma_op3_bind guarantees dof_state 8-byte alignment only (a 128-bit store here faulted on an
+                // 8-byte aligned base: found by tests/test_gpu_guard_bands.py)
+                float2* gd = reinterpret_cast<float2*>(p.dof_state) + (n * kA + a) * kDof;
 #pragma unroll
-                for (int jj = 0; jj < kDof / 2; ++jj)                               // :456-457 (offsets are zeros)
-                    gd[jj] = make_float4(p.default_dof_pos[2 * jj] + 0.0f, 0.0f, p.default_dof_pos[2 * jj + 1] + 0.0f, 0.0f);
+                for (int j = 0; j < kDof; ++j) gd[j] = make_float2(p.default_dof_pos[j] + 0.0f, 0.0f);   // :456-457 (offsets are zeros)
                 float uc[3] = {0.5f, 0.5f, 0.5f};
                 if (p.noise_mode == TK_NOISE_PHILOX) {
                     Philox4 d = philox_env(p.seed, effective_step(p.step, p.step_dev), p.env_off + n, kStreamCmd);
