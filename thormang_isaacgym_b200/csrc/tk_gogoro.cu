@@ -66,6 +66,7 @@ struct KParams {
     int n, num_dof, steering_joint, rear_wheel_joint, max_episode_length, speed_freq, yaw_freq;
     int vec_ok;
     int prefetch;                 // L2 prefetch of the tile inputs ahead of griddepcontrol.wait (thin grids, host decides)
+    int ldg_tiles;                // developer knob TK_GOGORO_LDG: input tiles through the load/store unit (measured slower)
     int dbg_reset;                // developer ablation mask (TK_GOGORO_DBG_RESET): 1 no resets, 2 no scalar stores, 4 no row fetch/stores, 8 no Philox
     long long* dbg_ts;            // developer timeline probe (tools/tile_timeline.py --task gogoro); NULL in normal use
     float max_steering, max_steering_change;
@@ -471,7 +472,24 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
     TK_GSTAMP(0);
 
     // full, 16-byte aligned tile: the bulk-copy (TMA) engine moves root / history / noise rows in and both obs rows out
-    if (bulk) {
+    // Developer knob (p.ldg_tiles, TK_GOGORO_LDG=1): the two input tiles through the load/store unit instead -- coalesced 128-bit
+    // loads held in registers across the scalar requests, stored to shared memory in front of the CTA barrier below.  Tried
+    // because a lone plain load lands 0.3-0.5 us after the dependency wait and the bulk copies 1.0-1.5 us after it
+    // (tools/probe_first_load.cu, tools/tile_timeline.py); measured SLOWER (see fill_kparams): the bulk copy is not the
+    // bottleneck of the thin launch.
+    const bool ldg = bulk && p.ldg_tiles && !use_noise && MODE == 0;
+    constexpr int kRoot4 = kTile * kRoot / 4, kHist4 = kTile * kHist / 4;      // 416 and 160 float4 per tile
+    float4 rt[(kRoot4 + kTile - 1) / kTile], ht[(kHist4 + kTile - 1) / kTile];
+    if (ldg) {
+        const float4* gr = reinterpret_cast<const float4*>(p.root + static_cast<size_t>(env0) * kRoot);
+        const float4* gh = reinterpret_cast<const float4*>(p.action_history + static_cast<size_t>(env0) * kHist);
+#pragma unroll
+        for (int k = 0; k < (kRoot4 + kTile - 1) / kTile; ++k)
+            if (tid + kTile * k < kRoot4) rt[k] = gr[tid + kTile * k];
+#pragma unroll
+        for (int k = 0; k < (kHist4 + kTile - 1) / kTile; ++k)
+            if (tid + kTile * k < kHist4) ht[k] = gh[tid + kTile * k];
+    } else if (bulk) {
         if (tid == 0) mbar_expect_tx(&s.bar, (kRoot + (MODE != 2 ? kHist : 0) + (use_noise ? kSensorNoise : 0)) * kTile * 4);
         __syncwarp();
         if (tid == 0) bulk_load(s.root, p.root + static_cast<size_t>(env0) * kRoot, kTile * kRoot * 4, &s.bar);
@@ -507,6 +525,14 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
         reset_bits = __ballot_sync(0xffffffffu, do_reset);
         const unsigned b1 = __ballot_sync(0xffffffffu, do_speed);
         if (lane == 0) { s.ballots[0][warp] = reset_bits; s.ballots[1][warp] = b1; }
+    }
+    if (ldg) {
+#pragma unroll
+        for (int k = 0; k < (kRoot4 + kTile - 1) / kTile; ++k)
+            if (tid + kTile * k < kRoot4) reinterpret_cast<float4*>(s.root)[tid + kTile * k] = rt[k];
+#pragma unroll
+        for (int k = 0; k < (kHist4 + kTile - 1) / kTile; ++k)
+            if (tid + kTile * k < kHist4) reinterpret_cast<float4*>(s.hist)[tid + kTile * k] = ht[k];
     }
     TK_GSTAMP(1);
     __syncthreads();                       // ballots, mbarrier init, cooperative copies visible to the whole CTA
@@ -564,7 +590,7 @@ __global__ void __launch_bounds__(kTile) gogoro_tile_kernel(const __grid_constan
             if (pre_env[q] >= 0 && !(p.dbg_reset & 4)) pre_rows[q] = reset_env_fetch(p, env0 + warp * 32 + pre_env[q], lane);
     }
     TK_GSTAMP(2);
-    if (bulk) mbar_wait(&s.bar, 0);        // bulk loads landed
+    if (bulk && !ldg) mbar_wait(&s.bar, 0);        // bulk loads landed
     if (!SPEC && MODE == 0 && reset_bits) {         // patch the staged rows of the envs that were reset
         int rank = 0;
         if (p.noise_mode == TK_NOISE_COMPACT) {
@@ -947,6 +973,8 @@ static void fill_kparams(const TkGogoro* h, KParams& k) {
     k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.action_history, 16) && aligned_to(B.obs_buf, 16) &&
                aligned_to(B.buffer_obs, 16);
     k.prefetch = h->prefetch;
+    k.ldg_tiles = 0;              // measured slower: 6.7 vs 6.3 us eager, 6.1 vs 5.8 us from a graph at 65536 envs; equal at 131072 / 262144
+    if (const char* env = getenv("TK_GOGORO_LDG")) k.ldg_tiles = atoi(env);
     { const char* env = getenv("TK_GOGORO_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
     k.max_steering = P.max_steering; k.max_steering_change = P.max_steering_change;
     pair_normal(P.imu_filter_noise, k.imu_filter); pair_normal(P.imu_noise, k.imu); pair_normal(P.speed_sensor_noise, k.speed_sensor);
