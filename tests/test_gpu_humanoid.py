@@ -430,3 +430,32 @@ def test_quad_kernel_matches_warp_kernel(n, monkeypatch):
                                                            "potentials", "prev_potentials", "dof_state", "root_states")})
     for k in outs[0]:
         assert torch.equal(outs[0][k], outs[1][k]), f"{k}: four-warp kernel differs from the one-warp kernel"
+
+
+def test_config4_one_million_envs_in_eight_shards():
+    """BASELINE config 4 exactly: 1,048,576 Humanoid envs as 8 range shards of 131072 with global env-id offsets (what 8
+    ranks run) against the unsharded run on one GPU: every output bit for bit, and the per-shard episode statistics (the
+    all-reduce payload) sum to the single-process vector."""
+    n, shards = 1048576, 8
+    asset = syn.humanoid_asset()
+    st = syn.humanoid_state(n, seed=4, asset=asset)
+    env, _, _ = U.make_humanoid_pair(n, state={k: v.clone() for k, v in st.items()}, asset=asset)
+    env.post_physics_step()                      # in-kernel Philox resets keyed by the global env id
+    keys = ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "timeout_buf", "potentials", "root_states")
+    full = {k: getattr(env, k).clone() for k in keys + ("dof_state",)}
+    total = env.episode_statistics().double().cpu()
+    del env
+    per = n // shards
+    acc = torch.zeros_like(total)
+    for r in range(shards):
+        sl = slice(r * per, (r + 1) * per)
+        sub = {k: (v[sl.start * 21:sl.stop * 21].clone() if k == "dof_state" else v[sl].clone()) for k, v in st.items()}
+        e2, _, _ = U.make_humanoid_pair(per, state=sub, asset=asset, envIdOffset=r * per)
+        e2.post_physics_step()
+        for k in keys:
+            assert torch.equal(getattr(e2, k), full[k][sl]), f"shard {r} {k}"
+        assert torch.equal(e2.dof_state, full["dof_state"][sl.start * 21:sl.stop * 21]), f"shard {r} dof_state"
+        acc += e2.episode_statistics().double().cpu()
+        del e2
+    U.close(acc, total, rtol=1e-9, atol=1e-3, what="sum of the shard statistics vs the single-process vector")
+    assert float(total[7]) == n
