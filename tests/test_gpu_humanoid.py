@@ -459,3 +459,39 @@ def test_config4_one_million_envs_in_eight_shards():
         del e2
     U.close(acc, total, rtol=1e-9, atol=1e-3, what="sum of the shard statistics vs the single-process vector")
     assert float(total[7]) == n
+
+
+def test_config5_ppo_rollout_shape_through_step():
+    """BASELINE config 5 at the rl_games PPO shape of cfg/train/HumanoidPPO.yaml:47,66 -- 4096 actors x horizon 32 -- through
+    the public VecTask.step (clamp + pre_physics -> fake physics -> fused post_physics with in-kernel Philox resets), obs
+    delivered into the [horizon, actors, obs] experience tensor by the kernel; every step compared with the oracle."""
+    n, horizon = 4096, 32
+    env, orc, st = U.make_humanoid_pair(n, seed=32)
+
+    def physics_t(root, dof_state, forces, dt):
+        root[:, 0:3] += dt * root[:, 7:10]
+        root[:, 2] -= 0.01
+        dof_state[:, 0] += dt * dof_state[:, 1]
+        dof_state[:, 1] += 0.001 * forces.reshape(-1)
+
+    env.sim.physics = lambda s: physics_t(s.root_states, s.dof_state, env.forces, 0.0166)
+    buf = torch.full((horizon, n, 110), float("nan"), device=DEV)
+    env.set_rollout_buffer(buf)
+    g = torch.Generator().manual_seed(9)
+    resets = 0
+    for t in range(horizon):
+        a = torch.rand(n, 21, generator=g) * 2.4 - 1.2          # beyond the clip range: the clamp of vec_task.py:327 is live
+        ids = orc.reset_buf.nonzero().flatten()
+        resets += len(ids)
+        pa, pb = env.philox_noise()                              # the draws the next post-physics launch will use
+        ua, ub = (pa.cpu()[ids], pb.cpu()[ids]) if len(ids) else syn.humanoid_reset_noise(1, seed=1)
+        obs_d, rew, reset, extras = env.step(a.to(DEV))
+        o_obs, o_rew, o_reset, o_ex = orc.step(a, ua, ub, physics=lambda o: physics_t(o.root_states, o.dof_state, o.forces, 0.0166))
+        assert obs_d["obs"].data_ptr() == buf[t].data_ptr()
+        U.exact(reset, o_reset, f"reset t={t}")
+        U.exact(extras["time_outs"], o_ex["time_outs"], f"time_outs t={t}")
+        U.humanoid_obs_close(buf[t], o_obs, f"rollout slot t={t}")
+        U.close(rew, o_rew, what=f"rew t={t}")
+        orc.root_states.copy_(env.root_states.cpu()); orc.dof_state.copy_(env.dof_state.cpu())
+        orc.potentials.copy_(env.potentials.cpu()); orc.prev_potentials.copy_(env.prev_potentials.cpu())
+    assert resets > 0 and bool(torch.isfinite(buf).all())
