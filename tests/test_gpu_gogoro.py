@@ -225,3 +225,40 @@ def test_speculative_reset_matches_lazy_reset(n, monkeypatch):
             "curent_speed_offset", "steer_offsets", "imu_offsets", "config_vector", "action_history", "root_tensor", "state_dof")})
     for k in outs[0]:
         assert torch.equal(outs[0][k], outs[1][k]), f"{k}: speculative reset differs from the lazy reset"
+
+
+def test_config5_ppo_rollout_shape_with_in_kernel_noise():
+    """The rl_games PPO shape of cfg/train/GogoroPPO.yaml:47,61 -- 4096 actors x horizon 64 -- with ALL noise drawn in the
+    kernels (Philox: steering noise in pre_physics, sensor / reset / resample draws in the fused post_physics, speculative
+    reset variant on this thin grid).  The draws of every step are materialised with philox_noise() and handed to the oracle,
+    which steps alongside; command resampling (progress hitting the update frequencies) and resets occur on the way."""
+    n, horizon = 4096, 64
+    env, orc, st = U.make_gogoro_pair(n, seed=64)
+    env.progress_buf[::7] = 280                      # some envs reach speed_freq_update (300) inside the horizon
+    orc.progress_buf[::7] = 280
+    g = torch.Generator().manual_seed(11)
+
+    def physics_t(root, dt):
+        root[:, 0:3] += dt * root[:, 7:10]
+        root[:, 10:13] *= 0.99
+
+    resets = resamples = 0
+    for t in range(horizon):
+        a = torch.rand(n, 1, generator=g) * 3 - 1.5
+        pn = {k: v.cpu() for k, v in env.philox_noise().items()}
+        ids = orc.reset_buf.nonzero().flatten()
+        speed_ids = ((orc.reset_buf == 0) & (orc.progress_buf + 1 == 300)).nonzero().flatten()
+        resets += len(ids); resamples += len(speed_ids)
+        env.pre_physics_step(a.to(DEV))
+        physics_t(env.root_tensor, 0.03)
+        env.post_physics_step()
+        orc.step(a, pn["steer_unit"], pn["sensor_unit"], pn["reset_unit"][ids] if len(ids) else pn["reset_unit"][:1],
+                 pn["speed_unit"][speed_ids] if len(speed_ids) else pn["speed_unit"][:1], pn["yaw_unit"],
+                 physics=lambda o: physics_t(o.root_tensor, 0.03))
+        U.exact(env.reset_buf, orc.reset_buf, f"reset t={t}")
+        U.exact(env.progress_buf, orc.progress_buf, f"progress t={t}")
+        U.gogoro_obs_close(env.obs_buf, orc.obs_buf, f"obs t={t}", noisy=True)
+        U.close(env.rew_buf, orc.rew_buf, rtol=2e-5, atol=2e-5, what=f"rew t={t}")
+        U.close(env.curent_speed, orc.curent_speed, what=f"curent_speed t={t}")
+        orc.root_tensor.copy_(env.root_tensor.cpu()); orc.yaw_command.copy_(env.yaw_command.cpu())
+    assert resets > 0 and resamples > 0
