@@ -509,8 +509,8 @@ struct TkHumanoid {
     long long* dbg_ts;
 };
 
-// the four-warp kernel runs while the whole grid is resident at once (7 CTAs / SM: up to 33152 envs on 148 SMs); measured
-// B200, us / step, four-warp vs one-warp: 6.7 / 8.3 at 16384 envs, 9.3 / 9.9 at 32768, 15.0 / 13.3 at 65536, 25.9 / 22.6 at 131072
+// fallback for the four-warp kernel's occupancy when the query fails (see tk_humanoid_create); measured B200, us / step,
+// four-warp vs one-warp without prefetch: 6.7 / 8.3 at 16384 envs, 9.3 / 9.9 at 32768, 15.0 / 13.3 at 65536, 25.9 / 22.6 at 131072
 static constexpr int kQuadMaxTilesPerSm = 7;
 static constexpr int kD = HumanoidSpec::D;
 static constexpr int kDAnt = AntSpec::D;
@@ -626,10 +626,25 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     // L2 prefetch ahead of griddepcontrol.wait pays only while the whole grid is resident at once and thin (measured:
     // 10.1 -> 8.3 us at 16384 envs, but +1.8 us at 65536 where it re-synchronises the staggered first wave)
-    if (h->prefetch < 0) h->prefetch = (h->tiles <= 4 * h->sm_count) ? 2 : 0;
-    // four-warp tiles while the grid is at most a few waves deep, one-warp tiles (most bytes in flight per SM) beyond
-    h->quad = (h->tiles <= kQuadMaxTilesPerSm * h->sm_count) ? 1 : 0;
+    // four-warp tiles while the WHOLE grid is resident at once (one wave of the four-warp kernel's own occupancy: 8 CTAs / SM
+    // for the Humanoid = 37888 envs on 148 SMs), one-warp tiles (most bytes in flight per SM) beyond.  Measured, us / step,
+    // four-warp + prefetch vs the previous choice: 8.2 vs 9.5 at 32768 envs, 8.7 vs 10.0 at 36864; one CTA past the wave the
+    // four-warp kernel collapses (14.3 vs 10.3 at 40960).
+    int quad_occ = kQuadMaxTilesPerSm;
+    {
+        int occ = 0;
+        cudaError_t oe = (params->variant == kVarAnt)
+            ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, humanoid_quad_kernel<AntSpec, true>, kQuadThreads, 0)
+            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, humanoid_quad_kernel<HumanoidSpec, true>, kQuadThreads, 0);
+        if (oe == cudaSuccess && occ > 0) quad_occ = occ;
+        else cudaGetLastError();
+    }
+    h->quad = (h->tiles <= quad_occ * h->sm_count) ? 1 : 0;
     if (const char* env = getenv("TK_HUMANOID_QUAD")) h->quad = atoi(env) != 0;
+    // the prefetch goes with the single wave: there the CTAs of launch k+1 become resident while launch k runs (or drains)
+    // and have slack ahead of the wait; measured with the four-warp kernel 7.5 -> 6.65 us at 16384 envs, 9.0 -> 7.9 at 24576,
+    // 9.55 -> 8.2 at 32768 (the one-warp kernel on such grids: 8.6 -> 8.0, 9.5 -> 8.6, 10.7 -> 10.5)
+    if (h->prefetch < 0) h->prefetch = (h->quad || h->tiles <= 4 * h->sm_count) ? 2 : 0;
     h->warm = 0;          // measured: no gain at 16384 envs (6.55 vs 6.58 / 7.09 us with 1 / 3), -3 % at 32768, +8 % at 65536
     if (const char* env = getenv("TK_HUMANOID_WARM")) h->warm = atoi(env);
     // the four-warp kernel only runs single-wave grids, where spacing the CTAs merely delays them (6.5 us with 0 cycles,
