@@ -266,8 +266,7 @@ def run_reference_arm(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": args.gpus,
         "steps": done, "warmup": max(1, min(args.warmup, 5)), "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, rotating_sets=max(3, -(-int(2.2 * L2_BYTES) // (n * (HUMANOID_BYTES_PER_ENV if args.task == "humanoid" else GOGORO_BYTES_PER_ENV)))),
-                                  note="same config as the GPU arm; the CPU arm itself steps one state set held in host memory"),
+        "config": workload_config(args, rotating_sets=max(3, -(-int(2.2 * L2_BYTES) // (n * (HUMANOID_BYTES_PER_ENV if args.task == "humanoid" else GOGORO_BYTES_PER_ENV))))),   # key for key the GPU arm's config
         "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": threads, "kind": "port",
                          "sample": f"{done} steps x {n} envs of the {args.task} post-physics path (reset+obs+reward), "
                                    "oracle/ torch port TorchScript-compiled like the reference, "
@@ -276,7 +275,9 @@ def run_reference_arm(args, rank, world):
         "gpu_launches": 0,
         "note": "the reference is Python/TorchScript and cannot travel to this box (isaacgym missing, sources not "
                 "copied): its CPU path is timed through the oracle port, pinned bit-for-bit to the reference's own JIT "
-                "functions in the build container (tests/golden)",
+                "functions in the build container (tests/golden).  The CPU arm steps ONE state set held in host memory; at "
+                "N > 1 rank 0 alone times its own shard (envs_per_gpu envs per step) on all host threads: the ratio against "
+                "the N-GPU line compares N GPUs with this one CPU pass",
     }
     print(json.dumps(line), flush=True)
 
