@@ -207,11 +207,14 @@ __global__ void __launch_bounds__(kTile) anymal_tile_kernel(const __grid_constan
             for (int j = 0; j < kDof; ++j) tsum += tq[j] * tq[j];
             const float r3 = tsum * p.k_torque;                                     // :352
             const float total = fmaxf(r1 + r2 + r3, 0.0f);                          // :356-357
+            // the fused step has just written the 13 contact norms into this lane's obs row (columns 21..33, same expression):
+            // the termination test reads them back instead of evaluating 1 + num_knee more IEEE square roots
+            const float* on = s.obs + lane * kObs + 21;
             const int bi = p.base_index * 3;
-            bool rs = norm3_ref(V3{cf[bi], cf[bi + 1], cf[bi + 2]}) > 1.0f;         // :359
+            bool rs = (MODE == 0 ? on[p.base_index] : norm3_ref(V3{cf[bi], cf[bi + 1], cf[bi + 2]})) > 1.0f;      // :359
             for (int k = 0; k < p.num_knee; ++k) {
                 const int ki = p.knee[k] * 3;
-                rs = rs || (norm3_ref(V3{cf[ki], cf[ki + 1], cf[ki + 2]}) > 1.0f);  // :360
+                rs = rs || ((MODE == 0 ? on[p.knee[k]] : norm3_ref(V3{cf[ki], cf[ki + 1], cf[ki + 2]})) > 1.0f);   // :360
             }
             const bool time_out = prog >= p.max_episode_length - 1;                 // :361
             out_reset = rs || time_out;                                             // :362

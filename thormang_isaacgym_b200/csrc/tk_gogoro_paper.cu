@@ -217,15 +217,26 @@ __device__ __forceinline__ void reset_env(const KParams& p, long long ne, const 
 // load -> store pairs and 47 zero stores in the middle of its tile's math: 3.5 us of a 27 us launch at 65536 envs).  q6 = the
 // env's new quaternion and planar velocity (columns 3..8), broadcast from its lane by the caller.  The ring slot and the
 // command-ring entry this step has just written (after the reset, as in the reference: :681 then :502-503) are left alone.
-__device__ __forceinline__ void reset_rows_warp(const KParams& p, long long ne, int lane, const float* q6, int slot) {
-    float rv = 0.0f;
-    if (lane < 2) rv = p.root_reset[ne * kRoot + lane];                             // :618
+// the three values per lane a reset's row traffic reads: requested as soon as the reset flags are known (ahead of the tile wait),
+// so that the writes at the end of the kernel do not sit on a cold DRAM round trip while the CTA holds its 25 KB of shared memory
+struct ResetFetch { float xy, pose0, pose1; };
+__device__ __forceinline__ ResetFetch reset_rows_fetch(const KParams& p, long long ne, int lane) {
+    ResetFetch f;
+    f.xy = (lane < 2) ? p.root_reset[ne * kRoot + lane] : 0.0f;                                     // :618
+    f.pose0 = (lane < p.num_dof) ? p.thormang_pose[ne * p.num_dof + lane] : 0.0f;                   // :647
+    f.pose1 = (lane + 32 < p.num_dof) ? p.thormang_pose[ne * p.num_dof + lane + 32] : 0.0f;
+    return f;
+}
+__device__ __forceinline__ void reset_rows_warp(const KParams& p, long long ne, int lane, const float* q6, int slot, const ResetFetch& f) {
+    float rv = f.xy;                                                                // :618
     rv = (lane == 2) ? 0.03f : rv;                                                  // :619
 #pragma unroll
     for (int c = 0; c < 6; ++c) rv = (lane == 3 + c) ? q6[c] : rv;                  // :635-641
     if (lane < kRoot) p.root[ne * kRoot + lane] = rv;                               // :645 (columns 9..12 <- 0, :636)
     float2* ds = reinterpret_cast<float2*>(p.state_dof) + ne * p.num_dof;
-    for (int j = lane; j < p.num_dof; j += 32) ds[j] = make_float2(p.thormang_pose[ne * p.num_dof + j], 0.0f);   // :647-648
+    if (lane < p.num_dof) ds[lane] = make_float2(f.pose0, 0.0f);                    // :647-648
+    if (lane + 32 < p.num_dof) ds[lane + 32] = make_float2(f.pose1, 0.0f);
+    for (int j = lane + 64; j < p.num_dof; j += 32) ds[j] = make_float2(p.thormang_pose[ne * p.num_dof + j], 0.0f);
     float4* cr = reinterpret_cast<float4*>(p.clean_ring + ne * kObs);
     for (int j = lane; j < kChunks; j += 32)
         if ((j >> 1) != slot) cr[j] = make_float4(0.f, 0.f, 0.f, 0.f);              // :681
@@ -327,6 +338,22 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
             prog += 1;                                                              // :384
             do_reset = p.reset[n] != 0 && !p.dbg_reset;                             // :385
             if (do_reset) prog = 0;                                                 // :678
+        }
+    }
+    constexpr int kPre = 2;                // resets per tile whose rows are requested ahead of the tile wait (2 % resetting: 3+ is rare)
+    ResetFetch pre_fetch[kPre];
+    unsigned reset_bits = 0;
+    if (MODE == 0) {
+        reset_bits = __ballot_sync(0xffffffffu, do_reset);
+        unsigned bits = reset_bits;
+#pragma unroll
+        for (int q = 0; q < kPre; ++q) {
+            pre_fetch[q] = ResetFetch{0.0f, 0.0f, 0.0f};
+            if (bits) {
+                const int e = __ffs(bits) - 1;
+                bits &= bits - 1;
+                pre_fetch[q] = reset_rows_fetch(p, static_cast<long long>(env0) + e, lane);
+            }
         }
     }
     __syncwarp();
@@ -507,14 +534,19 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
         for (int i = lane; i < nt * kObs; i += kTile) obs_tile[i] = s.frames[i];
     }
     if (MODE == 0) {                       // the row traffic of this tile's resets, off every env's critical path
-        unsigned bits = __ballot_sync(0xffffffffu, do_reset);
-        while (bits) {
+        unsigned bits = reset_bits;
+        for (int q = 0; bits; ++q) {
             const int e = __ffs(bits) - 1;
             bits &= bits - 1;
             float q6[6];
 #pragma unroll
             for (int c = 0; c < 6; ++c) q6[c] = __shfl_sync(0xffffffffu, reset_q6[c], e);
-            reset_rows_warp(p, static_cast<long long>(env0) + e, lane, q6, slot);
+            const long long ne = static_cast<long long>(env0) + e;
+            ResetFetch f;
+            if (q == 0) f = pre_fetch[0];
+            else if (q == 1) f = pre_fetch[kPre - 1];
+            else f = reset_rows_fetch(p, ne, lane);
+            reset_rows_warp(p, ne, lane, q6, slot, f);
         }
     }
     if (bulk && lane == 0) bulk_wait_read<0>();   // shared memory must stay alive until the engine has read it
