@@ -410,21 +410,30 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
             if (VAR == kTurning) {                      // sum of act_buff = the ring with this step's command in its slot (:742)
                 acc = o[6];
                 if (!do_reset) {
-#pragma unroll 1
+                    float h[kBuf];                  // all 20 shared loads first (independent), then the sum in the reference's order
+#pragma unroll
+                    for (int t = 0; t < kBuf; ++t) h[t] = s.cmd[lane * kBuf + t];
+#pragma unroll
                     for (int t = 0; t < kBuf; ++t)
-                        if (t != slot) acc += s.cmd[lane * kBuf + t];
+                        if (t != slot) acc += h[t];
                 }
             } else if (!do_reset) {
-                int t_slot = slot + 1;
-                if (t_slot == kBuf) t_slot = 0;
-                float a0 = s.cmd[lane * kBuf + t_slot] / 0.5f;                      // :722
-#pragma unroll 1
+                // the 19 older commands in time order (ring slot + 1 .. slot + 19): all shared loads first -- they are independent --
+                // then the 18 squared differences accumulated in the reference's order (a load -> subtract -> accumulate chain
+                // per iteration held 5 % of the kernel's stall samples at 65536 envs)
+                float h[kBuf - 1];
+#pragma unroll
+                for (int t = 0; t < kBuf - 1; ++t) {
+                    int idx = slot + 1 + t;
+                    idx -= (idx >= kBuf) ? kBuf : 0;
+                    h[t] = s.cmd[lane * kBuf + idx] / 0.5f;                         // :722
+                }
+                float a0 = h[0];
+#pragma unroll
                 for (int t = 1; t < kBuf - 1; ++t) {
-                    if (++t_slot == kBuf) t_slot = 0;
-                    const float a1 = s.cmd[lane * kBuf + t_slot] / 0.5f;
-                    const float d = a1 - a0;
+                    const float d = h[t] - a0;
                     acc += d * d;                                                   // :747 diff(...)**2
-                    a0 = a1;
+                    a0 = h[t];
                 }
                 prev_cmd = a0 * 0.5f;                                               // buffer_obs[:,-2,6] (exact: power of two)
                 const float d = o[6] / 0.5f - a0;
