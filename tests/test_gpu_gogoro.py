@@ -262,3 +262,27 @@ def test_config5_ppo_rollout_shape_with_in_kernel_noise():
         U.close(env.curent_speed, orc.curent_speed, what=f"curent_speed t={t}")
         orc.root_tensor.copy_(env.root_tensor.cpu()); orc.yaw_command.copy_(env.yaw_command.cpu())
     assert resets > 0 and resamples > 0
+
+
+@pytest.mark.parametrize("cuts", [(1,), (333,), (127, 128, 700), (512, 513)])
+def test_ragged_shards_with_global_env_ids(cuts):
+    """Env-range sharding at arbitrary cut points (offsets that are no multiple of the 128-env tile): all in-kernel draws are
+    keyed by the global env id, so the shards reproduce the unsharded step bit for bit (resets and resampling included)."""
+    n = 1000
+    st = syn.gogoro_state(n, seed=78)
+    st["reset_buf"][::9] = 1
+    st["progress_buf"][5::11] = 299
+    env, _, _ = U.make_gogoro_pair(n, state={k: v.clone() for k, v in st.items()})
+    env.post_physics_step()
+    keys = ("obs_buf", "buffer_obs", "rew_buf", "reset_buf", "progress_buf", "yaw_command", "curent_speed", "curent_command",
+            "imu_offsets", "steer_offsets", "action_history", "root_tensor")
+    full = {k: getattr(env, k).clone() for k in keys + ("state_dof",)}
+    edges = (0,) + tuple(cuts) + (n,)
+    for lo, hi in zip(edges[:-1], edges[1:]):
+        sub = {k: (v[lo * 39:hi * 39].clone() if k == "state_dof" else v[lo:hi].clone()) for k, v in st.items()}
+        e2, _, _ = U.make_gogoro_pair(hi - lo, state=sub, envIdOffset=lo)
+        e2.noise_seed = env.noise_seed
+        e2.post_physics_step()
+        for k in keys:
+            assert torch.equal(getattr(e2, k), full[k][lo:hi]), f"shard [{lo},{hi}) {k}"
+        assert torch.equal(e2.state_dof, full["state_dof"][lo * 39:hi * 39]), f"shard [{lo},{hi}) state_dof"

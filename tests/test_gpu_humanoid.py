@@ -495,3 +495,25 @@ def test_config5_ppo_rollout_shape_through_step():
         orc.root_states.copy_(env.root_states.cpu()); orc.dof_state.copy_(env.dof_state.cpu())
         orc.potentials.copy_(env.potentials.cpu()); orc.prev_potentials.copy_(env.prev_potentials.cpu())
     assert resets > 0 and bool(torch.isfinite(buf).all())
+
+
+@pytest.mark.parametrize("cuts", [(1,), (333,), (31, 64, 700), (512, 513)])
+def test_ragged_shards_with_global_env_ids(cuts):
+    """Env-range sharding at ARBITRARY cut points (shard sizes 1, 31, 333 ...; offsets that are no multiple of the 32-env tile):
+    in-kernel Philox noise is keyed by the global env id, so the shards must reproduce the unsharded step bit for bit."""
+    n = 1000
+    asset = syn.humanoid_asset()
+    st = syn.humanoid_state(n, seed=77, asset=asset)
+    st["reset_buf"][::9] = 1
+    env, _, _ = U.make_humanoid_pair(n, state={k: v.clone() for k, v in st.items()}, asset=asset)
+    env.post_physics_step()
+    keys = ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "potentials", "root_states")
+    full = {k: getattr(env, k).clone() for k in keys + ("dof_state",)}
+    edges = (0,) + tuple(cuts) + (n,)
+    for lo, hi in zip(edges[:-1], edges[1:]):
+        sub = {k: (v[lo * 21:hi * 21].clone() if k == "dof_state" else v[lo:hi].clone()) for k, v in st.items()}
+        e2, _, _ = U.make_humanoid_pair(hi - lo, state=sub, asset=asset, envIdOffset=lo)
+        e2.post_physics_step()
+        for k in keys:
+            assert torch.equal(getattr(e2, k), full[k][lo:hi]), f"shard [{lo},{hi}) {k}"
+        assert torch.equal(e2.dof_state, full["dof_state"][lo * 21:hi * 21]), f"shard [{lo},{hi}) dof_state"
