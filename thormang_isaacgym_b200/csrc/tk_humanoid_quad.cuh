@@ -117,6 +117,23 @@ __global__ void __launch_bounds__(kQuadThreads, TK_HUMANOID_QUAD_MIN_CTAS) human
         while (clock64() < until) __nanosleep(32);
     }
 
+    // ---- per-env scalars (coalesced, warp 0), requested ahead of the bulk copies (issuing one holds its lane ~0.25 us and the
+    // scalars were the last thing a tile waited for).  The reset set of the tile is published
+    // through shared memory: all four warps must agree on it, and warp 0 overwrites reset_buf at the end of the step.
+    long long prog = 0;
+    bool do_reset = false;
+    float pot_old = 0.0f, ret_old = 0.0f;
+    if (warp == 0) {
+        if (valid) {
+            pot_old = p.pot[n];
+            if (FUSED) {
+                prog = p.progress[n] + 1;                         // humanoid.py:288
+                do_reset = p.reset[n] != 0 && !p.dbg_reset;                       // :291
+                if (p.ep_return) ret_old = p.ep_return[n];
+                if (p.randomize) p.randomize[n] += 1;             // :289
+            }
+        }
+    }
     if (bulk) {
         if (warp == 0) {
             if (lane == 0) mbar_expect_tx(&bar, WT::kIn * 4);
@@ -136,25 +153,9 @@ __global__ void __launch_bounds__(kQuadThreads, TK_HUMANOID_QUAD_MIN_CTAS) human
         coop(in + WT::oRoot, g_root, nt * kRoot);
     }
 
-    // ---- per-env scalars (coalesced, warp 0), overlapped with the bulk loads.  The reset set of the tile is published
-    // through shared memory: all four warps must agree on it, and warp 0 overwrites reset_buf at the end of the step.
-    long long prog = 0;
-    bool do_reset = false;
-    float pot_old = 0.0f, ret_old = 0.0f;
-    if (warp == 0) {
-        if (valid) {
-            pot_old = p.pot[n];
-            if (FUSED) {
-                prog = p.progress[n] + 1;                         // humanoid.py:288
-                do_reset = p.reset[n] != 0 && !p.dbg_reset;                       // :291
-                if (p.ep_return) ret_old = p.ep_return[n];
-                if (p.randomize) p.randomize[n] += 1;             // :289
-            }
-        }
-        if (FUSED) {
-            const unsigned bits = __ballot_sync(0xffffffffu, do_reset);
-            if (lane == 0) s_reset_bits = bits;
-        }
+    if (warp == 0 && FUSED) {
+        const unsigned bits = __ballot_sync(0xffffffffu, do_reset);
+        if (lane == 0) s_reset_bits = bits;
     }
     TK_QSTAMP(1);
     __syncthreads();   // s_reset_bits, the mbarrier init and (generic path) the cooperative copies are visible to every warp
