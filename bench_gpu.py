@@ -644,7 +644,10 @@ def run_gpu_arm(args, rank, world):
                      "peak_source": peak_src,
                      "kernel": "humanoid_warp_kernel<21,true>" if task == "humanoid" else "gogoro_tile_kernel<0>",
                      "algorithmic_bytes_per_env_step": bpe,
-                     "how": "algorithmic bytes x envs per launch / (CUDA-event time of the timed region / launches), rank 0"},
+                     "how": "algorithmic bytes x envs per launch / (CUDA-event time of the timed region / launches), rank 0",
+                     "not_counted": "the launch also writes up_vec / heading_vec (24 B per env: SURVEY 8(a) H2 '+24 B if written'), "
+                                    "the timeout mask (1 B) and reads + writes the running episode return (8 B) for the statistics: "
+                                    "33 B per env-step on top of the 924 the fraction is computed from"},
         "e2e": e2e,
         "gpu_launches": res["launches"],
         "clocks": clocks,
