@@ -14,7 +14,7 @@ import bench as B   # noqa: E402  (constants, ClockSampler, CPU arm)
 HORIZON = 32        # PPO horizon_length of cfg/train/HumanoidPPO.yaml:66: statistics are all-reduced once per horizon
 
 
-def _make_humanoid(n, seed, device, env_off=0, stats=True):
+def _make_humanoid(n, seed, device, env_off=0, stats=True, debug_vectors=True):
     import torch
     from thormang_isaacgym_b200 import config as tcfg
     from thormang_isaacgym_b200 import synthetic as syn
@@ -25,6 +25,10 @@ def _make_humanoid(n, seed, device, env_off=0, stats=True):
     cfg = tcfg.humanoid_cfg(n, seed=1234)
     cfg["env"]["envIdOffset"] = env_off
     cfg["env"]["episodeStatistics"] = stats
+    # up_vec / heading_vec (humanoid.py:246) are read by the viewer's debug drawing only (:298-316) and are not part of the
+    # 924 B per env-step of SURVEY 8(a) ("+24 B if written").  The reference assigns them every step, so the headline and
+    # every default line refresh them too (the task's default); extras *_no_debug_vectors time the same launches without
+    cfg["env"]["writeDebugVectors"] = bool(debug_vectors)
     sim = FakeSim(n, 21, device, num_sensor_floats=12, asset=asset)
     sim.load_state(st)
     cfg["sim_backend"] = sim
@@ -645,9 +649,10 @@ def run_gpu_arm(args, rank, world):
                      "kernel": "humanoid_warp_kernel<21,true>" if task == "humanoid" else "gogoro_tile_kernel<0>",
                      "algorithmic_bytes_per_env_step": bpe,
                      "how": "algorithmic bytes x envs per launch / (CUDA-event time of the timed region / launches), rank 0",
-                     "not_counted": "the launch also writes up_vec / heading_vec (24 B per env: SURVEY 8(a) H2 '+24 B if written'), "
-                                    "the timeout mask (1 B) and reads + writes the running episode return (8 B) for the statistics: "
-                                    "33 B per env-step on top of the 924 the fraction is computed from"},
+                     "not_counted": "the launch also writes up_vec / heading_vec (24 B per env: SURVEY 8(a) H2 '+24 B if written'; the "
+                                    "reference assigns them every step, only its debug drawing reads them), the timeout mask (1 B) and "
+                                    "reads + writes the running episode return (8 B) for the statistics: 33 B per env-step on top of "
+                                    "the 924 the fraction is computed from; extras *_no_debug_vectors time the launches without the 24"},
         "e2e": e2e,
         "gpu_launches": res["launches"],
         "clocks": clocks,
@@ -678,6 +683,8 @@ def run_gpu_arm(args, rank, world):
                                     ("humanoid_32768", "humanoid", 32768, False),
                                     ("humanoid_65536", "humanoid", 65536, False),
                                     ("humanoid_65536_cuda_graph", "humanoid", 65536, True),
+                                    ("humanoid_65536_no_debug_vectors", "humanoid", 65536, "vec"),
+                                    ("humanoid_131072_no_debug_vectors", "humanoid", 131072, "vec"),
                                     ("humanoid_262144", "humanoid", 262144, False),
                                     ("humanoid_1048576", "humanoid", 1048576, False),
                                     ("config3_gogoro_65536", "gogoro", 65536, False),
@@ -692,7 +699,10 @@ def run_gpu_arm(args, rank, world):
                                     ("n1_gogoro_paper_262144", "gogoro_paper", 262144, False),
                                     ("n1_gogoro_paper_1048576", "gogoro_paper", 1048576, False)):
                 k = 300 if m <= 262144 else 60
-                r = _kernel_bench(torch, t, m, device, k, 20, seed=77, graph=gr)
+                if gr == "vec":
+                    r = _kernel_bench(torch, t, m, device, k, 20, seed=77, cfg_patch={"debug_vectors": False})
+                else:
+                    r = _kernel_bench(torch, t, m, device, k, 20, seed=77, graph=gr)
                 k = r["steps"]
                 b = B.BYTES_PER_ENV[t]
                 gbs = m * b / (r["ms_total"] / k * 1e-3) / 1e9

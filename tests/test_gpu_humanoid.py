@@ -517,3 +517,23 @@ def test_ragged_shards_with_global_env_ids(cuts):
         for k in keys:
             assert torch.equal(getattr(e2, k), full[k][lo:hi]), f"shard [{lo},{hi}) {k}"
         assert torch.equal(e2.dof_state, full["dof_state"][lo * 21:hi * 21]), f"shard [{lo},{hi}) dof_state"
+
+
+def test_write_debug_vectors_switch():
+    """cfg env.writeDebugVectors = False: up_vec / heading_vec (read by the reference's debug drawing only, humanoid.py:298-316)
+    keep their initial values, every other output of the fused step is bit-identical to the default (which refreshes them)."""
+    n = 4099
+    outs = []
+    for flag in (True, False):
+        env, _, st = U.make_humanoid_pair(n, seed=5, writeDebugVectors=flag)
+        up0, head0 = env.up_vec.clone(), env.heading_vec.clone()
+        env.post_physics_step()
+        torch.cuda.synchronize()
+        if flag:
+            assert not torch.equal(env.up_vec, up0) and not torch.equal(env.heading_vec, head0)
+        else:
+            assert torch.equal(env.up_vec, up0) and torch.equal(env.heading_vec, head0)
+        outs.append({k: getattr(env, k).clone() for k in ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "timeout_buf",
+                                                           "potentials", "prev_potentials", "dof_state", "root_states")})
+    for k in outs[0]:
+        assert torch.equal(outs[0][k], outs[1][k]), k

@@ -105,6 +105,9 @@ class Humanoid(VecTask):
         # humanoid.py:289 bumps randomize_buf every step, but only domain randomisation (out of scope, randomize is
         # False in Humanoid.yaml:64) ever reads it: the kernel skips that 16 B/env read-modify-write unless asked
         self.track_randomize_buf = bool(env.get("trackRandomizeBuf", False))
+        # up_vec / heading_vec (humanoid.py:246) are read by the debug drawing only (:298-316); True keeps the reference's
+        # behaviour of refreshing them every step (24 B per env-step), False leaves them at their initial values
+        self.write_debug_vectors = bool(env.get("writeDebugVectors", True))
         self.episode_stats = torch.zeros(nat.TK_STATS, device=dev, dtype=torch.float64)
         # in-kernel reset noise
         self.noise_seed = int(cfg.get("seed", 0)) & 0xFFFFFFFFFFFFFFFF
@@ -179,8 +182,10 @@ class Humanoid(VecTask):
                 ("rew_buf", self.rew_buf), ("reset_buf", self.reset_buf), ("progress_buf", self.progress_buf),
                 ("timeout_buf", self.timeout_buf),
                 ("randomize_buf", self.randomize_buf if self.track_randomize_buf else None),
-                ("potentials", self.potentials), ("prev_potentials", self.prev_potentials), ("up_vec", self.up_vec),
-                ("heading_vec", self.heading_vec), ("initial_root_states", self.initial_root_states),
+                ("potentials", self.potentials), ("prev_potentials", self.prev_potentials),
+                ("up_vec", self.up_vec if self.write_debug_vectors else None),
+                ("heading_vec", self.heading_vec if self.write_debug_vectors else None),
+                ("initial_root_states", self.initial_root_states),
                 ("initial_dof_pos", self.initial_dof_pos), ("episode_return", self.episode_return)):
             if t is not None:
                 if not t.is_contiguous() or t.device != torch.device(self.device):
