@@ -105,6 +105,7 @@ struct Smem {
     alignas(16) float la[kTile * kA * kDof];      // row reads straight from global (88 B rows, 176 B lane stride) lived on L1
                                                   // sector reuse: the step time followed the L1 size left by the shared-memory
                                                   // carve-out (336 us with 60 KB of L1, 400 us with 28 KB, 524288 envs)
+    alignas(16) float sums[kRows * 4];            // fused step: the four 22-DOF sums of a row, observation lane -> reward lane
     alignas(8) uint64_t bar;
 };
 
@@ -316,6 +317,14 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
 
     float my_rew = 0.f, my_dist = 0.f;
     int my_flag = 0;                        // bit 0: up_proj < 0.90, bit 1: distance to the table > 0.40
+    // Fused step: the reward lane was the long pole of a tile (row math 4.1 us against the observation lane's 1.5 us,
+    // tools/op3_timeline.py, and the CTA lives as long as its slowest warp).  The four sums over the 22 DOFs (:619-630) read
+    // what the observation lane walks anyway, so THAT lane accumulates them (same order, same bits) and hands them over
+    // through shared memory; the reward lane keeps its other terms in registers across one CTA barrier and adds everything
+    // up in the reference's order afterwards.
+    constexpr bool kSplitSums = MODE == 0;
+    float t_progress = 0.f, t_up = 0.f, t_air = 0.f, t_angz = 0.f, t_step = 0.f, t_nofly = 0.f, t_dist = 0.f, t_hold = 0.f;
+    bool t_still = false;
     if (valid) {
         if (!(MODE == 0 && do_reset)) {
 #pragma unroll
@@ -356,11 +365,32 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
 #pragma unroll
             for (int c = 0; c < kObs / 8; ++c)
                 if (obs_piece_ready(c) < 0) store_obs_piece(o, c, v, p.obs32);
+            const float2* otq2 = reinterpret_cast<const float2*>(s.tq) + row * (kDof / 2);
+            const float2* optq2 = reinterpret_cast<const float2*>(s.ptq) + row * (kDof / 2);
+            const float2* ola2 = reinterpret_cast<const float2*>(s.la) + row * (kDof / 2);
+            float tsum = 0.0f, legsum = 0.0f, ratesum = 0.0f, standsum = 0.0f;
 #pragma unroll
             for (int jj = 0; jj < kDof / 2; ++jj) {
                 float4 d = lds128(dof4 + jj);
                 const float2 ac = act2[jj];
                 if (rst) d = make_float4(p.default_dof_pos[2 * jj] + 0.0f, 0.0f, p.default_dof_pos[2 * jj + 1] + 0.0f, 0.0f);   // :456-457
+                if (kSplitSums) {                                                   // compute_op3_reward :619-630 for the reward lane
+                    const float2 t = otq2[jj], pt = optq2[jj];
+                    float2 l = ola2[jj];
+                    if (rst) l = make_float2(0.0f, 0.0f);                           // :486 last_actions of a reset env
+                    const float px[2] = {d.x, d.z};
+                    const float tv[2] = {t.x, t.y}, ptv[2] = {pt.x, pt.y}, av[2] = {ac.x, ac.y}, lv[2] = {l.x, l.y};
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int j = 2 * jj + h;
+                        tsum += fabsf(ptv[h] - tv[h]);                              // :619
+                        const float dev = fabsf(px[h] - p.default_dof_pos[j]);
+                        standsum += dev;                                            // :630
+                        if ((j >= 2 && j <= 7) || (j >= 11 && j <= 17) || j == 21) legsum += dev;   // :622-623
+                        const float da = lv[h] - av[h];
+                        ratesum += da * da;                                         // :627
+                    }
+                }
                 v[9 + 2 * jj] = (d.x - p.default_dof_pos[2 * jj]) * p.dof_pos_scale;                // :695
                 v[10 + 2 * jj] = (d.z - p.default_dof_pos[2 * jj + 1]) * p.dof_pos_scale;
                 v[31 + 2 * jj] = d.y * p.dof_vel_scale;
@@ -371,6 +401,7 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
                 for (int c = 0; c < kObs / 8; ++c)
                     if (obs_piece_ready(c) >= 0 && (obs_piece_ready(c) >> 1) == jj) store_obs_piece(o, c, v, p.obs32);
             }
+            if (kSplitSums) reinterpret_cast<float4*>(s.sums)[row] = make_float4(tsum, legsum, ratesum, standsum);
         } else {                                                                    // compute_reward :360-409, this agent
             bool zero_last = false;
             if (rst) {                                                              // reset_idx :440-489, this env's lanes
@@ -448,7 +479,7 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
             const float2* la2 = reinterpret_cast<const float2*>(s.la) + row * (kDof / 2);
             float tsum = 0.0f, legsum = 0.0f, ratesum = 0.0f, standsum = 0.0f;
 #pragma unroll
-            for (int jj = 0; jj < kDof / 2; ++jj) {
+            for (int jj = 0; jj < (kSplitSums ? 0 : kDof / 2); ++jj) {              // fused step: the observation lane has them
                 const float4 d = lds128(dof4 + jj);                                  // only the positions are used here
                 const float2 t = tq2[jj], pt = ptq2[jj], ac = act2[jj];
                 float2 l = la2[jj];
@@ -466,22 +497,43 @@ __global__ void __launch_bounds__(threads_of<MODE>(), TK_OP3_MIN_CTAS) op3_tile_
                     ratesum += da * da;                                             // :627
                 }
             }
-            const float rew_torque = tsum * p.k_torque;
-            const float rew_syns = legsum * p.k_syns;                               // :624
-            const float rew_action_rate = ratesum * p.k_rate;
-            const float rew_stand_still = (standsum * (still ? 1.0f : 0.0f)) * p.k_stand;
             const float dz = p.targets[2] - ang_raw.z;
             const float rew_ang_vel_z = expf(-(dz * dz) / 0.1f) * 0.1f;             // :632-633
             my_dist = norm3_ref(V3{r[0] - tb[0], r[1] - tb[1], r[2] - tb[2]});      // :644
             const float rew_distobject = expf(-my_dist / 0.32f) * 0.5f;             // :645
-            float total = progress_reward + 2.0f;                                   // :648-649, left to right (rew_orient is -0)
-            total += rew_torque; total += rew_up; total += rew_airtime; total += rew_ang_vel_z; total += step_sum;
-            total += rew_no_fly; total += rew_stand_still; total += rew_action_rate; total += rew_syns;
-            total += rew_distobject;
-            if (MODE == 0) p.pre_rew[n * kA + a] = total;
-            total += hold;
-            my_rew = fmaxf(total, 0.0f);                                            // :650
             my_flag = (up_proj < 0.90f ? 1 : 0) | (my_dist > 0.40f ? 2 : 0);        // :654-655
+            if (kSplitSums) {                   // the total is formed behind the CTA barrier below, once the sums are there
+                t_progress = progress_reward; t_up = rew_up; t_air = rew_airtime; t_angz = rew_ang_vel_z; t_step = step_sum;
+                t_nofly = rew_no_fly; t_dist = rew_distobject; t_hold = hold; t_still = still;
+            } else {
+                const float rew_torque = tsum * p.k_torque;
+                const float rew_syns = legsum * p.k_syns;                           // :624
+                const float rew_action_rate = ratesum * p.k_rate;
+                const float rew_stand_still = (standsum * (still ? 1.0f : 0.0f)) * p.k_stand;
+                float total = progress_reward + 2.0f;                               // :648-649, left to right (rew_orient is -0)
+                total += rew_torque; total += rew_up; total += rew_airtime; total += rew_ang_vel_z; total += step_sum;
+                total += rew_no_fly; total += rew_stand_still; total += rew_action_rate; total += rew_syns;
+                total += rew_distobject;
+                total += hold;
+                my_rew = fmaxf(total, 0.0f);                                        // :650
+            }
+        }
+    }
+    if (kSplitSums) {
+        __syncthreads();                                // the observation lanes' sums are in shared memory
+        if (role_rew && valid) {
+            const float4 sm = reinterpret_cast<const float4*>(s.sums)[row];         // (tsum, legsum, ratesum, standsum)
+            const float rew_torque = sm.x * p.k_torque;
+            const float rew_syns = sm.y * p.k_syns;                                 // :624
+            const float rew_action_rate = sm.z * p.k_rate;
+            const float rew_stand_still = (sm.w * (t_still ? 1.0f : 0.0f)) * p.k_stand;
+            float total = t_progress + 2.0f;                                        // :648-649, left to right (rew_orient is -0)
+            total += rew_torque; total += t_up; total += t_air; total += t_angz; total += t_step;
+            total += t_nofly; total += rew_stand_still; total += rew_action_rate; total += rew_syns;
+            total += t_dist;
+            p.pre_rew[n * kA + a] = total;
+            total += t_hold;
+            my_rew = fmaxf(total, 0.0f);                                            // :650
         }
     }
     TK_OSTAMP(4);
