@@ -22,7 +22,13 @@ int cuda_fail(cudaError_t e, const char* what) {
 
 const char* last_error() { return g_error; }
 
-__global__ void advance_epoch_kernel(unsigned long long* epoch) { *epoch += 1ull; }
+// The step kernels read the epoch AHEAD of their griddepcontrol.wait (tk_gogoro.cu, tk_humanoid_tile.cuh, tk_gogoro_paper.cu): this
+// kernel never triggers its dependents early, and the fence makes the new value visible device-wide before its only thread exits,
+// i.e. before the implicit trigger at completion can release a programmatic dependent.
+__global__ void advance_epoch_kernel(unsigned long long* epoch) {
+    *epoch += 1ull;
+    __threadfence();
+}
 
 // Launch-floor probe: the shell of the fused kernels (programmatic dependent launch, dynamic shared memory of the
 // same size, one 4-byte store per CTA when `sink` is given) with nothing in between.
