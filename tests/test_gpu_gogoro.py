@@ -286,3 +286,31 @@ def test_ragged_shards_with_global_env_ids(cuts):
         for k in keys:
             assert torch.equal(getattr(e2, k), full[k][lo:hi]), f"shard [{lo},{hi}) {k}"
         assert torch.equal(e2.state_dof, full["state_dof"][lo * 39:hi * 39]), f"shard [{lo},{hi}) state_dof"
+
+
+def test_cuda_graph_epoch_directly_in_front_of_the_step_many_replays():
+    """The fused kernel reads the device-side noise epoch AHEAD of its dependency wait.  Worst case for that: a graph whose
+    epoch kernel sits directly in front of ONE post_physics launch, replayed 40 times back to back -- every replay must use
+    the epoch bumped by its own graph (bit-identical to eager launches keyed (epoch << 32) | step), never a stale one."""
+    n, replays = 4096, 40
+    env_a, _, st = U.make_gogoro_pair(n, seed=62)
+    env_b, _, _ = U.make_gogoro_pair(n, seed=62, state={k: v.clone() for k, v in st.items()})
+    for e in (env_a, env_b):
+        e.reset_buf[::5] = 1                       # plenty of resets: the reset draws depend on the epoch too
+    for r in range(replays):
+        env_a.step_count = (r + 1) << 32           # captured host step 0, device epoch r + 1
+        env_a.post_physics_step()
+        env_a.reset_buf[::5] = 1
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    env_b.step_count = 0
+    with torch.cuda.graph(g):
+        env_b.advance_noise_epoch()
+        env_b.post_physics_step()
+        env_b.reset_buf[::5] = 1
+    for _ in range(replays):
+        g.replay()
+    torch.cuda.synchronize()
+    for name in ("obs_buf", "buffer_obs", "rew_buf", "progress_buf", "root_tensor", "yaw_command", "curent_speed",
+                 "imu_offsets", "steer_offsets", "config_vector"):
+        U.exact(getattr(env_b, name), getattr(env_a, name), f"graph vs eager after {replays} replays: {name}")

@@ -537,3 +537,31 @@ def test_write_debug_vectors_switch():
                                                            "potentials", "prev_potentials", "dof_state", "root_states")})
     for k in outs[0]:
         assert torch.equal(outs[0][k], outs[1][k]), k
+
+
+@pytest.mark.parametrize("n", [4096, 65536])      # four-warp kernel | one-warp kernel
+def test_cuda_graph_epoch_directly_in_front_of_the_step_many_replays(n):
+    """Both tile kernels resolve the device-side noise epoch AHEAD of their dependency wait.  Worst case: a graph whose epoch
+    kernel sits directly in front of ONE post_physics launch, replayed 40 times back to back; the reset noise of every replay
+    must be that of ITS epoch (bit-identical to eager launches keyed (epoch << 32) | step)."""
+    replays = 40
+    env_a, _, st = U.make_humanoid_pair(n, seed=33)
+    env_b, _, _ = U.make_humanoid_pair(n, seed=33, state={k: v.clone() for k, v in st.items()})
+    for e in (env_a, env_b):
+        e.reset_buf[::5] = 1
+    for r in range(replays):
+        env_a.step_count = (r + 1) << 32
+        env_a.post_physics_step()
+        env_a.reset_buf[::5] = 1
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    env_b.step_count = 0
+    with torch.cuda.graph(g):
+        env_b.advance_noise_epoch()
+        env_b.post_physics_step()
+        env_b.reset_buf[::5] = 1
+    for _ in range(replays):
+        g.replay()
+    torch.cuda.synchronize()
+    for name in ("obs_buf", "rew_buf", "progress_buf", "dof_state", "root_states", "potentials", "prev_potentials"):
+        U.exact(getattr(env_b, name), getattr(env_a, name), f"graph vs eager after {replays} replays: {name}")
