@@ -298,3 +298,33 @@ def test_error_behaviour():
     import ctypes as C
     assert env._lib.tk_gogoro_paper_post_physics(env._handle, C.byref(bad), env._stream()) == -1
     assert b"TK_NOISE_DENSE" in env._lib.tk_last_error()
+
+
+@pytest.mark.parametrize("turning", [False, True])
+def test_cuda_graph_epoch_directly_in_front_of_the_step_many_replays(turning):
+    """In-kernel Philox noise under graph replay: the fused kernel resolves the device-side epoch ahead of its dependency
+    wait.  Epoch kernel directly in front of one post_physics step (two kernels), 25 replays, against eager launches keyed
+    (epoch << 32) | step."""
+    n, replays = 2048, 25
+    st = syn.gogoro_paper_state(n, seed=83)
+    env_a, _, _ = U.make_gogoro_paper_pair(n, seed=83, state={k: v.clone() for k, v in st.items()}, turning=turning)
+    env_b, _, _ = U.make_gogoro_paper_pair(n, seed=83, state={k: v.clone() for k, v in st.items()}, turning=turning)
+    for e in (env_a, env_b):
+        e.reset_buf[::7] = 1
+    for r in range(replays):
+        env_a.step_count = (r + 1) << 32
+        env_a.post_physics_step()
+        env_a.reset_buf[::7] = 1
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    env_b.step_count = 0
+    with torch.cuda.graph(g):
+        env_b.advance_noise_epoch()
+        env_b.post_physics_step()
+        env_b.reset_buf[::7] = 1
+    for _ in range(replays):
+        g.replay()
+    torch.cuda.synchronize()
+    for name in ("obs_buf", "rew_buf", "progress_buf", "root_tensor", "yaw_command", "curent_speed", "steer_delay"):
+        U.exact(getattr(env_b, name), getattr(env_a, name), f"graph vs eager after {replays} replays: {name}")
+    U.exact(env_b.buffer_obs, env_a.buffer_obs, "clean frames")
