@@ -636,7 +636,7 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
         cudaError_t oe = (params->variant == kVarAnt)
             ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, humanoid_quad_kernel<AntSpec, true>, kQuadThreads, 0)
             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, humanoid_quad_kernel<HumanoidSpec, true>, kQuadThreads, 0);
-        if (oe == cudaSuccess && occ > 0) quad_occ = occ;
+        if (oe == cudaSuccess && occ > 0) quad_occ = occ < 8 ? occ : 8;      // measured up to 8 per SM (Humanoid); Ant's smaller tiles would allow more
         else cudaGetLastError();
     }
     h->quad = (h->tiles <= quad_occ * h->sm_count) ? 1 : 0;
