@@ -36,8 +36,11 @@ GOGORO_PAPER_BYTES_PER_ENV = 1509
 # SURVEY.md 8(f) N2 Anymal: reads root 52 + dof_state 96 + torques 48 + contact 156 + commands 12 + progress 8 +
 # reset 8; writes obs 244 + reward 4 + reset 8 + progress 8 + timeout 1
 ANYMAL_BYTES_PER_ENV = 645
+# SURVEY 8(f) N2 Ant (ant.py:213-287,318-408): reads root 52 + dof_state 64 + sensors 96 + actions 32 + potentials 8 + progress 8 +
+# reset 8 = 268; writes obs 240 + potentials 8 + reward 4 + reset 8 + progress 8 = 268 (+ timeout 1, episode return 8, up / heading 24)
+ANT_BYTES_PER_ENV = 536
 MA_OP3_BYTES_PER_ENV = 2545      # csrc/tk_ma_op3.cu header: 1404 B read + 1141 B written per env-step (two robots + table)
-BYTES_PER_ENV = {"ma_op3": MA_OP3_BYTES_PER_ENV, "anymal": ANYMAL_BYTES_PER_ENV, "humanoid": HUMANOID_BYTES_PER_ENV, "gogoro": GOGORO_BYTES_PER_ENV, "gogoro_paper": GOGORO_PAPER_BYTES_PER_ENV}
+BYTES_PER_ENV = {"ant": ANT_BYTES_PER_ENV, "ma_op3": MA_OP3_BYTES_PER_ENV, "anymal": ANYMAL_BYTES_PER_ENV, "humanoid": HUMANOID_BYTES_PER_ENV, "gogoro": GOGORO_BYTES_PER_ENV, "gogoro_paper": GOGORO_PAPER_BYTES_PER_ENV}
 L2_BYTES = 126 * 1024 * 1024
 METRIC = "env-steps/sec (obs+reward+reset)"
 

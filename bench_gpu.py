@@ -111,6 +111,28 @@ def _make_anymal(n, seed, device, env_off=0):
     return env, st
 
 
+def _make_ant(n, seed, device, env_off=0):
+    """Ant through the Humanoid kernel templates (AntSpec: D = 8, 60 obs, 24 sensor floats, every reward term live)."""
+    import torch
+    from thormang_isaacgym_b200 import config as tcfg
+    from thormang_isaacgym_b200 import synthetic as syn
+    from thormang_isaacgym_b200.sim.fake_sim import FakeSim
+    from thormang_isaacgym_b200.tasks.ant import Ant
+    asset = syn.ant_asset()
+    st = syn.ant_state(n, seed=seed, asset=asset, fallen_frac=0.01)     # ~1 % of the envs below the termination height, like the Humanoid workload
+    cfg = tcfg.ant_cfg(n, seed=1234)
+    cfg["env"]["envIdOffset"] = env_off
+    cfg["env"]["episodeStatistics"] = True
+    sim = FakeSim(n, 8, device, num_sensor_floats=24, asset=asset)
+    sim.load_state(st)
+    cfg["sim_backend"] = sim
+    dev_index = torch.device(device).index or 0
+    env = Ant(cfg, device, f"cuda:{dev_index}", -1, True)
+    for name in ("actions", "progress_buf", "reset_buf", "potentials", "prev_potentials"):
+        getattr(env, name).copy_(st[name].to(device))
+    return env, st
+
+
 def _make_ma_op3(n, seed, device, env_off=0, grip_all_reduce=False):
     """MA_OP3: two OP3 + table per env, 51 rigid bodies; ~1 % of the envs in reset per step."""
     import torch
@@ -135,8 +157,8 @@ def _make_ma_op3(n, seed, device, env_off=0, grip_all_reduce=False):
     return env, st
 
 
-_MAKERS = {"ma_op3": _make_ma_op3, "anymal": _make_anymal, "humanoid": _make_humanoid, "gogoro": _make_gogoro, "gogoro_paper": _make_gogoro_paper}
-_LAUNCHES_PER_STEP = {"ma_op3": 2, "anymal": 1, "humanoid": 1, "gogoro": 1, "gogoro_paper": 2}   # the paper variant: fused kernel + reward finalize
+_MAKERS = {"ant": _make_ant, "ma_op3": _make_ma_op3, "anymal": _make_anymal, "humanoid": _make_humanoid, "gogoro": _make_gogoro, "gogoro_paper": _make_gogoro_paper}
+_LAUNCHES_PER_STEP = {"ant": 1, "ma_op3": 2, "anymal": 1, "humanoid": 1, "gogoro": 1, "gogoro_paper": 2}   # the paper variant: fused kernel + reward finalize
 
 
 def _rotating_sets(n, bytes_per_env):
@@ -690,6 +712,8 @@ def run_gpu_arm(args, rank, world):
                                     ("config3_gogoro_65536", "gogoro", 65536, False),
                                     ("config3_gogoro_65536_cuda_graph", "gogoro", 65536, True),
                                     ("gogoro_4194304", "gogoro", 4194304, False),
+                                    ("n2_ant_65536", "ant", 65536, False),
+                                    ("n2_ant_1048576", "ant", 1048576, False),
                                     ("n2_anymal_65536", "anymal", 65536, False),
                                     ("n2_anymal_1048576", "anymal", 1048576, False),
                                     ("n3_ma_op3_65536", "ma_op3", 65536, False),

@@ -640,6 +640,13 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
         else cudaGetLastError();
     }
     h->quad = (h->tiles <= quad_occ * h->sm_count) ? 1 : 0;
+    // Ant (60 obs, 48 copy columns, every reward term live in warp 0) does not profit from the four-warp split: measured, us / step,
+    // four-warp + prefetch vs one-warp + prefetch: 9.05 / 7.47 at 16384 envs, 9.13 / 7.97 at 32768.  Its one-warp kernel takes the
+    // bulk-engine prefetch while the grid fits one wave (10.9 -> 10.4 us at 65536; 14.1 -> 14.9 at 98304: off beyond)
+    if (params->variant == kVarAnt) {
+        h->quad = 0;
+        if (h->prefetch < 0) h->prefetch = (h->tiles <= 14 * h->sm_count) ? 1 : 0;
+    }
     if (const char* env = getenv("TK_HUMANOID_QUAD")) h->quad = atoi(env) != 0;
     // the prefetch goes with the single wave: there the CTAs of launch k+1 become resident while launch k runs (or drains)
     // and have slack ahead of the wait; measured with the four-warp kernel 7.5 -> 6.65 us at 16384 envs, 9.0 -> 7.9 at 24576,
