@@ -89,6 +89,7 @@ struct KParams {
     int delay_w, use_delay;
     int variant;                   // kPaper | kTurning
     int vec_ok;
+    int prefetch;      // L2 prefetch of the tile ahead of griddepcontrol.wait (TK_PAPER_PREFETCH overrides)
     int spec;          // speculative reset draws ahead of the wait (thin grids; TK_PAPER_SPEC overrides)
     int dbg_reset;     // developer ablation (TK_PAPER_DBG_RESET=1): reset flags ignored
     int stagger_cycles, stagger_ctas, sm_count;   // first-wave stagger, see paper_tile_kernel
@@ -268,6 +269,23 @@ __global__ void __launch_bounds__(kTile) paper_tile_kernel(const __grid_constant
     // previous kernel of the stream drains; nothing of global memory is touched before griddepcontrol.wait
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (bulk && lane == 0) mbar_init(&s.bar, 1);
+    // L2 prefetch of the tile ahead of the dependency wait (single-wave grids, host decides: p.prefetch): a hint, nothing is
+    // consumed, stream order intact (see tk_humanoid_tile.cuh)
+    if (bulk && p.prefetch) {
+        if (lane == 0 && MODE != 2) bulk_prefetch_l2(obs_tile + kCh, kShiftBytes);
+        else if (lane == 1) bulk_prefetch_l2(p.root + static_cast<size_t>(env0) * kRoot, kTile * kRoot * 4);
+        else if (lane == 2 && MODE != 2) bulk_prefetch_l2(p.cmd_ring + static_cast<size_t>(env0) * kBuf, kTile * kBuf * 4);
+        else if (lane == 3) prefetch_l2(p.yaw_command + env0);
+        else if (lane == 4) prefetch_l2(p.curent_command + env0);
+        else if (lane == 5) prefetch_l2(p.steer_delay + env0);
+        else if (lane == 6) prefetch_l2(p.steer_delay + env0 + 16);
+        else if (lane == 7 && MODE != 2) prefetch_l2(p.progress + env0);
+        else if (lane == 8 && MODE != 2) prefetch_l2(p.progress + env0 + 16);
+        else if (lane == 9 && MODE == 0) prefetch_l2(p.reset + env0);
+        else if (lane == 10 && MODE == 0) prefetch_l2(p.reset + env0 + 16);
+        else if (lane == 11 && MODE != 2) prefetch_l2(p.curent_imu_x_offset + env0);
+        else if (lane == 12 && MODE != 2) prefetch_l2(p.curent_speed_offset + env0);
+    }
     // Ahead of the wait: everything that is a pure function of (seed, step, global env id).  The noise epoch of CUDA-graph
     // replays is written only by tk_gogoro_paper_advance_epoch's single-thread kernel, a plain launch that never triggers its
     // dependents early (see tk_gogoro.cu).  Sensor draws always; the reset draws speculatively for EVERY env on thin grids
@@ -818,6 +836,10 @@ static void fill_kparams(const TkGogoroPaper* h, KParams& k) {
     { const char* env = getenv("TK_PAPER_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
     k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.command_ring, 16);
     k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count;
+    // measured on / off, us per step: 4096 envs 10.6 / 10.9, 16384 12.2 / 13.1, 32768 14.8 / 15.7, 65536 23.3 / 24.2, 262144 72.3 / 73.3,
+    // 1 M 268.9 / 272.4 -- on at every size (the predecessor of the fused kernel is the short finalize grid of the previous step)
+    k.prefetch = 1;
+    if (const char* env = getenv("TK_PAPER_PREFETCH")) k.prefetch = atoi(env);
     k.spec = (h->tiles <= 16 * h->sm_count) ? 1 : 0;
     if (const char* env = getenv("TK_PAPER_SPEC")) k.spec = atoi(env);
     k.fin_vec_ok = aligned_to(B.rew_buf, 16) && aligned_to(B.reset_buf, 16) && (!B.episode_return || aligned_to(B.episode_return, 16));
