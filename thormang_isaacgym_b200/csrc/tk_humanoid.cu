@@ -651,7 +651,13 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     // the prefetch goes with the single wave: there the CTAs of launch k+1 become resident while launch k runs (or drains)
     // and have slack ahead of the wait; measured with the four-warp kernel 7.5 -> 6.65 us at 16384 envs, 9.0 -> 7.9 at 24576,
     // 9.55 -> 8.2 at 32768 (the one-warp kernel on such grids: 8.6 -> 8.0, 9.5 -> 8.6, 10.7 -> 10.5)
-    if (h->prefetch < 0) h->prefetch = (h->quad || h->tiles <= 4 * h->sm_count) ? 2 : 0;
+    // Between the four-warp kernel's wave and the ONE-warp kernel's own (12 CTAs / SM: 37888 .. 56832 Humanoid envs) the one-warp
+    // kernel takes the bulk-engine prefetch: 10.3 -> 8.7 us at 40960 envs, 11.2 -> 10.3 at 49152, 12.1 -> 11.3 at 56832 (71 % of
+    // peak); one tile past the wave it costs (65536: 13.3 -> 15.5+ us), so the switch is the wave itself.
+    if (h->prefetch < 0) {
+        if (h->quad || h->tiles <= 4 * h->sm_count) h->prefetch = 2;
+        else h->prefetch = (params->variant != kVarAnt && h->tiles <= h->stagger_slots * h->sm_count) ? 1 : 0;
+    }
     h->warm = 0;          // measured: no gain at 16384 envs (6.55 vs 6.58 / 7.09 us with 1 / 3), -3 % at 32768, +8 % at 65536
     if (const char* env = getenv("TK_HUMANOID_WARM")) h->warm = atoi(env);
     // the four-warp kernel only runs single-wave grids, where spacing the CTAs merely delays them (6.5 us with 0 cycles,
