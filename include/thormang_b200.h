@@ -437,6 +437,33 @@ int tk_gogoro_paper_stats(TkGogoroPaper* h, double* stats_out, int32_t accumulat
 int tk_gogoro_paper_philox_noise(TkGogoroPaper* h, uint64_t seed, uint64_t step, int64_t env_id_offset, float* sensor_unit,
                                  float* reset_unit, float* speed_unit, float* yaw_unit, void* stream);
 
+/* No counterpart in the reference: an allocation-free twin of tk_gogoro_paper_diff_sums, added for this library's users.
+ *
+ * Every other entry point of this section needs a TkGogoroPaper handle, and tk_gogoro_paper_create reserves the handle's
+ * work areas with cudaMalloc.  Some hosts are not in a position to do that: a plug-in running inside a simulator or
+ * trainer that has already claimed the whole device heap for its own pool, code running where the implicit device-wide
+ * synchronisation of cudaMalloc / cudaFree is forbidden (a real-time step loop, a host callback), or a sidecar that must not
+ * disturb another process's memory accounting on the GPU.  Such a caller can still produce the per-GPU payload of the
+ * reward's cross-env term (what range-sharded runs all-reduce between the two kernels of a step) with this call.  It takes
+ * no handle, calls no cudaMalloc / cudaFree / allocating library routine, and keeps its scratch (1024 fp64 block partials and
+ * an arrival counter, 8448 bytes) in a fixed array built into the library; every GPU that loads the library holds those
+ * bytes until the process exits.
+ *
+ *   command_ring [num_envs,20] fp32 (device): the clean command ring (TkGogoroPaperBuffers.command_ring) as the fused step
+ *                left it; newest_slot = the ring slot that step wrote (completed steps before it, modulo 20).
+ *   variant      TK_GOGORO_PAPER_VARIANT_PAPER: sums_out = {sum over envs of the 19 squared differences of consecutive
+ *                commands / 0.5 in time order, 19 * num_envs};  _TURNING: {sum of the ring, 20 * num_envs}.
+ *   sums_out     [2] fp64 (device).  Equal to tk_gogoro_paper_diff_sums after the same step up to fp64 summation order.
+ *
+ * Limit: num_envs <= 1,048,576 per call; larger sizes are refused with TK_ERR_INVALID (split the env range, the sums add).
+ * Runs on the CURRENT device.  The first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ * which may load the module); make that first call before any stream capture.  All calls on a device share the one
+ * array: it still holds the previous call's partials (each call overwrites the ones it uses and clears the arrival
+ * counter on `stream` before its kernel), and two calls that overlap on the GPU -- different streams, or different host
+ * threads on different streams -- race on it and return garbage.  Calls on one stream are safe back to back. */
+int tk_gogoro_paper_diff_sums_static(const float* command_ring, int64_t num_envs, int32_t variant, int32_t newest_slot,
+                                     double* sums_out, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Anymal  (isaacgymenvs/tasks/anymal.py, cfg/task/Anymal.yaml) -- SURVEY.md 8(f) row N2: the canonical
  * `targets = action_scale * actions + default_dof_pos` PD-target write (:229-232) and contact-force termination

@@ -191,6 +191,7 @@ SYMBOLS = {
     "tk_gogoro_paper_compute_obs_rwd": (C.c_int, [_p, C.POINTER(GogoroPaperNoise), _p]),
     "tk_gogoro_paper_post_physics": (C.c_int, [_p, C.POINTER(GogoroPaperNoise), _p]),
     "tk_gogoro_paper_diff_sums": (C.c_int, [_p, _p, _p]),
+    "tk_gogoro_paper_diff_sums_static": (C.c_int, [_p, _i64, _i32, _i32, _p, _p]),
     "tk_gogoro_paper_finalize_reward": (C.c_int, [_p, _p, _p]),
     "tk_gogoro_paper_reset_idx": (C.c_int, [_p, _p, _i32, _p, _p]),
     "tk_gogoro_paper_clean_frames": (C.c_int, [_p, _p, _p]),

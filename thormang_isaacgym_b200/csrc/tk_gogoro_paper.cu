@@ -30,6 +30,7 @@
 // of the command ring in place of the squared differences.  reward3 (:738-741) compares min with min: identically 1.
 #include "tk_common.cuh"
 
+#include <atomic>
 #include <cstdlib>
 #include <new>
 
@@ -688,6 +689,82 @@ __global__ void __launch_bounds__(256) paper_diff_sums_kernel(const double* __re
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// tk_gogoro_paper_diff_sums_static: the same {sum, count} pair as paper_diff_sums_kernel, recomputed from the command ring
+// the caller passes, with every byte of scratch in this file-scope array (no handle, hence no cudaMalloc anywhere).
+// Layout: kStaticBlocks fp64 block partials, then one 32-bit arrival counter at byte kStaticBlocks * 8.
+// Each loaded copy of the library holds kStaticBytes on every GPU it touches until the process exits.
+// ---------------------------------------------------------------------------------------------
+constexpr long long kStaticMaxEnvs = 1ll << 20;      // 1,048,576 envs: BASELINE config 4, the largest shape the repo runs
+constexpr int kStaticBlocks = 1024;                  // grid cap; blocks walk the envs with a grid stride
+constexpr int kStaticThreads = 256;
+constexpr int kStaticMaxDevices = 64;           // per-device address cache of the entry point
+constexpr size_t kStaticBytes = kStaticBlocks * sizeof(double) + 256;
+static __device__ __align__(256) unsigned char g_diff_scratch[kStaticBytes];
+
+template <int VAR>
+__global__ void __launch_bounds__(kStaticThreads) paper_diff_sums_static_kernel(const float* __restrict__ ring, long long n, int slot,
+                                                                                unsigned char* __restrict__ scratch,
+                                                                                double* __restrict__ out) {
+    __shared__ double red[kStaticThreads / 32];
+    __shared__ bool last;
+    double* partial = reinterpret_cast<double*>(scratch);
+    unsigned int* arrived = reinterpret_cast<unsigned int*>(scratch + kStaticBlocks * sizeof(double));
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    double mine = 0.0;
+    for (long long e = static_cast<long long>(blockIdx.x) * kStaticThreads + tid; e < n; e += static_cast<long long>(gridDim.x) * kStaticThreads) {
+        const float* row = ring + e * kBuf;
+        float acc = 0.0f;
+        if (VAR == kTurning) {                       // newest command first, then the other 19 in slot order (the fused kernel's order)
+            acc = row[slot];
+#pragma unroll
+            for (int t = 0; t < kBuf; ++t)
+                if (t != slot) acc += row[t];
+        } else {                                     // time order: slot + 1 (oldest) .. slot + 19, slot (newest)
+            int idx = slot + 1;
+            idx -= (idx >= kBuf) ? kBuf : 0;
+            float a0 = row[idx] / 0.5f;
+#pragma unroll
+            for (int t = 1; t < kBuf; ++t) {
+                idx = slot + 1 + t;
+                idx -= (idx >= kBuf) ? kBuf : 0;
+                const float v = row[idx] / 0.5f;
+                const float d = v - a0;
+                acc += d * d;
+                a0 = v;
+            }
+        }
+        mine += static_cast<double>(acc);            // fp32 inside an env, fp64 across envs: as in the fused kernel
+    }
+    mine = warp_sum(mine);
+    if (lane == 0) red[warp] = mine;
+    __syncthreads();
+    if (tid == 0) {
+        double b = 0.0;
+#pragma unroll
+        for (int w = 0; w < kStaticThreads / 32; ++w) b += red[w];
+        partial[blockIdx.x] = b;                     // overwritten, never accumulated: nothing of the previous call survives
+        __threadfence();
+        last = atomicAdd(arrived, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    double v = 0.0;
+    for (int i = tid; i < static_cast<int>(gridDim.x); i += kStaticThreads) v += __ldcg(partial + i);
+    v = warp_sum(v);
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    if (tid == 0) {
+        double S = 0.0;
+#pragma unroll
+        for (int w = 0; w < kStaticThreads / 32; ++w) S += red[w];
+        out[0] = S;
+        out[1] = static_cast<double>(n) * (VAR == kTurning ? kBuf : kBuf - 1);
+        *arrived = 0u;                               // the host also clears it ahead of every launch
+    }
+}
+
 // pre_physics_step :342-378, one env per thread
 __global__ void __launch_bounds__(256) paper_pre_kernel(const __grid_constant__ KParams p, const float* __restrict__ actions,
                                                          int zero_fill) {
@@ -1101,5 +1178,43 @@ int tk_gogoro_paper_philox_noise(TkGogoroPaper* h, uint64_t seed, uint64_t step,
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }
+
+int tk_gogoro_paper_diff_sums_static(const float* command_ring, int64_t num_envs, int32_t variant, int32_t newest_slot,
+                                     double* sums_out, void* stream) {
+    // argument checks first: they need no GPU
+    TK_REQUIRE(command_ring && sums_out, TK_ERR_INVALID, "null argument");
+    TK_REQUIRE(variant == kPaper || variant == kTurning, TK_ERR_INVALID, "unknown variant %d", variant);
+    TK_REQUIRE(newest_slot >= 0 && newest_slot < kBuf, TK_ERR_INVALID, "newest_slot %d is not a ring slot (0..%d)", newest_slot, kBuf - 1);
+    TK_REQUIRE(num_envs > 0, TK_ERR_INVALID, "num_envs must be positive (got %lld)", static_cast<long long>(num_envs));
+    TK_REQUIRE(num_envs <= kStaticMaxEnvs, TK_ERR_INVALID,
+               "tk_gogoro_paper_diff_sums_static takes at most %lld envs per call (got %lld): its scratch is a fixed array inside "
+               "the library; split the range, or use tk_gogoro_paper_diff_sums with a handle",
+               kStaticMaxEnvs, static_cast<long long>(num_envs));
+    // Set-up, once per device and with that device current: g_diff_scratch names a host-side shadow of the array here, the
+    // kernel needs the address the array has on THIS GPU.
+    static std::atomic<unsigned char*> dev_ptr[kStaticMaxDevices];
+    int dev = -1;
+    TK_CUDA(cudaGetDevice(&dev));
+    TK_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, TK_ERR_INVALID, "device ordinal %d beyond the %d this entry point keeps addresses for", dev,
+               kStaticMaxDevices);
+    unsigned char* scratch = dev_ptr[dev].load(std::memory_order_acquire);
+    if (!scratch) {
+        TK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&scratch), g_diff_scratch));
+        TK_REQUIRE(scratch != nullptr, TK_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address on device %d", dev);
+        dev_ptr[dev].store(scratch, std::memory_order_release);
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // the arrival counter must start at zero whatever an earlier (possibly failed) launch left behind
+    TK_CUDA(cudaMemsetAsync(scratch + kStaticBlocks * sizeof(double), 0, sizeof(unsigned int), st));
+    const long long want = (num_envs + kStaticThreads - 1) / kStaticThreads;
+    const unsigned grid = static_cast<unsigned>(want < kStaticBlocks ? want : kStaticBlocks);
+    if (variant == kTurning)
+        paper_diff_sums_static_kernel<kTurning><<<grid, kStaticThreads, 0, st>>>(command_ring, num_envs, newest_slot, scratch, sums_out);
+    else
+        paper_diff_sums_static_kernel<kPaper><<<grid, kStaticThreads, 0, st>>>(command_ring, num_envs, newest_slot, scratch, sums_out);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
 
 }  // extern "C"
