@@ -215,7 +215,7 @@ def test_speculative_reset_matches_lazy_reset(n, monkeypatch):
         st["reset_buf"][i] = 1
     outs = []
     for spec in ("0", "1"):
-        monkeypatch.setenv("TK_GOGORO_SPEC", spec)          # read at every launch
+        monkeypatch.setenv("TK_GOGORO_SPEC", spec)          # read when the handle is created
         env, _, _ = U.make_gogoro_pair(n, state={k: v.clone() for k, v in st.items()})
         for _ in range(3):
             env.post_physics_step()
@@ -314,3 +314,33 @@ def test_cuda_graph_epoch_directly_in_front_of_the_step_many_replays():
     for name in ("obs_buf", "buffer_obs", "rew_buf", "progress_buf", "root_tensor", "yaw_command", "curent_speed",
                  "imu_offsets", "steer_offsets", "config_vector"):
         U.exact(getattr(env_b, name), getattr(env_a, name), f"graph vs eager after {replays} replays: {name}")
+
+
+def test_cuda_graph_epoch_bump_recorded_after_the_steps():
+    """A graph [step, step, advance_epoch] on a handle whose epoch was never bumped before the capture: the captured
+    launches must still read the device-side epoch word (a NULL baked in at capture time would make every replay draw
+    the noise of replay 0).  Replay r runs host steps 0 and 1 under epoch r."""
+    n, replays = 2048, 6
+    env_a, _, st = U.make_gogoro_pair(n, seed=63)
+    env_b, _, _ = U.make_gogoro_pair(n, seed=63, state={k: v.clone() for k, v in st.items()})
+    for e in (env_a, env_b):
+        e.reset_buf[::5] = 1
+    for r in range(replays):
+        for host_step in (0, 1):
+            env_a.step_count = (r << 32) | host_step
+            env_a.post_physics_step()
+            env_a.reset_buf[::5] = 1
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for host_step in (0, 1):
+            env_b.step_count = host_step
+            env_b.post_physics_step()
+            env_b.reset_buf[::5] = 1
+        env_b.advance_noise_epoch()
+    for _ in range(replays):
+        g.replay()
+    torch.cuda.synchronize()
+    for name in ("obs_buf", "buffer_obs", "rew_buf", "progress_buf", "root_tensor", "yaw_command", "curent_speed",
+                 "imu_offsets", "steer_offsets", "config_vector"):
+        U.exact(getattr(env_b, name), getattr(env_a, name), f"[step, step, bump] graph vs eager after {replays} replays: {name}")

@@ -950,12 +950,23 @@ struct TkGogoro {
     bool epoch_used;      // tk_gogoro_advance_epoch was called: the kernels must read the device-side epoch (NULL otherwise)
     long long* dbg_ts;
     int prefetch;         // TK_GOGORO_PREFETCH: L2 prefetch ahead of griddepcontrol.wait (default: thin grids only)
+    int knob_ldg, knob_spec, dbg_reset;   // developer knobs, read once in tk_gogoro_create
 };
 
 static void pair_uniform(const double* in, float* out) { out[0] = static_cast<float>(in[0]); out[1] = static_cast<float>(in[1] - in[0]); }
 static void pair_normal(const double* in, float* out) { out[0] = static_cast<float>(in[0]); out[1] = static_cast<float>(in[1]); }
 
-static void fill_kparams(const TkGogoro* h, KParams& k) {
+// The device-side epoch word, or NULL while nobody can have bumped it (saves the eager path one dependent load).  A launch
+// that is being CAPTURED always gets the word: tk_gogoro_advance_epoch may be recorded after it in the same graph, or be
+// called between replays, and a NULL baked into the graph would make every replay draw the same Philox noise.
+static unsigned long long* epoch_word(const TkGogoro* h, cudaStream_t st) {
+    if (h->epoch_used) return h->step_dev;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) { cudaGetLastError(); return h->step_dev; }
+    return cs == cudaStreamCaptureStatusNone ? nullptr : h->step_dev;
+}
+
+static void fill_kparams(const TkGogoro* h, KParams& k, cudaStream_t st) {
     const TkGogoroParams& P = h->params;
     const TkGogoroBuffers& B = h->buf;
     k.root = B.root_tensor; k.state_dof = B.state_dof; k.obs_buf = B.obs_buf; k.buffer_obs = B.buffer_obs; k.rew = B.rew_buf;
@@ -967,15 +978,15 @@ static void fill_kparams(const TkGogoro* h, KParams& k) {
     k.vel_cmd = B.dof_speed_command; k.ep_return = B.episode_return;
     k.partials = h->partials; k.tile_base_reset = h->bases; k.tile_base_speed = h->bases + h->tiles;
     k.reset_unit = nullptr; k.sensor_unit = nullptr; k.speed_unit = nullptr; k.yaw_unit = nullptr; k.reset_rows = 0;
-    k.seed = 0; k.step = 0; k.env_off = 0; k.noise_mode = TK_NOISE_NONE; k.step_dev = h->epoch_used ? h->step_dev : nullptr; k.dbg_ts = h->dbg_ts;
+    k.seed = 0; k.step = 0; k.env_off = 0; k.noise_mode = TK_NOISE_NONE; k.step_dev = epoch_word(h, st); k.dbg_ts = h->dbg_ts;
     k.n = P.num_envs; k.num_dof = P.num_dof; k.steering_joint = P.steering_joint; k.rear_wheel_joint = P.rear_wheel_joint;
     k.max_episode_length = P.max_episode_length; k.speed_freq = P.speed_freq_update; k.yaw_freq = P.yaw_freq_update;
     k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.action_history, 16) && aligned_to(B.obs_buf, 16) &&
                aligned_to(B.buffer_obs, 16);
     k.prefetch = h->prefetch;
     k.ldg_tiles = 0;              // measured slower: 6.7 vs 6.3 us eager, 6.1 vs 5.8 us from a graph at 65536 envs; equal at 131072 / 262144
-    if (const char* env = getenv("TK_GOGORO_LDG")) k.ldg_tiles = atoi(env);
-    { const char* env = getenv("TK_GOGORO_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
+    if (h->knob_ldg != kKnobUnset) k.ldg_tiles = h->knob_ldg;
+    k.dbg_reset = h->dbg_reset;
     k.max_steering = P.max_steering; k.max_steering_change = P.max_steering_change;
     pair_normal(P.imu_filter_noise, k.imu_filter); pair_normal(P.imu_noise, k.imu); pair_normal(P.speed_sensor_noise, k.speed_sensor);
     pair_normal(P.steering_action_noise, k.steer_action); pair_uniform(P.speed_range, k.speed);
@@ -1008,6 +1019,9 @@ int tk_gogoro_create(const TkGogoroParams* params, TkGogoro** out) {
     h->last_grid = 0;
     h->dbg_ts = nullptr;
     h->epoch_used = false;
+    h->knob_ldg = knob_int("TK_GOGORO_LDG");
+    h->knob_spec = knob_int("TK_GOGORO_SPEC");
+    h->dbg_reset = ablation_knob("TK_GOGORO_DBG_RESET");
     {   // the prefetch pays while the whole grid is resident at once (the CTAs sit at the wait while the previous kernel
         // drains); on deep grids it would only double the requests of a bandwidth-bound stream
         int sms = 148;
@@ -1015,7 +1029,7 @@ int tk_gogoro_create(const TkGogoroParams* params, TkGogoro** out) {
         // measured (HBM-cold, prefetch + speculative reset on / off): 65536 envs 6.2 / 8.4 us, 131072 7.1 / 9.8, 262144 13.5 / 14.7,
         // 1048576 47.6 / 40.0 -- the switch sits at two waves of resident CTAs
         h->prefetch = (h->tiles <= 16 * sms) ? 1 : 0;
-        if (const char* env = getenv("TK_GOGORO_PREFETCH")) h->prefetch = atoi(env);
+        if (const char* env = knob("TK_GOGORO_PREFETCH")) h->prefetch = atoi(env);
     }
     h->partials = nullptr; h->counts = nullptr; h->bases = nullptr; h->step_dev = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
@@ -1069,7 +1083,7 @@ int tk_gogoro_pre_physics(TkGogoro* h, const float* actions, const float* steer_
     TK_REQUIRE(actions != nullptr, TK_ERR_INVALID, "null actions");
     TK_CUDA(cudaSetDevice(h->params.device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    KParams k; fill_kparams(h, k);
+    KParams k; fill_kparams(h, k, static_cast<cudaStream_t>(stream));
     k.seed = seed; k.step = step; k.env_off = env_id_offset;
     const int blocks = (k.n + 255) / 256;
     if (zero_fill) {
@@ -1088,7 +1102,7 @@ int tk_gogoro_compute_observations(TkGogoro* h, float* obs_out, void* stream) {
     if (int rc = check_bound(h)) return rc;
     TK_REQUIRE(obs_out != nullptr, TK_ERR_INVALID, "null obs_out");
     TK_CUDA(cudaSetDevice(h->params.device));
-    KParams k; fill_kparams(h, k);
+    KParams k; fill_kparams(h, k, static_cast<cudaStream_t>(stream));
     gogoro_tile_kernel<2><<<h->tiles, kTile, 0, static_cast<cudaStream_t>(stream)>>>(k, obs_out);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
@@ -1098,7 +1112,7 @@ int tk_gogoro_compute_reward(TkGogoro* h, const float* cur_obs, void* stream) {
     if (int rc = check_bound(h)) return rc;
     TK_REQUIRE(cur_obs != nullptr, TK_ERR_INVALID, "null cur_obs");
     TK_CUDA(cudaSetDevice(h->params.device));
-    KParams k; fill_kparams(h, k);
+    KParams k; fill_kparams(h, k, static_cast<cudaStream_t>(stream));
     gogoro_reward_kernel<<<(k.n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(k, cur_obs);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
@@ -1108,7 +1122,7 @@ int tk_gogoro_compute_obs_rwd(TkGogoro* h, const float* sensor_unit, uint64_t se
                               void* stream) {
     if (int rc = check_bound(h)) return rc;
     TK_CUDA(cudaSetDevice(h->params.device));
-    KParams k; fill_kparams(h, k);
+    KParams k; fill_kparams(h, k, static_cast<cudaStream_t>(stream));
     k.sensor_unit = sensor_unit;
     k.noise_mode = sensor_unit ? TK_NOISE_DENSE : TK_NOISE_PHILOX;
     k.seed = seed; k.step = step; k.env_off = env_id_offset;
@@ -1123,7 +1137,7 @@ int tk_gogoro_reset_idx(TkGogoro* h, const int64_t* env_ids, int32_t kcount, con
     if (kcount == 0) return TK_OK;
     TK_REQUIRE(kcount > 0 && env_ids && unit, TK_ERR_INVALID, "bad reset_idx arguments");
     TK_CUDA(cudaSetDevice(h->params.device));
-    KParams k; fill_kparams(h, k);
+    KParams k; fill_kparams(h, k, static_cast<cudaStream_t>(stream));
     gogoro_reset_idx_kernel<<<(kcount + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
         k, reinterpret_cast<const long long*>(env_ids), kcount, unit);
     TK_CUDA(cudaGetLastError());
@@ -1135,7 +1149,7 @@ int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream
     TK_REQUIRE(noise != nullptr, TK_ERR_INVALID, "null noise descriptor");
     TK_CUDA(cudaSetDevice(h->params.device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    KParams k; fill_kparams(h, k);
+    KParams k; fill_kparams(h, k, static_cast<cudaStream_t>(stream));
     const int mode = noise->reset.mode;
     TK_REQUIRE(mode >= TK_NOISE_NONE && mode <= TK_NOISE_PHILOX, TK_ERR_INVALID, "bad noise mode %d", mode);
     k.noise_mode = mode;
@@ -1167,7 +1181,7 @@ int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream
         float* no_out = nullptr;
         // thin grids with in-kernel noise: the speculative-reset variant (see spec_reset); TK_GOGORO_SPEC=0/1 overrides
         bool spec = mode == TK_NOISE_PHILOX && h->prefetch != 0;
-        if (const char* env = getenv("TK_GOGORO_SPEC")) spec = mode == TK_NOISE_PHILOX && atoi(env) != 0;
+        if (h->knob_spec != kKnobUnset) spec = mode == TK_NOISE_PHILOX && h->knob_spec != 0;
         if (spec) cudaLaunchKernelEx(&cfg, gogoro_tile_kernel<0, true>, k, no_out);
         else cudaLaunchKernelEx(&cfg, gogoro_tile_kernel<0, false>, k, no_out);
     }
@@ -1207,7 +1221,7 @@ int tk_gogoro_philox_noise(TkGogoro* h, uint64_t seed, uint64_t step, int64_t en
     TK_REQUIRE(h != nullptr, TK_ERR_INVALID, "null handle");
     TK_CUDA(cudaSetDevice(h->params.device));
     gogoro_philox_kernel<<<(h->params.num_envs + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        h->params.num_envs, seed, step, env_id_offset, h->epoch_used ? h->step_dev : nullptr, steer_unit, sensor_unit, reset_unit,
+        h->params.num_envs, seed, step, env_id_offset, epoch_word(h, static_cast<cudaStream_t>(stream)), steer_unit, sensor_unit, reset_unit,
         speed_unit, yaw_unit);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
