@@ -177,7 +177,12 @@ int tk_humanoid_philox_noise(TkHumanoid* h, uint64_t seed, uint64_t step, int64_
                              float* unit_pos, float* unit_vel, void* stream);
 
 /* Bump the device-side noise epoch (one single-thread kernel).  Host-supplied `step` values are frozen inside a captured
- * CUDA graph; capturing ONE call of this per graph makes every replay draw fresh Philox noise.  Not needed otherwise. */
+ * CUDA graph; capturing ONE call of this per graph makes every replay draw fresh Philox noise.  Not needed otherwise.
+ * Invariant the step kernels rely on (all tk_*_advance_epoch): they load the epoch word AHEAD of their programmatic
+ * dependency wait.  That is sound only because this call is a plain (non-programmatic) one-thread launch that fences
+ * device-wide behind the increment and never triggers its dependents early, and because NOTHING else writes the word.
+ * Do not write the handle's epoch word from other kernels or copies, and do not re-implement this bump as a kernel that
+ * issues griddepcontrol.launch_dependents. */
 int tk_humanoid_advance_epoch(TkHumanoid* h, void* stream);
 
 /* Episode statistics.  Every tk_humanoid_post_physics adds its per-CTA partial sums into a handle-owned
@@ -285,7 +290,9 @@ int tk_gogoro_reset_idx(TkGogoro* h, const int64_t* env_ids, int32_t k, const fl
 /* Gogoro.post_physics_step (gogoro_new.py:373-389) + vec_task.py:345, ONE fused kernel. */
 int tk_gogoro_post_physics(TkGogoro* h, const TkGogoroNoise* noise, void* stream);
 
-/* same as tk_humanoid_advance_epoch */
+/* same as tk_humanoid_advance_epoch.  Ordering inside a capture is free: a launch recorded while its stream is being
+ * captured always reads the device-side epoch word, whether this call is recorded before the steps, after them, or is
+ * made between replays (eager launches skip that load until this has been called once on the handle). */
 int tk_gogoro_advance_epoch(TkGogoro* h, void* stream);
 
 /* stats: sum reward, #reset, #timeout, sum episode_return of reset envs, sum episode length of reset envs,

@@ -273,3 +273,17 @@ def test_bad_variant_is_rejected():
     h = C.c_void_p()
     assert lib.tk_gogoro_paper_create(C.byref(p), C.byref(h)) == -1
     assert b"TK_GOGORO_PAPER_VARIANT" in lib.tk_last_error()
+
+
+def test_supplied_draws_of_the_wrong_width_are_refused():
+    """The TURNING variant reads 8 reset draws per row: a [N,5] tensor (the paper variant's shape) must be refused on the
+    host instead of being read out of bounds on the device."""
+    n = 64
+    env, _, _ = U.make_gogoro_paper_pair(n, seed=5, turning=True)
+    nz = syn.gogoro_paper_noise(n, seed=6)                      # reset_cols = 5
+    with pytest.raises(ValueError, match="reset_unit"):
+        env.post_physics_step(nz["sensor_unit"].to(DEV), nz["reset_unit"].to(DEV), nz["speed_unit"].to(DEV), nz["yaw_unit"].to(DEV))
+    with pytest.raises(ValueError, match="sensor_unit"):
+        env.post_physics_step(nz["sensor_unit"][:, :5].to(DEV), None, None, None)
+    with pytest.raises(ValueError, match="unit"):
+        env.reset_idx(torch.arange(4, device=DEV), torch.rand(4, 5))

@@ -34,6 +34,17 @@ def make(seed: int, task: str, num_envs: int, sim_device: str = "cuda:0", rl_dev
         rank, world, device, rank_seed = parallel.init_multi_gpu(seed)
         sim_device = rl_device = device
         parallel.shard_cfg(cfg, rank, world)
-        cfg["rank_seed"] = rank_seed               # train.py:80-82 (host-side torch RNG); cfg["seed"] keys the kernels
+        cfg["rank_seed"] = rank_seed               # train.py:80-82; cfg["seed"] keys the kernels
+        # set_seed(seed + rank) of train.py:80-82: the host-side torch draws (reset_idx without supplied draws, the DR
+        # `corr` tensor) must differ between ranks like the reference's
+        import torch
+        torch.manual_seed(rank_seed)
+        if torch.cuda.is_available():
+            torch.cuda.manual_seed_all(rank_seed)
+        import logging
+        logging.getLogger("thormang_isaacgym_b200").info(
+            "multi_gpu: rank %d/%d on %s owns envs [%d, %d) of the GLOBAL num_envs=%d (the reference reads num_envs per rank); "
+            "host RNG seed %d", rank, world, device, cfg["env"].get("envIdOffset", 0),
+            cfg["env"].get("envIdOffset", 0) + cfg["env"]["numEnvs"], num_envs, rank_seed)
     return isaacgym_task_map[task](cfg, rl_device, sim_device, graphics_device_id, headless,
                                    virtual_screen_capture, force_render)

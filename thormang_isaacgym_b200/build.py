@@ -15,7 +15,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libthormang_b200.so")
 SOURCES = ["tk_common.cu", "tk_humanoid.cu", "tk_gogoro.cu", "tk_gogoro_paper.cu", "tk_anymal.cu", "tk_ma_op3.cu", "tk_epilogue.cu"]
-HEADERS = ["tk_common.cuh", "tk_humanoid_tile.cuh", os.path.join("..", "..", "include", "thormang_b200.h")]
+HEADERS = ["tk_common.cuh", "tk_humanoid_tile.cuh", "tk_humanoid_quad.cuh", os.path.join("..", "..", "include", "thormang_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

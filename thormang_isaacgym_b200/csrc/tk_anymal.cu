@@ -359,6 +359,7 @@ struct TkAnymal {
     int tiles, use_pdl, sm_count, stagger_cycles, stagger_slots;
     double* partials;
     unsigned long long* step_dev;
+    int knob_prefetch, dbg_reset;      // developer knobs, read once in tk_anymal_create
 };
 
 static void fill_kparams(const TkAnymal* h, KParams& k) {
@@ -376,8 +377,8 @@ static void fill_kparams(const TkAnymal* h, KParams& k) {
     // pays while the whole grid is resident at once (one wave: 11 CTAs / SM = 52096 envs): 7.0 -> 6.5 us at 16384 envs, 8.3 -> 7.4 at
     // 32768, 9.4 -> 8.8 at 49152; beyond the wave it costs (11.8 -> 12.4 us at 65536)
     k.prefetch = (h->tiles <= h->stagger_slots * h->sm_count) ? 1 : 0;
-    if (const char* env = getenv("TK_ANYMAL_PREFETCH")) k.prefetch = atoi(env);
-    { const char* env = getenv("TK_ANYMAL_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
+    if (h->knob_prefetch != kKnobUnset) k.prefetch = h->knob_prefetch;
+    k.dbg_reset = h->dbg_reset;
     k.vec_ok = aligned_to(B.root_states, 16) && aligned_to(B.dof_state, 16) && aligned_to(B.torques, 16) &&
                aligned_to(B.contact_forces, 16) && aligned_to(B.commands, 16) && aligned_to(B.obs_buf, 16);
     k.dof_pos_scale = P.dof_pos_scale; k.dof_vel_scale = P.dof_vel_scale; k.action_scale = P.action_scale;
@@ -431,7 +432,9 @@ int tk_anymal_create(const TkAnymalParams* params, TkAnymal** out) {
     h->params = *params;
     h->bound = false; h->ran = false;
     h->use_pdl = 1;
-    if (const char* env = getenv("TK_ANYMAL_PDL")) h->use_pdl = atoi(env) != 0;
+    if (const char* env = knob("TK_ANYMAL_PDL")) h->use_pdl = atoi(env) != 0;
+    h->knob_prefetch = knob_int("TK_ANYMAL_PREFETCH");
+    h->dbg_reset = ablation_knob("TK_ANYMAL_DBG_RESET");
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     h->sm_count = 148;
     cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, params->device);
@@ -442,7 +445,7 @@ int tk_anymal_create(const TkAnymalParams* params, TkAnymal** out) {
         else cudaGetLastError();
     }
     if (h->tiles <= h->sm_count * 2) h->stagger_cycles = 0;      // a thin single wave is only delayed by it
-    if (const char* env = getenv("TK_ANYMAL_STAGGER")) h->stagger_cycles = atoi(env);
+    if (const char* env = knob("TK_ANYMAL_STAGGER")) h->stagger_cycles = atoi(env);
     h->partials = nullptr; h->step_dev = nullptr;
     cudaError_t e = cudaMalloc(&h->partials, sizeof(double) * TK_STATS * kStatSlots);
     if (e == cudaSuccess) e = cudaMemset(h->partials, 0, sizeof(double) * TK_STATS * kStatSlots);

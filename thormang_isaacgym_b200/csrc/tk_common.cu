@@ -3,6 +3,10 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
+#include <mutex>
+#include <set>
+#include <string>
 
 namespace tk {
 
@@ -21,6 +25,32 @@ int cuda_fail(cudaError_t e, const char* what) {
 }
 
 const char* last_error() { return g_error; }
+
+const char* knob(const char* name) {
+    const char* v = getenv(name);
+    if (!v) return nullptr;
+    static std::mutex mu;
+    static std::set<std::string> warned;
+    std::lock_guard<std::mutex> lock(mu);
+    if (warned.insert(name).second)
+        fprintf(stderr, "[thormang_b200] developer knob %s=%s is active: kernels / launch parameters differ from the defaults\n", name, v);
+    return v;
+}
+
+int knob_int(const char* name) {
+    const char* v = knob(name);
+    return v ? atoi(v) : kKnobUnset;
+}
+
+int ablation_knob(const char* name) {
+#ifdef TK_DEVELOPER_KNOBS
+    const char* v = knob(name);
+    return v ? atoi(v) : 0;
+#else
+    (void)name;
+    return 0;
+#endif
+}
 
 // The step kernels read the epoch AHEAD of their griddepcontrol.wait (tk_gogoro.cu, tk_humanoid_tile.cuh, tk_gogoro_paper.cu): this
 // kernel never triggers its dependents early, and the fence makes the new value visible device-wide before its only thread exits,

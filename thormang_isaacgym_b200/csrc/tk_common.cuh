@@ -21,6 +21,15 @@ void set_error(const char* fmt, ...);
 int cuda_fail(cudaError_t e, const char* what);
 const char* last_error();
 
+// Developer knobs (TK_* environment variables of the tuning tools).  They are read when a handle is CREATED and kept in
+// it -- never on the launch path -- and a knob that is set announces itself once on stderr, so a stray variable cannot
+// change a trainer's kernels unnoticed.  The *_DBG_RESET ablations, which switch the reset prologue off and thereby break
+// parity with the reference, exist only in builds made with -DTK_DEVELOPER_KNOBS (TK_NVCC_EXTRA of build.py).
+constexpr int kKnobUnset = -2147483647 - 1;
+const char* knob(const char* name);                  // getenv + one warning per name
+int knob_int(const char* name);                      // kKnobUnset when the variable is not set
+int ablation_knob(const char* name);                 // 0 unless built with -DTK_DEVELOPER_KNOBS
+
 #define TK_CUDA(call)                                                   \
     do {                                                                \
         cudaError_t _e = (call);                                        \
@@ -283,7 +292,8 @@ __global__ void advance_epoch_kernel(unsigned long long* epoch);
 
 // ---------------------------------------------------------------------------------------------
 // Episode-statistics partials: kStatSlots rows of TK_STATS fp64 accumulators per handle.  A tile adds its eight warp
-// sums to row (tile & (kStatSlots-1)) with RED.ADD.F64 (no return value); tk_*_stats sums the rows in a fixed order.
+// sums to row (tile & (kStatSlots-1)) with RED.ADD.F64 (no return value); tk_*_stats sums the rows in a fixed order
+// (the adds INTO a row arrive in scheduling order: sums are reproducible to fp64 rounding, not bit for bit).
 // 256 rows keep same-address contention negligible (one address hit by every CTA cost 20 % at 32768 CTAs) and keep
 // the finalize kernel at ~2 us (a row per tile made it a 40 us single-CTA walk over 4096 rows).  fp64 adds of
 // warp-level fp32 sums: the order of the REDs within a row is not fixed, results agree to ~1e-13 relative.

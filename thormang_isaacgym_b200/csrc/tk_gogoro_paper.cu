@@ -888,6 +888,7 @@ struct TkGogoroPaper {
     bool ran;
     int stagger_cycles, stagger_slots, sm_count;
     int use_pdl;      // programmatic dependent launch of the two step kernels (TK_GOGORO_PAPER_PDL=0 disables)
+    int knob_prefetch, knob_spec, dbg_reset;   // developer knobs, read once in tk_gogoro_paper_create
 };
 
 static void pair_uniform(const double* in, float* out) { out[0] = static_cast<float>(in[0]); out[1] = static_cast<float>(in[1] - in[0]); }
@@ -910,15 +911,15 @@ static void fill_kparams(const TkGogoroPaper* h, KParams& k) {
     k.n = P.num_envs; k.num_dof = P.num_dof; k.steering_joint = P.steering_joint; k.rear_wheel_joint = P.rear_wheel_joint;
     k.max_episode_length = P.max_episode_length; k.speed_freq = P.speed_freq_update; k.yaw_freq = P.yaw_freq_update;
     k.delay_w = P.delay_width; k.use_delay = P.use_steer_delay; k.variant = P.variant;
-    { const char* env = getenv("TK_PAPER_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
+    k.dbg_reset = h->dbg_reset;
     k.vec_ok = aligned_to(B.root_tensor, 16) && aligned_to(B.command_ring, 16);
     k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count;
     // measured on / off, us per step: 4096 envs 10.6 / 10.9, 16384 12.2 / 13.1, 32768 14.8 / 15.7, 65536 23.3 / 24.2, 262144 72.3 / 73.3,
     // 1 M 268.9 / 272.4 -- on at every size (the predecessor of the fused kernel is the short finalize grid of the previous step)
     k.prefetch = 1;
-    if (const char* env = getenv("TK_PAPER_PREFETCH")) k.prefetch = atoi(env);
+    if (h->knob_prefetch != kKnobUnset) k.prefetch = h->knob_prefetch;
     k.spec = (h->tiles <= 16 * h->sm_count) ? 1 : 0;
-    if (const char* env = getenv("TK_PAPER_SPEC")) k.spec = atoi(env);
+    if (h->knob_spec != kKnobUnset) k.spec = h->knob_spec;
     k.fin_vec_ok = aligned_to(B.rew_buf, 16) && aligned_to(B.reset_buf, 16) && (!B.episode_return || aligned_to(B.episode_return, 16));
     k.max_steering = P.max_steering; k.start_speed = P.start_speed;
     k.delay_lo = static_cast<float>(P.command_delay[0]);
@@ -968,7 +969,10 @@ int tk_gogoro_paper_create(const TkGogoroPaperParams* params, TkGogoroPaper** ou
     h->params = *params;
     h->bound = false; h->ran = false;
     h->use_pdl = 1;
-    if (const char* env = getenv("TK_GOGORO_PAPER_PDL")) h->use_pdl = atoi(env) != 0;
+    if (const char* env = knob("TK_GOGORO_PAPER_PDL")) h->use_pdl = atoi(env) != 0;
+    h->knob_prefetch = knob_int("TK_PAPER_PREFETCH");
+    h->knob_spec = knob_int("TK_PAPER_SPEC");
+    h->dbg_reset = ablation_knob("TK_PAPER_DBG_RESET");
     h->tiles = (params->num_envs + kTile - 1) / kTile;
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, params->device);
@@ -978,8 +982,8 @@ int tk_gogoro_paper_create(const TkGogoroPaperParams* params, TkGogoroPaper** ou
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, paper_tile_kernel<0, kPaper>, kTile, 0) == cudaSuccess && occ > 0) h->stagger_slots = occ;
         else cudaGetLastError();
     }
-    if (const char* env = getenv("TK_GOGORO_PAPER_STAGGER")) h->stagger_cycles = atoi(env);
-    if (const char* env = getenv("TK_GOGORO_PAPER_STAGGER_SLOTS")) h->stagger_slots = atoi(env);
+    if (const char* env = knob("TK_GOGORO_PAPER_STAGGER")) h->stagger_cycles = atoi(env);
+    if (const char* env = knob("TK_GOGORO_PAPER_STAGGER_SLOTS")) h->stagger_slots = atoi(env);
     (void)sms;
     h->finalize_grid = (params->num_envs + 1023) / 1024;            // four envs per thread, 256 threads
     h->partials = nullptr; h->diff_slots = nullptr; h->tick = nullptr; h->done_ctr = nullptr; h->step_dev = nullptr;

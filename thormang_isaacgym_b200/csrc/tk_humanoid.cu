@@ -507,6 +507,7 @@ struct TkHumanoid {
     int quad;             // TK_HUMANOID_QUAD: four-warp tile kernel (tk_humanoid_quad.cuh) 1 | one-warp kernel 0; default by grid size
     unsigned long long* step_dev;
     long long* dbg_ts;
+    int dbg_reset, coop_store, knob_prefetch_slots;   // developer knobs, read once in tk_humanoid_create
 };
 
 // fallback for the four-warp kernel's occupancy when the query fails (see tk_humanoid_create); measured B200, us / step,
@@ -550,11 +551,11 @@ static void fill_kparams(const TkHumanoid* h, KParams& k) {
     k.partials = h->partials; k.tile_rank_base = h->tile_base; k.dbg_ts = h->dbg_ts; k.step_dev = h->step_dev;
     k.prefetch = h->prefetch;
     k.warm = h->warm;
-    { const char* env = getenv("TK_HUMANOID_DBG_RESET"); k.dbg_reset = env ? atoi(env) : 0; }
-    { const char* env = getenv("TK_HUMANOID_COOP_STORE"); k.coop_store = env ? atoi(env) : 0; }
+    k.dbg_reset = h->dbg_reset;
+    k.coop_store = h->coop_store;
     k.stagger_cycles = h->stagger_cycles; k.sm_count = h->sm_count; k.stagger_ctas = h->stagger_slots * h->sm_count; k.stagger_free = h->stagger_free;
     k.prefetch_ctas = k.stagger_ctas;
-    if (const char* env = getenv("TK_HUMANOID_PREFETCH_SLOTS")) k.prefetch_ctas = atoi(env) * h->sm_count;
+    if (h->knob_prefetch_slots != kKnobUnset) k.prefetch_ctas = h->knob_prefetch_slots * h->sm_count;
     k.unit_a = nullptr; k.unit_b = nullptr; k.noise_rows = 0; k.seed = 0; k.step = 0; k.env_off = 0;
     k.noise_mode = TK_NOISE_NONE;
     k.n = P.num_envs;
@@ -599,7 +600,10 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
     h->dbg_ts = nullptr;
     h->use_pdl = 1;
     h->obs_copy = nullptr;
-    if (const char* env = getenv("TK_HUMANOID_PDL")) h->use_pdl = atoi(env) != 0;
+    if (const char* env = knob("TK_HUMANOID_PDL")) h->use_pdl = atoi(env) != 0;
+    h->dbg_reset = ablation_knob("TK_HUMANOID_DBG_RESET");
+    { const int v = knob_int("TK_HUMANOID_COOP_STORE"); h->coop_store = v == kKnobUnset ? 0 : v; }
+    h->knob_prefetch_slots = knob_int("TK_HUMANOID_PREFETCH_SLOTS");
     // First-wave stagger (see the kernel): 500 SM cycles per resident slot; anything in 400..700 measured the same
     // (B200: 16.5 -> 14.0 us at 65536 envs, 25.4 -> 23.0 us at 131072).  The slot count is the kernel's real occupancy.
     h->stagger_cycles = 500; h->stagger_slots = 12; h->smem_pad = 0; h->sm_count = 148;
@@ -613,12 +617,12 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
         else cudaGetLastError();
     }
     h->prefetch = -1;   // auto, resolved below
-    if (const char* env = getenv("TK_HUMANOID_PREFETCH")) h->prefetch = atoi(env);
-    if (const char* env = getenv("TK_HUMANOID_STAGGER")) h->stagger_cycles = atoi(env);
-    if (const char* env = getenv("TK_HUMANOID_STAGGER_SLOTS")) h->stagger_slots = atoi(env);
+    if (const char* env = knob("TK_HUMANOID_PREFETCH")) h->prefetch = atoi(env);
+    if (const char* env = knob("TK_HUMANOID_STAGGER")) h->stagger_cycles = atoi(env);
+    if (const char* env = knob("TK_HUMANOID_STAGGER_SLOTS")) h->stagger_slots = atoi(env);
     h->stagger_free = 0;
-    if (const char* env = getenv("TK_HUMANOID_STAGGER_FREE")) h->stagger_free = atoi(env);
-    if (const char* env = getenv("TK_HUMANOID_SMEM_PAD")) {
+    if (const char* env = knob("TK_HUMANOID_STAGGER_FREE")) h->stagger_free = atoi(env);
+    if (const char* env = knob("TK_HUMANOID_SMEM_PAD")) {
         h->smem_pad = atoi(env);
         cudaFuncSetAttribute(humanoid_warp_kernel<HumanoidSpec, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_pad);
         cudaFuncSetAttribute(humanoid_warp_kernel<AntSpec, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_pad);
@@ -647,7 +651,7 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
         h->quad = 0;
         if (h->prefetch < 0) h->prefetch = (h->tiles <= 14 * h->sm_count) ? 1 : 0;
     }
-    if (const char* env = getenv("TK_HUMANOID_QUAD")) h->quad = atoi(env) != 0;
+    if (const char* env = knob("TK_HUMANOID_QUAD")) h->quad = atoi(env) != 0;
     // the prefetch goes with the single wave: there the CTAs of launch k+1 become resident while launch k runs (or drains)
     // and have slack ahead of the wait; measured with the four-warp kernel 7.5 -> 6.65 us at 16384 envs, 9.0 -> 7.9 at 24576,
     // 9.55 -> 8.2 at 32768 (the one-warp kernel on such grids: 8.6 -> 8.0, 9.5 -> 8.6, 10.7 -> 10.5)
@@ -659,11 +663,11 @@ int tk_humanoid_create(const TkHumanoidParams* params, TkHumanoid** out) {
         else h->prefetch = (params->variant != kVarAnt && h->tiles <= h->stagger_slots * h->sm_count) ? 1 : 0;
     }
     h->warm = 0;          // measured: no gain at 16384 envs (6.55 vs 6.58 / 7.09 us with 1 / 3), -3 % at 32768, +8 % at 65536
-    if (const char* env = getenv("TK_HUMANOID_WARM")) h->warm = atoi(env);
+    if (const char* env = knob("TK_HUMANOID_WARM")) h->warm = atoi(env);
     // the four-warp kernel only runs single-wave grids, where spacing the CTAs merely delays them (6.5 us with 0 cycles,
     // 6.8 with 500, 7.4 with 1000 at 16384 envs)
-    if (h->quad && !getenv("TK_HUMANOID_STAGGER")) h->stagger_cycles = 0;
-    if (h->quad && !getenv("TK_HUMANOID_STAGGER_SLOTS")) {      // the stagger counts the resident CTAs of the kernel that runs
+    if (h->quad && !knob("TK_HUMANOID_STAGGER")) h->stagger_cycles = 0;
+    if (h->quad && !knob("TK_HUMANOID_STAGGER_SLOTS")) {      // the stagger counts the resident CTAs of the kernel that runs
         int occ = 0;
         cudaError_t oe = (params->variant == kVarAnt)
             ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, humanoid_quad_kernel<AntSpec, true>, kQuadThreads, 0)

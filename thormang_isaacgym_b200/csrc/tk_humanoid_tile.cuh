@@ -462,7 +462,8 @@ __global__ void TK_HUMANOID_BOUNDS humanoid_warp_kernel(const __grid_constant__ 
         if (p.obs2) warp_copy(p.obs2 + static_cast<size_t>(env0) * OBS, buf, nt * OBS, lane);
     }
 
-    // ---- statistics partials: one row per tile, fixed reduction order -> deterministic
+    // ---- statistics partials: tiles that share a slot (tile & 255) add with fp64 RED.ADD in arrival order, so the last bits of the
+    //      sums can differ from run to run (counts are exact); tests compare them at rtol 1e-9
     if (FUSED) {
         const unsigned m_reset = __ballot_sync(0xffffffffu, out_reset);
         const unsigned m_to = __ballot_sync(0xffffffffu, out_timeout);

@@ -818,7 +818,7 @@ static cudaError_t launch_tile_nf(const TkOp3* h, const KParams& k, cudaStream_t
     static int opted = 0;    // dynamic shared memory this instantiation has been opted in for
     static int pad = -1;     // TK_OP3_SMEM_PAD (developer knob): extra dynamic shared memory per CTA = fewer resident CTAs per SM
     if (pad < 0) {
-        const char* env = getenv("TK_OP3_SMEM_PAD");
+        const char* env = knob("TK_OP3_SMEM_PAD");
         pad = env ? atoi(env) : 0;
     }
     const int bytes = static_cast<int>(sizeof(Smem)) + pad + ((MODE != 1 && k.contact_tile) ? kTile * k.nb * 12 : 0);
@@ -838,7 +838,7 @@ static cudaError_t launch_tile_nf(const TkOp3* h, const KParams& k, cudaStream_t
                 occ = 6;
             }
             slots = occ;
-            const char* env = getenv("TK_OP3_STAGGER");
+            const char* env = knob("TK_OP3_STAGGER");
             cycles = env ? atoi(env) : 0;      // measured: no effect at 65536 .. 524288 envs (16-env tiles: many waves)
         }
         kk.stagger_ctas = slots * h->sm_count;

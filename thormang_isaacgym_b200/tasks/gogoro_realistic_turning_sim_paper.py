@@ -257,6 +257,9 @@ class Gogoro(VecTask):
                 t = t.to(self.device, dtype=torch.float).contiguous()
                 if t.shape[0] != self.n_envs:
                     raise ValueError(f"{field}: supplied draws are addressed by env id, need {self.n_envs} rows")
+                want = {"sensor_unit": (SENSOR_NOISE_COLS,), "reset_unit": (self.RESET_NOISE_COLS,)}.get(field, ())
+                if tuple(t.shape[1:]) != want:      # the kernels index these with a fixed row stride
+                    raise ValueError(f"{field}: need shape {(self.n_envs,) + want}, got {tuple(t.shape)}")
                 keep.append(t)
             setattr(nz, field, nat.ptr(t))
         keep.append(nz)
@@ -298,6 +301,8 @@ class Gogoro(VecTask):
             unit = torch.rand((k, self.RESET_NOISE_COLS), device=self.device)
         ids = env_ids.to(device=self.device, dtype=torch.long).contiguous()
         unit = unit.to(self.device, dtype=torch.float).contiguous()
+        if tuple(unit.shape) != (k, self.RESET_NOISE_COLS):      # the kernel reads RESET_NOISE_COLS floats per row
+            raise ValueError(f"unit: need shape {(k, self.RESET_NOISE_COLS)}, got {tuple(unit.shape)}")
         nat.check(self._lib.tk_gogoro_paper_reset_idx(self._handle, nat.ptr(ids), k, nat.ptr(unit), self._stream()),
                   "tk_gogoro_paper_reset_idx")
 
