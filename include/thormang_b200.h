@@ -701,6 +701,17 @@ int tk_step_noise_clamp(const float* in, int64_t count, const TkNoiseLambda* lam
 int tk_step_noise_units(int64_t count, int32_t distribution, uint64_t seed, uint64_t step, int64_t elem_offset, float* unit_out,
                         void* stream);
 
+/* env_ids = reset_buf.nonzero().squeeze(-1) cast to int32 -- the id list every reset_idx hands to
+ * gym.set_actor_root_state_tensor_indexed / gym.set_dof_state_tensor_indexed (humanoid.py:290,264-271;
+ * gogoro_new.py:377,506,547,552; anymal.py:277-283).  The fused tk_*_post_physics kernels consume AND overwrite reset_buf,
+ * so an adapter in front of a simulator that keeps its own copy of the state calls this FIRST, on the same stream: ids_out
+ * [num_envs] int32 receives the ids of the non-zero entries in ascending order (what nonzero() returns), count_out [1]
+ * int32 their number (both device memory); after the fused step it pushes exactly those rows.
+ * scratch: tk_reset_ids_scratch_bytes(num_envs) bytes of device memory owned by the caller (4 bytes per 1024 envs), reusable
+ * across calls on one stream.  No allocation, no synchronisation. */
+int64_t tk_reset_ids_scratch_bytes(int64_t num_envs);
+int tk_reset_ids(const int64_t* reset_buf, int64_t num_envs, int32_t* ids_out, int32_t* count_out, int32_t* scratch, void* stream);
+
 /* Second destination of the Humanoid / Ant obs tile: every tk_humanoid_post_physics / _compute_observations after this call
  * also stores the [N,obs] rows at obs_copy (16-byte aligned; NULL switches it off) straight from the kernel's shared-memory
  * tile -- slot t of an rl_games [horizon, N, obs] rollout buffer when clipObservations is inf and no observation noise is

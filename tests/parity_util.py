@@ -93,7 +93,7 @@ def gogoro_obs_close(got, want, what="obs", noisy=False):
 
 
 # ------------------------------------------------------------------------------------------------
-def make_humanoid_pair(n, seed=1234, device="cuda:0", state=None, asset=None, start_rotation=None, **env_over):
+def make_humanoid_pair(n, seed=1234, device="cuda:0", state=None, asset=None, start_rotation=None, sim_cls=None, **env_over):
     """(cuda task, cpu oracle, state) initialised from the same synthetic snapshot."""
     from thormang_isaacgym_b200.sim.fake_sim import FakeSim
     from thormang_isaacgym_b200.tasks.humanoid import Humanoid
@@ -102,7 +102,7 @@ def make_humanoid_pair(n, seed=1234, device="cuda:0", state=None, asset=None, st
     cfg = tcfg.humanoid_cfg(n, seed=seed)
     cfg["env"]["trackRandomizeBuf"] = True
     cfg["env"].update(env_over)
-    sim = FakeSim(n, 21, device, num_sensor_floats=12, asset=asset)
+    sim = (sim_cls or FakeSim)(n, 21, device, num_sensor_floats=12, asset=asset)
     sim.load_state(state)
     cfg["sim_backend"] = sim
     env = Humanoid(cfg, device, device, -1, True)
@@ -121,7 +121,7 @@ def make_humanoid_pair(n, seed=1234, device="cuda:0", state=None, asset=None, st
     return env, orc, state
 
 
-def make_gogoro_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
+def make_gogoro_pair(n, seed=1234, device="cuda:0", state=None, sim_cls=None, **env_over):
     from thormang_isaacgym_b200.sim.fake_sim import FakeSim
     from thormang_isaacgym_b200.tasks.gogoro_new import Gogoro
     state = state or syn.gogoro_state(n, seed=seed)
@@ -129,7 +129,7 @@ def make_gogoro_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
     cfg["env"].update(env_over)
     cfg["env"]["resetOnInit"] = False
     names = ["steering_joint", "rear_wheel_joint"] + [f"j{i}" for i in range(37)]
-    sim = FakeSim(n, 39, device, num_sensor_floats=0, dof_names=names)
+    sim = (sim_cls or FakeSim)(n, 39, device, num_sensor_floats=0, dof_names=names)
     sim.load_state(state)
     cfg["sim_backend"] = sim
     env = Gogoro(cfg, device, device, -1, True)

@@ -225,6 +225,8 @@ SYMBOLS = {
     "tk_step_noise_clamp": (C.c_int, [_p, _i64, C.POINTER(NoiseLambda), _p, _p, _u64, _u64, _i64, _f, _p, _p, _p]),
     "tk_step_noise_units": (C.c_int, [_i64, _i32, _u64, _u64, _i64, _p, _p]),
     "tk_humanoid_set_obs_copy": (C.c_int, [_p, _p]),
+    "tk_reset_ids_scratch_bytes": (_i64, [_i64]),
+    "tk_reset_ids": (C.c_int, [_p, _i64, _p, _p, _p, _p]),
 }
 
 _lib = None

@@ -129,6 +129,79 @@ static int to_lambda(const TkNoiseLambda* nl, Lambda& l) {
     return TK_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Reset id list: env_ids = reset_buf.nonzero().squeeze(-1) -> int32 (humanoid.py:290 + :264, gogoro_new.py:377 + :506),
+// ascending like nonzero().  Two small launches: per-chunk counts, then each chunk sums the counts in front of it
+// (<= 1024 ints at 1M envs) and writes its ids in order.  4 consecutive envs per thread, 1024 per block.
+// ---------------------------------------------------------------------------------------------
+constexpr int kIdsThreads = 256;
+constexpr int kIdsPerThread = 4;
+constexpr int kIdsChunk = kIdsThreads * kIdsPerThread;
+
+__device__ __forceinline__ unsigned ids_flags(const long long* __restrict__ reset, long long n, long long first) {
+    unsigned m = 0;
+#pragma unroll
+    for (int j = 0; j < kIdsPerThread; ++j)
+        if (first + j < n && reset[first + j] != 0) m |= 1u << j;
+    return m;
+}
+
+// block-wide sum of one int per thread -> every thread; red[kIdsThreads / 32 + 1] shared
+__device__ __forceinline__ int ids_block_sum(int v, int* red) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();                      // red may still be read by a previous use
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    int t = 0;
+#pragma unroll
+    for (int w = 0; w < kIdsThreads / 32; ++w) t += red[w];
+    return t;
+}
+
+__global__ void __launch_bounds__(kIdsThreads) reset_ids_count_kernel(const long long* __restrict__ reset, long long n,
+                                                                      int* __restrict__ chunk_counts) {
+    __shared__ int red[kIdsThreads / 32];
+    const long long first = (static_cast<long long>(blockIdx.x) * kIdsThreads + threadIdx.x) * kIdsPerThread;
+    const int total = ids_block_sum(__popc(ids_flags(reset, n, first)), red);
+    if (threadIdx.x == 0) chunk_counts[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(kIdsThreads) reset_ids_write_kernel(const long long* __restrict__ reset, long long n,
+                                                                      const int* __restrict__ chunk_counts, int* __restrict__ ids_out,
+                                                                      int* __restrict__ count_out) {
+    __shared__ int red[kIdsThreads / 32];
+    __shared__ int warp_excl[kIdsThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int before = 0;
+    for (int j = threadIdx.x; j < static_cast<int>(blockIdx.x); j += kIdsThreads) before += chunk_counts[j];
+    const int base = ids_block_sum(before, red);
+    const long long first = (static_cast<long long>(blockIdx.x) * kIdsThreads + threadIdx.x) * kIdsPerThread;
+    const unsigned m = ids_flags(reset, n, first);
+    const int c = __popc(m);
+    int incl = c;                          // inclusive scan inside the warp
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += y;
+    }
+    __syncthreads();
+    if (lane == 31) red[warp] = incl;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int run = 0;
+#pragma unroll
+        for (int w = 0; w < kIdsThreads / 32; ++w) { warp_excl[w] = run; run += red[w]; }
+        if (blockIdx.x == gridDim.x - 1) *count_out = base + run;
+    }
+    __syncthreads();
+    int at = base + warp_excl[warp] + incl - c;
+#pragma unroll
+    for (int j = 0; j < kIdsPerThread; ++j)
+        if (m & (1u << j)) ids_out[at++] = static_cast<int>(first + j);
+}
+
 extern "C" {
 
 int tk_step_noise_clamp(const float* in, int64_t count, const TkNoiseLambda* lambda, const float* corr, const float* unit,
@@ -160,6 +233,25 @@ int tk_step_noise_units(int64_t count, int32_t distribution, uint64_t seed, uint
     const long long threads = (count + 3) / 4;
     philox_unit_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
         count, distribution, seed, step, zero_epoch, elem_offset, unit_out);
+    TK_CUDA(cudaGetLastError());
+    return TK_OK;
+}
+
+int64_t tk_reset_ids_scratch_bytes(int64_t num_envs) {
+    if (num_envs <= 0) return 0;
+    return static_cast<int64_t>(sizeof(int)) * ((num_envs + kIdsChunk - 1) / kIdsChunk);
+}
+
+int tk_reset_ids(const int64_t* reset_buf, int64_t num_envs, int32_t* ids_out, int32_t* count_out, int32_t* scratch, void* stream) {
+    TK_REQUIRE(reset_buf && ids_out && count_out && scratch, TK_ERR_INVALID, "null argument");
+    TK_REQUIRE(num_envs > 0 && num_envs <= 2147483647ll, TK_ERR_INVALID, "num_envs %lld does not fit int32 env ids", static_cast<long long>(num_envs));
+    TK_REQUIRE(aligned_to(reset_buf, 8) && aligned_to(ids_out, 4) && aligned_to(count_out, 4) && aligned_to(scratch, 4), TK_ERR_ALIGN,
+               "reset_buf must be 8-byte, the int32 arrays 4-byte aligned");
+    const unsigned chunks = static_cast<unsigned>((num_envs + kIdsChunk - 1) / kIdsChunk);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const long long* reset = reinterpret_cast<const long long*>(reset_buf);
+    reset_ids_count_kernel<<<chunks, kIdsThreads, 0, st>>>(reset, num_envs, scratch);
+    reset_ids_write_kernel<<<chunks, kIdsThreads, 0, st>>>(reset, num_envs, scratch, ids_out, count_out);
     TK_CUDA(cudaGetLastError());
     return TK_OK;
 }

@@ -23,6 +23,11 @@ import torch
 
 
 class FakeSim:
+    # The task's tensors ARE this simulator's state: resets written by the kernels need no push and nothing has to be
+    # refreshed.  A backend without this attribute (or with False) is treated as keeping its own state: the tasks then call
+    # refresh_* in front of the fused step and set_*_indexed with the reset id list behind it (sim/detached_sim.py).
+    aliases_task_memory = True
+
     def __init__(self, num_envs: int, num_dof: int, device, num_sensor_floats: int = 12,
                  dof_names: Optional[List[str]] = None, asset: Optional[Dict[str, torch.Tensor]] = None,
                  physics: Optional[Callable[["FakeSim"], None]] = None, slab: bool = False, num_bodies: int = 0,

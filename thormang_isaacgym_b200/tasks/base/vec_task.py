@@ -147,6 +147,38 @@ class VecTask(Env):
     @abc.abstractmethod
     def post_physics_step(self): ...
 
+    # ---- reset hand-off to a simulator that keeps its own state -----------------------------------------
+    # The reference's reset_idx passes env_ids_int32 to gym.set_actor_root_state_tensor_indexed / set_dof_state_tensor_indexed
+    # (humanoid.py:264-271, gogoro_new.py:547,552).  The fused kernels reset rows of the task's tensors and overwrite
+    # reset_buf, so the id list is taken (tk_reset_ids) BEFORE the fused step and the rows are pushed behind it.  A backend
+    # that shares memory with the task (FakeSim.aliases_task_memory) needs neither, and pays nothing.
+    def _sim_detached(self) -> bool:
+        d = getattr(self, "_detached", None)
+        if d is None:
+            d = self._detached = not getattr(self.sim, "aliases_task_memory", False)
+        return d
+
+    def _collect_reset_ids(self, stream=None):
+        """Enqueue env_ids = reset_buf.nonzero() -> int32 on the task's stream (no sync)."""
+        from ... import _native as nat
+        if getattr(self, "_reset_ids", None) is None:
+            n, dev = self.num_envs, self.device
+            lib = nat.lib()
+            self._reset_ids = torch.empty(n, device=dev, dtype=torch.int32)
+            self._reset_count = torch.zeros(1, device=dev, dtype=torch.int32)
+            self._reset_scratch = torch.empty(max(1, lib.tk_reset_ids_scratch_bytes(n) // 4), device=dev, dtype=torch.int32)
+            self._reset_ids_fn = lib.tk_reset_ids
+        if stream is None:
+            stream = nat.current_stream_ptr(torch.device(self.device))
+        nat.check(self._reset_ids_fn(nat.ptr(self.reset_buf), self.num_envs, nat.ptr(self._reset_ids), nat.ptr(self._reset_count),
+                                     nat.ptr(self._reset_scratch), stream), "tk_reset_ids")
+
+    def _collected_reset_ids(self) -> Optional[torch.Tensor]:
+        """The id list of the last _collect_reset_ids (int32, ascending) or None when it is empty.  Reads the count back:
+        the same host synchronisation the reference's nonzero() + len(env_ids) makes (humanoid.py:290-291)."""
+        k = int(self._reset_count.item())
+        return self._reset_ids[:k] if k > 0 else None
+
     # ---- step prologue / epilogue as one fused kernel each (SURVEY 8(f) N4) -----------------------------------------
     def _noise_clamp(self, tensor, which, clip, noisy_out, clamped_out, unit=None):
         """``clamp(noise_lambda(tensor), +-clip)`` of vec_task.py:323-327 / :347-353 in ONE pass (csrc/tk_epilogue.cu).

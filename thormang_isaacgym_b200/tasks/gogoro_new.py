@@ -215,6 +215,14 @@ class Gogoro(VecTask):
         o = (self.buffer_obs[:, -1] if cur_obs is None else cur_obs).contiguous()
         nat.check(self._lib.tk_gogoro_compute_reward(self._handle, nat.ptr(o), self._stream()), "tk_gogoro_compute_reward")
 
+    def _push_resets(self, ids_int32):
+        """gogoro_new.py:547,552: the reset rows reach a simulator that keeps its own state only through these two calls
+        (the reference asserts both)."""
+        if ids_int32 is None:
+            return
+        assert self.sim.set_actor_root_state_tensor_indexed(self.root_tensor, ids_int32)
+        assert self.sim.set_dof_state_tensor_indexed(self.state_dof, ids_int32)
+
     def compute_obs_rwd(self, sensor_unit: Optional[torch.Tensor] = None):
         """gogoro_new.py:424-462.  ``sensor_unit`` [N,5]: the five N(0,1) draws of :451-460 in draw order."""
         self.sim.refresh_actor_root_state_tensor()
@@ -238,11 +246,23 @@ class Gogoro(VecTask):
         ids = env_ids.to(device=self.device, dtype=torch.long).contiguous()
         nat.check(self._lib.tk_gogoro_reset_idx(self._handle, nat.ptr(ids), k, nat.ptr(unit.contiguous()), self._stream()),
                   "tk_gogoro_reset_idx")
+        if self._sim_detached():
+            self._push_resets(ids.to(torch.int32))                                # gogoro_new.py:506
 
     def post_physics_step(self, sensor_unit: Optional[torch.Tensor] = None, reset_unit: Optional[torch.Tensor] = None,
                           speed_unit: Optional[torch.Tensor] = None, yaw_unit: Optional[torch.Tensor] = None,
                           noise_mode: Optional[int] = None):
         """gogoro_new.py:373-389 + vec_task.py:345 as one fused kernel (Philox noise unless the draws are supplied)."""
+        if self._sim_detached():                # a simulator with its own state (sim/detached_sim.py, PhysX)
+            self.sim.refresh_actor_root_state_tensor()                            # gogoro_new.py:425-426
+            self.sim.refresh_dof_state_tensor()
+            self._collect_reset_ids()                                             # :377 -- the fused kernel consumes reset_buf
+            self._post_physics_fused(sensor_unit, reset_unit, speed_unit, yaw_unit, noise_mode)
+            self._push_resets(self._collected_reset_ids())
+            return
+        self._post_physics_fused(sensor_unit, reset_unit, speed_unit, yaw_unit, noise_mode)
+
+    def _post_physics_fused(self, sensor_unit, reset_unit, speed_unit, yaw_unit, noise_mode):
         supplied = sensor_unit is not None or reset_unit is not None
         if not supplied and noise_mode is None and speed_unit is None and yaw_unit is None:
             # production path: in-kernel Philox, nothing allocated per step

@@ -224,13 +224,24 @@ class Humanoid(VecTask):
                   "tk_humanoid_pre_physics")
         self.sim.set_dof_actuation_force_tensor(self.forces)
 
-    def compute_observations(self):
-        """humanoid.py:239-251."""
+    def _refresh_sim_tensors(self):
+        """humanoid.py:240-243."""
         self.sim.refresh_dof_state_tensor()
         self.sim.refresh_actor_root_state_tensor()
         self.sim.refresh_force_sensor_tensor()
         if self._HAS_DOF_FORCE:
             self.sim.refresh_dof_force_tensor()
+
+    def _push_resets(self, ids_int32):
+        """humanoid.py:264-271: the reset rows reach a simulator that keeps its own state only through these two calls."""
+        if ids_int32 is None:
+            return
+        self.sim.set_actor_root_state_tensor_indexed(self.initial_root_states, ids_int32)
+        self.sim.set_dof_state_tensor_indexed(self.dof_state, ids_int32)
+
+    def compute_observations(self):
+        """humanoid.py:239-251."""
+        self._refresh_sim_tensors()
         nat.check(self._lib.tk_humanoid_compute_observations(self._handle, self._stream()),
                   "tk_humanoid_compute_observations")
 
@@ -252,10 +263,16 @@ class Humanoid(VecTask):
         nat.check(self._lib.tk_humanoid_reset_idx(self._handle, nat.ptr(ids), k, nat.ptr(unit_pos.contiguous()),
                                                   nat.ptr(unit_vel.contiguous()), self._stream()),
                   "tk_humanoid_reset_idx")
+        if self._sim_detached():
+            self._push_resets(ids.to(torch.int32))                                # humanoid.py:264
 
     def post_physics_step(self, unit_pos: Optional[torch.Tensor] = None, unit_vel: Optional[torch.Tensor] = None,
                           noise_mode: Optional[int] = None):
         """humanoid.py:287-296 + vec_task.py:345 as one fused kernel."""
+        detached = self._sim_detached()
+        if detached:                            # a simulator with its own state: fetch it, and note who is about to be reset
+            self._refresh_sim_tensors()
+            self._collect_reset_ids()           # humanoid.py:290 -- the fused kernel consumes reset_buf
         noise = self._noise                     # one struct per task object: nothing is allocated per step
         if unit_pos is None and noise_mode is None:
             if not self._noise_is_philox:       # the default path touches only what changes from step to step
@@ -275,6 +292,8 @@ class Humanoid(VecTask):
         if rc:
             nat.check(rc, "tk_humanoid_post_physics")
         self.step_count += 1
+        if detached:
+            self._push_resets(self._collected_reset_ids())
 
     # ------------------------------------------------------------------------------------------
     def reward_terms(self) -> torch.Tensor:
