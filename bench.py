@@ -238,7 +238,7 @@ def cpu_config1(n=4096, warmup=5, reps=50):
                             asset["motor_efforts"], jit=True)
     orc.actions, orc.progress_buf, orc.reset_buf, orc.potentials = st["actions"], st["progress_buf"], st["reset_buf"], st["potentials"]
     out = {"envs": n, "what": "compute_observations + compute_reward (no reset), CPU torch " + torch.__version__,
-           "kind": "port (oracle/, pinned bit-for-bit to the reference's JIT functions)", "warmup": warmup, "reps": reps,
+           "kind": "port (oracle/, pinned bit-for-bit to the reference's JIT functions; the isaacgym.torch_utils helpers under them are an un-vendored dependency restated in oracle/isaac_helpers.py: parity unpinned there)", "warmup": warmup, "reps": reps,
            "torch": torch.__version__, "parallel_info": torch.__config__.parallel_info().strip().splitlines()[:8]}
     before = torch.get_num_threads()
     for label, threads in (("all_threads", os.cpu_count() or 1), ("single_thread", 1)):

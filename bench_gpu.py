@@ -668,7 +668,7 @@ def run_gpu_arm(args, rank, world):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": B.recorded_traffic(task)[0], "traffic_note": B.recorded_traffic(task)[1],
                      "peak_source": peak_src,
-                     "kernel": "humanoid_warp_kernel<21,true>" if task == "humanoid" else "gogoro_tile_kernel<0>",
+                     "kernel": "humanoid_warp_kernel<Spec<21,12,1,0>,true>" if task == "humanoid" else "gogoro_tile_kernel<0>",
                      "algorithmic_bytes_per_env_step": bpe,
                      "how": "algorithmic bytes x envs per launch / (CUDA-event time of the timed region / launches), rank 0",
                      "not_counted": "the launch also writes up_vec / heading_vec (24 B per env: SURVEY 8(a) H2 '+24 B if written'; the "

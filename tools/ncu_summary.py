@@ -77,10 +77,13 @@ def launches_summary(path):
     rows = [r for r in csv.reader(open(path)) if len(r) > 5]
     hdr = rows[0]
     ki, mi, vi, ii = hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Value"), hdr.index("ID")
+    gi = hdr.index("Grid Size") if "Grid Size" in hdr else None
     per = defaultdict(dict)
     for r in rows[1:]:
         try:
-            per[(r[ii], r[ki][:100])][r[mi]] = float(r[vi].replace(",", ""))
+            # one row per (kernel, grid): a bench run launches the same kernel at several sizes (headline, extras, e2e chunks)
+            name = r[ki][:100] + (" grid=" + r[gi].replace(" ", "") if gi is not None else "")
+            per[(r[ii], name)][r[mi]] = float(r[vi].replace(",", ""))
         except ValueError:
             pass
     agg = defaultdict(lambda: defaultdict(list))
