@@ -201,7 +201,7 @@ def gogoro_paper_frame_close(got, want, what="frame", noisy=False):
                     bound=None)      # noise + offsets added after the wrap (:525-538): open range
 
 
-def make_gogoro_paper_pair(n, seed=1234, device="cuda:0", state=None, turning=False, **env_over):
+def make_gogoro_paper_pair(n, seed=1234, device="cuda:0", state=None, turning=False, sim_cls=None, **env_over):
     """(cuda task, cpu oracle, state) of the 8x20 Gogoro variant from one synthetic snapshot (SURVEY 8f N1);
     ``turning``: the gogoro_realistic_turning.py sibling (task ``GogoroTurning``, oracle ``GogoroTurningOracle``)."""
     from oracle import gogoro_paper_oracle as gp
@@ -217,7 +217,7 @@ def make_gogoro_paper_pair(n, seed=1234, device="cuda:0", state=None, turning=Fa
     cfg["env"].update(env_over)
     cfg["env"]["resetOnInit"] = False
     names = ["steering_joint", "rear_wheel_joint"] + [f"j{i}" for i in range(37)]
-    sim = FakeSim(n, 39, device, num_sensor_floats=0, dof_names=names)
+    sim = (sim_cls or FakeSim)(n, 39, device, num_sensor_floats=0, dof_names=names)
     sim.load_state(state)
     cfg["sim_backend"] = sim
     env = GogoroPaper(cfg, device, device, -1, True)
@@ -238,7 +238,7 @@ def make_gogoro_paper_pair(n, seed=1234, device="cuda:0", state=None, turning=Fa
     return env, orc, state
 
 
-def make_anymal_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
+def make_anymal_pair(n, seed=1234, device="cuda:0", state=None, sim_cls=None, **env_over):
     """(cuda Anymal task, cpu AnymalOracle, state) from one synthetic snapshot."""
     from oracle import anymal_oracle as ao
     from thormang_isaacgym_b200.sim.fake_sim import FakeSim
@@ -247,7 +247,7 @@ def make_anymal_pair(n, seed=1234, device="cuda:0", state=None, **env_over):
     cfg = tcfg.anymal_cfg(n, seed=seed)
     cfg["env"].update(env_over)
     cfg["env"]["resetOnInit"] = False
-    sim = FakeSim(n, 12, device, num_sensor_floats=0, dof_names=list(tcfg.ANYMAL_DOF_NAMES), num_bodies=13)
+    sim = (sim_cls or FakeSim)(n, 12, device, num_sensor_floats=0, dof_names=list(tcfg.ANYMAL_DOF_NAMES), num_bodies=13)
     sim.load_state(state)
     cfg["sim_backend"] = sim
     env = Anymal(cfg, device, device, -1, True)

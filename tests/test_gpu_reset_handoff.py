@@ -142,3 +142,45 @@ def test_gogoro_on_a_detached_simulator_equals_the_aliasing_run():
             assert torch.equal(env_d.sim.pushed_ids["root"], want_ids) and torch.equal(env_d.sim.pushed_ids["dof"], want_ids)
     assert total_resets > 0
     assert env_d.sim.calls["refresh_root_states"] == horizon
+
+
+def _twin_rollout(env_a, env_d, act_dim, horizon, names, root_name, dof_name, seed):
+    g = torch.Generator().manual_seed(seed)
+    n, total = env_a.num_envs, 0
+    for env in (env_a, env_d):
+        env.sim.physics = lambda s: _physics(s.root_states, s.dof_state, None)
+    for t in range(horizon):
+        a = (torch.rand(n, act_dim, generator=g) * 2 - 1).to(DEV)
+        want_ids = env_a.reset_buf.nonzero(as_tuple=False).flatten().to(torch.int32)
+        for env in (env_a, env_d):
+            env.pre_physics_step(a)
+            env.sim.simulate()
+            env.post_physics_step()
+        torch.cuda.synchronize()
+        for name in names + (root_name, dof_name):
+            U.exact(getattr(env_d, name), getattr(env_a, name), f"t={t} {name}")
+        U.exact(env_d.sim.private.root_states, env_a.sim.root_states, f"t={t} simulator-side root state")
+        U.exact(env_d.sim.private.dof_state, env_a.sim.dof_state, f"t={t} simulator-side dof state")
+        if want_ids.numel():
+            total += want_ids.numel()
+            assert torch.equal(env_d.sim.pushed_ids["root"], want_ids) and torch.equal(env_d.sim.pushed_ids["dof"], want_ids)
+    assert total > 0, "the rollout must contain resets"
+    assert env_d.sim.calls["refresh_root_states"] == horizon and env_d.sim.calls["refresh_dof_state"] == horizon
+
+
+def test_anymal_on_a_detached_simulator_equals_the_aliasing_run():
+    n = 900
+    env_a, _, st = U.make_anymal_pair(n, seed=51)
+    env_d, _, _ = U.make_anymal_pair(n, seed=51, state={k: v.clone() for k, v in st.items()}, sim_cls=DetachedSim)
+    _twin_rollout(env_a, env_d, 12, 6, ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "commands"), "root_states", "dof_state", 6)
+    assert env_d.sim.calls["refresh_net_contact_force"] == 6
+
+
+@pytest.mark.parametrize("turning", [False, True], ids=["paper", "turning"])
+def test_gogoro_8x20_on_a_detached_simulator_equals_the_aliasing_run(turning):
+    n = 700
+    env_a, _, st = U.make_gogoro_paper_pair(n, seed=61, turning=turning)
+    env_d, _, _ = U.make_gogoro_paper_pair(n, seed=61, state={k: v.clone() for k, v in st.items()}, turning=turning,
+                                           sim_cls=DetachedSim)
+    _twin_rollout(env_a, env_d, 1, 6, ("obs_buf", "rew_buf", "reset_buf", "progress_buf", "command_ring", "yaw_command"),
+                  "root_tensor", "state_dof", 7)

@@ -173,11 +173,22 @@ class Anymal(VecTask):
                                                   1 if self._clip_in_kernel else 0, self._stream()), "tk_anymal_pre_physics")
         self.sim.set_dof_position_target_tensor(self.targets)
 
-    def compute_observations(self):
-        """:262-283."""
+    def _refresh_sim_tensors(self):
+        """:263-266."""
         for f in ("refresh_dof_state_tensor", "refresh_actor_root_state_tensor", "refresh_net_contact_force_tensor",
                   "refresh_dof_force_tensor"):
             getattr(self.sim, f)()
+
+    def _push_resets(self, ids_int32):
+        """anymal.py:302-308: the reset rows reach a simulator that keeps its own state only through these two calls."""
+        if ids_int32 is None:
+            return
+        self.sim.set_actor_root_state_tensor_indexed(self.initial_root_states, ids_int32)
+        self.sim.set_dof_state_tensor_indexed(self.dof_state, ids_int32)
+
+    def compute_observations(self):
+        """:262-283."""
+        self._refresh_sim_tensors()
         nat.check(self._lib.tk_anymal_compute_observations(self._handle, self._stream()), "tk_anymal_compute_observations")
 
     def compute_reward(self, actions=None):
@@ -197,11 +208,17 @@ class Anymal(VecTask):
         ids = env_ids.to(device=dev, dtype=torch.long).contiguous()
         nat.check(self._lib.tk_anymal_reset_idx(self._handle, nat.ptr(ids), k, nat.ptr(unit_pos), nat.ptr(unit_vel),
                                                 nat.ptr(unit_cmd), self._stream()), "tk_anymal_reset_idx")
+        if self._sim_detached():
+            self._push_resets(ids.to(torch.int32))                                # anymal.py:301
 
     def post_physics_step(self, unit_pos: Optional[torch.Tensor] = None, unit_vel: Optional[torch.Tensor] = None,
                           unit_cmd: Optional[torch.Tensor] = None):
         """:234-242 + vec_task.py:345 as one fused kernel.  Supplied draws are addressed by env id ([N, ...]);
         in-kernel Philox noise when none is given."""
+        detached = self._sim_detached()
+        if detached:                            # a simulator with its own state (sim/detached_sim.py, PhysX)
+            self._refresh_sim_tensors()
+            self._collect_reset_ids()           # anymal.py:238 -- the fused kernel consumes reset_buf
         stream = nat.current_stream_ptr(self._torch_device)
         if unit_pos is None and unit_vel is None and unit_cmd is None:
             nz = self._philox_noise
@@ -223,6 +240,8 @@ class Anymal(VecTask):
         if rc:
             nat.check(rc, "tk_anymal_post_physics")
         self.step_count += 1
+        if detached:
+            self._push_resets(self._collected_reset_ids())
 
     def philox_noise(self, step: Optional[int] = None):
         n, dev = self.num_envs, self.device

@@ -305,12 +305,27 @@ class Gogoro(VecTask):
             raise ValueError(f"unit: need shape {(k, self.RESET_NOISE_COLS)}, got {tuple(unit.shape)}")
         nat.check(self._lib.tk_gogoro_paper_reset_idx(self._handle, nat.ptr(ids), k, nat.ptr(unit), self._stream()),
                   "tk_gogoro_paper_reset_idx")
+        if self._sim_detached():
+            self._push_resets(ids.to(torch.int32))                                # :604
+
+    def _push_resets(self, ids_int32):
+        """:645,650 (gogoro_realistic_turning.py:643,648): the reset rows reach a simulator that keeps its own state only
+        through these two calls (the reference asserts both)."""
+        if ids_int32 is None:
+            return
+        assert self.sim.set_actor_root_state_tensor_indexed(self.root_tensor, ids_int32)
+        assert self.sim.set_dof_state_tensor_indexed(self.state_dof, ids_int32)
 
     def post_physics_step(self, sensor_unit: Optional[torch.Tensor] = None, reset_unit: Optional[torch.Tensor] = None,
                           speed_unit: Optional[torch.Tensor] = None, yaw_unit: Optional[torch.Tensor] = None):
         """:382-412 + vec_task.py:345: the fused kernel and the finalize kernel.  Supplied draws are addressed by
         env id ([N, ...] tensors); in-kernel Philox noise when none is given."""
         keep = []
+        detached = self._sim_detached()
+        if detached:                            # a simulator with its own state (sim/detached_sim.py, PhysX)
+            self.sim.refresh_actor_root_state_tensor()                            # :491-492
+            self.sim.refresh_dof_state_tensor()
+            self._collect_reset_ids()                                             # :386 -- the fused kernel consumes reset_buf
         nz = self._noise(sensor_unit, reset_unit, speed_unit, yaw_unit, keep)
         stream = nat.current_stream_ptr(self._torch_device)
         rc = self._post_physics(self._handle, nz, stream)
@@ -319,6 +334,8 @@ class Gogoro(VecTask):
         self._finalize(stream)
         self.step_count += 1
         self.curent_step += 1
+        if detached:
+            self._push_resets(self._collected_reset_ids())
 
     def philox_noise(self, step: Optional[int] = None):
         """Materialise the in-kernel draws of ``step``: dict(sensor_unit, reset_unit, speed_unit, yaw_unit)."""
